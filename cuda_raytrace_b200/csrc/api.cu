@@ -1,0 +1,303 @@
+// The extern "C" surface declared in include/b2rt.h.  Host-side only: argument checks, scene
+// staging, buffer management; every compute step is a kernel in sort.cu / build.cu / trace.cu.
+// There is deliberately no CPU path: without a usable CUDA device b2rt_create fails.
+#include "b2rt_internal.cuh"
+#include <string.h>
+#include <math.h>
+
+static std::string g_create_error;
+
+static int invert34(const float m[12], float out[12]) {
+    // general 3x4 affine inverse in double
+    double a = m[0], b = m[1], c = m[2], d = m[4], e = m[5], f = m[6], g = m[8], h = m[9], i = m[10];
+    double det = a * (e * i - f * h) - b * (d * i - f * g) + c * (d * h - e * g);
+    if (det == 0.0) return -1;
+    double id = 1.0 / det;
+    double r[9] = {(e * i - f * h) * id, (c * h - b * i) * id, (b * f - c * e) * id,
+                   (f * g - d * i) * id, (a * i - c * g) * id, (c * d - a * f) * id,
+                   (d * h - e * g) * id, (b * g - a * h) * id, (a * e - b * d) * id};
+    for (int row = 0; row < 3; ++row) {
+        for (int col = 0; col < 3; ++col) out[4 * row + col] = (float)r[3 * row + col];
+        out[4 * row + 3] = (float)-(r[3 * row] * m[3] + r[3 * row + 1] * m[7] + r[3 * row + 2] * m[11]);
+    }
+    return 0;
+}
+
+extern "C" {
+
+int b2rt_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+int b2rt_create(int device, uint64_t seed, b2rt_ctx **out) {
+    if (!out) return B2RT_E_ARG;
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) {
+        g_create_error = std::string("b2rt_create: no CUDA device (") + cudaGetErrorString(e) +
+                         "); this library has no CPU fallback";
+        cudaGetLastError();
+        return B2RT_E_CUDA;
+    }
+    if (device < 0 || device >= n) { g_create_error = "b2rt_create: bad device index"; return B2RT_E_ARG; }
+    b2rt_ctx *ctx = new b2rt_ctx();
+    ctx->device = device; ctx->seed = seed;
+#define CK(call) if ((e = (call)) != cudaSuccess) { g_create_error = std::string(#call) + ": " + cudaGetErrorString(e); delete ctx; return B2RT_E_CUDA; }
+    CK(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10) {
+        g_create_error = "b2rt_create: device is not sm_100-class (kernels are built for sm_100a only)";
+        delete ctx; return B2RT_E_CUDA;
+    }
+    ctx->sm_count = prop.multiProcessorCount;
+    CK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    CK(cudaEventCreate(&ctx->ev0)); CK(cudaEventCreate(&ctx->ev1));
+    CK(cudaEventCreate(&ctx->evb0)); CK(cudaEventCreate(&ctx->evb1));
+    CK(ctx->d_counters.reserve(64));
+    CK(cudaMemsetAsync(ctx->d_counters.p, 0, 64, ctx->stream));
+#undef CK
+    *out = ctx;
+    return B2RT_OK;
+}
+
+void b2rt_destroy(b2rt_ctx *ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    DevBuf *bufs[] = {&ctx->d_verts, &ctx->d_idx, &ctx->d_analytic, &ctx->d_prim_kind, &ctx->d_leaf_box,
+                      &ctx->d_scene_box, &ctx->d_keys, &ctx->d_vals, &ctx->d_keys_alt, &ctx->d_vals_alt,
+                      &ctx->d_hist, &ctx->d_bin_parent, &ctx->d_bin_child, &ctx->d_bin_box, &ctx->d_bin_flag,
+                      &ctx->d_bin_cost, &ctx->d_bin_count, &ctx->d_wide_tmp, &ctx->d_wide_flag,
+                      &ctx->d_wide_index, &ctx->d_queue_a, &ctx->d_queue_b, &ctx->d_counters,
+                      &ctx->d_wide_nodes, &ctx->d_prim_recs, &ctx->d_leaf_prims, &ctx->d_rays, &ctx->d_hits,
+                      &ctx->d_occ, &ctx->d_scan_tmp};
+    for (DevBuf *b : bufs) b->release();
+    cudaEventDestroy(ctx->ev0); cudaEventDestroy(ctx->ev1);
+    cudaEventDestroy(ctx->evb0); cudaEventDestroy(ctx->evb1);
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+const char *b2rt_last_error(b2rt_ctx *ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+int b2rt_clear_scene(b2rt_ctx *ctx) {
+    if (!ctx) return B2RT_E_ARG;
+    ctx->h_verts.clear(); ctx->h_idx.clear(); ctx->h_tri_prim.clear(); ctx->h_analytic.clear();
+    ctx->h_analytic_prim.clear(); ctx->h_analytic_type.clear(); ctx->h_prim_material.clear();
+    ctx->h_prim_light.clear(); ctx->h_materials.clear(); ctx->h_lights.clear();
+    ctx->n_prims = 0; ctx->built = false;
+    return B2RT_OK;
+}
+
+int b2rt_add_mesh(b2rt_ctx *ctx, int32_t nverts, const float *P, int32_t ntris, const int32_t *idx,
+                  const float *N, const float *uv, int32_t material_id, int32_t arealight_id,
+                  int32_t *first_prim) {
+    if (!ctx) return B2RT_E_ARG;
+    if (nverts < 0 || ntris < 0 || (nverts && !P) || (ntris && !idx)) { ctx->err = "add_mesh: bad sizes/pointers"; return B2RT_E_ARG; }
+    if ((int64_t)ctx->n_prims + ntris >= (1ll << 28)) { ctx->err = "add_mesh: more than 2^28 primitives"; return B2RT_E_ARG; }
+    for (int64_t k = 0; k < 3ll * ntris; ++k)
+        if (idx[k] < 0 || idx[k] >= nverts) { ctx->err = "add_mesh: vertex index out of range"; return B2RT_E_ARG; }
+    (void)N; (void)uv;  // shading attributes: consumed by the shade stage (not by traversal)
+    int32_t vbase = (int32_t)(ctx->h_verts.size() / 3);
+    ctx->h_verts.insert(ctx->h_verts.end(), P, P + 3ll * nverts);
+    size_t ib = ctx->h_idx.size();
+    ctx->h_idx.resize(ib + 3ll * ntris);
+    for (int64_t k = 0; k < 3ll * ntris; ++k) ctx->h_idx[ib + k] = idx[k] + vbase;
+    if (first_prim) *first_prim = ctx->n_prims;
+    for (int32_t t = 0; t < ntris; ++t) {
+        ctx->h_tri_prim.push_back(ctx->n_prims++);
+        ctx->h_prim_material.push_back(material_id);
+        ctx->h_prim_light.push_back(arealight_id);
+    }
+    ctx->built = false;
+    return B2RT_OK;
+}
+
+static int add_analytic(b2rt_ctx *ctx, int type, const float o2w[12], const float *w2o, float radius,
+                        float height, float inner, int32_t material_id, int32_t arealight_id, int32_t *prim) {
+    if (!ctx) return B2RT_E_ARG;
+    if (!o2w || !(radius > 0.f)) { ctx->err = "add_sphere/disk: bad arguments"; return B2RT_E_ARG; }
+    AnalyticPrim a;
+    memcpy(a.o2w, o2w, sizeof(a.o2w));
+    if (w2o) memcpy(a.w2o, w2o, sizeof(a.w2o));
+    else if (invert34(o2w, a.w2o)) { ctx->err = "add_sphere/disk: singular transform"; return B2RT_E_ARG; }
+    a.radius = radius; a.height = height; a.inner = inner; a.pad = 0.f;
+    ctx->h_analytic.push_back(a);
+    ctx->h_analytic_type.push_back(type);
+    if (prim) *prim = ctx->n_prims;
+    ctx->h_analytic_prim.push_back(ctx->n_prims++);
+    ctx->h_prim_material.push_back(material_id);
+    ctx->h_prim_light.push_back(arealight_id);
+    ctx->built = false;
+    return B2RT_OK;
+}
+
+int b2rt_add_sphere(b2rt_ctx *ctx, const float o2w[12], const float *w2o, float radius, int32_t material_id,
+                    int32_t arealight_id, int32_t *prim) {
+    return add_analytic(ctx, B2RT_PRIM_SPHERE, o2w, w2o, radius, 0.f, 0.f, material_id, arealight_id, prim);
+}
+
+int b2rt_add_disk(b2rt_ctx *ctx, const float o2w[12], const float *w2o, float height, float radius,
+                  float inner_radius, int32_t material_id, int32_t arealight_id, int32_t *prim) {
+    return add_analytic(ctx, B2RT_PRIM_DISK, o2w, w2o, radius, height, inner_radius, material_id, arealight_id,
+                        prim);
+}
+
+int b2rt_add_material(b2rt_ctx *ctx, int32_t type, const float rgb[3], const float rgb_kt[3], float ior,
+                      int32_t *material_id) {
+    if (!ctx) return B2RT_E_ARG;
+    if (type < B2RT_MAT_MATTE || type > B2RT_MAT_GLASS || !rgb) { ctx->err = "add_material: bad arguments"; return B2RT_E_ARG; }
+    Material m;
+    m.type = type; memcpy(m.kd, rgb, 12);
+    if (rgb_kt) memcpy(m.kt, rgb_kt, 12); else m.kt[0] = m.kt[1] = m.kt[2] = 1.f;
+    m.ior = ior;
+    if (material_id) *material_id = (int32_t)ctx->h_materials.size();
+    ctx->h_materials.push_back(m);
+    return B2RT_OK;
+}
+
+int b2rt_add_light(b2rt_ctx *ctx, int32_t type, const float p[3], const float rgb[3], int32_t prim,
+                   int32_t nsamples, int32_t *light_id) {
+    if (!ctx) return B2RT_E_ARG;
+    if (type < B2RT_LIGHT_POINT || type > B2RT_LIGHT_DISK_AREA || !rgb) { ctx->err = "add_light: bad arguments"; return B2RT_E_ARG; }
+    Light l;
+    l.type = type;
+    if (p) memcpy(l.p, p, 12); else l.p[0] = l.p[1] = l.p[2] = 0.f;
+    memcpy(l.rgb, rgb, 12);
+    l.prim = prim; l.nsamples = nsamples > 0 ? nsamples : 1;
+    if (light_id) *light_id = (int32_t)ctx->h_lights.size();
+    ctx->h_lights.push_back(l);
+    return B2RT_OK;
+}
+
+int b2rt_build_accel(b2rt_ctx *ctx) {
+    if (!ctx) return B2RT_E_ARG;
+    B2RT_CUDA(ctx, cudaSetDevice(ctx->device));
+    return b2rt_build_impl(ctx);
+}
+
+int b2rt_accel_info_get(b2rt_ctx *ctx, b2rt_accel_info *info) {
+    if (!ctx || !info) return B2RT_E_ARG;
+    if (!ctx->built) { ctx->err = "accel_info: no acceleration structure built"; return B2RT_E_STATE; }
+    *info = ctx->info;
+    return B2RT_OK;
+}
+
+int b2rt_accel_download(b2rt_ctx *ctx, uint32_t *morton, int32_t *prim_order, int32_t *bin_parent,
+                        int32_t *bin_child, float *bin_box, uint32_t *wide_nodes, int32_t *leaf_prims) {
+    if (!ctx) return B2RT_E_ARG;
+    if (!ctx->built) { ctx->err = "accel_download: no acceleration structure built"; return B2RT_E_STATE; }
+    const int64_t n = ctx->n_prims;
+    cudaStream_t st = ctx->stream;
+    auto dn = [&](void *dst, const DevBuf &src, size_t bytes) -> cudaError_t {
+        if (!dst || !bytes) return cudaSuccess;
+        return cudaMemcpyAsync(dst, src.p, bytes, cudaMemcpyDeviceToHost, st);
+    };
+    B2RT_CUDA(ctx, dn(morton, ctx->d_keys, n * 4));
+    B2RT_CUDA(ctx, dn(prim_order, ctx->d_vals, n * 4));
+    if (n >= 1) {
+        B2RT_CUDA(ctx, dn(bin_parent, ctx->d_bin_parent, (2 * n - 1) * 4));
+        B2RT_CUDA(ctx, dn(bin_child, ctx->d_bin_child, 2 * (n - 1) * 4));
+        B2RT_CUDA(ctx, dn(bin_box, ctx->d_bin_box, (2 * n - 1) * 24));
+    }
+    B2RT_CUDA(ctx, dn(wide_nodes, ctx->d_wide_nodes, (size_t)ctx->info.n_wide_nodes * 128));
+    B2RT_CUDA(ctx, dn(leaf_prims, ctx->d_leaf_prims, n * 4));
+    B2RT_CUDA(ctx, cudaStreamSynchronize(st));
+    return B2RT_OK;
+}
+
+static int check_status(b2rt_ctx *ctx) {
+    uint32_t s = 0;
+    B2RT_CUDA(ctx, cudaMemcpyAsync(&s, ctx->d_counters.as<uint32_t>() + 8, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    B2RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (s) {
+        cudaMemsetAsync(ctx->d_counters.as<uint32_t>() + 8, 0, 4, ctx->stream);
+        ctx->err = "traversal stack overflow on " + std::to_string(s) + " rays";
+        return B2RT_E_OVERFLOW;
+    }
+    return B2RT_OK;
+}
+
+static int trace_common(b2rt_ctx *ctx, int64_t nrays, const b2rt_ray *rays, b2rt_hit *hits, uint8_t *occ,
+                        int where, bool any) {
+    if (!ctx) return B2RT_E_ARG;
+    if (nrays < 0 || (nrays && (!rays || (!hits && !occ)))) { ctx->err = "trace: bad arguments"; return B2RT_E_ARG; }
+    if (!ctx->built) { ctx->err = "trace: b2rt_build_accel has not been called"; return B2RT_E_STATE; }
+    if (nrays == 0) return B2RT_OK;
+    B2RT_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (where == B2RT_DEVICE) return b2rt_trace_impl(ctx, nrays, rays, hits, occ, any);
+    if (where != B2RT_HOST) { ctx->err = "trace: where must be B2RT_HOST or B2RT_DEVICE"; return B2RT_E_ARG; }
+    cudaStream_t st = ctx->stream;
+    B2RT_CUDA(ctx, ctx->d_rays.reserve((size_t)nrays * sizeof(b2rt_ray)));
+    B2RT_CUDA(ctx, cudaMemcpyAsync(ctx->d_rays.p, rays, (size_t)nrays * sizeof(b2rt_ray), cudaMemcpyHostToDevice, st));
+    int rc;
+    if (any) {
+        B2RT_CUDA(ctx, ctx->d_occ.reserve((size_t)nrays));
+        rc = b2rt_trace_impl(ctx, nrays, ctx->d_rays.as<b2rt_ray>(), nullptr, ctx->d_occ.as<uint8_t>(), true);
+        if (rc) return rc;
+        B2RT_CUDA(ctx, cudaMemcpyAsync(occ, ctx->d_occ.p, (size_t)nrays, cudaMemcpyDeviceToHost, st));
+    } else {
+        B2RT_CUDA(ctx, ctx->d_hits.reserve((size_t)nrays * sizeof(b2rt_hit)));
+        rc = b2rt_trace_impl(ctx, nrays, ctx->d_rays.as<b2rt_ray>(), ctx->d_hits.as<b2rt_hit>(), nullptr, false);
+        if (rc) return rc;
+        B2RT_CUDA(ctx, cudaMemcpyAsync(hits, ctx->d_hits.p, (size_t)nrays * sizeof(b2rt_hit), cudaMemcpyDeviceToHost, st));
+    }
+    return check_status(ctx);
+}
+
+int b2rt_trace_closest(b2rt_ctx *ctx, int64_t nrays, const b2rt_ray *rays, b2rt_hit *hits, int where) {
+    return trace_common(ctx, nrays, rays, hits, nullptr, where, false);
+}
+int b2rt_trace_any(b2rt_ctx *ctx, int64_t nrays, const b2rt_ray *rays, uint8_t *occluded, int where) {
+    return trace_common(ctx, nrays, rays, nullptr, occluded, where, true);
+}
+
+int b2rt_sort_pairs(b2rt_ctx *ctx, int64_t n, uint32_t *keys, uint32_t *vals, int key_bits) {
+    if (!ctx) return B2RT_E_ARG;
+    if (n < 0 || key_bits < 1 || key_bits > 32 || (n && (!keys || !vals))) { ctx->err = "sort_pairs: bad arguments"; return B2RT_E_ARG; }
+    if (n <= 1) return B2RT_OK;
+    B2RT_CUDA(ctx, cudaSetDevice(ctx->device));
+    B2RT_CUDA(ctx, ctx->d_keys_alt.reserve((size_t)n * 4));
+    B2RT_CUDA(ctx, ctx->d_vals_alt.reserve((size_t)n * 4));
+    bool in_alt = false;
+    int rc = b2rt_sort_pairs_impl(ctx, n, keys, vals, ctx->d_keys_alt.as<uint32_t>(), ctx->d_vals_alt.as<uint32_t>(),
+                                  key_bits, &in_alt);
+    if (rc) return rc;
+    if (in_alt) {
+        B2RT_CUDA(ctx, cudaMemcpyAsync(keys, ctx->d_keys_alt.p, (size_t)n * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+        B2RT_CUDA(ctx, cudaMemcpyAsync(vals, ctx->d_vals_alt.p, (size_t)n * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+    }
+    return B2RT_OK;
+}
+
+int b2rt_sync(b2rt_ctx *ctx) {
+    if (!ctx) return B2RT_E_ARG;
+    B2RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return check_status(ctx);
+}
+
+int b2rt_timer_start(b2rt_ctx *ctx) {
+    if (!ctx) return B2RT_E_ARG;
+    B2RT_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+    return B2RT_OK;
+}
+int b2rt_timer_stop(b2rt_ctx *ctx, float *ms) {
+    if (!ctx || !ms) return B2RT_E_ARG;
+    B2RT_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+    B2RT_CUDA(ctx, cudaEventSynchronize(ctx->ev1));
+    B2RT_CUDA(ctx, cudaEventElapsedTime(ms, ctx->ev0, ctx->ev1));
+    return B2RT_OK;
+}
+int b2rt_launch_count(b2rt_ctx *ctx, int64_t *n, int reset) {
+    if (!ctx) return B2RT_E_ARG;
+    if (n) *n = ctx->launches;
+    if (reset) ctx->launches = 0;
+    return B2RT_OK;
+}
+void *b2rt_stream(b2rt_ctx *ctx) { return ctx ? (void *)ctx->stream : nullptr; }
+
+}  // extern "C"

@@ -1,0 +1,529 @@
+// K1 + K3 + K4: deterministic LBVH builder (bounds + Morton, Karras topology + refit + SAH leaf
+// collapse, greedy wide collapse to 4-wide 128-byte nodes).  K2 (the sort) lives in sort.cu.
+//
+// Replaces the reference's request for OptiX's closed "Sbvh" builder (cuda_render/cudarender.cpp:44,50)
+// fed by trianglemesh_bounds / sphere_bounds / disk_bounds (cuda_render/util/shape/cudatrianglemesh.cu:83-99,
+// cudasphere.cu:74-79, cudadisk.cu:87-96).  CPU analogue in the oracle: BVHAccel
+// (pbrt-v2/src/accelerators/bvh.cpp:153-380) -- a different (SAH-recursive) tree, so topology parity
+// is against oracle/oracle_port.c (same arithmetic, -ffp-contract=off there, -fmad=false here) and
+// hit parity is against pbrt itself.
+//
+// Every float result below is order-independent (min/max) or evaluated in one fixed order, and every
+// index comes from integer prefix sums, so the output bytes are identical across runs and GPUs.
+#include "b2rt_internal.cuh"
+#include <math.h>
+
+namespace {
+
+__device__ __forceinline__ uint32_t f2ord(float f) {
+    uint32_t b = __float_as_uint(f);
+    return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__device__ __forceinline__ float ord2f(uint32_t o) {
+    uint32_t b = (o & 0x80000000u) ? (o & 0x7fffffffu) : ~o;
+    return __uint_as_float(b);
+}
+
+__global__ void init_scene_box_kernel(uint32_t *box) {
+    int i = threadIdx.x;
+    if (i < 12) box[i] = ((i % 6) < 3) ? 0xffffffffu : 0u;  // mins start at +max, maxes at 0
+}
+
+__device__ __forceinline__ void xform_point(const float *m, float x, float y, float z, float &ox, float &oy,
+                                            float &oz) {
+    ox = m[0] * x + m[1] * y + m[2] * z + m[3];
+    oy = m[4] * x + m[5] * y + m[6] * z + m[7];
+    oz = m[8] * x + m[9] * y + m[10] * z + m[11];
+}
+
+// K1a: per-prim AABB -> leaf_box[6*p]; block-reduced centroid and scene bounds -> ordered-int atomics.
+__global__ void __launch_bounds__(256)
+prim_bounds_kernel(const float *__restrict__ verts, const int32_t *__restrict__ idx,
+                   const int32_t *__restrict__ prim_kind, const AnalyticPrim *__restrict__ analytic,
+                   const int32_t *__restrict__ analytic_type, int n, float *__restrict__ leaf_box,
+                   uint32_t *__restrict__ scene_box) {
+    int p = blockIdx.x * blockDim.x + threadIdx.x;
+    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    bool ok = p < n;
+    if (ok) {
+        int kind = prim_kind[p];
+        if (kind >= 0) {
+            const int32_t *t = idx + 3 * (int64_t)kind;
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                const float *v = verts + 3 * (int64_t)t[k];
+#pragma unroll
+                for (int a = 0; a < 3; ++a) { lo[a] = fminf(lo[a], v[a]); hi[a] = fmaxf(hi[a], v[a]); }
+            }
+        } else {
+            const AnalyticPrim &A = analytic[~kind];
+            float r = A.radius;
+            float z0 = analytic_type[~kind] == B2RT_PRIM_SPHERE ? -r : A.height;
+            float z1 = analytic_type[~kind] == B2RT_PRIM_SPHERE ? r : A.height;
+            for (int c = 0; c < 8; ++c) {
+                float x, y, z;
+                xform_point(A.o2w, (c & 1) ? r : -r, (c & 2) ? r : -r, (c & 4) ? z1 : z0, x, y, z);
+                float q[3] = {x, y, z};
+#pragma unroll
+                for (int a = 0; a < 3; ++a) { lo[a] = fminf(lo[a], q[a]); hi[a] = fmaxf(hi[a], q[a]); }
+            }
+            // pad analytic boxes by a few ulps of their extent: the corner transform is rounded
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                float pad = 1e-5f * fmaxf(fmaxf(fabsf(lo[a]), fabsf(hi[a])), hi[a] - lo[a]);
+                lo[a] -= pad; hi[a] += pad;
+            }
+        }
+        float *b = leaf_box + 6 * (int64_t)p;
+        b[0] = lo[0]; b[1] = lo[1]; b[2] = lo[2]; b[3] = hi[0]; b[4] = hi[1]; b[5] = hi[2];
+    }
+    // centroid (same expression as the Morton kernel)
+    float c[3];
+#pragma unroll
+    for (int a = 0; a < 3; ++a) c[a] = 0.5f * (lo[a] + hi[a]);
+    float cmin[3], cmax[3], smin[3], smax[3];
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        cmin[a] = ok ? c[a] : INFINITY; cmax[a] = ok ? c[a] : -INFINITY;
+        smin[a] = lo[a]; smax[a] = hi[a];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            cmin[a] = fminf(cmin[a], __shfl_xor_sync(0xffffffffu, cmin[a], o));
+            cmax[a] = fmaxf(cmax[a], __shfl_xor_sync(0xffffffffu, cmax[a], o));
+            smin[a] = fminf(smin[a], __shfl_xor_sync(0xffffffffu, smin[a], o));
+            smax[a] = fmaxf(smax[a], __shfl_xor_sync(0xffffffffu, smax[a], o));
+        }
+    }
+    if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            if (cmin[a] <= cmax[a]) {
+                atomicMin(&scene_box[a], f2ord(cmin[a]));
+                atomicMax(&scene_box[3 + a], f2ord(cmax[a]));
+                atomicMin(&scene_box[6 + a], f2ord(smin[a]));
+                atomicMax(&scene_box[9 + a], f2ord(smax[a]));
+            }
+        }
+    }
+}
+
+__device__ __forceinline__ uint32_t expand_bits10(uint32_t v) {
+    v = (v * 0x00010001u) & 0xFF0000FFu;
+    v = (v * 0x00000101u) & 0x0F00F00Fu;
+    v = (v * 0x00000011u) & 0xC30C30C3u;
+    v = (v * 0x00000005u) & 0x49249249u;
+    return v;
+}
+
+// K1b: 30-bit Morton code of the quantised centroid; value = prim id (so a stable sort breaks ties by id)
+__global__ void __launch_bounds__(256)
+morton_kernel(const float *__restrict__ leaf_box, const uint32_t *__restrict__ scene_box, int n,
+              uint32_t *__restrict__ keys, uint32_t *__restrict__ vals) {
+    int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    const float *b = leaf_box + 6 * (int64_t)p;
+    uint32_t q[3];
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        float cmin = ord2f(scene_box[a]), cmax = ord2f(scene_box[3 + a]);
+        float ext = cmax - cmin;
+        float scale = ext > 0.f ? 1024.f / ext : 0.f;
+        float c = 0.5f * (b[a] + b[3 + a]);
+        float f = (c - cmin) * scale;
+        int qi = (int)f;
+        q[a] = (uint32_t)min(max(qi, 0), 1023);
+    }
+    keys[p] = (expand_bits10(q[0]) << 2) | (expand_bits10(q[1]) << 1) | expand_bits10(q[2]);
+    vals[p] = (uint32_t)p;
+}
+
+// ---- K3: Karras 2012 topology -----------------------------------------------------------------
+__device__ __forceinline__ int delta(const uint32_t *__restrict__ keys, int n, int i, int j) {
+    if (j < 0 || j >= n) return -1;
+    uint32_t a = keys[i], b = keys[j];
+    if (a == b) return 32 + __clz((uint32_t)i ^ (uint32_t)j);
+    return __clz(a ^ b);
+}
+
+// node numbering: internal i in [0,n-1) -> i ; leaf j -> (n-1)+j
+__global__ void __launch_bounds__(256)
+karras_topology_kernel(const uint32_t *__restrict__ keys, int n, int32_t *__restrict__ parent,
+                       int32_t *__restrict__ child, int2 *__restrict__ range) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    int d = (delta(keys, n, i, i + 1) - delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
+    int dmin = delta(keys, n, i, i - d);
+    int lmax = 2;
+    while (delta(keys, n, i, i + lmax * d) > dmin) lmax <<= 1;
+    int l = 0;
+    for (int t = lmax >> 1; t >= 1; t >>= 1)
+        if (delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+    int j = i + l * d;
+    int dnode = delta(keys, n, i, j);
+    int s = 0;
+    for (int t = (l + 1) >> 1;; t = (t + 1) >> 1) {
+        if (delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+        if (t == 1) break;
+    }
+    int gamma = i + s * d + min(d, 0);
+    int first = min(i, j), last = max(i, j);
+    int left = (first == gamma) ? (n - 1) + gamma : gamma;
+    int right = (last == gamma + 1) ? (n - 1) + gamma + 1 : gamma + 1;
+    child[2 * i] = left; child[2 * i + 1] = right;
+    parent[left] = i; parent[right] = i;
+    range[i] = make_int2(first, last);
+    if (i == 0) parent[0] = -1;
+}
+
+__device__ __forceinline__ float box_area(const float *b) {
+    float dx = b[3] - b[0], dy = b[4] - b[1], dz = b[5] - b[2];
+    return 2.f * (dx * dy + dy * dz + dz * dx);
+}
+
+// bottom-up refit + SAH leaf-collapse decision.  flag[i]: arrival counter.  collapse[i]=1 when the
+// whole subtree of internal i is cheaper as one leaf (count <= B2RT_LEAF_MAX).
+__global__ void __launch_bounds__(256)
+refit_kernel(const float *__restrict__ leaf_box, const uint32_t *__restrict__ vals, int n,
+             const int32_t *__restrict__ parent, const int32_t *__restrict__ child,
+             const int2 *__restrict__ range, float *box, float *cost, uint32_t *flag,
+             uint8_t *__restrict__ collapse) {
+    int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    int node = (n - 1) + j;
+    {
+        const float *s = leaf_box + 6 * (int64_t)vals[j];
+        float *d = box + 6 * (int64_t)node;
+        float b[6];
+#pragma unroll
+        for (int a = 0; a < 6; ++a) { b[a] = s[a]; d[a] = b[a]; }
+        cost[node] = box_area(b);  // one prim, prim cost 1
+    }
+    __threadfence();
+    int cur = parent[node];
+    while (cur >= 0) {
+        if (atomicAdd(&flag[cur], 1u) == 0u) return;  // first arriver leaves; second owns the node
+        __threadfence();
+        int l = child[2 * cur], r = child[2 * cur + 1];
+        const volatile float *bl = box + 6 * (int64_t)l, *br = box + 6 * (int64_t)r;
+        float b[6];
+#pragma unroll
+        for (int a = 0; a < 3; ++a) { b[a] = fminf(bl[a], br[a]); b[3 + a] = fmaxf(bl[3 + a], br[3 + a]); }
+        float *d = box + 6 * (int64_t)cur;
+#pragma unroll
+        for (int a = 0; a < 6; ++a) d[a] = b[a];
+        float area = box_area(b);
+        float cl = ((const volatile float *)cost)[l], cr = ((const volatile float *)cost)[r];
+        float c_int = area + (cl + cr);  // node cost 1
+        int2 rg = range[cur];
+        int cnt = rg.y - rg.x + 1;
+        float c_leaf = area * (float)cnt;
+        bool col = (cnt <= B2RT_LEAF_MAX) && (c_leaf <= c_int);
+        collapse[cur] = col ? 1 : 0;
+        cost[cur] = col ? c_leaf : c_int;
+        __threadfence();
+        cur = parent[cur];
+    }
+}
+
+// ---- K4: wide collapse ---------------------------------------------------------------------------
+struct WideTmp { int32_t c[4]; };  // binary node ids of the (up to 4) children, -1 = unused
+
+__device__ __forceinline__ bool is_openable(int node, int n, const uint8_t *collapse) {
+    return node < n - 1 && !collapse[node];
+}
+
+// one thread per wide root in the current level's queue
+__global__ void __launch_bounds__(128)
+wide_collapse_level_kernel(const int32_t *__restrict__ queue_in, int nq, int n,
+                           const int32_t *__restrict__ child, const float *__restrict__ box,
+                           const uint8_t *__restrict__ collapse, WideTmp *__restrict__ tmp,
+                           uint32_t *__restrict__ wide_flag, int32_t *__restrict__ queue_out,
+                           uint32_t *__restrict__ out_count) {
+    int qi = blockIdx.x * blockDim.x + threadIdx.x;
+    if (qi >= nq) return;
+    int root = queue_in[qi];
+    int c[4]; int m = 2;
+    c[0] = child[2 * root]; c[1] = child[2 * root + 1]; c[2] = -1; c[3] = -1;
+    while (m < 4) {
+        int best = -1; float best_area = -1.f;
+        for (int k = 0; k < m; ++k) {
+            if (!is_openable(c[k], n, collapse)) continue;
+            float a = box_area(box + 6 * (int64_t)c[k]);
+            if (a > best_area) { best_area = a; best = k; }   // first max wins: deterministic
+        }
+        if (best < 0) break;
+        int node = c[best];
+        // keep order: left child takes the slot, right child is inserted right after it
+        for (int k = m; k > best + 1; --k) c[k] = c[k - 1];
+        c[best] = child[2 * node]; c[best + 1] = child[2 * node + 1];
+        ++m;
+    }
+    WideTmp t;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) t.c[k] = c[k];
+    tmp[root] = t;
+    wide_flag[root] = 1u;
+    for (int k = 0; k < m; ++k)
+        if (is_openable(c[k], n, collapse)) queue_out[atomicAdd(out_count, 1u)] = c[k];
+}
+
+__global__ void __launch_bounds__(128)
+wide_emit_kernel(int n, const WideTmp *__restrict__ tmp, const uint32_t *__restrict__ wide_flag,
+                 const uint32_t *__restrict__ wide_index, const float *__restrict__ box,
+                 const int2 *__restrict__ range, const uint8_t *__restrict__ collapse,
+                 WideNode *__restrict__ nodes) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1 || !wide_flag[i]) return;
+    WideTmp t = tmp[i];
+    WideNode w;
+    int used = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        int c = t.c[k];
+        if (c < 0) {
+            w.lox[k] = w.loy[k] = w.loz[k] = INFINITY;
+            w.hix[k] = w.hiy[k] = w.hiz[k] = -INFINITY;
+            w.child[k] = B2RT_CHILD_EMPTY;
+            continue;
+        }
+        ++used;
+        const float *b = box + 6 * (int64_t)c;
+        w.lox[k] = b[0]; w.loy[k] = b[1]; w.loz[k] = b[2];
+        w.hix[k] = b[3]; w.hiy[k] = b[4]; w.hiz[k] = b[5];
+        if (c >= n - 1) {
+            w.child[k] = (int32_t)(0x80000000u | ((uint32_t)(c - (n - 1)) << 3));          // 1 prim
+        } else if (collapse[c]) {
+            int2 rg = range[c];
+            w.child[k] = (int32_t)(0x80000000u | ((uint32_t)rg.x << 3) | (uint32_t)(rg.y - rg.x));
+        } else {
+            w.child[k] = (int32_t)wide_index[c];
+        }
+    }
+    w.meta[0] = used; w.meta[1] = i; w.meta[2] = 0; w.meta[3] = 0;
+    nodes[wide_index[i]] = w;
+}
+
+// n == 1 (or a root that collapsed to a single leaf): one node, one leaf child covering everything
+__global__ void wide_single_kernel(int n, const float *__restrict__ box_root, WideNode *__restrict__ nodes) {
+    if (threadIdx.x != 0) return;
+    WideNode w;
+    for (int k = 0; k < 4; ++k) {
+        w.lox[k] = w.loy[k] = w.loz[k] = INFINITY;
+        w.hix[k] = w.hiy[k] = w.hiz[k] = -INFINITY;
+        w.child[k] = B2RT_CHILD_EMPTY; w.meta[k] = 0;
+    }
+    if (n > 0) {
+        w.lox[0] = box_root[0]; w.loy[0] = box_root[1]; w.loz[0] = box_root[2];
+        w.hix[0] = box_root[3]; w.hiy[0] = box_root[4]; w.hiz[0] = box_root[5];
+        w.child[0] = (int32_t)(0x80000000u | (uint32_t)(n - 1));
+        w.meta[0] = 1;
+    }
+    nodes[0] = w;
+}
+
+// leaf-ordered primitive records + leaf_prims (prim id per slot)
+__global__ void __launch_bounds__(256)
+prim_records_kernel(const float *__restrict__ verts, const int32_t *__restrict__ idx,
+                    const int32_t *__restrict__ prim_kind, const int32_t *__restrict__ analytic_type,
+                    const uint32_t *__restrict__ vals, int n, PrimRec *__restrict__ recs,
+                    int32_t *__restrict__ leaf_prims) {
+    int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    int p = (int)vals[j];
+    leaf_prims[j] = p;
+    int kind = prim_kind[p];
+    PrimRec r;
+    if (kind >= 0) {
+        const int32_t *t = idx + 3 * (int64_t)kind;
+        const float *p1 = verts + 3 * (int64_t)t[0], *p2 = verts + 3 * (int64_t)t[1],
+                    *p3 = verts + 3 * (int64_t)t[2];
+        r.a = make_float4(p1[0], p1[1], p1[2], __int_as_float(p));
+        r.b = make_float4(p2[0] - p1[0], p2[1] - p1[1], p2[2] - p1[2], __int_as_float(B2RT_PRIM_TRI));
+        r.c = make_float4(p3[0] - p1[0], p3[1] - p1[1], p3[2] - p1[2], __int_as_float(0));
+    } else {
+        r.a = make_float4(0, 0, 0, __int_as_float(p));
+        r.b = make_float4(0, 0, 0, __int_as_float(analytic_type[~kind]));
+        r.c = make_float4(0, 0, 0, __int_as_float(~kind));
+    }
+    recs[j] = r;
+}
+
+}  // namespace
+
+int b2rt_build_impl(b2rt_ctx *ctx) {
+    const int n = ctx->n_prims;
+    cudaStream_t st = ctx->stream;
+    ctx->built = false;
+    B2RT_CUDA(ctx, cudaEventRecord(ctx->evb0, st));
+
+    // ---- upload flattened scene -----------------------------------------------------------------
+    std::vector<int32_t> kind(n);
+    for (size_t t = 0; t < ctx->h_tri_prim.size(); ++t) kind[ctx->h_tri_prim[t]] = (int32_t)t;
+    for (size_t a = 0; a < ctx->h_analytic_prim.size(); ++a) kind[ctx->h_analytic_prim[a]] = ~(int32_t)a;
+    auto up = [&](DevBuf &b, const void *src, size_t bytes) -> cudaError_t {
+        cudaError_t e = b.reserve(bytes ? bytes : 16);
+        if (e != cudaSuccess || !bytes) return e;
+        return cudaMemcpyAsync(b.p, src, bytes, cudaMemcpyHostToDevice, st);
+    };
+    DevBuf &d_atype = ctx->d_queue_b;  // analytic types live in their own small buffer below
+    (void)d_atype;
+    B2RT_CUDA(ctx, up(ctx->d_verts, ctx->h_verts.data(), ctx->h_verts.size() * sizeof(float)));
+    B2RT_CUDA(ctx, up(ctx->d_idx, ctx->h_idx.data(), ctx->h_idx.size() * sizeof(int32_t)));
+    B2RT_CUDA(ctx, up(ctx->d_prim_kind, kind.data(), kind.size() * sizeof(int32_t)));
+    // analytic prims + their types packed in one buffer: [AnalyticPrim x m][int32 type x m]
+    size_t m = ctx->h_analytic.size();
+    std::vector<uint8_t> apack(m * sizeof(AnalyticPrim) + m * sizeof(int32_t) + 16);
+    if (m) {
+        memcpy(apack.data(), ctx->h_analytic.data(), m * sizeof(AnalyticPrim));
+        memcpy(apack.data() + m * sizeof(AnalyticPrim), ctx->h_analytic_type.data(), m * sizeof(int32_t));
+    }
+    B2RT_CUDA(ctx, up(ctx->d_analytic, apack.data(), apack.size()));
+    B2RT_CUDA(ctx, cudaStreamSynchronize(st));  // host vectors above go out of scope
+    const AnalyticPrim *d_an = ctx->d_analytic.as<AnalyticPrim>();
+    const int32_t *d_an_type = (const int32_t *)((const uint8_t *)ctx->d_analytic.p + m * sizeof(AnalyticPrim));
+
+    const int nn = n > 0 ? n : 1;
+    B2RT_CUDA(ctx, ctx->d_leaf_box.reserve((size_t)nn * 6 * sizeof(float)));
+    B2RT_CUDA(ctx, ctx->d_scene_box.reserve(16 * sizeof(uint32_t)));
+    B2RT_CUDA(ctx, ctx->d_keys.reserve((size_t)nn * 4));
+    B2RT_CUDA(ctx, ctx->d_vals.reserve((size_t)nn * 4));
+    B2RT_CUDA(ctx, ctx->d_keys_alt.reserve((size_t)nn * 4));
+    B2RT_CUDA(ctx, ctx->d_vals_alt.reserve((size_t)nn * 4));
+    B2RT_CUDA(ctx, ctx->d_bin_parent.reserve((size_t)(2 * nn) * 4));
+    B2RT_CUDA(ctx, ctx->d_bin_child.reserve((size_t)(2 * nn) * 4));
+    B2RT_CUDA(ctx, ctx->d_bin_count.reserve((size_t)nn * sizeof(int2)));   // ranges
+    B2RT_CUDA(ctx, ctx->d_bin_box.reserve((size_t)(2 * nn) * 6 * sizeof(float)));
+    B2RT_CUDA(ctx, ctx->d_bin_cost.reserve((size_t)(2 * nn) * sizeof(float)));
+    B2RT_CUDA(ctx, ctx->d_bin_flag.reserve((size_t)nn * 5));               // uint32 flag + uint8 collapse
+    B2RT_CUDA(ctx, ctx->d_wide_tmp.reserve((size_t)nn * sizeof(WideTmp)));
+    B2RT_CUDA(ctx, ctx->d_wide_flag.reserve((size_t)nn * 4));
+    B2RT_CUDA(ctx, ctx->d_wide_index.reserve((size_t)nn * 4));
+    B2RT_CUDA(ctx, ctx->d_queue_a.reserve((size_t)nn * 4));
+    B2RT_CUDA(ctx, ctx->d_queue_b.reserve((size_t)nn * 4));
+    B2RT_CUDA(ctx, ctx->d_counters.reserve(64));
+    B2RT_CUDA(ctx, ctx->d_prim_recs.reserve((size_t)nn * sizeof(PrimRec)));
+    B2RT_CUDA(ctx, ctx->d_leaf_prims.reserve((size_t)nn * 4));
+
+    b2rt_accel_info &info = ctx->info;
+    info = b2rt_accel_info{};
+    info.n_prims = n; info.n_tris = (int)ctx->h_tri_prim.size(); info.wide_width = 4; info.n_leaf_slots = n;
+
+    uint32_t *scene_box = ctx->d_scene_box.as<uint32_t>();
+    float *leaf_box = ctx->d_leaf_box.as<float>();
+    float *bin_box = ctx->d_bin_box.as<float>();
+    int n_wide = 1, depth = 1;
+
+    if (n == 0) {
+        B2RT_CUDA(ctx, ctx->d_wide_nodes.reserve(sizeof(WideNode)));
+        wide_single_kernel<<<1, 32, 0, st>>>(0, nullptr, ctx->d_wide_nodes.as<WideNode>());
+        B2RT_LAUNCH_CHECK(ctx);
+    } else {
+        const int grid = (n + 255) / 256;
+        init_scene_box_kernel<<<1, 32, 0, st>>>(scene_box);
+        B2RT_LAUNCH_CHECK(ctx);
+        prim_bounds_kernel<<<grid, 256, 0, st>>>(ctx->d_verts.as<float>(), ctx->d_idx.as<int32_t>(),
+                                                 ctx->d_prim_kind.as<int32_t>(), d_an, d_an_type, n, leaf_box,
+                                                 scene_box);
+        B2RT_LAUNCH_CHECK(ctx);
+        morton_kernel<<<grid, 256, 0, st>>>(leaf_box, scene_box, n, ctx->d_keys.as<uint32_t>(),
+                                            ctx->d_vals.as<uint32_t>());
+        B2RT_LAUNCH_CHECK(ctx);
+        bool in_alt = false;
+        int rc = b2rt_sort_pairs_impl(ctx, n, ctx->d_keys.as<uint32_t>(), ctx->d_vals.as<uint32_t>(),
+                                      ctx->d_keys_alt.as<uint32_t>(), ctx->d_vals_alt.as<uint32_t>(), 30, &in_alt);
+        if (rc) return rc;
+        if (in_alt) { std::swap(ctx->d_keys, ctx->d_keys_alt); std::swap(ctx->d_vals, ctx->d_vals_alt); }
+        uint32_t *keys = ctx->d_keys.as<uint32_t>(), *vals = ctx->d_vals.as<uint32_t>();
+
+        prim_records_kernel<<<grid, 256, 0, st>>>(ctx->d_verts.as<float>(), ctx->d_idx.as<int32_t>(),
+                                                  ctx->d_prim_kind.as<int32_t>(), d_an_type, vals, n,
+                                                  ctx->d_prim_recs.as<PrimRec>(), ctx->d_leaf_prims.as<int32_t>());
+        B2RT_LAUNCH_CHECK(ctx);
+
+        int32_t *parent = ctx->d_bin_parent.as<int32_t>(), *child = ctx->d_bin_child.as<int32_t>();
+        int2 *range = ctx->d_bin_count.as<int2>();
+        uint32_t *flag = ctx->d_bin_flag.as<uint32_t>();
+        uint8_t *collapse = (uint8_t *)(flag + nn);
+        float *cost = ctx->d_bin_cost.as<float>();
+        B2RT_CUDA(ctx, cudaMemsetAsync(flag, 0, (size_t)nn * 5, st));
+        if (n == 1) {
+            B2RT_CUDA(ctx, cudaMemcpyAsync(bin_box, leaf_box, 6 * sizeof(float), cudaMemcpyDeviceToDevice, st));
+            int32_t m1 = -1;
+            B2RT_CUDA(ctx, cudaMemcpyAsync(parent, &m1, 4, cudaMemcpyHostToDevice, st));
+            B2RT_CUDA(ctx, ctx->d_wide_nodes.reserve(sizeof(WideNode)));
+            wide_single_kernel<<<1, 32, 0, st>>>(1, bin_box, ctx->d_wide_nodes.as<WideNode>());
+            B2RT_LAUNCH_CHECK(ctx);
+        } else {
+            karras_topology_kernel<<<(n - 1 + 255) / 256, 256, 0, st>>>(keys, n, parent, child, range);
+            B2RT_LAUNCH_CHECK(ctx);
+            refit_kernel<<<grid, 256, 0, st>>>(leaf_box, vals, n, parent, child, range, bin_box, cost, flag,
+                                               collapse);
+            B2RT_LAUNCH_CHECK(ctx);
+            uint8_t root_collapsed = 0;
+            B2RT_CUDA(ctx, cudaMemcpyAsync(&root_collapsed, collapse, 1, cudaMemcpyDeviceToHost, st));
+            B2RT_CUDA(ctx, cudaStreamSynchronize(st));
+            if (root_collapsed) {
+                B2RT_CUDA(ctx, ctx->d_wide_nodes.reserve(sizeof(WideNode)));
+                wide_single_kernel<<<1, 32, 0, st>>>(n, bin_box, ctx->d_wide_nodes.as<WideNode>());
+                B2RT_LAUNCH_CHECK(ctx);
+            } else {
+                // level-synchronous greedy collapse; the queues are only work lists (their order does
+                // not reach the output: node indices come from the prefix sum over wide_flag)
+                uint32_t *wide_flag = ctx->d_wide_flag.as<uint32_t>();
+                uint32_t *wide_index = ctx->d_wide_index.as<uint32_t>();
+                uint32_t *counter = ctx->d_counters.as<uint32_t>();
+                int32_t *qa = ctx->d_queue_a.as<int32_t>(), *qb = ctx->d_queue_b.as<int32_t>();
+                B2RT_CUDA(ctx, cudaMemsetAsync(wide_flag, 0, (size_t)nn * 4, st));
+                B2RT_CUDA(ctx, cudaMemsetAsync(qa, 0, 4, st));  // queue = {root 0}
+                uint32_t nq = 1;
+                depth = 0;
+                while (nq > 0) {
+                    ++depth;
+                    B2RT_CUDA(ctx, cudaMemsetAsync(counter, 0, 4, st));
+                    wide_collapse_level_kernel<<<(nq + 127) / 128, 128, 0, st>>>(
+                        qa, (int)nq, n, child, bin_box, collapse, ctx->d_wide_tmp.as<WideTmp>(), wide_flag, qb,
+                        counter);
+                    B2RT_LAUNCH_CHECK(ctx);
+                    B2RT_CUDA(ctx, cudaMemcpyAsync(&nq, counter, 4, cudaMemcpyDeviceToHost, st));
+                    B2RT_CUDA(ctx, cudaStreamSynchronize(st));
+                    std::swap(qa, qb);
+                }
+                B2RT_CUDA(ctx, cudaMemcpyAsync(wide_index, wide_flag, (size_t)(n - 1) * 4,
+                                               cudaMemcpyDeviceToDevice, st));
+                rc = b2rt_exclusive_scan_u32(ctx, wide_index, n - 1, counter + 4);
+                if (rc) return rc;
+                uint32_t total = 0;
+                B2RT_CUDA(ctx, cudaMemcpyAsync(&total, counter + 4, 4, cudaMemcpyDeviceToHost, st));
+                B2RT_CUDA(ctx, cudaStreamSynchronize(st));
+                n_wide = (int)total;
+                B2RT_CUDA(ctx, ctx->d_wide_nodes.reserve((size_t)n_wide * sizeof(WideNode)));
+                wide_emit_kernel<<<(n - 1 + 127) / 128, 128, 0, st>>>(
+                    n, ctx->d_wide_tmp.as<WideTmp>(), wide_flag, wide_index, bin_box, range, collapse,
+                    ctx->d_wide_nodes.as<WideNode>());
+                B2RT_LAUNCH_CHECK(ctx);
+            }
+            float c0 = 0.f, rootbox[6];
+            B2RT_CUDA(ctx, cudaMemcpyAsync(&c0, cost, 4, cudaMemcpyDeviceToHost, st));
+            B2RT_CUDA(ctx, cudaMemcpyAsync(rootbox, bin_box, 24, cudaMemcpyDeviceToHost, st));
+            B2RT_CUDA(ctx, cudaStreamSynchronize(st));
+            float dx = rootbox[3] - rootbox[0], dy = rootbox[4] - rootbox[1], dz = rootbox[5] - rootbox[2];
+            float ra = 2.f * (dx * dy + dy * dz + dz * dx);
+            info.sah_cost = ra > 0.f ? c0 / ra : 0.f;
+        }
+        uint32_t sb[12];
+        B2RT_CUDA(ctx, cudaMemcpyAsync(sb, scene_box, sizeof(sb), cudaMemcpyDeviceToHost, st));
+        B2RT_CUDA(ctx, cudaStreamSynchronize(st));
+        for (int a = 0; a < 6; ++a) {
+            uint32_t o = sb[6 + a];
+            uint32_t b = (o & 0x80000000u) ? (o & 0x7fffffffu) : ~o;
+            memcpy(&info.bounds[a], &b, 4);
+        }
+    }
+    info.n_wide_nodes = n_wide;
+    info.max_depth = depth;
+    B2RT_CUDA(ctx, cudaEventRecord(ctx->evb1, st));
+    B2RT_CUDA(ctx, cudaEventSynchronize(ctx->evb1));
+    B2RT_CUDA(ctx, cudaEventElapsedTime(&info.build_ms, ctx->evb0, ctx->evb1));
+    ctx->built = true;
+    return B2RT_OK;
+}

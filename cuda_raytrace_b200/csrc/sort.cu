@@ -1,0 +1,206 @@
+// K2: hand-written, CUB-free, stable LSD radix sort of (key32, value32) pairs + a generic
+// exclusive scan.  Replaces nothing in the reference directly: the reference sorts nothing on the
+// device -- its spatial structures are built by closed OptiX ("Sbvh", cuda_render/cudarender.cpp:44)
+// and by pbrt's CPU KdTree (cuda_render/photon_mapping/photonmappingrenderer.cpp:150-180).
+//
+// Determinism: every step is integer arithmetic whose result does not depend on scheduling --
+// per-block digit histograms, an exclusive scan, and a stable in-block ranking (warp w owns a
+// contiguous sub-tile, lanes rank by __match_any_sync + popc of lower lanes).  Equal keys keep
+// their input order, so with value = original index ties break by index.
+#include "b2rt_internal.cuh"
+
+namespace {
+
+constexpr int SORT_THREADS = 256;
+constexpr int SORT_WARPS = SORT_THREADS / 32;
+constexpr int SORT_ITEMS = 16;                       // keys per thread
+constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS; // 4096 keys per block
+constexpr int RADIX = 256;
+
+// ---- per-block digit histogram --------------------------------------------------------------
+__global__ void __launch_bounds__(SORT_THREADS)
+radix_hist_kernel(const uint32_t *__restrict__ keys, int64_t n, int shift, uint32_t *__restrict__ hist,
+                  int nblocks) {
+    __shared__ uint32_t sh[SORT_WARPS][RADIX];
+    for (int i = threadIdx.x; i < SORT_WARPS * RADIX; i += SORT_THREADS) (&sh[0][0])[i] = 0;
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    int64_t base = (int64_t)blockIdx.x * SORT_TILE + warp * (32 * SORT_ITEMS);
+#pragma unroll
+    for (int r = 0; r < SORT_ITEMS; ++r) {
+        int64_t i = base + r * 32 + lane;
+        if (i < n) atomicAdd(&sh[warp][(keys[i] >> shift) & 0xff], 1u);
+    }
+    __syncthreads();
+    for (int d = threadIdx.x; d < RADIX; d += SORT_THREADS) {
+        uint32_t s = 0;
+#pragma unroll
+        for (int w = 0; w < SORT_WARPS; ++w) s += sh[w][d];
+        hist[(int64_t)d * nblocks + blockIdx.x] = s;
+    }
+}
+
+// ---- stable scatter ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(SORT_THREADS)
+radix_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__restrict__ vals_in,
+                     uint32_t *__restrict__ keys_out, uint32_t *__restrict__ vals_out, int64_t n, int shift,
+                     const uint32_t *__restrict__ scanned_hist, int nblocks) {
+    __shared__ uint32_t sh[SORT_WARPS][RADIX];  // first: running warp histogram; then: final bases
+    for (int i = threadIdx.x; i < SORT_WARPS * RADIX; i += SORT_THREADS) (&sh[0][0])[i] = 0;
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t lt = (1u << lane) - 1u;
+    int64_t base = (int64_t)blockIdx.x * SORT_TILE + warp * (32 * SORT_ITEMS);
+
+    uint32_t k[SORT_ITEMS], v[SORT_ITEMS], rank[SORT_ITEMS];
+#pragma unroll
+    for (int r = 0; r < SORT_ITEMS; ++r) {
+        int64_t i = base + r * 32 + lane;
+        bool ok = i < n;
+        k[r] = ok ? keys_in[i] : 0u;
+        v[r] = ok ? vals_in[i] : 0u;
+        uint32_t d = ok ? ((k[r] >> shift) & 0xff) : 0x100u;
+        uint32_t peers = __match_any_sync(0xffffffffu, d);
+        int leader = __ffs(peers) - 1;
+        uint32_t before = 0;
+        if (lane == leader && ok) {
+            before = sh[warp][d];
+            sh[warp][d] = before + __popc(peers);
+        }
+        before = __shfl_sync(0xffffffffu, before, leader);
+        rank[r] = before + __popc(peers & lt);
+        __syncwarp();
+    }
+    __syncthreads();
+    // turn per-warp counts into absolute output bases: global + warps before me
+    for (int d = threadIdx.x; d < RADIX; d += SORT_THREADS) {
+        uint32_t run = scanned_hist[(int64_t)d * nblocks + blockIdx.x];
+#pragma unroll
+        for (int w = 0; w < SORT_WARPS; ++w) {
+            uint32_t c = sh[w][d];
+            sh[w][d] = run;
+            run += c;
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < SORT_ITEMS; ++r) {
+        int64_t i = base + r * 32 + lane;
+        if (i < n) {
+            uint32_t d = (k[r] >> shift) & 0xff;
+            uint32_t pos = sh[warp][d] + rank[r];
+            keys_out[pos] = k[r];
+            vals_out[pos] = v[r];
+        }
+    }
+}
+
+// ---- exclusive scan (reduce-then-scan, recursive) ------------------------------------------------
+constexpr int SCAN_THREADS = 512;
+constexpr int SCAN_ITEMS = 8;
+constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
+
+__global__ void __launch_bounds__(SCAN_THREADS)
+scan_tile_kernel(uint32_t *__restrict__ data, int64_t n, uint32_t *__restrict__ block_sums) {
+    __shared__ uint32_t warp_sums[SCAN_THREADS / 32];
+    int64_t base = (int64_t)blockIdx.x * SCAN_TILE + (int64_t)threadIdx.x * SCAN_ITEMS;
+    uint32_t x[SCAN_ITEMS];
+    uint32_t sum = 0;
+#pragma unroll
+    for (int j = 0; j < SCAN_ITEMS; ++j) {
+        x[j] = (base + j < n) ? data[base + j] : 0u;
+        sum += x[j];
+    }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t inc = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31) warp_sums[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+        uint32_t w = (lane < SCAN_THREADS / 32) ? warp_sums[lane] : 0u;
+        uint32_t winc = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t t = __shfl_up_sync(0xffffffffu, winc, o);
+            if (lane >= o) winc += t;
+        }
+        if (lane < SCAN_THREADS / 32) warp_sums[lane] = winc - w;
+        if (lane == SCAN_THREADS / 32 - 1 && block_sums) block_sums[blockIdx.x] = winc;
+    }
+    __syncthreads();
+    uint32_t run = warp_sums[warp] + inc - sum;
+#pragma unroll
+    for (int j = 0; j < SCAN_ITEMS; ++j) {
+        if (base + j < n) data[base + j] = run;
+        run += x[j];
+    }
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS)
+scan_add_kernel(uint32_t *__restrict__ data, int64_t n, const uint32_t *__restrict__ block_offsets) {
+    uint32_t off = block_offsets[blockIdx.x];
+    int64_t base = (int64_t)blockIdx.x * SCAN_TILE + (int64_t)threadIdx.x * SCAN_ITEMS;
+#pragma unroll
+    for (int j = 0; j < SCAN_ITEMS; ++j)
+        if (base + j < n) data[base + j] += off;
+}
+
+int scan_rec(b2rt_ctx *ctx, uint32_t *d, int64_t n, uint32_t *tmp, uint32_t *d_total) {
+    int64_t nb = (n + SCAN_TILE - 1) / SCAN_TILE;
+    if (nb <= 1) {
+        scan_tile_kernel<<<1, SCAN_THREADS, 0, ctx->stream>>>(d, n, d_total);
+        B2RT_LAUNCH_CHECK(ctx);
+        return B2RT_OK;
+    }
+    scan_tile_kernel<<<(unsigned)nb, SCAN_THREADS, 0, ctx->stream>>>(d, n, tmp);
+    B2RT_LAUNCH_CHECK(ctx);
+    int rc = scan_rec(ctx, tmp, nb, tmp + ((nb + 3) & ~3ll), d_total);
+    if (rc) return rc;
+    scan_add_kernel<<<(unsigned)nb, SCAN_THREADS, 0, ctx->stream>>>(d, n, tmp);
+    B2RT_LAUNCH_CHECK(ctx);
+    return B2RT_OK;
+}
+
+}  // namespace
+
+int b2rt_exclusive_scan_u32(b2rt_ctx *ctx, uint32_t *d, int64_t n, uint32_t *d_total) {
+    if (n <= 0) return B2RT_OK;
+    // temp: sum over levels of ceil(n/TILE^k) (+ padding)
+    size_t need = 0;
+    for (int64_t m = (n + SCAN_TILE - 1) / SCAN_TILE; m > 1; m = (m + SCAN_TILE - 1) / SCAN_TILE)
+        need += ((m + 3) & ~3ll);
+    need += 8;
+    B2RT_CUDA(ctx, ctx->d_scan_tmp.reserve(need * sizeof(uint32_t)));
+    return scan_rec(ctx, d, n, ctx->d_scan_tmp.as<uint32_t>(), d_total);
+}
+
+int b2rt_sort_pairs_impl(b2rt_ctx *ctx, int64_t n, uint32_t *keys, uint32_t *vals, uint32_t *keys_alt,
+                         uint32_t *vals_alt, int key_bits, bool *result_in_alt) {
+    *result_in_alt = false;
+    if (n <= 1) return B2RT_OK;
+    if (n >= (1ll << 32)) { ctx->err = "sort: n must be < 2^32"; return B2RT_E_ARG; }
+    int passes = (key_bits + 7) / 8;
+    int nblocks = (int)((n + SORT_TILE - 1) / SORT_TILE);
+    B2RT_CUDA(ctx, ctx->d_hist.reserve((size_t)RADIX * nblocks * sizeof(uint32_t)));
+    uint32_t *hist = ctx->d_hist.as<uint32_t>();
+    uint32_t *kin = keys, *vin = vals, *kout = keys_alt, *vout = vals_alt;
+    for (int p = 0; p < passes; ++p) {
+        int shift = 8 * p;
+        radix_hist_kernel<<<nblocks, SORT_THREADS, 0, ctx->stream>>>(kin, n, shift, hist, nblocks);
+        B2RT_LAUNCH_CHECK(ctx);
+        int rc = b2rt_exclusive_scan_u32(ctx, hist, (int64_t)RADIX * nblocks, nullptr);
+        if (rc) return rc;
+        radix_scatter_kernel<<<nblocks, SORT_THREADS, 0, ctx->stream>>>(kin, vin, kout, vout, n, shift, hist,
+                                                                        nblocks);
+        B2RT_LAUNCH_CHECK(ctx);
+        uint32_t *t;
+        t = kin; kin = kout; kout = t;
+        t = vin; vin = vout; vout = t;
+    }
+    *result_in_alt = (passes & 1) != 0;
+    return B2RT_OK;
+}

@@ -1,0 +1,199 @@
+// TEST INFRASTRUCTURE ONLY -- never linked into, imported by or executed from the product path.
+//
+// A thin extern "C" face over the UNMODIFIED reference CPU renderer (pbrt-v2, compiled from
+// /root/reference/pbrt-v2/src by oracle/Makefile into oracle/_ref/libpbrt.a).  It lets the
+// Python tests and bench.py's cpu_baseline / --impl reference arm push the same flat arrays the
+// GPU library receives through pbrt's own BVHAccel / Triangle / Sphere / Disk code.
+//
+// What it exercises in the reference (all paths relative to /root/reference):
+//   scene build      pbrt-v2/src/shapes/trianglemesh.cpp:42-72, 119-124 (Refine),
+//                    pbrt-v2/src/accelerators/bvh.cpp:153-202 (SAH build, maxPrims 4 as api.cpp:494)
+//   closest hit      pbrt-v2/src/accelerators/bvh.cpp:388-439 -> shapes/trianglemesh.cpp:146-227
+//   any hit          pbrt-v2/src/accelerators/bvh.cpp:442-488 -> shapes/trianglemesh.cpp:230-300
+//   brute force      the loop of pbrt-v2/src/renderers/aggregatetest.cpp:93-102
+//
+// Primitive ids: pbrt numbers shapes by creation order (core/shape.cpp:45); we refine every mesh
+// ourselves, in submission order, and remember shapeId -> global primitive index, so ids agree
+// with b2rt's "order of submission" numbering.
+#include "pbrt.h"
+#include "shapes/trianglemesh.h"
+#include "shapes/sphere.h"
+#include "shapes/disk.h"
+#include "accelerators/bvh.h"
+#include "materials/matte.h"
+#include "textures/constant.h"
+#include "primitive.h"
+#include "intersection.h"
+#include "paramset.h"
+#include <thread>
+#include <vector>
+#include <unordered_map>
+#include <chrono>
+
+namespace {
+struct RefScene {
+    std::vector<Transform *> xforms;                 // kept alive for the shapes
+    std::vector<Reference<Shape> > shapes;           // intersectable shapes, global prim order
+    std::vector<Reference<Primitive> > prims;
+    std::unordered_map<uint32_t, int> id2prim;       // pbrt shapeId -> global prim index
+    Reference<Material> mtl;
+    Primitive *accel;
+    double build_seconds;
+    RefScene() : accel(NULL), build_seconds(0) {
+        Reference<Texture<Spectrum> > kd = new ConstantTexture<Spectrum>(Spectrum(0.5f));
+        Reference<Texture<float> > sig = new ConstantTexture<float>(0.f);
+        mtl = new MatteMaterial(kd, sig, NULL);
+    }
+    void push(const Reference<Shape> &s) {
+        id2prim[s->shapeId] = (int)shapes.size();
+        shapes.push_back(s);
+        prims.push_back(new GeometricPrimitive(s, mtl, NULL));
+    }
+};
+
+Transform *from12(const float m[12]) {
+    Matrix4x4 M(m[0], m[1], m[2], m[3], m[4], m[5], m[6], m[7], m[8], m[9], m[10], m[11], 0, 0, 0, 1);
+    return new Transform(M);
+}
+
+template <typename F> void parallel_for(int64_t n, int nthreads, F f) {
+    if (nthreads <= 1) { f(0, n); return; }
+    std::vector<std::thread> th;
+    int64_t chunk = (n + nthreads - 1) / nthreads;
+    for (int t = 0; t < nthreads; ++t) {
+        int64_t lo = t * chunk, hi = std::min(n, lo + chunk);
+        if (lo >= hi) break;
+        th.emplace_back([=]() { f(lo, hi); });
+    }
+    for (auto &t : th) t.join();
+}
+}  // namespace
+
+extern "C" {
+
+void *ref_scene_create() { return new RefScene(); }
+
+// world-space vertices (identity transform), same as what the GPU library is given
+int ref_scene_add_mesh(void *h, int nverts, const float *P, int ntris, const int *idx) {
+    RefScene *s = (RefScene *)h;
+    Transform *I = new Transform();
+    s->xforms.push_back(I);
+    Reference<Shape> mesh = new TriangleMesh(I, I, false, ntris, nverts, idx, (const Point *)P,
+                                             NULL, NULL, NULL, Reference<Texture<float> >());
+    std::vector<Reference<Shape> > tris;
+    mesh->Refine(tris);
+    int first = (int)s->shapes.size();
+    for (size_t i = 0; i < tris.size(); ++i) s->push(tris[i]);
+    return first;
+}
+
+int ref_scene_add_sphere(void *h, const float o2w[12], float radius) {
+    RefScene *s = (RefScene *)h;
+    Transform *t = from12(o2w);
+    Transform *ti = new Transform(Inverse(*t));
+    s->xforms.push_back(t); s->xforms.push_back(ti);
+    int first = (int)s->shapes.size();
+    s->push(new Sphere(t, ti, false, radius, -radius, radius, 360.f));
+    return first;
+}
+
+int ref_scene_add_disk(void *h, const float o2w[12], float height, float radius, float inner) {
+    RefScene *s = (RefScene *)h;
+    Transform *t = from12(o2w);
+    Transform *ti = new Transform(Inverse(*t));
+    s->xforms.push_back(t); s->xforms.push_back(ti);
+    int first = (int)s->shapes.size();
+    s->push(new Disk(t, ti, false, height, radius, inner, 360.f));
+    return first;
+}
+
+// BVHAccel exactly as RenderOptions::MakeScene makes it by default ("sah", maxnodeprims 4)
+double ref_scene_build(void *h) {
+    RefScene *s = (RefScene *)h;
+    auto t0 = std::chrono::steady_clock::now();
+    ParamSet ps;
+    s->accel = CreateBVHAccelerator(s->prims, ps);
+    s->build_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    return s->build_seconds;
+}
+
+int ref_scene_nprims(void *h) { return (int)((RefScene *)h)->shapes.size(); }
+
+void ref_scene_destroy(void *h) {
+    RefScene *s = (RefScene *)h;
+    if (!s) return;
+    delete s->accel;   // shapes are ref-counted; transforms leak on purpose (test infra)
+    delete s;
+}
+
+// rays: 8 floats each {ox,oy,oz,tmin, dx,dy,dz,tmax}.  Outputs: t (INF on miss), prim (-1), u, v.
+// Returns seconds spent inside the traversal loop.
+double ref_intersect(void *h, int64_t nrays, const float *rays, float *t_out, int *prim_out,
+                     float *uv_out, int nthreads) {
+    RefScene *s = (RefScene *)h;
+    auto t0 = std::chrono::steady_clock::now();
+    parallel_for(nrays, nthreads, [=](int64_t lo, int64_t hi) {
+        for (int64_t i = lo; i < hi; ++i) {
+            const float *r = rays + 8 * i;
+            Ray ray(Point(r[0], r[1], r[2]), Vector(r[4], r[5], r[6]), r[3], r[7]);
+            Intersection isect;
+            if (s->accel->Intersect(ray, &isect)) {
+                t_out[i] = ray.maxt;
+                prim_out[i] = s->id2prim.find(isect.shapeId)->second;
+                if (uv_out) { uv_out[2 * i] = isect.dg.u; uv_out[2 * i + 1] = isect.dg.v; }
+            } else {
+                t_out[i] = INFINITY; prim_out[i] = -1;
+                if (uv_out) { uv_out[2 * i] = 0; uv_out[2 * i + 1] = 0; }
+            }
+        }
+    });
+    return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+}
+
+double ref_intersectp(void *h, int64_t nrays, const float *rays, unsigned char *occ, int nthreads) {
+    RefScene *s = (RefScene *)h;
+    auto t0 = std::chrono::steady_clock::now();
+    parallel_for(nrays, nthreads, [=](int64_t lo, int64_t hi) {
+        for (int64_t i = lo; i < hi; ++i) {
+            const float *r = rays + 8 * i;
+            Ray ray(Point(r[0], r[1], r[2]), Vector(r[4], r[5], r[6]), r[3], r[7]);
+            occ[i] = s->accel->IntersectP(ray) ? 1 : 0;
+        }
+    });
+    return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+}
+
+// Exhaustive loop over every shape with pbrt's own Shape::Intersect, each against the ORIGINAL
+// [tmin,tmax] (no shrinking), winner = (min t, then min prim index).  nties counts rays whose
+// winning t is shared by >1 primitive (where pbrt's BVH answer depends on traversal order).
+double ref_intersect_brute(void *h, int64_t nrays, const float *rays, float *t_out, int *prim_out,
+                           int64_t *nties, int nthreads) {
+    RefScene *s = (RefScene *)h;
+    std::vector<int64_t> ties(std::max(1, nthreads) + 1, 0);
+    int64_t chunk = nthreads > 1 ? (nrays + nthreads - 1) / nthreads : nrays;
+    auto t0 = std::chrono::steady_clock::now();
+    parallel_for(nrays, nthreads, [&, chunk](int64_t lo, int64_t hi) {
+        int64_t myties = 0;
+        for (int64_t i = lo; i < hi; ++i) {
+            const float *r = rays + 8 * i;
+            Ray ray(Point(r[0], r[1], r[2]), Vector(r[4], r[5], r[6]), r[3], r[7]);
+            float best = INFINITY; int bp = -1; int cnt = 0;
+            for (size_t k = 0; k < s->shapes.size(); ++k) {
+                float t, eps; DifferentialGeometry dg;
+                if (s->shapes[k]->Intersect(ray, &t, &eps, &dg)) {
+                    if (t < best) { best = t; bp = (int)k; cnt = 1; }
+                    else if (t == best) ++cnt;
+                }
+            }
+            t_out[i] = best; prim_out[i] = bp;
+            if (cnt > 1) ++myties;
+        }
+        ties[chunk ? lo / chunk : 0] = myties;
+    });
+    if (nties) { *nties = 0; for (auto v : ties) *nties += v; }
+    return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+}
+
+int ref_num_cores() { return NumSystemCores(); }
+
+}  // extern "C"
