@@ -1,0 +1,230 @@
+"""ctypes binding of the b2rt C ABI (include/b2rt.h) -- used by tests/ and bench.py.
+
+This is NOT the product's host layer (that is the C++ shim implementing the reference's
+cuda_render/cudaapi.h:8-19 on top of the same C ABI); it only loads libb2rt.so and forwards.
+There is no fallback of any kind: if the library is missing or no B200 is visible, calls raise.
+"""
+import ctypes as C
+import os
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libb2rt.so")
+
+HOST, DEVICE = 0, 1
+MAT_MATTE, MAT_MIRROR, MAT_GLASS = 0, 1, 2
+LIGHT_POINT, LIGHT_DISK_AREA = 0, 1
+
+RAY_DTYPE = np.dtype([("o", np.float32, 3), ("tmin", np.float32), ("d", np.float32, 3), ("tmax", np.float32)])
+HIT_DTYPE = np.dtype([("t", np.float32), ("prim", np.int32), ("b1", np.float32), ("b2", np.float32)])
+
+
+class AccelInfo(C.Structure):
+    _fields_ = [("n_prims", C.c_int32), ("n_tris", C.c_int32), ("n_wide_nodes", C.c_int32),
+                ("n_leaf_slots", C.c_int32), ("max_depth", C.c_int32), ("wide_width", C.c_int32),
+                ("bounds", C.c_float * 6), ("sah_cost", C.c_float), ("build_ms", C.c_float)]
+
+
+class B2rtError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"b2rt error {code}: {msg}")
+        self.code = code
+
+
+# every symbol include/b2rt.h declares (tests check the .so exports exactly these)
+SYMBOLS = [
+    "b2rt_create", "b2rt_destroy", "b2rt_last_error", "b2rt_device_count", "b2rt_add_mesh", "b2rt_add_sphere",
+    "b2rt_add_disk", "b2rt_add_material", "b2rt_add_light", "b2rt_clear_scene", "b2rt_build_accel",
+    "b2rt_accel_info_get", "b2rt_accel_download", "b2rt_trace_closest", "b2rt_trace_any", "b2rt_sort_pairs",
+    "b2rt_sync", "b2rt_timer_start", "b2rt_timer_stop", "b2rt_launch_count", "b2rt_stream",
+]
+
+_lib = None
+
+
+def load():
+    """Load libb2rt.so (built by __graft_entry__.build()).  Raises if it is missing."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise FileNotFoundError(f"{LIB_PATH} not built: run `python -c 'import __graft_entry__ as g; g.build()'`")
+    lib = C.CDLL(LIB_PATH)
+    vp, i32, i64, fp = C.c_void_p, C.c_int32, C.c_int64, C.POINTER(C.c_float)
+    ip = C.POINTER(C.c_int32)
+    lib.b2rt_create.argtypes = [C.c_int, C.c_uint64, C.POINTER(vp)]
+    lib.b2rt_destroy.argtypes = [vp]
+    lib.b2rt_destroy.restype = None
+    lib.b2rt_last_error.argtypes = [vp]
+    lib.b2rt_last_error.restype = C.c_char_p
+    lib.b2rt_device_count.argtypes = []
+    lib.b2rt_add_mesh.argtypes = [vp, i32, vp, i32, vp, vp, vp, i32, i32, ip]
+    lib.b2rt_add_sphere.argtypes = [vp, vp, vp, C.c_float, i32, i32, ip]
+    lib.b2rt_add_disk.argtypes = [vp, vp, vp, C.c_float, C.c_float, C.c_float, i32, i32, ip]
+    lib.b2rt_add_material.argtypes = [vp, i32, vp, vp, C.c_float, ip]
+    lib.b2rt_add_light.argtypes = [vp, i32, vp, vp, i32, i32, ip]
+    lib.b2rt_clear_scene.argtypes = [vp]
+    lib.b2rt_build_accel.argtypes = [vp]
+    lib.b2rt_accel_info_get.argtypes = [vp, C.POINTER(AccelInfo)]
+    lib.b2rt_accel_download.argtypes = [vp] + [vp] * 7
+    lib.b2rt_trace_closest.argtypes = [vp, i64, vp, vp, C.c_int]
+    lib.b2rt_trace_any.argtypes = [vp, i64, vp, vp, C.c_int]
+    lib.b2rt_sort_pairs.argtypes = [vp, i64, vp, vp, C.c_int]
+    lib.b2rt_sync.argtypes = [vp]
+    lib.b2rt_timer_start.argtypes = [vp]
+    lib.b2rt_timer_stop.argtypes = [vp, fp]
+    lib.b2rt_launch_count.argtypes = [vp, C.POINTER(i64), C.c_int]
+    lib.b2rt_stream.argtypes = [vp]
+    lib.b2rt_stream.restype = vp
+    _lib = lib
+    return lib
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def _f32(a, shape=None):
+    a = np.ascontiguousarray(a, dtype=np.float32)
+    if shape is not None:
+        a = a.reshape(shape)
+    return a
+
+
+class Context:
+    """One b2rt context = one GPU (the reference's CudaRender singleton, cuda_render/cudaapi.cpp:3)."""
+
+    def __init__(self, device=0, seed=0):
+        self.lib = load()
+        h = C.c_void_p()
+        rc = self.lib.b2rt_create(device, seed, C.byref(h))
+        if rc:
+            raise B2rtError(rc, self.lib.b2rt_last_error(None).decode())
+        self.h = h
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.b2rt_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _ck(self, rc):
+        if rc:
+            raise B2rtError(rc, self.lib.b2rt_last_error(self.h).decode())
+
+    # ---- scene --------------------------------------------------------------------------------
+    def add_mesh(self, P, idx, material=-1, arealight=-1):
+        P = _f32(P, (-1, 3))
+        idx = np.ascontiguousarray(idx, dtype=np.int32).reshape(-1, 3)
+        first = C.c_int32()
+        self._ck(self.lib.b2rt_add_mesh(self.h, len(P), _ptr(P), len(idx), _ptr(idx), None, None, material,
+                                        arealight, C.byref(first)))
+        return first.value
+
+    def add_sphere(self, o2w, radius, w2o=None, material=-1, arealight=-1):
+        o2w = _f32(o2w, (12,))
+        w2o = None if w2o is None else _f32(w2o, (12,))
+        p = C.c_int32()
+        self._ck(self.lib.b2rt_add_sphere(self.h, _ptr(o2w), _ptr(w2o), radius, material, arealight, C.byref(p)))
+        return p.value
+
+    def add_disk(self, o2w, height, radius, inner=0.0, w2o=None, material=-1, arealight=-1):
+        o2w = _f32(o2w, (12,))
+        w2o = None if w2o is None else _f32(w2o, (12,))
+        p = C.c_int32()
+        self._ck(self.lib.b2rt_add_disk(self.h, _ptr(o2w), _ptr(w2o), height, radius, inner, material, arealight,
+                                        C.byref(p)))
+        return p.value
+
+    def add_material(self, mtype, rgb, kt=None, ior=1.5):
+        rgb = _f32(rgb, (3,))
+        kt = None if kt is None else _f32(kt, (3,))
+        m = C.c_int32()
+        self._ck(self.lib.b2rt_add_material(self.h, mtype, _ptr(rgb), _ptr(kt), ior, C.byref(m)))
+        return m.value
+
+    def add_light(self, ltype, rgb, p=None, prim=-1, nsamples=1):
+        rgb = _f32(rgb, (3,))
+        p = None if p is None else _f32(p, (3,))
+        l = C.c_int32()
+        self._ck(self.lib.b2rt_add_light(self.h, ltype, _ptr(p), _ptr(rgb), prim, nsamples, C.byref(l)))
+        return l.value
+
+    def clear_scene(self):
+        self._ck(self.lib.b2rt_clear_scene(self.h))
+
+    # ---- accel --------------------------------------------------------------------------------
+    def build_accel(self):
+        self._ck(self.lib.b2rt_build_accel(self.h))
+        return self.accel_info()
+
+    def accel_info(self):
+        info = AccelInfo()
+        self._ck(self.lib.b2rt_accel_info_get(self.h, C.byref(info)))
+        return info
+
+    def accel_download(self):
+        info = self.accel_info()
+        n, nw = info.n_prims, info.n_wide_nodes
+        out = {
+            "morton": np.zeros(n, np.uint32), "prim_order": np.zeros(n, np.int32),
+            "bin_parent": np.zeros(max(2 * n - 1, 0), np.int32), "bin_child": np.zeros(max(2 * (n - 1), 0), np.int32),
+            "bin_box": np.zeros((max(2 * n - 1, 0), 6), np.float32), "wide_nodes": np.zeros((nw, 32), np.uint32),
+            "leaf_prims": np.zeros(n, np.int32),
+        }
+        self._ck(self.lib.b2rt_accel_download(self.h, *[_ptr(out[k]) for k in (
+            "morton", "prim_order", "bin_parent", "bin_child", "bin_box", "wide_nodes", "leaf_prims")]))
+        return out
+
+    # ---- rays ---------------------------------------------------------------------------------
+    def trace_closest(self, rays):
+        """Host-buffer call: rays is an (n,8) float32 / RAY_DTYPE array; returns a HIT_DTYPE array."""
+        rays = np.ascontiguousarray(rays)
+        n = rays.shape[0]
+        hits = np.zeros(n, HIT_DTYPE)
+        self._ck(self.lib.b2rt_trace_closest(self.h, n, _ptr(rays), _ptr(hits), HOST))
+        return hits
+
+    def trace_any(self, rays):
+        rays = np.ascontiguousarray(rays)
+        n = rays.shape[0]
+        occ = np.zeros(n, np.uint8)
+        self._ck(self.lib.b2rt_trace_any(self.h, n, _ptr(rays), _ptr(occ), HOST))
+        return occ
+
+    def trace_closest_device(self, nrays, rays_ptr, hits_ptr):
+        self._ck(self.lib.b2rt_trace_closest(self.h, nrays, C.c_void_p(rays_ptr), C.c_void_p(hits_ptr), DEVICE))
+
+    def trace_any_device(self, nrays, rays_ptr, occ_ptr):
+        self._ck(self.lib.b2rt_trace_any(self.h, nrays, C.c_void_p(rays_ptr), C.c_void_p(occ_ptr), DEVICE))
+
+    def sort_pairs_device(self, n, keys_ptr, vals_ptr, key_bits=32):
+        self._ck(self.lib.b2rt_sort_pairs(self.h, n, C.c_void_p(keys_ptr), C.c_void_p(vals_ptr), key_bits))
+
+    # ---- timing -------------------------------------------------------------------------------
+    def sync(self):
+        self._ck(self.lib.b2rt_sync(self.h))
+
+    def timer_start(self):
+        self._ck(self.lib.b2rt_timer_start(self.h))
+
+    def timer_stop(self):
+        ms = C.c_float()
+        self._ck(self.lib.b2rt_timer_stop(self.h, C.byref(ms)))
+        return ms.value
+
+    def launch_count(self, reset=False):
+        n = C.c_int64()
+        self._ck(self.lib.b2rt_launch_count(self.h, C.byref(n), int(reset)))
+        return n.value
+
+    @property
+    def stream(self):
+        return self.lib.b2rt_stream(self.h)

@@ -1,0 +1,151 @@
+"""Procedural synthetic inputs: everything is generated from a seed, no assets.
+
+Cfg2 = 1 M-triangle fbm heightfield + primary / shadow / incoherent ray sets.
+Cfg4 = same generator at 2000x2000 (8 M triangles).
+"""
+import numpy as np
+
+
+def _hash2(ix, iz, seed):
+    """32-bit integer hash of a lattice point -> float in [0,1)."""
+    h = (ix.astype(np.uint64) * np.uint64(0x9E3779B1) + iz.astype(np.uint64) * np.uint64(0x85EBCA77)
+         + np.uint64(seed) * np.uint64(0xC2B2AE3D)) & np.uint64(0xFFFFFFFF)
+    h ^= h >> np.uint64(15)
+    h = (h * np.uint64(0x2C1B3C6D)) & np.uint64(0xFFFFFFFF)
+    h ^= h >> np.uint64(12)
+    h = (h * np.uint64(0x297A2D39)) & np.uint64(0xFFFFFFFF)
+    h ^= h >> np.uint64(15)
+    return (h & np.uint64(0xFFFFFF)).astype(np.float64) / float(1 << 24)
+
+
+def _value_noise(x, z, seed):
+    x0 = np.floor(x).astype(np.int64)
+    z0 = np.floor(z).astype(np.int64)
+    fx, fz = x - x0, z - z0
+    sx, sz = fx * fx * (3 - 2 * fx), fz * fz * (3 - 2 * fz)
+    a = _hash2(x0, z0, seed)
+    b = _hash2(x0 + 1, z0, seed)
+    c = _hash2(x0, z0 + 1, seed)
+    d = _hash2(x0 + 1, z0 + 1, seed)
+    return (a * (1 - sx) + b * sx) * (1 - sz) + (c * (1 - sx) + d * sx) * sz
+
+
+def fbm(x, z, seed=1234, octaves=4):
+    v = np.zeros_like(x, dtype=np.float64)
+    amp, freq = 0.5, 4.0
+    for o in range(octaves):
+        v += amp * (_value_noise(x * freq, z * freq, seed + o) * 2 - 1)
+        amp *= 0.5
+        freq *= 2.0
+    return v
+
+
+def heightfield_mesh(nx, nz, ntris=None, seed=1234, shuffle=True):
+    """(nx+1)x(nz+1) vertex grid over [-1,1]^2, y = 0.15*fbm; 2*nx*nz triangles (+ a 2-triangle ground quad
+    at the end), trimmed to exactly `ntris`, triangle order shuffled (seeded) so it is not spatially sorted."""
+    xs = np.linspace(-1.0, 1.0, nx + 1)
+    zs = np.linspace(-1.0, 1.0, nz + 1)
+    X, Z = np.meshgrid(xs, zs, indexing="xy")          # (nz+1, nx+1)
+    Y = 0.15 * fbm(X, Z, seed)
+    P = np.stack([X, Y, Z], -1).reshape(-1, 3).astype(np.float32)
+    i = np.arange(nx)[None, :] + (nx + 1) * np.arange(nz)[:, None]
+    a, b, c, d = i, i + 1, i + (nx + 1), i + (nx + 2)
+    tris = np.stack([np.stack([a, c, b], -1), np.stack([b, c, d], -1)], 2).reshape(-1, 3)
+    # ground quad below the terrain
+    g0 = len(P)
+    ground = np.array([[-1.5, -0.4, -1.5], [1.5, -0.4, -1.5], [1.5, -0.4, 1.5], [-1.5, -0.4, 1.5]], np.float32)
+    P = np.concatenate([P, ground])
+    gt = np.array([[g0, g0 + 2, g0 + 1], [g0, g0 + 3, g0 + 2]])
+    if ntris is not None:
+        tris = tris[: ntris - 2]
+    tris = np.concatenate([tris, gt]).astype(np.int32)
+    if shuffle:
+        rng = np.random.default_rng(seed)
+        tris = tris[rng.permutation(len(tris))]
+    return P, np.ascontiguousarray(tris)
+
+
+def cfg2_mesh(ntris=1_000_000, seed=1234):
+    """708x707 grid trimmed to exactly 1 000 000 triangles."""
+    if ntris == 1_000_000:
+        return heightfield_mesh(708, 707, ntris, seed)
+    side = int(np.ceil(np.sqrt(ntris / 2)))
+    return heightfield_mesh(side, side, ntris, seed)
+
+
+def cfg4_mesh(seed=1234):
+    return heightfield_mesh(2000, 2000, 8_000_000, seed)
+
+
+def pack_rays(o, d, tmin, tmax):
+    n = len(o)
+    r = np.empty((n, 8), np.float32)
+    r[:, 0:3] = o
+    r[:, 3] = tmin
+    r[:, 4:7] = d
+    r[:, 7] = tmax
+    return r
+
+
+def pinhole_rays(width, height, eye=(0.0, 1.2, 2.5), look=(0.0, 0.0, 0.0), up=(0.0, 1.0, 0.0), fov=45.0,
+                 spp=1, seed=7):
+    """Primary rays through pixel centres (spp=1) or seeded jitter (spp>1); normalised directions."""
+    eye = np.asarray(eye, np.float64)
+    f = np.asarray(look, np.float64) - eye
+    f /= np.linalg.norm(f)
+    s = np.cross(f, np.asarray(up, np.float64))
+    s /= np.linalg.norm(s)
+    u = np.cross(s, f)
+    th = np.tan(np.radians(fov) / 2)
+    aspect = width / height
+    py, px = np.meshgrid(np.arange(height), np.arange(width), indexing="ij")
+    px = np.repeat(px.reshape(-1), spp).astype(np.float64)
+    py = np.repeat(py.reshape(-1), spp).astype(np.float64)
+    if spp == 1:
+        jx = jy = 0.5
+    else:
+        rng = np.random.default_rng(seed)
+        jx, jy = rng.random(len(px)), rng.random(len(px))
+    sx = (2 * (px + jx) / width - 1) * th * aspect
+    sy = (1 - 2 * (py + jy) / height) * th
+    d = f[None, :] + sx[:, None] * s[None, :] + sy[:, None] * u[None, :]
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    o = np.broadcast_to(eye, d.shape)
+    return pack_rays(o, d, 0.0, np.inf)
+
+
+def incoherent_rays(n, lo, hi, seed=99):
+    """Origins uniform in the box, directions uniform on the sphere (aggregatetest-style,
+    pbrt-v2/src/renderers/aggregatetest.cpp:74-83)."""
+    rng = np.random.default_rng(seed)
+    lo, hi = np.asarray(lo, np.float64), np.asarray(hi, np.float64)
+    o = lo + rng.random((n, 3)) * (hi - lo)
+    z = 1 - 2 * rng.random(n)
+    r = np.sqrt(np.maximum(0, 1 - z * z))
+    phi = 2 * np.pi * rng.random(n)
+    d = np.stack([r * np.cos(phi), r * np.sin(phi), z], -1)
+    return pack_rays(o, d, 0.0, np.inf)
+
+
+def shadow_rays(primary, hits_t, hits_prim, light=(0.5, 3.0, 0.5)):
+    """Segment rays from each primary hit to a point light: d = light - p (unnormalised), tmin 1e-3*t... the
+    reference's form (cuda_render/simple_render/simplerender.cu:65): tmin 1e-3, tmax 1-1e-3 on the segment."""
+    ok = hits_prim >= 0
+    o = primary[ok, 0:3].astype(np.float64) + primary[ok, 4:7].astype(np.float64) * hits_t[ok, None].astype(np.float64)
+    d = np.asarray(light, np.float64)[None, :] - o
+    return pack_rays(o, d, 1e-3, 1.0 - 1e-3)
+
+
+def cornell_geometry():
+    """Appendix D Cornell box as flat arrays: list of (P, idx, rgb) quads + two boxes."""
+    def quad(p):
+        return np.asarray(p, np.float32), np.array([[0, 1, 2], [0, 2, 3]], np.int32)
+    white, red, green = (0.73, 0.73, 0.73), (0.65, 0.05, 0.05), (0.12, 0.45, 0.15)
+    parts = [
+        (*quad([[-1, 0, -1], [1, 0, -1], [1, 0, 1], [-1, 0, 1]]), white),      # floor
+        (*quad([[-1, 2, -1], [-1, 2, 1], [1, 2, 1], [1, 2, -1]]), white),      # ceiling
+        (*quad([[-1, 0, -1], [-1, 2, -1], [1, 2, -1], [1, 0, -1]]), white),    # back
+        (*quad([[-1, 0, -1], [-1, 0, 1], [-1, 2, 1], [-1, 2, -1]]), red),      # left
+        (*quad([[1, 0, -1], [1, 2, -1], [1, 2, 1], [1, 0, 1]]), green),        # right
+    ]
+    return parts

@@ -51,9 +51,14 @@ struct RefScene {
     }
 };
 
-Transform *from12(const float m[12]) {
-    Matrix4x4 M(m[0], m[1], m[2], m[3], m[4], m[5], m[6], m[7], m[8], m[9], m[10], m[11], 0, 0, 0, 1);
-    return new Transform(M);
+Matrix4x4 mat12(const float m[12]) {
+    return Matrix4x4(m[0], m[1], m[2], m[3], m[4], m[5], m[6], m[7], m[8], m[9], m[10], m[11], 0, 0, 0, 1);
+}
+// o2w and w2o are both caller-supplied so the GPU library and pbrt see the very same floats
+void make_xforms(RefScene *s, const float o2w[12], const float w2o[12], Transform **t, Transform **ti) {
+    *t = new Transform(mat12(o2w), mat12(w2o));
+    *ti = new Transform(mat12(w2o), mat12(o2w));
+    s->xforms.push_back(*t); s->xforms.push_back(*ti);
 }
 
 template <typename F> void parallel_for(int64_t n, int nthreads, F f) {
@@ -87,21 +92,20 @@ int ref_scene_add_mesh(void *h, int nverts, const float *P, int ntris, const int
     return first;
 }
 
-int ref_scene_add_sphere(void *h, const float o2w[12], float radius) {
+int ref_scene_add_sphere(void *h, const float o2w[12], const float w2o[12], float radius) {
     RefScene *s = (RefScene *)h;
-    Transform *t = from12(o2w);
-    Transform *ti = new Transform(Inverse(*t));
-    s->xforms.push_back(t); s->xforms.push_back(ti);
+    Transform *t, *ti;
+    make_xforms(s, o2w, w2o, &t, &ti);
     int first = (int)s->shapes.size();
     s->push(new Sphere(t, ti, false, radius, -radius, radius, 360.f));
     return first;
 }
 
-int ref_scene_add_disk(void *h, const float o2w[12], float height, float radius, float inner) {
+int ref_scene_add_disk(void *h, const float o2w[12], const float w2o[12], float height, float radius,
+                       float inner) {
     RefScene *s = (RefScene *)h;
-    Transform *t = from12(o2w);
-    Transform *ti = new Transform(Inverse(*t));
-    s->xforms.push_back(t); s->xforms.push_back(ti);
+    Transform *t, *ti;
+    make_xforms(s, o2w, w2o, &t, &ti);
     int first = (int)s->shapes.size();
     s->push(new Disk(t, ti, false, height, radius, inner, 360.f));
     return first;

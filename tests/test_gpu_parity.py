@@ -1,0 +1,208 @@
+"""GPU parity tests (-m gpu): every call goes through the C ABI (libb2rt.so via ctypes).
+Bars: bit-exact for hit primitive ids, hit distances (the primitive tests reproduce pbrt's arithmetic),
+BVH topology, Morton order; occlusion flags exact."""
+import numpy as np
+import pytest
+import torch
+
+from helpers import CASES, load_golden, case_scene, fill, fill_ctx, bits
+from oracle import oracle as O
+from cuda_raytrace_b200 import scenes as S
+
+pytestmark = pytest.mark.gpu
+
+
+def _dev(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+# ---- K2: radix sort -------------------------------------------------------------------------------
+@pytest.mark.parametrize("n,bits_", [(1, 32), (2, 32), (31, 8), (4096, 16), (4097, 32), (100_003, 30),
+                                     (1_000_000, 32), (5_000_000, 24)])
+def test_sort_pairs_matches_stable_sort(ctx, n, bits_):
+    rng = np.random.default_rng(n)
+    eff = 8 * ((bits_ + 7) // 8)
+    keys = rng.integers(0, 2 ** eff, n, dtype=np.uint64).astype(np.uint32)
+    if n > 1000:
+        keys[: n // 3] = keys[n // 2: n // 2 + n // 3]      # plenty of duplicates: stability matters
+    vals = np.arange(n, dtype=np.uint32)
+    dk, dv = _dev(keys.view(np.int32)), _dev(vals.view(np.int32))
+    ctx.sort_pairs_device(n, dk.data_ptr(), dv.data_ptr(), bits_)
+    ctx.sync()
+    order = np.argsort(keys, kind="stable")
+    assert np.array_equal(dv.cpu().numpy().view(np.uint32), order.astype(np.uint32))
+    assert np.array_equal(dk.cpu().numpy().view(np.uint32), keys[order])
+    ek, ev = O.sort_pairs(keys, vals, bits_)
+    assert np.array_equal(ev, dv.cpu().numpy().view(np.uint32))
+
+
+# ---- K1/K3/K4: builder topology, bit-exact against the CPU restatement ----------------------------------
+def _tri_only_ctx(ctx, P, idx):
+    ctx.clear_scene()
+    ctx.add_mesh(P, idx)
+    return ctx.build_accel()
+
+
+@pytest.mark.parametrize("shape", [(1, 1), (3, 2), (12, 9), (40, 40), (224, 224)])
+def test_lbvh_bit_exact_vs_restatement(ctx, shape):
+    P, idx = S.heightfield_mesh(shape[0], shape[1], None, seed=11)
+    info = _tri_only_ctx(ctx, P, idx)
+    got = ctx.accel_download()
+    ps = O.PortScene()
+    ps.add_mesh(P, idx)
+    exp = O.lbvh_build(ps.tri_boxes())
+    n = len(idx)
+    assert info.n_prims == n
+    assert np.array_equal(got["morton"], exp["morton"])
+    assert np.array_equal(got["prim_order"], exp["prim_order"])
+    assert np.array_equal(got["leaf_prims"], exp["prim_order"])
+    assert np.array_equal(got["bin_parent"], exp["bin_parent"])
+    assert np.array_equal(got["bin_child"], exp["bin_child"])
+    assert np.array_equal(bits(got["bin_box"]), bits(exp["bin_box"]))
+    assert got["wide_nodes"].shape == exp["wide_nodes"].shape
+    assert np.array_equal(got["wide_nodes"], exp["wide_nodes"])
+
+
+def test_lbvh_degenerate_and_tiny(ctx):
+    # one triangle; two identical triangles; 50 identical triangles (all Morton codes equal)
+    tri = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0]], np.float32)
+    for copies in (1, 2, 50):
+        P = np.tile(tri, (copies, 1))
+        idx = np.arange(3 * copies, dtype=np.int32).reshape(-1, 3)
+        info = _tri_only_ctx(ctx, P, idx)
+        got = ctx.accel_download()
+        ps = O.PortScene()
+        ps.add_mesh(P, idx)
+        exp = O.lbvh_build(ps.tri_boxes())
+        assert np.array_equal(got["wide_nodes"], exp["wide_nodes"])
+        rays = S.pack_rays(np.array([[0.2, 0.2, 1.0]]), np.array([[0, 0, -1.0]]), 0.0, np.inf)
+        h = ctx.trace_closest(rays)
+        assert h["prim"][0] == 0 and h["t"][0] == 1.0      # ties -> min prim id
+    # empty scene: builds, everything misses
+    ctx.clear_scene()
+    ctx.build_accel()
+    h = ctx.trace_closest(rays)
+    assert h["prim"][0] == -1 and np.isinf(h["t"][0])
+    assert ctx.trace_any(rays)[0] == 0
+    assert len(ctx.trace_closest(np.zeros((0, 8), np.float32))) == 0
+
+
+def test_build_is_deterministic_across_runs(ctx):
+    P, idx = S.cfg2_mesh(100_000)
+    _tri_only_ctx(ctx, P, idx)
+    a = ctx.accel_download()
+    for _ in range(2):
+        _tri_only_ctx(ctx, P, idx)
+        b = ctx.accel_download()
+        for k in a:
+            assert np.array_equal(a[k].view(np.uint32) if a[k].dtype == np.float32 else a[k],
+                                  b[k].view(np.uint32) if b[k].dtype == np.float32 else b[k]), k
+
+
+# ---- K5: traversal vs the reference's golden vectors and the oracle ---------------------------------
+@pytest.mark.parametrize("name", CASES)
+def test_trace_matches_reference_golden(ctx, name):
+    g = load_golden(name)
+    fill_ctx(ctx, case_scene(name))
+    ctx.build_accel()
+    rays = g["rays"]
+    hits = ctx.trace_closest(rays)
+    # distances: bit-identical to pbrt BVHAccel::Intersect on every ray
+    assert np.array_equal(bits(hits["t"]), bits(g["bvh_t"]))
+    # ids: identical to pbrt's exhaustive loop (min t, min id) where it was run ...
+    sel = g["brute_sel"]
+    assert np.array_equal(hits["prim"][sel], g["brute_prim"])
+    # ... and to pbrt's BVH except on exact-t ties
+    assert int((hits["prim"] != g["bvh_prim"]).sum()) <= int(g["nties"])
+    miss = hits["prim"] < 0
+    assert np.array_equal(miss, g["bvh_prim"] < 0)
+    # barycentrics against pbrt's (u,v) = (b1+b2, b2)
+    same = (hits["prim"] == g["bvh_prim"]) & (hits["prim"] >= 0) & (hits["b1"] + hits["b2"] != 0)
+    tri = same & (g["bvh_uv"][:, 0] == hits["b1"] + hits["b2"])
+    assert tri.sum() >= 0.95 * ((hits["b1"] != 0) | (hits["b2"] != 0)).sum()
+    # any-hit == pbrt IntersectP
+    occ = ctx.trace_any(rays)
+    assert np.array_equal(occ, g["occluded"])
+
+
+def test_trace_bit_exact_vs_oracle_random_scenes(ctx):
+    for seed, (nx, nz) in enumerate([(5, 7), (33, 20), (90, 90)]):
+        P, idx = S.heightfield_mesh(nx, nz, None, seed=100 + seed)
+        ps = O.PortScene()
+        ps.add_mesh(P, idx)
+        _tri_only_ctx(ctx, P, idx)
+        rays = np.concatenate([S.incoherent_rays(3000, [-1.3, -0.5, -1.3], [1.3, 0.8, 1.3], seed=seed),
+                               S.pinhole_rays(40, 30)])
+        # finite segments too
+        rays[::3, 7] = 0.8
+        rays[::5, 3] = 0.05
+        t, prim, b1, b2 = ps.intersect(rays, 8)
+        h = ctx.trace_closest(rays)
+        assert np.array_equal(h["prim"], prim)
+        assert np.array_equal(bits(h["t"]), bits(t))
+        assert np.array_equal(bits(h["b1"]), bits(b1)) and np.array_equal(bits(h["b2"]), bits(b2))
+        assert np.array_equal(ctx.trace_any(rays), ps.occluded(rays, 8))
+
+
+def test_device_pointer_path_equals_host_path(ctx):
+    P, idx = S.cfg2_mesh(100_000)
+    _tri_only_ctx(ctx, P, idx)
+    rays = S.pinhole_rays(320, 180)
+    h = ctx.trace_closest(rays)
+    d_r = _dev(rays)
+    d_h = torch.zeros((len(rays), 4), dtype=torch.float32, device="cuda")
+    d_o = torch.zeros(len(rays), dtype=torch.uint8, device="cuda")
+    ctx.trace_closest_device(len(rays), d_r.data_ptr(), d_h.data_ptr())
+    ctx.trace_any_device(len(rays), d_r.data_ptr(), d_o.data_ptr())
+    ctx.sync()
+    got = d_h.cpu().numpy().view(h.dtype).reshape(-1)
+    assert np.array_equal(got["prim"], h["prim"]) and np.array_equal(bits(got["t"]), bits(h["t"]))
+    assert np.array_equal(d_o.cpu().numpy(), (h["prim"] >= 0).astype(np.uint8))
+
+
+# ---- full-size properties (BASELINE Cfg2: 1 M triangles, 1920x1080) ------------------------------------
+def test_cfg2_full_size_properties(ctx):
+    P, idx = S.cfg2_mesh()
+    assert len(idx) == 1_000_000
+    info = _tri_only_ctx(ctx, P, idx)
+    assert info.n_prims == 1_000_000
+    acc = ctx.accel_download()
+    # Morton order sorted; prim order is a permutation; leaf coverage exact
+    assert (np.diff(acc["morton"].astype(np.int64)) >= 0).all()
+    assert np.array_equal(np.sort(acc["prim_order"]), np.arange(1_000_000, dtype=np.int32))
+    refs = acc["wide_nodes"][:, 24:28].reshape(-1)
+    leaf = refs[(refs & 0x80000000) != 0]
+    first, cnt = (leaf & 0x7FFFFFFF) >> 3, (leaf & 7) + 1
+    cover = np.zeros(1_000_001, np.int64)
+    np.add.at(cover, first, 1)
+    np.add.at(cover, first + cnt, -1)
+    assert (np.cumsum(cover)[:-1] == 1).all()
+    # primary rays: each hit point re-derived from (prim, b1, b2) lies on the ray at distance t
+    rays = S.pinhole_rays(1920, 1080)
+    h = ctx.trace_closest(rays)
+    ok = h["prim"] >= 0
+    assert ok.mean() > 0.5
+    tri = idx[h["prim"][ok]]
+    p1, p2, p3 = P[tri[:, 0]].astype(np.float64), P[tri[:, 1]].astype(np.float64), P[tri[:, 2]].astype(np.float64)
+    b1, b2 = h["b1"][ok, None].astype(np.float64), h["b2"][ok, None].astype(np.float64)
+    ph = (1 - b1 - b2) * p1 + b1 * p2 + b2 * p3
+    pr = rays[ok, 0:3].astype(np.float64) + rays[ok, 4:7].astype(np.float64) * h["t"][ok, None].astype(np.float64)
+    assert np.abs(ph - pr).max() < 2e-4
+    # idempotence + any-hit consistency: occluded <=> closest hit exists
+    h2 = ctx.trace_closest(rays)
+    assert np.array_equal(h2.view(np.uint32), h.view(np.uint32))
+    assert np.array_equal(ctx.trace_any(rays), ok.astype(np.uint8))
+    # shadow rays toward the light: a segment clipped just before its own hit point is never blocked by
+    # geometry farther than the segment
+    sh = S.shadow_rays(rays, h["t"], h["prim"])
+    occ = ctx.trace_any(sh)
+    hs = ctx.trace_closest(sh)
+    assert np.array_equal(occ, (hs["prim"] >= 0).astype(np.uint8))
+    assert (hs["t"][hs["prim"] >= 0] <= sh[hs["prim"] >= 0, 7]).all()
+    # a sample of rays against the exhaustive oracle (1 M triangles x 300 rays)
+    rng = np.random.default_rng(1)
+    sel = rng.choice(len(rays), 300, replace=False)
+    ps = O.PortScene()
+    ps.add_mesh(P, idx)
+    t, prim, _, _ = ps.intersect(rays[sel], 8)
+    assert np.array_equal(h["prim"][sel], prim) and np.array_equal(bits(h["t"][sel]), bits(t))
