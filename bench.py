@@ -1,0 +1,376 @@
+#!/usr/bin/env python
+"""bench.py -- the driver contract (one JSON line on stdout, rank 0).
+
+Workload (N=1): BASELINE.json configs[1] = "Synthetic 1M-triangle procedural mesh, 1920x1080 primary+shadow
+rays 1 spp (intersection throughput)" -- SURVEY.md 8(d) Cfg2.  One step = one pass of the hot path over one
+frame's rays: closest-hit over the 2 073 600 primary rays, then any-hit over the shadow rays of every primary
+hit (the reference's SimpleRenderer frame, cuda_render/simple_render/simplerender.cu:22-28,47-78).
+
+  value      Mrays/s = (primary + shadow rays of all ranks) / max-over-ranks device time, rays resident in HBM
+  e2e        same metric through the C ABI with HOST (pinned) buffers: b2rt_trace_closest/any(..., B2RT_HOST)
+             copy the rays in and the hits / occlusion flags out inside the timed region
+  roofline   dominant kernel = trace_kernel<closest>; algorithmic bytes = 48 B/ray (32 in + 16 out)
+  cpu_baseline  the reference's own CPU path (pbrt-v2 BVHAccel::Intersect/IntersectP from oracle/_ref, built from
+             /root/reference in the build container) on the same rays, all host threads; falls back to nothing
+             else -- if oracle/_ref is absent the C port's exhaustive loop is timed on a small sample ("port")
+
+N>1 (torchrun): weak scaling, no data-path collective -- rank r traces sample r of every pixel (its own
+1920x1080 ray set with a rank-specific sub-pixel offset) against its own replicated, deterministic BVH.
+
+--impl reference: times the reference's CPU implementation of the same step on the host cores (rank 0 only).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "Mrays/s (closest-hit primary + any-hit shadow rays, 1M-triangle scene, 1920x1080, 1 spp)"
+LIGHT = (0.5, 3.0, 0.5)
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--tris", type=int, default=1_000_000)
+    ap.add_argument("--width", type=int, default=1920)
+    ap.add_argument("--height", type=int, default=1080)
+    ap.add_argument("--cpu-sample", type=int, default=0, help="rays in the cpu_baseline sample (0 = auto)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def make_workload(args, rank):
+    from cuda_raytrace_b200 import scenes as S
+    P, idx = S.cfg2_mesh(args.tris)
+    if rank == 0:
+        rays = S.pinhole_rays(args.width, args.height)          # pixel centres
+    else:
+        rays = S.pinhole_rays(args.width, args.height, spp=2, seed=1000 + rank)[::2].copy()  # jittered sample
+    return P, idx, rays
+
+
+class ClockSampler:
+    """nvidia-smi clocks line of /opt/skills/guides/B200_PROFILING.md, sampled during the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, smax, power, reasons = [], [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); smax.append(float(f[2])); power.append(float(f[3]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(smax) if smax else None,
+                "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def cpu_reference_step(P, idx, rays, shadow, nthreads, sample=None):
+    """The reference's CPU path on (a sample of) one step.  Returns dict(value Mrays/s, kind, cores, sample)."""
+    from oracle import oracle as O
+    if O.ref_available():
+        rs = O.RefScene()
+        rs.add_mesh(P, idx)
+        build_s = rs.build()
+        nth = nthreads or rs.num_cores()
+        r1 = rays if sample is None else rays[:: max(1, len(rays) // sample)]
+        r2 = shadow if sample is None else shadow[:: max(1, len(shadow) // sample)]
+        rs.intersect(r1[: 20000], nth)                                   # warm the page cache / threads
+        _, _, _, s1 = rs.intersect(r1, nth)
+        _, s2 = rs.occluded(r2, nth)
+        rs.close()
+        n = len(r1) + len(r2)
+        return {"value": n / (s1 + s2) / 1e6, "unit": "Mrays/s", "cores": nth, "kind": "reference",
+                "sample": "%d primary (BVHAccel::Intersect) + %d shadow (IntersectP) rays of the step, pbrt-v2 "
+                          "BVHAccel built in %.2f s (excluded)" % (len(r1), len(r2), build_s),
+                "closest_mrays": len(r1) / s1 / 1e6, "any_mrays": len(r2) / s2 / 1e6, "seconds": s1 + s2}
+    # port: exhaustive loop over all prims -- O(n_prims) per ray, so only a tiny sample
+    ps = O.PortScene()
+    ps.add_mesh(P, idx)
+    k = 64 if sample is None else max(16, min(sample, 256))
+    r1 = rays[:: max(1, len(rays) // k)]
+    nth = nthreads or os.cpu_count()
+    t0 = time.perf_counter()
+    ps.intersect(r1, nth)
+    s = time.perf_counter() - t0
+    return {"value": len(r1) / s / 1e6, "unit": "Mrays/s", "cores": nth, "kind": "port",
+            "sample": "%d primary rays, exhaustive loop over all prims (no CPU BVH in the port)" % len(r1),
+            "seconds": s}
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's CPU implementation of the step, host cores, rank 0 only."""
+    if rank != 0:
+        return
+    P, idx, rays = make_workload(args, 0)
+    from oracle import oracle as O
+    if O.ref_available():
+        rs = O.RefScene()
+        rs.add_mesh(P, idx)
+        build_s = rs.build()
+        nth = rs.num_cores()
+        t, prim, _, _ = rs.intersect(rays, nth)
+        from cuda_raytrace_b200 import scenes as S
+        shadow = S.shadow_rays(rays, t, prim, LIGHT)
+        for _ in range(args.warmup):
+            rs.intersect(rays, nth); rs.occluded(shadow, nth)
+        secs = []
+        for _ in range(args.steps):
+            _, _, _, s1 = rs.intersect(rays, nth)
+            _, s2 = rs.occluded(shadow, nth)
+            secs.append(s1 + s2)
+        rs.close()
+        total = sum(secs)
+        nrays = len(rays) + len(shadow)
+        v = nrays * args.steps / total / 1e6
+        kind, sample = "reference", ("full step: %d primary + %d shadow rays through pbrt-v2 BVHAccel "
+                                     "(built in %.2f s, excluded)" % (len(rays), len(shadow), build_s))
+    else:
+        cb = cpu_reference_step(P, idx, rays, rays, None, sample=64)
+        v, nth, kind, sample, total = cb["value"], cb["cores"], cb["kind"], cb["sample"], cb["seconds"]
+        args.steps = 1
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "Mrays/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": total / args.steps * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(args, len(idx)),
+            "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": nth, "kind": kind, "sample": sample},
+            "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, ntris):
+    return {"workload": "Cfg2: %d-triangle fbm heightfield (seed 1234, shuffled), %dx%d pinhole primary rays 1 spp + "
+                        "one shadow ray per hit to a point light" % (ntris, args.width, args.height),
+            "cache": "L2 flushed between timed steps (256 MiB write); step working set ~220 MB > 126 MB L2",
+            "sharding": "rank r traces sample r of every pixel against its own replicated BVH (no collective)"}
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        return run_reference(args, rank, world)
+
+    import torch
+    import torch.distributed as dist
+    from cuda_raytrace_b200 import b2rt, scenes as S
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the b2rt path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    P, idx, rays = make_workload(args, rank)
+    n1 = len(rays)
+    ctx = b2rt.Context(local_rank, seed=1)
+    ctx.add_mesh(P, idx)
+    info = ctx.build_accel()
+    stream = torch.cuda.ExternalStream(ctx.stream, device=local_rank)
+
+    # primary hits once (host path) -> shadow rays, the simple renderer's second ray type
+    hits0 = ctx.trace_closest(rays)
+    shadow = S.shadow_rays(rays, hits0["t"], hits0["prim"], LIGHT)
+    n2 = len(shadow)
+
+    with torch.cuda.stream(stream):
+        d_rays = torch.from_numpy(rays).cuda(non_blocking=False)
+        d_shadow = torch.from_numpy(shadow).cuda(non_blocking=False)
+        d_hits = torch.empty((n1, 4), dtype=torch.float32, device="cuda")
+        d_occ = torch.empty(n2, dtype=torch.uint8, device="cuda")
+        flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    ctx.sync()
+
+    def step_device():
+        ctx.trace_closest_device(n1, d_rays.data_ptr(), d_hits.data_ptr())
+        ctx.trace_any_device(n2, d_shadow.data_ptr(), d_occ.data_ptr())
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def flush_l2():
+        with torch.cuda.stream(stream):
+            flush.fill_(1)
+
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    for _ in range(max(args.warmup, 3)):
+        flush_l2(); step_device()
+    ctx.sync()
+    # a step is < 1 ms, nvidia-smi samples every 100 ms: keep the SAME load running (untimed) before and after
+    # the timed steps so that the clock samples bracket the timed region under identical load
+    def soak(seconds, min_samples):
+        t_end = time.perf_counter() + seconds
+        while time.perf_counter() < t_end or (rank == 0 and sampler.proc and len(sampler.lines) < min_samples
+                                              and time.perf_counter() < t_end + 5.0):
+            for _ in range(20):
+                flush_l2(); step_device()
+            ctx.sync()
+    soak(1.0, 3)
+
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(args.steps)]
+    ctx.launch_count(reset=True)
+    barrier()
+    wall0 = time.perf_counter()
+    for k in range(args.steps):
+        flush_l2()
+        ev[k][0].record(stream)
+        ctx.trace_closest_device(n1, d_rays.data_ptr(), d_hits.data_ptr())
+        ev[k][1].record(stream)
+        ctx.trace_any_device(n2, d_shadow.data_ptr(), d_occ.data_ptr())
+        ev[k][2].record(stream)
+    ctx.sync()
+    barrier()
+    wall = time.perf_counter() - wall0
+    launches = ctx.launch_count()
+    soak(0.4, 0)
+    clocks = sampler.stop() if rank == 0 else None
+    ms_closest = sum(e[0].elapsed_time(e[1]) for e in ev)
+    ms_any = sum(e[1].elapsed_time(e[2]) for e in ev)
+    ms_total = ms_closest + ms_any
+
+    # ---- extra (not part of `value`): incoherent closest-hit rays, the aggregatetest distribution ----------------
+    inc = S.incoherent_rays(n1, info.bounds[0:3], info.bounds[3:6], seed=99 + rank)
+    with torch.cuda.stream(stream):
+        d_inc = torch.from_numpy(inc).cuda()
+    e_inc = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    for _ in range(2):
+        ctx.trace_closest_device(n1, d_inc.data_ptr(), d_hits.data_ptr())
+    flush_l2()
+    e_inc[0].record(stream)
+    for _ in range(5):
+        ctx.trace_closest_device(n1, d_inc.data_ptr(), d_hits.data_ptr())
+    e_inc[1].record(stream)
+    ctx.sync()
+    inc_mrays = 5 * n1 / (e_inc[0].elapsed_time(e_inc[1]) * 1e-3) / 1e6
+    del d_inc
+    ctx.trace_closest_device(n1, d_rays.data_ptr(), d_hits.data_ptr())   # restore d_hits for the parity guard
+    ctx.sync()
+
+    # ---- e2e: the same step through the C ABI with host (pinned) buffers --------------------------------------
+    h_rays = torch.from_numpy(rays).pin_memory()
+    h_shadow = torch.from_numpy(shadow).pin_memory()
+    h_hits = torch.empty((n1, 4), dtype=torch.float32).pin_memory()
+    h_occ = torch.empty(n2, dtype=torch.uint8).pin_memory()
+    lib, H = ctx.lib, ctx.h
+
+    def step_host():
+        rc = lib.b2rt_trace_closest(H, n1, h_rays.data_ptr(), h_hits.data_ptr(), b2rt.HOST)
+        rc |= lib.b2rt_trace_any(H, n2, h_shadow.data_ptr(), h_occ.data_ptr(), b2rt.HOST)
+        if rc:
+            raise RuntimeError(lib.b2rt_last_error(H).decode())
+
+    for _ in range(3):
+        step_host()
+    e2e_steps = args.steps
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        step_host()                      # each call ends with a stream sync (results are in host memory)
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    barrier()
+    # parity guard on the bench inputs themselves: device and host paths must agree bit for bit
+    assert np.array_equal(h_hits.numpy().view(np.uint32), d_hits.cpu().numpy().view(np.uint32))
+
+    times = torch.tensor([ms_total, ms_closest, ms_any, e2e_s * 1e3], dtype=torch.float64, device="cuda")
+    counts = torch.tensor([n1, n2], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(times, op=dist.ReduceOp.MAX)
+        dist.all_reduce(counts, op=dist.ReduceOp.SUM)
+    ms_total_m, ms_closest_m, ms_any_m, e2e_ms_m = times.tolist()
+    N1, N2 = counts.tolist()
+
+    if rank == 0:
+        peaks = {}
+        pk_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+        if os.path.exists(pk_path):
+            peaks = json.load(open(pk_path))
+        peak = peaks.get("hbm_gbs", 6650.0)
+        peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
+        per_launch_ms = ms_closest / args.steps
+        achieved = 48.0 * n1 / (per_launch_ms * 1e-3) / 1e9
+        value = (N1 + N2) * args.steps / (ms_total_m * 1e-3) / 1e6
+        line = {
+            "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_total_m / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(args, len(idx)),
+            "closest_hit_mrays": N1 * args.steps / (ms_closest_m * 1e-3) / 1e6,
+            "any_hit_mrays": N2 * args.steps / (ms_any_m * 1e-3) / 1e6,
+            "incoherent_closest_hit_mrays": inc_mrays,
+            "rays_per_step": {"closest": int(N1), "any": int(N2)},
+            "accel": {"n_prims": info.n_prims, "wide_nodes": info.n_wide_nodes, "build_ms": info.build_ms,
+                      "sah_cost": info.sah_cost},
+            "e2e": {"value": (N1 + N2) * e2e_steps / (e2e_ms_m * 1e-3) / 1e6, "unit": "Mrays/s",
+                    "h2d_bytes_per_step": int(32 * (n1 + n2)), "d2h_bytes_per_step": int(16 * n1 + n2),
+                    "ms_per_step": e2e_ms_m / e2e_steps, "api": "b2rt_trace_closest/b2rt_trace_any(B2RT_HOST)"},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "kernel": "trace_kernel<closest>", "achieved": achieved, "peak": peak,
+                         "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": 48 * n1,
+                         "note": "traversal is latency/issue bound, not HBM bound (SURVEY 8(d)); see profiles/"},
+            "clocks": clocks, "wall_s_timed_region": wall,
+        }
+        if not args.no_cpu_baseline:
+            smp = args.cpu_sample or None
+            line["cpu_baseline"] = cpu_reference_step(P, idx, rays, shadow, None, sample=smp)
+        print(json.dumps(line), flush=True)
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
