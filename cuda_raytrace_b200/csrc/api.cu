@@ -74,7 +74,12 @@ void b2rt_destroy(b2rt_ctx *ctx) {
                       &ctx->d_bin_cost, &ctx->d_bin_count, &ctx->d_wide_tmp, &ctx->d_wide_flag,
                       &ctx->d_wide_index, &ctx->d_queue_a, &ctx->d_queue_b, &ctx->d_counters,
                       &ctx->d_wide_nodes, &ctx->d_prim_recs, &ctx->d_leaf_prims, &ctx->d_rays, &ctx->d_hits,
-                      &ctx->d_occ, &ctx->d_scan_tmp};
+                      &ctx->d_occ, &ctx->d_scan_tmp, &ctx->d_prim_material, &ctx->d_prim_light, &ctx->d_materials,
+                      &ctx->d_lights, &ctx->d_light_cdf, &ctx->d_slots, &ctx->d_cnt_c, &ctx->d_cnt_i, &ctx->d_grid_box,
+                      &ctx->d_queries, &ctx->d_q_rgb, &ctx->d_q_r2, &ctx->d_q_found, &ctx->d_q_idx};
+    for (PhotonMap &m : ctx->maps) {
+        m.photons.release(); m.sorted.release(); m.cell_start.release(); m.keys.release(); m.order.release();
+    }
     for (DevBuf *b : bufs) b->release();
     cudaEventDestroy(ctx->ev0); cudaEventDestroy(ctx->ev1);
     cudaEventDestroy(ctx->evb0); cudaEventDestroy(ctx->evb1);
@@ -177,6 +182,8 @@ int b2rt_add_light(b2rt_ctx *ctx, int32_t type, const float p[3], const float rg
 int b2rt_build_accel(b2rt_ctx *ctx) {
     if (!ctx) return B2RT_E_ARG;
     B2RT_CUDA(ctx, cudaSetDevice(ctx->device));
+    int rc = b2rt_upload_tables(ctx);
+    if (rc) return rc;
     return b2rt_build_impl(ctx);
 }
 

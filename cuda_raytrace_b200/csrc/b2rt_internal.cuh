@@ -53,7 +53,22 @@ struct AnalyticPrim {
 };
 
 struct Material { int32_t type; float kd[3]; float kt[3]; float ior; };
-struct Light { int32_t type; float p[3]; float rgb[3]; int32_t prim; int32_t nsamples; };
+// analytic/area/n are derived at build time for disk area lights: analytic = index into the analytic table,
+// area = Disk::Area() (shapes/disk.cpp:132-135), n = Normalize(ObjectToWorld(Normal(0,0,1))) (disk.cpp:154)
+struct Light { int32_t type; float p[3]; float rgb[3]; int32_t prim; int32_t nsamples; int32_t analytic; float area; float n[3]; };
+
+// one photon map (caustic or indirect): photons in path order as traced, then the hash-grid built over them
+struct PhotonMap {
+    DevBuf photons;          // b2rt_photon[n], path order (bit-identical for any GPU count)
+    int64_t n = 0;
+    int64_t n_paths = 0;     // paths emitted while this map was still collecting (pbrt nCausticPaths / nIndirectPaths)
+    // grid
+    bool grid_built = false;
+    DevBuf sorted;           // b2rt_photon[n] in (cell key, path-order index) order
+    DevBuf cell_start;       // uint32[n_cells+1]
+    DevBuf keys, order;      // uint32[n] sorted cell keys / original indices (kept for parity downloads)
+    b2rt_grid_info grid{};
+};
 
 struct b2rt_ctx {
     int device = 0;
@@ -87,6 +102,10 @@ struct b2rt_ctx {
     DevBuf d_wide_nodes, d_prim_recs, d_leaf_prims;
     DevBuf d_rays, d_hits, d_occ;  // staging for host-pointer calls
     DevBuf d_scan_tmp;
+    DevBuf d_prim_material, d_prim_light, d_materials, d_lights, d_light_cdf;
+    DevBuf d_slots, d_cnt_c, d_cnt_i, d_grid_box;
+    DevBuf d_queries, d_q_rgb, d_q_r2, d_q_found, d_q_idx;
+    PhotonMap maps[2];       // B2RT_MAP_CAUSTIC, B2RT_MAP_INDIRECT
     b2rt_accel_info info{};
 };
 
@@ -115,5 +134,13 @@ int b2rt_sort_pairs_impl(b2rt_ctx *ctx, int64_t n, uint32_t *keys, uint32_t *val
 int b2rt_build_impl(b2rt_ctx *ctx);
 int b2rt_trace_impl(b2rt_ctx *ctx, int64_t n, const b2rt_ray *d_rays, b2rt_hit *d_hits, uint8_t *d_occ,
                     bool any_hit);
+struct DScene;
+int b2rt_upload_tables(b2rt_ctx *ctx);
+int b2rt_photons_trace_impl(b2rt_ctx *ctx, int64_t first_path, int64_t n_paths, int max_depth, int flags,
+                            int64_t n_stored[2]);
+int b2rt_photon_grid_build_impl(b2rt_ctx *ctx, int map, float cell_size, float target_per_cell);
+int b2rt_gather_impl(b2rt_ctx *ctx, int map, int64_t nq, const b2rt_query *d_queries, int k, float max_dist2,
+                     float *d_rgb, float *d_r2, int32_t *d_found, int32_t *d_idx);
+void b2rt_fill_dscene(b2rt_ctx *ctx, DScene *sc);
 // exclusive scan of n uint32 in place (single pass, small n helper used by build)
 int b2rt_exclusive_scan_u32(b2rt_ctx *ctx, uint32_t *d, int64_t n, uint32_t *d_total);

@@ -1,0 +1,263 @@
+// K12: radiance estimate over the photon hash grid -- k-nearest and fixed-radius modes.
+//
+// Replaces KdTreeLookup / processPhoton / photonGatheringCamera (cuda_render/photon_mapping/gathering.cu:11-126),
+// which walk a CPU-built kd-tree per thread with a private stack.  The estimator is pbrt's LPhoton
+// (pbrt-v2/src/integrators/photonmap.cpp:207-260) for a diffuse surface, not the reference's unweighted PPM sum:
+//   maxDist2 = d2 of the k-th nearest photon if >= k lie within the search radius, else the radius itself
+//   L = INV_PI * Kd * sum_{i in set, Dot(Nf, wi_i) > 0}  (3*INV_PI*(1 - d2_i/maxDist2)^2 / (nPaths*maxDist2)) * alpha_i
+// The set is the k smallest (d2, index-in-sorted-array) pairs with d2 < radius2 -- exactly what pbrt's heap keeps
+// (photonmap.cpp:187-204) up to ties in d2.
+//
+// One warp per query.  Shells of cells around the query's cell are scanned outwards; within a shell each row of
+// x-adjacent cells is one contiguous range of the sorted photon array, read with coalesced 16-byte loads, lanes
+// testing 32 photons at a time.  Candidates (64-bit key = d2 bits << 32 | index) are appended to a per-warp
+// shared-memory buffer by ballot compaction; when it fills, a warp-cooperative bitonic sort keeps the k smallest and
+// tightens the bound.  The scan stops after the first shell whose outer boundary is farther than the bound.
+#include "b2rt_shade.cuh"
+
+namespace {
+
+constexpr int GATHER_WARPS = 4;
+constexpr int GATHER_CAP = 256;          // candidate buffer entries per warp (k <= GATHER_CAP - 32)
+constexpr int GATHER_PER_LANE = GATHER_CAP / 32;
+
+struct GatherGrid {
+    float lo[3]; float cell, inv, slack;
+    int dims[3];
+};
+
+__device__ __forceinline__ uint64_t shfl_xor_u64(uint64_t v, int m) {
+    uint32_t lo = __shfl_xor_sync(0xffffffffu, (uint32_t)v, m), hi = __shfl_xor_sync(0xffffffffu, (uint32_t)(v >> 32), m);
+    return ((uint64_t)hi << 32) | lo;
+}
+
+// ascending bitonic sort of GATHER_CAP keys; element e lives in lane e / PER_LANE, register e % PER_LANE
+__device__ __forceinline__ void warp_sort(uint64_t (&v)[GATHER_PER_LANE], int lane) {
+#pragma unroll
+    for (int size = 2; size <= GATHER_CAP; size <<= 1) {
+#pragma unroll
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+            if (stride >= GATHER_PER_LANE) {
+                const int lm = stride / GATHER_PER_LANE;
+#pragma unroll
+                for (int j = 0; j < GATHER_PER_LANE; ++j) {
+                    const int e = lane * GATHER_PER_LANE + j;
+                    uint64_t o = shfl_xor_u64(v[j], lm);
+                    bool up = (e & size) == 0;            // ascending block
+                    bool lower = (e & stride) == 0;       // I hold the lower index of the pair
+                    bool take_min = (up == lower);
+                    v[j] = take_min ? (o < v[j] ? o : v[j]) : (o > v[j] ? o : v[j]);
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < GATHER_PER_LANE; ++j) {
+                    if ((j & stride) == 0) {
+                        const int e = lane * GATHER_PER_LANE + j;
+                        bool up = (e & size) == 0;
+                        uint64_t a = v[j], b = v[j + stride];
+                        bool sw = up ? (b < a) : (a < b);
+                        v[j] = sw ? b : a; v[j + stride] = sw ? a : b;
+                    }
+                }
+            }
+        }
+    }
+}
+
+// keep the k smallest of cand[0..count): sorts the buffer, returns min(count, k); buffer is ascending afterwards
+__device__ __noinline__ int warp_select(uint64_t *cand, int count, int k, int lane) {
+    uint64_t v[GATHER_PER_LANE];
+#pragma unroll
+    for (int j = 0; j < GATHER_PER_LANE; ++j) {
+        int e = lane * GATHER_PER_LANE + j;
+        v[j] = e < count ? cand[e] : 0xffffffffffffffffull;
+    }
+    warp_sort(v, lane);
+#pragma unroll
+    for (int j = 0; j < GATHER_PER_LANE; ++j) cand[lane * GATHER_PER_LANE + j] = v[j];
+    __syncwarp();
+    return count < k ? count : k;
+}
+
+__device__ __forceinline__ f3 oct_decode(uint32_t w) {
+    float x = (float)(int)(int16_t)(w & 0xffffu) / 32767.f, y = (float)(int)(int16_t)(w >> 16) / 32767.f;
+    float z = 1.f - fabsf(x) - fabsf(y);
+    if (z < 0.f) {
+        float ox = (1.f - fabsf(y)) * (x >= 0.f ? 1.f : -1.f);
+        float oy = (1.f - fabsf(x)) * (y >= 0.f ? 1.f : -1.f);
+        x = ox; y = oy;
+    }
+    return normalize3(mk3(x, y, z));
+}
+
+// KNN = true: k nearest within radius;  false: every photon within the radius (no candidate buffer)
+template <bool KNN>
+__global__ void __launch_bounds__(GATHER_WARPS * 32)
+gather_kernel(const b2rt_photon *__restrict__ photons, const uint32_t *__restrict__ cell_start, GatherGrid g,
+              const b2rt_query *__restrict__ queries, int64_t nq, int k, float max_dist2, float n_paths,
+              float *__restrict__ out_rgb, float *__restrict__ out_r2, int32_t *__restrict__ out_found,
+              int32_t *__restrict__ idx_out) {
+    __shared__ uint64_t s_cand[GATHER_WARPS][GATHER_CAP];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint64_t *cand = s_cand[warp];
+    const uint32_t lt = (1u << lane) - 1u;
+    for (int64_t q = (int64_t)blockIdx.x * GATHER_WARPS + warp; q < nq; q += (int64_t)gridDim.x * GATHER_WARPS) {
+        const float4 *qp = reinterpret_cast<const float4 *>(queries + q);
+        float4 q0 = __ldg(qp), q1 = __ldg(qp + 1), q2 = __ldg(qp + 2);
+        const float px = q0.x, py = q0.y, pz = q0.z;
+        const f3 nf = mk3(q0.w, q1.x, q1.y), kd = mk3(q1.z, q1.w, q2.x);
+        int c[3];
+        c[0] = min(max((int)floorf((px - g.lo[0]) * g.inv), 0), g.dims[0] - 1);
+        c[1] = min(max((int)floorf((py - g.lo[1]) * g.inv), 0), g.dims[1] - 1);
+        c[2] = min(max((int)floorf((pz - g.lo[2]) * g.inv), 0), g.dims[2] - 1);
+        const float qa[3] = {px, py, pz};
+        uint64_t bound = (uint64_t)__float_as_uint(max_dist2) << 32;   // accept keys < bound  <=>  d2 < radius2
+        int count = 0;
+        f3 acc = mk3(0.f, 0.f, 0.f);       // fixed-radius mode accumulates directly
+        int found_fr = 0;
+        const int smax = max(max(g.dims[0], g.dims[1]), g.dims[2]);
+        for (int s = 0; s < smax; ++s) {
+            const int z0 = max(c[2] - s, 0), z1 = min(c[2] + s, g.dims[2] - 1);
+            const int y0 = max(c[1] - s, 0), y1 = min(c[1] + s, g.dims[1] - 1);
+            const int x0 = c[0] - s, x1 = c[0] + s;
+            for (int z = z0; z <= z1; ++z) {
+                for (int y = y0; y <= y1; ++y) {
+                    const bool face = (abs(z - c[2]) == s) || (abs(y - c[1]) == s);
+                    const int row = (z * g.dims[1] + y) * g.dims[0];
+                    // face rows: the whole x run; interior rows: the two end cells only
+                    for (int part = 0; part < (face ? 1 : 2); ++part) {
+                        int xa, xb;
+                        if (face) { xa = max(x0, 0); xb = min(x1, g.dims[0] - 1); }
+                        else if (part == 0) { xa = xb = x0; if (x0 < 0) continue; }
+                        else { xa = xb = x1; if (x1 > g.dims[0] - 1 || s == 0) continue; }
+                        const uint32_t b = __ldg(cell_start + row + xa), e = __ldg(cell_start + row + xb + 1);
+                        for (uint32_t i0 = b; i0 < e; i0 += 32) {
+                            const uint32_t i = i0 + lane;
+                            bool pass = false;
+                            uint64_t key = 0;
+                            float4 pa;
+                            if (i < e) {
+                                pa = __ldg(reinterpret_cast<const float4 *>(photons + i));
+                                float dx = pa.x - px, dy = pa.y - py, dz = pa.z - pz;
+                                float d2 = dx * dx + dy * dy + dz * dz;
+                                key = ((uint64_t)__float_as_uint(d2) << 32) | i;
+                                pass = key < bound;
+                            }
+                            if (KNN) {
+                                uint32_t m = __ballot_sync(0xffffffffu, pass);
+                                if (m) {
+                                    if (pass) cand[count + __popc(m & lt)] = key;
+                                    count += __popc(m);
+                                    __syncwarp();
+                                    if (count > GATHER_CAP - 32) {
+                                        count = warp_select(cand, count, k, lane);
+                                        if (count == k) bound = cand[k - 1];       // only keys below the current k-th
+                                    }
+                                }
+                            } else if (pass) {
+                                float d2 = __uint_as_float((uint32_t)(key >> 32));
+                                f3 wi = oct_decode(__float_as_uint(pa.w));
+                                if (dot3(nf, wi) > 0.f) {
+                                    float4 pb = __ldg(reinterpret_cast<const float4 *>(photons + i) + 1);
+                                    float sk = 1.f - d2 / max_dist2;
+                                    float w = 3.f * B2_INV_PI * sk * sk / (n_paths * max_dist2);
+                                    acc = acc + mk3(w * pb.x, w * pb.y, w * pb.z);
+                                }
+                                ++found_fr;
+                            }
+                        }
+                    }
+                }
+            }
+            // distance from the query to the outside of the scanned block; sides already at the grid edge do not count
+            float dmin = INFINITY;
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                if (c[a] - s > 0) dmin = fminf(dmin, qa[a] - (g.lo[a] + (float)(c[a] - s) * g.cell));
+                if (c[a] + s < g.dims[a] - 1) dmin = fminf(dmin, (g.lo[a] + (float)(c[a] + s + 1) * g.cell) - qa[a]);
+            }
+            if (dmin == INFINITY) break;                 // whole grid scanned
+            dmin -= g.slack;
+            float r2 = __uint_as_float((uint32_t)(bound >> 32));
+            if (KNN && count > k) {                      // tighten before deciding
+                count = warp_select(cand, count, k, lane);
+                if (count == k) bound = cand[k - 1];
+                r2 = __uint_as_float((uint32_t)(bound >> 32));
+            }
+            if (dmin > 0.f && dmin * dmin >= r2) break;
+        }
+        if (KNN) {
+            count = warp_select(cand, count, k, lane);
+            const float md2 = (count == k) ? __uint_as_float((uint32_t)(cand[k - 1] >> 32)) : max_dist2;
+            for (int j = lane; j < count; j += 32) {
+                uint64_t key = cand[j];
+                uint32_t i = (uint32_t)key;
+                float d2 = __uint_as_float((uint32_t)(key >> 32));
+                const float4 *pp = reinterpret_cast<const float4 *>(photons + i);
+                float4 pa = __ldg(pp), pb = __ldg(pp + 1);
+                f3 wi = oct_decode(__float_as_uint(pa.w));
+                if (dot3(nf, wi) > 0.f) {
+                    float sk = 1.f - d2 / md2;
+                    float w = 3.f * B2_INV_PI * sk * sk / (n_paths * md2);
+                    acc = acc + mk3(w * pb.x, w * pb.y, w * pb.z);
+                }
+            }
+            if (idx_out)
+                for (int j = lane; j < k; j += 32) idx_out[q * k + j] = j < count ? (int32_t)(uint32_t)cand[j] : -1;
+            if (lane == 0) {
+                if (out_r2) out_r2[q] = md2;
+                if (out_found) out_found[q] = count;
+            }
+            __syncwarp();
+        } else {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) found_fr += __shfl_xor_sync(0xffffffffu, found_fr, o);
+            if (lane == 0) {
+                if (out_r2) out_r2[q] = max_dist2;
+                if (out_found) out_found[q] = found_fr;
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            acc.x = acc.x + __shfl_xor_sync(0xffffffffu, acc.x, o);
+            acc.y = acc.y + __shfl_xor_sync(0xffffffffu, acc.y, o);
+            acc.z = acc.z + __shfl_xor_sync(0xffffffffu, acc.z, o);
+        }
+        if (lane == 0 && out_rgb) {
+            out_rgb[3 * q + 0] = acc.x * kd.x * B2_INV_PI;
+            out_rgb[3 * q + 1] = acc.y * kd.y * B2_INV_PI;
+            out_rgb[3 * q + 2] = acc.z * kd.z * B2_INV_PI;
+        }
+    }
+}
+
+}  // namespace
+
+int b2rt_gather_impl(b2rt_ctx *ctx, int map, int64_t nq, const b2rt_query *d_queries, int k, float max_dist2,
+                     float *d_rgb, float *d_r2, int32_t *d_found, int32_t *d_idx) {
+    PhotonMap &m = ctx->maps[map];
+    if (nq <= 0) return B2RT_OK;
+    GatherGrid g;
+    for (int a = 0; a < 3; ++a) { g.lo[a] = m.grid.origin[a]; g.dims[a] = m.grid.dims[a]; }
+    g.cell = m.grid.cell_size; g.inv = m.grid.inv_cell;
+    float mx = 0.f;
+    for (int a = 0; a < 3; ++a) {
+        float hi = m.grid.origin[a] + (float)m.grid.dims[a] * m.grid.cell_size;
+        mx = fmaxf(mx, fmaxf(fabsf(m.grid.origin[a]), fabsf(hi)));
+    }
+    g.slack = 1e-5f * mx;
+    int64_t blocks = (nq + GATHER_WARPS - 1) / GATHER_WARPS;
+    int64_t cap = (int64_t)ctx->sm_count * 16;
+    if (blocks > cap) blocks = cap;
+    float npaths = (float)m.n_paths;    // pbrt: int nPaths * float maxDist2
+    if (k > 0)
+        gather_kernel<true><<<(unsigned)blocks, GATHER_WARPS * 32, 0, ctx->stream>>>(
+            m.sorted.as<b2rt_photon>(), m.cell_start.as<uint32_t>(), g, d_queries, nq, k, max_dist2, npaths, d_rgb,
+            d_r2, d_found, d_idx);
+    else
+        gather_kernel<false><<<(unsigned)blocks, GATHER_WARPS * 32, 0, ctx->stream>>>(
+            m.sorted.as<b2rt_photon>(), m.cell_start.as<uint32_t>(), g, d_queries, nq, k, max_dist2, npaths, d_rgb,
+            d_r2, d_found, d_idx);
+    B2RT_LAUNCH_CHECK(ctx);
+    return B2RT_OK;
+}

@@ -98,6 +98,61 @@ int b2rt_accel_download(b2rt_ctx *ctx, uint32_t *morton, int32_t *prim_order, in
 int b2rt_trace_closest(b2rt_ctx *ctx, int64_t nrays, const b2rt_ray *rays, b2rt_hit *hits, int where);
 int b2rt_trace_any(b2rt_ctx *ctx, int64_t nrays, const b2rt_ray *rays, uint8_t *occluded, int where);
 
+
+/* ---- photon pass: replaces photontracing_camera / photontracing_closest_hit (cuda_render/photon_mapping/
+ * photontracing.cu:80-185) and the host-side CreatePhotonMap kd-tree build (photonmappingrenderer.cpp:150-180) -- */
+enum { B2RT_MAP_CAUSTIC = 0, B2RT_MAP_INDIRECT = 1 };
+/* 32-byte photon (the reference's CudaPhoton is 40 B, photon_mapping/photonmapping.h:32-40).
+ * wi_oct: incident direction, octahedral 2 x snorm16 (low half x, high half y); path = emitting path index. */
+typedef struct { float p[3]; uint32_t wi_oct; float alpha[3]; uint32_t path; } b2rt_photon;
+typedef struct {
+    float   origin[3];        /* lower corner of the grid = min photon position per axis */
+    float   cell_size, inv_cell;
+    int32_t dims[3];
+    int32_t n_cells;
+    int64_t n_photons;
+    float   build_ms;
+} b2rt_grid_info;
+
+/* Trace paths [first_path, first_path+n_paths) from the lights (counter-based RNG: the photons of a path depend only
+ * on (seed, path index)), append the deposits in path order to the caustic / indirect maps.  Deposit, bounce and
+ * Russian-roulette rules follow pbrt's PhotonShootingTask (integrators/photonmap.cpp:416-514), finalgather off.
+ * flags: bit0 = collect caustic photons, bit1 = collect indirect photons.  n_stored[2] (may be NULL) receives the
+ * number of photons this call appended to each map. */
+int b2rt_photons_trace(b2rt_ctx *ctx, int64_t first_path, int64_t n_paths, int32_t max_depth, int32_t flags,
+                       int64_t n_stored[2]);
+/* pbrt's stopping rule (photonmap.cpp:521-576): shoot batches of `batch_paths` until each map holds at least the
+ * wanted number of photons; a map stops collecting (and stops counting paths) once it is full. */
+int b2rt_photons_shoot(b2rt_ctx *ctx, int64_t n_caustic_wanted, int64_t n_indirect_wanted, int32_t max_depth,
+                       int64_t batch_paths, int64_t n_paths_out[2], int64_t n_stored_out[2]);
+int b2rt_photons_clear(b2rt_ctx *ctx);
+int b2rt_photons_count(b2rt_ctx *ctx, int32_t map, int64_t *n_photons, int64_t *n_paths);
+/* copy the photons of a map (path order) to the host / replace them from the host (checkpoint, tests, and the
+ * receive side of the multi-GPU allgather).  where = B2RT_HOST or B2RT_DEVICE. */
+int b2rt_photons_download(b2rt_ctx *ctx, int32_t map, b2rt_photon *out, int64_t capacity, int where);
+int b2rt_photons_upload(b2rt_ctx *ctx, int32_t map, const b2rt_photon *in, int64_t n, int64_t n_paths, int where);
+void *b2rt_photons_device_ptr(b2rt_ctx *ctx, int32_t map);   /* path-order array on the device (NCCL send buffer) */
+
+/* hash-grid build (cell-key sort + prefix-sum cell ranges).  cell_size <= 0: chosen from the photon density so that
+ * an occupied cell holds about `target_per_cell` photons (<= 0: 8).  Bit-exact definition in DESIGN.md. */
+int b2rt_photon_grid_build(b2rt_ctx *ctx, int32_t map, float cell_size, float target_per_cell);
+int b2rt_photon_grid_info(b2rt_ctx *ctx, int32_t map, b2rt_grid_info *info);
+/* parity hooks: sorted cell keys[n], sorted->path-order index[n], cell_start[n_cells+1], sorted photons[n] */
+int b2rt_photon_grid_download(b2rt_ctx *ctx, int32_t map, uint32_t *keys, uint32_t *order, uint32_t *cell_start,
+                              b2rt_photon *sorted);
+
+/* ---- radiance estimate: replaces KdTreeLookup / photonGatheringCamera (photon_mapping/gathering.cu:25-126) with
+ * pbrt's estimator LPhoton (integrators/photonmap.cpp:214-260): k nearest photons within sqrt(max_dist2), Simpson
+ * kernel, k/(nPaths*maxDist2) normalisation.  k <= 0 selects the fixed-radius mode (all photons within the radius).
+ * query: 48 bytes {p[3], n[3] (faceforwarded shading normal Nf), kd[3] (rho of the diffuse lobe), 3 pad}. */
+typedef struct { float p[3]; float n[3]; float kd[3]; float pad[3]; } b2rt_query;
+int b2rt_gather(b2rt_ctx *ctx, int32_t map, int64_t nqueries, const b2rt_query *queries, int32_t k, float max_dist2,
+                float *out_rgb, float *out_radius2, int32_t *out_found, int where);
+/* parity hook: the selected photon set per query (indices into the SORTED photon array, ascending (d2, index));
+ * idx_out[nqueries*k], -1 padded */
+int b2rt_gather_sets(b2rt_ctx *ctx, int32_t map, int64_t nqueries, const b2rt_query *queries, int32_t k,
+                     float max_dist2, int32_t *idx_out, int where);
+
 /* generic device sort exposed for tests/bench of the hand-written radix sort (K2):
  * stable LSD sort of (key32,value32) pairs on `key_bits` low bits; device pointers only. */
 int b2rt_sort_pairs(b2rt_ctx *ctx, int64_t n, uint32_t *keys, uint32_t *vals, int key_bits);
