@@ -149,3 +149,87 @@ def cornell_geometry():
         (*quad([[1, 0, -1], [1, 2, -1], [1, 2, 1], [1, 0, 1]]), green),        # right
     ]
     return parts
+
+
+# ---- full scene descriptions (geometry + materials + lights), neutral format shared by the b2rt binding, the C oracle
+# ---- and the .pbrt writer ------------------------------------------------------------------------------------------
+MATTE, MIRROR, GLASS = 0, 1, 2
+
+
+def xf_translate(tx, ty, tz):
+    o2w = np.array([1, 0, 0, tx, 0, 1, 0, ty, 0, 0, 1, tz], np.float32)
+    w2o = np.array([1, 0, 0, -tx, 0, 1, 0, -ty, 0, 0, 1, -tz], np.float32)
+    return o2w, w2o
+
+
+def xf_disk_down(x, y, z):
+    """pbrt `Translate x y z  Rotate 90 1 0 0`: object z axis -> world -y (a ceiling light facing down)."""
+    o2w = np.array([1, 0, 0, x, 0, 0, -1, y, 0, 1, 0, z], np.float32)
+    w2o = np.array([1, 0, 0, -x, 0, 0, 1, -z, 0, -1, 0, y], np.float32)
+    return o2w, w2o
+
+
+def _box(lo, hi):
+    """axis-aligned box as 12 outward-facing triangles"""
+    x0, y0, z0 = lo
+    x1, y1, z1 = hi
+    P = np.array([[x0, y0, z0], [x1, y0, z0], [x1, y1, z0], [x0, y1, z0],
+                  [x0, y0, z1], [x1, y0, z1], [x1, y1, z1], [x0, y1, z1]], np.float32)
+    q = [[0, 3, 2, 1], [4, 5, 6, 7], [0, 1, 5, 4], [3, 7, 6, 2], [0, 4, 7, 3], [1, 2, 6, 5]]
+    idx = np.array([[a, b, c] for a, b, c, d in q] + [[a, c, d] for a, b, c, d in q], np.int32)
+    return P, idx
+
+
+def cornell_scene(spheres=True, boxes=False, wide=1.0, light="disk"):
+    """SURVEY Appendix D.  spheres: glass + mirror sphere (Cfg3 flavour); boxes: the two matte boxes (Cfg1 flavour);
+    wide: x half-extent of the box (1.78 for the 16:9 Cfg3 frame)."""
+    W = float(wide)
+    mats = [(MATTE, (0.73, 0.73, 0.73), (0, 0, 0), 1.5), (MATTE, (0.65, 0.05, 0.05), (0, 0, 0), 1.5),
+            (MATTE, (0.12, 0.45, 0.15), (0, 0, 0), 1.5), (GLASS, (1, 1, 1), (1, 1, 1), 1.5),
+            (MIRROR, (0.9, 0.9, 0.9), (0, 0, 0), 1.5)]
+    q = np.array([[0, 1, 2], [0, 2, 3]], np.int32)
+
+    def quad(p):
+        return np.asarray(p, np.float32)
+    shapes = [
+        ("mesh", quad([[-W, 0, -1], [W, 0, -1], [W, 0, 1], [-W, 0, 1]]), q, 0),       # floor
+        ("mesh", quad([[-W, 2, -1], [-W, 2, 1], [W, 2, 1], [W, 2, -1]]), q, 0),       # ceiling
+        ("mesh", quad([[-W, 0, -1], [-W, 2, -1], [W, 2, -1], [W, 0, -1]]), q, 0),     # back
+        ("mesh", quad([[-W, 0, -1], [-W, 0, 1], [-W, 2, 1], [-W, 2, -1]]), q, 1),     # left (red)
+        ("mesh", quad([[W, 0, -1], [W, 2, -1], [W, 2, 1], [W, 0, 1]]), q, 2),         # right (green)
+    ]
+    if boxes:
+        shapes.append(("mesh", *_box((-0.7, 0.0, -0.6), (-0.15, 1.2, -0.05)), 0))
+        shapes.append(("mesh", *_box((0.15, 0.0, 0.0), (0.7, 0.6, 0.55)), 0))
+    if spheres:
+        shapes.append(("sphere", *xf_translate(0.4, 0.35, 0.3), 0.35, 3))
+        shapes.append(("sphere", *xf_translate(-0.45, 0.35, -0.3), 0.35, 4))
+    lights = []
+    if light == "disk":
+        shapes.append(("disk", *xf_disk_down(0.0, 1.98, 0.0), 0.0, 0.3, 0.0, 0))
+        lights.append(("disk", len(shapes) - 1, (17.0, 12.0, 4.0), 4))
+    else:
+        lights.append(("point", (0.0, 1.9, 0.0), (3.0, 3.0, 3.0)))
+    return {"materials": mats, "shapes": shapes, "lights": lights}
+
+
+def fill_scene(target, desc):
+    """target: anything with add_material / add_mesh / add_sphere / add_disk / add_light in the b2rt.Context signature
+    (b2rt.Context itself, or oracle.PortScene).  Returns the first prim id of every shape."""
+    mids = [target.add_material(t, kd, kt, ior) for (t, kd, kt, ior) in desc["materials"]]
+    first = []
+    light_of_shape = {l[1]: i for i, l in enumerate(desc["lights"]) if l[0] == "disk"}
+    for si, sh in enumerate(desc["shapes"]):
+        al = light_of_shape.get(si, -1)
+        if sh[0] == "mesh":
+            first.append(target.add_mesh(sh[1], sh[2], material=mids[sh[3]], arealight=al))
+        elif sh[0] == "sphere":
+            first.append(target.add_sphere(sh[1], sh[3], w2o=sh[2], material=mids[sh[4]], arealight=al))
+        else:
+            first.append(target.add_disk(sh[1], sh[3], sh[4], sh[5], w2o=sh[2], material=mids[sh[6]], arealight=al))
+    for l in desc["lights"]:
+        if l[0] == "disk":
+            target.add_light(1, l[2], prim=first[l[1]], nsamples=l[3])
+        else:
+            target.add_light(0, l[2], p=l[1])
+    return first

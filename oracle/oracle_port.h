@@ -25,4 +25,27 @@ void port_prim_boxes(int nprims, const int32_t *kind, const float *verts, const 
 
 /* (3) stable LSD radix sort restatement (std stable sort semantics) */
 void port_sort_pairs(int64_t n, uint32_t *keys, uint32_t *vals, int key_bits);
+
+/* (4) photon pass / hash grid / radiance estimate restatements (oracle_photon.c) */
+typedef struct {
+    int32_t nprims; const int32_t *kind; const float *verts; const int32_t *idx; const float *analytic; /* as in (1) */
+    const int32_t *prim_material;   /* per prim, -1 = default grey matte 0.5 */
+    int32_t nmaterials; const float *materials;   /* 8 floats each: type(0 matte,1 mirror,2 glass), kd/kr[3], kt[3], ior */
+    int32_t nlights; const float *lights;         /* 8 floats each: type(0 point,1 disk area), p[3], rgb[3], prim */
+} port_scene;
+typedef struct { float p[3]; uint32_t wi_oct; float alpha[3]; uint32_t path; } port_photon;   /* == b2rt_photon */
+void port_philox(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1, uint32_t out[4]);
+void port_sincos_quarter(float q, float *s, float *c);
+/* traces paths [first, first+n); appends to out_c / out_i (capacities cap_c / cap_i); returns 0, or -1 on overflow */
+int port_photon_trace(const port_scene *sc, uint64_t seed, int64_t first_path, int64_t n_paths, int max_depth,
+                      int flags, port_photon *out_c, int64_t cap_c, int64_t *n_c, port_photon *out_i, int64_t cap_i,
+                      int64_t *n_i);
+/* grid over n photons: fills origin[3], dims[3], *cell, *inv, keys[n] (sorted), order[n], cell_start (caller allocates
+ * after a first call with cell_start == NULL to learn dims) */
+void port_grid_build(int64_t n, const port_photon *ph, float cell_size, float target_per_cell, float origin[3],
+                     int32_t dims[3], float *cell, float *inv, uint32_t *keys, uint32_t *order, uint32_t *cell_start);
+/* brute-force k nearest (by (d2, index)) within max_dist2 over the SORTED photon array + pbrt's LPhoton for a diffuse
+ * surface.  query = 12 floats {p, n, kd, pad}.  k <= 0: fixed radius.  idx_out may be NULL (k entries per query). */
+void port_gather(int64_t n, const port_photon *sorted, int64_t n_paths, int64_t nq, const float *queries, int k,
+                 float max_dist2, float *rgb, float *r2_out, int32_t *found, int32_t *idx_out);
 #endif
