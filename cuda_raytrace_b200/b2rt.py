@@ -228,3 +228,129 @@ class Context:
     @property
     def stream(self):
         return self.lib.b2rt_stream(self.h)
+
+
+# ---- photon pass / hash grid / radiance estimate (include/b2rt.h, second half) ---------------------------------------
+MAP_CAUSTIC, MAP_INDIRECT = 0, 1
+PHOTON_DTYPE = np.dtype([("p", np.float32, 3), ("wi_oct", np.uint32), ("alpha", np.float32, 3), ("path", np.uint32)])
+QUERY_DTYPE = np.dtype([("p", np.float32, 3), ("n", np.float32, 3), ("kd", np.float32, 3), ("pad", np.float32, 3)])
+
+
+class GridInfo(C.Structure):
+    _fields_ = [("origin", C.c_float * 3), ("cell_size", C.c_float), ("inv_cell", C.c_float), ("dims", C.c_int32 * 3),
+                ("n_cells", C.c_int32), ("n_photons", C.c_int64), ("build_ms", C.c_float)]
+
+
+SYMBOLS += [
+    "b2rt_photons_trace", "b2rt_photons_shoot", "b2rt_photons_clear", "b2rt_photons_count", "b2rt_photons_download",
+    "b2rt_photons_upload", "b2rt_photons_device_ptr", "b2rt_photon_grid_build", "b2rt_photon_grid_info",
+    "b2rt_photon_grid_download", "b2rt_gather", "b2rt_gather_sets",
+]
+
+
+def _bind_photon(lib):
+    vp, i32, i64, f = C.c_void_p, C.c_int32, C.c_int64, C.c_float
+    lib.b2rt_photons_trace.argtypes = [vp, i64, i64, i32, i32, vp]
+    lib.b2rt_photons_shoot.argtypes = [vp, i64, i64, i32, i64, vp, vp]
+    lib.b2rt_photons_clear.argtypes = [vp]
+    lib.b2rt_photons_count.argtypes = [vp, i32, C.POINTER(i64), C.POINTER(i64)]
+    lib.b2rt_photons_download.argtypes = [vp, i32, vp, i64, C.c_int]
+    lib.b2rt_photons_upload.argtypes = [vp, i32, vp, i64, i64, C.c_int]
+    lib.b2rt_photons_device_ptr.argtypes = [vp, i32]
+    lib.b2rt_photons_device_ptr.restype = vp
+    lib.b2rt_photon_grid_build.argtypes = [vp, i32, f, f]
+    lib.b2rt_photon_grid_info.argtypes = [vp, i32, C.POINTER(GridInfo)]
+    lib.b2rt_photon_grid_download.argtypes = [vp, i32, vp, vp, vp, vp]
+    lib.b2rt_gather.argtypes = [vp, i32, i64, vp, i32, f, vp, vp, vp, C.c_int]
+    lib.b2rt_gather_sets.argtypes = [vp, i32, i64, vp, i32, f, vp, C.c_int]
+
+
+_load_core = load
+
+
+def load():  # noqa: F811
+    lib = _load_core()
+    if not getattr(lib, "_b2rt_photon_bound", False):
+        _bind_photon(lib)
+        lib._b2rt_photon_bound = True
+    return lib
+
+
+def _photons_trace(self, first_path, n_paths, max_depth=5, caustic=True, indirect=True):
+    st = (C.c_int64 * 2)()
+    self._ck(self.lib.b2rt_photons_trace(self.h, first_path, n_paths, max_depth, (1 if caustic else 0) | (2 if indirect else 0), st))
+    return st[0], st[1]
+
+
+def _photons_shoot(self, n_caustic, n_indirect, max_depth=5, batch_paths=65536):
+    npaths, nst = (C.c_int64 * 2)(), (C.c_int64 * 2)()
+    self._ck(self.lib.b2rt_photons_shoot(self.h, n_caustic, n_indirect, max_depth, batch_paths, npaths, nst))
+    return (npaths[0], npaths[1]), (nst[0], nst[1])
+
+
+def _photons_clear(self):
+    self._ck(self.lib.b2rt_photons_clear(self.h))
+
+
+def _photons_count(self, which):
+    n, p = C.c_int64(), C.c_int64()
+    self._ck(self.lib.b2rt_photons_count(self.h, which, C.byref(n), C.byref(p)))
+    return n.value, p.value
+
+
+def _photons_download(self, which):
+    n, _ = self.photons_count(which)
+    out = np.zeros(n, PHOTON_DTYPE)
+    self._ck(self.lib.b2rt_photons_download(self.h, which, _ptr(out), n, HOST))
+    return out
+
+
+def _photons_upload(self, which, photons, n_paths):
+    photons = np.ascontiguousarray(photons, PHOTON_DTYPE)
+    self._ck(self.lib.b2rt_photons_upload(self.h, which, _ptr(photons), len(photons), n_paths, HOST))
+
+
+def _grid_build(self, which, cell_size=0.0, target_per_cell=0.0):
+    self._ck(self.lib.b2rt_photon_grid_build(self.h, which, cell_size, target_per_cell))
+    gi = GridInfo()
+    self._ck(self.lib.b2rt_photon_grid_info(self.h, which, C.byref(gi)))
+    return gi
+
+
+def _grid_download(self, which):
+    gi = GridInfo()
+    self._ck(self.lib.b2rt_photon_grid_info(self.h, which, C.byref(gi)))
+    n = gi.n_photons
+    out = {"keys": np.zeros(n, np.uint32), "order": np.zeros(n, np.uint32),
+           "cell_start": np.zeros(gi.n_cells + 1, np.uint32), "sorted": np.zeros(n, PHOTON_DTYPE), "info": gi}
+    self._ck(self.lib.b2rt_photon_grid_download(self.h, which, _ptr(out["keys"]), _ptr(out["order"]),
+                                                _ptr(out["cell_start"]), _ptr(out["sorted"])))
+    return out
+
+
+def make_queries(p, n, kd):
+    q = np.zeros(len(p), QUERY_DTYPE)
+    q["p"], q["n"], q["kd"] = p, n, kd
+    return q
+
+
+def _gather(self, which, queries, k, max_dist2):
+    queries = np.ascontiguousarray(queries, QUERY_DTYPE)
+    nq = len(queries)
+    rgb, r2, found = np.zeros((nq, 3), np.float32), np.zeros(nq, np.float32), np.zeros(nq, np.int32)
+    self._ck(self.lib.b2rt_gather(self.h, which, nq, _ptr(queries), k, max_dist2, _ptr(rgb), _ptr(r2), _ptr(found), HOST))
+    return rgb, r2, found
+
+
+def _gather_sets(self, which, queries, k, max_dist2):
+    queries = np.ascontiguousarray(queries, QUERY_DTYPE)
+    idx = np.zeros((len(queries), k), np.int32)
+    self._ck(self.lib.b2rt_gather_sets(self.h, which, len(queries), _ptr(queries), k, max_dist2, _ptr(idx), HOST))
+    return idx
+
+
+for _n, _f in [("photons_trace", _photons_trace), ("photons_shoot", _photons_shoot), ("photons_clear", _photons_clear),
+               ("photons_count", _photons_count), ("photons_download", _photons_download),
+               ("photons_upload", _photons_upload), ("grid_build", _grid_build), ("grid_download", _grid_download),
+               ("gather", _gather), ("gather_sets", _gather_sets)]:
+    setattr(Context, _n, _f)

@@ -162,7 +162,7 @@ int b2rt_upload_tables(b2rt_ctx *ctx) {
             float phimax = ((float)M_PI / 180.f) * 360.f;
             L.analytic = a;
             L.area = phimax * 0.5f * (D.radius * D.radius - D.inner * D.inner);
-            float nx = D.w2o[2], ny = D.w2o[6], nz = D.w2o[10];
+            float nx = D.w2o[8], ny = D.w2o[9], nz = D.w2o[10];   // w2o^T (0,0,1)
             float inv = 1.f / sqrtf(nx * nx + ny * ny + nz * nz);
             L.n[0] = nx * inv; L.n[1] = ny * inv; L.n[2] = nz * inv;
             float pi = (float)M_PI;

@@ -227,3 +227,229 @@ class RefScene:
             self.h = None
 
     __del__ = close
+
+
+# ---- photon pass / grid / estimator restatements (oracle_photon.c) ----------------------------------------------------
+PHOTON_DTYPE = np.dtype([("p", np.float32, 3), ("wi_oct", np.uint32), ("alpha", np.float32, 3), ("path", np.uint32)])
+
+
+class _CScene(C.Structure):
+    _fields_ = [("nprims", C.c_int32), ("kind", C.c_void_p), ("verts", C.c_void_p), ("idx", C.c_void_p),
+                ("analytic", C.c_void_p), ("prim_material", C.c_void_p), ("nmaterials", C.c_int32),
+                ("materials", C.c_void_p), ("nlights", C.c_int32), ("lights", C.c_void_p)]
+
+
+def _bind_photon():
+    lib = port()
+    if getattr(lib, "_photon_bound", False):
+        return lib
+    vp, i64, f = C.c_void_p, C.c_int64, C.c_float
+    lib.port_photon_trace.argtypes = [C.POINTER(_CScene), C.c_uint64, i64, i64, C.c_int, C.c_int, vp, i64,
+                                      C.POINTER(i64), vp, i64, C.POINTER(i64)]
+    lib.port_grid_build.argtypes = [i64, vp, f, f, vp, vp, C.POINTER(f), C.POINTER(f), vp, vp, vp]
+    lib.port_grid_build.restype = None
+    lib.port_gather.argtypes = [i64, vp, i64, i64, vp, C.c_int, f, vp, vp, vp, vp]
+    lib.port_gather.restype = None
+    lib.port_sincos_quarter.argtypes = [f, C.POINTER(f), C.POINTER(f)]
+    lib.port_sincos_quarter.restype = None
+    lib.port_philox.argtypes = [C.c_uint32] * 6 + [vp]
+    lib.port_philox.restype = None
+    lib._photon_bound = True
+    return lib
+
+
+class PortFullScene:
+    """Scene with materials and lights, same method signatures as cuda_raytrace_b200.b2rt.Context so that
+    scenes.fill_scene() fills either."""
+
+    def __init__(self):
+        self.geo = PortScene()
+        self.prim_material = []
+        self.materials = []
+        self.lights = []
+
+    def add_material(self, mtype, rgb, kt=None, ior=1.5):
+        kt = (1.0, 1.0, 1.0) if kt is None else kt
+        self.materials.append([float(mtype), *map(float, rgb), *map(float, kt), float(ior)])
+        return len(self.materials) - 1
+
+    def add_mesh(self, P, idx, material=-1, arealight=-1):
+        first = self.geo.add_mesh(P, idx)
+        self.prim_material.extend([material] * len(np.asarray(idx).reshape(-1, 3)))
+        return first
+
+    def add_sphere(self, o2w, radius, w2o=None, material=-1, arealight=-1):
+        self.prim_material.append(material)
+        return self.geo.add_sphere(o2w, w2o, radius)
+
+    def add_disk(self, o2w, height, radius, inner=0.0, w2o=None, material=-1, arealight=-1):
+        self.prim_material.append(material)
+        return self.geo.add_disk(o2w, w2o, height, radius, inner)
+
+    def add_light(self, ltype, rgb, p=None, prim=-1, nsamples=1):
+        p = (0.0, 0.0, 0.0) if p is None else p
+        self.lights.append([float(ltype), *map(float, p), *map(float, rgb), float(prim)])
+        return len(self.lights) - 1
+
+    def _cscene(self):
+        kind, verts, idx, an = self.geo._arrays()
+        pm = np.asarray(self.prim_material, np.int32)
+        mats = np.asarray(self.materials, np.float32).reshape(-1, 8)
+        lights = np.asarray(self.lights, np.float32).reshape(-1, 8)
+        keep = (kind, verts, idx, an, pm, mats, lights)
+        cs = _CScene(len(kind), _p(kind).value, _p(verts).value, _p(idx).value, _p(an).value, _p(pm).value, len(mats),
+                     _p(mats).value if len(mats) else None, len(lights), _p(lights).value if len(lights) else None)
+        return cs, keep
+
+    def photon_trace(self, seed, first_path, n_paths, max_depth=5, caustic=True, indirect=True):
+        lib = _bind_photon()
+        cs, keep = self._cscene()
+        cap = n_paths * max_depth + 1
+        oc, oi = np.zeros(cap, PHOTON_DTYPE), np.zeros(cap, PHOTON_DTYPE)
+        nc, ni = C.c_int64(0), C.c_int64(0)
+        rc = lib.port_photon_trace(C.byref(cs), seed, first_path, n_paths, max_depth,
+                                   (1 if caustic else 0) | (2 if indirect else 0), _p(oc), cap, C.byref(nc), _p(oi), cap,
+                                   C.byref(ni))
+        assert rc == 0, rc
+        del keep
+        return oc[: nc.value].copy(), oi[: ni.value].copy()
+
+
+def grid_build(photons, cell_size=0.0, target_per_cell=0.0):
+    lib = _bind_photon()
+    photons = np.ascontiguousarray(photons, PHOTON_DTYPE)
+    n = len(photons)
+    origin, dims = np.zeros(3, np.float32), np.zeros(3, np.int32)
+    cell, inv = C.c_float(), C.c_float()
+    lib.port_grid_build(n, _p(photons), cell_size, target_per_cell, _p(origin), _p(dims), C.byref(cell), C.byref(inv),
+                        None, None, None)
+    ncell = int(dims[0]) * int(dims[1]) * int(dims[2])
+    keys, order, cs = np.zeros(n, np.uint32), np.zeros(n, np.uint32), np.zeros(ncell + 1, np.uint32)
+    lib.port_grid_build(n, _p(photons), cell_size, target_per_cell, _p(origin), _p(dims), C.byref(cell), C.byref(inv),
+                        _p(keys), _p(order), _p(cs))
+    return {"origin": origin, "dims": dims, "cell_size": cell.value, "inv_cell": inv.value, "keys": keys,
+            "order": order, "cell_start": cs, "sorted": photons[order]}
+
+
+def gather(sorted_photons, n_paths, queries, k, max_dist2, want_sets=False):
+    """queries: (nq,12) float32 {p, n, kd, pad}.  Returns rgb, r2, found[, idx]."""
+    lib = _bind_photon()
+    sp = np.ascontiguousarray(sorted_photons, PHOTON_DTYPE)
+    q = np.ascontiguousarray(queries).view(np.float32).reshape(-1, 12)
+    nq = len(q)
+    rgb, r2, found = np.zeros((nq, 3), np.float32), np.zeros(nq, np.float32), np.zeros(nq, np.int32)
+    idx = np.zeros((nq, max(k, 1)), np.int32) if want_sets else None
+    lib.port_gather(len(sp), _p(sp), n_paths, nq, _p(q), k, max_dist2, _p(rgb), _p(r2), _p(found), _p(idx))
+    return (rgb, r2, found, idx) if want_sets else (rgb, r2, found)
+
+
+def sincos_quarter(q):
+    lib = _bind_photon()
+    s, c = C.c_float(), C.c_float()
+    lib.port_sincos_quarter(float(q), C.byref(s), C.byref(c))
+    return s.value, c.value
+
+
+class RefPhotonScene:
+    """The reference's own CPU photon mapper (pbrt-v2 PhotonIntegrator) behind oracle/ref_photon.cpp; method
+    signatures follow b2rt.Context so scenes.fill_scene() fills it."""
+
+    def __init__(self):
+        if not ref_available():
+            raise FileNotFoundError(REF_SO)
+        lib = C.CDLL(REF_SO)
+        vp, i64, f, i = C.c_void_p, C.c_int64, C.c_float, C.c_int
+        lib.ref_pm_create.restype = vp
+        lib.ref_pm_add_material.argtypes = [vp, i, vp, vp, f]
+        lib.ref_pm_add_mesh.argtypes = [vp, i, vp, i, vp, i]
+        lib.ref_pm_add_sphere.argtypes = [vp, vp, vp, f, i]
+        lib.ref_pm_add_disk.argtypes = [vp, vp, vp, f, f, f, i, vp, i]
+        lib.ref_pm_add_point_light.argtypes = [vp, vp, vp]
+        lib.ref_pm_build.argtypes = [vp]
+        lib.ref_pm_shoot.argtypes = [vp, i, i, i, i, vp, i64, vp, i64, vp, vp]
+        lib.ref_pm_lphoton.argtypes = [i64, vp, i, i64, vp, i, f, vp]
+        lib.ref_pm_lphoton.restype = None
+        self.lib = lib
+        self.h = C.c_void_p(lib.ref_pm_create())
+        self.nprims = 0
+        self.disks = {}          # first prim -> deferred disk args (a disk becomes an area light in add_light)
+        self.built = False
+
+    def add_material(self, mtype, rgb, kt=None, ior=1.5):
+        a = np.asarray(rgb, np.float32)
+        b = np.asarray((1, 1, 1) if kt is None else kt, np.float32)
+        return self.lib.ref_pm_add_material(self.h, int(mtype), _p(a), _p(b), float(ior))
+
+    def add_mesh(self, P, idx, material=-1, arealight=-1):
+        P = np.ascontiguousarray(P, np.float32).reshape(-1, 3)
+        idx = np.ascontiguousarray(idx, np.int32).reshape(-1, 3)
+        self.lib.ref_pm_add_mesh(self.h, len(P), _p(P), len(idx), _p(idx), material)
+        first = self.nprims
+        self.nprims += len(idx)
+        return first
+
+    def add_sphere(self, o2w, radius, w2o=None, material=-1, arealight=-1):
+        a, b = np.ascontiguousarray(o2w, np.float32), np.ascontiguousarray(w2o, np.float32)
+        self.lib.ref_pm_add_sphere(self.h, _p(a), _p(b), radius, material)
+        self.nprims += 1
+        return self.nprims - 1
+
+    def add_disk(self, o2w, height, radius, inner=0.0, w2o=None, material=-1, arealight=-1):
+        args = (np.ascontiguousarray(o2w, np.float32), np.ascontiguousarray(w2o, np.float32), height, radius, inner,
+                material)
+        if arealight >= 0:
+            self.disks[self.nprims] = args      # created in add_light, when L is known
+        else:
+            self.lib.ref_pm_add_disk(self.h, _p(args[0]), _p(args[1]), height, radius, inner, material, None, 0)
+        self.nprims += 1
+        return self.nprims - 1
+
+    def add_light(self, ltype, rgb, p=None, prim=-1, nsamples=1):
+        L = np.asarray(rgb, np.float32)
+        if ltype == 1:
+            a, b, h, r, inner, mat = self.disks.pop(prim)
+            self.lib.ref_pm_add_disk(self.h, _p(a), _p(b), h, r, inner, mat, _p(L), nsamples)
+        else:
+            pp = np.asarray(p, np.float32)
+            self.lib.ref_pm_add_point_light(self.h, _p(pp), _p(L))
+
+    def shoot(self, n_caustic, n_indirect, max_depth=5, ncores=1):
+        """pbrt's PhotonIntegrator::Preprocess.  Returns (caustic, indirect) as (n,9) float arrays {p, alpha, wi},
+        and (nCausticPaths, nIndirectPaths)."""
+        if not self.built:
+            self.lib.ref_pm_build(self.h)
+            self.built = True
+        cap_c, cap_i = 2 * n_caustic + 600000, 2 * n_indirect + 600000
+        oc, oi = np.zeros((cap_c, 9), np.float32), np.zeros((cap_i, 9), np.float32)
+        npaths, nst = (C.c_int64 * 2)(), (C.c_int64 * 2)()
+        rc = self.lib.ref_pm_shoot(self.h, n_caustic, n_indirect, max_depth, ncores, _p(oc), cap_c, _p(oi), cap_i,
+                                   npaths, nst)
+        assert rc == 0
+        return oc[: nst[0]].copy(), oi[: nst[1]].copy(), (npaths[0], npaths[1])
+
+    def lphoton(self, photons9, n_paths, queries, k, max_dist2):
+        ph = np.ascontiguousarray(photons9, np.float32).reshape(-1, 9)
+        q = np.ascontiguousarray(queries).view(np.float32).reshape(-1, 12)
+        out = np.zeros((len(q), 3), np.float32)
+        self.lib.ref_pm_lphoton(len(ph), _p(ph), int(n_paths), len(q), _p(q), k, max_dist2, _p(out))
+        return out
+
+
+def oct_decode(w):
+    """numpy restatement of the photon direction decoding (float32 throughout)."""
+    w = np.asarray(w, np.uint32)
+    x = (w & 0xFFFF).astype(np.uint16).view(np.int16).astype(np.float32) / np.float32(32767)
+    y = (w >> 16).astype(np.uint16).view(np.int16).astype(np.float32) / np.float32(32767)
+    z = np.float32(1) - np.abs(x) - np.abs(y)
+    neg = z < 0
+    ox = (np.float32(1) - np.abs(y)) * np.where(x >= 0, np.float32(1), np.float32(-1))
+    oy = (np.float32(1) - np.abs(x)) * np.where(y >= 0, np.float32(1), np.float32(-1))
+    x, y = np.where(neg, ox, x), np.where(neg, oy, y)
+    v = np.stack([x, y, z], -1).astype(np.float32)
+    return v / np.linalg.norm(v, axis=-1, keepdims=True).astype(np.float32)
+
+
+def photons_to9(ph):
+    out = np.zeros((len(ph), 9), np.float32)
+    out[:, 0:3], out[:, 3:6], out[:, 6:9] = ph["p"], ph["alpha"], oct_decode(ph["wi_oct"])
+    return out

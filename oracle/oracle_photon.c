@@ -272,7 +272,7 @@ static void derive_lights(const port_scene *sc, olight *L, float *cdf /* 2n+2 */
             float phimax = ((float)M_PI / 180.f) * 360.f;
             L[i].analytic = a;
             L[i].area = phimax * 0.5f * (D[24] * D[24] - D[26] * D[26]);       /* Disk::Area */
-            L[i].n = vnormalize(V(D[12 + 2], D[12 + 6], D[12 + 10]));
+            L[i].n = vnormalize(V(D[12 + 8], D[12 + 9], D[12 + 10]));   /* w2o^T (0,0,1) */
             float pi = (float)M_PI;                              /* DiffuseAreaLight::Power = Lemit * area * M_PI */
             P = V(L[i].rgb.x * L[i].area * pi, L[i].rgb.y * L[i].area * pi, L[i].rgb.z * L[i].area * pi);
         }
