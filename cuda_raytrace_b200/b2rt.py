@@ -354,3 +354,55 @@ for _n, _f in [("photons_trace", _photons_trace), ("photons_shoot", _photons_sho
                ("photons_upload", _photons_upload), ("grid_build", _grid_build), ("grid_download", _grid_download),
                ("gather", _gather), ("gather_sets", _gather_sets)]:
     setattr(Context, _n, _f)
+
+
+# ---- camera pass ------------------------------------------------------------------------------------------------------
+class Camera(C.Structure):
+    _fields_ = [("o", C.c_float * 3), ("A", C.c_float * 3), ("B", C.c_float * 3), ("C", C.c_float * 3),
+                ("xres", C.c_int32), ("yres", C.c_int32)]
+
+
+class FrameParams(C.Structure):
+    _fields_ = [("spp", C.c_int32), ("max_specular_depth", C.c_int32), ("nused", C.c_int32), ("max_dist2", C.c_float),
+                ("use_caustic", C.c_int32), ("use_indirect", C.c_int32), ("direct_lighting", C.c_int32),
+                ("x0", C.c_int32), ("x1", C.c_int32), ("y0", C.c_int32), ("y1", C.c_int32)]
+
+
+SYMBOLS += ["b2rt_render_frame"]
+
+
+def pbrt_camera(eye, look, up, fov, xres, yres):
+    """pbrt `LookAt` + `Camera "perspective"` (core/transform.cpp LookAt, cameras/perspective.cpp:45-78): left-handed,
+    fov spans the shorter image axis.  Returns the b2rt_camera whose rays equal GenerateRay's for lensradius 0."""
+    eye, look, up = (np.asarray(v, np.float64) for v in (eye, look, up))
+    d = look - eye
+    d /= np.linalg.norm(d)
+    left = np.cross(up / np.linalg.norm(up), d)
+    left /= np.linalg.norm(left)
+    nup = np.cross(d, left)
+    aspect = xres / yres
+    sw = (-aspect, aspect, -1.0, 1.0) if aspect > 1 else (-1.0, 1.0, -1.0 / aspect, 1.0 / aspect)
+    t = np.tan(np.radians(fov) / 2)
+    cam = Camera()
+    A = sw[0] * t * left + sw[3] * t * nup + d
+    B = (sw[1] - sw[0]) / xres * t * left
+    Cv = -(sw[3] - sw[2]) / yres * t * nup
+    for dst, src in ((cam.o, eye), (cam.A, A), (cam.B, B), (cam.C, Cv)):
+        for i in range(3):
+            dst[i] = float(src[i])
+    cam.xres, cam.yres = xres, yres
+    return cam
+
+
+def _render_frame(self, cam, spp=1, max_specular_depth=5, nused=50, max_dist=0.1, caustic=True, indirect=True,
+                  direct=True, window=None):
+    x0, x1, y0, y1 = window if window else (0, cam.xres, 0, cam.yres)
+    fp = FrameParams(spp, max_specular_depth, nused, float(np.float32(max_dist) * np.float32(max_dist)), int(caustic),
+                     int(indirect), int(direct), x0, x1, y0, y1)
+    out = np.zeros((y1 - y0, x1 - x0, 3), np.float32)
+    self.lib.b2rt_render_frame.argtypes = [C.c_void_p, C.POINTER(Camera), C.POINTER(FrameParams), C.c_void_p, C.c_int]
+    self._ck(self.lib.b2rt_render_frame(self.h, C.byref(cam), C.byref(fp), _ptr(out), HOST))
+    return out
+
+
+Context.render_frame = _render_frame

@@ -206,4 +206,36 @@ int b2rt_gather_sets(b2rt_ctx *ctx, int32_t map, int64_t nqueries, const b2rt_qu
     return gather_common(ctx, map, nqueries, queries, k, max_dist2, nullptr, nullptr, nullptr, idx_out, where);
 }
 
+int b2rt_render_frame(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_params *fp, float *out_rgb, int where) {
+    if (!ctx) return B2RT_E_ARG;
+    if (!cam || !fp || !out_rgb || fp->spp < 1 || fp->x0 < 0 || fp->y0 < 0 || fp->x1 > cam->xres || fp->y1 > cam->yres ||
+        fp->x0 >= fp->x1 || fp->y0 >= fp->y1 || fp->nused > 224 || !(fp->max_dist2 > 0.f)) {
+        ctx->err = "render_frame: bad arguments"; return B2RT_E_ARG;
+    }
+    int rc = need_built(ctx, "render_frame");
+    if (rc) return rc;
+    B2RT_CUDA(ctx, cudaSetDevice(ctx->device));
+    const size_t bytes = (size_t)(fp->x1 - fp->x0) * (fp->y1 - fp->y0) * 12;
+    float *d_out = out_rgb;
+    if (where != B2RT_DEVICE) {
+        B2RT_CUDA(ctx, ctx->d_frame.reserve(bytes));
+        d_out = ctx->d_frame.as<float>();
+    }
+    rc = b2rt_render_impl(ctx, cam, fp, d_out);
+    if (rc) return rc;
+    if (where != B2RT_DEVICE)
+        B2RT_CUDA(ctx, cudaMemcpyAsync(out_rgb, d_out, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    rc = status_check(ctx);
+    if (rc) return rc;
+    uint32_t dropped = 0;
+    B2RT_CUDA(ctx, cudaMemcpyAsync(&dropped, ctx->d_counters.as<uint32_t>() + 9, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    B2RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (dropped) {
+        cudaMemsetAsync(ctx->d_counters.as<uint32_t>() + 9, 0, 4, ctx->stream);
+        ctx->err = "render_frame: " + std::to_string(dropped) + " samples had more diffuse leaves than slots";
+        return B2RT_E_OVERFLOW;
+    }
+    return B2RT_OK;
+}
+
 }  // extern "C"

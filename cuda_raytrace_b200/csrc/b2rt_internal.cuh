@@ -105,6 +105,7 @@ struct b2rt_ctx {
     DevBuf d_prim_material, d_prim_light, d_materials, d_lights, d_light_cdf;
     DevBuf d_slots, d_cnt_c, d_cnt_i, d_grid_box;
     DevBuf d_queries, d_q_rgb, d_q_r2, d_q_found, d_q_idx;
+    DevBuf d_samples, d_qslots, d_qcnt, d_q_rgb2, d_frame;
     PhotonMap maps[2];       // B2RT_MAP_CAUSTIC, B2RT_MAP_INDIRECT
     b2rt_accel_info info{};
 };
@@ -139,6 +140,7 @@ int b2rt_upload_tables(b2rt_ctx *ctx);
 int b2rt_photons_trace_impl(b2rt_ctx *ctx, int64_t first_path, int64_t n_paths, int max_depth, int flags,
                             int64_t n_stored[2]);
 int b2rt_photon_grid_build_impl(b2rt_ctx *ctx, int map, float cell_size, float target_per_cell);
+int b2rt_render_impl(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_params *fp, float *d_out);
 int b2rt_gather_impl(b2rt_ctx *ctx, int map, int64_t nq, const b2rt_query *d_queries, int k, float max_dist2,
                      float *d_rgb, float *d_r2, int32_t *d_found, int32_t *d_idx);
 void b2rt_fill_dscene(b2rt_ctx *ctx, DScene *sc);

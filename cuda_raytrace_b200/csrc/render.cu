@@ -1,0 +1,303 @@
+// K14 camera rays, K6/K7 shading with direct lighting and the specular tree, K13 film: the camera pass.
+//
+// Replaces raytracing_camera / raytracing_closest_hit / directLight / shadow_any_hit
+// (cuda_render/photon_mapping/raytracing.cu:19-147), simple_camera / simple_cloest_hit
+// (simple_render/simplerender.cu:22-78), finalGatheringCamera (photon_mapping/gathering.cu:129-146), the CPU camera
+// ray loop PbrtCamera::preLaunch (util/camera/pbrtcamera.cpp:57-122) and the CPU film loop
+// (photonmappingrenderer.cpp:247-273).  Radiance follows pbrt's PhotonIntegrator::Li with finalgather off
+// (pbrt-v2/src/integrators/photonmap.cpp:624-781): Le + UniformSampleAllLights with MIS
+// (core/integrator.cpp:47-174) + LPhoton(caustic) + LPhoton(indirect) + SpecularReflect + SpecularTransmit
+// (core/integrator.cpp:177-258, both branches followed, depth < maxspeculardepth).
+//
+// One thread per camera sample walks the specular tree depth-first with an explicit stack; shadow rays and MIS rays
+// are traced inline.  Every diffuse leaf leaves a gather query (throughput folded into its kd) in the sample's slot
+// row; a scan over the per-sample leaf counts compacts them, K12 runs once per photon map over the compact array,
+// and the film kernel adds everything up per pixel in a fixed order.  Pixel jitter and light samples are
+// Philox(seed, pixel, sample), so an image tile is bit-identical no matter which GPU renders it.
+#include "b2rt_shade.cuh"
+
+namespace {
+
+constexpr int RENDER_THREADS = 128;
+constexpr int MAX_TREE_DEPTH = 8;
+
+__device__ __forceinline__ float power_heuristic(float f, float g) { return (f * f) / (f * f + g * g); }
+
+// Shape::Pdf(p, wi) for the disk light (core/shape.cpp:95-108); also returns the hit distance
+__device__ __forceinline__ float disk_light_pdf(const AnalyticPrim &D, const LightD &L, f3 p, f3 wi) {
+    RayD r;
+    r.ox = p.x; r.oy = p.y; r.oz = p.z; r.dx = wi.x; r.dy = wi.y; r.dz = wi.z; r.tmin = 1e-3f;
+    float t;
+    if (!disk_test(r, D, INFINITY, t)) return 0.f;
+    f3 dv = wi * t;
+    float d2 = dv.x * dv.x + dv.y * dv.y + dv.z * dv.z;
+    float pdf = d2 / (fabsf(dot3(L.n, -wi)) * L.area);
+    return isinf(pdf) ? 0.f : pdf;
+}
+
+// UniformSampleAllLights + EstimateDirect for a Lambertian surface (flags = BSDF_ALL & ~BSDF_SPECULAR)
+__device__ f3 direct_lighting(const DScene &sc, const Surface &s, const Mat &m, f3 wo, uint32_t c0, uint32_t c1,
+                              uint32_t node, uint32_t k0, uint32_t k1, bool &overflow) {
+    f3 L = mk3(0.f, 0.f, 0.f);
+    const f3 f_lambert = m.kd * B2_INV_PI;
+    for (int li = 0; li < sc.n_lights; ++li) {
+        LightD Lt = load_light(sc, li);
+        const int ns = Lt.type == B2RT_LIGHT_POINT ? 1 : max(Lt.nsamples, 1);
+        f3 Ld = mk3(0.f, 0.f, 0.f);
+        for (int j = 0; j < ns; ++j) {
+            u4 r = philox4x32_10(c0, c1, node, 0x100u + (uint32_t)(li * 64 + j), k0, k1);
+            HitD h;
+            if (Lt.type == B2RT_LIGHT_POINT) {
+                // PointLight::Sample_L (lights/point.cpp:50-57): delta light, no MIS
+                f3 dl = Lt.p - s.p;
+                float d2 = dl.x * dl.x + dl.y * dl.y + dl.z * dl.z;
+                f3 wi = normalize3(dl);
+                bool same = dot3(wi, s.n) * dot3(wo, s.n) > 0.f;
+                if (!same) continue;
+                // visibility segment p -> lightPos: direction (lightPos - p), [rayEps, 1]
+                if (traverse<true>(sc.nodes, sc.recs, sc.analytic, s.p.x, s.p.y, s.p.z, dl.x, dl.y, dl.z, s.ray_eps, 1.f, h,
+                                   overflow))
+                    continue;
+                float w = fabsf(dot3(wi, s.n));     // / lightPdf (= 1)
+                Ld = Ld + mk3(f_lambert.x * (Lt.rgb.x / d2) * w, f_lambert.y * (Lt.rgb.y / d2) * w,
+                              f_lambert.z * (Lt.rgb.z / d2) * w);
+                continue;
+            }
+            const AnalyticPrim &D = sc.analytic[Lt.analytic];
+            // ---- light sampling (lights/diffuse.cpp:69-81) ----
+            {
+                f3 ps = disk_sample_point(D, u01(r.x), u01(r.y));
+                f3 dl = ps - s.p;
+                f3 wi = normalize3(dl);
+                float lpdf = disk_light_pdf(D, Lt, s.p, wi);
+                bool emits = dot3(Lt.n, -wi) > 0.f;
+                bool same = dot3(wi, s.n) * dot3(wo, s.n) > 0.f;
+                if (lpdf > 0.f && emits && same) {
+                    if (!traverse<true>(sc.nodes, sc.recs, sc.analytic, s.p.x, s.p.y, s.p.z, dl.x, dl.y, dl.z, s.ray_eps,
+                                        1.f - 1e-3f, h, overflow)) {
+                        f3 wil = to_local(s, wi), wol = to_local(s, wo);
+                        float bpdf = (wol.z * wil.z > 0.f) ? fabsf(wil.z) * B2_INV_PI : 0.f;
+                        float w = fabsf(dot3(wi, s.n)) * power_heuristic(lpdf, bpdf) / lpdf;
+                        Ld = Ld + mk3(f_lambert.x * Lt.rgb.x * w, f_lambert.y * Lt.rgb.y * w, f_lambert.z * Lt.rgb.z * w);
+                    }
+                }
+            }
+            // ---- BSDF sampling ----
+            {
+                BsdfSample bs;
+                if (!sample_bsdf(s, m, wo, u01(r.z), u01(r.w), 0.f, bs) || is_black(bs.f) || !(bs.pdf > 0.f)) continue;
+                float lpdf = disk_light_pdf(D, Lt, s.p, bs.wi);
+                if (lpdf == 0.f) continue;
+                float weight = power_heuristic(bs.pdf, lpdf);
+                if (traverse<false>(sc.nodes, sc.recs, sc.analytic, s.p.x, s.p.y, s.p.z, bs.wi.x, bs.wi.y, bs.wi.z, s.ray_eps,
+                                    INFINITY, h, overflow) &&
+                    h.prim == Lt.prim && dot3(Lt.n, -bs.wi) > 0.f) {
+                    float w = bs.absdot * weight / bs.pdf;
+                    Ld = Ld + mk3(bs.f.x * Lt.rgb.x * w, bs.f.y * Lt.rgb.y * w, bs.f.z * Lt.rgb.z * w);
+                }
+            }
+        }
+        float inv = 1.f / (float)ns;
+        L = L + Ld * inv;
+    }
+    return L;
+}
+
+struct TreeNode { f3 o, d; float tmin; f3 T; int depth; uint32_t id; };
+
+// K14 + K6 + K7.  sample s (chunk-local) -> pixel (crop-window row-major) and sample number k.
+__global__ void __launch_bounds__(RENDER_THREADS)
+render_li_kernel(DScene sc, b2rt_camera cam, b2rt_frame_params fp, uint32_t seed_lo, uint32_t seed_hi, int64_t first_sample,
+                 int64_t n_samples, int slots, float *__restrict__ sample_rgb, b2rt_query *__restrict__ qslots,
+                 uint32_t *__restrict__ qcnt, uint32_t *status) {
+    int64_t ls = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (ls >= n_samples) return;
+    const int64_t s = first_sample + ls;
+    const int cw = fp.x1 - fp.x0;
+    const int64_t pix = s / fp.spp;
+    const int k = (int)(s % fp.spp);
+    const int px = fp.x0 + (int)(pix % cw), py = fp.y0 + (int)(pix / cw);
+    const uint32_t gpix = (uint32_t)py * (uint32_t)cam.xres + (uint32_t)px;    // global pixel id: tiling-independent
+    const uint32_t k0 = seed_lo ^ 0x43414d52u, k1 = seed_hi;                     // 'CAMR' stream
+    u4 rj = philox4x32_10(gpix, (uint32_t)k, 0u, 0u, k0, k1);
+    const float fx = (float)px + u01(rj.x), fy = (float)py + u01(rj.y);
+    f3 d0 = mk3(cam.A[0] + fx * cam.B[0] + fy * cam.C[0], cam.A[1] + fx * cam.B[1] + fy * cam.C[1],
+                cam.A[2] + fx * cam.B[2] + fy * cam.C[2]);
+
+    TreeNode stack[MAX_TREE_DEPTH + 1];
+    int sp = 0;
+    stack[sp].o = mk3(cam.o[0], cam.o[1], cam.o[2]); stack[sp].d = normalize3(d0); stack[sp].tmin = 0.f;
+    stack[sp].T = mk3(1.f, 1.f, 1.f); stack[sp].depth = 0; stack[sp].id = 1u; ++sp;
+    f3 L = mk3(0.f, 0.f, 0.f);
+    uint32_t nq = 0;
+    bool overflow = false, dropped = false;
+    b2rt_query *myq = qslots + ls * slots;
+    while (sp > 0) {
+        TreeNode nd = stack[--sp];
+        HitD h;
+        if (!traverse<false>(sc.nodes, sc.recs, sc.analytic, nd.o.x, nd.o.y, nd.o.z, nd.d.x, nd.d.y, nd.d.z, nd.tmin, INFINITY, h,
+                             overflow))
+            continue;
+        Surface sf = make_surface(sc, h, nd.o, nd.d);
+        Mat m = load_material(sc, sf.material);
+        f3 wo = -nd.d;
+        if (sf.light >= 0 && sf.light < sc.n_lights && dot3(sf.n, wo) > 0.f) {     // isect.Le(wo): DiffuseAreaLight::L
+            const Light &Lg = sc.lights[sf.light];
+            L = L + nd.T * mk3(Lg.rgb[0], Lg.rgb[1], Lg.rgb[2]);
+        }
+        if (m.type == B2RT_MAT_MATTE) {
+            if (fp.direct_lighting)
+                L = L + nd.T * direct_lighting(sc, sf, m, wo, gpix, (uint32_t)k, nd.id, k0, k1, overflow);
+            if (fp.use_caustic || fp.use_indirect) {
+                if ((int)nq < slots) {
+                    f3 nf = dot3(sf.n, wo) < 0.f ? -sf.n : sf.n;              // Faceforward(n, wo)
+                    f3 kd = m.kd * nd.T;
+                    float4 *dst = reinterpret_cast<float4 *>(myq + nq);
+                    dst[0] = make_float4(sf.p.x, sf.p.y, sf.p.z, nf.x);
+                    dst[1] = make_float4(nf.y, nf.z, kd.x, kd.y);
+                    dst[2] = make_float4(kd.z, 0.f, 0.f, 0.f);
+                    ++nq;
+                } else dropped = true;
+            }
+            continue;
+        }
+        if (nd.depth + 1 >= fp.max_specular_depth) continue;
+        // SpecularReflect / SpecularTransmit: single-lobe sampling, pdf 1, weight f*|cos|/pdf = F*Kr or (1-F)*Kt
+        f3 wol = to_local(sf, wo);
+        float F = (m.type == B2RT_MAT_GLASS) ? fresnel_dielectric(wol.z, 1.f, m.ior) : 1.f;
+        if (m.type == B2RT_MAT_GLASS && !is_black(m.kt)) {
+            f3 wil;
+            if (refract_local(wol, m.ior, wil) && wil.z != 0.f && sp < MAX_TREE_DEPTH) {
+                float ac = fabsf(wil.z);
+                f3 w = mk3((1.f - F) * m.kt.x / ac * ac, (1.f - F) * m.kt.y / ac * ac, (1.f - F) * m.kt.z / ac * ac);
+                if (!is_black(w)) {
+                    stack[sp].o = sf.p; stack[sp].d = to_world(sf, wil); stack[sp].tmin = sf.ray_eps;
+                    stack[sp].T = nd.T * w; stack[sp].depth = nd.depth + 1; stack[sp].id = nd.id * 2u + 1u; ++sp;
+                }
+            }
+        }
+        if (!is_black(m.kd) && wol.z != 0.f && sp < MAX_TREE_DEPTH) {
+            f3 wil = mk3(-wol.x, -wol.y, wol.z);
+            float ac = fabsf(wil.z);
+            f3 w = mk3(F * m.kd.x / ac * ac, F * m.kd.y / ac * ac, F * m.kd.z / ac * ac);
+            if (!is_black(w)) {
+                stack[sp].o = sf.p; stack[sp].d = to_world(sf, wil); stack[sp].tmin = sf.ray_eps;
+                stack[sp].T = nd.T * w; stack[sp].depth = nd.depth + 1; stack[sp].id = nd.id * 2u; ++sp;
+            }
+        }
+    }
+    sample_rgb[3 * ls + 0] = L.x; sample_rgb[3 * ls + 1] = L.y; sample_rgb[3 * ls + 2] = L.z;
+    qcnt[ls] = nq;
+    if (overflow) atomicAdd(status, 1u);
+    if (dropped) atomicAdd(status + 1, 1u);
+}
+
+}  // namespace
+
+namespace {
+
+__global__ void __launch_bounds__(256)
+query_compact_kernel(const b2rt_query *__restrict__ qslots, const uint32_t *__restrict__ qoff, const uint32_t *__restrict__ qtot,
+                     int64_t n_samples, int slots, b2rt_query *__restrict__ out) {
+    int64_t ls = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (ls >= n_samples) return;
+    uint32_t o = qoff[ls];
+    uint32_t n = ((ls + 1 < n_samples) ? qoff[ls + 1] : qtot[0]) - o;
+    const float4 *src = reinterpret_cast<const float4 *>(qslots + ls * slots);
+    float4 *dst = reinterpret_cast<float4 *>(out + o);
+    for (uint32_t j = 0; j < 3 * n; ++j) dst[j] = src[j];
+}
+
+// K13 (box filter, radius 0.5: a sample only reaches its own pixel, film/image.cpp:77-137 with filters/box.cpp):
+// pixel = mean over its spp samples of (Le + direct + sum over the sample's leaves of caustic + indirect estimates)
+__global__ void __launch_bounds__(256)
+film_resolve_kernel(const float *__restrict__ sample_rgb, const uint32_t *__restrict__ qoff, const uint32_t *__restrict__ qtot,
+                    const float *__restrict__ rgb_c, const float *__restrict__ rgb_i, int64_t n_samples, int spp,
+                    int64_t first_pixel, int64_t n_pixels, float *__restrict__ out_rgb) {
+    int64_t lp = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (lp >= n_pixels) return;
+    f3 acc = mk3(0.f, 0.f, 0.f);
+    for (int k = 0; k < spp; ++k) {
+        int64_t ls = lp * spp + k;
+        f3 L = mk3(sample_rgb[3 * ls], sample_rgb[3 * ls + 1], sample_rgb[3 * ls + 2]);
+        uint32_t o = qoff[ls];
+        uint32_t n = ((ls + 1 < n_samples) ? qoff[ls + 1] : qtot[0]) - o;
+        for (uint32_t j = o; j < o + n; ++j) {
+            if (rgb_c) L = L + mk3(rgb_c[3 * j], rgb_c[3 * j + 1], rgb_c[3 * j + 2]);
+            if (rgb_i) L = L + mk3(rgb_i[3 * j], rgb_i[3 * j + 1], rgb_i[3 * j + 2]);
+        }
+        acc = acc + L;
+    }
+    float inv = 1.f / (float)spp;
+    float *o = out_rgb + 3 * (first_pixel + lp);
+    o[0] = acc.x * inv; o[1] = acc.y * inv; o[2] = acc.z * inv;
+}
+
+}  // namespace
+
+// d_out: device buffer of (x1-x0)*(y1-y0)*3 floats, crop-window row-major
+int b2rt_render_impl(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_params *fp, float *d_out) {
+    cudaStream_t st = ctx->stream;
+    DScene sc;
+    b2rt_fill_dscene(ctx, &sc);
+    const int64_t n_pixels = (int64_t)(fp->x1 - fp->x0) * (fp->y1 - fp->y0);
+    const bool any_spec = [&] {
+        for (const Material &m : ctx->h_materials) if (m.type != B2RT_MAT_MATTE) return true;
+        return false;
+    }();
+    int slots = 1;
+    if (any_spec) { int d = fp->max_specular_depth < 1 ? 1 : fp->max_specular_depth; slots = 1 << (d - 1 > 5 ? 5 : d - 1); }
+    const bool use_c = fp->use_caustic && ctx->maps[0].grid_built && ctx->maps[0].n > 0;
+    const bool use_i = fp->use_indirect && ctx->maps[1].grid_built && ctx->maps[1].n > 0;
+    b2rt_frame_params p = *fp;
+    p.use_caustic = use_c; p.use_indirect = use_i;
+    // chunk = whole pixels, at most ~2M samples
+    int64_t chunk_pixels = (1ll << 21) / fp->spp;
+    if (chunk_pixels < 1) chunk_pixels = 1;
+    if (chunk_pixels > n_pixels) chunk_pixels = n_pixels;
+    const int64_t cs = chunk_pixels * fp->spp;
+    B2RT_CUDA(ctx, ctx->d_samples.reserve((size_t)cs * 12));
+    B2RT_CUDA(ctx, ctx->d_qslots.reserve((size_t)cs * slots * sizeof(b2rt_query)));
+    B2RT_CUDA(ctx, ctx->d_qcnt.reserve((size_t)cs * 4));
+    B2RT_CUDA(ctx, ctx->d_queries.reserve((size_t)cs * slots * sizeof(b2rt_query)));
+    B2RT_CUDA(ctx, ctx->d_q_rgb.reserve((size_t)cs * slots * 12));
+    B2RT_CUDA(ctx, ctx->d_q_rgb2.reserve((size_t)cs * slots * 12));
+    uint32_t *counters = ctx->d_counters.as<uint32_t>();
+    for (int64_t p0 = 0; p0 < n_pixels; p0 += chunk_pixels) {
+        const int64_t np = (p0 + chunk_pixels <= n_pixels) ? chunk_pixels : n_pixels - p0;
+        const int64_t ns = np * fp->spp;
+        uint32_t *qcnt = ctx->d_qcnt.as<uint32_t>();
+        render_li_kernel<<<(unsigned)((ns + RENDER_THREADS - 1) / RENDER_THREADS), RENDER_THREADS, 0, st>>>(
+            sc, *cam, p, (uint32_t)ctx->seed, (uint32_t)(ctx->seed >> 32), p0 * fp->spp, ns, slots,
+            ctx->d_samples.as<float>(), ctx->d_qslots.as<b2rt_query>(), qcnt, counters + 8);
+        B2RT_LAUNCH_CHECK(ctx);
+        int rc = b2rt_exclusive_scan_u32(ctx, qcnt, ns, counters + 12);
+        if (rc) return rc;
+        const float *rgb_c = nullptr, *rgb_i = nullptr;
+        if (use_c || use_i) {
+            uint32_t tot = 0;
+            B2RT_CUDA(ctx, cudaMemcpyAsync(&tot, counters + 12, 4, cudaMemcpyDeviceToHost, st));
+            B2RT_CUDA(ctx, cudaStreamSynchronize(st));
+            query_compact_kernel<<<(unsigned)((ns + 255) / 256), 256, 0, st>>>(ctx->d_qslots.as<b2rt_query>(), qcnt,
+                                                                               counters + 12, ns, slots,
+                                                                               ctx->d_queries.as<b2rt_query>());
+            B2RT_LAUNCH_CHECK(ctx);
+            if (use_c) {
+                rc = b2rt_gather_impl(ctx, 0, tot, ctx->d_queries.as<b2rt_query>(), fp->nused, fp->max_dist2,
+                                      ctx->d_q_rgb.as<float>(), nullptr, nullptr, nullptr);
+                if (rc) return rc;
+                rgb_c = ctx->d_q_rgb.as<float>();
+            }
+            if (use_i) {
+                rc = b2rt_gather_impl(ctx, 1, tot, ctx->d_queries.as<b2rt_query>(), fp->nused, fp->max_dist2,
+                                      ctx->d_q_rgb2.as<float>(), nullptr, nullptr, nullptr);
+                if (rc) return rc;
+                rgb_i = ctx->d_q_rgb2.as<float>();
+            }
+        }
+        film_resolve_kernel<<<(unsigned)((np + 255) / 256), 256, 0, st>>>(ctx->d_samples.as<float>(), qcnt, counters + 12,
+                                                                          rgb_c, rgb_i, ns, fp->spp, p0, np, d_out);
+        B2RT_LAUNCH_CHECK(ctx);
+    }
+    return B2RT_OK;
+}

@@ -233,3 +233,69 @@ def fill_scene(target, desc):
         else:
             target.add_light(0, l[2], p=l[1])
     return first
+
+
+# ---- .pbrt text writer (for the reference's CPU renderer and for the drop-in run) and PFM reader ------------------------
+def _m16(o2w):
+    """row-major 3x4 -> pbrt `Transform [16]` (column-major 4x4)"""
+    m = np.vstack([np.asarray(o2w, np.float64).reshape(3, 4), [0, 0, 0, 1]])
+    return " ".join("%.9g" % v for v in m.T.reshape(-1))
+
+
+def to_pbrt(desc, eye, look, up, fov, xres, yres, spp, integrator, filename, renderer=None, sampler="lowdiscrepancy"):
+    """integrator: the full `SurfaceIntegrator ...` line.  Only features the reference's GPU path translates are used."""
+    L = ["LookAt %g %g %g  %g %g %g  %g %g %g" % (*eye, *look, *up),
+         'Camera "perspective" "float fov" [%g]' % fov,
+         'Film "image" "integer xresolution" [%d] "integer yresolution" [%d] "string filename" ["%s"]' % (xres, yres, filename),
+         'Sampler "%s" "integer pixelsamples" [%d]' % (sampler, spp), 'PixelFilter "box"', integrator]
+    if renderer:
+        L.append('Renderer "%s"' % renderer)
+    L.append("WorldBegin")
+    light_of_shape = {l[1]: l for l in desc["lights"] if l[0] == "disk"}
+    for l in desc["lights"]:
+        if l[0] == "point":
+            L.append('LightSource "point" "point from" [%g %g %g] "rgb I" [%g %g %g]' % (*l[1], *l[2]))
+    for si, sh in enumerate(desc["shapes"]):
+        mid = sh[3] if sh[0] == "mesh" else (sh[4] if sh[0] == "sphere" else sh[6])
+        t, kd, kt, ior = desc["materials"][mid]
+        L.append("AttributeBegin")
+        if t == MATTE:
+            L.append('  Material "matte" "rgb Kd" [%g %g %g]' % tuple(kd))
+        elif t == MIRROR:
+            L.append('  Material "mirror" "rgb Kr" [%g %g %g]' % tuple(kd))
+        else:
+            L.append('  Material "glass" "rgb Kr" [%g %g %g] "rgb Kt" [%g %g %g] "float index" [%g]' % (*kd, *kt, ior))
+        if si in light_of_shape:
+            l = light_of_shape[si]
+            L.append('  AreaLightSource "diffuse" "rgb L" [%g %g %g] "integer nsamples" [%d]' % (*l[2], l[3]))
+        if sh[0] == "mesh":
+            L.append('  Shape "trianglemesh" "integer indices" [%s] "point P" [%s]' % (
+                " ".join(str(int(v)) for v in np.asarray(sh[2]).reshape(-1)),
+                " ".join("%.9g" % v for v in np.asarray(sh[1], np.float64).reshape(-1))))
+        elif sh[0] == "sphere":
+            L.append('  Transform [%s]\n  Shape "sphere" "float radius" [%g]' % (_m16(sh[1]), sh[3]))
+        else:
+            L.append('  Transform [%s]\n  Shape "disk" "float height" [%g] "float radius" [%g] "float innerradius" [%g]' % (
+                _m16(sh[1]), sh[3], sh[4], sh[5]))
+        L.append("AttributeEnd")
+    L.append("WorldEnd")
+    return "\n".join(L) + "\n"
+
+
+def read_pfm(path):
+    with open(path, "rb") as f:
+        kind = f.readline().strip()
+        w, h = map(int, f.readline().split())
+        scale = float(f.readline())
+        data = np.frombuffer(f.read(), "<f4" if scale < 0 else ">f4")
+    img = data.reshape(h, w, 3 if kind == b"PF" else 1)
+    return np.ascontiguousarray(img[::-1]).astype(np.float32)      # PFM stores bottom row first
+
+
+def image_metrics(img, ref):
+    """exrdiff-style metrics (pbrt-v2/src/tools/exrdiff.cpp:73-103), normalised by the reference's mean:
+    mean |a-b| / mean b  (mean relative error),  RMSE / mean b,  and the bias of the image mean."""
+    a, b = np.asarray(img, np.float64), np.asarray(ref, np.float64)
+    mb = b.mean()
+    return {"mean_rel": float(np.abs(a - b).mean() / mb), "rmse_rel": float(np.sqrt(((a - b) ** 2).mean()) / mb),
+            "bias_rel": float((a.mean() - mb) / mb)}

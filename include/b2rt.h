@@ -153,6 +153,24 @@ int b2rt_gather(b2rt_ctx *ctx, int32_t map, int64_t nqueries, const b2rt_query *
 int b2rt_gather_sets(b2rt_ctx *ctx, int32_t map, int64_t nqueries, const b2rt_query *queries, int32_t k,
                      float max_dist2, int32_t *idx_out, int where);
 
+/* ---- camera pass: replaces the four launches of PhotonMappingRenderer::render / SimpleRenderer::render
+ * (cuda_render/photon_mapping/photonmappingrenderer.cpp:31-45,108-139,228-277; simple_render/simplerender.cpp:18-103)
+ * including the CPU camera-ray loop (util/camera/pbrtcamera.cpp:57-122) and the CPU film loop. ------------------- */
+/* pinhole camera: ray origin o, direction Normalize(A + x*B + y*C) for continuous raster coordinates (x, y) --
+ * exactly the rays pbrt's PerspectiveCamera::GenerateRay produces with lensradius 0 (cameras/perspective.cpp:81-114) */
+typedef struct { float o[3]; float A[3]; float B[3]; float C[3]; int32_t xres, yres; } b2rt_camera;
+typedef struct {
+    int32_t spp;                 /* samples per pixel (box filter, radius 0.5) */
+    int32_t max_specular_depth;  /* pbrt maxspeculardepth (default 5) */
+    int32_t nused;               /* photons per estimate (pbrt nused, default 50); <= 0: fixed radius */
+    float   max_dist2;           /* pbrt maxdist squared */
+    int32_t use_caustic, use_indirect, direct_lighting;   /* which terms of PhotonIntegrator::Li to evaluate */
+    int32_t x0, x1, y0, y1;      /* crop window in pixels [x0,x1) x [y0,y1): the image tile this call renders */
+} b2rt_frame_params;
+/* out_rgb: (x1-x0)*(y1-y0)*3 floats, row-major within the crop window.  Photon maps must have been shot and their
+ * grids built if use_caustic / use_indirect are set (maps that are empty or unbuilt contribute nothing). */
+int b2rt_render_frame(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_params *fp, float *out_rgb, int where);
+
 /* generic device sort exposed for tests/bench of the hand-written radix sort (K2):
  * stable LSD sort of (key32,value32) pairs on `key_bits` low bits; device pointers only. */
 int b2rt_sort_pairs(b2rt_ctx *ctx, int64_t n, uint32_t *keys, uint32_t *vals, int key_bits);
