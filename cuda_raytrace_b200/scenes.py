@@ -249,7 +249,7 @@ def to_pbrt(desc, eye, look, up, fov, xres, yres, spp, integrator, filename, ren
          'Film "image" "integer xresolution" [%d] "integer yresolution" [%d] "string filename" ["%s"]' % (xres, yres, filename),
          'Sampler "%s" "integer pixelsamples" [%d]' % (sampler, spp), 'PixelFilter "box"', integrator]
     if renderer:
-        L.append('Renderer "%s"' % renderer)
+        L.append(renderer if renderer.startswith("Renderer") else 'Renderer "%s"' % renderer)
     L.append("WorldBegin")
     light_of_shape = {l[1]: l for l in desc["lights"] if l[0] == "disk"}
     for l in desc["lights"]:

@@ -1,0 +1,339 @@
+// Implementation of the pbrt-facing boundary on top of the b2rt C ABI.  See cudarender.h / cuda_render/cudaapi.h.
+//
+// What each piece replaces in the reference (paths relative to /root/reference):
+//   CudaRenderInit / CreateCudaShape / CudaObjectInstance / CreateCudaRenderer   cuda_render/cudaapi.cpp:3-26
+//   CudaRender::createCudaShape (+ material cache, light index)                  cuda_render/cudarender.cpp:136-196
+//   shape conversion        cuda_render/util/shape/{cudatrianglemesh,cudasphere,cudadisk}.cpp
+//   material conversion     cuda_render/util/material/cudamaterial.cpp:8-75
+//   light conversion        cuda_render/util/light/cudalight.cpp:16-133
+//   camera rays             cuda_render/util/camera/pbrtcamera.cpp:57-122 (CPU loop -> three probe rays)
+//   film                    cuda_render/photon_mapping/photonmappingrenderer.cpp:247-283
+#include "cudarender.h"
+#include "cuda_render/cudaapi.h"
+#include "scene.h"
+#include "camera.h"
+#include "film.h"
+#include "sampler.h"
+#include "light.h"
+#include "material.h"
+#include "reflection.h"
+#include "intersection.h"
+#include "shapes/trianglemesh.h"
+#include "shapes/sphere.h"
+#include "shapes/disk.h"
+#include "lights/point.h"
+#include "lights/diffuse.h"
+#include <string.h>
+
+// ---- friend accessors: the fork's pbrt headers befriend these class names (shapes/trianglemesh.h:69,
+// ---- shapes/sphere.h:62, shapes/disk.h:45, lights/point.h:62, lights/diffuse.h:66) ----------------------------------
+class CudaTriangleMesh {
+public:
+    static int ntris(const TriangleMesh *m) { return m->ntris; }
+    static int nverts(const TriangleMesh *m) { return m->nverts; }
+    static const int *indices(const TriangleMesh *m) { return m->vertexIndex; }
+    static const Point *points(const TriangleMesh *m) { return m->p; }     // already in world space (trianglemesh.cpp:69-71)
+};
+class CudaSphere {
+public:
+    static float radius(const Sphere *s) { return s->radius; }
+};
+class CudaDisk {
+public:
+    static float height(const Disk *d) { return d->height; }
+    static float radius(const Disk *d) { return d->radius; }
+    static float inner(const Disk *d) { return d->innerRadius; }
+};
+class CudaLight {
+public:
+    static Point pos(const PointLight *l) { return l->lightPos; }
+    static Spectrum intensity(const PointLight *l) { return l->Intensity; }
+    static Spectrum emitted(const DiffuseAreaLight *l) { return l->Lemit; }
+};
+
+static CudaRender *gCudaRender = NULL;     // one renderer per process, like the reference (cudaapi.cpp:3)
+
+void CudaRenderInit() { gCudaRender = new CudaRender(); }
+
+void CreateCudaShape(const std::string &name, Reference<Shape> &shape, std::vector<Reference<Primitive> > *currentInstance,
+                     const Material *material, int lightIndex) {
+    gCudaRender->createCudaShape(name, shape, currentInstance, material, lightIndex);
+}
+
+void CudaObjectInstance(std::vector<Reference<Primitive> > *key, const Transform &transform) {
+    gCudaRender->objectInstance(key, transform);
+}
+
+Renderer *CreateCudaRenderer(Sampler *sampler, Camera *camera, const ParamSet &params, const std::string &rendername) {
+    gCudaRender->createRenderer(sampler, camera, params, rendername);
+    return gCudaRender;      // pbrt deletes it after Render (core/api.cpp:1199)
+}
+
+static void m34(const Matrix4x4 &m, float out[12]) {
+    for (int r = 0; r < 3; ++r) for (int c = 0; c < 4; ++c) out[4 * r + c] = m.m[r][c];
+}
+static void rgb3(const Spectrum &s, float out[3]) { s.ToRGB(out); }
+
+CudaRender::CudaRender() : ctx_(NULL), renderer_(NULL), sampler_(NULL), camera_(NULL) {
+    int device = 0;
+    if (const char *e = getenv("B2RT_DEVICE")) device = atoi(e);
+    uint64_t seed = 0;
+    if (const char *e = getenv("B2RT_SEED")) seed = strtoull(e, NULL, 0);
+    int rc = b2rt_create(device, seed, &ctx_);
+    if (rc) Severe("CudaRender: %s", b2rt_last_error(NULL));      // no CPU fallback: abort like cudashape.cpp:32
+}
+
+CudaRender::~CudaRender() {
+    delete renderer_;
+    delete sampler_;
+    delete camera_;
+    b2rt_destroy(ctx_);
+    if (gCudaRender == this) gCudaRender = NULL;
+}
+
+void CudaRender::check(int rc, const char *what) {
+    if (rc) Severe("CudaRender: %s failed: %s", what, b2rt_last_error(ctx_));
+}
+
+void CudaRender::createRenderer(Sampler *sampler, Camera *camera, const ParamSet &params, const std::string &name) {
+    sampler_ = sampler; camera_ = camera;
+    delete renderer_;
+    if (name == "simple") renderer_ = new SimpleRenderer(params);          // cudarender.cpp:126-134
+    else renderer_ = new PhotonMappingRenderer(params);
+}
+
+// Material -> (type, Kd|Kr, Kt, ior) through the public GetBSDF interface: evaluate the BSDF the material builds on a
+// dummy hit (textures are evaluated once at a default DifferentialGeometry like cudamaterial.cpp:35-42, so constants
+// only) and read the lobes back.  Unlike the reference this recovers glass Kr/Kt/index, which GlassMaterial keeps
+// private without a friend (materials/glass.h:44-60).
+int CudaRender::materialId(const Material *material) {
+    std::map<const Material *, int>::iterator it = materialCache_.find(material);
+    if (it != materialCache_.end()) return it->second;
+    int id = -1;
+    if (material) {
+        MemoryArena arena;
+        Vector dpdu(1, 0, 0), dpdv(0, 1, 0);
+        DifferentialGeometry dg(Point(0, 0, 0), dpdu, dpdv, Normal(0, 0, 0), Normal(0, 0, 0), 0.f, 0.f, NULL);
+        BSDF *bsdf = material->GetBSDF(dg, dg, arena);
+        Vector n(dg.nn), wi;
+        float kd[3] = {0.5f, 0.5f, 0.5f}, kt[3] = {0, 0, 0}, pdf = 0.f, ior = bsdf->eta;
+        int type = -1;
+        if (bsdf->NumComponents(BxDFType(BSDF_DIFFUSE | BSDF_REFLECTION)) > 0) {
+            rgb3(bsdf->f(n, n, BxDFType(BSDF_DIFFUSE | BSDF_REFLECTION)) * M_PI, kd);
+            type = B2RT_MAT_MATTE;
+        } else if (bsdf->NumComponents(BxDFType(BSDF_SPECULAR | BSDF_TRANSMISSION)) > 0) {
+            // glass at normal incidence: reflection lobe = F*Kr/cos, transmission lobe = (1-F)*Kt/cos, cos = 1
+            float F = ((ior - 1.f) / (ior + 1.f)) * ((ior - 1.f) / (ior + 1.f));
+            Spectrum fr = bsdf->Sample_f(n, &wi, BSDFSample(0.5f, 0.5f, 0.5f), &pdf, BxDFType(BSDF_SPECULAR | BSDF_REFLECTION));
+            rgb3(pdf > 0.f && F > 0.f ? fr / F : Spectrum(0.f), kd);
+            Spectrum ft = bsdf->Sample_f(n, &wi, BSDFSample(0.5f, 0.5f, 0.5f), &pdf, BxDFType(BSDF_SPECULAR | BSDF_TRANSMISSION));
+            rgb3(pdf > 0.f ? ft / (1.f - F) : Spectrum(0.f), kt);
+            type = B2RT_MAT_GLASS;
+        } else if (bsdf->NumComponents(BxDFType(BSDF_SPECULAR | BSDF_REFLECTION)) > 0) {
+            Spectrum fr = bsdf->Sample_f(n, &wi, BSDFSample(0.5f, 0.5f, 0.5f), &pdf, BxDFType(BSDF_SPECULAR | BSDF_REFLECTION));
+            rgb3(fr, kd);
+            type = B2RT_MAT_MIRROR;
+        }
+        if (type < 0) {
+            Warning("CudaRender: material not supported, using grey matte");        // cudamaterial.cpp:20
+            type = B2RT_MAT_MATTE;
+        }
+        check(b2rt_add_material(ctx_, type, kd, kt, ior, &id), "b2rt_add_material");
+    }
+    materialCache_[material] = id;
+    return id;
+}
+
+// hand one flattened shape (optionally moved by an instance transform) to the GPU library
+int CudaRender::submit(const ShapeRec &r, const Transform *extra, int lightIndex) {
+    int prim = -1;
+    const int al = lightIndex;      // b2rt area-light id == pbrt light index (lights are added in scene->lights order)
+    if (r.kind == 0) {
+        std::vector<float> P = r.P;
+        if (extra)
+            for (size_t i = 0; i + 2 < P.size(); i += 3) {
+                Point q = (*extra)(Point(P[i], P[i + 1], P[i + 2]));
+                P[i] = q.x; P[i + 1] = q.y; P[i + 2] = q.z;
+            }
+        check(b2rt_add_mesh(ctx_, (int)(P.size() / 3), P.data(), (int)(r.idx.size() / 3), r.idx.data(), NULL, NULL,
+                            r.material, al, &prim), "b2rt_add_mesh");
+    } else {
+        float o2w[12], w2o[12];
+        memcpy(o2w, r.o2w, sizeof(o2w)); memcpy(w2o, r.w2o, sizeof(w2o));
+        if (extra) {
+            Matrix4x4 a(r.o2w[0], r.o2w[1], r.o2w[2], r.o2w[3], r.o2w[4], r.o2w[5], r.o2w[6], r.o2w[7], r.o2w[8], r.o2w[9],
+                        r.o2w[10], r.o2w[11], 0, 0, 0, 1);
+            Transform t = (*extra) * Transform(a);
+            m34(t.GetMatrix(), o2w); m34(t.GetInverseMatrix(), w2o);
+        }
+        if (r.kind == 1) check(b2rt_add_sphere(ctx_, o2w, w2o, r.radius, r.material, al, &prim), "b2rt_add_sphere");
+        else check(b2rt_add_disk(ctx_, o2w, w2o, r.height, r.radius, r.inner, r.material, al, &prim), "b2rt_add_disk");
+    }
+    return prim;
+}
+
+// by shape NAME, like CudaShape::CreateCudaShape (util/shape/cudashape.cpp:13-28); anything else warns and is skipped
+// (cudarender.cpp:140-144)
+void CudaRender::createCudaShape(const std::string &name, Reference<Shape> &shape,
+                                 std::vector<Reference<Primitive> > *currentInstance, const Material *material,
+                                 int lightIndex) {
+    ShapeRec r;
+    r.radius = r.height = r.inner = 0.f;
+    if (name == "trianglemesh") {
+        const TriangleMesh *m = static_cast<const TriangleMesh *>(shape.GetPtr());
+        r.kind = 0;
+        const Point *p = CudaTriangleMesh::points(m);
+        r.P.resize(3 * (size_t)CudaTriangleMesh::nverts(m));
+        for (int i = 0; i < CudaTriangleMesh::nverts(m); ++i) { r.P[3 * i] = p[i].x; r.P[3 * i + 1] = p[i].y; r.P[3 * i + 2] = p[i].z; }
+        r.idx.assign(CudaTriangleMesh::indices(m), CudaTriangleMesh::indices(m) + 3 * (size_t)CudaTriangleMesh::ntris(m));
+    } else if (name == "sphere") {
+        const Sphere *s = static_cast<const Sphere *>(shape.GetPtr());
+        r.kind = 1; r.radius = CudaSphere::radius(s);
+    } else if (name == "disk") {
+        const Disk *d = static_cast<const Disk *>(shape.GetPtr());
+        r.kind = 2; r.radius = CudaDisk::radius(d); r.height = CudaDisk::height(d); r.inner = CudaDisk::inner(d);
+    } else {
+        Warning("CudaRender: shape \"%s\" is not supported by the CUDA renderer, skipped", name.c_str());
+        return;
+    }
+    if (r.kind != 0) {
+        m34(shape->ObjectToWorld->GetMatrix(), r.o2w);
+        m34(shape->WorldToObject->GetMatrix(), r.w2o);
+    }
+    r.material = materialId(material);
+    if (currentInstance) { instances_[currentInstance].push_back(r); return; }      // inside ObjectBegin/End: deferred
+    int prim = submit(r, NULL, lightIndex);
+    if (lightIndex >= 0) {
+        if (r.kind == 2) lightPrims_[lightIndex] = prim;
+        else Warning("CudaRender: only disks can be area lights (cudalight.cpp:35-56); emission of light %d ignored", lightIndex);
+    }
+}
+
+// instances are flattened: the shapes of the ObjectBegin block are re-submitted under the instance transform
+// (the reference builds an OptiX Transform node instead, cudarender.cpp:88-103)
+void CudaRender::objectInstance(std::vector<Reference<Primitive> > *key, const Transform &transform) {
+    std::map<std::vector<Reference<Primitive> > *, std::vector<ShapeRec> >::iterator it = instances_.find(key);
+    if (it == instances_.end()) return;
+    for (size_t i = 0; i < it->second.size(); ++i) submit(it->second[i], &transform, -1);
+}
+
+void CudaRender::Render(const Scene *scene) {
+    // lights, in scene->lights order so that ids agree with the lightIndex api.cpp passed for area-light shapes
+    for (size_t i = 0; i < scene->lights.size(); ++i) {
+        const Light *l = scene->lights[i];
+        float rgb[3], p[3] = {0, 0, 0};
+        int id = -1;
+        if (const PointLight *pl = dynamic_cast<const PointLight *>(l)) {
+            Point q = CudaLight::pos(pl);
+            p[0] = q.x; p[1] = q.y; p[2] = q.z;
+            rgb3(CudaLight::intensity(pl), rgb);
+            check(b2rt_add_light(ctx_, B2RT_LIGHT_POINT, p, rgb, -1, 1, &id), "b2rt_add_light");
+        } else if (const DiffuseAreaLight *al = dynamic_cast<const DiffuseAreaLight *>(l)) {
+            std::map<int, int>::const_iterator it = lightPrims_.find((int)i);
+            rgb3(CudaLight::emitted(al), rgb);
+            if (it == lightPrims_.end()) {
+                Warning("CudaRender: area light %d is not on a disk, treated as black", (int)i);
+                rgb[0] = rgb[1] = rgb[2] = 0.f;
+                check(b2rt_add_light(ctx_, B2RT_LIGHT_POINT, p, rgb, -1, 1, &id), "b2rt_add_light");
+            } else {
+                check(b2rt_add_light(ctx_, B2RT_LIGHT_DISK_AREA, NULL, rgb, it->second, l->nSamples, &id), "b2rt_add_light");
+            }
+        } else {
+            Warning("CudaRender: light %d has a type the CUDA renderer does not translate, treated as black", (int)i);
+            rgb[0] = rgb[1] = rgb[2] = 0.f;
+            check(b2rt_add_light(ctx_, B2RT_LIGHT_POINT, p, rgb, -1, 1, &id), "b2rt_add_light");
+        }
+    }
+    check(b2rt_build_accel(ctx_), "b2rt_build_accel");
+    renderer_->render(scene, this, camera_);
+}
+
+// ---- camera + film helpers -----------------------------------------------------------------------------------------
+// Recover the pinhole model d(x,y) ~ A + x*B + y*C from three rays of the pbrt camera itself (public GenerateRay), so
+// any projective pbrt camera with lensradius 0 works without friend access (cameras/perspective.cpp:81-114).
+static b2rt_camera probeCamera(const Camera *camera) {
+    const int W = camera->film->xResolution, H = camera->film->yResolution;
+    struct { float x, y; } pts[4] = {{W * .5f, H * .5f}, {0, 0}, {(float)W, 0}, {0, (float)H}};
+    Vector d[4]; Point o;
+    for (int i = 0; i < 4; ++i) {
+        CameraSample cs;
+        cs.imageX = pts[i].x; cs.imageY = pts[i].y; cs.lensU = cs.lensV = 0.5f; cs.time = 0.f;
+        Ray r;
+        camera->GenerateRay(cs, &r);
+        d[i] = Normalize(r.d); o = r.o;
+    }
+    Vector u[4];
+    for (int i = 1; i < 4; ++i) u[i] = d[i] / Dot(d[i], d[0]);      // un-normalise onto the plane dot(., forward) = 1
+    b2rt_camera c;
+    c.o[0] = o.x; c.o[1] = o.y; c.o[2] = o.z;
+    Vector B = (u[2] - u[1]) / (float)W, C = (u[3] - u[1]) / (float)H;
+    c.A[0] = u[1].x; c.A[1] = u[1].y; c.A[2] = u[1].z;
+    c.B[0] = B.x; c.B[1] = B.y; c.B[2] = B.z;
+    c.C[0] = C.x; c.C[1] = C.y; c.C[2] = C.z;
+    c.xres = W; c.yres = H;
+    return c;
+}
+
+// resolved pixels -> pbrt Film (film/image.cpp:77-137 AddSample at the pixel centre, then WriteImage :178-213), the
+// same hand-off the reference does per sample on the CPU (photonmappingrenderer.cpp:251-283)
+static void writeFilm(Camera *camera, const std::vector<float> &rgb) {
+    const int W = camera->film->xResolution, H = camera->film->yResolution;
+    for (int y = 0; y < H; ++y)
+        for (int x = 0; x < W; ++x) {
+            CameraSample cs;
+            cs.imageX = x + 0.5f; cs.imageY = y + 0.5f; cs.lensU = cs.lensV = 0.5f; cs.time = 0.f;
+            const float *c = &rgb[3 * ((size_t)y * W + x)];
+            float v[3] = {c[0], c[1], c[2]};
+            for (int k = 0; k < 3; ++k) if (!(v[k] >= 0.f) || isinf(v[k])) v[k] = 0.f;      // NaN / negative / inf guard
+            camera->film->AddSample(cs, Spectrum::FromRGB(v));
+        }
+    camera->film->WriteImage();
+}
+
+static b2rt_frame_params frameParams(const b2rt_camera &cam, Sampler *sampler) {
+    b2rt_frame_params fp;
+    memset(&fp, 0, sizeof(fp));
+    fp.spp = sampler ? sampler->samplesPerPixel : 1;
+    fp.max_specular_depth = 5; fp.nused = 50; fp.max_dist2 = 0.01f;
+    fp.direct_lighting = 1;
+    fp.x0 = 0; fp.x1 = cam.xres; fp.y0 = 0; fp.y1 = cam.yres;
+    return fp;
+}
+
+SimpleRenderer::SimpleRenderer(const ParamSet &) {}
+
+void SimpleRenderer::render(const Scene *, CudaRender *cr, Camera *camera) {
+    b2rt_camera cam = probeCamera(camera);
+    b2rt_frame_params fp = frameParams(cam, cr->sampler());
+    std::vector<float> img((size_t)cam.xres * cam.yres * 3);
+    cr->check(b2rt_render_frame(cr->ctx(), &cam, &fp, img.data(), B2RT_HOST), "b2rt_render_frame");
+    writeFilm(camera, img);
+}
+
+PhotonMappingRenderer::PhotonMappingRenderer(const ParamSet &params) {
+    nCaustic = params.FindOneInt("causticphotons", 20000);          // names and defaults: photonmap.cpp:784-801
+    nIndirect = params.FindOneInt("indirectphotons", 100000);
+    nUsed = params.FindOneInt("nused", 50);
+    maxSpecularDepth = params.FindOneInt("maxspeculardepth", 5);
+    maxPhotonDepth = params.FindOneInt("maxphotondepth", 5);
+    maxDist = params.FindOneFloat("maxdist", .1f);
+}
+
+void PhotonMappingRenderer::render(const Scene *scene, CudaRender *cr, Camera *camera) {
+    b2rt_ctx *ctx = cr->ctx();
+    if (scene->lights.size() > 0 && (nCaustic > 0 || nIndirect > 0)) {
+        int64_t paths[2], stored[2];
+        int64_t batch = 65536;
+        cr->check(b2rt_photons_shoot(ctx, nCaustic, nIndirect, maxPhotonDepth, batch, paths, stored), "b2rt_photons_shoot");
+        for (int m = 0; m < 2; ++m) cr->check(b2rt_photon_grid_build(ctx, m, 0.f, 0.f), "b2rt_photon_grid_build");
+        Info("CudaRender: %lld caustic photons from %lld paths, %lld indirect photons from %lld paths",
+             (long long)stored[0], (long long)paths[0], (long long)stored[1], (long long)paths[1]);
+    }
+    b2rt_camera cam = probeCamera(camera);
+    b2rt_frame_params fp = frameParams(cam, cr->sampler());
+    fp.max_specular_depth = maxSpecularDepth; fp.nused = nUsed; fp.max_dist2 = maxDist * maxDist;
+    fp.use_caustic = nCaustic > 0; fp.use_indirect = nIndirect > 0;
+    std::vector<float> img((size_t)cam.xres * cam.yres * 3);
+    cr->check(b2rt_render_frame(ctx, &cam, &fp, img.data(), B2RT_HOST), "b2rt_render_frame");
+    writeFilm(camera, img);
+}

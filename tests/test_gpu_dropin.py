@@ -1,0 +1,52 @@
+"""Drop-in test (-m gpu): the reference's own pbrt-v2 front end, built with -DHAS_CUDA_RENDER against shim/ (the
+cudaapi.h boundary) and libb2rt.so, renders a .pbrt scene file with `-c` (the reference's --force_cudarender switch,
+pbrt-v2/src/main/pbrt.cpp:51) and is compared with the same binary's CPU path on the same file.
+The binary is built in the build container (make -C shim; needs /root/reference) and travels to the GPU box."""
+import os
+import subprocess
+import numpy as np
+import pytest
+
+from cuda_raytrace_b200 import scenes as S
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BIN = os.path.join(ROOT, "shim", "_build", "pbrt_b2rt")
+EYE, LOOK, UP, FOV = (0, 1, 3.4), (0, 1, 0), (0, 1, 0), 40
+
+
+def _run(tmp_path, name, integrator, renderer, spp, res=96):
+    out = {}
+    for tag, flag in (("gpu", ["-c"]), ("cpu", [])):
+        pf = str(tmp_path / ("%s_%s.pfm" % (name, tag)))
+        scene = str(tmp_path / ("%s_%s.pbrt" % (name, tag)))
+        with open(scene, "w") as f:
+            f.write(S.to_pbrt(S.cornell_scene(boxes=True), EYE, LOOK, UP, FOV, res, res, spp, integrator, pf, renderer=renderer))
+        r = subprocess.run([BIN, "--quiet"] + flag + [scene], capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stderr[-2000:]
+        out[tag] = S.read_pfm(pf)
+    return out["gpu"], out["cpu"]
+
+
+def _block(img, b):
+    h, w, _ = img.shape
+    return img[: h // b * b, : w // b * b].reshape(h // b, b, w // b, b, 3).mean((1, 3))
+
+
+@pytest.mark.skipif(not os.path.exists(BIN), reason="shim/_build/pbrt_b2rt not built (needs /root/reference)")
+def test_dropin_simple_renderer_matches_cpu_directlighting(tmp_path):
+    gpu, cpu = _run(tmp_path, "simple", 'SurfaceIntegrator "directlighting" "integer maxdepth" [5]', "simple", spp=256)
+    m = S.image_metrics(_block(gpu, 8), _block(cpu, 8))
+    assert abs(m["bias_rel"]) < 0.005, m
+    assert m["mean_rel"] < 0.01, m
+
+
+@pytest.mark.skipif(not os.path.exists(BIN), reason="shim/_build/pbrt_b2rt not built (needs /root/reference)")
+def test_dropin_photon_renderer_matches_cpu_photonmap(tmp_path):
+    prm = ('"integer causticphotons" [20000] "integer indirectphotons" [300000] "integer nused" [100] "float maxdist" [0.4] '
+           '"integer maxphotondepth" [5] "integer maxspeculardepth" [5]')
+    gpu, cpu = _run(tmp_path, "photon", 'SurfaceIntegrator "photonmap" "bool finalgather" ["false"] ' + prm,
+                    'Renderer "photonmap" ' + prm, spp=64)
+    m = S.image_metrics(_block(gpu, 8), _block(cpu, 8))
+    assert abs(m["bias_rel"]) < 0.01, m
+    assert m["mean_rel"] < 0.03, m
