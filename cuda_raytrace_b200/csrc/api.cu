@@ -2,6 +2,7 @@
 // staging, buffer management; every compute step is a kernel in sort.cu / build.cu / trace.cu.
 // There is deliberately no CPU path: without a usable CUDA device b2rt_create fails.
 #include "b2rt_internal.cuh"
+#include <stdlib.h>
 #include <string.h>
 #include <math.h>
 
@@ -54,9 +55,17 @@ int b2rt_create(int device, uint64_t seed, b2rt_ctx **out) {
         delete ctx; return B2RT_E_CUDA;
     }
     ctx->sm_count = prop.multiProcessorCount;
+    if (const char *v = getenv("B2RT_TRACE_VARIANT")) ctx->trace_variant = atoi(v);
+    if (const char *v = getenv("B2RT_TRACE_REFILL")) ctx->trace_refill = atoi(v);
+    if (const char *v = getenv("B2RT_GATHER_VARIANT")) ctx->gather_variant = atoi(v);
     CK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
     CK(cudaEventCreate(&ctx->ev0)); CK(cudaEventCreate(&ctx->ev1));
     CK(cudaEventCreate(&ctx->evb0)); CK(cudaEventCreate(&ctx->evb1));
+    CK(cudaStreamCreateWithFlags(&ctx->stream_in, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&ctx->stream_out, cudaStreamNonBlocking));
+    CK(cudaEventCreateWithFlags(&ctx->ev_in, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&ctx->ev_k, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&ctx->ev_out, cudaEventDisableTiming));
     CK(ctx->d_counters.reserve(64));
     CK(cudaMemsetAsync(ctx->d_counters.p, 0, 64, ctx->stream));
 #undef CK
@@ -79,11 +88,13 @@ void b2rt_destroy(b2rt_ctx *ctx) {
                       &ctx->d_queries, &ctx->d_q_rgb, &ctx->d_q_r2, &ctx->d_q_found, &ctx->d_q_idx,
                       &ctx->d_samples, &ctx->d_qslots, &ctx->d_qcnt, &ctx->d_q_rgb2, &ctx->d_frame};
     for (PhotonMap &m : ctx->maps) {
-        m.photons.release(); m.sorted.release(); m.cell_start.release(); m.keys.release(); m.order.release();
+        m.photons.release(); m.sorted.release(); m.cell_start.release(); m.keys.release(); m.order.release(); m.pos4.release(); m.coarse.release();
     }
     for (DevBuf *b : bufs) b->release();
     cudaEventDestroy(ctx->ev0); cudaEventDestroy(ctx->ev1);
     cudaEventDestroy(ctx->evb0); cudaEventDestroy(ctx->evb1);
+    cudaEventDestroy(ctx->ev_in); cudaEventDestroy(ctx->ev_k); cudaEventDestroy(ctx->ev_out);
+    cudaStreamDestroy(ctx->stream_in); cudaStreamDestroy(ctx->stream_out);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -241,19 +252,32 @@ static int trace_common(b2rt_ctx *ctx, int64_t nrays, const b2rt_ray *rays, b2rt
     if (where != B2RT_HOST) { ctx->err = "trace: where must be B2RT_HOST or B2RT_DEVICE"; return B2RT_E_ARG; }
     cudaStream_t st = ctx->stream;
     B2RT_CUDA(ctx, ctx->d_rays.reserve((size_t)nrays * sizeof(b2rt_ray)));
-    B2RT_CUDA(ctx, cudaMemcpyAsync(ctx->d_rays.p, rays, (size_t)nrays * sizeof(b2rt_ray), cudaMemcpyHostToDevice, st));
-    int rc;
-    if (any) {
-        B2RT_CUDA(ctx, ctx->d_occ.reserve((size_t)nrays));
-        rc = b2rt_trace_impl(ctx, nrays, ctx->d_rays.as<b2rt_ray>(), nullptr, ctx->d_occ.as<uint8_t>(), true);
+    if (any) B2RT_CUDA(ctx, ctx->d_occ.reserve((size_t)nrays));
+    else B2RT_CUDA(ctx, ctx->d_hits.reserve((size_t)nrays * sizeof(b2rt_hit)));
+    // Chunked pipeline over three streams: the upload of chunk i+1, the traversal of chunk i and the download of
+    // chunk i-1 overlap (PCIe is full duplex; with pinned caller memory the copies are asynchronous).
+    const int64_t CH = 1 << 18;
+    B2RT_CUDA(ctx, cudaEventRecord(ctx->ev_k, st));                 // everything queued so far on the main stream
+    B2RT_CUDA(ctx, cudaStreamWaitEvent(ctx->stream_in, ctx->ev_k, 0));
+    for (int64_t c0 = 0; c0 < nrays; c0 += CH) {
+        const int64_t cn = nrays - c0 < CH ? nrays - c0 : CH;
+        b2rt_ray *dr = ctx->d_rays.as<b2rt_ray>() + c0;
+        B2RT_CUDA(ctx, cudaMemcpyAsync(dr, rays + c0, (size_t)cn * sizeof(b2rt_ray), cudaMemcpyHostToDevice, ctx->stream_in));
+        B2RT_CUDA(ctx, cudaEventRecord(ctx->ev_in, ctx->stream_in));
+        B2RT_CUDA(ctx, cudaStreamWaitEvent(st, ctx->ev_in, 0));
+        int rc = any ? b2rt_trace_impl(ctx, cn, dr, nullptr, ctx->d_occ.as<uint8_t>() + c0, true)
+                     : b2rt_trace_impl(ctx, cn, dr, ctx->d_hits.as<b2rt_hit>() + c0, nullptr, false);
         if (rc) return rc;
-        B2RT_CUDA(ctx, cudaMemcpyAsync(occ, ctx->d_occ.p, (size_t)nrays, cudaMemcpyDeviceToHost, st));
-    } else {
-        B2RT_CUDA(ctx, ctx->d_hits.reserve((size_t)nrays * sizeof(b2rt_hit)));
-        rc = b2rt_trace_impl(ctx, nrays, ctx->d_rays.as<b2rt_ray>(), ctx->d_hits.as<b2rt_hit>(), nullptr, false);
-        if (rc) return rc;
-        B2RT_CUDA(ctx, cudaMemcpyAsync(hits, ctx->d_hits.p, (size_t)nrays * sizeof(b2rt_hit), cudaMemcpyDeviceToHost, st));
+        B2RT_CUDA(ctx, cudaEventRecord(ctx->ev_k, st));
+        B2RT_CUDA(ctx, cudaStreamWaitEvent(ctx->stream_out, ctx->ev_k, 0));
+        if (any)
+            B2RT_CUDA(ctx, cudaMemcpyAsync(occ + c0, ctx->d_occ.as<uint8_t>() + c0, (size_t)cn, cudaMemcpyDeviceToHost, ctx->stream_out));
+        else
+            B2RT_CUDA(ctx, cudaMemcpyAsync(hits + c0, ctx->d_hits.as<b2rt_hit>() + c0, (size_t)cn * sizeof(b2rt_hit),
+                                           cudaMemcpyDeviceToHost, ctx->stream_out));
     }
+    B2RT_CUDA(ctx, cudaEventRecord(ctx->ev_out, ctx->stream_out));
+    B2RT_CUDA(ctx, cudaStreamWaitEvent(st, ctx->ev_out, 0));
     return check_status(ctx);
 }
 

@@ -67,6 +67,9 @@ struct PhotonMap {
     DevBuf sorted;           // b2rt_photon[n] in (cell key, path-order index) order
     DevBuf cell_start;       // uint32[n_cells+1]
     DevBuf keys, order;      // uint32[n] sorted cell keys / original indices (kept for parity downloads)
+    DevBuf pos4;             // float4[n] {x, y, z, bits(sorted index)}: what the gather's distance tests read
+    DevBuf coarse;           // uint32[cdims.x*cdims.y*cdims.z] photons per coarse cell (4^3 fine cells)
+    int32_t cdims[3] = {0, 0, 0};
     b2rt_grid_info grid{};
 };
 
@@ -76,8 +79,17 @@ struct b2rt_ctx {
     uint64_t seed = 0;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, evb0 = nullptr, evb1 = nullptr;
+    // host-buffer calls: upload / download streams and the events that chain the chunks
+    cudaStream_t stream_in = nullptr, stream_out = nullptr;
+    cudaEvent_t ev_in = nullptr, ev_k = nullptr, ev_out = nullptr;
     std::string err;
     int64_t launches = 0;
+    // kernel variants (environment overrides for A/B measurements: B2RT_TRACE_VARIANT, B2RT_TRACE_REFILL,
+    // B2RT_GATHER_VARIANT); results are identical for every setting
+    int trace_variant = 0;       // 0: one thread per ray, 1: persistent grid + ray pool
+    int trace_refill = 0;        // persistent: refill idle lanes when fewer than this many lanes are active
+    int pt_blocks_per_sm[2] = {0, 0};
+    int gather_variant = 0;      // 0: per-row scan with direct loads, 1: coarse table + TMA-staged tiles
 
     // host-side staging of the scene (flattened)
     std::vector<float> h_verts;      // xyz

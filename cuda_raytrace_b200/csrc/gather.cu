@@ -231,6 +231,289 @@ gather_kernel(const b2rt_photon *__restrict__ photons, const uint32_t *__restric
     }
 }
 
+
+// ---- tiled variant (default) ---------------------------------------------------------------------------------------
+// Two-level scan with TMA-staged photon tiles.  The fine grid keeps its bit-exact definition; on top of it sits a
+// coarse table (G2_C^3 fine cells per coarse cell, photon count each) built with the grid.
+//   * shells of COARSE cells around the query; the 32 lanes look up 32 coarse cells at once (count > 0 and box
+//     closer than the current bound), so empty space costs one 4-byte load per 64 fine cells;
+//   * a surviving coarse cell is 16 fine rows (z, y) of 4 x-adjacent cells = 16 contiguous runs of the sorted
+//     position array; 16 lanes fetch the run bounds at once (two coarse cells per round);
+//   * the runs are copied into the warp's shared-memory tile by the TMA: each lane issues one
+//     cp.async.bulk.shared.global for its run at the lane's prefix offset, all completing on the warp's mbarrier.
+//     The tile comes out dense, so the distance tests run on full 32-lane batches with conflict-free LDS.128;
+//   * positions are stored as {x, y, z, bits(index)}: the candidate key (d2 << 32 | index) needs no index
+//     arithmetic; alpha / wi are only touched for the k selected photons.
+// The selected set is the k smallest (d2, index) keys below the radius -- the same definition as the simple
+// kernel and the brute-force oracle, so results are bit-identical whatever the scan order.
+constexpr int G2_C = 4, G2_SHIFT = 2;
+constexpr int G2_STAGE = 512;            // staged positions per warp
+
+struct Gather2Grid {
+    float lo[3]; float cell, inv, slack;
+    int dims[3]; int cdims[3];
+};
+
+__device__ __forceinline__ uint32_t smem_addr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                     "selp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    } while (!ok);
+}
+__device__ __forceinline__ void tma_bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// squared distance from q to the box [lo, hi] per axis; sides flagged open extend to infinity (edge cells also hold
+// the photons that were clamped into them)
+__device__ __forceinline__ float axis_gap(float q, float lo, float hi, bool open_lo, bool open_hi, float slack) {
+    float d = 0.f;
+    if (!open_lo) d = fmaxf(d, lo - q - slack);
+    if (!open_hi) d = fmaxf(d, q - hi - slack);
+    return d;
+}
+
+template <bool KNN>
+__global__ void __launch_bounds__(GATHER_WARPS * 32)
+gather_tiled_kernel(const float4 *__restrict__ pos4, const b2rt_photon *__restrict__ photons,
+                    const uint32_t *__restrict__ cell_start, const uint32_t *__restrict__ coarse, Gather2Grid g,
+                    const b2rt_query *__restrict__ queries, int64_t nq, int k, float max_dist2, float n_paths,
+                    float *__restrict__ out_rgb, float *__restrict__ out_r2, int32_t *__restrict__ out_found,
+                    int32_t *__restrict__ idx_out) {
+    __shared__ __align__(128) float4 s_stage[GATHER_WARPS][G2_STAGE];
+    __shared__ uint64_t s_cand[GATHER_WARPS][GATHER_CAP];
+    __shared__ __align__(8) uint64_t s_bar[GATHER_WARPS];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint64_t *cand = s_cand[warp];
+    const float4 *stage = s_stage[warp];
+    const uint32_t stage_a = smem_addr(s_stage[warp]), bar = smem_addr(&s_bar[warp]);
+    const uint32_t lt = (1u << lane) - 1u;
+    if (lane == 0) mbar_init(bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    __syncthreads();
+    uint32_t phase = 0;
+
+    for (int64_t q = (int64_t)blockIdx.x * GATHER_WARPS + warp; q < nq; q += (int64_t)gridDim.x * GATHER_WARPS) {
+        const float4 *qp = reinterpret_cast<const float4 *>(queries + q);
+        const float4 q0 = __ldg(qp), q1 = __ldg(qp + 1), q2 = __ldg(qp + 2);
+        const float qa[3] = {q0.x, q0.y, q0.z};
+        const f3 nf = mk3(q0.w, q1.x, q1.y), kd = mk3(q1.z, q1.w, q2.x);
+        int C[3];
+#pragma unroll
+        for (int a = 0; a < 3; ++a)
+            C[a] = min(max((int)floorf((qa[a] - g.lo[a]) * g.inv), 0), g.dims[a] - 1) >> G2_SHIFT;
+        uint64_t bound = (uint64_t)__float_as_uint(max_dist2) << 32;
+        int count = 0;
+        f3 acc = mk3(0.f, 0.f, 0.f);
+        int found_fr = 0;
+        int smax = 0;
+#pragma unroll
+        for (int a = 0; a < 3; ++a) smax = max(smax, max(C[a], g.cdims[a] - 1 - C[a]));
+
+        for (int S = 0; S <= smax; ++S) {
+            const int w = 2 * S + 1, n_face = w * w;
+            const int ntask = S == 0 ? 1 : 2 * n_face + (2 * S - 1) * 8 * S;
+            for (int t0 = 0; t0 < ntask; t0 += 32) {
+                const int t = t0 + lane;
+                bool ok = t < ntask;
+                int ox = 0, oy = 0, oz = 0;
+                if (S > 0 && ok) {
+                    if (t < 2 * n_face) {
+                        const int u = t < n_face ? t : t - n_face;
+                        oz = t < n_face ? -S : S;
+                        oy = u / w - S; ox = u % w - S;
+                    } else {
+                        const int tt = t - 2 * n_face, per = 8 * S;
+                        const int layer = tt / per, r = tt % per, side = r / (2 * S), o = r % (2 * S);
+                        oz = layer - (S - 1);
+                        if (side == 0) { ox = -S + o; oy = -S; }
+                        else if (side == 1) { ox = S; oy = -S + o; }
+                        else if (side == 2) { ox = S - o; oy = S; }
+                        else { ox = -S; oy = S - o; }
+                    }
+                }
+                const int X = C[0] + ox, Y = C[1] + oy, Z = C[2] + oz;
+                ok = ok && X >= 0 && Y >= 0 && Z >= 0 && X < g.cdims[0] && Y < g.cdims[1] && Z < g.cdims[2];
+                if (ok) {
+                    const float r2 = __uint_as_float((uint32_t)(bound >> 32));
+                    const int P[3] = {X, Y, Z};
+                    float d2 = 0.f;
+#pragma unroll
+                    for (int a = 0; a < 3; ++a) {
+                        const int f0 = P[a] << G2_SHIFT, f1 = min(f0 + G2_C, g.dims[a]);
+                        const float gap = axis_gap(qa[a], g.lo[a] + (float)f0 * g.cell, g.lo[a] + (float)f1 * g.cell,
+                                                   f0 == 0, f1 == g.dims[a], g.slack);
+                        d2 += gap * gap;
+                    }
+                    ok = d2 < r2 && __ldg(coarse + ((int64_t)Z * g.cdims[1] + Y) * g.cdims[0] + X) != 0u;
+                }
+                uint32_t mask = __ballot_sync(0xffffffffu, ok);
+                const int packed = X | (Y << 10) | (Z << 20);
+                while (mask) {
+                    // two coarse cells per round: lanes 0-15 take the rows of the first, lanes 16-31 of the second
+                    const int l0 = __ffs(mask) - 1;
+                    mask &= mask - 1;
+                    int l1 = -1;
+                    if (mask) { l1 = __ffs(mask) - 1; mask &= mask - 1; }
+                    const int src = lane < 16 ? l0 : l1;
+                    const int pk = __shfl_sync(0xffffffffu, packed, src < 0 ? 0 : src);
+                    const int cx = pk & 1023, cy = (pk >> 10) & 1023, cz = (pk >> 20) & 1023;
+                    const int row = lane & 15;
+                    const int z = (cz << G2_SHIFT) + (row >> 2), y = (cy << G2_SHIFT) + (row & 3);
+                    const int xa = cx << G2_SHIFT, xb = min(xa + G2_C, g.dims[0]);     // cells [xa, xb)
+                    bool valid = src >= 0 && z < g.dims[2] && y < g.dims[1];
+                    if (valid) {
+                        const float r2 = __uint_as_float((uint32_t)(bound >> 32));
+                        float gx = axis_gap(qa[0], g.lo[0] + (float)xa * g.cell, g.lo[0] + (float)xb * g.cell, xa == 0,
+                                            xb == g.dims[0], g.slack);
+                        float gy = axis_gap(qa[1], g.lo[1] + (float)y * g.cell, g.lo[1] + (float)(y + 1) * g.cell, y == 0,
+                                            y + 1 == g.dims[1], g.slack);
+                        float gz = axis_gap(qa[2], g.lo[2] + (float)z * g.cell, g.lo[2] + (float)(z + 1) * g.cell, z == 0,
+                                            z + 1 == g.dims[2], g.slack);
+                        valid = gx * gx + gy * gy + gz * gz < r2;
+                    }
+                    uint32_t b = 0, e = 0;
+                    if (valid) {
+                        const int64_t rb = ((int64_t)z * g.dims[1] + y) * g.dims[0];
+                        b = __ldg(cell_start + rb + xa);
+                        e = __ldg(cell_start + rb + xb);
+                    }
+                    // ---- stage the runs [b, e) of all lanes into the warp's tile, G2_STAGE positions at a time ----
+                    while (true) {
+                        const int n = (int)(e - b);
+                        int inc = n;
+#pragma unroll
+                        for (int o = 1; o < 32; o <<= 1) {
+                            const int up = __shfl_up_sync(0xffffffffu, inc, o);
+                            if (lane >= o) inc += up;
+                        }
+                        const int all = __shfl_sync(0xffffffffu, inc, 31);
+                        if (all == 0) break;
+                        const int off = inc - n;
+                        const int take = off < G2_STAGE ? min(n, G2_STAGE - off) : 0;
+                        const int total = min(all, G2_STAGE);
+                        fence_proxy_async_smem();          // earlier generic reads of the tile before the async writes
+                        __syncwarp();
+                        if (lane == 0) mbar_expect_tx(bar, (uint32_t)total * 16u);
+                        __syncwarp();
+                        if (take > 0) tma_bulk_g2s(stage_a + (uint32_t)off * 16u, pos4 + b, (uint32_t)take * 16u, bar);
+                        b += (uint32_t)take;
+                        mbar_wait(bar, phase);
+                        phase ^= 1u;
+                        for (int i0 = 0; i0 < total; i0 += 32) {
+                            const int i = i0 + lane;
+                            bool pass = false;
+                            uint64_t key = 0;
+                            if (i < total) {
+                                const float4 pa = stage[i];
+                                const float dx = pa.x - qa[0], dy = pa.y - qa[1], dz = pa.z - qa[2];
+                                const float d2 = dx * dx + dy * dy + dz * dz;
+                                key = ((uint64_t)__float_as_uint(d2) << 32) | __float_as_uint(pa.w);
+                                pass = key < bound;
+                            }
+                            if (KNN) {
+                                const uint32_t m = __ballot_sync(0xffffffffu, pass);
+                                if (m) {
+                                    if (pass) cand[count + __popc(m & lt)] = key;
+                                    count += __popc(m);
+                                    __syncwarp();
+                                    if (count > GATHER_CAP - 32) {
+                                        count = warp_select(cand, count, k, lane);
+                                        if (count == k) bound = cand[k - 1];
+                                    }
+                                }
+                            } else if (pass) {
+                                const float d2 = __uint_as_float((uint32_t)(key >> 32));
+                                const float4 *pp = reinterpret_cast<const float4 *>(photons + (uint32_t)key);
+                                const float4 pa = __ldg(pp);
+                                const f3 wi = oct_decode(__float_as_uint(pa.w));
+                                if (dot3(nf, wi) > 0.f) {
+                                    const float4 pb = __ldg(pp + 1);
+                                    const float sk = 1.f - d2 / max_dist2;
+                                    const float wgt = 3.f * B2_INV_PI * sk * sk / (n_paths * max_dist2);
+                                    acc = acc + mk3(wgt * pb.x, wgt * pb.y, wgt * pb.z);
+                                }
+                                ++found_fr;
+                            }
+                        }
+                        __syncwarp();
+                    }
+                }
+            }
+            // ---- after the shell: tighten, then decide whether anything outside the scanned block can still matter ----
+            if (KNN && count > k) {
+                count = warp_select(cand, count, k, lane);
+                if (count == k) bound = cand[k - 1];
+            }
+            float dmin = INFINITY;
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                const int f0 = (C[a] - S) << G2_SHIFT, f1 = (C[a] + S + 1) << G2_SHIFT;
+                if (f0 > 0) dmin = fminf(dmin, qa[a] - (g.lo[a] + (float)f0 * g.cell));
+                if (f1 < g.dims[a]) dmin = fminf(dmin, (g.lo[a] + (float)f1 * g.cell) - qa[a]);
+            }
+            if (dmin == INFINITY) break;
+            dmin -= g.slack;
+            const float r2 = __uint_as_float((uint32_t)(bound >> 32));
+            if (dmin > 0.f && dmin * dmin >= r2) break;
+        }
+
+        if (KNN) {
+            count = warp_select(cand, count, k, lane);
+            const float md2 = (count == k) ? __uint_as_float((uint32_t)(cand[k - 1] >> 32)) : max_dist2;
+            for (int j = lane; j < count; j += 32) {
+                const uint64_t key = cand[j];
+                const uint32_t i = (uint32_t)key;
+                const float d2 = __uint_as_float((uint32_t)(key >> 32));
+                const float4 *pp = reinterpret_cast<const float4 *>(photons + i);
+                const float4 pa = __ldg(pp), pb = __ldg(pp + 1);
+                const f3 wi = oct_decode(__float_as_uint(pa.w));
+                if (dot3(nf, wi) > 0.f) {
+                    const float sk = 1.f - d2 / md2;
+                    const float wgt = 3.f * B2_INV_PI * sk * sk / (n_paths * md2);
+                    acc = acc + mk3(wgt * pb.x, wgt * pb.y, wgt * pb.z);
+                }
+            }
+            if (idx_out)
+                for (int j = lane; j < k; j += 32) idx_out[q * k + j] = j < count ? (int32_t)(uint32_t)cand[j] : -1;
+            if (lane == 0) {
+                if (out_r2) out_r2[q] = md2;
+                if (out_found) out_found[q] = count;
+            }
+            __syncwarp();
+        } else {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) found_fr += __shfl_xor_sync(0xffffffffu, found_fr, o);
+            if (lane == 0) {
+                if (out_r2) out_r2[q] = max_dist2;
+                if (out_found) out_found[q] = found_fr;
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            acc.x = acc.x + __shfl_xor_sync(0xffffffffu, acc.x, o);
+            acc.y = acc.y + __shfl_xor_sync(0xffffffffu, acc.y, o);
+            acc.z = acc.z + __shfl_xor_sync(0xffffffffu, acc.z, o);
+        }
+        if (lane == 0 && out_rgb) {
+            out_rgb[3 * q + 0] = acc.x * kd.x * B2_INV_PI;
+            out_rgb[3 * q + 1] = acc.y * kd.y * B2_INV_PI;
+            out_rgb[3 * q + 2] = acc.z * kd.z * B2_INV_PI;
+        }
+    }
+}
+
 }  // namespace
 
 int b2rt_gather_impl(b2rt_ctx *ctx, int map, int64_t nq, const b2rt_query *d_queries, int k, float max_dist2,
@@ -250,6 +533,24 @@ int b2rt_gather_impl(b2rt_ctx *ctx, int map, int64_t nq, const b2rt_query *d_que
     int64_t cap = (int64_t)ctx->sm_count * 16;
     if (blocks > cap) blocks = cap;
     float npaths = (float)m.n_paths;    // pbrt: int nPaths * float maxDist2
+    if (ctx->gather_variant == 1) {
+        Gather2Grid g2;
+        for (int a = 0; a < 3; ++a) { g2.lo[a] = g.lo[a]; g2.dims[a] = g.dims[a]; g2.cdims[a] = m.cdims[a]; }
+        g2.cell = g.cell; g2.inv = g.inv; g2.slack = g.slack;
+        cap = (int64_t)ctx->sm_count * 4;       // 40 KB shared memory per block: 4 blocks per SM, persistent over queries
+        blocks = (nq + GATHER_WARPS - 1) / GATHER_WARPS;
+        if (blocks > cap) blocks = cap;
+        if (k > 0)
+            gather_tiled_kernel<true><<<(unsigned)blocks, GATHER_WARPS * 32, 0, ctx->stream>>>(
+                m.pos4.as<float4>(), m.sorted.as<b2rt_photon>(), m.cell_start.as<uint32_t>(), m.coarse.as<uint32_t>(), g2,
+                d_queries, nq, k, max_dist2, npaths, d_rgb, d_r2, d_found, d_idx);
+        else
+            gather_tiled_kernel<false><<<(unsigned)blocks, GATHER_WARPS * 32, 0, ctx->stream>>>(
+                m.pos4.as<float4>(), m.sorted.as<b2rt_photon>(), m.cell_start.as<uint32_t>(), m.coarse.as<uint32_t>(), g2,
+                d_queries, nq, k, max_dist2, npaths, d_rgb, d_r2, d_found, d_idx);
+        B2RT_LAUNCH_CHECK(ctx);
+        return B2RT_OK;
+    }
     if (k > 0)
         gather_kernel<true><<<(unsigned)blocks, GATHER_WARPS * 32, 0, ctx->stream>>>(
             m.sorted.as<b2rt_photon>(), m.cell_start.as<uint32_t>(), g, d_queries, nq, k, max_dist2, npaths, d_rgb,

@@ -303,13 +303,34 @@ grid_keys_kernel(const b2rt_photon *__restrict__ ph, int64_t n, GridParams g, ui
 
 __global__ void __launch_bounds__(256)
 grid_reorder_kernel(const b2rt_photon *__restrict__ ph, const uint32_t *__restrict__ order, int64_t n,
-                    b2rt_photon *__restrict__ sorted) {
+                    b2rt_photon *__restrict__ sorted, float4 *__restrict__ pos4) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const float4 *src = reinterpret_cast<const float4 *>(ph + order[i]);
     float4 a = __ldg(src), b = __ldg(src + 1);
     float4 *dst = reinterpret_cast<float4 *>(sorted + i);
     dst[0] = a; dst[1] = b;
+    pos4[i] = make_float4(a.x, a.y, a.z, __uint_as_float((uint32_t)i));
+}
+
+// photons per coarse cell (4^3 fine cells): 16 fine rows, each an x-run of <= 4 cells = one cell_start difference
+__global__ void __launch_bounds__(256)
+grid_coarse_kernel(const uint32_t *__restrict__ cell_start, int dx, int dy, int dz, int cx, int cy, int cz,
+                   uint32_t *__restrict__ coarse) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= cx * cy * cz) return;
+    const int X = i % cx, Y = (i / cx) % cy, Z = i / (cx * cy);
+    const int xa = X * 4, xb = min(xa + 4, dx);
+    uint32_t cnt = 0;
+    for (int zs = 0; zs < 4; ++zs)
+        for (int ys = 0; ys < 4; ++ys) {
+            const int z = Z * 4 + zs, y = Y * 4 + ys;
+            if (z < dz && y < dy) {
+                const int64_t rb = ((int64_t)z * dy + y) * dx;
+                cnt += cell_start[rb + xb] - cell_start[rb + xa];
+            }
+        }
+    coarse[i] = cnt;
 }
 
 }  // namespace
@@ -371,6 +392,10 @@ int b2rt_photon_grid_build_impl(b2rt_ctx *ctx, int map, float cell_size, float t
     B2RT_CUDA(ctx, m.keys.reserve((size_t)nn * 4));
     B2RT_CUDA(ctx, m.order.reserve((size_t)nn * 4));
     B2RT_CUDA(ctx, m.sorted.reserve((size_t)nn * sizeof(b2rt_photon)));
+    B2RT_CUDA(ctx, m.pos4.reserve((size_t)nn * sizeof(float4)));
+    for (int a = 0; a < 3; ++a) m.cdims[a] = (dims[a] + 3) / 4;
+    const int n_coarse = m.cdims[0] * m.cdims[1] * m.cdims[2];
+    B2RT_CUDA(ctx, m.coarse.reserve((size_t)n_coarse * 4));
     if (n > 0) {
         B2RT_CUDA(ctx, ctx->d_keys_alt.reserve((size_t)n * 4));
         B2RT_CUDA(ctx, ctx->d_vals_alt.reserve((size_t)n * 4));
@@ -390,8 +415,15 @@ int b2rt_photon_grid_build_impl(b2rt_ctx *ctx, int map, float cell_size, float t
         if (in_alt) { std::swap(m.keys, ctx->d_keys_alt); std::swap(m.order, ctx->d_vals_alt); }
         rc = b2rt_exclusive_scan_u32(ctx, m.cell_start.as<uint32_t>(), n_cells + 1, nullptr);
         if (rc) return rc;
-        grid_reorder_kernel<<<grid, 256, 0, st>>>(ph, m.order.as<uint32_t>(), n, m.sorted.as<b2rt_photon>());
+        grid_reorder_kernel<<<grid, 256, 0, st>>>(ph, m.order.as<uint32_t>(), n, m.sorted.as<b2rt_photon>(),
+                                                  m.pos4.as<float4>());
         B2RT_LAUNCH_CHECK(ctx);
+        grid_coarse_kernel<<<(n_coarse + 255) / 256, 256, 0, st>>>(m.cell_start.as<uint32_t>(), dims[0], dims[1], dims[2],
+                                                                   m.cdims[0], m.cdims[1], m.cdims[2],
+                                                                   m.coarse.as<uint32_t>());
+        B2RT_LAUNCH_CHECK(ctx);
+    } else {
+        B2RT_CUDA(ctx, cudaMemsetAsync(m.coarse.p, 0, (size_t)n_coarse * 4, st));
     }
     B2RT_CUDA(ctx, cudaEventRecord(ctx->evb1, st));
     B2RT_CUDA(ctx, cudaEventSynchronize(ctx->evb1));

@@ -41,6 +41,156 @@ trace_kernel(const WideNode *__restrict__ nodes, const PrimRec *__restrict__ rec
     }
 }
 
+
+// ---- persistent variant -----------------------------------------------------------------------------------------
+// One resident grid (blocks = SMs x occupancy) pulls rays from a global pool instead of one thread per ray:
+//   * a warp fetches 32 consecutive rays at a time (caller order, so a warp stays coherent for camera rays);
+//   * when fewer than `refill` lanes of the warp are still traversing, the idle lanes are refilled from the pool
+//     -- ranks from __ballot_sync + __popc, one atomicAdd per warp -- so long rays do not hold 31 idle lanes;
+//   * the traversal stack lives in shared memory, one column per thread (bank = lane: conflict-free); only entries
+//     deeper than PT_SSTACK spill to a local array;
+//   * while-while loop: descend through internal nodes without leaving the node branch, then test the leaf.
+// Results are identical to trace_kernel by construction: the winner is (min t, then min prim id), independent of
+// the visiting order.
+constexpr int PT_THREADS = 128;
+constexpr int PT_SSTACK = 12;
+
+template <bool ANY>
+__global__ void __launch_bounds__(PT_THREADS)
+trace_persistent_kernel(const WideNode *__restrict__ nodes, const PrimRec *__restrict__ recs,
+                        const AnalyticPrim *__restrict__ analytic, const b2rt_ray *__restrict__ rays,
+                        b2rt_hit *__restrict__ hits, uint8_t *__restrict__ occ, int64_t nrays,
+                        unsigned long long *pool, int refill, uint32_t *status) {
+    __shared__ int32_t s_stack[PT_SSTACK][PT_THREADS];
+    int32_t l_stack[B2RT_STACK_SIZE - PT_SSTACK];
+    const int tid = threadIdx.x, lane = tid & 31;
+    const uint32_t lt = (1u << lane) - 1u;
+
+    RayD r;
+    float idx = 0.f, idy = 0.f, idz = 0.f;
+    float best_t = 0.f, best_b1 = 0.f, best_b2 = 0.f;
+    int best_prim = 0x7fffffff;
+    bool found = false, active = false, exhausted = false;
+    int sp = 0;
+    int32_t cur = 0;
+    int64_t my = 0;
+
+#define PT_PUSH(v) do { if (sp < PT_SSTACK) s_stack[sp][tid] = (v); else l_stack[sp - PT_SSTACK] = (v); ++sp; } while (0)
+#define PT_POP() (--sp, (sp < PT_SSTACK) ? s_stack[sp][tid] : l_stack[sp - PT_SSTACK])
+
+    for (;;) {
+        // ---- refill idle lanes from the pool ----------------------------------------------------------------
+        const uint32_t idle = __ballot_sync(0xffffffffu, !active);
+        if (idle && !exhausted) {
+            const int want = __popc(idle);
+            unsigned long long base = 0;
+            if (lane == 0) base = atomicAdd(pool, (unsigned long long)want);
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (!active) {
+                const int64_t i = (int64_t)base + __popc(idle & lt);
+                if (i < nrays) {
+                    const float4 *rp = reinterpret_cast<const float4 *>(rays + i);
+                    const float4 r0 = __ldg(rp), r1 = __ldg(rp + 1);
+                    r.ox = r0.x; r.oy = r0.y; r.oz = r0.z; r.tmin = r0.w;
+                    r.dx = r1.x; r.dy = r1.y; r.dz = r1.z;
+                    r.ddx = r1.x; r.ddy = r1.y; r.ddz = r1.z;
+                    idx = 1.f / r1.x; idy = 1.f / r1.y; idz = 1.f / r1.z;
+                    best_t = r1.w; best_prim = 0x7fffffff; best_b1 = 0.f; best_b2 = 0.f;
+                    found = false; sp = 0; cur = 0; my = i; active = true;
+                }
+            }
+            if ((int64_t)base + want >= nrays) exhausted = true;
+        }
+        if (!__any_sync(0xffffffffu, active)) break;
+
+        // ---- traverse until this ray ends or the warp has thinned out ------------------------------------------
+        while (active) {
+            bool done = false;
+            // internal nodes
+            while (cur >= 0) {
+                const float4 *np = reinterpret_cast<const float4 *>(nodes + cur);
+                const float4 lox = __ldg(np), hix = __ldg(np + 1), loy = __ldg(np + 2), hiy = __ldg(np + 3),
+                             loz = __ldg(np + 4), hiz = __ldg(np + 5);
+                const int4 ch = __ldg(reinterpret_cast<const int4 *>(np + 6));
+                float tn[4]; int32_t cr[4];
+                const float lx[4] = {lox.x, lox.y, lox.z, lox.w}, hx[4] = {hix.x, hix.y, hix.z, hix.w};
+                const float ly[4] = {loy.x, loy.y, loy.z, loy.w}, hy[4] = {hiy.x, hiy.y, hiy.z, hiy.w};
+                const float lz[4] = {loz.x, loz.y, loz.z, loz.w}, hz[4] = {hiz.x, hiz.y, hiz.z, hiz.w};
+                cr[0] = ch.x; cr[1] = ch.y; cr[2] = ch.z; cr[3] = ch.w;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    float t0x = (lx[k] - r.ox) * idx, t1x = (hx[k] - r.ox) * idx;
+                    float t0y = (ly[k] - r.oy) * idy, t1y = (hy[k] - r.oy) * idy;
+                    float t0z = (lz[k] - r.oz) * idz, t1z = (hz[k] - r.oz) * idz;
+                    float tnear = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), r.tmin));
+                    float tfar = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), best_t));
+                    float tn_p = tnear - fabsf(tnear) * 2e-6f;
+                    float tf_p = tfar + fabsf(tfar) * 2e-6f;
+                    bool h = (tn_p <= tf_p) && (cr[k] != B2RT_CHILD_EMPTY);
+                    tn[k] = h ? tnear : INFINITY;
+                }
+#define B2RT_CSWAP(a, b)                                                                  \
+    if (tn[b] < tn[a]) { float tt = tn[a]; tn[a] = tn[b]; tn[b] = tt; int32_t cc = cr[a]; cr[a] = cr[b]; cr[b] = cc; }
+                B2RT_CSWAP(0, 1) B2RT_CSWAP(2, 3) B2RT_CSWAP(0, 2) B2RT_CSWAP(1, 3) B2RT_CSWAP(1, 2)
+#undef B2RT_CSWAP
+                const int nhit = (tn[0] < INFINITY) + (tn[1] < INFINITY) + (tn[2] < INFINITY) + (tn[3] < INFINITY);
+                if (nhit == 0) {
+                    if (sp == 0) { done = true; break; }
+                    cur = PT_POP();
+                    continue;
+                }
+                if (sp + 3 > B2RT_STACK_SIZE) { atomicAdd(status, 1u); done = true; break; }
+                if (nhit > 3) PT_PUSH(cr[3]);
+                if (nhit > 2) PT_PUSH(cr[2]);
+                if (nhit > 1) PT_PUSH(cr[1]);
+                cur = cr[0];
+            }
+            if (!done) {
+                // leaf: 1..8 primitive records
+                const uint32_t ref = (uint32_t)cur & 0x7fffffffu;
+                const uint32_t first = ref >> 3, cnt = (ref & 7u) + 1u;
+                for (uint32_t s = first; s < first + cnt; ++s) {
+                    const float4 *pp = reinterpret_cast<const float4 *>(recs + s);
+                    const float4 A = __ldg(pp), B = __ldg(pp + 1), C = __ldg(pp + 2);
+                    const int prim = __float_as_int(A.w);
+                    const int type = __float_as_int(B.w);
+                    float t, b1 = 0.f, b2 = 0.f;
+                    bool h;
+                    if (type == B2RT_PRIM_TRI) h = tri_test(r, A, B, C, best_t, t, b1, b2);
+                    else if (type == B2RT_PRIM_SPHERE) h = sphere_test(r, analytic[__float_as_int(C.w)], best_t, t);
+                    else h = disk_test(r, analytic[__float_as_int(C.w)], best_t, t);
+                    if (h) {
+                        if (ANY) { found = true; break; }
+                        if (t < best_t || prim < best_prim) {
+                            best_t = t; best_prim = prim; best_b1 = b1; best_b2 = b2; found = true;
+                        }
+                    }
+                }
+                if ((ANY && found) || sp == 0) done = true;
+                else cur = PT_POP();
+            }
+            if (done) {
+                if (ANY) {
+                    occ[my] = found ? 1 : 0;
+                } else {
+                    float4 o;
+                    o.x = found ? best_t : INFINITY; o.y = __int_as_float(found ? best_prim : -1);
+                    o.z = best_b1; o.w = best_b2;
+                    *reinterpret_cast<float4 *>(hits + my) = o;
+                }
+                active = false;
+                break;
+            }
+            if (!exhausted && __popc(__activemask()) < refill) break;
+        }
+        __syncwarp();
+    }
+#undef PT_PUSH
+#undef PT_POP
+}
+
+__global__ void pool_reset_kernel(unsigned long long *pool) { *pool = 0ull; }
+
 }  // namespace
 int b2rt_trace_impl(b2rt_ctx *ctx, int64_t n, const b2rt_ray *d_rays, b2rt_hit *d_hits, uint8_t *d_occ,
                     bool any_hit) {
@@ -49,6 +199,29 @@ int b2rt_trace_impl(b2rt_ctx *ctx, int64_t n, const b2rt_ray *d_rays, b2rt_hit *
     const PrimRec *recs = ctx->d_prim_recs.as<PrimRec>();
     const AnalyticPrim *an = ctx->d_analytic.as<AnalyticPrim>();
     uint32_t *status = ctx->d_counters.as<uint32_t>() + 8;
+    if (ctx->trace_variant == 1) {
+        // persistent grid: every SM holds as many blocks as the occupancy calculator allows
+        int &per_sm = any_hit ? ctx->pt_blocks_per_sm[1] : ctx->pt_blocks_per_sm[0];
+        if (per_sm == 0) {
+            if (any_hit) B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_persistent_kernel<true>, PT_THREADS, 0));
+            else B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_persistent_kernel<false>, PT_THREADS, 0));
+            if (per_sm < 1) per_sm = 1;
+        }
+        int64_t blocks = (int64_t)ctx->sm_count * per_sm;
+        int64_t need = (n + PT_THREADS - 1) / PT_THREADS;
+        if (blocks > need) blocks = need;
+        unsigned long long *pool = reinterpret_cast<unsigned long long *>(ctx->d_counters.as<uint32_t>() + 12);
+        pool_reset_kernel<<<1, 1, 0, ctx->stream>>>(pool);
+        B2RT_LAUNCH_CHECK(ctx);
+        if (any_hit)
+            trace_persistent_kernel<true><<<(unsigned)blocks, PT_THREADS, 0, ctx->stream>>>(
+                nodes, recs, an, d_rays, nullptr, d_occ, n, pool, ctx->trace_refill, status);
+        else
+            trace_persistent_kernel<false><<<(unsigned)blocks, PT_THREADS, 0, ctx->stream>>>(
+                nodes, recs, an, d_rays, d_hits, nullptr, n, pool, ctx->trace_refill, status);
+        B2RT_LAUNCH_CHECK(ctx);
+        return B2RT_OK;
+    }
     int64_t grid = (n + TRACE_THREADS - 1) / TRACE_THREADS;
     if (any_hit)
         trace_kernel<true><<<(unsigned)grid, TRACE_THREADS, 0, ctx->stream>>>(nodes, recs, an, d_rays, nullptr,
