@@ -57,7 +57,9 @@ int b2rt_create(int device, uint64_t seed, b2rt_ctx **out) {
     ctx->sm_count = prop.multiProcessorCount;
     if (const char *v = getenv("B2RT_TRACE_VARIANT")) ctx->trace_variant = atoi(v);
     if (const char *v = getenv("B2RT_TRACE_REFILL")) ctx->trace_refill = atoi(v);
+    if (const char *v = getenv("B2RT_TRACE_CHUNK")) ctx->trace_chunk = atoi(v);
     if (const char *v = getenv("B2RT_GATHER_VARIANT")) ctx->gather_variant = atoi(v);
+    if (const char *v = getenv("B2RT_PHOTON_VARIANT")) ctx->photon_variant = atoi(v);
     CK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
     CK(cudaEventCreate(&ctx->ev0)); CK(cudaEventCreate(&ctx->ev1));
     CK(cudaEventCreate(&ctx->evb0)); CK(cudaEventCreate(&ctx->evb1));
@@ -66,8 +68,8 @@ int b2rt_create(int device, uint64_t seed, b2rt_ctx **out) {
     CK(cudaEventCreateWithFlags(&ctx->ev_in, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&ctx->ev_k, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&ctx->ev_out, cudaEventDisableTiming));
-    CK(ctx->d_counters.reserve(64));
-    CK(cudaMemsetAsync(ctx->d_counters.p, 0, 64, ctx->stream));
+    CK(ctx->d_counters.reserve(256));
+    CK(cudaMemsetAsync(ctx->d_counters.p, 0, 256, ctx->stream));
 #undef CK
     *out = ctx;
     return B2RT_OK;

@@ -89,7 +89,11 @@ struct b2rt_ctx {
     int trace_variant = 0;       // 0: one thread per ray, 1: persistent grid + ray pool
     int trace_refill = 0;        // persistent: refill idle lanes when fewer than this many lanes are active
     int pt_blocks_per_sm[2] = {0, 0};
-    int gather_variant = 0;      // 0: per-row scan with direct loads, 1: coarse table + TMA-staged tiles
+    int trace_chunk = 256;       // persistent: consecutive rays a warp takes from the pool per atomicAdd
+    int photon_variant = 1;      // 0: one thread per path, 1: resident grid with path regeneration
+    int photon_blocks_per_sm = 0;
+    int gather_blocks_per_sm[2] = {0, 0};
+    int gather_variant = 1;      // 0: per-row scan with direct loads, 1: coarse table + TMA-staged tiles
 
     // host-side staging of the scene (flattened)
     std::vector<float> h_verts;      // xyz

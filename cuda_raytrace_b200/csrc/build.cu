@@ -400,7 +400,7 @@ int b2rt_build_impl(b2rt_ctx *ctx) {
     B2RT_CUDA(ctx, ctx->d_wide_index.reserve((size_t)nn * 4));
     B2RT_CUDA(ctx, ctx->d_queue_a.reserve((size_t)nn * 4));
     B2RT_CUDA(ctx, ctx->d_queue_b.reserve((size_t)nn * 4));
-    B2RT_CUDA(ctx, ctx->d_counters.reserve(64));
+    B2RT_CUDA(ctx, ctx->d_counters.reserve(256));
     B2RT_CUDA(ctx, ctx->d_prim_recs.reserve((size_t)nn * sizeof(PrimRec)));
     B2RT_CUDA(ctx, ctx->d_leaf_prims.reserve((size_t)nn * 4));
 

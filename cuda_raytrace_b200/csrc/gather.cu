@@ -20,6 +20,9 @@ namespace {
 constexpr int GATHER_WARPS = 4;
 constexpr int GATHER_CAP = 256;          // candidate buffer entries per warp (k <= GATHER_CAP - 32)
 constexpr int GATHER_PER_LANE = GATHER_CAP / 32;
+// candidate slot of element e: XOR swizzle inside aligned groups of 8 so that the sort's lane-strided 64-bit
+// accesses (element lane*PL + j) spread over all banks; consecutive elements still map to distinct slots
+#define CI(e) ((e) ^ (((e) >> 3) & 7))
 
 struct GatherGrid {
     float lo[3]; float cell, inv, slack;
@@ -31,51 +34,68 @@ __device__ __forceinline__ uint64_t shfl_xor_u64(uint64_t v, int m) {
     return ((uint64_t)hi << 32) | lo;
 }
 
-// ascending bitonic sort of GATHER_CAP keys; element e lives in lane e / PER_LANE, register e % PER_LANE
-__device__ __forceinline__ void warp_sort(uint64_t (&v)[GATHER_PER_LANE], int lane) {
+// ascending bitonic sort of 32*PL keys; element e lives in lane e / PL, register e % PL.
+// The stages that stay inside a lane (stride < PL) are unrolled; the cross-lane stages run as ROLLED loops over
+// (size, lane mask) so the whole network is a few hundred instructions and stays resident in the instruction cache
+// (the fully unrolled 256-key network is ~37 KB of straight-line code: ncu showed the kernel stalled on
+// instruction fetch, "no_instruction", for 10 warps per issue).
+__device__ __forceinline__ void key_ce(uint64_t &a, uint64_t &b, bool up) {
+    const bool sw = up ? (b < a) : (a < b);
+    const uint64_t lo = sw ? b : a, hi = sw ? a : b;
+    a = lo; b = hi;
+}
+template <int PL>
+__device__ __forceinline__ void warp_sort(uint64_t (&v)[PL], int lane) {
 #pragma unroll
-    for (int size = 2; size <= GATHER_CAP; size <<= 1) {
+    for (int size = 2; size <= PL; size <<= 1) {
 #pragma unroll
         for (int stride = size >> 1; stride > 0; stride >>= 1) {
-            if (stride >= GATHER_PER_LANE) {
-                const int lm = stride / GATHER_PER_LANE;
 #pragma unroll
-                for (int j = 0; j < GATHER_PER_LANE; ++j) {
-                    const int e = lane * GATHER_PER_LANE + j;
-                    uint64_t o = shfl_xor_u64(v[j], lm);
-                    bool up = (e & size) == 0;            // ascending block
-                    bool lower = (e & stride) == 0;       // I hold the lower index of the pair
-                    bool take_min = (up == lower);
-                    v[j] = take_min ? (o < v[j] ? o : v[j]) : (o > v[j] ? o : v[j]);
-                }
-            } else {
+            for (int j = 0; j < PL; ++j)
+                if ((j & stride) == 0) key_ce(v[j], v[j + stride], ((lane * PL + j) & size) == 0);
+        }
+    }
+#pragma unroll 1
+    for (int size = 2 * PL; size <= 32 * PL; size <<= 1) {
+        const bool up = ((lane * PL) & size) == 0;
+#pragma unroll 1
+        for (int lm = size / (2 * PL); lm > 0; lm >>= 1) {
+            const bool take_min = (up == ((lane & lm) == 0));
 #pragma unroll
-                for (int j = 0; j < GATHER_PER_LANE; ++j) {
-                    if ((j & stride) == 0) {
-                        const int e = lane * GATHER_PER_LANE + j;
-                        bool up = (e & size) == 0;
-                        uint64_t a = v[j], b = v[j + stride];
-                        bool sw = up ? (b < a) : (a < b);
-                        v[j] = sw ? b : a; v[j + stride] = sw ? a : b;
-                    }
-                }
+            for (int j = 0; j < PL; ++j) {
+                const uint64_t o = shfl_xor_u64(v[j], lm);
+                v[j] = take_min ? (o < v[j] ? o : v[j]) : (o > v[j] ? o : v[j]);
             }
+        }
+#pragma unroll
+        for (int stride = PL >> 1; stride > 0; stride >>= 1) {
+#pragma unroll
+            for (int j = 0; j < PL; ++j)
+                if ((j & stride) == 0) key_ce(v[j], v[j + stride], up);
         }
     }
 }
 
-// keep the k smallest of cand[0..count): sorts the buffer, returns min(count, k); buffer is ascending afterwards
-__device__ __noinline__ int warp_select(uint64_t *cand, int count, int k, int lane) {
-    uint64_t v[GATHER_PER_LANE];
+template <int PL>
+__device__ __noinline__ void warp_sort_buffer(uint64_t *cand, int count, int lane) {
+    uint64_t v[PL];
 #pragma unroll
-    for (int j = 0; j < GATHER_PER_LANE; ++j) {
-        int e = lane * GATHER_PER_LANE + j;
-        v[j] = e < count ? cand[e] : 0xffffffffffffffffull;
+    for (int j = 0; j < PL; ++j) {
+        int e = lane * PL + j;
+        v[j] = e < count ? cand[CI(e)] : 0xffffffffffffffffull;
     }
-    warp_sort(v, lane);
+    warp_sort<PL>(v, lane);
 #pragma unroll
-    for (int j = 0; j < GATHER_PER_LANE; ++j) cand[lane * GATHER_PER_LANE + j] = v[j];
+    for (int j = 0; j < PL; ++j) cand[CI(lane * PL + j)] = v[j];
     __syncwarp();
+}
+
+// keep the k smallest of cand[0..count): sorts the buffer (network sized to the next of 64 / 128 / 256 entries),
+// returns min(count, k); cand[0..min(count,k)) is ascending afterwards
+__device__ __forceinline__ int warp_select(uint64_t *cand, int count, int k, int lane) {
+    if (count <= 64) warp_sort_buffer<2>(cand, count, lane);
+    else if (count <= 128) warp_sort_buffer<4>(cand, count, lane);
+    else warp_sort_buffer<GATHER_PER_LANE>(cand, count, lane);
     return count < k ? count : k;
 }
 
@@ -146,12 +166,12 @@ gather_kernel(const b2rt_photon *__restrict__ photons, const uint32_t *__restric
                             if (KNN) {
                                 uint32_t m = __ballot_sync(0xffffffffu, pass);
                                 if (m) {
-                                    if (pass) cand[count + __popc(m & lt)] = key;
+                                    if (pass) cand[CI(count + __popc(m & lt))] = key;
                                     count += __popc(m);
                                     __syncwarp();
                                     if (count > GATHER_CAP - 32) {
                                         count = warp_select(cand, count, k, lane);
-                                        if (count == k) bound = cand[k - 1];       // only keys below the current k-th
+                                        if (count == k) bound = cand[CI(k - 1)];       // only keys below the current k-th
                                     }
                                 }
                             } else if (pass) {
@@ -181,16 +201,16 @@ gather_kernel(const b2rt_photon *__restrict__ photons, const uint32_t *__restric
             float r2 = __uint_as_float((uint32_t)(bound >> 32));
             if (KNN && count > k) {                      // tighten before deciding
                 count = warp_select(cand, count, k, lane);
-                if (count == k) bound = cand[k - 1];
+                if (count == k) bound = cand[CI(k - 1)];
                 r2 = __uint_as_float((uint32_t)(bound >> 32));
             }
             if (dmin > 0.f && dmin * dmin >= r2) break;
         }
         if (KNN) {
             count = warp_select(cand, count, k, lane);
-            const float md2 = (count == k) ? __uint_as_float((uint32_t)(cand[k - 1] >> 32)) : max_dist2;
+            const float md2 = (count == k) ? __uint_as_float((uint32_t)(cand[CI(k - 1)] >> 32)) : max_dist2;
             for (int j = lane; j < count; j += 32) {
-                uint64_t key = cand[j];
+                uint64_t key = cand[CI(j)];
                 uint32_t i = (uint32_t)key;
                 float d2 = __uint_as_float((uint32_t)(key >> 32));
                 const float4 *pp = reinterpret_cast<const float4 *>(photons + i);
@@ -203,7 +223,7 @@ gather_kernel(const b2rt_photon *__restrict__ photons, const uint32_t *__restric
                 }
             }
             if (idx_out)
-                for (int j = lane; j < k; j += 32) idx_out[q * k + j] = j < count ? (int32_t)(uint32_t)cand[j] : -1;
+                for (int j = lane; j < k; j += 32) idx_out[q * k + j] = j < count ? (int32_t)(uint32_t)cand[CI(j)] : -1;
             if (lane == 0) {
                 if (out_r2) out_r2[q] = md2;
                 if (out_found) out_found[q] = count;
@@ -309,18 +329,46 @@ gather_tiled_kernel(const float4 *__restrict__ pos4, const b2rt_photon *__restri
         const float4 q0 = __ldg(qp), q1 = __ldg(qp + 1), q2 = __ldg(qp + 2);
         const float qa[3] = {q0.x, q0.y, q0.z};
         const f3 nf = mk3(q0.w, q1.x, q1.y), kd = mk3(q1.z, q1.w, q2.x);
-        int C[3];
+        int C[3], cf[3];
 #pragma unroll
-        for (int a = 0; a < 3; ++a)
-            C[a] = min(max((int)floorf((qa[a] - g.lo[a]) * g.inv), 0), g.dims[a] - 1) >> G2_SHIFT;
-        uint64_t bound = (uint64_t)__float_as_uint(max_dist2) << 32;
-        int count = 0;
-        f3 acc = mk3(0.f, 0.f, 0.f);
-        int found_fr = 0;
+        for (int a = 0; a < 3; ++a) {
+            cf[a] = min(max((int)floorf((qa[a] - g.lo[a]) * g.inv), 0), g.dims[a] - 1);
+            C[a] = cf[a] >> G2_SHIFT;
+        }
         int smax = 0;
 #pragma unroll
         for (int a = 0; a < 3; ++a) smax = max(smax, max(C[a], g.cdims[a] - 1 - C[a]));
-
+        // First search radius from the local photon density (performance only: the result is defined by the k smallest
+        // keys below max_dist2 and does not depend on it).  N8 = photons in the 2x2x2 coarse cells nearest to the query,
+        // taken as lying on a surface patch of (8 cells)^2; radius expected to hold 1.6 k photons (<= 128 candidates: the small sort network).  If fewer than k are
+        // found the search is repeated with 4x the squared radius.
+        float r2_try = max_dist2;
+        if (KNN) {
+            uint32_t n8 = 0;
+            if (lane < 8) {
+                const int o[3] = {lane & 1, (lane >> 1) & 1, lane >> 2};
+                int P[3];
+                bool in = true;
+#pragma unroll
+                for (int a = 0; a < 3; ++a) {
+                    P[a] = C[a] - ((cf[a] & (G2_C - 1)) < G2_C / 2 ? 1 : 0) + o[a];
+                    in = in && P[a] >= 0 && P[a] < g.cdims[a];
+                }
+                if (in) n8 = __ldg(coarse + ((int64_t)P[2] * g.cdims[1] + P[1]) * g.cdims[0] + P[0]);
+            }
+            n8 = __reduce_add_sync(0xffffffffu, n8);
+            if (n8 > 0) {
+                const float est = (1.6f * 64.f * B2_INV_PI) * (float)k * g.cell * g.cell / (float)n8;
+                r2_try = fminf(est, max_dist2);
+            }
+        }
+        uint64_t bound;
+        int count;
+        f3 acc = mk3(0.f, 0.f, 0.f);
+        int found_fr = 0;
+      for (;;) {
+        bound = (uint64_t)__float_as_uint(r2_try) << 32;
+        count = 0;
         for (int S = 0; S <= smax; ++S) {
             const int w = 2 * S + 1, n_face = w * w;
             const int ntask = S == 0 ? 1 : 2 * n_face + (2 * S - 1) * 8 * S;
@@ -425,12 +473,12 @@ gather_tiled_kernel(const float4 *__restrict__ pos4, const b2rt_photon *__restri
                             if (KNN) {
                                 const uint32_t m = __ballot_sync(0xffffffffu, pass);
                                 if (m) {
-                                    if (pass) cand[count + __popc(m & lt)] = key;
+                                    if (pass) cand[CI(count + __popc(m & lt))] = key;
                                     count += __popc(m);
                                     __syncwarp();
                                     if (count > GATHER_CAP - 32) {
                                         count = warp_select(cand, count, k, lane);
-                                        if (count == k) bound = cand[k - 1];
+                                        if (count == k) bound = cand[CI(k - 1)];
                                     }
                                 }
                             } else if (pass) {
@@ -454,7 +502,7 @@ gather_tiled_kernel(const float4 *__restrict__ pos4, const b2rt_photon *__restri
             // ---- after the shell: tighten, then decide whether anything outside the scanned block can still matter ----
             if (KNN && count > k) {
                 count = warp_select(cand, count, k, lane);
-                if (count == k) bound = cand[k - 1];
+                if (count == k) bound = cand[CI(k - 1)];
             }
             float dmin = INFINITY;
 #pragma unroll
@@ -468,12 +516,15 @@ gather_tiled_kernel(const float4 *__restrict__ pos4, const b2rt_photon *__restri
             const float r2 = __uint_as_float((uint32_t)(bound >> 32));
             if (dmin > 0.f && dmin * dmin >= r2) break;
         }
+        if (!KNN || count >= k || r2_try >= max_dist2) break;
+        r2_try = fminf(r2_try * 4.f, max_dist2);
+      }
 
         if (KNN) {
-            count = warp_select(cand, count, k, lane);
-            const float md2 = (count == k) ? __uint_as_float((uint32_t)(cand[k - 1] >> 32)) : max_dist2;
+            if (count > 0) count = warp_select(cand, count, k, lane);
+            const float md2 = (count == k) ? __uint_as_float((uint32_t)(cand[CI(k - 1)] >> 32)) : max_dist2;
             for (int j = lane; j < count; j += 32) {
-                const uint64_t key = cand[j];
+                const uint64_t key = cand[CI(j)];
                 const uint32_t i = (uint32_t)key;
                 const float d2 = __uint_as_float((uint32_t)(key >> 32));
                 const float4 *pp = reinterpret_cast<const float4 *>(photons + i);
@@ -486,7 +537,7 @@ gather_tiled_kernel(const float4 *__restrict__ pos4, const b2rt_photon *__restri
                 }
             }
             if (idx_out)
-                for (int j = lane; j < k; j += 32) idx_out[q * k + j] = j < count ? (int32_t)(uint32_t)cand[j] : -1;
+                for (int j = lane; j < k; j += 32) idx_out[q * k + j] = j < count ? (int32_t)(uint32_t)cand[CI(j)] : -1;
             if (lane == 0) {
                 if (out_r2) out_r2[q] = md2;
                 if (out_found) out_found[q] = count;
@@ -537,7 +588,13 @@ int b2rt_gather_impl(b2rt_ctx *ctx, int map, int64_t nq, const b2rt_query *d_que
         Gather2Grid g2;
         for (int a = 0; a < 3; ++a) { g2.lo[a] = g.lo[a]; g2.dims[a] = g.dims[a]; g2.cdims[a] = m.cdims[a]; }
         g2.cell = g.cell; g2.inv = g.inv; g2.slack = g.slack;
-        cap = (int64_t)ctx->sm_count * 4;       // 40 KB shared memory per block: 4 blocks per SM, persistent over queries
+        int &per_sm = ctx->gather_blocks_per_sm[k > 0 ? 1 : 0];      // resident grid, persistent over the queries
+        if (per_sm == 0) {
+            if (k > 0) B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, gather_tiled_kernel<true>, GATHER_WARPS * 32, 0));
+            else B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, gather_tiled_kernel<false>, GATHER_WARPS * 32, 0));
+            if (per_sm < 1) per_sm = 1;
+        }
+        cap = (int64_t)ctx->sm_count * per_sm;
         blocks = (nq + GATHER_WARPS - 1) / GATHER_WARPS;
         if (blocks > cap) blocks = cap;
         if (k > 0)

@@ -98,6 +98,99 @@ photon_trace_kernel(DScene sc, uint32_t seed_lo, uint32_t seed_hi, int64_t first
     if (overflow) atomicAdd(status, 1u);
 }
 
+// Path-regeneration variant of K8: a resident grid, every lane always owns a live path.  Each loop iteration is one
+// bounce; lanes whose path ended take the next path index from a global pool (ranks from __ballot_sync + __popc, one
+// atomicAdd per warp) and emit there, so the traversal and shading of an iteration run with (nearly) all 32 lanes
+// instead of the lanes that happen to survive to bounce b.  A path's randomness and its slot row depend only on its
+// index, so the output is byte-identical to photon_trace_kernel.
+__global__ void __launch_bounds__(PHOTON_THREADS)
+photon_trace_regen_kernel(DScene sc, uint32_t seed_lo, uint32_t seed_hi, int64_t first_path, int64_t n_paths,
+                          int max_depth, int flags, b2rt_photon *__restrict__ slots, uint32_t *__restrict__ cnt_c,
+                          uint32_t *__restrict__ cnt_i, unsigned long long *pool, uint32_t *status) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t lt = (1u << lane) - 1u;
+    const bool want_c = flags & 1, want_i = flags & 2;
+    bool alive = false, exhausted = false, overflow = false;
+    int64_t li = 0;
+    uint32_t p_lo = 0, p_hi = 0, nc = 0, ni = 0;
+    f3 o = mk3(0.f, 0.f, 0.f), d = mk3(0.f, 0.f, 1.f), alpha = mk3(0.f, 0.f, 0.f);
+    float tmin = 0.f;
+    bool specular_path = true;
+    int n_isect = 0;
+    for (;;) {
+        const uint32_t idle = __ballot_sync(0xffffffffu, !alive);
+        if (idle && !exhausted) {
+            const int want = __popc(idle);
+            unsigned long long base = 0;
+            if (lane == 0) base = atomicAdd(pool, (unsigned long long)want);
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (!alive) {
+                const int64_t i = (int64_t)base + __popc(idle & lt);
+                if (i < n_paths) {
+                    li = i;
+                    const uint64_t path = (uint64_t)(first_path + li);
+                    p_lo = (uint32_t)path; p_hi = (uint32_t)(path >> 32);
+                    nc = 0; ni = 0; specular_path = true; n_isect = 0;
+                    u4 r0 = philox4x32_10(p_lo, p_hi, 0u, 0u, seed_lo, seed_hi);
+                    u4 r1 = philox4x32_10(p_lo, p_hi, 0u, 1u, seed_lo, seed_hi);
+                    alive = emit_photon(sc, u01(r0.x), u01(r0.y), u01(r0.z), u01(r1.x), u01(r1.y), o, d, tmin, alpha);
+                    if (!alive) { cnt_c[li] = 0; cnt_i[li] = 0; }
+                }
+            }
+            if ((int64_t)base + want >= n_paths) exhausted = true;
+        }
+        if (!__any_sync(0xffffffffu, alive)) {
+            if (exhausted) break;
+            continue;
+        }
+        if (alive) {
+            // one bounce
+            bool cont_path = false;
+            HitD h;
+            if (traverse<false>(sc.nodes, sc.recs, sc.analytic, o.x, o.y, o.z, d.x, d.y, d.z, tmin, INFINITY, h, overflow)) {
+                ++n_isect;
+                Surface s = make_surface(sc, h, o, d);
+                Mat m = load_material(sc, s.material);
+                f3 wo = -d;
+                if (m.type == B2RT_MAT_MATTE) {
+                    bool caustic = specular_path && n_isect > 1;
+                    bool dep = caustic ? want_c : (n_isect > 1 && want_i);
+                    if (dep) {
+                        float4 *dst = reinterpret_cast<float4 *>(slots + li * max_depth + nc + ni);
+                        dst[0] = make_float4(s.p.x, s.p.y, s.p.z, __uint_as_float(oct_encode(wo)));
+                        dst[1] = make_float4(alpha.x, alpha.y, alpha.z, __uint_as_float(p_lo));
+                        if (caustic) ++nc; else ++ni;
+                    }
+                }
+                if (n_isect < max_depth) {
+                    u4 rb = philox4x32_10(p_lo, p_hi, (uint32_t)n_isect, 0u, seed_lo, seed_hi);
+                    BsdfSample bs;
+                    if (sample_bsdf(s, m, wo, u01(rb.x), u01(rb.y), u01(rb.z), bs) && !is_black(bs.f) && bs.pdf != 0.f) {
+                        f3 anew = mk3(alpha.x * bs.f.x * bs.absdot / bs.pdf, alpha.y * bs.f.y * bs.absdot / bs.pdf,
+                                      alpha.z * bs.f.z * bs.absdot / bs.pdf);
+                        float cont = fminf(1.f, lum(anew) / lum(alpha));
+                        if (!(u01(rb.w) > cont)) {
+                            alpha = mk3(anew.x / cont, anew.y / cont, anew.z / cont);
+                            specular_path = specular_path && bs.specular;
+                            if (want_i || specular_path) {
+                                o = s.p; d = bs.wi; tmin = s.ray_eps;
+                                cont_path = true;
+                            }
+                        }
+                    }
+                }
+            }
+            if (!cont_path) {
+                cnt_c[li] = nc; cnt_i[li] = ni;
+                alive = false;
+            }
+        }
+    }
+    if (overflow) atomicAdd(status, 1u);
+}
+
+__global__ void photon_pool_reset_kernel(unsigned long long *pool) { *pool = 0ull; }
+
 // place the deposits in path order: out_c[off_c[path] + 0..nc), out_i[off_i[path] + 0..ni)
 __global__ void __launch_bounds__(256)
 photon_compact_kernel(const b2rt_photon *__restrict__ slots, const uint32_t *__restrict__ off_c,
@@ -215,9 +308,25 @@ int b2rt_photons_trace_impl(b2rt_ctx *ctx, int64_t first_path, int64_t n_paths, 
     uint32_t *cnt_c = ctx->d_cnt_c.as<uint32_t>(), *cnt_i = ctx->d_cnt_i.as<uint32_t>();
     uint32_t *counters = ctx->d_counters.as<uint32_t>();
     unsigned grid = (unsigned)((n_paths + PHOTON_THREADS - 1) / PHOTON_THREADS);
-    photon_trace_kernel<<<grid, PHOTON_THREADS, 0, st>>>(sc, (uint32_t)ctx->seed, (uint32_t)(ctx->seed >> 32), first_path,
-                                                         n_paths, max_depth, flags, ctx->d_slots.as<b2rt_photon>(),
-                                                         cnt_c, cnt_i, counters + 8);
+    if (ctx->photon_variant == 1) {
+        if (ctx->photon_blocks_per_sm == 0) {
+            B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx->photon_blocks_per_sm, photon_trace_regen_kernel,
+                                                                         PHOTON_THREADS, 0));
+            if (ctx->photon_blocks_per_sm < 1) ctx->photon_blocks_per_sm = 1;
+        }
+        unsigned long long *pool = reinterpret_cast<unsigned long long *>(counters + 18);
+        photon_pool_reset_kernel<<<1, 1, 0, st>>>(pool);
+        B2RT_LAUNCH_CHECK(ctx);
+        unsigned pgrid = (unsigned)std::min<int64_t>(grid, (int64_t)ctx->sm_count * ctx->photon_blocks_per_sm);
+        photon_trace_regen_kernel<<<pgrid, PHOTON_THREADS, 0, st>>>(sc, (uint32_t)ctx->seed, (uint32_t)(ctx->seed >> 32),
+                                                                   first_path, n_paths, max_depth, flags,
+                                                                   ctx->d_slots.as<b2rt_photon>(), cnt_c, cnt_i, pool,
+                                                                   counters + 8);
+    } else {
+        photon_trace_kernel<<<grid, PHOTON_THREADS, 0, st>>>(sc, (uint32_t)ctx->seed, (uint32_t)(ctx->seed >> 32), first_path,
+                                                             n_paths, max_depth, flags, ctx->d_slots.as<b2rt_photon>(),
+                                                             cnt_c, cnt_i, counters + 8);
+    }
     B2RT_LAUNCH_CHECK(ctx);
     int rc = b2rt_exclusive_scan_u32(ctx, cnt_c, n_paths, counters + 10);
     if (rc) return rc;

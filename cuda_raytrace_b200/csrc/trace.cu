@@ -60,7 +60,7 @@ __global__ void __launch_bounds__(PT_THREADS)
 trace_persistent_kernel(const WideNode *__restrict__ nodes, const PrimRec *__restrict__ recs,
                         const AnalyticPrim *__restrict__ analytic, const b2rt_ray *__restrict__ rays,
                         b2rt_hit *__restrict__ hits, uint8_t *__restrict__ occ, int64_t nrays,
-                        unsigned long long *pool, int refill, uint32_t *status) {
+                        unsigned long long *pool, int refill, int chunk, uint32_t *status) {
     __shared__ int32_t s_stack[PT_SSTACK][PT_THREADS];
     int32_t l_stack[B2RT_STACK_SIZE - PT_SSTACK];
     const int tid = threadIdx.x, lane = tid & 31;
@@ -73,33 +73,40 @@ trace_persistent_kernel(const WideNode *__restrict__ nodes, const PrimRec *__res
     bool found = false, active = false, exhausted = false;
     int sp = 0;
     int32_t cur = 0;
-    int64_t my = 0;
+    int64_t my = 0, w_next = 0, w_end = 0;      // warp-uniform: the warp's current chunk of the ray pool
 
 #define PT_PUSH(v) do { if (sp < PT_SSTACK) s_stack[sp][tid] = (v); else l_stack[sp - PT_SSTACK] = (v); ++sp; } while (0)
 #define PT_POP() (--sp, (sp < PT_SSTACK) ? s_stack[sp][tid] : l_stack[sp - PT_SSTACK])
 
     for (;;) {
-        // ---- refill idle lanes from the pool ----------------------------------------------------------------
-        const uint32_t idle = __ballot_sync(0xffffffffu, !active);
-        if (idle && !exhausted) {
-            const int want = __popc(idle);
-            unsigned long long base = 0;
-            if (lane == 0) base = atomicAdd(pool, (unsigned long long)want);
-            base = __shfl_sync(0xffffffffu, base, 0);
-            if (!active) {
-                const int64_t i = (int64_t)base + __popc(idle & lt);
-                if (i < nrays) {
-                    const float4 *rp = reinterpret_cast<const float4 *>(rays + i);
-                    const float4 r0 = __ldg(rp), r1 = __ldg(rp + 1);
-                    r.ox = r0.x; r.oy = r0.y; r.oz = r0.z; r.tmin = r0.w;
-                    r.dx = r1.x; r.dy = r1.y; r.dz = r1.z;
-                    r.ddx = r1.x; r.ddy = r1.y; r.ddz = r1.z;
-                    idx = 1.f / r1.x; idy = 1.f / r1.y; idz = 1.f / r1.z;
-                    best_t = r1.w; best_prim = 0x7fffffff; best_b1 = 0.f; best_b2 = 0.f;
-                    found = false; sp = 0; cur = 0; my = i; active = true;
-                }
+        // ---- refill idle lanes: the warp owns a chunk [w_next, w_end) of consecutive rays (one atomicAdd on the
+        // global pool per chunk), idle lanes take the next rays of the chunk in lane order ---------------------------
+        uint32_t idle = __ballot_sync(0xffffffffu, !active);
+        while (idle && !exhausted) {
+            if (w_next >= w_end) {
+                unsigned long long base = 0;
+                if (lane == 0) base = atomicAdd(pool, (unsigned long long)chunk);
+                base = __shfl_sync(0xffffffffu, base, 0);
+                if ((int64_t)base >= nrays) { exhausted = true; break; }
+                w_next = (int64_t)base;
+                w_end = (int64_t)base + chunk < nrays ? (int64_t)base + chunk : nrays;
             }
-            if ((int64_t)base + want >= nrays) exhausted = true;
+            const int rank = __popc(idle & lt);
+            const int64_t i = w_next + rank;
+            if (!active && i < w_end) {
+                const float4 *rp = reinterpret_cast<const float4 *>(rays + i);
+                const float4 r0 = __ldg(rp), r1 = __ldg(rp + 1);
+                r.ox = r0.x; r.oy = r0.y; r.oz = r0.z; r.tmin = r0.w;
+                r.dx = r1.x; r.dy = r1.y; r.dz = r1.z;
+                r.ddx = r1.x; r.ddy = r1.y; r.ddz = r1.z;
+                idx = 1.f / r1.x; idy = 1.f / r1.y; idz = 1.f / r1.z;
+                best_t = r1.w; best_prim = 0x7fffffff; best_b1 = 0.f; best_b2 = 0.f;
+                found = false; sp = 0; cur = 0; my = i; active = true;
+            }
+            const int64_t avail = w_end - w_next;
+            const int want = __popc(idle);
+            w_next += want < avail ? want : avail;
+            idle = __ballot_sync(0xffffffffu, !active);
         }
         if (!__any_sync(0xffffffffu, active)) break;
 
@@ -210,15 +217,16 @@ int b2rt_trace_impl(b2rt_ctx *ctx, int64_t n, const b2rt_ray *d_rays, b2rt_hit *
         int64_t blocks = (int64_t)ctx->sm_count * per_sm;
         int64_t need = (n + PT_THREADS - 1) / PT_THREADS;
         if (blocks > need) blocks = need;
-        unsigned long long *pool = reinterpret_cast<unsigned long long *>(ctx->d_counters.as<uint32_t>() + 12);
+        unsigned long long *pool = reinterpret_cast<unsigned long long *>(ctx->d_counters.as<uint32_t>() + 16);
+        const int chunk = ctx->trace_chunk >= 32 ? (ctx->trace_chunk & ~31) : 32;
         pool_reset_kernel<<<1, 1, 0, ctx->stream>>>(pool);
         B2RT_LAUNCH_CHECK(ctx);
         if (any_hit)
             trace_persistent_kernel<true><<<(unsigned)blocks, PT_THREADS, 0, ctx->stream>>>(
-                nodes, recs, an, d_rays, nullptr, d_occ, n, pool, ctx->trace_refill, status);
+                nodes, recs, an, d_rays, nullptr, d_occ, n, pool, ctx->trace_refill, chunk, status);
         else
             trace_persistent_kernel<false><<<(unsigned)blocks, PT_THREADS, 0, ctx->stream>>>(
-                nodes, recs, an, d_rays, d_hits, nullptr, n, pool, ctx->trace_refill, status);
+                nodes, recs, an, d_rays, d_hits, nullptr, n, pool, ctx->trace_refill, chunk, status);
         B2RT_LAUNCH_CHECK(ctx);
         return B2RT_OK;
     }
