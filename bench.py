@@ -9,7 +9,7 @@ hit (the reference's SimpleRenderer frame, cuda_render/simple_render/simplerende
   value      Mrays/s = (primary + shadow rays of all ranks) / max-over-ranks device time, rays resident in HBM
   e2e        same metric through the C ABI with HOST (pinned) buffers: b2rt_trace_closest/any(..., B2RT_HOST)
              copy the rays in and the hits / occlusion flags out inside the timed region
-  roofline   dominant kernel = trace_kernel<closest>; algorithmic bytes = 48 B/ray (32 in + 16 out)
+  roofline   dominant kernel = trace_spec_kernel<closest> (persistent ray-pool traversal); algorithmic bytes = 48 B/ray (32 in + 16 out)
   cpu_baseline  the reference's own CPU path (pbrt-v2 BVHAccel::Intersect/IntersectP from oracle/_ref, built from
              /root/reference in the build container) on the same rays, all host threads; falls back to nothing
              else -- if oracle/_ref is absent the C port's exhaustive loop is timed on a small sample ("port")
@@ -33,6 +33,8 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
+_TV = os.environ.get("B2RT_TRACE_VARIANT", "2")
+TRACE_KERNEL = {"0": "trace_kernel<closest>", "1": "trace_persistent_kernel<closest>"}.get(_TV, "trace_spec_kernel<closest>")
 METRIC = "Mrays/s (closest-hit primary + any-hit shadow rays, 1M-triangle scene, 1920x1080, 1 spp)"
 LIGHT = (0.5, 3.0, 0.5)
 
@@ -398,13 +400,13 @@ def main():
             "any_hit_mrays": N2 * args.steps / (ms_any_m * 1e-3) / 1e6,
             "incoherent_closest_hit_mrays": inc_mrays,
             "rays_per_step": {"closest": int(N1), "any": int(N2)},
-            "accel": {"n_prims": info.n_prims, "wide_nodes": info.n_wide_nodes, "build_ms": info.build_ms,
+            "accel": {"n_prims": info.n_prims, "wide_nodes": info.n_wide_nodes, "build_ms": info.build_ms, "upload_ms": info.upload_ms,
                       "sah_cost": info.sah_cost},
             "e2e": {"value": (N1 + N2) * e2e_steps / (e2e_ms_m * 1e-3) / 1e6, "unit": "Mrays/s",
                     "h2d_bytes_per_step": int(32 * (n1 + n2)), "d2h_bytes_per_step": int(16 * n1 + n2),
                     "ms_per_step": e2e_ms_m / e2e_steps, "api": "b2rt_trace_closest/b2rt_trace_any(B2RT_HOST)"},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "kernel": "trace_kernel<closest>", "achieved": achieved, "peak": peak,
+            "roofline": {"bound": "hbm", "kernel": TRACE_KERNEL, "achieved": achieved, "peak": peak,
                          "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": 48 * n1,
                          "note": "traversal is latency/issue bound, not HBM bound (SURVEY 8(d)); see profiles/"},

@@ -22,7 +22,7 @@ HIT_DTYPE = np.dtype([("t", np.float32), ("prim", np.int32), ("b1", np.float32),
 class AccelInfo(C.Structure):
     _fields_ = [("n_prims", C.c_int32), ("n_tris", C.c_int32), ("n_wide_nodes", C.c_int32),
                 ("n_leaf_slots", C.c_int32), ("max_depth", C.c_int32), ("wide_width", C.c_int32),
-                ("bounds", C.c_float * 6), ("sah_cost", C.c_float), ("build_ms", C.c_float)]
+                ("bounds", C.c_float * 6), ("sah_cost", C.c_float), ("build_ms", C.c_float), ("upload_ms", C.c_float)]
 
 
 class B2rtError(RuntimeError):

@@ -62,7 +62,7 @@ int b2rt_create(int device, uint64_t seed, b2rt_ctx **out) {
     if (const char *v = getenv("B2RT_PHOTON_VARIANT")) ctx->photon_variant = atoi(v);
     CK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
     CK(cudaEventCreate(&ctx->ev0)); CK(cudaEventCreate(&ctx->ev1));
-    CK(cudaEventCreate(&ctx->evb0)); CK(cudaEventCreate(&ctx->evb1));
+    CK(cudaEventCreate(&ctx->evb0)); CK(cudaEventCreate(&ctx->evb1)); CK(cudaEventCreate(&ctx->evb_mid));
     CK(cudaStreamCreateWithFlags(&ctx->stream_in, cudaStreamNonBlocking));
     CK(cudaStreamCreateWithFlags(&ctx->stream_out, cudaStreamNonBlocking));
     CK(cudaEventCreateWithFlags(&ctx->ev_in, cudaEventDisableTiming));
@@ -94,7 +94,7 @@ void b2rt_destroy(b2rt_ctx *ctx) {
     }
     for (DevBuf *b : bufs) b->release();
     cudaEventDestroy(ctx->ev0); cudaEventDestroy(ctx->ev1);
-    cudaEventDestroy(ctx->evb0); cudaEventDestroy(ctx->evb1);
+    cudaEventDestroy(ctx->evb0); cudaEventDestroy(ctx->evb1); cudaEventDestroy(ctx->evb_mid);
     cudaEventDestroy(ctx->ev_in); cudaEventDestroy(ctx->ev_k); cudaEventDestroy(ctx->ev_out);
     cudaStreamDestroy(ctx->stream_in); cudaStreamDestroy(ctx->stream_out);
     cudaStreamDestroy(ctx->stream);

@@ -78,7 +78,7 @@ struct b2rt_ctx {
     int sm_count = B2RT_SM_COUNT_DEFAULT;
     uint64_t seed = 0;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr, evb0 = nullptr, evb1 = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, evb0 = nullptr, evb1 = nullptr, evb_mid = nullptr;
     // host-buffer calls: upload / download streams and the events that chain the chunks
     cudaStream_t stream_in = nullptr, stream_out = nullptr;
     cudaEvent_t ev_in = nullptr, ev_k = nullptr, ev_out = nullptr;
@@ -86,10 +86,10 @@ struct b2rt_ctx {
     int64_t launches = 0;
     // kernel variants (environment overrides for A/B measurements: B2RT_TRACE_VARIANT, B2RT_TRACE_REFILL,
     // B2RT_GATHER_VARIANT); results are identical for every setting
-    int trace_variant = 0;       // 0: one thread per ray, 1: persistent grid + ray pool
+    int trace_variant = 2;       // 0: one thread per ray, 1: persistent grid + ray pool, 2: + postponed leaves
     int trace_refill = 0;        // persistent: refill idle lanes when fewer than this many lanes are active
-    int pt_blocks_per_sm[2] = {0, 0};
-    int trace_chunk = 256;       // persistent: consecutive rays a warp takes from the pool per atomicAdd
+    int pt_blocks_per_sm[4] = {0, 0, 0, 0};
+    int trace_chunk = 32;        // persistent: consecutive rays a warp takes from the pool per atomicAdd
     int photon_variant = 1;      // 0: one thread per path, 1: resident grid with path regeneration
     int photon_blocks_per_sm = 0;
     int gather_blocks_per_sm[2] = {0, 0};

@@ -404,6 +404,7 @@ int b2rt_build_impl(b2rt_ctx *ctx) {
     B2RT_CUDA(ctx, ctx->d_prim_recs.reserve((size_t)nn * sizeof(PrimRec)));
     B2RT_CUDA(ctx, ctx->d_leaf_prims.reserve((size_t)nn * 4));
 
+    B2RT_CUDA(ctx, cudaEventRecord(ctx->evb_mid, st));      // scene resident, buffers reserved: the build proper starts here
     b2rt_accel_info &info = ctx->info;
     info = b2rt_accel_info{};
     info.n_prims = n; info.n_tris = (int)ctx->h_tri_prim.size(); info.wide_width = 4; info.n_leaf_slots = n;
@@ -523,7 +524,8 @@ int b2rt_build_impl(b2rt_ctx *ctx) {
     info.max_depth = depth;
     B2RT_CUDA(ctx, cudaEventRecord(ctx->evb1, st));
     B2RT_CUDA(ctx, cudaEventSynchronize(ctx->evb1));
-    B2RT_CUDA(ctx, cudaEventElapsedTime(&info.build_ms, ctx->evb0, ctx->evb1));
+    B2RT_CUDA(ctx, cudaEventElapsedTime(&info.upload_ms, ctx->evb0, ctx->evb_mid));
+    B2RT_CUDA(ctx, cudaEventElapsedTime(&info.build_ms, ctx->evb_mid, ctx->evb1));
     ctx->built = true;
     return B2RT_OK;
 }

@@ -39,8 +39,11 @@ __device__ __forceinline__ uint64_t shfl_xor_u64(uint64_t v, int m) {
 // (size, lane mask) so the whole network is a few hundred instructions and stays resident in the instruction cache
 // (the fully unrolled 256-key network is ~37 KB of straight-line code: ncu showed the kernel stalled on
 // instruction fetch, "no_instruction", for 10 warps per issue).
+// `up` differs between lanes: the swap decision is formed with logic ops so it compiles to predicates + selects, not to
+// a divergent branch (ncu: the branchy form ran with 13 of 32 threads per instruction)
 __device__ __forceinline__ void key_ce(uint64_t &a, uint64_t &b, bool up) {
-    const bool sw = up ? (b < a) : (a < b);
+    const uint32_t lt = b < a, gt = a < b, u = up;
+    const bool sw = ((lt & u) | (gt & (u ^ 1u))) != 0u;
     const uint64_t lo = sw ? b : a, hi = sw ? a : b;
     a = lo; b = hi;
 }
@@ -500,7 +503,10 @@ gather_tiled_kernel(const float4 *__restrict__ pos4, const b2rt_photon *__restri
                 }
             }
             // ---- after the shell: tighten, then decide whether anything outside the scanned block can still matter ----
-            if (KNN && count > k) {
+            // The first radius already comes from the local density, so the bound is only re-tightened between shells
+            // when the buffer is more than half full (keeps later sorts on the small networks); otherwise the single
+            // sort at the end is the only one a query pays for.
+            if (KNN && count > k && count > GATHER_CAP / 2) {
                 count = warp_select(cand, count, k, lane);
                 if (count == k) bound = cand[CI(k - 1)];
             }

@@ -16,6 +16,7 @@ constexpr int SORT_WARPS = SORT_THREADS / 32;
 constexpr int SORT_ITEMS = 16;                       // keys per thread
 constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS; // 4096 keys per block
 constexpr int RADIX = 256;
+static_assert(SORT_THREADS == RADIX, "the scatter kernel maps one thread to one digit");
 
 // ---- per-block digit histogram --------------------------------------------------------------
 __global__ void __launch_bounds__(SORT_THREADS)
@@ -41,24 +42,33 @@ radix_hist_kernel(const uint32_t *__restrict__ keys, int64_t n, int shift, uint3
 }
 
 // ---- stable scatter ---------------------------------------------------------------------------
+// Ranks are computed as before (warp w owns a contiguous sub-tile; lanes rank by __match_any_sync + popc of lower
+// lanes), but the tile is first permuted into digit order in shared memory and then written out by consecutive
+// threads: all elements of one digit of one block are contiguous in the output, so the global stores are coalesced
+// runs instead of 4-byte scatters (ncu r01b: the direct scatter reached ~0.8 TB/s of the 6.5 TB/s copy peak).
 __global__ void __launch_bounds__(SORT_THREADS)
 radix_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__restrict__ vals_in,
                      uint32_t *__restrict__ keys_out, uint32_t *__restrict__ vals_out, int64_t n, int shift,
                      const uint32_t *__restrict__ scanned_hist, int nblocks) {
-    __shared__ uint32_t sh[SORT_WARPS][RADIX];  // first: running warp histogram; then: final bases
+    __shared__ uint32_t sh[SORT_WARPS][RADIX];  // first: running warp histogram; then: exclusive count of earlier warps
+    __shared__ uint32_t s_off[RADIX];           // first tile slot of digit d
+    __shared__ uint32_t s_gadj[RADIX];          // global position of digit d's first element minus s_off[d]
+    __shared__ uint32_t s_wsum[SORT_WARPS];
+    __shared__ uint32_t s_key[SORT_TILE], s_val[SORT_TILE];
     for (int i = threadIdx.x; i < SORT_WARPS * RADIX; i += SORT_THREADS) (&sh[0][0])[i] = 0;
     __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t lt = (1u << lane) - 1u;
-    int64_t base = (int64_t)blockIdx.x * SORT_TILE + warp * (32 * SORT_ITEMS);
+    const int64_t tile0 = (int64_t)blockIdx.x * SORT_TILE;
+    const int64_t base = tile0 + warp * (32 * SORT_ITEMS);
+    const int tile_n = (int)(n - tile0 < SORT_TILE ? n - tile0 : SORT_TILE);
 
-    uint32_t k[SORT_ITEMS], v[SORT_ITEMS], rank[SORT_ITEMS];
+    uint32_t k[SORT_ITEMS], rank[SORT_ITEMS];
 #pragma unroll
     for (int r = 0; r < SORT_ITEMS; ++r) {
         int64_t i = base + r * 32 + lane;
         bool ok = i < n;
         k[r] = ok ? keys_in[i] : 0u;
-        v[r] = ok ? vals_in[i] : 0u;
         uint32_t d = ok ? ((k[r] >> shift) & 0xff) : 0x100u;
         uint32_t peers = __match_any_sync(0xffffffffu, d);
         int leader = __ffs(peers) - 1;
@@ -72,15 +82,31 @@ radix_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__res
         __syncwarp();
     }
     __syncthreads();
-    // turn per-warp counts into absolute output bases: global + warps before me
-    for (int d = threadIdx.x; d < RADIX; d += SORT_THREADS) {
-        uint32_t run = scanned_hist[(int64_t)d * nblocks + blockIdx.x];
+    // thread d: per-warp counts of digit d -> exclusive over warps; block total -> exclusive scan over the digits
+    {
+        const int d = threadIdx.x;          // SORT_THREADS == RADIX
+        uint32_t run = 0;
 #pragma unroll
         for (int w = 0; w < SORT_WARPS; ++w) {
             uint32_t c = sh[w][d];
             sh[w][d] = run;
             run += c;
         }
+        uint32_t inc = run;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) s_wsum[warp] = inc;
+        __syncthreads();
+        uint32_t wbase = 0;
+#pragma unroll
+        for (int w = 0; w < SORT_WARPS; ++w)
+            if (w < warp) wbase += s_wsum[w];
+        const uint32_t off = wbase + inc - run;
+        s_off[d] = off;
+        s_gadj[d] = scanned_hist[(int64_t)d * nblocks + blockIdx.x] - off;
     }
     __syncthreads();
 #pragma unroll
@@ -88,10 +114,17 @@ radix_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__res
         int64_t i = base + r * 32 + lane;
         if (i < n) {
             uint32_t d = (k[r] >> shift) & 0xff;
-            uint32_t pos = sh[warp][d] + rank[r];
-            keys_out[pos] = k[r];
-            vals_out[pos] = v[r];
+            uint32_t lp = s_off[d] + sh[warp][d] + rank[r];
+            s_key[lp] = k[r];
+            s_val[lp] = vals_in[i];
         }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < tile_n; i += SORT_THREADS) {
+        uint32_t key = s_key[i];
+        uint32_t pos = s_gadj[(key >> shift) & 0xff] + (uint32_t)i;
+        keys_out[pos] = key;
+        vals_out[pos] = s_val[i];
     }
 }
 

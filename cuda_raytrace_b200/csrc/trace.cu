@@ -196,6 +196,181 @@ trace_persistent_kernel(const WideNode *__restrict__ nodes, const PrimRec *__res
 #undef PT_POP
 }
 
+// ---- speculative variant (B2RT_TRACE_VARIANT=2) ------------------------------------------------------------------------
+// Same pool / shared-memory stack as above, plus:
+//   * postponed leaves (Aila & Laine's speculative while-while): a lane that reaches a leaf parks it and keeps
+//     descending; the warp leaves the node loop only when every lane has a parked leaf or nothing left to visit,
+//     so both the node loop and the primitive loop run with more lanes;
+//   * a branch-free triangle test (same operations and roundings as tri_test, one predicate at the end).
+// Box tests only prune; accepted primitives and their (t, b1, b2) are computed by the same expressions, so the
+// results are bit-identical to the other variants.
+__device__ __forceinline__ bool tri_test_nobranch(const RayD &r, const float4 &A, const float4 &B, const float4 &C,
+                                                  float tmax, float &t_out, float &b1_out, float &b2_out) {
+    const double e1x = B.x, e1y = B.y, e1z = B.z, e2x = C.x, e2y = C.y, e2z = C.z;
+    const float s1x = cross_comp(r.ddy, e2z, r.ddz, e2y);
+    const float s1y = cross_comp(r.ddz, e2x, r.ddx, e2z);
+    const float s1z = cross_comp(r.ddx, e2y, r.ddy, e2x);
+    const float divisor = s1x * B.x + s1y * B.y + s1z * B.z;
+    const float inv = 1.f / divisor;
+    const float dvx = r.ox - A.x, dvy = r.oy - A.y, dvz = r.oz - A.z;
+    const float b1 = (dvx * s1x + dvy * s1y + dvz * s1z) * inv;
+    const double ddvx = dvx, ddvy = dvy, ddvz = dvz;
+    const float s2x = cross_comp(ddvy, e1z, ddvz, e1y);
+    const float s2y = cross_comp(ddvz, e1x, ddvx, e1z);
+    const float s2z = cross_comp(ddvx, e1y, ddvy, e1x);
+    const float b2 = (r.dx * s2x + r.dy * s2y + r.dz * s2z) * inv;
+    const float t = (C.x * s2x + C.y * s2y + C.z * s2z) * inv;
+    // every comparison is false on NaN, so a zero divisor (inv = inf, products NaN or inf) is rejected as in tri_test
+    const bool ok = (divisor != 0.f) & (b1 >= 0.f) & (b1 <= 1.f) & (b2 >= 0.f) & (b1 + b2 <= 1.f) & (t >= r.tmin) & (t <= tmax);
+    t_out = t; b1_out = b1; b2_out = b2;
+    return ok;
+}
+
+template <bool ANY>
+__global__ void __launch_bounds__(PT_THREADS)
+trace_spec_kernel(const WideNode *__restrict__ nodes, const PrimRec *__restrict__ recs,
+                  const AnalyticPrim *__restrict__ analytic, const b2rt_ray *__restrict__ rays,
+                  b2rt_hit *__restrict__ hits, uint8_t *__restrict__ occ, int64_t nrays,
+                  unsigned long long *pool, int refill, int chunk, uint32_t *status) {
+    __shared__ int32_t s_stack[PT_SSTACK][PT_THREADS];
+    int32_t l_stack[B2RT_STACK_SIZE - PT_SSTACK];
+    const int tid = threadIdx.x, lane = tid & 31;
+    const uint32_t lt = (1u << lane) - 1u;
+    constexpr int32_t NONE = B2RT_CHILD_EMPTY;       // "nothing": never a valid node index or leaf reference
+
+    RayD r;
+    float idx = 0.f, idy = 0.f, idz = 0.f;
+    float best_t = 0.f, best_b1 = 0.f, best_b2 = 0.f;
+    int best_prim = 0x7fffffff;
+    bool found = false, active = false, exhausted = false;
+    int sp = 0;
+    int32_t cur = NONE, leaf = NONE;
+    int64_t my = 0, w_next = 0, w_end = 0;
+
+#define PT_PUSH(v) do { if (sp < PT_SSTACK) s_stack[sp][tid] = (v); else l_stack[sp - PT_SSTACK] = (v); ++sp; } while (0)
+#define PT_POP() (--sp, (sp < PT_SSTACK) ? s_stack[sp][tid] : l_stack[sp - PT_SSTACK])
+
+    for (;;) {
+        uint32_t idle = __ballot_sync(0xffffffffu, !active);
+        while (idle && !exhausted) {
+            if (w_next >= w_end) {
+                unsigned long long base = 0;
+                if (lane == 0) base = atomicAdd(pool, (unsigned long long)chunk);
+                base = __shfl_sync(0xffffffffu, base, 0);
+                if ((int64_t)base >= nrays) { exhausted = true; break; }
+                w_next = (int64_t)base;
+                w_end = (int64_t)base + chunk < nrays ? (int64_t)base + chunk : nrays;
+            }
+            const int64_t i = w_next + __popc(idle & lt);
+            if (!active && i < w_end) {
+                const float4 *rp = reinterpret_cast<const float4 *>(rays + i);
+                const float4 r0 = __ldg(rp), r1 = __ldg(rp + 1);
+                r.ox = r0.x; r.oy = r0.y; r.oz = r0.z; r.tmin = r0.w;
+                r.dx = r1.x; r.dy = r1.y; r.dz = r1.z;
+                r.ddx = r1.x; r.ddy = r1.y; r.ddz = r1.z;
+                idx = 1.f / r1.x; idy = 1.f / r1.y; idz = 1.f / r1.z;
+                best_t = r1.w; best_prim = 0x7fffffff; best_b1 = 0.f; best_b2 = 0.f;
+                found = false; sp = 0; cur = 0; leaf = NONE; my = i; active = true;
+            }
+            const int64_t avail = w_end - w_next;
+            const int want = __popc(idle);
+            w_next += want < avail ? want : avail;
+            idle = __ballot_sync(0xffffffffu, !active);
+        }
+        if (!__any_sync(0xffffffffu, active)) break;
+
+        while (active) {
+            // ---- node loop: descend; park the first leaf met and keep going until the whole warp has one ---------
+            while (cur >= 0 && cur != NONE) {
+                const float4 *np = reinterpret_cast<const float4 *>(nodes + cur);
+                const float4 lox = __ldg(np), hix = __ldg(np + 1), loy = __ldg(np + 2), hiy = __ldg(np + 3),
+                             loz = __ldg(np + 4), hiz = __ldg(np + 5);
+                const int4 ch = __ldg(reinterpret_cast<const int4 *>(np + 6));
+                float tn[4]; int32_t cr[4];
+                const float lx[4] = {lox.x, lox.y, lox.z, lox.w}, hx[4] = {hix.x, hix.y, hix.z, hix.w};
+                const float ly[4] = {loy.x, loy.y, loy.z, loy.w}, hy[4] = {hiy.x, hiy.y, hiy.z, hiy.w};
+                const float lz[4] = {loz.x, loz.y, loz.z, loz.w}, hz[4] = {hiz.x, hiz.y, hiz.z, hiz.w};
+                cr[0] = ch.x; cr[1] = ch.y; cr[2] = ch.z; cr[3] = ch.w;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const float t0x = (lx[k] - r.ox) * idx, t1x = (hx[k] - r.ox) * idx;
+                    const float t0y = (ly[k] - r.oy) * idy, t1y = (hy[k] - r.oy) * idy;
+                    const float t0z = (lz[k] - r.oz) * idz, t1z = (hz[k] - r.oz) * idz;
+                    const float tnear = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), r.tmin));
+                    const float tfar = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), best_t));
+                    const float tn_p = __fmaf_rn(fabsf(tnear), -2e-6f, tnear);      // conservative pad, one FFMA each
+                    const float tf_p = __fmaf_rn(fabsf(tfar), 2e-6f, tfar);
+                    const bool h = (tn_p <= tf_p) && (cr[k] != B2RT_CHILD_EMPTY);
+                    tn[k] = h ? tnear : INFINITY;
+                }
+#define B2RT_CSWAP(a, b)                                                                  \
+    if (tn[b] < tn[a]) { float tt = tn[a]; tn[a] = tn[b]; tn[b] = tt; int32_t cc = cr[a]; cr[a] = cr[b]; cr[b] = cc; }
+                B2RT_CSWAP(0, 1) B2RT_CSWAP(2, 3) B2RT_CSWAP(0, 2) B2RT_CSWAP(1, 3) B2RT_CSWAP(1, 2)
+#undef B2RT_CSWAP
+                const int nhit = (tn[0] < INFINITY) + (tn[1] < INFINITY) + (tn[2] < INFINITY) + (tn[3] < INFINITY);
+                if (nhit == 0) {
+                    cur = sp > 0 ? PT_POP() : NONE;
+                } else {
+                    if (sp + 3 > B2RT_STACK_SIZE) { atomicAdd(status, 1u); sp = 0; cur = NONE; leaf = NONE; break; }
+                    if (nhit > 3) PT_PUSH(cr[3]);
+                    if (nhit > 2) PT_PUSH(cr[2]);
+                    if (nhit > 1) PT_PUSH(cr[1]);
+                    cur = cr[0];
+                }
+                if (cur < 0 && leaf == NONE) {          // park this leaf, continue with the next entry
+                    leaf = cur;
+                    cur = sp > 0 ? PT_POP() : NONE;
+                }
+                if (!__any_sync(__activemask(), leaf == NONE)) break;
+            }
+            // ---- primitive loop: the parked leaf, then `cur` while it is a leaf as well ------------------------------
+            while (leaf != NONE) {
+                const uint32_t ref = (uint32_t)leaf & 0x7fffffffu;
+                const uint32_t first = ref >> 3, cnt = (ref & 7u) + 1u;
+                for (uint32_t s = first; s < first + cnt; ++s) {
+                    const float4 *pp = reinterpret_cast<const float4 *>(recs + s);
+                    const float4 A = __ldg(pp), B = __ldg(pp + 1), C = __ldg(pp + 2);
+                    const int prim = __float_as_int(A.w);
+                    const int type = __float_as_int(B.w);
+                    float t, b1 = 0.f, b2 = 0.f;
+                    bool h;
+                    if (type == B2RT_PRIM_TRI) h = tri_test_nobranch(r, A, B, C, best_t, t, b1, b2);
+                    else if (type == B2RT_PRIM_SPHERE) h = sphere_test(r, analytic[__float_as_int(C.w)], best_t, t);
+                    else h = disk_test(r, analytic[__float_as_int(C.w)], best_t, t);
+                    if (h) {
+                        if (ANY) { found = true; break; }
+                        if (t < best_t || prim < best_prim) {
+                            best_t = t; best_prim = prim; best_b1 = b1; best_b2 = b2; found = true;
+                        }
+                    }
+                }
+                if (ANY && found) { cur = NONE; sp = 0; leaf = NONE; break; }
+                leaf = NONE;
+                if (cur < 0) {                          // the next entry is a leaf too
+                    leaf = cur;
+                    cur = sp > 0 ? PT_POP() : NONE;
+                }
+            }
+            if (cur == NONE) {                          // nothing left: leaf == NONE here
+                if (ANY) {
+                    occ[my] = found ? 1 : 0;
+                } else {
+                    float4 o;
+                    o.x = found ? best_t : INFINITY; o.y = __int_as_float(found ? best_prim : -1);
+                    o.z = best_b1; o.w = best_b2;
+                    *reinterpret_cast<float4 *>(hits + my) = o;
+                }
+                active = false;
+                break;
+            }
+            if (!exhausted && __popc(__activemask()) < refill) break;
+        }
+        __syncwarp();
+    }
+#undef PT_PUSH
+#undef PT_POP
+}
+
 __global__ void pool_reset_kernel(unsigned long long *pool) { *pool = 0ull; }
 
 }  // namespace
@@ -206,9 +381,15 @@ int b2rt_trace_impl(b2rt_ctx *ctx, int64_t n, const b2rt_ray *d_rays, b2rt_hit *
     const PrimRec *recs = ctx->d_prim_recs.as<PrimRec>();
     const AnalyticPrim *an = ctx->d_analytic.as<AnalyticPrim>();
     uint32_t *status = ctx->d_counters.as<uint32_t>() + 8;
-    if (ctx->trace_variant == 1) {
+    if (ctx->trace_variant == 1 || ctx->trace_variant == 2) {
+        const bool spec = ctx->trace_variant == 2;
         // persistent grid: every SM holds as many blocks as the occupancy calculator allows
-        int &per_sm = any_hit ? ctx->pt_blocks_per_sm[1] : ctx->pt_blocks_per_sm[0];
+        int &per_sm = ctx->pt_blocks_per_sm[(spec ? 2 : 0) + (any_hit ? 1 : 0)];
+        if (per_sm == 0 && spec) {
+            if (any_hit) B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_spec_kernel<true>, PT_THREADS, 0));
+            else B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_spec_kernel<false>, PT_THREADS, 0));
+            if (per_sm < 1) per_sm = 1;
+        }
         if (per_sm == 0) {
             if (any_hit) B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_persistent_kernel<true>, PT_THREADS, 0));
             else B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_persistent_kernel<false>, PT_THREADS, 0));
@@ -221,7 +402,13 @@ int b2rt_trace_impl(b2rt_ctx *ctx, int64_t n, const b2rt_ray *d_rays, b2rt_hit *
         const int chunk = ctx->trace_chunk >= 32 ? (ctx->trace_chunk & ~31) : 32;
         pool_reset_kernel<<<1, 1, 0, ctx->stream>>>(pool);
         B2RT_LAUNCH_CHECK(ctx);
-        if (any_hit)
+        if (spec && any_hit)
+            trace_spec_kernel<true><<<(unsigned)blocks, PT_THREADS, 0, ctx->stream>>>(
+                nodes, recs, an, d_rays, nullptr, d_occ, n, pool, ctx->trace_refill, chunk, status);
+        else if (spec)
+            trace_spec_kernel<false><<<(unsigned)blocks, PT_THREADS, 0, ctx->stream>>>(
+                nodes, recs, an, d_rays, d_hits, nullptr, n, pool, ctx->trace_refill, chunk, status);
+        else if (any_hit)
             trace_persistent_kernel<true><<<(unsigned)blocks, PT_THREADS, 0, ctx->stream>>>(
                 nodes, recs, an, d_rays, nullptr, d_occ, n, pool, ctx->trace_refill, chunk, status);
         else

@@ -50,7 +50,9 @@ typedef struct {
     int32_t max_depth, wide_width;
     float   bounds[6];          /* scene AABB lo.xyz hi.xyz */
     float   sah_cost;           /* SAH cost of the wide tree (node cost 1, prim cost 1) */
-    float   build_ms;           /* device time of the last b2rt_build_accel */
+    float   build_ms;           /* device time of the last b2rt_build_accel: bounds, Morton, sort, topology, refit,
+                                   wide collapse (scene already resident) */
+    float   upload_ms;          /* host->device copy of the flattened scene + buffer allocation before it */
 } b2rt_accel_info;
 
 /* ---- lifetime ------------------------------------------------------------------------------ */

@@ -1,5 +1,5 @@
 """Stage timings of the photon-mapping frame (BASELINE Cfg3 flavour): shoot, grid build, camera pass with kNN gather.
-python tools/bench_photon.py [n_indirect] [n_caustic] [xres] [yres] [k]"""
+python tools/bench_photon.py [n_indirect] [n_caustic] [xres] [yres] [k] [reps]"""
 import os
 import sys
 import time
@@ -14,12 +14,13 @@ nc = int(sys.argv[2]) if len(sys.argv) > 2 else 2_000_000
 xres = int(sys.argv[3]) if len(sys.argv) > 3 else 1920
 yres = int(sys.argv[4]) if len(sys.argv) > 4 else 1080
 k = int(sys.argv[5]) if len(sys.argv) > 5 else 64
+reps = int(sys.argv[6]) if len(sys.argv) > 6 else 3
 desc = S.cornell_scene(spheres=True, boxes=False, wide=1.78)
 with b2rt.Context(0, seed=3) as ctx:
     S.fill_scene(ctx, desc)
     ctx.build_accel()
     cam = b2rt.pbrt_camera((0, 1, 3.4), (0, 1, 0), (0, 1, 0), 40, xres, yres)
-    for rep in range(3):
+    for rep in range(reps):
         ctx.sync(); t0 = time.perf_counter()
         (pc, pi), (sc, si) = ctx.photons_shoot(nc, ni, batch_paths=4_000_000)
         ctx.sync(); t1 = time.perf_counter()
