@@ -33,6 +33,17 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
+# The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints "NCCL version ..." from C at
+# communicator creation, seen at N = 2), so keep a private copy of the real stdout for the JSON line and send
+# everything else that targets fd 1 to stderr.
+_JSON_OUT = os.fdopen(os.dup(1), "w")
+os.dup2(2, 1)
+
+
+def emit(line):
+    _JSON_OUT.write(json.dumps(line) + "\n")
+    _JSON_OUT.flush()
+
 _TV = os.environ.get("B2RT_TRACE_VARIANT", "2")
 TRACE_KERNEL = {"0": "trace_kernel<closest>", "1": "trace_persistent_kernel<closest>"}.get(_TV, "trace_spec_kernel<closest>")
 METRIC = "Mrays/s (closest-hit primary + any-hit shadow rays, 1M-triangle scene, 1920x1080, 1 spp)"
@@ -185,7 +196,7 @@ def run_reference(args, rank, world):
             "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": nth, "kind": kind, "sample": sample},
             "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def workload_config(args, ntris):
@@ -417,7 +428,7 @@ def main():
         if not args.no_cpu_baseline:
             smp = args.cpu_sample or None
             line["cpu_baseline"] = cpu_reference_step(P, idx, rays, shadow, None, sample=smp)
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 

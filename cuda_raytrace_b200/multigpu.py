@@ -47,6 +47,16 @@ def allgather_varlen(local, group=None):
     return torch.cat([o[:c] for o, c in zip(out, counts)], 0), counts
 
 
+def _ctx_stream_waits_for_torch(ctx):
+    """The library issues its copies on its own non-blocking stream; torch (NCCL, cat, the caching allocator) works on
+    torch's current stream.  Before the library touches a torch tensor, its stream must wait for torch's: without this
+    the upload below could read the gathered array before torch.cat had written it (seen on 2 x B200: photon maps
+    not byte-identical to the single-GPU trace)."""
+    import torch
+    dev = torch.cuda.current_device()
+    torch.cuda.ExternalStream(ctx.stream, device=dev).wait_stream(torch.cuda.current_stream(dev))
+
+
 def shoot_sharded(ctx, n_paths, max_depth=5, caustic=True, indirect=True, group=None):
     """Trace this rank's slice of [0, n_paths), then assemble both photon maps on every rank (all-gather).  Returns the
     stored counts (caustic, indirect).  The assembled arrays equal a single-GPU trace of the whole range byte for byte."""
@@ -63,9 +73,12 @@ def shoot_sharded(ctx, n_paths, max_depth=5, caustic=True, indirect=True, group=
         dev = torch.device("cuda", torch.cuda.current_device())
         local = torch.empty((n, 32), dtype=torch.uint8, device=dev)
         if n:
+            _ctx_stream_waits_for_torch(ctx)        # `local` may reuse a block torch is still reading
+            # the call synchronises the library stream before it returns, so torch may use `local` right away
             ctx._ck(ctx.lib.b2rt_photons_download(ctx.h, which, local.data_ptr(), n, b2rt.DEVICE))
         allp, counts = allgather_varlen(local, group)
         allp = allp.contiguous()
+        _ctx_stream_waits_for_torch(ctx)            # all_gather + cat must have finished before the library copies
         on = (caustic if which == b2rt.MAP_CAUSTIC else indirect)
         ctx._ck(ctx.lib.b2rt_photons_upload(ctx.h, which, allp.data_ptr(), allp.shape[0], n_paths if on else 0, b2rt.DEVICE))
         totals.append(int(allp.shape[0]))
