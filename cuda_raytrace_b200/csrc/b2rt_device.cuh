@@ -232,9 +232,35 @@ static __device__ __noinline__ bool disk_test(const RayD &r, const AnalyticPrim 
 
 constexpr int B2RT_STACK_SIZE = 64;
 
-// Wide-BVH traversal of one ray.  Winner among all accepted primitives is (min t, then min primitive id):
-// order-independent, so the answer does not depend on tree shape.  Node boxes are tested conservatively (padded
-// slab test) so the tree never hides a primitive that the exhaustive loop would accept.
+// Same operations and roundings as tri_test, evaluated without early exits: one predicate at the end.  Every
+// comparison is false on NaN, so a zero divisor (inv = inf, products NaN or inf) is rejected exactly as in tri_test.
+__device__ __forceinline__ bool tri_test_nobranch(const RayD &r, const float4 &A, const float4 &B, const float4 &C,
+                                                  float tmax, float &t_out, float &b1_out, float &b2_out) {
+    const double e1x = B.x, e1y = B.y, e1z = B.z, e2x = C.x, e2y = C.y, e2z = C.z;
+    const float s1x = cross_comp(r.ddy, e2z, r.ddz, e2y);
+    const float s1y = cross_comp(r.ddz, e2x, r.ddx, e2z);
+    const float s1z = cross_comp(r.ddx, e2y, r.ddy, e2x);
+    const float divisor = s1x * B.x + s1y * B.y + s1z * B.z;
+    const float inv = 1.f / divisor;
+    const float dvx = r.ox - A.x, dvy = r.oy - A.y, dvz = r.oz - A.z;
+    const float b1 = (dvx * s1x + dvy * s1y + dvz * s1z) * inv;
+    const double ddvx = dvx, ddvy = dvy, ddvz = dvz;
+    const float s2x = cross_comp(ddvy, e1z, ddvz, e1y);
+    const float s2y = cross_comp(ddvz, e1x, ddvx, e1z);
+    const float s2z = cross_comp(ddvx, e1y, ddvy, e1x);
+    const float b2 = (r.dx * s2x + r.dy * s2y + r.dz * s2z) * inv;
+    const float t = (C.x * s2x + C.y * s2y + C.z * s2z) * inv;
+    const bool ok = (divisor != 0.f) & (b1 >= 0.f) & (b1 <= 1.f) & (b2 >= 0.f) & (b1 + b2 <= 1.f) & (t >= r.tmin) & (t <= tmax);
+    t_out = t; b1_out = b1; b2_out = b2;
+    return ok;
+}
+
+// Wide-BVH traversal of one ray, inlined into the photon and camera kernels.  Winner among all accepted primitives is
+// (min t, then min primitive id): order-independent, so the answer does not depend on tree shape or visiting order.
+// Node boxes are tested conservatively (padded slab test) so the tree never hides a primitive that the exhaustive loop
+// would accept.  Speculative while-while loop: a lane that reaches a leaf parks it and keeps descending until every
+// lane that is still in the node loop has one, then the parked leaves are tested together (the if-if form ran the
+// primitive tests of these kernels with 2.5-6 of 32 threads per instruction).
 // Returns true on a hit (ANY: any accepted primitive).  `overflow` is set if the stack would have overflowed.
 template <bool ANY>
 __device__ __forceinline__ bool traverse(const WideNode *__restrict__ nodes, const PrimRec *__restrict__ recs,
@@ -246,6 +272,7 @@ __device__ __forceinline__ bool traverse(const WideNode *__restrict__ nodes, con
     r.dx = dx; r.dy = dy; r.dz = dz;
     r.ddx = dx; r.ddy = dy; r.ddz = dz;
     const float idx = 1.f / dx, idy = 1.f / dy, idz = 1.f / dz;
+    constexpr int32_t NONE = B2RT_CHILD_EMPTY;      // "nothing": never a valid node index or leaf reference
 
     float best_t = tmax;
     int best_prim = 0x7fffffff, best_slot = -1;
@@ -254,11 +281,11 @@ __device__ __forceinline__ bool traverse(const WideNode *__restrict__ nodes, con
 
     int32_t stack[B2RT_STACK_SIZE];
     int sp = 0;
-    int32_t cur = 0;  // root
+    int32_t cur = 0, leaf = NONE;  // root
 
-    while (true) {
-        if (cur >= 0) {
-            // ---- internal node: test 4 child boxes ------------------------------------------------
+    while (cur != NONE || leaf != NONE) {
+        // ---- node loop -----------------------------------------------------------------------------
+        while (cur >= 0 && cur != NONE) {
             const float4 *np = reinterpret_cast<const float4 *>(nodes + cur);
             float4 lox = __ldg(np), hix = __ldg(np + 1), loy = __ldg(np + 2), hiy = __ldg(np + 3),
                    loz = __ldg(np + 4), hiz = __ldg(np + 5);
@@ -276,8 +303,8 @@ __device__ __forceinline__ bool traverse(const WideNode *__restrict__ nodes, con
                 float tnear = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), r.tmin));
                 float tfar = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), best_t));
                 // conservative padding: widen the slab interval by a few ulps on both ends
-                float tn_p = tnear - fabsf(tnear) * 2e-6f;
-                float tf_p = tfar + fabsf(tfar) * 2e-6f;
+                float tn_p = __fmaf_rn(fabsf(tnear), -2e-6f, tnear);
+                float tf_p = __fmaf_rn(fabsf(tfar), 2e-6f, tfar);
                 bool h = (tn_p <= tf_p) && (cr[k] != B2RT_CHILD_EMPTY);
                 tn[k] = h ? tnear : INFINITY;
             }
@@ -288,18 +315,23 @@ __device__ __forceinline__ bool traverse(const WideNode *__restrict__ nodes, con
 #undef B2RT_CSWAP
             int nhit = (tn[0] < INFINITY) + (tn[1] < INFINITY) + (tn[2] < INFINITY) + (tn[3] < INFINITY);
             if (nhit == 0) {
-                if (sp == 0) break;
-                cur = stack[--sp];
-                continue;
+                cur = sp > 0 ? stack[--sp] : NONE;
+            } else {
+                if (sp + 3 > B2RT_STACK_SIZE) { overflow = true; sp = 0; cur = NONE; leaf = NONE; break; }
+                if (nhit > 3) stack[sp++] = cr[3];
+                if (nhit > 2) stack[sp++] = cr[2];
+                if (nhit > 1) stack[sp++] = cr[1];
+                cur = cr[0];
             }
-            if (sp + 3 > B2RT_STACK_SIZE) { overflow = true; break; }
-            if (nhit > 3) stack[sp++] = cr[3];
-            if (nhit > 2) stack[sp++] = cr[2];
-            if (nhit > 1) stack[sp++] = cr[1];
-            cur = cr[0];
-        } else {
-            // ---- leaf: 1..8 primitive records -----------------------------------------------------
-            uint32_t ref = (uint32_t)cur & 0x7fffffffu;
+            if (cur < 0 && leaf == NONE) {      // park this leaf, continue with the next entry
+                leaf = cur;
+                cur = sp > 0 ? stack[--sp] : NONE;
+            }
+            if (!__any_sync(__activemask(), leaf == NONE)) break;
+        }
+        // ---- primitive loop: the parked leaf, then `cur` while it is a leaf as well ---------------------
+        while (leaf != NONE) {
+            uint32_t ref = (uint32_t)leaf & 0x7fffffffu;
             uint32_t first = ref >> 3, cnt = (ref & 7u) + 1u;
             for (uint32_t s = first; s < first + cnt; ++s) {
                 const float4 *pp = reinterpret_cast<const float4 *>(recs + s);
@@ -308,7 +340,7 @@ __device__ __forceinline__ bool traverse(const WideNode *__restrict__ nodes, con
                 int type = __float_as_int(B.w);
                 float t, b1 = 0.f, b2 = 0.f;
                 bool h;
-                if (type == B2RT_PRIM_TRI) h = tri_test(r, A, B, C, best_t, t, b1, b2);
+                if (type == B2RT_PRIM_TRI) h = tri_test_nobranch(r, A, B, C, best_t, t, b1, b2);
                 else if (type == B2RT_PRIM_SPHERE) h = sphere_test(r, analytic[__float_as_int(C.w)], best_t, t);
                 else h = disk_test(r, analytic[__float_as_int(C.w)], best_t, t);
                 if (h) {
@@ -318,9 +350,12 @@ __device__ __forceinline__ bool traverse(const WideNode *__restrict__ nodes, con
                     }
                 }
             }
-            if (ANY && found) break;
-            if (sp == 0) break;
-            cur = stack[--sp];
+            if (ANY && found) { cur = NONE; leaf = NONE; break; }
+            leaf = NONE;
+            if (cur < 0) {                      // the next entry is a leaf too
+                leaf = cur;
+                cur = sp > 0 ? stack[--sp] : NONE;
+            }
         }
     }
     hit.t = found ? best_t : INFINITY;

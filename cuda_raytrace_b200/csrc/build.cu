@@ -94,16 +94,27 @@ prim_bounds_kernel(const float *__restrict__ verts, const int32_t *__restrict__ 
             smax[a] = fmaxf(smax[a], __shfl_xor_sync(0xffffffffu, smax[a], o));
         }
     }
+    // warp results -> shared-memory atomics -> 12 global atomics per BLOCK (min / max are order-independent, so the
+    // bounds stay bit-exact; one global atomic per warp and value serialised 375 k atomics on 12 addresses at 1 M prims)
+    __shared__ uint32_t s_box[12];
+    if (threadIdx.x < 12) s_box[threadIdx.x] = (threadIdx.x % 6) < 3 ? 0xffffffffu : 0u;
+    __syncthreads();
     if ((threadIdx.x & 31) == 0) {
 #pragma unroll
         for (int a = 0; a < 3; ++a) {
             if (cmin[a] <= cmax[a]) {
-                atomicMin(&scene_box[a], f2ord(cmin[a]));
-                atomicMax(&scene_box[3 + a], f2ord(cmax[a]));
-                atomicMin(&scene_box[6 + a], f2ord(smin[a]));
-                atomicMax(&scene_box[9 + a], f2ord(smax[a]));
+                atomicMin(&s_box[a], f2ord(cmin[a]));
+                atomicMax(&s_box[3 + a], f2ord(cmax[a]));
+                atomicMin(&s_box[6 + a], f2ord(smin[a]));
+                atomicMax(&s_box[9 + a], f2ord(smax[a]));
             }
         }
+    }
+    __syncthreads();
+    if (threadIdx.x < 12) {
+        const uint32_t v = s_box[threadIdx.x];
+        if ((threadIdx.x % 6) < 3) { if (v != 0xffffffffu) atomicMin(&scene_box[threadIdx.x], v); }
+        else if (v != 0u) atomicMax(&scene_box[threadIdx.x], v);
     }
 }
 

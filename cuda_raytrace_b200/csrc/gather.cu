@@ -42,8 +42,9 @@ __device__ __forceinline__ uint64_t shfl_xor_u64(uint64_t v, int m) {
 // `up` differs between lanes: the swap decision is formed with logic ops so it compiles to predicates + selects, not to
 // a divergent branch (ncu: the branchy form ran with 13 of 32 threads per instruction)
 __device__ __forceinline__ void key_ce(uint64_t &a, uint64_t &b, bool up) {
-    const uint32_t lt = b < a, gt = a < b, u = up;
-    const bool sw = ((lt & u) | (gt & (u ^ 1u))) != 0u;
+    // one 64-bit comparison: ascending swaps when b < a, descending when !(b < a); the latter also swaps equal keys,
+    // which changes nothing
+    const bool sw = (b < a) == up;
     const uint64_t lo = sw ? b : a, hi = sw ? a : b;
     a = lo; b = hi;
 }
@@ -67,7 +68,7 @@ __device__ __forceinline__ void warp_sort(uint64_t (&v)[PL], int lane) {
 #pragma unroll
             for (int j = 0; j < PL; ++j) {
                 const uint64_t o = shfl_xor_u64(v[j], lm);
-                v[j] = take_min ? (o < v[j] ? o : v[j]) : (o > v[j] ? o : v[j]);
+                v[j] = ((o < v[j]) == take_min) ? o : v[j];      // min or max of the pair with one comparison
             }
         }
 #pragma unroll
@@ -270,7 +271,7 @@ gather_kernel(const b2rt_photon *__restrict__ photons, const uint32_t *__restric
 // The selected set is the k smallest (d2, index) keys below the radius -- the same definition as the simple
 // kernel and the brute-force oracle, so results are bit-identical whatever the scan order.
 constexpr int G2_C = 4, G2_SHIFT = 2;
-constexpr int G2_STAGE = 512;            // staged positions per warp
+constexpr int G2_STAGE = 256;            // staged positions per warp (4 KB: six blocks per SM fit)
 
 struct Gather2Grid {
     float lo[3]; float cell, inv, slack;
@@ -308,7 +309,7 @@ __device__ __forceinline__ float axis_gap(float q, float lo, float hi, bool open
 }
 
 template <bool KNN>
-__global__ void __launch_bounds__(GATHER_WARPS * 32)
+__global__ void __launch_bounds__(GATHER_WARPS * 32, 6)
 gather_tiled_kernel(const float4 *__restrict__ pos4, const b2rt_photon *__restrict__ photons,
                     const uint32_t *__restrict__ cell_start, const uint32_t *__restrict__ coarse, Gather2Grid g,
                     const b2rt_query *__restrict__ queries, int64_t nq, int k, float max_dist2, float n_paths,

@@ -204,28 +204,6 @@ trace_persistent_kernel(const WideNode *__restrict__ nodes, const PrimRec *__res
 //   * a branch-free triangle test (same operations and roundings as tri_test, one predicate at the end).
 // Box tests only prune; accepted primitives and their (t, b1, b2) are computed by the same expressions, so the
 // results are bit-identical to the other variants.
-__device__ __forceinline__ bool tri_test_nobranch(const RayD &r, const float4 &A, const float4 &B, const float4 &C,
-                                                  float tmax, float &t_out, float &b1_out, float &b2_out) {
-    const double e1x = B.x, e1y = B.y, e1z = B.z, e2x = C.x, e2y = C.y, e2z = C.z;
-    const float s1x = cross_comp(r.ddy, e2z, r.ddz, e2y);
-    const float s1y = cross_comp(r.ddz, e2x, r.ddx, e2z);
-    const float s1z = cross_comp(r.ddx, e2y, r.ddy, e2x);
-    const float divisor = s1x * B.x + s1y * B.y + s1z * B.z;
-    const float inv = 1.f / divisor;
-    const float dvx = r.ox - A.x, dvy = r.oy - A.y, dvz = r.oz - A.z;
-    const float b1 = (dvx * s1x + dvy * s1y + dvz * s1z) * inv;
-    const double ddvx = dvx, ddvy = dvy, ddvz = dvz;
-    const float s2x = cross_comp(ddvy, e1z, ddvz, e1y);
-    const float s2y = cross_comp(ddvz, e1x, ddvx, e1z);
-    const float s2z = cross_comp(ddvx, e1y, ddvy, e1x);
-    const float b2 = (r.dx * s2x + r.dy * s2y + r.dz * s2z) * inv;
-    const float t = (C.x * s2x + C.y * s2y + C.z * s2z) * inv;
-    // every comparison is false on NaN, so a zero divisor (inv = inf, products NaN or inf) is rejected as in tri_test
-    const bool ok = (divisor != 0.f) & (b1 >= 0.f) & (b1 <= 1.f) & (b2 >= 0.f) & (b1 + b2 <= 1.f) & (t >= r.tmin) & (t <= tmax);
-    t_out = t; b1_out = b1; b2_out = b2;
-    return ok;
-}
-
 template <bool ANY>
 __global__ void __launch_bounds__(PT_THREADS)
 trace_spec_kernel(const WideNode *__restrict__ nodes, const PrimRec *__restrict__ recs,

@@ -12,6 +12,7 @@ fi
 timeout 900 python bench.py > $O/bench.json 2> $O/bench.err; echo "bench rc=$?" >> $O/bench.err
 timeout 600 python bench.py --impl reference --steps 5 --warmup 1 > $O/bench_ref.json 2> $O/bench_ref.err
 timeout 600 python tools/bench_photon.py > $O/photon.log 2>&1
+timeout 900 python tools/bench_cfg4.py > $O/cfg4.json 2> $O/cfg4.err
 if [ -z "$SKIP_NCU" ]; then
 NCU="ncu --clock-control none"
 timeout 900 $NCU --metrics gpu__time_duration.sum -c 400 --csv --log-file $O/launches_bench.csv \
