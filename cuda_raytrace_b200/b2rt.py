@@ -405,4 +405,16 @@ def _render_frame(self, cam, spp=1, max_specular_depth=5, nused=50, max_dist=0.1
     return out
 
 
+def _render_frame_device(self, cam, out_ptr, spp=1, max_specular_depth=5, nused=50, max_dist=0.1, caustic=True,
+                         indirect=True, direct=True, window=None):
+    """Same as render_frame, but the (y1-y0, x1-x0, 3) float32 image is written to the DEVICE pointer `out_ptr`
+    (b2rt_render_frame(..., B2RT_DEVICE)); the call returns after the library stream has finished."""
+    x0, x1, y0, y1 = window if window else (0, cam.xres, 0, cam.yres)
+    fp = FrameParams(spp, max_specular_depth, nused, float(np.float32(max_dist) * np.float32(max_dist)), int(caustic),
+                     int(indirect), int(direct), x0, x1, y0, y1)
+    self.lib.b2rt_render_frame.argtypes = [C.c_void_p, C.POINTER(Camera), C.POINTER(FrameParams), C.c_void_p, C.c_int]
+    self._ck(self.lib.b2rt_render_frame(self.h, C.byref(cam), C.byref(fp), C.c_void_p(out_ptr), DEVICE))
+
+
 Context.render_frame = _render_frame
+Context.render_frame_device = _render_frame_device

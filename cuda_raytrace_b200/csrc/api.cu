@@ -60,6 +60,7 @@ int b2rt_create(int device, uint64_t seed, b2rt_ctx **out) {
     if (const char *v = getenv("B2RT_TRACE_CHUNK")) ctx->trace_chunk = atoi(v);
     if (const char *v = getenv("B2RT_GATHER_VARIANT")) ctx->gather_variant = atoi(v);
     if (const char *v = getenv("B2RT_PHOTON_VARIANT")) ctx->photon_variant = atoi(v);
+    if (const char *v = getenv("B2RT_HOST_CHUNK")) { long c = atol(v); if (c >= 1024) ctx->host_chunk = c; }
     CK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
     CK(cudaEventCreate(&ctx->ev0)); CK(cudaEventCreate(&ctx->ev1));
     CK(cudaEventCreate(&ctx->evb0)); CK(cudaEventCreate(&ctx->evb1)); CK(cudaEventCreate(&ctx->evb_mid));
@@ -258,7 +259,7 @@ static int trace_common(b2rt_ctx *ctx, int64_t nrays, const b2rt_ray *rays, b2rt
     else B2RT_CUDA(ctx, ctx->d_hits.reserve((size_t)nrays * sizeof(b2rt_hit)));
     // Chunked pipeline over three streams: the upload of chunk i+1, the traversal of chunk i and the download of
     // chunk i-1 overlap (PCIe is full duplex; with pinned caller memory the copies are asynchronous).
-    const int64_t CH = 1 << 18;
+    const int64_t CH = ctx->host_chunk;
     B2RT_CUDA(ctx, cudaEventRecord(ctx->ev_k, st));                 // everything queued so far on the main stream
     B2RT_CUDA(ctx, cudaStreamWaitEvent(ctx->stream_in, ctx->ev_k, 0));
     for (int64_t c0 = 0; c0 < nrays; c0 += CH) {

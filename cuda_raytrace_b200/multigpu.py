@@ -57,45 +57,83 @@ def _ctx_stream_waits_for_torch(ctx):
     torch.cuda.ExternalStream(ctx.stream, device=dev).wait_stream(torch.cuda.current_stream(dev))
 
 
-def shoot_sharded(ctx, n_paths, max_depth=5, caustic=True, indirect=True, group=None):
-    """Trace this rank's slice of [0, n_paths), then assemble both photon maps on every rank (all-gather).  Returns the
-    stored counts (caustic, indirect).  The assembled arrays equal a single-GPU trace of the whole range byte for byte."""
+def assemble_map(ctx, which, n_paths, group=None):
+    """Replace this rank's slice of photon map `which` by the concatenation of all ranks' slices in rank order.
+    Counts first (one int64 per rank), then the payload: every rank copies its photons straight into its place in the
+    final array and the slices are broadcast in place (one broadcast per rank instead of a padded
+    all-gather + cat), then one copy hands the array to the library.  Returns the total photon count."""
     import torch
+    import torch.distributed as dist
+    from . import b2rt
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    n, _ = ctx.photons_count(which)
+    dev = torch.device("cuda", torch.cuda.current_device())
+    mine = torch.tensor([n], dtype=torch.int64, device=dev)
+    counts = [torch.zeros_like(mine) for _ in range(world)]
+    dist.all_gather(counts, mine, group=group)
+    counts = [int(c.item()) for c in counts]
+    offs = np.concatenate([[0], np.cumsum(counts)]).astype(np.int64)
+    total = int(offs[-1])
+    out = torch.empty((max(total, 1), 32), dtype=torch.uint8, device=dev)
+    if n:
+        _ctx_stream_waits_for_torch(ctx)            # `out` may reuse a block torch is still reading
+        # synchronous on return, so torch may broadcast from the slice right away
+        ctx._ck(ctx.lib.b2rt_photons_download(ctx.h, which, out[int(offs[rank]):].data_ptr(), n, b2rt.DEVICE))
+    works = [dist.broadcast(out[int(offs[r]):int(offs[r + 1])], src=dist.get_global_rank(group, r) if group else r,
+                            group=group, async_op=True) for r in range(world) if counts[r]]
+    for w in works:
+        w.wait()
+    _ctx_stream_waits_for_torch(ctx)                # the broadcasts must have finished before the library copies
+    ctx._ck(ctx.lib.b2rt_photons_upload(ctx.h, which, out.data_ptr(), total, n_paths, b2rt.DEVICE))
+    return total
+
+
+def shoot_sharded(ctx, n_paths, max_depth=5, caustic=True, indirect=True, group=None):
+    """Trace this rank's slice of [0, n_paths), then assemble both photon maps on every rank.  Returns the stored counts
+    (caustic, indirect).  The assembled arrays equal a single-GPU trace of the whole range byte for byte."""
     import torch.distributed as dist
     from . import b2rt
     rank, world = dist.get_rank(group), dist.get_world_size(group)
     first, count = path_range(n_paths, rank, world)
     ctx.photons_clear()
     ctx.photons_trace(first, count, max_depth=max_depth, caustic=caustic, indirect=indirect)
-    totals = []
-    for which in (b2rt.MAP_CAUSTIC, b2rt.MAP_INDIRECT):
-        n, _ = ctx.photons_count(which)
-        dev = torch.device("cuda", torch.cuda.current_device())
-        local = torch.empty((n, 32), dtype=torch.uint8, device=dev)
-        if n:
-            _ctx_stream_waits_for_torch(ctx)        # `local` may reuse a block torch is still reading
-            # the call synchronises the library stream before it returns, so torch may use `local` right away
-            ctx._ck(ctx.lib.b2rt_photons_download(ctx.h, which, local.data_ptr(), n, b2rt.DEVICE))
-        allp, counts = allgather_varlen(local, group)
-        allp = allp.contiguous()
-        _ctx_stream_waits_for_torch(ctx)            # all_gather + cat must have finished before the library copies
-        on = (caustic if which == b2rt.MAP_CAUSTIC else indirect)
-        ctx._ck(ctx.lib.b2rt_photons_upload(ctx.h, which, allp.data_ptr(), allp.shape[0], n_paths if on else 0, b2rt.DEVICE))
-        totals.append(int(allp.shape[0]))
-    return tuple(totals)
+    return (assemble_map(ctx, b2rt.MAP_CAUSTIC, n_paths if caustic else 0, group),
+            assemble_map(ctx, b2rt.MAP_INDIRECT, n_paths if indirect else 0, group))
+
+
+_pinned_frames = {}
 
 
 def render_sharded(ctx, cam, group=None, **kw):
-    """Each rank renders its band; rank 0 returns the composited (yres, xres, 3) image, the others None."""
+    """Each rank renders its band; rank 0 returns the composited (yres, xres, 3) image, the others None.  With NCCL the
+    returned array is a view of a pinned buffer that the next call with the same resolution overwrites.
+    NCCL: the band is rendered straight into a CUDA tensor, the bands are gathered on rank 0's GPU and the finished image
+    crosses PCIe once, into pinned memory (the first version went band -> pageable host -> device -> all-gather -> host
+    and made the 4K frame slower on two GPUs than on one).  gloo (CPU tests): host arrays all the way."""
     import torch
     import torch.distributed as dist
     rank, world = dist.get_rank(group), dist.get_world_size(group)
     x0, x1, y0, y1 = band_window(cam.yres, cam.xres, rank, world)
-    band = ctx.render_frame(cam, window=(x0, x1, y0, y1), **kw) if y1 > y0 else np.zeros((0, cam.xres, 3), np.float32)
-    t = torch.from_numpy(band.reshape(-1, cam.xres * 3))
-    if torch.cuda.is_available() and dist.get_backend(group) == "nccl":
-        t = t.cuda()
-    allb, _ = allgather_varlen(t, group)
+    if not (torch.cuda.is_available() and dist.get_backend(group) == "nccl"):
+        band = ctx.render_frame(cam, window=(x0, x1, y0, y1), **kw) if y1 > y0 else np.zeros((0, cam.xres, 3), np.float32)
+        allb, _ = allgather_varlen(torch.from_numpy(band.reshape(-1, cam.xres * 3)), group)
+        return allb.numpy().reshape(cam.yres, cam.xres, 3) if rank == 0 else None
+    dev = torch.device("cuda", torch.cuda.current_device())
+    rows = [band_window(cam.yres, cam.xres, r, world) for r in range(world)]
+    pad = max(max(w[3] - w[2] for w in rows), 1)
+    band = torch.empty((pad, cam.xres * 3), dtype=torch.float32, device=dev)
+    if y1 > y0:
+        _ctx_stream_waits_for_torch(ctx)            # `band` may reuse a block torch is still reading
+        ctx.render_frame_device(cam, band.data_ptr(), window=(x0, x1, y0, y1), **kw)     # synchronous on return
+    parts = [torch.empty_like(band) for _ in range(world)] if rank == 0 else None
+    dist.gather(band, parts, dst=0, group=group)
     if rank != 0:
         return None
-    return allb.cpu().numpy().reshape(cam.yres, cam.xres, 3)
+    img = torch.cat([p[: w[3] - w[2]] for p, w in zip(parts, rows)], 0)
+    key = (cam.yres, cam.xres)
+    if key not in _pinned_frames:
+        _pinned_frames[key] = torch.empty((cam.yres, cam.xres * 3), dtype=torch.float32).pin_memory()
+    host = _pinned_frames[key]
+    host.copy_(img, non_blocking=True)
+    torch.cuda.current_stream().synchronize()
+    return host.numpy().reshape(cam.yres, cam.xres, 3)

@@ -46,20 +46,7 @@ def shoot(n_paths):
 
 def assemble(n_paths):
     """all-gather of both maps (the second half of multigpu.shoot_sharded)"""
-    totals = []
-    for which in (b2rt.MAP_CAUSTIC, b2rt.MAP_INDIRECT):
-        n, _ = ctx.photons_count(which)
-        local_t = torch.empty((n, 32), dtype=torch.uint8, device="cuda")
-        if n:
-            M._ctx_stream_waits_for_torch(ctx)
-            ctx._ck(ctx.lib.b2rt_photons_download(ctx.h, which, local_t.data_ptr(), n, b2rt.DEVICE))
-        allp, _ = M.allgather_varlen(local_t)
-        allp = allp.contiguous()
-        M._ctx_stream_waits_for_torch(ctx)
-        ctx._ck(ctx.lib.b2rt_photons_upload(ctx.h, which, allp.data_ptr(), allp.shape[0], n_paths, b2rt.DEVICE))
-        totals.append(int(allp.shape[0]))
-        del allp, local_t
-    return totals
+    return [M.assemble_map(ctx, which, n_paths) for which in (b2rt.MAP_CAUSTIC, b2rt.MAP_INDIRECT)]
 
 
 for n_paths in sweep:
