@@ -46,6 +46,11 @@ def emit(line):
 
 _TV = os.environ.get("B2RT_TRACE_VARIANT", "2")
 TRACE_KERNEL = {"0": "trace_kernel<closest>", "1": "trace_persistent_kernel<closest>"}.get(_TV, "trace_spec_kernel<closest>")
+# dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the default closest-hit kernel on this exact workload,
+# from the ncu --set full capture of `bench.py --steps 2 --warmup 3` (profiles/r01h_ncu_trace.md, re-captured r01m):
+# 136 MB read + 25.8 MB written, against 99.5 MB of compulsory ray / hit bytes (the difference is the cold 52 MB scene).
+TRAFFIC_BYTES = 161.8e6 if _TV == "2" else None
+TRAFFIC_SOURCE = "ncu --set full, r01m capture (profiles/r01h_ncu_trace.md): dram read 136 MB + write 25.8 MB per launch"
 METRIC = "Mrays/s (closest-hit primary + any-hit shadow rays, 1M-triangle scene, 1920x1080, 1 spp)"
 LIGHT = (0.5, 3.0, 0.5)
 
@@ -418,7 +423,8 @@ def main():
                     "ms_per_step": e2e_ms_m / e2e_steps, "api": "b2rt_trace_closest/b2rt_trace_any(B2RT_HOST)"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": TRACE_KERNEL, "achieved": achieved, "peak": peak,
-                         "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "unit": "GB/s", "frac": achieved / peak, "traffic": TRAFFIC_BYTES if (args.tris, n1) == (1_000_000, 2073600) else None,
+                         "traffic_source": TRAFFIC_SOURCE, "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": 48 * n1,
                          "note": "traversal is latency/issue bound, not HBM bound (SURVEY 8(d)); see profiles/"},
             "clocks": clocks, "wall_s_timed_region": wall,

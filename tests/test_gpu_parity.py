@@ -206,3 +206,75 @@ def test_cfg2_full_size_properties(ctx):
     ps.add_mesh(P, idx)
     t, prim, _, _ = ps.intersect(rays[sel], 8)
     assert np.array_equal(h["prim"][sel], prim) and np.array_equal(bits(h["t"][sel]), bits(t))
+
+
+# ---- edge cases of the boundary -------------------------------------------------------------------------------------
+def test_empty_batches_and_call_order_errors(built):
+    from cuda_raytrace_b200 import b2rt
+    with b2rt.Context(0, seed=1) as c:
+        rays = S.pinhole_rays(4, 4)
+        with pytest.raises(b2rt.B2rtError) as e:        # trace before build: B2RT_E_STATE, like the reference's
+            c.trace_closest(rays)                       # launch-before-compile being an error rather than garbage
+        assert e.value.code == -3
+        c.add_mesh(*S.heightfield_mesh(4, 4, None, seed=1))
+        c.build_accel()
+        assert len(c.trace_closest(rays[:0])) == 0 and len(c.trace_any(rays[:0])) == 0      # empty batch is not an error
+        with pytest.raises(b2rt.B2rtError) as e:
+            c._ck(c.lib.b2rt_trace_closest(c.h, 5, None, None, b2rt.HOST))
+        assert e.value.code == -1
+        with pytest.raises(b2rt.B2rtError) as e:        # gather before any grid was built
+            c.gather(1, np.zeros(1, b2rt.QUERY_DTYPE), 8, 0.01)
+        assert e.value.code in (-1, -3)
+        h = c.trace_closest(rays)                       # the context is still usable after the errors
+        assert h.shape == (16,)
+
+
+def test_axis_parallel_and_degenerate_rays_match_oracle(ctx):
+    """Zero direction components (1/d = inf in the slab test), rays lying in the plane of box faces, zero-length and
+    inverted segments: everything must still equal the exhaustive oracle loop."""
+    P, idx = S.heightfield_mesh(24, 24, None, seed=9)
+    ps = O.PortScene()
+    ps.add_mesh(P, idx)
+    _tri_only_ctx(ctx, P, idx)
+    rng = np.random.default_rng(4)
+    n = 6000
+    rays = np.zeros((n, 8), np.float32)
+    rays[:, 0:3] = rng.uniform([-1.1, -0.4, -1.1], [1.1, 1.0, 1.1], (n, 3))
+    rays[:, 7] = np.inf
+    axis = rng.integers(0, 3, n)
+    sign = rng.choice([-1.0, 1.0], n)
+    rays[np.arange(n), 4 + axis] = sign                               # exactly axis-parallel
+    rays[: n // 3, 0:3] = P[rng.integers(0, len(P), n // 3)]          # origins exactly on vertices (box planes)
+    rays[: n // 3, 1] += 0.5
+    rays[n // 3: n // 2, 5] = -1.0; rays[n // 3: n // 2, 4] = 0; rays[n // 3: n // 2, 6] = 0    # straight down
+    two = rng.uniform(-1, 1, (n // 4, 3)).astype(np.float32)
+    two[:, rng.integers(0, 3)] = 0.0                                  # one zero component, two free
+    rays[-n // 4:, 4:7] = two
+    rays[5::17, 7] = rays[5::17, 3]                                   # zero-length segment
+    rays[7::19, 3] = 5.0; rays[7::19, 7] = 1.0                        # tmin > tmax
+    t, prim, b1, b2 = ps.intersect(rays, 8)
+    h = ctx.trace_closest(rays)
+    assert (prim >= 0).sum() > 500
+    assert np.array_equal(h["prim"], prim) and np.array_equal(bits(h["t"]), bits(t))
+    assert np.array_equal(ctx.trace_any(rays), ps.occluded(rays, 8))
+
+
+def test_chunked_host_path_with_ragged_tail(ctx):
+    """The host-buffer call is a pipeline over 256 K-ray chunks: a batch that is not a multiple of the chunk must give
+    the bytes of the single-launch device path, in the caller's order."""
+    P, idx = S.cfg2_mesh(100_000)
+    _tri_only_ctx(ctx, P, idx)
+    base = S.pinhole_rays(640, 360)
+    reps = (2 * 262144 + 777) // len(base) + 1
+    rays = np.ascontiguousarray(np.tile(base, (reps, 1))[: 2 * 262144 + 777])
+    rays[:, 0] += np.linspace(0, 0.05, len(rays), dtype=np.float32)   # every ray distinct
+    h = ctx.trace_closest(rays)
+    o = ctx.trace_any(rays)
+    d_r = _dev(rays)
+    d_h = torch.zeros((len(rays), 4), dtype=torch.float32, device="cuda")
+    d_o = torch.zeros(len(rays), dtype=torch.uint8, device="cuda")
+    ctx.trace_closest_device(len(rays), d_r.data_ptr(), d_h.data_ptr())
+    ctx.trace_any_device(len(rays), d_r.data_ptr(), d_o.data_ptr())
+    ctx.sync()
+    assert np.array_equal(d_h.cpu().numpy().view(np.uint32).reshape(-1), np.ascontiguousarray(h).view(np.uint32))
+    assert np.array_equal(d_o.cpu().numpy(), o)
