@@ -232,6 +232,15 @@ static __device__ __noinline__ bool disk_test(const RayD &r, const AnalyticPrim 
 
 constexpr int B2RT_STACK_SIZE = 64;
 
+// Reciprocal direction for the slab test, clamped to +-FLT_MAX.  With 1/0 = inf a ray that runs exactly in the plane of a
+// box face gives (plane - origin) * inf = 0 * inf = NaN, fminf(NaN, +inf) = +inf, and the box - which the ray grazes -
+// would be rejected: the node test must only ever err on the accepting side (found by
+// tests/test_gpu_parity.py::test_axis_parallel_and_degenerate_rays_match_oracle: rays straight down through mesh
+// vertices lost their hits).  With a finite factor the product is 0 and the slab is [0, big].
+__device__ __forceinline__ float slab_rcp(float d) {
+    return fminf(fmaxf(1.f / d, -3.402823466e38f), 3.402823466e38f);
+}
+
 // Same operations and roundings as tri_test, evaluated without early exits: one predicate at the end.  Every
 // comparison is false on NaN, so a zero divisor (inv = inf, products NaN or inf) is rejected exactly as in tri_test.
 __device__ __forceinline__ bool tri_test_nobranch(const RayD &r, const float4 &A, const float4 &B, const float4 &C,
@@ -271,7 +280,7 @@ __device__ __forceinline__ bool traverse(const WideNode *__restrict__ nodes, con
     r.ox = ox; r.oy = oy; r.oz = oz; r.tmin = tmin;
     r.dx = dx; r.dy = dy; r.dz = dz;
     r.ddx = dx; r.ddy = dy; r.ddz = dz;
-    const float idx = 1.f / dx, idy = 1.f / dy, idz = 1.f / dz;
+    const float idx = slab_rcp(dx), idy = slab_rcp(dy), idz = slab_rcp(dz);
     constexpr int32_t NONE = B2RT_CHILD_EMPTY;      // "nothing": never a valid node index or leaf reference
 
     float best_t = tmax;

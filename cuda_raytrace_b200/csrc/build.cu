@@ -278,6 +278,19 @@ wide_collapse_level_kernel(const int32_t *__restrict__ queue_in, int nq, int n,
         if (is_openable(c[k], n, collapse)) queue_out[atomicAdd(out_count, 1u)] = c[k];
 }
 
+// Absolute margin added to every child box stored in a wide node: 2^-21 of the largest root-box coordinate (~4 ulps at
+// scene scale).  A slab test cannot follow a ray that runs exactly IN the plane shared by two sibling boxes (a ray
+// through a mesh vertex, an axis-parallel ray along a wall): the interval of one of the two boxes ends at exactly 0 and
+// no relative padding of t widens it, so triangles touching the plane from that side were never tested although
+// pbrt's triangle test accepts the boundary hit (tests/test_gpu_parity.py::
+// test_axis_parallel_and_degenerate_rays_match_oracle).  With the margin the ray is strictly inside both boxes.
+// One float subtract / add per plane; oracle/oracle_port.c (port_lbvh_build) does the same, so node bytes stay bit-exact.
+__device__ __forceinline__ float node_box_pad(const float *root) {
+    float m = fmaxf(fmaxf(fmaxf(fabsf(root[0]), fabsf(root[1])), fmaxf(fabsf(root[2]), fabsf(root[3]))),
+                    fmaxf(fabsf(root[4]), fabsf(root[5])));
+    return m * 4.76837158203125e-07f;
+}
+
 __global__ void __launch_bounds__(128)
 wide_emit_kernel(int n, const WideTmp *__restrict__ tmp, const uint32_t *__restrict__ wide_flag,
                  const uint32_t *__restrict__ wide_index, const float *__restrict__ box,
@@ -288,6 +301,7 @@ wide_emit_kernel(int n, const WideTmp *__restrict__ tmp, const uint32_t *__restr
     WideTmp t = tmp[i];
     WideNode w;
     int used = 0;
+    const float pad = node_box_pad(box);        // box[0..5] = root
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
         int c = t.c[k];
@@ -299,8 +313,8 @@ wide_emit_kernel(int n, const WideTmp *__restrict__ tmp, const uint32_t *__restr
         }
         ++used;
         const float *b = box + 6 * (int64_t)c;
-        w.lox[k] = b[0]; w.loy[k] = b[1]; w.loz[k] = b[2];
-        w.hix[k] = b[3]; w.hiy[k] = b[4]; w.hiz[k] = b[5];
+        w.lox[k] = b[0] - pad; w.loy[k] = b[1] - pad; w.loz[k] = b[2] - pad;
+        w.hix[k] = b[3] + pad; w.hiy[k] = b[4] + pad; w.hiz[k] = b[5] + pad;
         if (c >= n - 1) {
             w.child[k] = (int32_t)(0x80000000u | ((uint32_t)(c - (n - 1)) << 3));          // 1 prim
         } else if (collapse[c]) {
@@ -324,8 +338,9 @@ __global__ void wide_single_kernel(int n, const float *__restrict__ box_root, Wi
         w.child[k] = B2RT_CHILD_EMPTY; w.meta[k] = 0;
     }
     if (n > 0) {
-        w.lox[0] = box_root[0]; w.loy[0] = box_root[1]; w.loz[0] = box_root[2];
-        w.hix[0] = box_root[3]; w.hiy[0] = box_root[4]; w.hiz[0] = box_root[5];
+        const float pad = node_box_pad(box_root);
+        w.lox[0] = box_root[0] - pad; w.loy[0] = box_root[1] - pad; w.loz[0] = box_root[2] - pad;
+        w.hix[0] = box_root[3] + pad; w.hiy[0] = box_root[4] + pad; w.hiz[0] = box_root[5] + pad;
         w.child[0] = (int32_t)(0x80000000u | (uint32_t)(n - 1));
         w.meta[0] = 1;
     }

@@ -373,14 +373,18 @@ gather_tiled_kernel(const float4 *__restrict__ pos4, const b2rt_photon *__restri
       for (;;) {
         bound = (uint64_t)__float_as_uint(r2_try) << 32;
         count = 0;
-        for (int S = 0; S <= smax; ++S) {
+        // The first round covers the query's coarse cell and its 26 neighbours at once (shells 0 and 1: where almost every
+        // query ends), decoded with constant divisors; from S = 2 on, one shell surface per iteration.
+        for (int S = 1; S <= smax || S == 1; ++S) {
             const int w = 2 * S + 1, n_face = w * w;
-            const int ntask = S == 0 ? 1 : 2 * n_face + (2 * S - 1) * 8 * S;
+            const int ntask = S == 1 ? 27 : 2 * n_face + (2 * S - 1) * 8 * S;
             for (int t0 = 0; t0 < ntask; t0 += 32) {
                 const int t = t0 + lane;
                 bool ok = t < ntask;
                 int ox = 0, oy = 0, oz = 0;
-                if (S > 0 && ok) {
+                if (S == 1) {
+                    ox = t % 3 - 1; oy = (t / 3) % 3 - 1; oz = t / 9 - 1;
+                } else if (ok) {
                     if (t < 2 * n_face) {
                         const int u = t < n_face ? t : t - n_face;
                         oz = t < n_face ? -S : S;

@@ -99,7 +99,7 @@ trace_persistent_kernel(const WideNode *__restrict__ nodes, const PrimRec *__res
                 r.ox = r0.x; r.oy = r0.y; r.oz = r0.z; r.tmin = r0.w;
                 r.dx = r1.x; r.dy = r1.y; r.dz = r1.z;
                 r.ddx = r1.x; r.ddy = r1.y; r.ddz = r1.z;
-                idx = 1.f / r1.x; idy = 1.f / r1.y; idz = 1.f / r1.z;
+                idx = slab_rcp(r1.x); idy = slab_rcp(r1.y); idz = slab_rcp(r1.z);
                 best_t = r1.w; best_prim = 0x7fffffff; best_b1 = 0.f; best_b2 = 0.f;
                 found = false; sp = 0; cur = 0; my = i; active = true;
             }
@@ -246,7 +246,7 @@ trace_spec_kernel(const WideNode *__restrict__ nodes, const PrimRec *__restrict_
                 r.ox = r0.x; r.oy = r0.y; r.oz = r0.z; r.tmin = r0.w;
                 r.dx = r1.x; r.dy = r1.y; r.dz = r1.z;
                 r.ddx = r1.x; r.ddy = r1.y; r.ddz = r1.z;
-                idx = 1.f / r1.x; idy = 1.f / r1.y; idz = 1.f / r1.z;
+                idx = slab_rcp(r1.x); idy = slab_rcp(r1.y); idz = slab_rcp(r1.z);
                 best_t = r1.w; best_prim = 0x7fffffff; best_b1 = 0.f; best_b2 = 0.f;
                 found = false; sp = 0; cur = 0; leaf = NONE; my = i; active = true;
             }

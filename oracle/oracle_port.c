@@ -335,10 +335,15 @@ int port_lbvh_build(int n, const float *box, uint32_t *morton, int32_t *order, i
 #define WI(node, field, k) (*(int32_t *)&W[32 * (size_t)(node) + 4 * (field) + (k)])
 #define W_EMPTY(node, k) do { WF(node,0,k)=inf; WF(node,2,k)=inf; WF(node,4,k)=inf; WF(node,1,k)=ninf; \
         WF(node,3,k)=ninf; WF(node,5,k)=ninf; WI(node,6,k)=CHILD_EMPTY; } while (0)
-#define W_BOX(node, k, b) do { WF(node,0,k)=(b)[0]; WF(node,2,k)=(b)[1]; WF(node,4,k)=(b)[2]; WF(node,1,k)=(b)[3]; \
-        WF(node,3,k)=(b)[4]; WF(node,5,k)=(b)[5]; } while (0)
+    /* absolute margin on every stored child box: 2^-21 * largest |root-box coordinate| (build.cu node_box_pad) */
+    float pad = 0.f;        /* set by W_PAD() once the root box bin_box[0..5] exists */
+#define W_PAD() do { float m_ = 0.f; for (int a_ = 0; a_ < 6; ++a_) m_ = fmaxf(m_, fabsf(bin_box[a_])); \
+        pad = m_ * 4.76837158203125e-07f; } while (0)
+#define W_BOX(node, k, b) do { WF(node,0,k)=(b)[0]-pad; WF(node,2,k)=(b)[1]-pad; WF(node,4,k)=(b)[2]-pad; \
+        WF(node,1,k)=(b)[3]+pad; WF(node,3,k)=(b)[4]+pad; WF(node,5,k)=(b)[5]+pad; } while (0)
     if (n == 1) {
         for (int k = 0; k < 4; ++k) { W_EMPTY(0, k); WI(0, 7, k) = 0; }
+        W_PAD();
         W_BOX(0, 0, bin_box); WI(0, 6, 0) = (int32_t)(0x80000000u | 0u); WI(0, 7, 0) = 1;
         free(range);
         return 1;
@@ -347,6 +352,7 @@ int port_lbvh_build(int n, const float *box, uint32_t *morton, int32_t *order, i
     memset(collapse, 0, (size_t)(n - 1));
     refit_rec(0, n, child, (const int32_t(*)[2])range, box, order, bin_box, cost, collapse);
     free(cost);
+    W_PAD();
     if (collapse[0]) {
         for (int k = 0; k < 4; ++k) { W_EMPTY(0, k); WI(0, 7, k) = 0; }
         W_BOX(0, 0, bin_box); WI(0, 6, 0) = (int32_t)(0x80000000u | (uint32_t)(n - 1)); WI(0, 7, 0) = 1;

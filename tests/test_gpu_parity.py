@@ -252,10 +252,19 @@ def test_axis_parallel_and_degenerate_rays_match_oracle(ctx):
     rays[-n // 4:, 4:7] = two
     rays[5::17, 7] = rays[5::17, 3]                                   # zero-length segment
     rays[7::19, 3] = 5.0; rays[7::19, 7] = 1.0                        # tmin > tmax
+    cls = np.full(n, "axis-parallel, random origin", dtype=object)
+    cls[: n // 3] = "axis-parallel, origin above a vertex"
+    cls[n // 3: n // 2] = "straight down, random origin"
+    cls[-n // 4:] = "one zero component"
+    cls[5::17] = "zero-length segment"
+    cls[7::19] = "tmin > tmax"
     t, prim, b1, b2 = ps.intersect(rays, 8)
     h = ctx.trace_closest(rays)
     assert (prim >= 0).sum() > 500
-    assert np.array_equal(h["prim"], prim) and np.array_equal(bits(h["t"]), bits(t))
+    bad = (h["prim"] != prim) | (bits(h["t"]) != bits(t))
+    report = {c: (int(bad[cls == c].sum()), int((cls == c).sum()), int(((prim >= 0) & (h["prim"] < 0) & (cls == c)).sum()))
+              for c in sorted(set(cls))}
+    assert not bad.any(), "mismatches per class (bad, rays, hits the GPU lost): %s" % report
     assert np.array_equal(ctx.trace_any(rays), ps.occluded(rays, 8))
 
 
