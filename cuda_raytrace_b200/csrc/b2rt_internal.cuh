@@ -93,8 +93,10 @@ struct b2rt_ctx {
     int64_t host_chunk = 1 << 18; // rays per chunk of the host-buffer pipeline (B2RT_HOST_CHUNK)
     int photon_variant = 1;      // 0: one thread per path, 1: resident grid with path regeneration
     int photon_blocks_per_sm = 0;
-    int gather_blocks_per_sm[2] = {0, 0};
-    int gather_variant = 1;      // 0: per-row scan with direct loads, 1: coarse table + TMA-staged tiles
+    int gather_blocks_per_sm[3] = {0, 0, 0};
+    int gather_qt = 8;           // gather variant 2: consecutive queries that share one staged tile (8, 16 or 32)
+    int gather_variant = 2;      // 0: per-row scan with direct loads, 1: coarse table + TMA-staged tiles per warp,
+                                 // 2: one TMA-staged tile shared by a block's 32 consecutive queries (k-nearest)
 
     // host-side staging of the scene (flattened)
     std::vector<float> h_verts;      // xyz

@@ -308,27 +308,82 @@ __device__ __forceinline__ float axis_gap(float q, float lo, float hi, bool open
     return d;
 }
 
-template <bool KNN>
-__global__ void __launch_bounds__(GATHER_WARPS * 32, 6)
-gather_tiled_kernel(const float4 *__restrict__ pos4, const b2rt_photon *__restrict__ photons,
-                    const uint32_t *__restrict__ cell_start, const uint32_t *__restrict__ coarse, Gather2Grid g,
-                    const b2rt_query *__restrict__ queries, int64_t nq, int k, float max_dist2, float n_paths,
-                    float *__restrict__ out_rgb, float *__restrict__ out_r2, int32_t *__restrict__ out_found,
-                    int32_t *__restrict__ idx_out) {
-    __shared__ __align__(128) float4 s_stage[GATHER_WARPS][G2_STAGE];
-    __shared__ uint64_t s_cand[GATHER_WARPS][GATHER_CAP];
-    __shared__ __align__(8) uint64_t s_bar[GATHER_WARPS];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    uint64_t *cand = s_cand[warp];
-    const float4 *stage = s_stage[warp];
-    const uint32_t stage_a = smem_addr(s_stage[warp]), bar = smem_addr(&s_bar[warp]);
-    const uint32_t lt = (1u << lane) - 1u;
-    if (lane == 0) mbar_init(bar, 1);
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    __syncthreads();
-    uint32_t phase = 0;
+struct GatherArgs {
+    const float4 *pos4; const b2rt_photon *photons; const uint32_t *cell_start; const uint32_t *coarse;
+    Gather2Grid g;
+    const b2rt_query *queries; int64_t nq; int k; float max_dist2, n_paths;
+    float *out_rgb, *out_r2; int32_t *out_found, *idx_out;
+};
 
-    for (int64_t q = (int64_t)blockIdx.x * GATHER_WARPS + warp; q < nq; q += (int64_t)gridDim.x * GATHER_WARPS) {
+// final selection, estimator sum and output of one query; cand[0..count) holds every candidate below the bound
+template <bool KNN>
+__device__ __forceinline__ void gather_finish(const GatherArgs &A, int64_t q, f3 nf, f3 kd, uint64_t *cand, int count,
+                                              f3 acc, int found_fr, int lane) {
+    const b2rt_photon *__restrict__ photons = A.photons;
+    const int k = A.k;
+    const float max_dist2 = A.max_dist2, n_paths = A.n_paths;
+    float *__restrict__ out_rgb = A.out_rgb, *__restrict__ out_r2 = A.out_r2;
+    int32_t *__restrict__ out_found = A.out_found, *__restrict__ idx_out = A.idx_out;
+    {
+        if (KNN) {
+            if (count > 0) count = warp_select(cand, count, k, lane);
+            const float md2 = (count == k) ? __uint_as_float((uint32_t)(cand[CI(k - 1)] >> 32)) : max_dist2;
+            for (int j = lane; j < count; j += 32) {
+                const uint64_t key = cand[CI(j)];
+                const uint32_t i = (uint32_t)key;
+                const float d2 = __uint_as_float((uint32_t)(key >> 32));
+                const float4 *pp = reinterpret_cast<const float4 *>(photons + i);
+                const float4 pa = __ldg(pp), pb = __ldg(pp + 1);
+                const f3 wi = oct_decode(__float_as_uint(pa.w));
+                if (dot3(nf, wi) > 0.f) {
+                    const float sk = 1.f - d2 / md2;
+                    const float wgt = 3.f * B2_INV_PI * sk * sk / (n_paths * md2);
+                    acc = acc + mk3(wgt * pb.x, wgt * pb.y, wgt * pb.z);
+                }
+            }
+            if (idx_out)
+                for (int j = lane; j < k; j += 32) idx_out[q * k + j] = j < count ? (int32_t)(uint32_t)cand[CI(j)] : -1;
+            if (lane == 0) {
+                if (out_r2) out_r2[q] = md2;
+                if (out_found) out_found[q] = count;
+            }
+            __syncwarp();
+        } else {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) found_fr += __shfl_xor_sync(0xffffffffu, found_fr, o);
+            if (lane == 0) {
+                if (out_r2) out_r2[q] = max_dist2;
+                if (out_found) out_found[q] = found_fr;
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            acc.x = acc.x + __shfl_xor_sync(0xffffffffu, acc.x, o);
+            acc.y = acc.y + __shfl_xor_sync(0xffffffffu, acc.y, o);
+            acc.z = acc.z + __shfl_xor_sync(0xffffffffu, acc.z, o);
+        }
+        if (lane == 0 && out_rgb) {
+            out_rgb[3 * q + 0] = acc.x * kd.x * B2_INV_PI;
+            out_rgb[3 * q + 1] = acc.y * kd.y * B2_INV_PI;
+            out_rgb[3 * q + 2] = acc.z * kd.z * B2_INV_PI;
+        }
+    }
+}
+
+// one query, one warp: coarse shells, TMA-staged rows, candidate buffer (the scan described above)
+template <bool KNN>
+__device__ __forceinline__ void gather_query_warp(const GatherArgs &A, int64_t q, float r2_first, uint64_t *cand,
+                                                  const float4 *stage, uint32_t stage_a, uint32_t bar, uint32_t &phase,
+                                                  int lane) {
+    const float4 *__restrict__ pos4 = A.pos4;
+    const b2rt_photon *__restrict__ photons = A.photons;
+    const uint32_t *__restrict__ cell_start = A.cell_start, *__restrict__ coarse = A.coarse;
+    const Gather2Grid &g = A.g;
+    const b2rt_query *__restrict__ queries = A.queries;
+    const int k = A.k;
+    const float max_dist2 = A.max_dist2, n_paths = A.n_paths;
+    const uint32_t lt = (1u << lane) - 1u;
+    {
         const float4 *qp = reinterpret_cast<const float4 *>(queries + q);
         const float4 q0 = __ldg(qp), q1 = __ldg(qp + 1), q2 = __ldg(qp + 2);
         const float qa[3] = {q0.x, q0.y, q0.z};
@@ -366,6 +421,7 @@ gather_tiled_kernel(const float4 *__restrict__ pos4, const b2rt_photon *__restri
                 r2_try = fminf(est, max_dist2);
             }
         }
+        if (KNN && r2_first > 0.f) r2_try = fminf(r2_first, max_dist2);     // caller already knows a radius that was too small
         uint64_t bound;
         int count;
         f3 acc = mk3(0.f, 0.f, 0.f);
@@ -531,47 +587,200 @@ gather_tiled_kernel(const float4 *__restrict__ pos4, const b2rt_photon *__restri
         r2_try = fminf(r2_try * 4.f, max_dist2);
       }
 
-        if (KNN) {
-            if (count > 0) count = warp_select(cand, count, k, lane);
-            const float md2 = (count == k) ? __uint_as_float((uint32_t)(cand[CI(k - 1)] >> 32)) : max_dist2;
-            for (int j = lane; j < count; j += 32) {
-                const uint64_t key = cand[CI(j)];
-                const uint32_t i = (uint32_t)key;
-                const float d2 = __uint_as_float((uint32_t)(key >> 32));
-                const float4 *pp = reinterpret_cast<const float4 *>(photons + i);
-                const float4 pa = __ldg(pp), pb = __ldg(pp + 1);
-                const f3 wi = oct_decode(__float_as_uint(pa.w));
-                if (dot3(nf, wi) > 0.f) {
-                    const float sk = 1.f - d2 / md2;
-                    const float wgt = 3.f * B2_INV_PI * sk * sk / (n_paths * md2);
-                    acc = acc + mk3(wgt * pb.x, wgt * pb.y, wgt * pb.z);
+        gather_finish<KNN>(A, q, nf, kd, cand, count, acc, found_fr, lane);
+    }
+}
+
+template <bool KNN>
+__global__ void __launch_bounds__(GATHER_WARPS * 32, 6)
+gather_tiled_kernel(const GatherArgs A) {
+    __shared__ __align__(128) float4 s_stage[GATHER_WARPS][G2_STAGE];
+    __shared__ uint64_t s_cand[GATHER_WARPS][GATHER_CAP];
+    __shared__ __align__(8) uint64_t s_bar[GATHER_WARPS];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t bar = smem_addr(&s_bar[warp]);
+    if (lane == 0) mbar_init(bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    __syncthreads();
+    uint32_t phase = 0;
+    for (int64_t q = (int64_t)blockIdx.x * GATHER_WARPS + warp; q < A.nq; q += (int64_t)gridDim.x * GATHER_WARPS)
+        gather_query_warp<KNN>(A, q, -1.f, s_cand[warp], s_stage[warp], smem_addr(s_stage[warp]), bar, phase, lane);
+}
+
+// ---- block-shared tile variant (default for k-nearest) ---------------------------------------------------------------
+// Queries arrive in pixel order, and neighbouring pixels select almost the same photons (a pixel is ~2 mm on the
+// Cornell walls, the k = 64 radius ~2 cm).  A block therefore takes GB_QT consecutive queries at once:
+//   A. warp 0, one lane per query: first radius from the coarse-cell density, the query's fine-cell box for that radius,
+//      warp-reduced to the union box of the tile;
+//   B. all threads: one (z, y) row of the union box each = one contiguous run of the position array; block prefix sum;
+//   C. every thread issues cp.async.bulk for its runs into ONE shared tile (<= GB_TCAP positions), one block mbarrier;
+//   D. each warp scans the shared tile for its 8 queries (distance test, ballot-compacted candidates, one sort);
+//   E. queries the tile cannot answer - fewer than k photons inside the first radius, a union box with too many rows
+//      or photons (sparse caustic regions, incoherent tiles, caustic hot spots) - fall back to gather_query_warp with
+//      a private slice of the tile as staging buffer.
+// Rows, staging and prefix sums are paid once per 32 queries instead of once per query (they were ~40 % of the
+// per-warp kernel's instructions).  The result set of a query is still the k smallest keys below the final bound.
+constexpr int GB_TCAP = 2048;
+constexpr int GB_ROWS = 2 * GATHER_WARPS * 32;
+static_assert(GATHER_WARPS * G2_STAGE <= GB_TCAP, "fallback staging slices must fit in the shared tile");
+
+template <int GB_QT>
+__global__ void __launch_bounds__(GATHER_WARPS * 32, 5)
+gather_block_kernel(const GatherArgs A) {
+    __shared__ __align__(128) float4 s_tile[GB_TCAP];
+    __shared__ uint64_t s_cand[GATHER_WARPS][GATHER_CAP];
+    __shared__ float4 s_q[GB_QT];
+    __shared__ int s_box[6];
+    __shared__ uint32_t s_wsum[GATHER_WARPS];
+    __shared__ __align__(8) uint64_t s_bar[GATHER_WARPS + 1];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const Gather2Grid &g = A.g;
+    const uint32_t lt = (1u << lane) - 1u;
+    uint64_t *cand = s_cand[warp];
+    const uint32_t wbar = smem_addr(&s_bar[warp]), bbar = smem_addr(&s_bar[GATHER_WARPS]), tile_a = smem_addr(s_tile);
+    if (lane == 0) mbar_init(wbar, 1);
+    if (tid == 0) mbar_init(bbar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    uint32_t wphase = 0, bphase = 0;
+    const int64_t ntiles = (A.nq + GB_QT - 1) / GB_QT;
+
+    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        fence_proxy_async_smem();       // generic reads of the previous tile before this tile's async writes
+        __syncthreads();
+        const int64_t q0 = tile * GB_QT;
+        const int nqt = (int)(A.nq - q0 < GB_QT ? A.nq - q0 : GB_QT);
+        // ---- A: per-query radius and cell box, union over the tile --------------------------------------------------
+        if (warp == 0) {
+            int lo[3] = {0x7fffffff, 0x7fffffff, 0x7fffffff}, hi[3] = {-1, -1, -1};
+            if (lane < nqt) {
+                const float4 a0 = __ldg(reinterpret_cast<const float4 *>(A.queries + q0 + lane));
+                const float pa[3] = {a0.x, a0.y, a0.z};
+                int C[3], cf[3];
+#pragma unroll
+                for (int a = 0; a < 3; ++a) {
+                    cf[a] = min(max((int)floorf((pa[a] - g.lo[a]) * g.inv), 0), g.dims[a] - 1);
+                    C[a] = cf[a] >> G2_SHIFT;
+                }
+                uint32_t n8 = 0;
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    const int o[3] = {c & 1, (c >> 1) & 1, c >> 2};
+                    int P[3];
+                    bool in = true;
+#pragma unroll
+                    for (int a = 0; a < 3; ++a) {
+                        P[a] = C[a] - ((cf[a] & (G2_C - 1)) < G2_C / 2 ? 1 : 0) + o[a];
+                        in = in && P[a] >= 0 && P[a] < g.cdims[a];
+                    }
+                    if (in) n8 += __ldg(A.coarse + ((int64_t)P[2] * g.cdims[1] + P[1]) * g.cdims[0] + P[0]);
+                }
+                float r2_try = A.max_dist2;
+                if (n8 > 0) r2_try = fminf((1.6f * 64.f * B2_INV_PI) * (float)A.k * g.cell * g.cell / (float)n8, A.max_dist2);
+                const float r = sqrtf(r2_try) * 1.0001f + g.slack;
+#pragma unroll
+                for (int a = 0; a < 3; ++a) {
+                    lo[a] = min(max((int)floorf((pa[a] - r - g.lo[a]) * g.inv), 0), g.dims[a] - 1);
+                    hi[a] = min(max((int)floorf((pa[a] + r - g.lo[a]) * g.inv), 0), g.dims[a] - 1);
+                }
+                s_q[lane] = make_float4(pa[0], pa[1], pa[2], r2_try);
+            }
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                lo[a] = __reduce_min_sync(0xffffffffu, lo[a]);
+                hi[a] = __reduce_max_sync(0xffffffffu, hi[a]);
+            }
+            if (lane == 0) { s_box[0] = lo[0]; s_box[1] = lo[1]; s_box[2] = lo[2]; s_box[3] = hi[0]; s_box[4] = hi[1]; s_box[5] = hi[2]; }
+        }
+        __syncthreads();
+        const int x0 = s_box[0], y0 = s_box[1], z0 = s_box[2], x1 = s_box[3], y1 = s_box[4], z1 = s_box[5];
+        const int ny = y1 - y0 + 1, nz = z1 - z0 + 1;
+        const int R = ny * nz;
+        bool tile_ok = R <= GB_ROWS;
+        // ---- B: one row of the union box per thread (two if R > 128), block prefix sum ------------------------------
+        uint32_t rb_[2] = {0, 0}, rn_[2] = {0, 0}, off = 0, T = 0;
+        if (tile_ok) {
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                const int row = tid + j * GATHER_WARPS * 32;
+                if (row < R) {
+                    const int z = z0 + row / ny, y = y0 + row % ny;
+                    const int64_t rb = ((int64_t)z * g.dims[1] + y) * g.dims[0];
+                    const uint32_t b = __ldg(A.cell_start + rb + x0), e = __ldg(A.cell_start + rb + x1 + 1);
+                    rb_[j] = b; rn_[j] = e - b;
                 }
             }
-            if (idx_out)
-                for (int j = lane; j < k; j += 32) idx_out[q * k + j] = j < count ? (int32_t)(uint32_t)cand[CI(j)] : -1;
-            if (lane == 0) {
-                if (out_r2) out_r2[q] = md2;
-                if (out_found) out_found[q] = count;
-            }
-            __syncwarp();
-        } else {
+            const uint32_t mine = rn_[0] + rn_[1];
+            uint32_t inc = mine;
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) found_fr += __shfl_xor_sync(0xffffffffu, found_fr, o);
-            if (lane == 0) {
-                if (out_r2) out_r2[q] = max_dist2;
-                if (out_found) out_found[q] = found_fr;
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t up = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o) inc += up;
+            }
+            if (lane == 31) s_wsum[warp] = inc;
+            __syncthreads();
+            uint32_t wbase = 0;
+#pragma unroll
+            for (int w = 0; w < GATHER_WARPS; ++w) { if (w < warp) wbase += s_wsum[w]; T += s_wsum[w]; }
+            off = wbase + inc - mine;
+            tile_ok = T <= GB_TCAP;
+        }
+        // ---- C: stage every run into the shared tile ---------------------------------------------------------------
+        if (tile_ok && T > 0) {
+            if (tid == 0) mbar_expect_tx(bbar, T * 16u);
+            if (rn_[0]) tma_bulk_g2s(tile_a + off * 16u, A.pos4 + rb_[0], rn_[0] * 16u, bbar);
+            if (rn_[1]) tma_bulk_g2s(tile_a + (off + rn_[0]) * 16u, A.pos4 + rb_[1], rn_[1] * 16u, bbar);
+            mbar_wait(bbar, bphase);
+            bphase ^= 1u;
+        }
+        // ---- D: each warp scans the shared tile for its queries ------------------------------------------------------
+        uint32_t failed = 0;
+        for (int j = 0; j < GB_QT / GATHER_WARPS; ++j) {
+            const int qi = warp + j * GATHER_WARPS;
+            if (qi >= nqt) break;
+            if (!tile_ok) { failed |= 1u << j; continue; }
+            const float4 qv = s_q[qi];
+            uint64_t bound = (uint64_t)__float_as_uint(qv.w) << 32;
+            int count = 0;
+            for (uint32_t i0 = 0; i0 < T; i0 += 32) {
+                const uint32_t i = i0 + lane;
+                bool pass = false;
+                uint64_t key = 0;
+                if (i < T) {
+                    const float4 pa = s_tile[i];
+                    const float dx = pa.x - qv.x, dy = pa.y - qv.y, dz = pa.z - qv.z;
+                    const float d2 = dx * dx + dy * dy + dz * dz;
+                    key = ((uint64_t)__float_as_uint(d2) << 32) | __float_as_uint(pa.w);
+                    pass = key < bound;
+                }
+                const uint32_t m = __ballot_sync(0xffffffffu, pass);
+                if (m) {
+                    if (pass) cand[CI(count + __popc(m & lt))] = key;
+                    count += __popc(m);
+                    __syncwarp();
+                    if (count > GATHER_CAP - 32) {
+                        count = warp_select(cand, count, A.k, lane);
+                        if (count == A.k) bound = cand[CI(A.k - 1)];
+                    }
+                }
+            }
+            if (count >= A.k || qv.w >= A.max_dist2) {
+                const float4 *qp = reinterpret_cast<const float4 *>(A.queries + q0 + qi);
+                const float4 a0 = __ldg(qp), a1 = __ldg(qp + 1), a2 = __ldg(qp + 2);
+                gather_finish<true>(A, q0 + qi, mk3(a0.w, a1.x, a1.y), mk3(a1.z, a1.w, a2.x), cand, count, mk3(0.f, 0.f, 0.f), 0, lane);
+            } else {
+                failed |= 1u << j;
             }
         }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            acc.x = acc.x + __shfl_xor_sync(0xffffffffu, acc.x, o);
-            acc.y = acc.y + __shfl_xor_sync(0xffffffffu, acc.y, o);
-            acc.z = acc.z + __shfl_xor_sync(0xffffffffu, acc.z, o);
-        }
-        if (lane == 0 && out_rgb) {
-            out_rgb[3 * q + 0] = acc.x * kd.x * B2_INV_PI;
-            out_rgb[3 * q + 1] = acc.y * kd.y * B2_INV_PI;
-            out_rgb[3 * q + 2] = acc.z * kd.z * B2_INV_PI;
+        // ---- E: fall-backs, after every warp is done with the shared tile ---------------------------------------------
+        fence_proxy_async_smem();       // this thread's reads of the shared tile before the fall-backs' async writes
+        if (__syncthreads_or(failed != 0u)) {
+            for (int j = 0; j < GB_QT / GATHER_WARPS; ++j) {
+                if (!((failed >> j) & 1u)) continue;
+                const int qi = warp + j * GATHER_WARPS;
+                const float r2_next = tile_ok ? s_q[qi].w * 4.f : -1.f;
+                gather_query_warp<true>(A, q0 + qi, r2_next, cand, s_tile + warp * G2_STAGE,
+                                        tile_a + (uint32_t)(warp * G2_STAGE) * 16u, wbar, wphase, lane);
+            }
         }
     }
 }
@@ -595,7 +804,7 @@ int b2rt_gather_impl(b2rt_ctx *ctx, int map, int64_t nq, const b2rt_query *d_que
     int64_t cap = (int64_t)ctx->sm_count * 16;
     if (blocks > cap) blocks = cap;
     float npaths = (float)m.n_paths;    // pbrt: int nPaths * float maxDist2
-    if (ctx->gather_variant == 1) {
+    if (ctx->gather_variant >= 1) {
         Gather2Grid g2;
         for (int a = 0; a < 3; ++a) { g2.lo[a] = g.lo[a]; g2.dims[a] = g.dims[a]; g2.cdims[a] = m.cdims[a]; }
         g2.cell = g.cell; g2.inv = g.inv; g2.slack = g.slack;
@@ -608,14 +817,24 @@ int b2rt_gather_impl(b2rt_ctx *ctx, int map, int64_t nq, const b2rt_query *d_que
         cap = (int64_t)ctx->sm_count * per_sm;
         blocks = (nq + GATHER_WARPS - 1) / GATHER_WARPS;
         if (blocks > cap) blocks = cap;
-        if (k > 0)
-            gather_tiled_kernel<true><<<(unsigned)blocks, GATHER_WARPS * 32, 0, ctx->stream>>>(
-                m.pos4.as<float4>(), m.sorted.as<b2rt_photon>(), m.cell_start.as<uint32_t>(), m.coarse.as<uint32_t>(), g2,
-                d_queries, nq, k, max_dist2, npaths, d_rgb, d_r2, d_found, d_idx);
-        else
-            gather_tiled_kernel<false><<<(unsigned)blocks, GATHER_WARPS * 32, 0, ctx->stream>>>(
-                m.pos4.as<float4>(), m.sorted.as<b2rt_photon>(), m.cell_start.as<uint32_t>(), m.coarse.as<uint32_t>(), g2,
-                d_queries, nq, k, max_dist2, npaths, d_rgb, d_r2, d_found, d_idx);
+        GatherArgs A;
+        A.pos4 = m.pos4.as<float4>(); A.photons = m.sorted.as<b2rt_photon>(); A.cell_start = m.cell_start.as<uint32_t>();
+        A.coarse = m.coarse.as<uint32_t>(); A.g = g2; A.queries = d_queries; A.nq = nq; A.k = k; A.max_dist2 = max_dist2;
+        A.n_paths = npaths; A.out_rgb = d_rgb; A.out_r2 = d_r2; A.out_found = d_found; A.idx_out = d_idx;
+        if (k > 0 && ctx->gather_variant == 2) {
+            const int qt = ctx->gather_qt == 32 ? 32 : (ctx->gather_qt == 16 ? 16 : 8);
+            int &bsm = ctx->gather_blocks_per_sm[2];
+            if (bsm == 0) {
+                B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bsm, gather_block_kernel<8>, GATHER_WARPS * 32, 0));
+                if (bsm < 1) bsm = 1;
+            }
+            int64_t nb = (nq + qt - 1) / qt;
+            if (nb > (int64_t)ctx->sm_count * bsm) nb = (int64_t)ctx->sm_count * bsm;
+            if (qt == 32) gather_block_kernel<32><<<(unsigned)nb, GATHER_WARPS * 32, 0, ctx->stream>>>(A);
+            else if (qt == 16) gather_block_kernel<16><<<(unsigned)nb, GATHER_WARPS * 32, 0, ctx->stream>>>(A);
+            else gather_block_kernel<8><<<(unsigned)nb, GATHER_WARPS * 32, 0, ctx->stream>>>(A);
+        } else if (k > 0) gather_tiled_kernel<true><<<(unsigned)blocks, GATHER_WARPS * 32, 0, ctx->stream>>>(A);
+        else gather_tiled_kernel<false><<<(unsigned)blocks, GATHER_WARPS * 32, 0, ctx->stream>>>(A);
         B2RT_LAUNCH_CHECK(ctx);
         return B2RT_OK;
     }

@@ -78,22 +78,32 @@ radix_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__res
     const int64_t base = tile0 + warp * (32 * SORT_ITEMS);
     const int tile_n = (int)(n - tile0 < SORT_TILE ? n - tile0 : SORT_TILE);
 
-    uint32_t k[SORT_ITEMS], rank[SORT_ITEMS];
+    // Three loops instead of one: the 16 loads and the 16 match.any are independent of each other and pipeline; only
+    // the counter updates are ordered (item r before item r+1 of the same digit: that order is the sort's stability).
+    uint32_t k[SORT_ITEMS], rank[SORT_ITEMS], peers[SORT_ITEMS];
 #pragma unroll
     for (int r = 0; r < SORT_ITEMS; ++r) {
         int64_t i = base + r * 32 + lane;
-        bool ok = i < n;
-        k[r] = ok ? keys_in[i] : 0u;
-        uint32_t d = ok ? ((k[r] >> shift) & 0xff) : 0x100u;
-        uint32_t peers = __match_any_sync(0xffffffffu, d);
-        int leader = __ffs(peers) - 1;
+        k[r] = i < n ? keys_in[i] : 0u;
+    }
+#pragma unroll
+    for (int r = 0; r < SORT_ITEMS; ++r) {
+        const bool ok = base + r * 32 + lane < n;
+        const uint32_t d = ok ? ((k[r] >> shift) & 0xff) : 0x100u;
+        peers[r] = __match_any_sync(0xffffffffu, d);
+    }
+#pragma unroll
+    for (int r = 0; r < SORT_ITEMS; ++r) {
+        const bool ok = base + r * 32 + lane < n;
+        const uint32_t d = (k[r] >> shift) & 0xff;
+        const int leader = __ffs(peers[r]) - 1;
         uint32_t before = 0;
         if (lane == leader && ok) {
             before = sh[warp][d];
-            sh[warp][d] = before + __popc(peers);
+            sh[warp][d] = before + __popc(peers[r]);
         }
         before = __shfl_sync(0xffffffffu, before, leader);
-        rank[r] = before + __popc(peers & lt);
+        rank[r] = before + __popc(peers[r] & lt);
         __syncwarp();
     }
     __syncthreads();

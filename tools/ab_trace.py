@@ -48,6 +48,6 @@ for name, anyhit in (("primary", False), ("shadow", True), ("incoherent", False)
     import hashlib
     buf = d_occ[:n] if anyhit else d_hits[:n]
     out.append("sha " + hashlib.sha256(buf.cpu().numpy().tobytes()).hexdigest()[:12])
-print("variant=%s refill=%s tris=%d | %s" % (os.environ.get("B2RT_TRACE_VARIANT", "0"), os.environ.get("B2RT_TRACE_REFILL", "0"),
+print("variant=%s refill=%s tris=%d | %s" % (os.environ.get("B2RT_TRACE_VARIANT", "2 (default)"), os.environ.get("B2RT_TRACE_REFILL", "0"),
                                             tris, " | ".join(out)), flush=True)
 ctx.close()
