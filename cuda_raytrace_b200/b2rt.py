@@ -36,7 +36,7 @@ SYMBOLS = [
     "b2rt_create", "b2rt_destroy", "b2rt_last_error", "b2rt_device_count", "b2rt_add_mesh", "b2rt_add_sphere",
     "b2rt_add_disk", "b2rt_add_material", "b2rt_add_light", "b2rt_clear_scene", "b2rt_build_accel",
     "b2rt_accel_info_get", "b2rt_accel_download", "b2rt_trace_closest", "b2rt_trace_any", "b2rt_sort_pairs",
-    "b2rt_sync", "b2rt_timer_start", "b2rt_timer_stop", "b2rt_launch_count", "b2rt_stream",
+    "b2rt_sync", "b2rt_timer_start", "b2rt_timer_stop", "b2rt_launch_count", "b2rt_stream", "b2rt_host_alloc", "b2rt_host_free",
 ]
 
 _lib = None
@@ -76,6 +76,10 @@ def load():
     lib.b2rt_launch_count.argtypes = [vp, C.POINTER(i64), C.c_int]
     lib.b2rt_stream.argtypes = [vp]
     lib.b2rt_stream.restype = vp
+    lib.b2rt_host_alloc.argtypes = [vp, i64]
+    lib.b2rt_host_alloc.restype = vp
+    lib.b2rt_host_free.argtypes = [vp, vp]
+    lib.b2rt_host_free.restype = None
     _lib = lib
     return lib
 
@@ -104,8 +108,25 @@ class Context:
 
     def close(self):
         if getattr(self, "h", None):
+            for ptr in getattr(self, "_pinned", []):
+                self.lib.b2rt_host_free(self.h, ptr)
+            self._pinned = []
             self.lib.b2rt_destroy(self.h)
             self.h = None
+
+    def pinned_empty(self, shape, dtype=np.float32):
+        """numpy array in page-locked host memory (b2rt_host_alloc), owned by the context and valid until close():
+        the buffer to hand to the host-pointer calls (`out=` of render_frame) so the copies run at PCIe speed."""
+        dtype = np.dtype(dtype)
+        n = int(np.prod(shape)) * dtype.itemsize
+        ptr = self.lib.b2rt_host_alloc(self.h, max(n, 1))
+        if not ptr:
+            raise B2rtError(-2, self.lib.b2rt_last_error(self.h).decode())
+        if not hasattr(self, "_pinned"):
+            self._pinned = []
+        self._pinned.append(ptr)
+        buf = (C.c_char * max(n, 1)).from_address(ptr)
+        return np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
 
     __del__ = close
 
@@ -395,11 +416,15 @@ def pbrt_camera(eye, look, up, fov, xres, yres):
 
 
 def _render_frame(self, cam, spp=1, max_specular_depth=5, nused=50, max_dist=0.1, caustic=True, indirect=True,
-                  direct=True, window=None):
+                  direct=True, window=None, out=None):
+    """out: optional (y1-y0, x1-x0, 3) float32 array to receive the image (e.g. from pinned_empty); default a new array."""
     x0, x1, y0, y1 = window if window else (0, cam.xres, 0, cam.yres)
     fp = FrameParams(spp, max_specular_depth, nused, float(np.float32(max_dist) * np.float32(max_dist)), int(caustic),
                      int(indirect), int(direct), x0, x1, y0, y1)
-    out = np.zeros((y1 - y0, x1 - x0, 3), np.float32)
+    if out is None:
+        out = np.zeros((y1 - y0, x1 - x0, 3), np.float32)
+    elif out.shape != (y1 - y0, x1 - x0, 3) or out.dtype != np.float32 or not out.flags["C_CONTIGUOUS"]:
+        raise ValueError("render_frame: out must be a C-contiguous float32 array of shape (y1-y0, x1-x0, 3)")
     self.lib.b2rt_render_frame.argtypes = [C.c_void_p, C.POINTER(Camera), C.POINTER(FrameParams), C.c_void_p, C.c_int]
     self._ck(self.lib.b2rt_render_frame(self.h, C.byref(cam), C.byref(fp), _ptr(out), HOST))
     return out

@@ -310,6 +310,21 @@ int b2rt_sort_pairs(b2rt_ctx *ctx, int64_t n, uint32_t *keys, uint32_t *vals, in
     return B2RT_OK;
 }
 
+void *b2rt_host_alloc(b2rt_ctx *ctx, int64_t bytes) {
+    if (!ctx || bytes <= 0) return nullptr;
+    void *p = nullptr;
+    if (cudaSetDevice(ctx->device) != cudaSuccess || cudaHostAlloc(&p, (size_t)bytes, cudaHostAllocPortable) != cudaSuccess) {
+        ctx->err = std::string("host_alloc: ") + cudaGetErrorString(cudaGetLastError());
+        return nullptr;
+    }
+    return p;
+}
+
+void b2rt_host_free(b2rt_ctx *ctx, void *p) {
+    (void)ctx;
+    if (p) cudaFreeHost(p);
+}
+
 int b2rt_sync(b2rt_ctx *ctx) {
     if (!ctx) return B2RT_E_ARG;
     B2RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));

@@ -177,6 +177,13 @@ int b2rt_render_frame(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_pa
  * stable LSD sort of (key32,value32) pairs on `key_bits` low bits; device pointers only. */
 int b2rt_sort_pairs(b2rt_ctx *ctx, int64_t n, uint32_t *keys, uint32_t *vals, int key_bits);
 
+/* ---- pinned host buffers ---------------------------------------------------------------------- */
+/* Page-locked host memory for the B2RT_HOST calls (rays in, hits / images out): with pageable memory the driver
+ * stages every copy and the chunked upload / trace / download pipeline of b2rt_trace_* cannot overlap.  The reference
+ * maps its output buffers instead (photonmappingrenderer.cpp:247-251, bOutput->map()).  Returns NULL on failure. */
+void *b2rt_host_alloc(b2rt_ctx *ctx, int64_t bytes);
+void  b2rt_host_free(b2rt_ctx *ctx, void *p);
+
 /* ---- timing / stream ----------------------------------------------------------------------- */
 int b2rt_sync(b2rt_ctx *ctx);
 int b2rt_timer_start(b2rt_ctx *ctx);            /* cudaEventRecord on the context stream */

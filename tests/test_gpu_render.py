@@ -40,6 +40,22 @@ def test_frame_is_deterministic_and_band_tiling_is_bit_identical(rctx):
     assert np.array_equal(win.view(np.uint32), full[7:33, 10:50].view(np.uint32))
 
 
+def test_pinned_output_buffer_and_device_output_equal_default(rctx):
+    """b2rt_host_alloc buffers as `out=` and the B2RT_DEVICE output path give the bytes of the default call."""
+    import torch
+    cam = b2rt.pbrt_camera(EYE, LOOK, UP, FOV, 80, 56)
+    kw = dict(spp=2, nused=30, max_dist=0.3)
+    ref = rctx.render_frame(cam, **kw)
+    pin = rctx.pinned_empty((56, 80, 3))
+    got = rctx.render_frame(cam, out=pin, **kw)
+    assert got is pin and np.array_equal(pin.view(np.uint32), ref.view(np.uint32))
+    with pytest.raises(ValueError):
+        rctx.render_frame(cam, out=np.zeros((5, 5, 3), np.float32), **kw)
+    dev = torch.zeros((20, 80, 3), dtype=torch.float32, device="cuda")
+    rctx.render_frame_device(cam, dev.data_ptr(), window=(0, 80, 10, 30), **kw)
+    assert np.array_equal(dev.cpu().numpy().view(np.uint32), ref[10:30].view(np.uint32))
+
+
 def test_terms_add_up(rctx):
     cam = b2rt.pbrt_camera(EYE, LOOK, UP, FOV, 48, 48)
     kw = dict(spp=2, nused=20, max_dist=0.2)

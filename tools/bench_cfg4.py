@@ -35,13 +35,14 @@ info = ctx.build_accel()
 cam = b2rt.pbrt_camera((0, 1.2, 2.5), (0, 0, 0), (0, 1, 0), 45, xres, yres)
 kw = dict(spp=spp, caustic=False, indirect=False, direct=True)
 
+frame_out = ctx.pinned_empty((yres, xres, 3))
 times = []
 img = None
 for rep in range(4):
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize(); ctx.sync(); t0 = time.perf_counter()
-    img = M.render_sharded(ctx, cam, **kw) if world > 1 else ctx.render_frame(cam, **kw)
+    img = M.render_sharded(ctx, cam, **kw) if world > 1 else ctx.render_frame(cam, out=frame_out, **kw)
     torch.cuda.synchronize(); ctx.sync(); t1 = time.perf_counter()
     tt = torch.tensor([t1 - t0], dtype=torch.float64, device="cuda")
     if world > 1:

@@ -28,6 +28,7 @@ S.fill_scene(ctx, S.cornell_scene(spheres=True, wide=1.78))
 ctx.build_accel()
 cam = b2rt.pbrt_camera((0, 1, 3.4), (0, 1, 0), (0, 1, 0), 40, 1920, 1080)
 
+frame_out = ctx.pinned_empty((1080, 1920, 3))
 
 def sync():
     ctx.sync()
@@ -66,7 +67,7 @@ for n_paths in sweep:
         if world > 1:
             M.render_sharded(ctx, cam, spp=1, nused=64, max_dist=0.1)
         else:
-            ctx.render_frame(cam, spp=1, nused=64, max_dist=0.1)
+            ctx.render_frame(cam, spp=1, nused=64, max_dist=0.1, out=frame_out)
         sync(); t4 = time.perf_counter()
         tt = torch.tensor([t1 - t0, t2 - t1, t3 - t2, t4 - t3, t4 - t0], dtype=torch.float64, device="cuda")
         if world > 1:

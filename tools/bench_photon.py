@@ -20,13 +20,14 @@ with b2rt.Context(0, seed=3) as ctx:
     S.fill_scene(ctx, desc)
     ctx.build_accel()
     cam = b2rt.pbrt_camera((0, 1, 3.4), (0, 1, 0), (0, 1, 0), 40, xres, yres)
+    frame_out = ctx.pinned_empty((yres, xres, 3))
     for rep in range(reps):
         ctx.sync(); t0 = time.perf_counter()
         (pc, pi), (sc, si) = ctx.photons_shoot(nc, ni, batch_paths=4_000_000)
         ctx.sync(); t1 = time.perf_counter()
         g0 = ctx.grid_build(0); g1 = ctx.grid_build(1)
         ctx.sync(); t2 = time.perf_counter()
-        img = ctx.render_frame(cam, spp=1, nused=k, max_dist=0.1)
+        img = ctx.render_frame(cam, spp=1, nused=k, max_dist=0.1, out=frame_out)
         ctx.sync(); t3 = time.perf_counter()
         imgd = ctx.render_frame(cam, spp=1, caustic=False, indirect=False)
         ctx.sync(); t4 = time.perf_counter()
