@@ -103,6 +103,107 @@ __device__ __forceinline__ int warp_select(uint64_t *cand, int count, int k, int
     return count < k ? count : k;
 }
 
+// Threshold selection: keep the k smallest keys of cand[0..count), count > k, IN BUFFER ORDER (no sort).
+// The d2 word T of the k-th smallest key is bracketed in the bit domain: a probe t costs one compare per held key and
+// one warp-wide REDUX; as soon as a probe has exactly k - 1 (or k) keys below it, T is the smallest key >= t (the
+// largest < t).  Probes alternate between interpolation on the counts (photons on a surface: the count grows linearly
+// in d2) and the midpoint of the bracket (bounds the worst case at 64 probes); typically 3-6 probes.  The first version
+// bisected bit by bit: ~27 dependent probes, slower than the sort network it replaced.  Ties in d2 at the threshold
+// are resolved by the index word (rare), and the survivors are ballot-compacted to the front of the buffer (exactly k
+// of them).  Returns the largest kept key.  Element e lives in lane e % 32, register e / 32 (conflict-free with the
+// slot swizzle).
+template <int PL>
+__device__ __noinline__ uint64_t warp_keep_k(uint64_t *cand, int count, int k, int lane) {
+    const uint32_t FULL = 0xffffffffu, lt = (1u << lane) - 1u;
+    uint32_t d[PL], dmax = 0u;
+#pragma unroll
+    for (int j = 0; j < PL; ++j) {
+        const int e = j * 32 + lane;
+        d[j] = FULL;
+        if (e < count) { d[j] = (uint32_t)(cand[CI(e)] >> 32); dmax = max(dmax, d[j]); }
+    }
+    // invariant: #(d < lo) = clo <= k - 1 and #(d < hi) = chi >= k, so lo <= T < hi
+    uint32_t lo = 0u, hi = __reduce_max_sync(FULL, dmax) + 1u, clo = 0u, chi = (uint32_t)count, T;
+    for (int it = 0;; ++it) {
+        if (hi - lo <= 1u) { T = lo; break; }
+        uint32_t t = lo + ((hi - lo) >> 1);
+        if (!(it & 1)) {
+            const float flo = __uint_as_float(lo), fhi = __uint_as_float(hi);
+            const float f = flo + (fhi - flo) * (((float)(k - (int)clo) - 0.5f) / (float)(chi - clo));
+            t = min(max(__float_as_uint(f), lo + 1u), hi - 1u);
+        }
+        uint32_t c = 0;
+#pragma unroll
+        for (int j = 0; j < PL; ++j) c += d[j] < t ? 1u : 0u;
+        c = __reduce_add_sync(FULL, c);
+        if ((int)c == k - 1) {            // T = the smallest key at or above the probe
+            uint32_t m = FULL;
+#pragma unroll
+            for (int j = 0; j < PL; ++j) m = min(m, d[j] >= t ? d[j] : FULL);
+            T = __reduce_min_sync(FULL, m);
+            break;
+        }
+        if ((int)c == k) {                // T = the largest key below the probe
+            uint32_t m = 0u;
+#pragma unroll
+            for (int j = 0; j < PL; ++j) m = max(m, d[j] < t ? d[j] : 0u);
+            T = __reduce_max_sync(FULL, m);
+            break;
+        }
+        if ((int)c < k) { lo = t; clo = c; } else { hi = t; chi = c; }
+    }
+    uint32_t c2 = 0, mx = 0;
+#pragma unroll
+    for (int j = 0; j < PL; ++j) {
+        c2 += (d[j] < T ? 1u : 0u) + (d[j] == T ? 0x10000u : 0u);
+        if (d[j] == T) mx = max(mx, (uint32_t)cand[CI(j * 32 + lane)]);
+    }
+    c2 = __reduce_add_sync(FULL, c2);
+    const int need = k - (int)(c2 & 0xffffu), ce = (int)(c2 >> 16);      // 1 <= need <= ce
+    uint32_t I;
+    if (ce == need) {
+        I = __reduce_max_sync(FULL, mx);
+    } else {                              // more keys tie at the threshold than fit: the `need` smallest indices
+        I = 0u;
+        for (uint32_t bit = 0x80000000u; bit; bit >>= 1) {
+            const uint32_t t = I | bit;
+            uint32_t c = 0;
+#pragma unroll
+            for (int j = 0; j < PL; ++j)
+                if (d[j] == T) c += (uint32_t)cand[CI(j * 32 + lane)] < t ? 1u : 0u;
+            c = __reduce_add_sync(FULL, c);
+            if ((int)c < need) I = t;
+        }
+    }
+    const uint64_t kth = ((uint64_t)T << 32) | I;
+    int out = 0;
+#pragma unroll
+    for (int j = 0; j < PL; ++j) {        // writes land at or before the slots this round has already read
+        const int e = j * 32 + lane;
+        const uint64_t key = e < count ? cand[CI(e)] : 0xffffffffffffffffull;
+        const bool keep = key <= kth;
+        const uint32_t m = __ballot_sync(FULL, keep);
+        if (keep) cand[CI(out + __popc(m & lt))] = key;
+        out += __popc(m);
+    }
+    __syncwarp();
+    return kth;
+}
+__device__ __forceinline__ uint64_t warp_keep(uint64_t *cand, int count, int k, int lane) {
+    if (count <= 64) return warp_keep_k<2>(cand, count, k, lane);
+    if (count <= 128) return warp_keep_k<4>(cand, count, k, lane);
+    return warp_keep_k<GATHER_PER_LANE>(cand, count, k, lane);
+}
+// reorder cand[0..count) by ascending photon index (the summation order of the estimator); used where the candidates
+// were not collected in cell order
+__device__ __forceinline__ void warp_sort_by_index(uint64_t *cand, int count, int lane) {
+    for (int e = lane; e < count; e += 32) { const uint64_t v = cand[CI(e)]; cand[CI(e)] = (v << 32) | (v >> 32); }
+    __syncwarp();
+    warp_select(cand, count, count, lane);
+    for (int e = lane; e < count; e += 32) { const uint64_t v = cand[CI(e)]; cand[CI(e)] = (v << 32) | (v >> 32); }
+    __syncwarp();
+}
+
 __device__ __forceinline__ f3 oct_decode(uint32_t w) {
     float x = (float)(int)(int16_t)(w & 0xffffu) / 32767.f, y = (float)(int)(int16_t)(w >> 16) / 32767.f;
     float z = 1.f - fabsf(x) - fabsf(y);
@@ -213,6 +314,10 @@ gather_kernel(const b2rt_photon *__restrict__ photons, const uint32_t *__restric
         if (KNN) {
             count = warp_select(cand, count, k, lane);
             const float md2 = (count == k) ? __uint_as_float((uint32_t)(cand[CI(k - 1)] >> 32)) : max_dist2;
+            if (idx_out)
+                for (int j = lane; j < k; j += 32) idx_out[q * k + j] = j < count ? (int32_t)(uint32_t)cand[CI(j)] : -1;
+            __syncwarp();
+            warp_sort_by_index(cand, count, lane);
             for (int j = lane; j < count; j += 32) {
                 uint64_t key = cand[CI(j)];
                 uint32_t i = (uint32_t)key;
@@ -226,8 +331,6 @@ gather_kernel(const b2rt_photon *__restrict__ photons, const uint32_t *__restric
                     acc = acc + mk3(w * pb.x, w * pb.y, w * pb.z);
                 }
             }
-            if (idx_out)
-                for (int j = lane; j < k; j += 32) idx_out[q * k + j] = j < count ? (int32_t)(uint32_t)cand[CI(j)] : -1;
             if (lane == 0) {
                 if (out_r2) out_r2[q] = md2;
                 if (out_found) out_found[q] = count;
@@ -316,9 +419,10 @@ struct GatherArgs {
 };
 
 // final selection, estimator sum and output of one query; cand[0..count) holds every candidate below the bound
+// `ordered`: the buffer is in ascending photon index (candidates collected in cell order)
 template <bool KNN>
 __device__ __forceinline__ void gather_finish(const GatherArgs &A, int64_t q, f3 nf, f3 kd, uint64_t *cand, int count,
-                                              f3 acc, int found_fr, int lane) {
+                                              f3 acc, int found_fr, int lane, bool ordered) {
     const b2rt_photon *__restrict__ photons = A.photons;
     const int k = A.k;
     const float max_dist2 = A.max_dist2, n_paths = A.n_paths;
@@ -326,8 +430,22 @@ __device__ __forceinline__ void gather_finish(const GatherArgs &A, int64_t q, f3
     int32_t *__restrict__ out_found = A.out_found, *__restrict__ idx_out = A.idx_out;
     {
         if (KNN) {
-            if (count > 0) count = warp_select(cand, count, k, lane);
-            const float md2 = (count == k) ? __uint_as_float((uint32_t)(cand[CI(k - 1)] >> 32)) : max_dist2;
+            float md2 = max_dist2;
+            if (idx_out) {                               // parity hook: the set ascending by (d2, index)
+                if (count > 0) count = warp_select(cand, count, k, lane);
+                if (count == k) md2 = __uint_as_float((uint32_t)(cand[CI(k - 1)] >> 32));
+                for (int j = lane; j < k; j += 32) idx_out[q * k + j] = j < count ? (int32_t)(uint32_t)cand[CI(j)] : -1;
+                __syncwarp();
+                ordered = false;
+            } else if (count > k) {
+                md2 = __uint_as_float((uint32_t)(warp_keep(cand, count, k, lane) >> 32));
+                count = k;
+            } else if (count == k) {
+                uint32_t mx = 0u;
+                for (int j = lane; j < count; j += 32) mx = max(mx, (uint32_t)(cand[CI(j)] >> 32));
+                md2 = __uint_as_float(__reduce_max_sync(0xffffffffu, mx));
+            }
+            if (!ordered && count > 1) warp_sort_by_index(cand, count, lane);
             for (int j = lane; j < count; j += 32) {
                 const uint64_t key = cand[CI(j)];
                 const uint32_t i = (uint32_t)key;
@@ -341,8 +459,6 @@ __device__ __forceinline__ void gather_finish(const GatherArgs &A, int64_t q, f3
                     acc = acc + mk3(wgt * pb.x, wgt * pb.y, wgt * pb.z);
                 }
             }
-            if (idx_out)
-                for (int j = lane; j < k; j += 32) idx_out[q * k + j] = j < count ? (int32_t)(uint32_t)cand[CI(j)] : -1;
             if (lane == 0) {
                 if (out_r2) out_r2[q] = md2;
                 if (out_found) out_found[q] = count;
@@ -540,10 +656,7 @@ __device__ __forceinline__ void gather_query_warp(const GatherArgs &A, int64_t q
                                     if (pass) cand[CI(count + __popc(m & lt))] = key;
                                     count += __popc(m);
                                     __syncwarp();
-                                    if (count > GATHER_CAP - 32) {
-                                        count = warp_select(cand, count, k, lane);
-                                        if (count == k) bound = cand[CI(k - 1)];
-                                    }
+                                    if (count > GATHER_CAP - 32) { bound = warp_keep(cand, count, k, lane); count = k; }
                                 }
                             } else if (pass) {
                                 const float d2 = __uint_as_float((uint32_t)(key >> 32));
@@ -567,10 +680,7 @@ __device__ __forceinline__ void gather_query_warp(const GatherArgs &A, int64_t q
             // The first radius already comes from the local density, so the bound is only re-tightened between shells
             // when the buffer is more than half full (keeps later sorts on the small networks); otherwise the single
             // sort at the end is the only one a query pays for.
-            if (KNN && count > k && count > GATHER_CAP / 2) {
-                count = warp_select(cand, count, k, lane);
-                if (count == k) bound = cand[CI(k - 1)];
-            }
+            if (KNN && count > k && count > GATHER_CAP / 2) { bound = warp_keep(cand, count, k, lane); count = k; }
             float dmin = INFINITY;
 #pragma unroll
             for (int a = 0; a < 3; ++a) {
@@ -587,7 +697,7 @@ __device__ __forceinline__ void gather_query_warp(const GatherArgs &A, int64_t q
         r2_try = fminf(r2_try * 4.f, max_dist2);
       }
 
-        gather_finish<KNN>(A, q, nf, kd, cand, count, acc, found_fr, lane);
+        gather_finish<KNN>(A, q, nf, kd, cand, count, acc, found_fr, lane, false);   // shells are not in cell order
     }
 }
 
@@ -757,16 +867,14 @@ gather_block_kernel(const GatherArgs A) {
                     if (pass) cand[CI(count + __popc(m & lt))] = key;
                     count += __popc(m);
                     __syncwarp();
-                    if (count > GATHER_CAP - 32) {
-                        count = warp_select(cand, count, A.k, lane);
-                        if (count == A.k) bound = cand[CI(A.k - 1)];
-                    }
+                    if (count > GATHER_CAP - 32) { bound = warp_keep(cand, count, A.k, lane); count = A.k; }   // keeps cell order
                 }
             }
             if (count >= A.k || qv.w >= A.max_dist2) {
                 const float4 *qp = reinterpret_cast<const float4 *>(A.queries + q0 + qi);
                 const float4 a0 = __ldg(qp), a1 = __ldg(qp + 1), a2 = __ldg(qp + 2);
-                gather_finish<true>(A, q0 + qi, mk3(a0.w, a1.x, a1.y), mk3(a1.z, a1.w, a2.x), cand, count, mk3(0.f, 0.f, 0.f), 0, lane);
+                gather_finish<true>(A, q0 + qi, mk3(a0.w, a1.x, a1.y), mk3(a1.z, a1.w, a2.x), cand, count, mk3(0.f, 0.f, 0.f), 0, lane,
+                                    R <= GATHER_WARPS * 32);     // one row per thread: the tile is in ascending photon index
             } else {
                 failed |= 1u << j;
             }

@@ -420,9 +420,14 @@ void port_grid_build(int64_t n, const port_photon *ph, float cell_size, float ta
     free(cur); free(k0);
 }
 
-/* ---- radiance estimate: brute-force k nearest by (d2, index) + LPhoton (photonmap.cpp:207-260), diffuse surface ---- */
+/* ---- radiance estimate: brute-force k nearest by (d2, index) + LPhoton (photonmap.cpp:207-260), diffuse surface;
+ * the sum runs over the selected set in ascending photon index ---- */
 static int cmp_u64(const void *a, const void *b) {
     uint64_t x = *(const uint64_t *)a, y = *(const uint64_t *)b;
+    return x < y ? -1 : (x > y ? 1 : 0);
+}
+static int cmp_idx(const void *a, const void *b) {
+    uint32_t x = (uint32_t)*(const uint64_t *)a, y = (uint32_t)*(const uint64_t *)b;
     return x < y ? -1 : (x > y ? 1 : 0);
 }
 void port_gather(int64_t n, const port_photon *sorted, int64_t n_paths, int64_t nq, const float *queries, int k,
@@ -445,7 +450,11 @@ void port_gather(int64_t n, const port_photon *sorted, int64_t n_paths, int64_t 
             qsort(keys, (size_t)m, 8, cmp_u64);
             if (cnt > k) cnt = k;
             if (cnt == k) { uint32_t b = (uint32_t)(keys[k - 1] >> 32); memcpy(&md2, &b, 4); }
-            /* same summation order as the warp: 32 strided partial sums, then an xor butterfly */
+            if (idx_out) for (int j = 0; j < k; ++j) idx_out[q * k + j] = j < cnt ? (int32_t)(uint32_t)keys[j] : -1;
+            /* summation order of the device kernels: the selected set in ascending photon index (= the order the
+             * grid cells store them, so a kernel that selects by threshold needs no sort), 32 strided partial sums,
+             * then an xor butterfly */
+            qsort(keys, (size_t)cnt, 8, cmp_idx);
             v3 part[32];
             for (int l = 0; l < 32; ++l) {
                 part[l] = V(0, 0, 0);
@@ -466,7 +475,6 @@ void port_gather(int64_t n, const port_photon *sorted, int64_t n_paths, int64_t 
                 memcpy(part, nx, sizeof(part));
             }
             acc = part[0];
-            if (idx_out) for (int j = 0; j < k; ++j) idx_out[q * k + j] = j < cnt ? (int32_t)(uint32_t)keys[j] : -1;
         } else {
             double ax = 0, ay = 0, az = 0;    /* fixed radius: order-free reference sum in double */
             for (int64_t j = 0; j < m; ++j) {
