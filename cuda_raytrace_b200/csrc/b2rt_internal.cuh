@@ -94,6 +94,8 @@ struct b2rt_ctx {
     int photon_variant = 1;      // 0: one thread per path, 1: resident grid with path regeneration
     int photon_blocks_per_sm = 0;
     int gather_blocks_per_sm[3] = {0, 0, 0};
+    float gather_target = 1.6f;  // first gather radius: sized to hold gather_target * k photons at the local density
+    int gather_tcap = 1024;      // gather variant 2: positions in the shared tile (1024 -> 7 blocks per SM, 2048 -> 5)
     int gather_qt = 8;           // gather variant 2: consecutive queries that share one staged tile (8, 16 or 32)
     int gather_variant = 2;      // 0: per-row scan with direct loads, 1: coarse table + TMA-staged tiles per warp,
                                  // 2: one TMA-staged tile shared by a block's 32 consecutive queries (k-nearest)

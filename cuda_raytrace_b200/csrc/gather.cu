@@ -414,7 +414,7 @@ __device__ __forceinline__ float axis_gap(float q, float lo, float hi, bool open
 struct GatherArgs {
     const float4 *pos4; const b2rt_photon *photons; const uint32_t *cell_start; const uint32_t *coarse;
     Gather2Grid g;
-    const b2rt_query *queries; int64_t nq; int k; float max_dist2, n_paths;
+    const b2rt_query *queries; int64_t nq; int k; float max_dist2, n_paths, target;
     float *out_rgb, *out_r2; int32_t *out_found, *idx_out;
 };
 
@@ -533,7 +533,7 @@ __device__ __forceinline__ void gather_query_warp(const GatherArgs &A, int64_t q
             }
             n8 = __reduce_add_sync(0xffffffffu, n8);
             if (n8 > 0) {
-                const float est = (1.6f * 64.f * B2_INV_PI) * (float)k * g.cell * g.cell / (float)n8;
+                const float est = (A.target * 64.f * B2_INV_PI) * (float)k * g.cell * g.cell / (float)n8;
                 r2_try = fminf(est, max_dist2);
             }
         }
@@ -730,13 +730,13 @@ gather_tiled_kernel(const GatherArgs A) {
 //      a private slice of the tile as staging buffer.
 // Rows, staging and prefix sums are paid once per 32 queries instead of once per query (they were ~40 % of the
 // per-warp kernel's instructions).  The result set of a query is still the k smallest keys below the final bound.
-constexpr int GB_TCAP = 2048;
 constexpr int GB_ROWS = 2 * GATHER_WARPS * 32;
-static_assert(GATHER_WARPS * G2_STAGE <= GB_TCAP, "fallback staging slices must fit in the shared tile");
 
-template <int GB_QT>
-__global__ void __launch_bounds__(GATHER_WARPS * 32, 5)
+// GB_TCAP = positions in the shared tile, GB_MINB = resident blocks per SM the register budget is capped for
+template <int GB_QT, int GB_TCAP, int GB_MINB>
+__global__ void __launch_bounds__(GATHER_WARPS * 32, GB_MINB)
 gather_block_kernel(const GatherArgs A) {
+    static_assert(GATHER_WARPS * G2_STAGE <= GB_TCAP, "fallback staging slices must fit in the shared tile");
     __shared__ __align__(128) float4 s_tile[GB_TCAP];
     __shared__ uint64_t s_cand[GATHER_WARPS][GATHER_CAP];
     __shared__ float4 s_q[GB_QT];
@@ -785,7 +785,7 @@ gather_block_kernel(const GatherArgs A) {
                     if (in) n8 += __ldg(A.coarse + ((int64_t)P[2] * g.cdims[1] + P[1]) * g.cdims[0] + P[0]);
                 }
                 float r2_try = A.max_dist2;
-                if (n8 > 0) r2_try = fminf((1.6f * 64.f * B2_INV_PI) * (float)A.k * g.cell * g.cell / (float)n8, A.max_dist2);
+                if (n8 > 0) r2_try = fminf((A.target * 64.f * B2_INV_PI) * (float)A.k * g.cell * g.cell / (float)n8, A.max_dist2);
                 const float r = sqrtf(r2_try) * 1.0001f + g.slack;
 #pragma unroll
                 for (int a = 0; a < 3; ++a) {
@@ -928,19 +928,22 @@ int b2rt_gather_impl(b2rt_ctx *ctx, int map, int64_t nq, const b2rt_query *d_que
         GatherArgs A;
         A.pos4 = m.pos4.as<float4>(); A.photons = m.sorted.as<b2rt_photon>(); A.cell_start = m.cell_start.as<uint32_t>();
         A.coarse = m.coarse.as<uint32_t>(); A.g = g2; A.queries = d_queries; A.nq = nq; A.k = k; A.max_dist2 = max_dist2;
-        A.n_paths = npaths; A.out_rgb = d_rgb; A.out_r2 = d_r2; A.out_found = d_found; A.idx_out = d_idx;
+        A.n_paths = npaths; A.target = ctx->gather_target; A.out_rgb = d_rgb; A.out_r2 = d_r2; A.out_found = d_found; A.idx_out = d_idx;
         if (k > 0 && ctx->gather_variant == 2) {
             const int qt = ctx->gather_qt == 32 ? 32 : (ctx->gather_qt == 16 ? 16 : 8);
+            // default: 1024-position tile, 7 blocks per SM (r01z sweep: camera pass 15.9 ms against 17.2 ms with 2048 / 5)
+            void (*kern)(const GatherArgs) = gather_block_kernel<8, 1024, 7>;
+            if (qt == 32) kern = gather_block_kernel<32, 2048, 5>;
+            else if (qt == 16) kern = gather_block_kernel<16, 2048, 5>;
+            else if (ctx->gather_tcap == 2048) kern = gather_block_kernel<8, 2048, 5>;
             int &bsm = ctx->gather_blocks_per_sm[2];
             if (bsm == 0) {
-                B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bsm, gather_block_kernel<8>, GATHER_WARPS * 32, 0));
+                B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bsm, kern, GATHER_WARPS * 32, 0));
                 if (bsm < 1) bsm = 1;
             }
             int64_t nb = (nq + qt - 1) / qt;
             if (nb > (int64_t)ctx->sm_count * bsm) nb = (int64_t)ctx->sm_count * bsm;
-            if (qt == 32) gather_block_kernel<32><<<(unsigned)nb, GATHER_WARPS * 32, 0, ctx->stream>>>(A);
-            else if (qt == 16) gather_block_kernel<16><<<(unsigned)nb, GATHER_WARPS * 32, 0, ctx->stream>>>(A);
-            else gather_block_kernel<8><<<(unsigned)nb, GATHER_WARPS * 32, 0, ctx->stream>>>(A);
+            kern<<<(unsigned)nb, GATHER_WARPS * 32, 0, ctx->stream>>>(A);
         } else if (k > 0) gather_tiled_kernel<true><<<(unsigned)blocks, GATHER_WARPS * 32, 0, ctx->stream>>>(A);
         else gather_tiled_kernel<false><<<(unsigned)blocks, GATHER_WARPS * 32, 0, ctx->stream>>>(A);
         B2RT_LAUNCH_CHECK(ctx);
