@@ -320,10 +320,17 @@ __device__ __forceinline__ bool traverse(const WideNode *__restrict__ nodes, con
             // sort the 4 (tn, child) pairs ascending by tn with a 5-comparator network
 #define B2RT_CSWAP(a, b)                                                                  \
     if (tn[b] < tn[a]) { float tt = tn[a]; tn[a] = tn[b]; tn[b] = tt; int32_t cc = cr[a]; cr[a] = cr[b]; cr[b] = cc; }
-            B2RT_CSWAP(0, 1) B2RT_CSWAP(2, 3) B2RT_CSWAP(0, 2) B2RT_CSWAP(1, 3) B2RT_CSWAP(1, 2)
+            if (!ANY) { B2RT_CSWAP(0, 1) B2RT_CSWAP(2, 3) B2RT_CSWAP(0, 2) B2RT_CSWAP(1, 3) B2RT_CSWAP(1, 2) }
 #undef B2RT_CSWAP
             int nhit = (tn[0] < INFINITY) + (tn[1] < INFINITY) + (tn[2] < INFINITY) + (tn[3] < INFINITY);
-            if (nhit == 0) {
+            if (ANY) {                          // any hit: the answer does not depend on the order, skip the network
+                if (sp + 3 > B2RT_STACK_SIZE) { overflow = true; sp = 0; cur = NONE; leaf = NONE; break; }
+                int32_t nxt = NONE;
+#pragma unroll
+                for (int k = 3; k >= 0; --k)
+                    if (tn[k] < INFINITY) { if (nxt != NONE) stack[sp++] = nxt; nxt = cr[k]; }
+                cur = nxt != NONE ? nxt : (sp > 0 ? stack[--sp] : NONE);
+            } else if (nhit == 0) {
                 cur = sp > 0 ? stack[--sp] : NONE;
             } else {
                 if (sp + 3 > B2RT_STACK_SIZE) { overflow = true; sp = 0; cur = NONE; leaf = NONE; break; }

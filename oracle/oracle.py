@@ -453,3 +453,64 @@ def photons_to9(ph):
     out = np.zeros((len(ph), 9), np.float32)
     out[:, 0:3], out[:, 3:6], out[:, 6:9] = ph["p"], ph["alpha"], oct_decode(ph["wi_oct"])
     return out
+
+
+# ---- film reconstruction (oracle_film.c; reference: pbrt's own ImageFilm through ref_film.cpp) -------------------------
+FILTERS = {"box": 0, "triangle": 1, "gaussian": 2, "mitchell": 3, "sinc": 4}
+
+
+def filter_args(name, xwidth=None, ywidth=None, **kw):
+    """(type, xwidth, ywidth, p0, p1) with pbrt's defaults (filters/*.cpp Create*Filter)."""
+    t = FILTERS[name]
+    dw = {0: 0.5, 1: 2.0, 2: 2.0, 3: 2.0, 4: 4.0}[t]
+    p0, p1 = {0: (0.0, 0.0), 1: (0.0, 0.0), 2: (kw.get("alpha", 2.0), 0.0), 3: (kw.get("B", 1 / 3), kw.get("C", 1 / 3)),
+              4: (kw.get("tau", 3.0), 0.0)}[t]
+    return t, float(dw if xwidth is None else xwidth), float(dw if ywidth is None else ywidth), float(p0), float(p1)
+
+
+def filter_table(flt):
+    lib = port()
+    out = np.zeros(256, np.float32)
+    lib.port_filter_table.argtypes = [C.c_int] + [C.c_float] * 4 + [C.c_void_p]
+    lib.port_filter_table.restype = None
+    lib.port_filter_table(flt[0], flt[1], flt[2], flt[3], flt[4], _p(out))
+    return out
+
+
+def film(flt, cells, spp, xy, rgb, pixels):
+    """cells = (cx0, cy0, cx1, cy1) sample cells, pixels = (x0, y0, x1, y1); xy (n, 2), rgb (n, 3), n = cells * spp,
+    cell row-major.  Returns (y1-y0, x1-x0, 3)."""
+    lib = port()
+    lib.port_film.argtypes = [C.c_int] + [C.c_float] * 4 + [C.c_int] * 5 + [C.c_void_p] * 2 + [C.c_int] * 4 + [C.c_void_p]
+    lib.port_film.restype = None
+    xy = np.ascontiguousarray(xy, np.float32)
+    rgb = np.ascontiguousarray(rgb, np.float32)
+    n = (cells[2] - cells[0]) * (cells[3] - cells[1]) * spp
+    assert xy.shape == (n, 2) and rgb.shape == (n, 3)
+    out = np.zeros((pixels[3] - pixels[1], pixels[2] - pixels[0], 3), np.float32)
+    lib.port_film(flt[0], flt[1], flt[2], flt[3], flt[4], *[int(c) for c in cells], int(spp), _p(xy), _p(rgb),
+                  *[int(c) for c in pixels], _p(out))
+    return out
+
+
+def read_pfm(path):
+    with open(path, "rb") as f:
+        assert f.readline().strip() == b"PF"
+        w, h = (int(v) for v in f.readline().split())
+        scale = float(f.readline())
+        data = np.frombuffer(f.read(), "<f4" if scale < 0 else ">f4").reshape(h, w, 3)
+    return data[::-1].astype(np.float32)        # PFM rows run bottom to top
+
+
+def ref_film(flt, xres, yres, xy, rgb, pixels=None):
+    """pbrt's ImageFilm (oracle/_ref) fed with the samples in the given order; pixels = crop window in pixels."""
+    import tempfile
+    lib = C.CDLL(REF_SO)
+    lib.ref_film.argtypes = [C.c_int] + [C.c_float] * 4 + [C.c_int] * 2 + [C.c_void_p, C.c_longlong, C.c_void_p, C.c_char_p]
+    x0, y0, x1, y1 = pixels if pixels is not None else (0, 0, xres, yres)
+    crop = np.array([x0 / xres, x1 / xres, y0 / yres, y1 / yres], np.float32)
+    s = np.ascontiguousarray(np.concatenate([np.asarray(xy, np.float32), np.asarray(rgb, np.float32)], 1))
+    with tempfile.TemporaryDirectory() as d:
+        path = os.path.join(d, "film.pfm")
+        lib.ref_film(flt[0], flt[1], flt[2], flt[3], flt[4], xres, yres, _p(crop), len(s), _p(s), path.encode())
+        return read_pfm(path)
