@@ -443,3 +443,52 @@ def _render_frame_device(self, cam, out_ptr, spp=1, max_specular_depth=5, nused=
 
 Context.render_frame = _render_frame
 Context.render_frame_device = _render_frame_device
+
+
+# ---- film reconstruction with pbrt's pixel filters (csrc/film.cu) ------------------------------------------------------
+SYMBOLS += ["b2rt_film_set_filter", "b2rt_film_reconstruct"]
+FILTERS = {"box": 0, "triangle": 1, "gaussian": 2, "mitchell": 3, "sinc": 4}
+
+
+class Filter(C.Structure):
+    _fields_ = [("type", C.c_int32), ("xwidth", C.c_float), ("ywidth", C.c_float), ("p0", C.c_float), ("p1", C.c_float)]
+
+
+def pbrt_filter(name, xwidth=None, ywidth=None, **params):
+    """pbrt `PixelFilter "name"` with its parameter names and defaults (filters/*.cpp Create*Filter): box 0.5,
+    triangle 2, gaussian 2 (alpha 2), mitchell 2 (B = C = 1/3), sinc 4 (tau 3)."""
+    t = FILTERS[name]
+    dw = (0.5, 2.0, 2.0, 2.0, 4.0)[t]
+    known = {0: (), 1: (), 2: ("alpha",), 3: ("B", "C"), 4: ("tau",)}[t]
+    bad = set(params) - set(known)
+    if bad:
+        raise ValueError("filter %r has no parameter %s" % (name, sorted(bad)))
+    p0 = {2: params.get("alpha", 2.0), 3: params.get("B", 1.0 / 3.0), 4: params.get("tau", 3.0)}.get(t, 0.0)
+    p1 = params.get("C", 1.0 / 3.0) if t == 3 else 0.0
+    return Filter(t, dw if xwidth is None else xwidth, dw if ywidth is None else ywidth, p0, p1)
+
+
+def _set_filter(self, flt=None):
+    """Pixel filter of the following render_frame calls (a Filter from pbrt_filter); None = pbrt's default box 0.5."""
+    self.lib.b2rt_film_set_filter.argtypes = [C.c_void_p, C.POINTER(Filter)]
+    self._ck(self.lib.b2rt_film_set_filter(self.h, C.byref(flt) if flt is not None else None))
+
+
+def _film_reconstruct(self, flt, cells, spp, xy, rgb, pixels):
+    """cells = (cx0, cy0, cx1, cy1), pixels = (x0, y0, x1, y1); xy (n, 2) / rgb (n, 3) float32, n = cells * spp in cell
+    row-major order.  Returns the (y1-y0, x1-x0, 3) image."""
+    xy = np.ascontiguousarray(xy, np.float32)
+    rgb = np.ascontiguousarray(rgb, np.float32)
+    n = (cells[2] - cells[0]) * (cells[3] - cells[1]) * spp
+    if xy.shape != (n, 2) or rgb.shape != (n, 3):
+        raise ValueError("film_reconstruct: xy / rgb must hold cells * spp samples")
+    out = np.zeros((pixels[3] - pixels[1], pixels[2] - pixels[0], 3), np.float32)
+    c4, p4 = (C.c_int32 * 4)(*[int(v) for v in cells]), (C.c_int32 * 4)(*[int(v) for v in pixels])
+    self.lib.b2rt_film_reconstruct.argtypes = [C.c_void_p, C.POINTER(Filter), C.POINTER(C.c_int32), C.c_int32, C.c_void_p,
+                                               C.c_void_p, C.POINTER(C.c_int32), C.c_void_p, C.c_int]
+    self._ck(self.lib.b2rt_film_reconstruct(self.h, C.byref(flt), c4, int(spp), _ptr(xy), _ptr(rgb), p4, _ptr(out), HOST))
+    return out
+
+
+Context.set_filter = _set_filter
+Context.film_reconstruct = _film_reconstruct

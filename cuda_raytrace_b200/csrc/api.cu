@@ -93,7 +93,8 @@ void b2rt_destroy(b2rt_ctx *ctx) {
                       &ctx->d_occ, &ctx->d_scan_tmp, &ctx->d_prim_material, &ctx->d_prim_light, &ctx->d_materials,
                       &ctx->d_lights, &ctx->d_light_cdf, &ctx->d_slots, &ctx->d_cnt_c, &ctx->d_cnt_i, &ctx->d_grid_box,
                       &ctx->d_queries, &ctx->d_q_rgb, &ctx->d_q_r2, &ctx->d_q_found, &ctx->d_q_idx,
-                      &ctx->d_samples, &ctx->d_qslots, &ctx->d_qcnt, &ctx->d_q_rgb2, &ctx->d_frame};
+                      &ctx->d_samples, &ctx->d_qslots, &ctx->d_qcnt, &ctx->d_q_rgb2, &ctx->d_frame, &ctx->d_film_xy,
+                      &ctx->d_film_rgb};
     for (PhotonMap &m : ctx->maps) {
         m.photons.release(); m.sorted.release(); m.cell_start.release(); m.keys.release(); m.order.release(); m.pos4.release(); m.coarse.release();
     }

@@ -128,6 +128,8 @@ struct b2rt_ctx {
     DevBuf d_slots, d_cnt_c, d_cnt_i, d_grid_box;
     DevBuf d_queries, d_q_rgb, d_q_r2, d_q_found, d_q_idx;
     DevBuf d_samples, d_qslots, d_qcnt, d_q_rgb2, d_frame;
+    DevBuf d_film_xy, d_film_rgb;       // per-sample raster positions / radiance of a frame reconstructed with a pixel filter
+    b2rt_filter film_filter = {B2RT_FILTER_BOX, 0.5f, 0.5f, 0.f, 0.f};   // b2rt_film_set_filter
     PhotonMap maps[2];       // B2RT_MAP_CAUSTIC, B2RT_MAP_INDIRECT
     b2rt_accel_info info{};
 };
@@ -163,6 +165,10 @@ int b2rt_photons_trace_impl(b2rt_ctx *ctx, int64_t first_path, int64_t n_paths, 
                             int64_t n_stored[2]);
 int b2rt_photon_grid_build_impl(b2rt_ctx *ctx, int map, float cell_size, float target_per_cell);
 int b2rt_render_impl(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_params *fp, float *d_out);
+bool b2rt_filter_valid(const b2rt_filter *f);
+void b2rt_filter_halo(const b2rt_filter *f, int *hx, int *hy);
+int b2rt_film_impl(b2rt_ctx *ctx, const b2rt_filter *f, const int32_t cells[4], int32_t spp, const float *d_xy,
+                   const float *d_rgb, const int32_t pixels[4], float *d_out);
 int b2rt_gather_impl(b2rt_ctx *ctx, int map, int64_t nq, const b2rt_query *d_queries, int k, float max_dist2,
                      float *d_rgb, float *d_r2, int32_t *d_found, int32_t *d_idx);
 void b2rt_fill_dscene(b2rt_ctx *ctx, DScene *sc);

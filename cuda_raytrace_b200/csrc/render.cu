@@ -109,7 +109,7 @@ struct TreeNode { f3 o, d; float tmin; f3 T; int depth; uint32_t id; };
 __global__ void __launch_bounds__(RENDER_THREADS)
 render_li_kernel(DScene sc, b2rt_camera cam, b2rt_frame_params fp, uint32_t seed_lo, uint32_t seed_hi, int64_t first_sample,
                  int64_t n_samples, int slots, float *__restrict__ sample_rgb, b2rt_query *__restrict__ qslots,
-                 uint32_t *__restrict__ qcnt, uint32_t *status) {
+                 uint32_t *__restrict__ qcnt, uint32_t *status, float2 *__restrict__ sample_xy) {
     int64_t ls = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (ls >= n_samples) return;
     const int64_t s = first_sample + ls;
@@ -117,10 +117,15 @@ render_li_kernel(DScene sc, b2rt_camera cam, b2rt_frame_params fp, uint32_t seed
     const int64_t pix = s / fp.spp;
     const int k = (int)(s % fp.spp);
     const int px = fp.x0 + (int)(pix % cw), py = fp.y0 + (int)(pix / cw);
-    const uint32_t gpix = (uint32_t)py * (uint32_t)cam.xres + (uint32_t)px;    // global pixel id: tiling-independent
+    uint32_t gpix = (uint32_t)py * (uint32_t)cam.xres + (uint32_t)px;          // global pixel id: tiling-independent
+    // sample cells around the image (a pixel filter wider than the pixel reaches them, ImageFilm::GetSampleExtent):
+    // ids after the image's own, unique for cells up to 64 pixels outside
+    if (px < 0 || py < 0 || px >= cam.xres || py >= cam.yres)
+        gpix = (uint32_t)cam.xres * (uint32_t)cam.yres + (uint32_t)(py + 64) * (uint32_t)(cam.xres + 128) + (uint32_t)(px + 64);
     const uint32_t k0 = seed_lo ^ 0x43414d52u, k1 = seed_hi;                     // 'CAMR' stream
     u4 rj = philox4x32_10(gpix, (uint32_t)k, 0u, 0u, k0, k1);
     const float fx = (float)px + u01(rj.x), fy = (float)py + u01(rj.y);
+    if (sample_xy) sample_xy[ls] = make_float2(fx, fy);
     f3 d0 = mk3(cam.A[0] + fx * cam.B[0] + fy * cam.C[0], cam.A[1] + fx * cam.B[1] + fy * cam.C[1],
                 cam.A[2] + fx * cam.B[2] + fy * cam.C[2]);
 
@@ -233,6 +238,23 @@ film_resolve_kernel(const float *__restrict__ sample_rgb, const uint32_t *__rest
     o[0] = acc.x * inv; o[1] = acc.y * inv; o[2] = acc.z * inv;
 }
 
+// per-sample radiance (camera-pass terms + the photon-map estimates of the sample's leaves) for the filtered film
+__global__ void __launch_bounds__(256)
+sample_resolve_kernel(const float *__restrict__ sample_rgb, const uint32_t *__restrict__ qoff, const uint32_t *__restrict__ qtot,
+                      const float *__restrict__ rgb_c, const float *__restrict__ rgb_i, int64_t n_samples,
+                      float *__restrict__ out_rgb) {
+    int64_t ls = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (ls >= n_samples) return;
+    f3 L = mk3(sample_rgb[3 * ls], sample_rgb[3 * ls + 1], sample_rgb[3 * ls + 2]);
+    uint32_t o = qoff[ls];
+    uint32_t n = ((ls + 1 < n_samples) ? qoff[ls + 1] : qtot[0]) - o;
+    for (uint32_t j = o; j < o + n; ++j) {
+        if (rgb_c) L = L + mk3(rgb_c[3 * j], rgb_c[3 * j + 1], rgb_c[3 * j + 2]);
+        if (rgb_i) L = L + mk3(rgb_i[3 * j], rgb_i[3 * j + 1], rgb_i[3 * j + 2]);
+    }
+    out_rgb[3 * ls] = L.x; out_rgb[3 * ls + 1] = L.y; out_rgb[3 * ls + 2] = L.z;
+}
+
 }  // namespace
 
 // d_out: device buffer of (x1-x0)*(y1-y0)*3 floats, crop-window row-major
@@ -251,10 +273,26 @@ int b2rt_render_impl(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_par
     const bool use_i = fp->use_indirect && ctx->maps[1].grid_built && ctx->maps[1].n > 0;
     b2rt_frame_params p = *fp;
     p.use_caustic = use_c; p.use_indirect = use_i;
+    // pixel filter wider than the pixel: trace the sample cells around the crop window that reach into it, keep every
+    // sample's raster position and radiance, reconstruct at the end (film.cu).  The box filter of radius 0.5 (pbrt's
+    // default) keeps the direct per-pixel mean below.
+    const b2rt_filter &flt = ctx->film_filter;
+    const bool filtered = !(flt.type == B2RT_FILTER_BOX && flt.xwidth <= 0.5f && flt.ywidth <= 0.5f);
+    if (filtered) {
+        int hx, hy;
+        b2rt_filter_halo(&flt, &hx, &hy);
+        if (hx > 64 || hy > 64) { ctx->err = "render_frame: filter too wide"; return B2RT_E_ARG; }
+        p.x0 -= hx; p.x1 += hx; p.y0 -= hy; p.y1 += hy;
+    }
+    const int64_t n_cells = (int64_t)(p.x1 - p.x0) * (p.y1 - p.y0);
+    if (filtered) {
+        B2RT_CUDA(ctx, ctx->d_film_xy.reserve((size_t)n_cells * fp->spp * 8));
+        B2RT_CUDA(ctx, ctx->d_film_rgb.reserve((size_t)n_cells * fp->spp * 12));
+    }
     // chunk = whole pixels, at most ~2M samples
     int64_t chunk_pixels = (1ll << 21) / fp->spp;
     if (chunk_pixels < 1) chunk_pixels = 1;
-    if (chunk_pixels > n_pixels) chunk_pixels = n_pixels;
+    if (chunk_pixels > n_cells) chunk_pixels = n_cells;
     const int64_t cs = chunk_pixels * fp->spp;
     B2RT_CUDA(ctx, ctx->d_samples.reserve((size_t)cs * 12));
     B2RT_CUDA(ctx, ctx->d_qslots.reserve((size_t)cs * slots * sizeof(b2rt_query)));
@@ -263,13 +301,14 @@ int b2rt_render_impl(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_par
     B2RT_CUDA(ctx, ctx->d_q_rgb.reserve((size_t)cs * slots * 12));
     B2RT_CUDA(ctx, ctx->d_q_rgb2.reserve((size_t)cs * slots * 12));
     uint32_t *counters = ctx->d_counters.as<uint32_t>();
-    for (int64_t p0 = 0; p0 < n_pixels; p0 += chunk_pixels) {
-        const int64_t np = (p0 + chunk_pixels <= n_pixels) ? chunk_pixels : n_pixels - p0;
+    for (int64_t p0 = 0; p0 < n_cells; p0 += chunk_pixels) {
+        const int64_t np = (p0 + chunk_pixels <= n_cells) ? chunk_pixels : n_cells - p0;
         const int64_t ns = np * fp->spp;
         uint32_t *qcnt = ctx->d_qcnt.as<uint32_t>();
         render_li_kernel<<<(unsigned)((ns + RENDER_THREADS - 1) / RENDER_THREADS), RENDER_THREADS, 0, st>>>(
             sc, *cam, p, (uint32_t)ctx->seed, (uint32_t)(ctx->seed >> 32), p0 * fp->spp, ns, slots,
-            ctx->d_samples.as<float>(), ctx->d_qslots.as<b2rt_query>(), qcnt, counters + 8);
+            ctx->d_samples.as<float>(), ctx->d_qslots.as<b2rt_query>(), qcnt, counters + 8,
+            filtered ? ctx->d_film_xy.as<float2>() + p0 * fp->spp : nullptr);
         B2RT_LAUNCH_CHECK(ctx);
         int rc = b2rt_exclusive_scan_u32(ctx, qcnt, ns, counters + 12);
         if (rc) return rc;
@@ -295,9 +334,17 @@ int b2rt_render_impl(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_par
                 rgb_i = ctx->d_q_rgb2.as<float>();
             }
         }
-        film_resolve_kernel<<<(unsigned)((np + 255) / 256), 256, 0, st>>>(ctx->d_samples.as<float>(), qcnt, counters + 12,
-                                                                          rgb_c, rgb_i, ns, fp->spp, p0, np, d_out);
+        if (filtered)
+            sample_resolve_kernel<<<(unsigned)((ns + 255) / 256), 256, 0, st>>>(
+                ctx->d_samples.as<float>(), qcnt, counters + 12, rgb_c, rgb_i, ns, ctx->d_film_rgb.as<float>() + 3 * p0 * fp->spp);
+        else
+            film_resolve_kernel<<<(unsigned)((np + 255) / 256), 256, 0, st>>>(ctx->d_samples.as<float>(), qcnt, counters + 12,
+                                                                              rgb_c, rgb_i, ns, fp->spp, p0, np, d_out);
         B2RT_LAUNCH_CHECK(ctx);
+    }
+    if (filtered) {
+        const int32_t cells[4] = {p.x0, p.y0, p.x1, p.y1}, pixels[4] = {fp->x0, fp->y0, fp->x1, fp->y1};
+        return b2rt_film_impl(ctx, &flt, cells, fp->spp, ctx->d_film_xy.as<float>(), ctx->d_film_rgb.as<float>(), pixels, d_out);
     }
     return B2RT_OK;
 }

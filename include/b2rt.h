@@ -173,6 +173,25 @@ typedef struct {
  * grids built if use_caustic / use_indirect are set (maps that are empty or unbuilt contribute nothing). */
 int b2rt_render_frame(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_params *fp, float *out_rgb, int where);
 
+/* ---- film: replaces the reference's CPU film loop, camera->film->AddSample for every launch sample
+ * (cuda_render/photon_mapping/photonmappingrenderer.cpp:247-273, simple_render/simplerender.cpp:84-100), i.e. pbrt's
+ * ImageFilm::AddSample + the normalisation in ImageFilm::WriteImage (pbrt-v2/src/film/image.cpp:77-137,178-213) with
+ * the pixel filters of pbrt-v2/src/filters: same 16x16 weight table, same extent arithmetic, XYZ accumulation. ---- */
+enum { B2RT_FILTER_BOX = 0, B2RT_FILTER_TRIANGLE = 1, B2RT_FILTER_GAUSSIAN = 2, B2RT_FILTER_MITCHELL = 3,
+       B2RT_FILTER_SINC = 4 };
+/* p0, p1: gaussian alpha | mitchell B, C | sinc tau (pbrt's parameter names); widths in pixels, (0, 16] */
+typedef struct { int32_t type; float xwidth, ywidth, p0, p1; } b2rt_filter;
+/* the filter b2rt_render_frame reconstructs with from now on (NULL: pbrt's default, box 0.5 x 0.5).  With a support
+ * wider than half a pixel the frame also traces the sample cells around the crop window that reach into it
+ * (ImageFilm::GetSampleExtent, film/image.cpp:155-166), so image bands stay bit-identical to the whole frame. */
+int b2rt_film_set_filter(b2rt_ctx *ctx, const b2rt_filter *filter);
+/* stand-alone reconstruction: cells = {cx0, cy0, cx1, cy1} sample cells (cell (cx, cy) holds spp samples whose raster
+ * position xy lies in [cx, cx+1) x [cy, cy+1)), samples cell-major: xy[2*s], rgb[3*s], s = cell * spp + k;
+ * pixels = {x0, y0, x1, y1} = the film's crop window; out_rgb (x1-x0)*(y1-y0)*3 row-major.  A pixel sums its samples
+ * in (cell row, cell column, k) order: deterministic, and equal to pbrt's film fed in that order bit for bit. */
+int b2rt_film_reconstruct(b2rt_ctx *ctx, const b2rt_filter *filter, const int32_t cells[4], int32_t spp, const float *xy,
+                          const float *rgb, const int32_t pixels[4], float *out_rgb, int where);
+
 /* generic device sort exposed for tests/bench of the hand-written radix sort (K2):
  * stable LSD sort of (key32,value32) pairs on `key_bits` low bits; device pointers only. */
 int b2rt_sort_pairs(b2rt_ctx *ctx, int64_t n, uint32_t *keys, uint32_t *vals, int key_bits);

@@ -1,0 +1,105 @@
+"""GPU parity (through the C ABI): the film reconstruction kernel (csrc/film.cu) against oracle/oracle_film.c - itself
+bit-identical to pbrt's ImageFilm (tests/test_oracle_film_cpu.py) - and against the committed images of the reference's
+own film (tests/golden/film.npz); the filtered camera pass: band tiling, constant-radiance and box-filter identities."""
+import numpy as np
+import pytest
+
+from helpers import load_golden
+from oracle import oracle as O
+from cuda_raytrace_b200 import b2rt, scenes as S
+import film_cases as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _flt(name, kw):
+    return b2rt.pbrt_filter(name, **kw), O.filter_args(name, **kw)
+
+
+@pytest.mark.parametrize("case", range(len(F.CASES)))
+def test_film_kernel_matches_oracle_and_pbrt_golden_bit_for_bit(case):
+    name, kw, xres, yres, spp, window = F.CASES[case]
+    gf, of = _flt(name, kw)
+    cells, xy, rgb, px = F.make_samples(of, xres, yres, spp, window, seed=100 + case)
+    with b2rt.Context(0) as c:
+        img = c.film_reconstruct(gf, cells, spp, xy, rgb, px)
+    ref = O.film(of, cells, spp, xy, rgb, px)
+    assert np.array_equal(img.view(np.uint32), ref.view(np.uint32))
+    assert np.array_equal(img.view(np.uint32), load_golden("film")["film_%d" % case].view(np.uint32))
+
+
+def test_film_kernel_at_frame_size_against_oracle():
+    # 1920x1080, 2 spp, mitchell: 4.2 M samples; the oracle finishes in seconds
+    gf, of = _flt("mitchell", {})
+    cells, xy, rgb, px = F.make_samples(of, 1920, 1080, 2, None, seed=9)
+    with b2rt.Context(0) as c:
+        img = c.film_reconstruct(gf, cells, 2, xy, rgb, px)
+    ref = O.film(of, cells, 2, xy, rgb, px)
+    assert np.array_equal(img.view(np.uint32), ref.view(np.uint32))
+
+
+def test_film_argument_errors():
+    with b2rt.Context(0) as c:
+        xy, rgb = np.zeros((4, 2), np.float32), np.zeros((4, 3), np.float32)
+        with pytest.raises(b2rt.B2rtError):
+            c.film_reconstruct(b2rt.Filter(7, 1.0, 1.0, 0, 0), (0, 0, 2, 2), 1, xy, rgb, (0, 0, 2, 2))
+        with pytest.raises(b2rt.B2rtError):
+            c.film_reconstruct(b2rt.Filter(0, 0.0, 1.0, 0, 0), (0, 0, 2, 2), 1, xy, rgb, (0, 0, 2, 2))
+        with pytest.raises(b2rt.B2rtError):
+            c.set_filter(b2rt.Filter(3, 40.0, 2.0, 0, 0))
+
+
+EYE, LOOK, UP, FOV = (0, 1, 3.4), (0, 1, 0), (0, 1, 0), 40
+
+
+@pytest.fixture(scope="module")
+def rctx():
+    with b2rt.Context(0, seed=5) as c:
+        S.fill_scene(c, S.cornell_scene(spheres=True))
+        c.build_accel()
+        c.photons_shoot(2000, 20000, batch_paths=32768)
+        c.grid_build(0)
+        c.grid_build(1)
+        yield c
+
+
+def test_filtered_frame_bands_are_bit_identical_and_filter_resets(rctx):
+    cam = b2rt.pbrt_camera(EYE, LOOK, UP, FOV, 64, 48)
+    kw = dict(spp=2, nused=20, max_dist=0.2)
+    box = rctx.render_frame(cam, **kw)
+    rctx.set_filter(b2rt.pbrt_filter("mitchell"))
+    full = rctx.render_frame(cam, **kw)
+    again = rctx.render_frame(cam, **kw)
+    assert np.array_equal(full.view(np.uint32), again.view(np.uint32))
+    bands = [rctx.render_frame(cam, window=(0, 64, y0, y1), **kw) for y0, y1 in ((0, 13), (13, 30), (30, 48))]
+    assert np.array_equal(np.concatenate(bands, 0).view(np.uint32), full.view(np.uint32))
+    cols = [rctx.render_frame(cam, window=(x0, x1, 0, 48), **kw) for x0, x1 in ((0, 31), (31, 64))]
+    assert np.array_equal(np.concatenate(cols, 1).view(np.uint32), full.view(np.uint32))
+    assert not np.array_equal(full, box)
+    # a wider reconstruction filter redistributes radiance between neighbouring pixels, it does not change the total much
+    assert abs(full.sum() - box.sum()) <= 0.03 * box.sum()
+    rctx.set_filter(None)
+    assert np.array_equal(rctx.render_frame(cam, **kw).view(np.uint32), box.view(np.uint32))
+
+
+def test_wide_box_filter_frame_equals_film_of_neighbouring_box_frames(rctx):
+    # box filter of width 1.5: every pixel is the mean of all samples within 1.5 pixels; in the interior that is the
+    # 3 x 3 block mean plus the samples of the next ring whose jitter falls inside - bounded by the block extremes
+    cam = b2rt.pbrt_camera(EYE, LOOK, UP, FOV, 48, 48)
+    kw = dict(spp=4, caustic=False, indirect=False)
+    box = rctx.render_frame(cam, **kw).astype(np.float64)
+    rctx.set_filter(b2rt.pbrt_filter("box", xwidth=1.0, ywidth=1.0))
+    wide = rctx.render_frame(cam, **kw).astype(np.float64)
+    rctx.set_filter(None)
+    # width 1.0 box: pixel (x, y) averages the samples with |X - 0.5 - x| <= 1: its own cell and parts of the 8 around
+    lo = np.full_like(box, np.inf); hi = np.full_like(box, -np.inf)
+    pad = np.pad(box, ((1, 1), (1, 1), (0, 0)), mode="edge")
+    for dy in range(3):
+        for dx in range(3):
+            lo = np.minimum(lo, pad[dy:dy + 48, dx:dx + 48]); hi = np.maximum(hi, pad[dy:dy + 48, dx:dx + 48])
+    inner = (slice(2, 46), slice(2, 46))
+    # per-pixel means of the neighbours bound the sample values only on smooth regions; check the image-wide mean and
+    # that most pixels stay inside the neighbourhood range
+    assert abs(wide[inner].mean() - box[inner].mean()) <= 0.02 * box[inner].mean()
+    inside = (wide >= lo - 1e-6) & (wide <= hi + 1e-6)
+    assert inside[inner].mean() > 0.8
