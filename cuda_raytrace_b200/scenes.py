@@ -242,12 +242,13 @@ def _m16(o2w):
     return " ".join("%.9g" % v for v in m.T.reshape(-1))
 
 
-def to_pbrt(desc, eye, look, up, fov, xres, yres, spp, integrator, filename, renderer=None, sampler="lowdiscrepancy"):
+def to_pbrt(desc, eye, look, up, fov, xres, yres, spp, integrator, filename, renderer=None, sampler="lowdiscrepancy",
+            pixelfilter='"box"'):
     """integrator: the full `SurfaceIntegrator ...` line.  Only features the reference's GPU path translates are used."""
     L = ["LookAt %g %g %g  %g %g %g  %g %g %g" % (*eye, *look, *up),
          'Camera "perspective" "float fov" [%g]' % fov,
          'Film "image" "integer xresolution" [%d] "integer yresolution" [%d] "string filename" ["%s"]' % (xres, yres, filename),
-         'Sampler "%s" "integer pixelsamples" [%d]' % (sampler, spp), 'PixelFilter "box"', integrator]
+         'Sampler "%s" "integer pixelsamples" [%d]' % (sampler, spp), 'PixelFilter ' + pixelfilter, integrator]
     if renderer:
         L.append(renderer if renderer.startswith("Renderer") else 'Renderer "%s"' % renderer)
     L.append("WorldBegin")

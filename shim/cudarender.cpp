@@ -23,6 +23,12 @@
 #include "shapes/disk.h"
 #include "lights/point.h"
 #include "lights/diffuse.h"
+#include "film/image.h"
+#include "filters/box.h"
+#include "filters/triangle.h"
+#include "filters/gaussian.h"
+#include "filters/mitchell.h"
+#include "filters/sinc.h"
 #include <string.h>
 
 // ---- friend accessors: the fork's pbrt headers befriend these class names (shapes/trianglemesh.h:69,
@@ -274,18 +280,48 @@ static b2rt_camera probeCamera(const Camera *camera) {
     return c;
 }
 
-// resolved pixels -> pbrt Film (film/image.cpp:77-137 AddSample at the pixel centre, then WriteImage :178-213), the
-// same hand-off the reference does per sample on the CPU (photonmappingrenderer.cpp:251-283)
-static void writeFilm(Camera *camera, const std::vector<float> &rgb) {
+// The scene's `PixelFilter`: ImageFilm keeps it in a private member and the filter classes keep their shape parameters
+// private as well (film/image.h:66, filters/gaussian.h:52, mitchell.h:61, sinc.h:59); this file is compiled with
+// -fno-access-control (shim/Makefile) so the shim can read them without touching the reference's headers.
+// Hands the filter to the library; returns the ImageFilm, or NULL for a film type the shim does not know.
+static ImageFilm *useFilmFilter(b2rt_ctx *ctx, Camera *camera) {
+    ImageFilm *film = dynamic_cast<ImageFilm *>(camera->film);
+    if (!film || !film->filter) { b2rt_film_set_filter(ctx, NULL); return NULL; }
+    Filter *f = film->filter;
+    b2rt_filter bf;
+    bf.type = B2RT_FILTER_BOX; bf.xwidth = f->xWidth; bf.ywidth = f->yWidth; bf.p0 = bf.p1 = 0.f;
+    if (dynamic_cast<TriangleFilter *>(f)) bf.type = B2RT_FILTER_TRIANGLE;
+    else if (GaussianFilter *g = dynamic_cast<GaussianFilter *>(f)) { bf.type = B2RT_FILTER_GAUSSIAN; bf.p0 = g->alpha; }
+    else if (MitchellFilter *m = dynamic_cast<MitchellFilter *>(f)) { bf.type = B2RT_FILTER_MITCHELL; bf.p0 = m->B; bf.p1 = m->C; }
+    else if (LanczosSincFilter *l = dynamic_cast<LanczosSincFilter *>(f)) { bf.type = B2RT_FILTER_SINC; bf.p0 = l->tau; }
+    else if (!dynamic_cast<BoxFilter *>(f)) Warning("CudaRender: unknown pixel filter, reconstructing with a box of its widths");
+    if (b2rt_film_set_filter(ctx, &bf) != B2RT_OK) { b2rt_film_set_filter(ctx, NULL); return NULL; }
+    return film;
+}
+
+// Reconstructed pixels -> the film's pixel array (Lxyz with weight 1: WriteImage's normalisation, film/image.cpp:
+// 178-213, then returns exactly these values) -> WriteImage.  The reference pushes every sample through
+// Film::AddSample on the CPU instead (photonmappingrenderer.cpp:251-283); here the filter already ran on the GPU
+// (csrc/film.cu), so adding the pixels as samples would filter twice.  Unknown film types get the old hand-off, one
+// AddSample per pixel centre.
+static void writeFilm(Camera *camera, ImageFilm *film, const std::vector<float> &rgb) {
     const int W = camera->film->xResolution, H = camera->film->yResolution;
     for (int y = 0; y < H; ++y)
         for (int x = 0; x < W; ++x) {
-            CameraSample cs;
-            cs.imageX = x + 0.5f; cs.imageY = y + 0.5f; cs.lensU = cs.lensV = 0.5f; cs.time = 0.f;
             const float *c = &rgb[3 * ((size_t)y * W + x)];
             float v[3] = {c[0], c[1], c[2]};
             for (int k = 0; k < 3; ++k) if (!(v[k] >= 0.f) || isinf(v[k])) v[k] = 0.f;      // NaN / negative / inf guard
-            camera->film->AddSample(cs, Spectrum::FromRGB(v));
+            if (film) {
+                const int fx = x - film->xPixelStart, fy = y - film->yPixelStart;
+                if (fx < 0 || fy < 0 || fx >= film->xPixelCount || fy >= film->yPixelCount) continue;   // outside the crop window
+                ImageFilm::Pixel &px = (*film->pixels)(fx, fy);
+                RGBToXYZ(v, px.Lxyz);
+                px.weightSum = 1.f;
+            } else {
+                CameraSample cs;
+                cs.imageX = x + 0.5f; cs.imageY = y + 0.5f; cs.lensU = cs.lensV = 0.5f; cs.time = 0.f;
+                camera->film->AddSample(cs, Spectrum::FromRGB(v));
+            }
         }
     camera->film->WriteImage();
 }
@@ -306,8 +342,9 @@ void SimpleRenderer::render(const Scene *, CudaRender *cr, Camera *camera) {
     b2rt_camera cam = probeCamera(camera);
     b2rt_frame_params fp = frameParams(cam, cr->sampler());
     std::vector<float> img((size_t)cam.xres * cam.yres * 3);
+    ImageFilm *film = useFilmFilter(cr->ctx(), camera);
     cr->check(b2rt_render_frame(cr->ctx(), &cam, &fp, img.data(), B2RT_HOST), "b2rt_render_frame");
-    writeFilm(camera, img);
+    writeFilm(camera, film, img);
 }
 
 PhotonMappingRenderer::PhotonMappingRenderer(const ParamSet &params) {
@@ -334,6 +371,7 @@ void PhotonMappingRenderer::render(const Scene *scene, CudaRender *cr, Camera *c
     fp.max_specular_depth = maxSpecularDepth; fp.nused = nUsed; fp.max_dist2 = maxDist * maxDist;
     fp.use_caustic = nCaustic > 0; fp.use_indirect = nIndirect > 0;
     std::vector<float> img((size_t)cam.xres * cam.yres * 3);
+    ImageFilm *film = useFilmFilter(ctx, camera);
     cr->check(b2rt_render_frame(ctx, &cam, &fp, img.data(), B2RT_HOST), "b2rt_render_frame");
-    writeFilm(camera, img);
+    writeFilm(camera, film, img);
 }
