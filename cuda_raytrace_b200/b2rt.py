@@ -490,5 +490,15 @@ def _film_reconstruct(self, flt, cells, spp, xy, rgb, pixels):
     return out
 
 
+def _film_reconstruct_device(self, flt, cells, spp, xy_ptr, rgb_ptr, pixels, out_ptr):
+    """film_reconstruct on DEVICE pointers (asynchronous on the library stream)."""
+    c4, p4 = (C.c_int32 * 4)(*[int(v) for v in cells]), (C.c_int32 * 4)(*[int(v) for v in pixels])
+    self.lib.b2rt_film_reconstruct.argtypes = [C.c_void_p, C.POINTER(Filter), C.POINTER(C.c_int32), C.c_int32, C.c_void_p,
+                                               C.c_void_p, C.POINTER(C.c_int32), C.c_void_p, C.c_int]
+    self._ck(self.lib.b2rt_film_reconstruct(self.h, C.byref(flt), c4, int(spp), C.c_void_p(xy_ptr), C.c_void_p(rgb_ptr), p4,
+                                            C.c_void_p(out_ptr), DEVICE))
+
+
 Context.set_filter = _set_filter
 Context.film_reconstruct = _film_reconstruct
+Context.film_reconstruct_device = _film_reconstruct_device

@@ -130,6 +130,8 @@ struct b2rt_ctx {
     DevBuf d_samples, d_qslots, d_qcnt, d_q_rgb2, d_frame;
     DevBuf d_film_xy, d_film_rgb;       // per-sample raster positions / radiance of a frame reconstructed with a pixel filter
     b2rt_filter film_filter = {B2RT_FILTER_BOX, 0.5f, 0.5f, 0.f, 0.f};   // b2rt_film_set_filter
+    int film_variant = 1;               // 1: shared-memory tiles (film_tile_kernel), 0: one thread per pixel (B2RT_FILM_VARIANT)
+    size_t film_smem_opt_in = 0;
     PhotonMap maps[2];       // B2RT_MAP_CAUSTIC, B2RT_MAP_INDIRECT
     b2rt_accel_info info{};
 };

@@ -110,6 +110,80 @@ film_filter_kernel(const FilmTable tab, const FilmArgs a, const float2 *__restri
     out[3 * lp] = c[0]; out[3 * lp + 1] = c[1]; out[3 * lp + 2] = c[2];
 }
 
+// Tiled version (default): a block owns a 32 x 8 pixel tile and walks the cell rows that reach it from top to bottom.
+// Each row's samples are staged ONCE in shared memory, already turned into what every pixel needs from them - the
+// shifted raster position and the XYZ radiance - laid out [sample k][cell] with an odd row pitch, so the staging stores
+// and the per-pixel reads (32 lanes = 32 consecutive cells, same k) are both conflict-free.  A pixel still sums its
+// samples in (cell row, cell column, k) order with the expressions of film_filter_kernel: same bits.
+// The one-thread-per-pixel kernel read every sample from global memory (2h+1)^2 times with one dependent load chain
+// per thread: 29 ms for a 3840 x 2160 x 16 spp Mitchell frame, 60 warps stalled on loads per issue (run r02e).
+constexpr int FILM_TW = 32, FILM_TH = 8;
+
+__global__ void __launch_bounds__(FILM_TW * FILM_TH)
+film_tile_kernel(const FilmTable tab, const FilmArgs a, const float2 *__restrict__ xy, const float *__restrict__ rgb,
+                 float *__restrict__ out, int pitch) {
+    extern __shared__ float s_dyn[];
+    __shared__ float s_tab[FT * FT];
+    const int tid = threadIdx.y * FILM_TW + threadIdx.x;
+    for (int i = tid; i < FT * FT; i += FILM_TW * FILM_TH) s_tab[i] = tab.w[i];
+    const int W = a.x1 - a.x0, cw = a.cx1 - a.cx0;
+    const int tx0 = a.x0 + blockIdx.x * FILM_TW, ty0 = a.y0 + blockIdx.y * FILM_TH;
+    const int x = tx0 + threadIdx.x, y = ty0 + threadIdx.y;
+    const bool live = x < a.x1 && y < a.y1;
+    const int col0 = max(a.cx0, tx0 - a.hx), col1 = min(a.cx1 - 1, min(tx0 + FILM_TW - 1, a.x1 - 1) + a.hx);    // staged cell columns
+    const int ncol = col1 - col0 + 1;
+    const int row0 = max(a.cy0, ty0 - a.hy), row1 = min(a.cy1 - 1, min(ty0 + FILM_TH - 1, a.y1 - 1) + a.hy);
+    const int ca = max(col0, x - a.hx), cb = min(col1, x + a.hx);
+    const int plane = pitch * a.spp;            // floats per staged quantity
+    float *s_dx = s_dyn, *s_dy = s_dyn + plane, *s_x = s_dyn + 2 * plane, *s_y = s_dyn + 3 * plane, *s_z = s_dyn + 4 * plane;
+    const float fx = (float)x, fy = (float)y;
+    float X = 0.f, Y = 0.f, Z = 0.f, wsum = 0.f;
+    for (int cy = row0; cy <= row1; ++cy) {
+        __syncthreads();                        // the previous row is consumed (first pass: s_tab is written)
+        const int64_t rowbase = ((int64_t)(cy - a.cy0) * cw + (col0 - a.cx0)) * a.spp;
+        const int nrow = ncol * a.spp;
+        for (int i = tid; i < nrow; i += FILM_TW * FILM_TH) {
+            const int cell = i / a.spp, k = i - cell * a.spp;
+            const float2 p = __ldg(xy + rowbase + i);
+            const float r = __ldg(rgb + 3 * (rowbase + i)), g = __ldg(rgb + 3 * (rowbase + i) + 1),
+                        b = __ldg(rgb + 3 * (rowbase + i) + 2);
+            const int o = k * pitch + cell;
+            s_dx[o] = p.x - 0.5f; s_dy[o] = p.y - 0.5f;
+            s_x[o] = 0.412453f * r + 0.357580f * g + 0.180423f * b;
+            s_y[o] = 0.212671f * r + 0.715160f * g + 0.072169f * b;
+            s_z[o] = 0.019334f * r + 0.119193f * g + 0.950227f * b;
+        }
+        __syncthreads();
+        if (!live || cy < y - a.hy || cy > y + a.hy) continue;
+        for (int cx = ca; cx <= cb; ++cx) {
+            const int c = cx - col0;
+            for (int k = 0; k < a.spp; ++k) {
+                const int o = k * pitch + c;
+                const float dx = s_dx[o], dy = s_dy[o];
+                // x >= Ceil2Int(v) <=> x >= v and x <= Floor2Int(v) <=> x <= v for an integer x
+                if (fx < dx - a.xw || fx > dx + a.xw || fy < dy - a.yw || fy > dy + a.yw) continue;
+                int ix = (int)floorf(fabsf((fx - dx) * a.invx * FT));
+                int iy = (int)floorf(fabsf((fy - dy) * a.invy * FT));
+                ix = min(ix, FT - 1); iy = min(iy, FT - 1);
+                const float w = s_tab[iy * FT + ix];
+                X += w * s_x[o]; Y += w * s_y[o]; Z += w * s_z[o]; wsum += w;
+            }
+        }
+    }
+    if (!live) return;
+    float c[3];
+    c[0] = 3.240479f * X - 1.537150f * Y - 0.498535f * Z;
+    c[1] = -0.969256f * X + 1.875991f * Y + 0.041556f * Z;
+    c[2] = 0.055648f * X - 0.204043f * Y + 1.057311f * Z;
+    if (wsum != 0.f) {
+        const float inv = 1.f / wsum;
+#pragma unroll
+        for (int j = 0; j < 3; ++j) { c[j] = c[j] * inv; if (!(c[j] > 0.f)) c[j] = 0.f; }
+    }
+    const int64_t lp = (int64_t)(y - a.y0) * W + (x - a.x0);
+    out[3 * lp] = c[0]; out[3 * lp + 1] = c[1]; out[3 * lp + 2] = c[2];
+}
+
 }  // namespace
 
 bool b2rt_filter_valid(const b2rt_filter *f) {
@@ -138,8 +212,21 @@ int b2rt_film_impl(b2rt_ctx *ctx, const b2rt_filter *f, const int32_t cells[4], 
     a.cx0 = cells[0]; a.cy0 = cells[1]; a.cx1 = cells[2]; a.cy1 = cells[3]; a.spp = spp;
     a.x0 = pixels[0]; a.y0 = pixels[1]; a.x1 = pixels[2]; a.y1 = pixels[3];
     const int64_t np = (int64_t)(a.x1 - a.x0) * (a.y1 - a.y0);
-    film_filter_kernel<<<(unsigned)((np + 127) / 128), 128, 0, ctx->stream>>>(tab, a, reinterpret_cast<const float2 *>(d_xy),
-                                                                             d_rgb, d_out);
+    // tiled kernel when one staged cell row fits in shared memory (5 floats per sample), else one thread per pixel
+    const int pitch = (FILM_TW + 2 * a.hx) | 1;
+    const size_t smem = (size_t)pitch * spp * 5 * sizeof(float);
+    if (ctx->film_variant != 0 && smem <= 160 * 1024) {
+        if (smem > 48 * 1024 && smem > ctx->film_smem_opt_in) {
+            B2RT_CUDA(ctx, cudaFuncSetAttribute(film_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            ctx->film_smem_opt_in = smem;
+        }
+        dim3 grid((unsigned)((a.x1 - a.x0 + FILM_TW - 1) / FILM_TW), (unsigned)((a.y1 - a.y0 + FILM_TH - 1) / FILM_TH));
+        film_tile_kernel<<<grid, dim3(FILM_TW, FILM_TH), smem, ctx->stream>>>(tab, a, reinterpret_cast<const float2 *>(d_xy),
+                                                                              d_rgb, d_out, pitch);
+    } else {
+        film_filter_kernel<<<(unsigned)((np + 127) / 128), 128, 0, ctx->stream>>>(tab, a, reinterpret_cast<const float2 *>(d_xy),
+                                                                                 d_rgb, d_out);
+    }
     B2RT_LAUNCH_CHECK(ctx);
     return B2RT_OK;
 }

@@ -28,13 +28,38 @@ def test_film_kernel_matches_oracle_and_pbrt_golden_bit_for_bit(case):
     assert np.array_equal(img.view(np.uint32), load_golden("film")["film_%d" % case].view(np.uint32))
 
 
-def test_film_kernel_at_frame_size_against_oracle():
-    # 1920x1080, 2 spp, mitchell: 4.2 M samples; the oracle finishes in seconds
+@pytest.mark.parametrize("variant", ["1", "0"])
+def test_film_kernel_at_frame_size_against_oracle(variant, monkeypatch):
+    # 1920x1080, 2 spp, mitchell: 4.2 M samples; the oracle finishes in seconds.  Variant 1 = shared-memory tiles
+    # (default), 0 = one thread per pixel; B2RT_FILM_VARIANT is read when the context is created
+    monkeypatch.setenv("B2RT_FILM_VARIANT", variant)
     gf, of = _flt("mitchell", {})
     cells, xy, rgb, px = F.make_samples(of, 1920, 1080, 2, None, seed=9)
     with b2rt.Context(0) as c:
         img = c.film_reconstruct(gf, cells, 2, xy, rgb, px)
     ref = O.film(of, cells, 2, xy, rgb, px)
+    assert np.array_equal(img.view(np.uint32), ref.view(np.uint32))
+
+
+@pytest.mark.parametrize("case", range(len(F.CASES)))
+def test_film_per_pixel_variant_matches_golden(case, monkeypatch):
+    monkeypatch.setenv("B2RT_FILM_VARIANT", "0")
+    name, kw, xres, yres, spp, window = F.CASES[case]
+    gf, of = _flt(name, kw)
+    cells, xy, rgb, px = F.make_samples(of, xres, yres, spp, window, seed=100 + case)
+    with b2rt.Context(0) as c:
+        img = c.film_reconstruct(gf, cells, spp, xy, rgb, px)
+    assert np.array_equal(img.view(np.uint32), load_golden("film")["film_%d" % case].view(np.uint32))
+
+
+def test_film_wide_filter_and_many_samples_per_pixel():
+    # sinc of width 6.5 (halo 7) and 40 spp: a staged cell row is 47 x 40 samples = 37 KB of shared memory; odd sizes
+    gf = b2rt.pbrt_filter("sinc", xwidth=6.5, ywidth=3.0, tau=2.0)
+    of = O.filter_args("sinc", xwidth=6.5, ywidth=3.0, tau=2.0)
+    cells, xy, rgb, px = F.make_samples(of, 77, 45, 40, (5, 3, 70, 41), seed=21)
+    with b2rt.Context(0) as c:
+        img = c.film_reconstruct(gf, cells, 40, xy, rgb, px)
+    ref = O.film(of, cells, 40, xy, rgb, px)
     assert np.array_equal(img.view(np.uint32), ref.view(np.uint32))
 
 

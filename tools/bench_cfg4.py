@@ -32,6 +32,8 @@ mat = ctx.add_material(S.MATTE, (0.7, 0.7, 0.7), (0, 0, 0), 1.5)
 ctx.add_mesh(P, idx, material=mat)
 ctx.add_light(0, (30.0, 30.0, 30.0), p=(0.5, 3.0, 0.5))
 info = ctx.build_accel()
+if os.environ.get("FILTER"):                 # pbrt PixelFilter name: box / triangle / gaussian / mitchell / sinc
+    ctx.set_filter(b2rt.pbrt_filter(os.environ["FILTER"]))
 cam = b2rt.pbrt_camera((0, 1.2, 2.5), (0, 0, 0), (0, 1, 0), 45, xres, yres)
 kw = dict(spp=spp, caustic=False, indirect=False, direct=True)
 

@@ -19,6 +19,8 @@ desc = S.cornell_scene(spheres=True, boxes=False, wide=1.78)
 with b2rt.Context(0, seed=3) as ctx:
     S.fill_scene(ctx, desc)
     ctx.build_accel()
+    if os.environ.get("FILTER"):             # pbrt PixelFilter name: box / triangle / gaussian / mitchell / sinc
+        ctx.set_filter(b2rt.pbrt_filter(os.environ["FILTER"]))
     cam = b2rt.pbrt_camera((0, 1, 3.4), (0, 1, 0), (0, 1, 0), 40, xres, yres)
     frame_out = ctx.pinned_empty((yres, xres, 3))
     for rep in range(reps):

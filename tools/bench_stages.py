@@ -17,7 +17,7 @@ peak = 6650.0
 pk = os.path.join(ROOT, "MEASURED_PEAKS.json")
 if os.path.exists(pk):
     peak = json.load(open(pk)).get("hbm_gbs", peak)
-out = {"peak_gbs": peak, "sort": [], "lbvh_build": [], "grid_build": []}
+out = {"peak_gbs": peak, "sort": [], "lbvh_build": [], "grid_build": [], "film": []}
 
 
 def med(f, reps=7):
@@ -79,4 +79,34 @@ with b2rt.Context(0, seed=3) as ctx:
         gbs = n * 204 / (ms * 1e-3) / 1e9
         out["grid_build"].append({"n_photons": int(n), "build_ms": ms, "Mphotons_per_s": n / ms / 1e3, "cells": list(gs[-1].dims),
                                   "algorithmic_GBs": gbs, "frac_of_peak": gbs / peak})
+# ---- K13: film reconstruction, 20 B / sample (position + radiance) + 12 B / pixel; every sample is re-read by the
+# (2h+1)^2 pixels whose support it may touch, out of L2 --------------------------------------------------------------
+with b2rt.Context(0, seed=1) as ctx:
+    stream = torch.cuda.ExternalStream(ctx.stream, device=0)
+    for name, xres, yres, spp in (("box", 1920, 1080, 4), ("mitchell", 1920, 1080, 4), ("mitchell", 3840, 2160, 16),
+                                  ("gaussian", 3840, 2160, 16), ("sinc", 1920, 1080, 4)):
+        flt = b2rt.pbrt_filter(name)
+        h = int(np.floor(flt.xwidth + 0.5))
+        cells = (-h, -h, xres + h, yres + h)
+        cw, ch = cells[2] - cells[0], cells[3] - cells[1]
+        n = cw * ch * spp
+        with torch.cuda.stream(stream):
+            cx = torch.arange(cells[0], cells[2], device="cuda", dtype=torch.float32).view(1, cw, 1).expand(ch, cw, spp)
+            cy = torch.arange(cells[1], cells[3], device="cuda", dtype=torch.float32).view(ch, 1, 1).expand(ch, cw, spp)
+            xy = (torch.stack([cx, cy], -1) + torch.rand(ch, cw, spp, 2, device="cuda")).reshape(n, 2).contiguous()
+            rgb = torch.rand(n, 3, device="cuda")
+            img = torch.empty(yres, xres, 3, device="cuda")
+        ctx.sync()
+
+        def one():
+            ctx.timer_start()
+            ctx.film_reconstruct_device(flt, cells, spp, xy.data_ptr(), rgb.data_ptr(), (0, 0, xres, yres), img.data_ptr())
+            return ctx.timer_stop()
+        one()
+        ms = med(one)
+        gbs = (n * 20 + xres * yres * 12) / (ms * 1e-3) / 1e9
+        out["film"].append({"filter": name, "xres": xres, "yres": yres, "spp": spp, "samples": n, "ms": ms,
+                            "Msamples_per_s": n / ms / 1e3, "algorithmic_GBs": gbs, "frac_of_peak": gbs / peak,
+                            "mean": float(img.mean().item())})
+        del xy, rgb, img
 print(json.dumps(out))
