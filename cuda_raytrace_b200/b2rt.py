@@ -502,3 +502,29 @@ def _film_reconstruct_device(self, flt, cells, spp, xy_ptr, rgb_ptr, pixels, out
 Context.set_filter = _set_filter
 Context.film_reconstruct = _film_reconstruct
 Context.film_reconstruct_device = _film_reconstruct_device
+
+
+# ---- image-plane sample patterns ----------------------------------------------------------------------------------------
+SYMBOLS += ["b2rt_sampler_set", "b2rt_sample_positions"]
+SAMPLERS = {"random": 0, "stratified": 1, "lowdiscrepancy": 2}
+
+
+def _set_sampler(self, name="random", xsamples=1, ysamples=1):
+    """pbrt `Sampler "name"`: random (default), stratified (xsamples * ysamples must equal spp) or lowdiscrepancy."""
+    self.lib.b2rt_sampler_set.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32]
+    self._ck(self.lib.b2rt_sampler_set(self.h, SAMPLERS[name] if isinstance(name, str) else int(name), int(xsamples), int(ysamples)))
+
+
+def _sample_positions(self, xres, yres, window, spp):
+    """(cells * spp, 2) raster positions of the camera samples of window = (x0, y0, x1, y1), cell-major."""
+    n = (window[2] - window[0]) * (window[3] - window[1]) * spp
+    out = np.zeros((max(n, 0), 2), np.float32)
+    w4 = (C.c_int32 * 4)(*[int(v) for v in window])
+    self.lib.b2rt_sample_positions.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c_int32), C.c_int32, C.c_void_p,
+                                               C.c_int]
+    self._ck(self.lib.b2rt_sample_positions(self.h, int(xres), int(yres), w4, int(spp), _ptr(out), HOST))
+    return out
+
+
+Context.set_sampler = _set_sampler
+Context.sample_positions = _sample_positions

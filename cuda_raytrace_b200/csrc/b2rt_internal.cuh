@@ -130,6 +130,7 @@ struct b2rt_ctx {
     DevBuf d_samples, d_qslots, d_qcnt, d_q_rgb2, d_frame;
     DevBuf d_film_xy, d_film_rgb;       // per-sample raster positions / radiance of a frame reconstructed with a pixel filter
     b2rt_filter film_filter = {B2RT_FILTER_BOX, 0.5f, 0.5f, 0.f, 0.f};   // b2rt_film_set_filter
+    int sampler_type = B2RT_SAMPLER_RANDOM, sampler_nx = 1, sampler_ny = 1;   // b2rt_sampler_set
     int film_variant = 1;               // 1: shared-memory tiles (film_tile_kernel), 0: one thread per pixel (B2RT_FILM_VARIANT)
     size_t film_smem_opt_in = 0;
     PhotonMap maps[2];       // B2RT_MAP_CAUSTIC, B2RT_MAP_INDIRECT
@@ -167,6 +168,7 @@ int b2rt_photons_trace_impl(b2rt_ctx *ctx, int64_t first_path, int64_t n_paths, 
                             int64_t n_stored[2]);
 int b2rt_photon_grid_build_impl(b2rt_ctx *ctx, int map, float cell_size, float target_per_cell);
 int b2rt_render_impl(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_params *fp, float *d_out);
+int b2rt_sample_positions_impl(b2rt_ctx *ctx, int xres, int yres, const int32_t window[4], int spp, float *d_xy);
 bool b2rt_filter_valid(const b2rt_filter *f);
 void b2rt_filter_halo(const b2rt_filter *f, int *hx, int *hy);
 int b2rt_film_impl(b2rt_ctx *ctx, const b2rt_filter *f, const int32_t cells[4], int32_t spp, const float *d_xy,

@@ -241,6 +241,41 @@ int b2rt_film_set_filter(b2rt_ctx *ctx, const b2rt_filter *f) {
     return B2RT_OK;
 }
 
+int b2rt_sampler_set(b2rt_ctx *ctx, int32_t type, int32_t xsamples, int32_t ysamples) {
+    if (!ctx) return B2RT_E_ARG;
+    if (type < B2RT_SAMPLER_RANDOM || type > B2RT_SAMPLER_LOWDISCREPANCY ||
+        (type == B2RT_SAMPLER_STRATIFIED && (xsamples < 1 || ysamples < 1))) {
+        ctx->err = "sampler_set: bad arguments"; return B2RT_E_ARG;
+    }
+    ctx->sampler_type = type;
+    ctx->sampler_nx = type == B2RT_SAMPLER_STRATIFIED ? xsamples : 1;
+    ctx->sampler_ny = type == B2RT_SAMPLER_STRATIFIED ? ysamples : 1;
+    return B2RT_OK;
+}
+
+int b2rt_sample_positions(b2rt_ctx *ctx, int32_t xres, int32_t yres, const int32_t window[4], int32_t spp, float *xy,
+                          int where) {
+    if (!ctx) return B2RT_E_ARG;
+    if (!window || !xy || spp < 1 || xres < 1 || yres < 1 || window[0] >= window[2] || window[1] >= window[3] ||
+        window[0] < -64 || window[1] < -64 || window[2] > xres + 64 || window[3] > yres + 64) {
+        ctx->err = "sample_positions: bad arguments"; return B2RT_E_ARG;
+    }
+    B2RT_CUDA(ctx, cudaSetDevice(ctx->device));
+    const int64_t n = (int64_t)(window[2] - window[0]) * (window[3] - window[1]) * spp;
+    float *d_xy = xy;
+    if (where != B2RT_DEVICE) {
+        B2RT_CUDA(ctx, ctx->d_film_xy.reserve((size_t)n * 8));
+        d_xy = ctx->d_film_xy.as<float>();
+    }
+    int rc = b2rt_sample_positions_impl(ctx, xres, yres, window, spp, d_xy);
+    if (rc) return rc;
+    if (where != B2RT_DEVICE) {
+        B2RT_CUDA(ctx, cudaMemcpyAsync(xy, d_xy, (size_t)n * 8, cudaMemcpyDeviceToHost, ctx->stream));
+        B2RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    }
+    return B2RT_OK;
+}
+
 int b2rt_film_reconstruct(b2rt_ctx *ctx, const b2rt_filter *f, const int32_t cells[4], int32_t spp, const float *xy,
                           const float *rgb, const int32_t pixels[4], float *out_rgb, int where) {
     if (!ctx) return B2RT_E_ARG;

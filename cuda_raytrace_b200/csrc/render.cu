@@ -105,11 +105,56 @@ __device__ f3 direct_lighting(const DScene &sc, const Surface &s, const Mat &m, 
 
 struct TreeNode { f3 o, d; float tmin; f3 T; int depth; uint32_t id; };
 
+// ---- K14 image-plane sample patterns: where inside its pixel sample k lies ------------------------------------------
+struct SamplerD { int type, nx, ny; };
+constexpr float ONE_MINUS_EPS = 0.9999999403953552f;          // core/montecarlo.h:48
+// (0,2)-sequence, pbrt Sample02 = VanDerCorput + Sobol2 with one random scramble each (core/montecarlo.h:272-295)
+__host__ __device__ __forceinline__ float ld_vdc(uint32_t n, uint32_t scramble) {
+    n = (n << 16) | (n >> 16);
+    n = ((n & 0x00ff00ffu) << 8) | ((n & 0xff00ff00u) >> 8);
+    n = ((n & 0x0f0f0f0fu) << 4) | ((n & 0xf0f0f0f0u) >> 4);
+    n = ((n & 0x33333333u) << 2) | ((n & 0xccccccccu) >> 2);
+    n = ((n & 0x55555555u) << 1) | ((n & 0xaaaaaaaau) >> 1);
+    n ^= scramble;
+    return fminf((float)((n >> 8) & 0xffffffu) / (float)(1 << 24), ONE_MINUS_EPS);
+}
+__host__ __device__ __forceinline__ float ld_sobol2(uint32_t n, uint32_t scramble) {
+    for (uint32_t v = 1u << 31; n != 0; n >>= 1, v ^= v >> 1)
+        if (n & 1u) scramble ^= v;
+    return fminf((float)((scramble >> 8) & 0xffffffu) / (float)(1 << 24), ONE_MINUS_EPS);
+}
+// offset of sample k inside pixel `gpix`.  random: two Philox uniforms (pbrt "random").  stratified: stratum
+// (k % nx, k / nx) with a Philox jitter, StratifiedSample2D (core/montecarlo.cpp:158-168; pbrt "stratified",
+// samplers/stratified.cpp:79-82).  lowdiscrepancy: point k of a (0,2)-sequence whose two scrambles are the pixel's own
+// Philox words - LDShuffleScrambled2D without its shuffle, which only permutes the order inside the pixel
+// (core/montecarlo.h:317-325, pbrt "lowdiscrepancy", samplers/lowdiscrepancy.cpp:67-79).
+__device__ __forceinline__ float2 pixel_offset(const SamplerD &sm, uint32_t gpix, uint32_t k, uint32_t k0, uint32_t k1) {
+    if (sm.type == B2RT_SAMPLER_LOWDISCREPANCY) {
+        const u4 sc = philox4x32_10(gpix, 0xffffffffu, 1u, 0u, k0, k1);
+        return make_float2(ld_vdc(k, sc.x), ld_sobol2(k, sc.y));
+    }
+    const u4 rj = philox4x32_10(gpix, k, 0u, 0u, k0, k1);
+    if (sm.type == B2RT_SAMPLER_STRATIFIED) {
+        const float dx = 1.f / (float)sm.nx, dy = 1.f / (float)sm.ny;
+        const int sx = (int)(k % (uint32_t)sm.nx), sy = (int)(k / (uint32_t)sm.nx);
+        return make_float2(fminf(((float)sx + u01(rj.x)) * dx, ONE_MINUS_EPS), fminf(((float)sy + u01(rj.y)) * dy, ONE_MINUS_EPS));
+    }
+    return make_float2(u01(rj.x), u01(rj.y));
+}
+__device__ __forceinline__ uint32_t global_pixel_id(int px, int py, int xres, int yres) {
+    uint32_t gpix = (uint32_t)py * (uint32_t)xres + (uint32_t)px;             // tiling-independent
+    // sample cells around the image (a pixel filter wider than the pixel reaches them, ImageFilm::GetSampleExtent):
+    // ids after the image's own, unique for cells up to 64 pixels outside
+    if (px < 0 || py < 0 || px >= xres || py >= yres)
+        gpix = (uint32_t)xres * (uint32_t)yres + (uint32_t)(py + 64) * (uint32_t)(xres + 128) + (uint32_t)(px + 64);
+    return gpix;
+}
+
 // K14 + K6 + K7.  sample s (chunk-local) -> pixel (crop-window row-major) and sample number k.
 __global__ void __launch_bounds__(RENDER_THREADS)
 render_li_kernel(DScene sc, b2rt_camera cam, b2rt_frame_params fp, uint32_t seed_lo, uint32_t seed_hi, int64_t first_sample,
                  int64_t n_samples, int slots, float *__restrict__ sample_rgb, b2rt_query *__restrict__ qslots,
-                 uint32_t *__restrict__ qcnt, uint32_t *status, float2 *__restrict__ sample_xy) {
+                 uint32_t *__restrict__ qcnt, uint32_t *status, float2 *__restrict__ sample_xy, SamplerD sm) {
     int64_t ls = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (ls >= n_samples) return;
     const int64_t s = first_sample + ls;
@@ -117,14 +162,10 @@ render_li_kernel(DScene sc, b2rt_camera cam, b2rt_frame_params fp, uint32_t seed
     const int64_t pix = s / fp.spp;
     const int k = (int)(s % fp.spp);
     const int px = fp.x0 + (int)(pix % cw), py = fp.y0 + (int)(pix / cw);
-    uint32_t gpix = (uint32_t)py * (uint32_t)cam.xres + (uint32_t)px;          // global pixel id: tiling-independent
-    // sample cells around the image (a pixel filter wider than the pixel reaches them, ImageFilm::GetSampleExtent):
-    // ids after the image's own, unique for cells up to 64 pixels outside
-    if (px < 0 || py < 0 || px >= cam.xres || py >= cam.yres)
-        gpix = (uint32_t)cam.xres * (uint32_t)cam.yres + (uint32_t)(py + 64) * (uint32_t)(cam.xres + 128) + (uint32_t)(px + 64);
+    const uint32_t gpix = global_pixel_id(px, py, cam.xres, cam.yres);
     const uint32_t k0 = seed_lo ^ 0x43414d52u, k1 = seed_hi;                     // 'CAMR' stream
-    u4 rj = philox4x32_10(gpix, (uint32_t)k, 0u, 0u, k0, k1);
-    const float fx = (float)px + u01(rj.x), fy = (float)py + u01(rj.y);
+    const float2 off = pixel_offset(sm, gpix, (uint32_t)k, k0, k1);
+    const float fx = (float)px + off.x, fy = (float)py + off.y;
     if (sample_xy) sample_xy[ls] = make_float2(fx, fy);
     f3 d0 = mk3(cam.A[0] + fx * cam.B[0] + fy * cam.C[0], cam.A[1] + fx * cam.B[1] + fy * cam.C[1],
                 cam.A[2] + fx * cam.B[2] + fy * cam.C[2]);
@@ -255,7 +296,34 @@ sample_resolve_kernel(const float *__restrict__ sample_rgb, const uint32_t *__re
     out_rgb[3 * ls] = L.x; out_rgb[3 * ls + 1] = L.y; out_rgb[3 * ls + 2] = L.z;
 }
 
+// parity hook: the raster positions of the camera samples of a crop window, sample-major as the camera pass walks them
+__global__ void __launch_bounds__(256)
+sample_positions_kernel(int xres, int yres, int x0, int y0, int cw, int spp, uint32_t seed_lo, uint32_t seed_hi, int64_t n,
+                        SamplerD sm, float2 *__restrict__ out) {
+    int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    const int64_t pix = s / spp;
+    const int k = (int)(s % spp);
+    const int px = x0 + (int)(pix % cw), py = y0 + (int)(pix / cw);
+    const float2 off = pixel_offset(sm, global_pixel_id(px, py, xres, yres), (uint32_t)k, seed_lo ^ 0x43414d52u, seed_hi);
+    out[s] = make_float2((float)px + off.x, (float)py + off.y);
+}
+
 }  // namespace
+
+int b2rt_sample_positions_impl(b2rt_ctx *ctx, int xres, int yres, const int32_t window[4], int spp, float *d_xy) {
+    SamplerD sm = {ctx->sampler_type, ctx->sampler_nx, ctx->sampler_ny};
+    if (sm.type == B2RT_SAMPLER_STRATIFIED && (int64_t)sm.nx * sm.ny != spp) {
+        ctx->err = "sample_positions: stratified sampler needs xsamples * ysamples == spp"; return B2RT_E_ARG;
+    }
+    const int cw = window[2] - window[0];
+    const int64_t n = (int64_t)cw * (window[3] - window[1]) * spp;
+    sample_positions_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(
+        xres, yres, window[0], window[1], cw, spp, (uint32_t)ctx->seed, (uint32_t)(ctx->seed >> 32), n, sm,
+        reinterpret_cast<float2 *>(d_xy));
+    B2RT_LAUNCH_CHECK(ctx);
+    return B2RT_OK;
+}
 
 // d_out: device buffer of (x1-x0)*(y1-y0)*3 floats, crop-window row-major
 int b2rt_render_impl(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_params *fp, float *d_out) {
@@ -284,6 +352,10 @@ int b2rt_render_impl(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_par
         if (hx > 64 || hy > 64) { ctx->err = "render_frame: filter too wide"; return B2RT_E_ARG; }
         p.x0 -= hx; p.x1 += hx; p.y0 -= hy; p.y1 += hy;
     }
+    SamplerD sm = {ctx->sampler_type, ctx->sampler_nx, ctx->sampler_ny};
+    if (sm.type == B2RT_SAMPLER_STRATIFIED && (int64_t)sm.nx * sm.ny != fp->spp) {
+        ctx->err = "render_frame: stratified sampler needs xsamples * ysamples == spp"; return B2RT_E_ARG;
+    }
     const int64_t n_cells = (int64_t)(p.x1 - p.x0) * (p.y1 - p.y0);
     if (filtered) {
         B2RT_CUDA(ctx, ctx->d_film_xy.reserve((size_t)n_cells * fp->spp * 8));
@@ -308,7 +380,7 @@ int b2rt_render_impl(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_par
         render_li_kernel<<<(unsigned)((ns + RENDER_THREADS - 1) / RENDER_THREADS), RENDER_THREADS, 0, st>>>(
             sc, *cam, p, (uint32_t)ctx->seed, (uint32_t)(ctx->seed >> 32), p0 * fp->spp, ns, slots,
             ctx->d_samples.as<float>(), ctx->d_qslots.as<b2rt_query>(), qcnt, counters + 8,
-            filtered ? ctx->d_film_xy.as<float2>() + p0 * fp->spp : nullptr);
+            filtered ? ctx->d_film_xy.as<float2>() + p0 * fp->spp : nullptr, sm);
         B2RT_LAUNCH_CHECK(ctx);
         int rc = b2rt_exclusive_scan_u32(ctx, qcnt, ns, counters + 12);
         if (rc) return rc;

@@ -248,7 +248,9 @@ def to_pbrt(desc, eye, look, up, fov, xres, yres, spp, integrator, filename, ren
     L = ["LookAt %g %g %g  %g %g %g  %g %g %g" % (*eye, *look, *up),
          'Camera "perspective" "float fov" [%g]' % fov,
          'Film "image" "integer xresolution" [%d] "integer yresolution" [%d] "string filename" ["%s"]' % (xres, yres, filename),
-         'Sampler "%s" "integer pixelsamples" [%d]' % (sampler, spp), 'PixelFilter ' + pixelfilter, integrator]
+         ('Sampler "stratified" "integer xsamples" [%d] "integer ysamples" [%d]' % (int(round(spp ** 0.5)), int(round(spp ** 0.5)))
+          if sampler == "stratified" else 'Sampler "%s" "integer pixelsamples" [%d]' % (sampler, spp)),
+         'PixelFilter ' + pixelfilter, integrator]
     if renderer:
         L.append(renderer if renderer.startswith("Renderer") else 'Renderer "%s"' % renderer)
     L.append("WorldBegin")

@@ -173,6 +173,18 @@ typedef struct {
  * grids built if use_caustic / use_indirect are set (maps that are empty or unbuilt contribute nothing). */
 int b2rt_render_frame(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_params *fp, float *out_rgb, int where);
 
+/* ---- image-plane samples: replaces the CPU sample loop PbrtCamera::preLaunch (cuda_render/util/camera/pbrtcamera.cpp:
+ * 57-122), which pulls every CameraSample out of pbrt's Sampler and uploads 72 bytes per ray.  The pattern of
+ * b2rt_render_frame's samples inside each pixel: pbrt "random" (the default), "stratified" (xsamples * ysamples = spp
+ * jittered strata, core/montecarlo.cpp:158-168) or "lowdiscrepancy" (a scrambled (0,2)-sequence per pixel,
+ * core/montecarlo.h:272-295,317-325).  Randomness is Philox(seed, pixel, sample): tiling-independent. ---- */
+enum { B2RT_SAMPLER_RANDOM = 0, B2RT_SAMPLER_STRATIFIED = 1, B2RT_SAMPLER_LOWDISCREPANCY = 2 };
+int b2rt_sampler_set(b2rt_ctx *ctx, int32_t type, int32_t xsamples, int32_t ysamples);
+/* parity hook: the continuous raster positions (imageX, imageY) of the samples of window = {x0, y0, x1, y1} (cells may
+ * lie up to 64 pixels outside the xres x yres image, as a filtered frame's halo does); xy[cells * spp * 2], cell-major */
+int b2rt_sample_positions(b2rt_ctx *ctx, int32_t xres, int32_t yres, const int32_t window[4], int32_t spp, float *xy,
+                          int where);
+
 /* ---- film: replaces the reference's CPU film loop, camera->film->AddSample for every launch sample
  * (cuda_render/photon_mapping/photonmappingrenderer.cpp:247-273, simple_render/simplerender.cpp:84-100), i.e. pbrt's
  * ImageFilm::AddSample + the normalisation in ImageFilm::WriteImage (pbrt-v2/src/film/image.cpp:77-137,178-213) with

@@ -514,3 +514,41 @@ def ref_film(flt, xres, yres, xy, rgb, pixels=None):
         path = os.path.join(d, "film.pfm")
         lib.ref_film(flt[0], flt[1], flt[2], flt[3], flt[4], xres, yres, _p(crop), len(s), _p(s), path.encode())
         return read_pfm(path)
+
+
+# ---- image-plane sample patterns (oracle_film.c port_sample_positions; reference: pbrt's Sample02 / StratifiedSample2D)
+SAMPLERS = {"random": 0, "stratified": 1, "lowdiscrepancy": 2}
+
+
+def sample_positions(sampler, seed, xres, yres, window, spp, nx=1, ny=1):
+    """window = (x0, y0, x1, y1) sample cells; returns (cells * spp, 2) raster positions, cell-major."""
+    lib = port()
+    lib.port_sample_positions.argtypes = [C.c_int] * 3 + [C.c_uint64] + [C.c_int] * 7 + [C.c_void_p]
+    lib.port_sample_positions.restype = None
+    n = (window[2] - window[0]) * (window[3] - window[1]) * spp
+    out = np.zeros((n, 2), np.float32)
+    lib.port_sample_positions(SAMPLERS[sampler], nx, ny, seed, xres, yres, *[int(v) for v in window], spp, _p(out))
+    return out
+
+
+def ld_point(n, s0, s1):
+    lib = port()
+    lib.port_vdc.restype = lib.port_sobol2.restype = C.c_float
+    lib.port_vdc.argtypes = lib.port_sobol2.argtypes = [C.c_uint32, C.c_uint32]
+    return np.float32(lib.port_vdc(n, s0)), np.float32(lib.port_sobol2(n, s1))
+
+
+def ref_ld_point(n, s0, s1):
+    lib = C.CDLL(REF_SO)
+    lib.ref_sample02.argtypes = [C.c_uint, C.c_uint, C.c_uint, C.c_void_p]
+    out = np.zeros(2, np.float32)
+    lib.ref_sample02(n, s0, s1, _p(out))
+    return out[0], out[1]
+
+
+def ref_stratified_centres(nx, ny):
+    lib = C.CDLL(REF_SO)
+    lib.ref_stratified_centres.argtypes = [C.c_int, C.c_int, C.c_void_p]
+    out = np.zeros((nx * ny, 2), np.float32)
+    lib.ref_stratified_centres(nx, ny, _p(out))
+    return out

@@ -113,3 +113,60 @@ void port_film(int type, float xw, float yw, float p0, float p1, int cx0, int cy
     }
     free(acc);
 }
+
+/* ---- image-plane sample patterns (K14): restatement of the per-pixel offsets of csrc/render.cu pixel_offset ----------
+ *   random          two Philox uniforms
+ *   stratified      StratifiedSample2D, pbrt-v2/src/core/montecarlo.cpp:158-168 (jitter = Philox uniforms)
+ *   lowdiscrepancy  Sample02 = VanDerCorput + Sobol2, pbrt-v2/src/core/montecarlo.h:272-295, scrambles = Philox words
+ * Pin: pbrt's own VanDerCorput / Sobol2 / StratifiedSample2D through oracle/ref_film.cpp (tests/test_oracle_film_cpu.py). */
+void port_philox(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1, uint32_t out[4]);
+static const float ONE_MINUS_EPS = 0.9999999403953552f;
+
+float port_vdc(uint32_t n, uint32_t scramble) {
+    n = (n << 16) | (n >> 16);
+    n = ((n & 0x00ff00ffu) << 8) | ((n & 0xff00ff00u) >> 8);
+    n = ((n & 0x0f0f0f0fu) << 4) | ((n & 0xf0f0f0f0u) >> 4);
+    n = ((n & 0x33333333u) << 2) | ((n & 0xccccccccu) >> 2);
+    n = ((n & 0x55555555u) << 1) | ((n & 0xaaaaaaaau) >> 1);
+    n ^= scramble;
+    float v = (float)((n >> 8) & 0xffffffu) / (float)(1 << 24);
+    return v < ONE_MINUS_EPS ? v : ONE_MINUS_EPS;
+}
+float port_sobol2(uint32_t n, uint32_t scramble) {
+    for (uint32_t v = 1u << 31; n != 0; n >>= 1, v ^= v >> 1)
+        if (n & 1u) scramble ^= v;
+    float r = (float)((scramble >> 8) & 0xffffffu) / (float)(1 << 24);
+    return r < ONE_MINUS_EPS ? r : ONE_MINUS_EPS;
+}
+static float u01f(uint32_t x) { return (float)(x >> 8) * 5.9604644775390625e-8f; }
+
+/* type 0 random, 1 stratified (nx * ny == spp), 2 lowdiscrepancy; window = sample cells, out xy[cells * spp * 2] */
+void port_sample_positions(int type, int nx, int ny, uint64_t seed, int xres, int yres, int x0, int y0, int x1, int y1,
+                           int spp, float *out) {
+    const uint32_t k0 = (uint32_t)seed ^ 0x43414d52u, k1 = (uint32_t)(seed >> 32);
+    int64_t s = 0;
+    for (int py = y0; py < y1; ++py)
+        for (int px = x0; px < x1; ++px) {
+            uint32_t gpix = (uint32_t)py * (uint32_t)xres + (uint32_t)px;
+            if (px < 0 || py < 0 || px >= xres || py >= yres)
+                gpix = (uint32_t)xres * (uint32_t)yres + (uint32_t)(py + 64) * (uint32_t)(xres + 128) + (uint32_t)(px + 64);
+            for (int k = 0; k < spp; ++k, ++s) {
+                uint32_t r[4];
+                float ox, oy;
+                if (type == 2) {
+                    port_philox(gpix, 0xffffffffu, 1u, 0u, k0, k1, r);
+                    ox = port_vdc((uint32_t)k, r[0]); oy = port_sobol2((uint32_t)k, r[1]);
+                } else {
+                    port_philox(gpix, (uint32_t)k, 0u, 0u, k0, k1, r);
+                    if (type == 1) {
+                        const float dx = 1.f / (float)nx, dy = 1.f / (float)ny;
+                        const int sx = k % nx, sy = k / nx;
+                        ox = ((float)sx + u01f(r[0])) * dx; oy = ((float)sy + u01f(r[1])) * dy;
+                        if (!(ox < ONE_MINUS_EPS)) ox = ONE_MINUS_EPS;
+                        if (!(oy < ONE_MINUS_EPS)) oy = ONE_MINUS_EPS;
+                    } else { ox = u01f(r[0]); oy = u01f(r[1]); }
+                }
+                out[2 * s] = (float)px + ox; out[2 * s + 1] = (float)py + oy;
+            }
+        }
+}

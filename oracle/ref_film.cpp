@@ -38,3 +38,17 @@ int ref_film(int type, float xw, float yw, float p0, float p1, int xres, int yre
 }
 
 }
+
+// pbrt's own (0,2)-sequence point and stratified strata centres (core/montecarlo.h:272-295, montecarlo.cpp:158-168)
+#include "montecarlo.h"
+#include "rng.h"
+extern "C" {
+void ref_sample02(unsigned n, unsigned s0, unsigned s1, float out[2]) {
+    uint32_t sc[2] = {s0, s1};
+    Sample02(n, sc, out);
+}
+void ref_stratified_centres(int nx, int ny, float *out) {
+    RNG rng(1);
+    StratifiedSample2D(out, nx, ny, rng, false);
+}
+}

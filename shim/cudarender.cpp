@@ -24,6 +24,8 @@
 #include "lights/point.h"
 #include "lights/diffuse.h"
 #include "film/image.h"
+#include "samplers/stratified.h"
+#include "samplers/lowdiscrepancy.h"
 #include "filters/box.h"
 #include "filters/triangle.h"
 #include "filters/gaussian.h"
@@ -326,6 +328,18 @@ static void writeFilm(Camera *camera, ImageFilm *film, const std::vector<float> 
     camera->film->WriteImage();
 }
 
+// The scene's `Sampler`: its pattern inside the pixel is reproduced on the GPU (b2rt_sampler_set) instead of pulling
+// every CameraSample through Sampler::GetMoreSamples on the CPU as the reference does (pbrtcamera.cpp:57-122).
+// stratified's strata counts are private members (samplers/stratified.h:56; this file has -fno-access-control).
+static void useSampler(b2rt_ctx *ctx, Sampler *sampler) {
+    int rc = B2RT_OK;
+    if (StratifiedSampler *st = dynamic_cast<StratifiedSampler *>(sampler))
+        rc = b2rt_sampler_set(ctx, B2RT_SAMPLER_STRATIFIED, st->xPixelSamples, st->yPixelSamples);
+    else if (dynamic_cast<LDSampler *>(sampler)) rc = b2rt_sampler_set(ctx, B2RT_SAMPLER_LOWDISCREPANCY, 1, 1);
+    else rc = b2rt_sampler_set(ctx, B2RT_SAMPLER_RANDOM, 1, 1);       // "random" and the samplers the GPU path has no pattern for
+    if (rc != B2RT_OK) b2rt_sampler_set(ctx, B2RT_SAMPLER_RANDOM, 1, 1);
+}
+
 static b2rt_frame_params frameParams(const b2rt_camera &cam, Sampler *sampler) {
     b2rt_frame_params fp;
     memset(&fp, 0, sizeof(fp));
@@ -343,6 +357,7 @@ void SimpleRenderer::render(const Scene *, CudaRender *cr, Camera *camera) {
     b2rt_frame_params fp = frameParams(cam, cr->sampler());
     std::vector<float> img((size_t)cam.xres * cam.yres * 3);
     ImageFilm *film = useFilmFilter(cr->ctx(), camera);
+    useSampler(cr->ctx(), cr->sampler());
     cr->check(b2rt_render_frame(cr->ctx(), &cam, &fp, img.data(), B2RT_HOST), "b2rt_render_frame");
     writeFilm(camera, film, img);
 }
@@ -372,6 +387,7 @@ void PhotonMappingRenderer::render(const Scene *scene, CudaRender *cr, Camera *c
     fp.use_caustic = nCaustic > 0; fp.use_indirect = nIndirect > 0;
     std::vector<float> img((size_t)cam.xres * cam.yres * 3);
     ImageFilm *film = useFilmFilter(ctx, camera);
+    useSampler(ctx, cr->sampler());
     cr->check(b2rt_render_frame(ctx, &cam, &fp, img.data(), B2RT_HOST), "b2rt_render_frame");
     writeFilm(camera, film, img);
 }

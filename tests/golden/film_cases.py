@@ -30,3 +30,18 @@ def make_samples(flt, xres, yres, spp, window, seed):
     xy = base + rng.random(base.shape, dtype=np.float32)
     rgb = (rng.random((len(xy), 3), dtype=np.float32) * np.float32(3)) ** 2
     return cells, xy, rgb, (x0, y0, x1, y1)
+
+
+def make_lattice_samples(flt, xres, yres, window=None):
+    """Edge cases of the extent arithmetic: 16 samples per cell on the lattice {0, 0.25, 0.5, 0.75}^2 - positions on
+    cell borders and pixel centres, where Ceil2Int / Floor2Int of imageX -+ width land exactly on integers."""
+    x0, y0, x1, y1 = window if window is not None else (0, 0, xres, yres)
+    hx, hy = halo(flt[1]), halo(flt[2])
+    cells = (x0 - hx, y0 - hy, x1 + hx, y1 + hy)
+    cx, cy = np.meshgrid(np.arange(cells[0], cells[2]), np.arange(cells[1], cells[3]))
+    base = np.stack([cx, cy], -1).reshape(-1, 1, 2).astype(np.float32)
+    off = np.stack(np.meshgrid(np.arange(4), np.arange(4)), -1).reshape(1, 16, 2).astype(np.float32) * np.float32(0.25)
+    xy = (base + off).reshape(-1, 2)
+    rng = np.random.default_rng(77)
+    rgb = rng.random((len(xy), 3), dtype=np.float32)
+    return cells, xy, rgb, (x0, y0, x1, y1)

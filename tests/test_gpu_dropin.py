@@ -15,14 +15,14 @@ BIN = os.path.join(ROOT, "shim", "_build", "pbrt_b2rt")
 EYE, LOOK, UP, FOV = (0, 1, 3.4), (0, 1, 0), (0, 1, 0), 40
 
 
-def _run(tmp_path, name, integrator, renderer, spp, res=96, pixelfilter='"box"'):
+def _run(tmp_path, name, integrator, renderer, spp, res=96, pixelfilter='"box"', sampler="lowdiscrepancy"):
     out = {}
     for tag, flag in (("gpu", ["-c"]), ("cpu", [])):
         pf = str(tmp_path / ("%s_%s.pfm" % (name, tag)))
         scene = str(tmp_path / ("%s_%s.pbrt" % (name, tag)))
         with open(scene, "w") as f:
             f.write(S.to_pbrt(S.cornell_scene(boxes=True), EYE, LOOK, UP, FOV, res, res, spp, integrator, pf, renderer=renderer,
-                              pixelfilter=pixelfilter))
+                              pixelfilter=pixelfilter, sampler=sampler))
         r = subprocess.run([BIN, "--quiet"] + flag + [scene], capture_output=True, text=True, timeout=600)
         assert r.returncode == 0, r.stderr[-2000:]
         out[tag] = S.read_pfm(pf)
@@ -70,3 +70,15 @@ def test_dropin_honours_the_scene_pixel_filter(tmp_path):
     assert edge > 0.02 * gbox.max(), edge
     # and per pixel the GPU image is closer to pbrt's Mitchell image than the box image is
     assert np.abs(gpu - cpu).mean() < np.abs(gbox - cpu).mean()
+
+
+@pytest.mark.skipif(not os.path.exists(BIN), reason="shim/_build/pbrt_b2rt not built (needs /root/reference)")
+@pytest.mark.parametrize("sampler", ["stratified", "random"])
+def test_dropin_follows_the_scene_sampler(tmp_path, sampler):
+    """`Sampler "stratified"` (16 x 16 strata) and `Sampler "random"`: the shim passes the pattern on with
+    b2rt_sampler_set; both backends converge to the same image."""
+    gpu, cpu = _run(tmp_path, sampler, 'SurfaceIntegrator "directlighting" "integer maxdepth" [5]', "simple", spp=256,
+                    res=64, sampler=sampler)
+    m = S.image_metrics(_block(gpu, 8), _block(cpu, 8))
+    assert abs(m["bias_rel"]) < 0.005, m
+    assert m["mean_rel"] < 0.012, m

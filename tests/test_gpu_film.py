@@ -128,3 +128,49 @@ def test_wide_box_filter_frame_equals_film_of_neighbouring_box_frames(rctx):
     assert abs(wide[inner].mean() - box[inner].mean()) <= 0.02 * box[inner].mean()
     inside = (wide >= lo - 1e-6) & (wide <= hi + 1e-6)
     assert inside[inner].mean() > 0.8
+
+
+@pytest.mark.parametrize("name,kw", [("box", {}), ("box", {"xwidth": 1.0, "ywidth": 0.75}), ("triangle", {}),
+                                     ("mitchell", {"xwidth": 1.5, "ywidth": 2.25})])
+@pytest.mark.parametrize("variant", ["1", "0"])
+def test_film_border_samples_match_oracle(name, kw, variant, monkeypatch):
+    # samples exactly on cell borders / pixel centres (the oracle is pinned to pbrt on the same set, CPU suite)
+    monkeypatch.setenv("B2RT_FILM_VARIANT", variant)
+    gf, of = _flt(name, kw)
+    cells, xy, rgb, px = F.make_lattice_samples(of, 13, 9, (1, 1, 12, 8))
+    with b2rt.Context(0) as c:
+        img = c.film_reconstruct(gf, cells, 16, xy, rgb, px)
+    assert np.array_equal(img.view(np.uint32), O.film(of, cells, 16, xy, rgb, px).view(np.uint32))
+
+
+# ---- image-plane sample patterns -----------------------------------------------------------------------------------------
+@pytest.mark.parametrize("sampler,nx,ny,spp", [("random", 1, 1, 5), ("stratified", 3, 2, 6), ("stratified", 4, 4, 16),
+                                               ("lowdiscrepancy", 1, 1, 8), ("lowdiscrepancy", 1, 1, 64)])
+def test_sample_positions_match_oracle_bit_for_bit(sampler, nx, ny, spp):
+    for seed, xres, yres, win in ((99, 12, 8, (-2, -1, 14, 9)), (2 ** 40 + 7, 640, 360, (100, 50, 300, 120))):
+        with b2rt.Context(0, seed=seed) as c:
+            c.set_sampler(sampler, nx, ny)
+            xy = c.sample_positions(xres, yres, win, spp)
+        ref = O.sample_positions(sampler, seed, xres, yres, win, spp, nx, ny)
+        assert np.array_equal(xy.view(np.uint32), ref.view(np.uint32))
+
+
+def test_sampler_errors_and_frames(rctx):
+    cam = b2rt.pbrt_camera(EYE, LOOK, UP, FOV, 48, 32)
+    kw = dict(spp=4, caustic=False, indirect=False)
+    base = rctx.render_frame(cam, **kw)
+    with pytest.raises(b2rt.B2rtError):
+        rctx.set_sampler(7)
+    rctx.set_sampler("stratified", 3, 2)
+    with pytest.raises(b2rt.B2rtError):
+        rctx.render_frame(cam, **kw)                                # 3 x 2 strata != 4 spp
+    imgs = {}
+    for name, nx, ny in (("stratified", 2, 2), ("lowdiscrepancy", 1, 1)):
+        rctx.set_sampler(name, nx, ny)
+        imgs[name] = rctx.render_frame(cam, **kw)
+        bands = [rctx.render_frame(cam, window=(0, 48, y0, y1), **kw) for y0, y1 in ((0, 11), (11, 32))]
+        assert np.array_equal(np.concatenate(bands, 0).view(np.uint32), imgs[name].view(np.uint32))
+        assert not np.array_equal(imgs[name], base)
+        assert abs(imgs[name].mean() - base.mean()) <= 0.1 * base.mean()      # 48 x 32 x 4 spp: Monte-Carlo noise
+    rctx.set_sampler("random")
+    assert np.array_equal(rctx.render_frame(cam, **kw).view(np.uint32), base.view(np.uint32))
