@@ -56,6 +56,18 @@ full = ctx.render_frame(cam, **kw)
 ok_img = True
 if rank == 0:
     ok_img = bool(np.array_equal(full.view(np.uint32), img.view(np.uint32)))
+# the same identity with a pixel filter wider than the pixel (every band re-traces its halo rows) and pbrt's
+# low-discrepancy pixel pattern
+ctx.set_filter(b2rt.pbrt_filter("mitchell")); ctx.set_sampler("lowdiscrepancy")
+dist.barrier(); torch.cuda.synchronize(); t0 = time.perf_counter()
+img_f = M.render_sharded(ctx, cam, **kw)
+torch.cuda.synchronize(); t1 = time.perf_counter()
+full_f = ctx.render_frame(cam, **kw)
+ok_filtered = True
+if rank == 0:
+    ok_filtered = bool(np.array_equal(full_f.view(np.uint32), np.asarray(img_f).view(np.uint32)))
+    print("mitchell + lowdiscrepancy banded frame: %.2f ms on rank 0" % ((t1 - t0) * 1e3), flush=True)
+ctx.set_filter(None); ctx.set_sampler("random")
 acc = hashlib.sha256(np.ascontiguousarray(ctx.accel_download()["wide_nodes"]).tobytes()).hexdigest()
 objs = [None] * world
 dist.all_gather_object(objs, (sharded_hash, single_hash, acc))
@@ -65,6 +77,7 @@ if rank == 0:
     print("photon maps identical to single-GPU on all ranks:", same_photons)
     print("BVH bytes identical across ranks:", same_bvh)
     print("banded frame identical to single-GPU frame:", ok_img)
-    assert same_photons and same_bvh and ok_img
+    print("banded mitchell-filtered, low-discrepancy frame identical to single-GPU frame:", ok_filtered)
+    assert same_photons and same_bvh and ok_img and ok_filtered
 ctx.close()
 dist.destroy_process_group()
