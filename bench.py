@@ -47,10 +47,10 @@ def emit(line):
 _TV = os.environ.get("B2RT_TRACE_VARIANT", "2")
 TRACE_KERNEL = {"0": "trace_kernel<closest>", "1": "trace_persistent_kernel<closest>"}.get(_TV, "trace_spec_kernel<closest>")
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the default closest-hit kernel on this exact workload,
-# from the ncu --set full capture of `bench.py --steps 2 --warmup 3` (profiles/r01h_ncu_trace.md, re-captured r01m):
-# 136 MB read + 25.8 MB written, against 99.5 MB of compulsory ray / hit bytes (the difference is the cold 52 MB scene).
+# from the ncu --set full capture of `bench.py --steps 2 --warmup 3` (profiles/r01h_ncu_trace.md, re-captured r01m and
+# r02m, profiles/r02m_ncu_full_summary.md): 135-136 MB read + 26 MB written, against 99.5 MB of compulsory ray / hit bytes (the difference is the cold 52 MB scene).
 TRAFFIC_BYTES = 161.8e6 if _TV == "2" else None
-TRAFFIC_SOURCE = "ncu --set full, r01m capture (profiles/r01h_ncu_trace.md): dram read 136 MB + write 25.8 MB per launch"
+TRAFFIC_SOURCE = "ncu --set full, r02m capture (profiles/r02m_ncu_full_summary.md): dram read 135 MB + write 26 MB per launch"
 METRIC = "Mrays/s (closest-hit primary + any-hit shadow rays, 1M-triangle scene, 1920x1080, 1 spp)"
 LIGHT = (0.5, 3.0, 0.5)
 

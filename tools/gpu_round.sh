@@ -21,7 +21,7 @@ timeout 900 $NCU --metrics gpu__time_duration.sum -c 2000 --csv --log-file $O/la
     python tools/bench_photon.py 8000000 2000000 1920 1080 64 1 > $O/ncu_photon.log 2>&1
 timeout 900 $NCU --set full --import-source on -k regex:trace_ -s 16 -c 2 -f -o $O/trace_full \
     python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-photon-extra > $O/ncu_trace_full.log 2>&1
-timeout 1200 $NCU --set full --import-source on -k regex:'gather_tiled|photon_trace_regen|render_li_kernel|grid_reorder_kernel|grid_keys_kernel' -s 4 \
+timeout 1200 $NCU --set full --import-source on -k regex:'gather_block|photon_trace_regen|render_li_kernel|grid_reorder_kernel|grid_keys_kernel' -s 4 \
     -c 14 -f -o $O/photon_full python tools/bench_photon.py 8000000 2000000 1920 1080 64 1 > $O/ncu_photon_full.log 2>&1
 fi
 ls -la $O
