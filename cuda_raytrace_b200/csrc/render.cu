@@ -21,90 +21,6 @@ namespace {
 constexpr int RENDER_THREADS = 128;
 constexpr int MAX_TREE_DEPTH = 8;
 
-__device__ __forceinline__ float power_heuristic(float f, float g) { return (f * f) / (f * f + g * g); }
-
-// Shape::Pdf(p, wi) for the disk light (core/shape.cpp:95-108); also returns the hit distance
-__device__ __forceinline__ float disk_light_pdf(const AnalyticPrim &D, const LightD &L, f3 p, f3 wi) {
-    RayD r;
-    r.ox = p.x; r.oy = p.y; r.oz = p.z; r.dx = wi.x; r.dy = wi.y; r.dz = wi.z; r.tmin = 1e-3f;
-    float t;
-    if (!disk_test(r, D, INFINITY, t)) return 0.f;
-    f3 dv = wi * t;
-    float d2 = dv.x * dv.x + dv.y * dv.y + dv.z * dv.z;
-    float pdf = d2 / (fabsf(dot3(L.n, -wi)) * L.area);
-    return isinf(pdf) ? 0.f : pdf;
-}
-
-// UniformSampleAllLights + EstimateDirect for a Lambertian surface (flags = BSDF_ALL & ~BSDF_SPECULAR)
-__device__ f3 direct_lighting(const DScene &sc, const Surface &s, const Mat &m, f3 wo, uint32_t c0, uint32_t c1,
-                              uint32_t node, uint32_t k0, uint32_t k1, bool &overflow) {
-    f3 L = mk3(0.f, 0.f, 0.f);
-    const f3 f_lambert = m.kd * B2_INV_PI;
-    for (int li = 0; li < sc.n_lights; ++li) {
-        LightD Lt = load_light(sc, li);
-        const int ns = Lt.type == B2RT_LIGHT_POINT ? 1 : max(Lt.nsamples, 1);
-        f3 Ld = mk3(0.f, 0.f, 0.f);
-        for (int j = 0; j < ns; ++j) {
-            u4 r = philox4x32_10(c0, c1, node, 0x100u + (uint32_t)(li * 64 + j), k0, k1);
-            HitD h;
-            if (Lt.type == B2RT_LIGHT_POINT) {
-                // PointLight::Sample_L (lights/point.cpp:50-57): delta light, no MIS
-                f3 dl = Lt.p - s.p;
-                float d2 = dl.x * dl.x + dl.y * dl.y + dl.z * dl.z;
-                f3 wi = normalize3(dl);
-                bool same = dot3(wi, s.n) * dot3(wo, s.n) > 0.f;
-                if (!same) continue;
-                // visibility segment p -> lightPos: direction (lightPos - p), [rayEps, 1]
-                if (traverse<true>(sc.nodes, sc.recs, sc.analytic, s.p.x, s.p.y, s.p.z, dl.x, dl.y, dl.z, s.ray_eps, 1.f, h,
-                                   overflow))
-                    continue;
-                float w = fabsf(dot3(wi, s.n));     // / lightPdf (= 1)
-                Ld = Ld + mk3(f_lambert.x * (Lt.rgb.x / d2) * w, f_lambert.y * (Lt.rgb.y / d2) * w,
-                              f_lambert.z * (Lt.rgb.z / d2) * w);
-                continue;
-            }
-            const AnalyticPrim &D = sc.analytic[Lt.analytic];
-            // ---- light sampling (lights/diffuse.cpp:69-81) ----
-            {
-                f3 ps = disk_sample_point(D, u01(r.x), u01(r.y));
-                f3 dl = ps - s.p;
-                f3 wi = normalize3(dl);
-                float lpdf = disk_light_pdf(D, Lt, s.p, wi);
-                bool emits = dot3(Lt.n, -wi) > 0.f;
-                bool same = dot3(wi, s.n) * dot3(wo, s.n) > 0.f;
-                if (lpdf > 0.f && emits && same) {
-                    if (!traverse<true>(sc.nodes, sc.recs, sc.analytic, s.p.x, s.p.y, s.p.z, dl.x, dl.y, dl.z, s.ray_eps,
-                                        1.f - 1e-3f, h, overflow)) {
-                        f3 wil = to_local(s, wi), wol = to_local(s, wo);
-                        float bpdf = (wol.z * wil.z > 0.f) ? fabsf(wil.z) * B2_INV_PI : 0.f;
-                        float w = fabsf(dot3(wi, s.n)) * power_heuristic(lpdf, bpdf) / lpdf;
-                        Ld = Ld + mk3(f_lambert.x * Lt.rgb.x * w, f_lambert.y * Lt.rgb.y * w, f_lambert.z * Lt.rgb.z * w);
-                    }
-                }
-            }
-            // ---- BSDF sampling ----
-            {
-                BsdfSample bs;
-                if (!sample_bsdf(s, m, wo, u01(r.z), u01(r.w), 0.f, bs) || is_black(bs.f) || !(bs.pdf > 0.f)) continue;
-                float lpdf = disk_light_pdf(D, Lt, s.p, bs.wi);
-                if (lpdf == 0.f) continue;
-                float weight = power_heuristic(bs.pdf, lpdf);
-                if (traverse<false>(sc.nodes, sc.recs, sc.analytic, s.p.x, s.p.y, s.p.z, bs.wi.x, bs.wi.y, bs.wi.z, s.ray_eps,
-                                    INFINITY, h, overflow) &&
-                    h.prim == Lt.prim && dot3(Lt.n, -bs.wi) > 0.f) {
-                    float w = bs.absdot * weight / bs.pdf;
-                    Ld = Ld + mk3(bs.f.x * Lt.rgb.x * w, bs.f.y * Lt.rgb.y * w, bs.f.z * Lt.rgb.z * w);
-                }
-            }
-        }
-        float inv = 1.f / (float)ns;
-        L = L + Ld * inv;
-    }
-    return L;
-}
-
-struct TreeNode { f3 o, d; float tmin; f3 T; int depth; uint32_t id; };
-
 // ---- K14 image-plane sample patterns: where inside its pixel sample k lies ------------------------------------------
 struct SamplerD { int type, nx, ny; };
 constexpr float ONE_MINUS_EPS = 0.9999999403953552f;          // core/montecarlo.h:48
@@ -150,6 +66,104 @@ __device__ __forceinline__ uint32_t global_pixel_id(int px, int py, int xres, in
     return gpix;
 }
 
+__device__ __forceinline__ float power_heuristic(float f, float g) { return (f * f) / (f * f + g * g); }
+
+// Shape::Pdf(p, wi) for the disk light (core/shape.cpp:95-108); also returns the hit distance
+__device__ __forceinline__ float disk_light_pdf(const AnalyticPrim &D, const LightD &L, f3 p, f3 wi) {
+    RayD r;
+    r.ox = p.x; r.oy = p.y; r.oz = p.z; r.dx = wi.x; r.dy = wi.y; r.dz = wi.z; r.tmin = 1e-3f;
+    float t;
+    if (!disk_test(r, D, INFINITY, t)) return 0.f;
+    f3 dv = wi * t;
+    float d2 = dv.x * dv.x + dv.y * dv.y + dv.z * dv.z;
+    float pdf = d2 / (fabsf(dot3(L.n, -wi)) * L.area);
+    return isinf(pdf) ? 0.f : pdf;
+}
+
+// UniformSampleAllLights + EstimateDirect for a Lambertian surface (flags = BSDF_ALL & ~BSDF_SPECULAR)
+__device__ f3 direct_lighting(const DScene &sc, const Surface &s, const Mat &m, f3 wo, uint32_t c0, uint32_t c1,
+                              uint32_t node, uint32_t k0, uint32_t k1, bool &overflow, const SamplerD &sm) {
+    f3 L = mk3(0.f, 0.f, 0.f);
+    const f3 f_lambert = m.kd * B2_INV_PI;
+    // With pbrt's stratified / low-discrepancy samplers the light and BSDF samples of the camera ray's own hit are not
+    // independent either: every light gets its ns 2D samples per pixel sample out of ONE pattern over the pixel's
+    // spp * ns samples (LDShuffleScrambled2D(ns, spp), samplers/lowdiscrepancy.cpp:67-79, core/sampler.cpp:96-106).
+    // Here: points [k * ns, (k + 1) * ns) of a (0,2)-sequence whose scrambles are Philox words of (pixel, light).
+    // Deeper nodes of the specular tree keep independent uniforms (pbrt re-uses the same sample values there).
+    const bool pattern = sm.type != B2RT_SAMPLER_RANDOM && node == 1u;
+    for (int li = 0; li < sc.n_lights; ++li) {
+        LightD Lt = load_light(sc, li);
+        const int ns = Lt.type == B2RT_LIGHT_POINT ? 1 : max(Lt.nsamples, 1);
+        f3 Ld = mk3(0.f, 0.f, 0.f);
+        u4 scr = {0u, 0u, 0u, 0u};
+        if (pattern && Lt.type != B2RT_LIGHT_POINT) scr = philox4x32_10(c0, 0xfffffffeu, (uint32_t)li, 0u, k0, k1);
+        for (int j = 0; j < ns; ++j) {
+            u4 r = philox4x32_10(c0, c1, node, 0x100u + (uint32_t)(li * 64 + j), k0, k1);
+            float u_l1 = u01(r.x), u_l2 = u01(r.y), u_b1 = u01(r.z), u_b2 = u01(r.w);
+            if (pattern) {
+                const uint32_t n = c1 * (uint32_t)ns + (uint32_t)j;
+                u_l1 = ld_vdc(n, scr.x); u_l2 = ld_sobol2(n, scr.y); u_b1 = ld_vdc(n, scr.z); u_b2 = ld_sobol2(n, scr.w);
+            }
+            HitD h;
+            if (Lt.type == B2RT_LIGHT_POINT) {
+                // PointLight::Sample_L (lights/point.cpp:50-57): delta light, no MIS
+                f3 dl = Lt.p - s.p;
+                float d2 = dl.x * dl.x + dl.y * dl.y + dl.z * dl.z;
+                f3 wi = normalize3(dl);
+                bool same = dot3(wi, s.n) * dot3(wo, s.n) > 0.f;
+                if (!same) continue;
+                // visibility segment p -> lightPos: direction (lightPos - p), [rayEps, 1]
+                if (traverse<true>(sc.nodes, sc.recs, sc.analytic, s.p.x, s.p.y, s.p.z, dl.x, dl.y, dl.z, s.ray_eps, 1.f, h,
+                                   overflow))
+                    continue;
+                float w = fabsf(dot3(wi, s.n));     // / lightPdf (= 1)
+                Ld = Ld + mk3(f_lambert.x * (Lt.rgb.x / d2) * w, f_lambert.y * (Lt.rgb.y / d2) * w,
+                              f_lambert.z * (Lt.rgb.z / d2) * w);
+                continue;
+            }
+            const AnalyticPrim &D = sc.analytic[Lt.analytic];
+            // ---- light sampling (lights/diffuse.cpp:69-81) ----
+            {
+                f3 ps = disk_sample_point(D, u_l1, u_l2);
+                f3 dl = ps - s.p;
+                f3 wi = normalize3(dl);
+                float lpdf = disk_light_pdf(D, Lt, s.p, wi);
+                bool emits = dot3(Lt.n, -wi) > 0.f;
+                bool same = dot3(wi, s.n) * dot3(wo, s.n) > 0.f;
+                if (lpdf > 0.f && emits && same) {
+                    if (!traverse<true>(sc.nodes, sc.recs, sc.analytic, s.p.x, s.p.y, s.p.z, dl.x, dl.y, dl.z, s.ray_eps,
+                                        1.f - 1e-3f, h, overflow)) {
+                        f3 wil = to_local(s, wi), wol = to_local(s, wo);
+                        float bpdf = (wol.z * wil.z > 0.f) ? fabsf(wil.z) * B2_INV_PI : 0.f;
+                        float w = fabsf(dot3(wi, s.n)) * power_heuristic(lpdf, bpdf) / lpdf;
+                        Ld = Ld + mk3(f_lambert.x * Lt.rgb.x * w, f_lambert.y * Lt.rgb.y * w, f_lambert.z * Lt.rgb.z * w);
+                    }
+                }
+            }
+            // ---- BSDF sampling ----
+            {
+                BsdfSample bs;
+                if (!sample_bsdf(s, m, wo, u_b1, u_b2, 0.f, bs) || is_black(bs.f) || !(bs.pdf > 0.f)) continue;
+                float lpdf = disk_light_pdf(D, Lt, s.p, bs.wi);
+                if (lpdf == 0.f) continue;
+                float weight = power_heuristic(bs.pdf, lpdf);
+                if (traverse<false>(sc.nodes, sc.recs, sc.analytic, s.p.x, s.p.y, s.p.z, bs.wi.x, bs.wi.y, bs.wi.z, s.ray_eps,
+                                    INFINITY, h, overflow) &&
+                    h.prim == Lt.prim && dot3(Lt.n, -bs.wi) > 0.f) {
+                    float w = bs.absdot * weight / bs.pdf;
+                    Ld = Ld + mk3(bs.f.x * Lt.rgb.x * w, bs.f.y * Lt.rgb.y * w, bs.f.z * Lt.rgb.z * w);
+                }
+            }
+        }
+        float inv = 1.f / (float)ns;
+        L = L + Ld * inv;
+    }
+    return L;
+}
+
+struct TreeNode { f3 o, d; float tmin; f3 T; int depth; uint32_t id; };
+
+
 // K14 + K6 + K7.  sample s (chunk-local) -> pixel (crop-window row-major) and sample number k.
 __global__ void __launch_bounds__(RENDER_THREADS)
 render_li_kernel(DScene sc, b2rt_camera cam, b2rt_frame_params fp, uint32_t seed_lo, uint32_t seed_hi, int64_t first_sample,
@@ -193,7 +207,7 @@ render_li_kernel(DScene sc, b2rt_camera cam, b2rt_frame_params fp, uint32_t seed
         }
         if (m.type == B2RT_MAT_MATTE) {
             if (fp.direct_lighting)
-                L = L + nd.T * direct_lighting(sc, sf, m, wo, gpix, (uint32_t)k, nd.id, k0, k1, overflow);
+                L = L + nd.T * direct_lighting(sc, sf, m, wo, gpix, (uint32_t)k, nd.id, k0, k1, overflow, sm);
             if (fp.use_caustic || fp.use_indirect) {
                 if ((int)nq < slots) {
                     f3 nf = dot3(sf.n, wo) < 0.f ? -sf.n : sf.n;              // Faceforward(n, wo)

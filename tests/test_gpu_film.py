@@ -174,3 +174,22 @@ def test_sampler_errors_and_frames(rctx):
         assert abs(imgs[name].mean() - base.mean()) <= 0.1 * base.mean()      # 48 x 32 x 4 spp: Monte-Carlo noise
     rctx.set_sampler("random")
     assert np.array_equal(rctx.render_frame(cam, **kw).view(np.uint32), base.view(np.uint32))
+
+
+def test_pattern_samplers_converge_faster_than_random(rctx):
+    """Direct lighting of the area light, 4 spp: with the stratified / low-discrepancy samplers the pixel positions AND
+    the light / BSDF samples of the camera hit come from one pattern per pixel, so the error against a converged image
+    must be clearly below the independent-uniform sampler's (same estimator, same expectation)."""
+    cam = b2rt.pbrt_camera(EYE, LOOK, UP, FOV, 96, 64)
+    kw = dict(caustic=False, indirect=False)
+    rctx.set_sampler("lowdiscrepancy")
+    ref = rctx.render_frame(cam, spp=2048, **kw).astype(np.float64)
+    err = {}
+    for name, nx, ny in (("random", 1, 1), ("stratified", 2, 2), ("lowdiscrepancy", 1, 1)):
+        rctx.set_sampler(name, nx, ny)
+        img = rctx.render_frame(cam, spp=4, **kw).astype(np.float64)
+        err[name] = float(np.sqrt(((img - ref) ** 2).mean()))
+        assert abs(img.mean() - ref.mean()) <= 0.02 * ref.mean(), (name, img.mean(), ref.mean())
+    rctx.set_sampler("random")
+    assert err["lowdiscrepancy"] < 0.85 * err["random"], err
+    assert err["stratified"] < 0.95 * err["random"], err
