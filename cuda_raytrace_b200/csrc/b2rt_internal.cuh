@@ -90,6 +90,7 @@ struct b2rt_ctx {
     int trace_refill = 0;        // persistent: refill idle lanes when fewer than this many lanes are active
     int pt_blocks_per_sm[4] = {0, 0, 0, 0};
     int trace_sort = -1;         // variant 2 child order: 2 = near to far, 1 = nearest first only, 0 = slot order, < 0 = 2 for closest / 0 for any hit
+    int trace_pool_flip = 0;     // which of the two ray-pool counters the next speculative-kernel launch uses
     int trace_chunk = 32;        // persistent: consecutive rays a warp takes from the pool per atomicAdd
     int64_t host_chunk = 1 << 18; // rays per chunk of the host-buffer pipeline (B2RT_HOST_CHUNK)
     int photon_variant = 1;      // 0: one thread per path, 1: resident grid with path regeneration

@@ -210,11 +210,14 @@ __global__ void __launch_bounds__(PT_THREADS)
 trace_spec_kernel(const WideNode *__restrict__ nodes, const PrimRec *__restrict__ recs,
                   const AnalyticPrim *__restrict__ analytic, const b2rt_ray *__restrict__ rays,
                   b2rt_hit *__restrict__ hits, uint8_t *__restrict__ occ, int64_t nrays,
-                  unsigned long long *pool, int refill, int chunk, uint32_t *status) {
+                  unsigned long long *pool, int refill, int chunk, uint32_t *status, unsigned long long *next_pool) {
     __shared__ int32_t s_stack[PT_SSTACK][PT_THREADS];
     int32_t l_stack[B2RT_STACK_SIZE - PT_SSTACK];
     const int tid = threadIdx.x, lane = tid & 31;
     const uint32_t lt = (1u << lane) - 1u;
+    // the ray-pool counter of the NEXT launch (the two counters alternate): zeroing it here saves the separate reset
+    // launch in front of every trace call
+    if (blockIdx.x == 0 && tid == 0) *next_pool = 0ull;
     constexpr int32_t NONE = B2RT_CHILD_EMPTY;       // "nothing": never a valid node index or leaf reference
 
     RayD r;
@@ -387,8 +390,15 @@ int b2rt_trace_impl(b2rt_ctx *ctx, int64_t n, const b2rt_ray *d_rays, b2rt_hit *
         if (blocks > need) blocks = need;
         unsigned long long *pool = reinterpret_cast<unsigned long long *>(ctx->d_counters.as<uint32_t>() + 16);
         const int chunk = ctx->trace_chunk >= 32 ? (ctx->trace_chunk & ~31) : 32;
-        pool_reset_kernel<<<1, 1, 0, ctx->stream>>>(pool);
-        B2RT_LAUNCH_CHECK(ctx);
+        unsigned long long *next_pool = pool;
+        if (spec) {                     // two counters (uint32 slots 16-17 and 20-21, zero at creation) used in turn
+            if (ctx->trace_pool_flip) pool = reinterpret_cast<unsigned long long *>(ctx->d_counters.as<uint32_t>() + 20);
+            else next_pool = reinterpret_cast<unsigned long long *>(ctx->d_counters.as<uint32_t>() + 20);
+            ctx->trace_pool_flip ^= 1;
+        } else {
+            pool_reset_kernel<<<1, 1, 0, ctx->stream>>>(pool);
+            B2RT_LAUNCH_CHECK(ctx);
+        }
         if (spec) {
             // default (trace_sort < 0): closest-hit rays visit children near to far; any-hit rays take them in slot order
             // (no sorting network: +9 % / +5 % on the 1 M / 8 M-triangle shadow rays, run r02b; for closest-hit rays slot
@@ -399,7 +409,7 @@ int b2rt_trace_impl(b2rt_ctx *ctx, int64_t n, const b2rt_ray *d_rays, b2rt_hit *
             if (ctx->trace_sort == 0) kern = any_hit ? trace_spec_kernel<true, 0> : trace_spec_kernel<false, 0>;
             kern<<<(unsigned)blocks, PT_THREADS, 0, ctx->stream>>>(nodes, recs, an, d_rays, any_hit ? nullptr : d_hits,
                                                                    any_hit ? d_occ : nullptr, n, pool, ctx->trace_refill,
-                                                                   chunk, status);
+                                                                   chunk, status, next_pool);
         }
         else if (any_hit)
             trace_persistent_kernel<true><<<(unsigned)blocks, PT_THREADS, 0, ctx->stream>>>(
