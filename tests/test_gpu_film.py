@@ -193,3 +193,40 @@ def test_pattern_samplers_converge_faster_than_random(rctx):
     rctx.set_sampler("random")
     assert err["lowdiscrepancy"] < 0.85 * err["random"], err
     assert err["stratified"] < 0.95 * err["random"], err
+
+
+def test_film_full_size_properties():
+    """BASELINE Cfg4 frame size (3840 x 2160, 8 spp, Mitchell): size-independent properties of the reconstruction -
+    a constant radiance field comes back as that constant, two runs and two band tilings give the same bits, and a
+    random sample of pixels equals the oracle's value for the same samples."""
+    gf, of = _flt("mitchell", {})
+    xres, yres, spp = 3840, 2160, 8
+    h = F.halo(of[1])
+    cells = (-h, -h, xres + h, yres + h)
+    cw, ch = cells[2] - cells[0], cells[3] - cells[1]
+    rng = np.random.default_rng(31)
+    xy = rng.random((ch, cw, spp, 2), dtype=np.float32)
+    xy[..., 0] += np.arange(cells[0], cells[2], dtype=np.float32)[None, :, None]
+    xy[..., 1] += np.arange(cells[1], cells[3], dtype=np.float32)[:, None, None]
+    xy = xy.reshape(-1, 2)
+    rgb = rng.random((len(xy), 3), dtype=np.float32)
+    with b2rt.Context(0) as c:
+        img = c.film_reconstruct(gf, cells, spp, xy, rgb, (0, 0, xres, yres))
+        again = c.film_reconstruct(gf, cells, spp, xy, rgb, (0, 0, xres, yres))
+        assert np.array_equal(img.view(np.uint32), again.view(np.uint32))
+        # a band of the frame from only the cell rows that reach it
+        y0, y1 = 1000, 1100
+        rows = slice((y0 - h - cells[1]) * cw * spp, (y1 + h - cells[1]) * cw * spp)
+        band = c.film_reconstruct(gf, (cells[0], y0 - h, cells[2], y1 + h), spp, xy[rows], rgb[rows], (0, y0, xres, y1))
+        assert np.array_equal(band.view(np.uint32), img[y0:y1].view(np.uint32))
+        const = c.film_reconstruct(gf, cells, spp, xy, np.full_like(rgb, 0.75), (0, 0, xres, yres))
+        assert np.abs(const - np.float32(0.75)).max() <= 2e-5
+    # oracle on a 64 x 48 window of the same samples
+    wx0, wy0, wx1, wy1 = 1900, 1050, 1964, 1098
+    sel = []
+    for cy in range(wy0 - h, wy1 + h):
+        a = ((cy - cells[1]) * cw + (wx0 - h - cells[0])) * spp
+        sel.append(np.arange(a, a + (wx1 - wx0 + 2 * h) * spp))
+    sel = np.concatenate(sel)
+    ref = O.film(of, (wx0 - h, wy0 - h, wx1 + h, wy1 + h), spp, xy[sel], rgb[sel], (wx0, wy0, wx1, wy1))
+    assert np.array_equal(ref.view(np.uint32), img[wy0:wy1, wx0:wx1].view(np.uint32))
