@@ -36,6 +36,8 @@ if os.environ.get("FILTER"):                 # pbrt PixelFilter name: box / tria
     ctx.set_filter(b2rt.pbrt_filter(os.environ["FILTER"]))
 cam = b2rt.pbrt_camera((0, 1.2, 2.5), (0, 0, 0), (0, 1, 0), 45, xres, yres)
 kw = dict(spp=spp, caustic=False, indirect=False, direct=True)
+ctx.set_sampler("lowdiscrepancy")               # (0,2)-sequence jitter
+skw = dict(kw, stripes=int(os.environ["STRIPES"])) if os.environ.get("STRIPES") else kw      # bands per rank (default 8)
 
 frame_out = ctx.pinned_empty((yres, xres, 3))
 times = []
@@ -44,7 +46,7 @@ for rep in range(4):
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize(); ctx.sync(); t0 = time.perf_counter()
-    img = M.render_sharded(ctx, cam, **kw) if world > 1 else ctx.render_frame(cam, out=frame_out, **kw)
+    img = M.render_sharded(ctx, cam, **skw) if world > 1 else ctx.render_frame(cam, out=frame_out, **kw)
     torch.cuda.synchronize(); ctx.sync(); t1 = time.perf_counter()
     tt = torch.tensor([t1 - t0], dtype=torch.float64, device="cuda")
     if world > 1:
@@ -54,7 +56,7 @@ ms = min(times[1:])
 if rank == 0:
     samples = xres * yres * spp
     lit = float((img.sum(-1) > 0).mean())
-    print(json.dumps({"workload": "Cfg4: %d triangles, %dx%d, %d spp, camera ray + shadow ray per sample, bands over %d GPU(s)"
+    print(json.dumps({"workload": "Cfg4: %d triangles, %dx%d, %d spp (0,2)-sequence, camera ray + shadow ray per sample, interleaved bands over %d GPU(s)"
                                   % (len(idx), xres, yres, spp, world),
                       "n_gpus": world, "ms_per_frame": ms, "all_ms": times, "Msamples_per_s": samples / ms / 1e3,
                       "Mrays_per_s_upper": 2 * samples / ms / 1e3, "lit_pixel_fraction": lit,
