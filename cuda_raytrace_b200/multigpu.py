@@ -122,7 +122,7 @@ _pinned_frames = {}
 
 
 def render_sharded(ctx, cam, group=None, **kw):
-    """Each rank renders its bands (interleaved stripes, `stripes=` per rank, default 8); rank 0 returns the composited
+    """Each rank renders its bands (interleaved stripes, `stripes=` per rank, default up to 8 with at least 64 rows per band); rank 0 returns the composited
     (yres, xres, 3) image, the others None.  With NCCL the
     returned array is a view of a pinned buffer that the next call with the same resolution overwrites.
     NCCL: the band is rendered straight into a CUDA tensor, the bands are gathered on rank 0's GPU and the finished image
@@ -142,7 +142,7 @@ def render_sharded(ctx, cam, group=None, **kw):
     # every rank samples the whole height of the image (a rank whose single band was all terrain took 1.7x the mean
     # band time on the 8 M-triangle 4K frame; SURVEY 8(e) asks for interleaved tiles for this reason)
     if stripes is None:
-        stripes = 8 if cam.yres >= 64 * world else 1
+        stripes = max(1, min(8, cam.yres // (64 * world)))      # bands of at least 64 rows: every band is a call
     nb = stripes * world
     edges = [cam.yres * b // nb for b in range(nb + 1)]
     mine = [b for b in range(nb) if b % world == rank]

@@ -37,7 +37,7 @@ if os.environ.get("FILTER"):                 # pbrt PixelFilter name: box / tria
 cam = b2rt.pbrt_camera((0, 1.2, 2.5), (0, 0, 0), (0, 1, 0), 45, xres, yres)
 kw = dict(spp=spp, caustic=False, indirect=False, direct=True)
 ctx.set_sampler("lowdiscrepancy")               # (0,2)-sequence jitter
-skw = dict(kw, stripes=int(os.environ["STRIPES"])) if os.environ.get("STRIPES") else kw      # bands per rank (default 8)
+skw = dict(kw, stripes=int(os.environ["STRIPES"])) if os.environ.get("STRIPES") else kw      # bands per rank (default: up to 8, at least 64 rows each)
 
 frame_out = ctx.pinned_empty((yres, xres, 3))
 times = []
