@@ -29,6 +29,33 @@ def band_window(yres, xres, rank, world):
     return 0, xres, y0, y1
 
 
+def stripe_plan(yres, world, stripes=None):
+    """Interleaved image stripes: the image rows are cut into stripes * world bands and band b belongs to rank
+    b % world, so every rank samples the whole height of the image.  Returns the nb + 1 row boundaries.  Default stripe
+    count: up to 8 per rank with bands of at least 64 rows (every band is one render call)."""
+    if stripes is None:
+        stripes = max(1, min(8, yres // (64 * world)))
+    nb = max(1, int(stripes)) * world
+    return [yres * b // nb for b in range(nb + 1)]
+
+
+def stripe_rows(edges, world, rank):
+    """[(y0, y1)] of the non-empty bands of `rank`, top to bottom - the order they are stacked in its buffer"""
+    return [(edges[b], edges[b + 1]) for b in range(len(edges) - 1) if b % world == rank and edges[b + 1] > edges[b]]
+
+
+def stripe_compose(parts, edges, world):
+    """parts[r] = rank r's stacked bands (anything sliceable by rows); returns the slices in image order"""
+    offs = [0] * world
+    pieces = []
+    for b in range(len(edges) - 1):
+        r, n = b % world, edges[b + 1] - edges[b]
+        if n:
+            pieces.append(parts[r][offs[r]:offs[r] + n])
+            offs[r] += n
+    return pieces
+
+
 def allgather_varlen(local, group=None):
     """local: 2-D torch tensor [n_local, width] (uint8 rows of a record array).  Returns (concatenation over ranks in
     rank order, per-rank counts).  Works with NCCL (CUDA tensors) and gloo (CPU tensors)."""
@@ -141,31 +168,19 @@ def render_sharded(ctx, cam, group=None, **kw):
     # interleaved stripes: the image is cut into stripes * world bands and rank r renders bands r, r + world, ... so
     # every rank samples the whole height of the image (a rank whose single band was all terrain took 1.7x the mean
     # band time on the 8 M-triangle 4K frame; SURVEY 8(e) asks for interleaved tiles for this reason)
-    if stripes is None:
-        stripes = max(1, min(8, cam.yres // (64 * world)))      # bands of at least 64 rows: every band is a call
-    nb = stripes * world
-    edges = [cam.yres * b // nb for b in range(nb + 1)]
-    mine = [b for b in range(nb) if b % world == rank]
-    rows_of = [sum(edges[b + 1] - edges[b] for b in range(nb) if b % world == r) for r in range(world)]
-    pad = max(max(rows_of), 1)
+    edges = stripe_plan(cam.yres, world, stripes)
+    pad = max(max(sum(y1 - y0 for y0, y1 in stripe_rows(edges, world, r)) for r in range(world)), 1)
     band = torch.empty((pad, cam.xres * 3), dtype=torch.float32, device=dev)
     _ctx_stream_waits_for_torch(ctx)                # `band` may reuse a block torch is still reading
     at = 0
-    for b in mine:
-        if edges[b + 1] > edges[b]:
-            ctx.render_frame_device(cam, band[at:].data_ptr(), window=(0, cam.xres, edges[b], edges[b + 1]), **kw)   # synchronous on return
-            at += edges[b + 1] - edges[b]
+    for by0, by1 in stripe_rows(edges, world, rank):
+        ctx.render_frame_device(cam, band[at:].data_ptr(), window=(0, cam.xres, by0, by1), **kw)   # synchronous on return
+        at += by1 - by0
     parts = [torch.empty_like(band) for _ in range(world)] if rank == 0 else None
     dist.gather(band, parts, dst=0, group=group)
     if rank != 0:
         return None
-    offs = [0] * world
-    pieces = []
-    for b in range(nb):
-        r, n = b % world, edges[b + 1] - edges[b]
-        pieces.append(parts[r][offs[r]:offs[r] + n])
-        offs[r] += n
-    img = torch.cat(pieces, 0)
+    img = torch.cat(stripe_compose(parts, edges, world), 0)
     key = (cam.yres, cam.xres)
     if key not in _pinned_frames:
         _pinned_frames[key] = torch.empty((cam.yres, cam.xres * 3), dtype=torch.float32).pin_memory()

@@ -59,3 +59,25 @@ def test_allgather_varlen_rank_order(counts):
     for rank, allp, got in res:
         assert got == counts
         assert np.array_equal(allp, exp)
+
+
+@pytest.mark.parametrize("yres,world,stripes", [(1080, 8, None), (2160, 2, None), (2160, 8, 4), (17, 4, 8), (5, 8, None), (64, 1, None),
+                                                (1000, 3, 7)])
+def test_interleaved_stripes_partition_and_compose(yres, world, stripes):
+    """render_sharded's band plan: the bands tile the rows exactly, band b belongs to rank b % world, and stacking each
+    rank's bands then composing them gives the image back (numpy stand-in for the gathered CUDA tensors)."""
+    edges = M.stripe_plan(yres, world, stripes)
+    assert edges[0] == 0 and edges[-1] == yres and all(a <= b for a, b in zip(edges, edges[1:]))
+    assert (len(edges) - 1) % world == 0
+    img = np.arange(yres * 3, dtype=np.float32).reshape(yres, 3)
+    covered = np.zeros(yres, np.int32)
+    parts = []
+    for r in range(world):
+        rows = M.stripe_rows(edges, world, r)
+        for y0, y1 in rows:
+            covered[y0:y1] += 1
+        parts.append(np.concatenate([img[y0:y1] for y0, y1 in rows] + [np.zeros((0, 3), np.float32)], 0))
+    assert (covered == 1).all()
+    assert np.array_equal(np.concatenate(M.stripe_compose(parts, edges, world), 0), img)
+    if stripes is None and yres >= 64 * world:
+        assert min(b - a for a, b in zip(edges, edges[1:])) >= 64 - 1          # default: bands of (about) 64 rows or more
