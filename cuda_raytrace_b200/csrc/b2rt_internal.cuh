@@ -95,11 +95,11 @@ struct b2rt_ctx {
     int64_t host_chunk = 1 << 18; // rays per chunk of the host-buffer pipeline (B2RT_HOST_CHUNK)
     int photon_variant = 1;      // 0: one thread per path, 1: resident grid with path regeneration
     int photon_blocks_per_sm = 0;
-    int gather_blocks_per_sm[3] = {0, 0, 0};
+    int gather_blocks_per_sm[4] = {0, 0, 0, 0};
     float gather_target = 1.6f;  // first gather radius: sized to hold gather_target * k photons at the local density
     int gather_tcap = 1024;      // gather variant 2: positions in the shared tile (1024 -> 7 blocks per SM, 2048 -> 5)
     int gather_qt = 8;           // gather variant 2: consecutive queries that share one staged tile (8, 16 or 32)
-    int gather_variant = 2;      // 0: per-row scan with direct loads, 1: coarse table + TMA-staged tiles per warp,
+    int gather_variant = 2;      // 0: row-by-row scan, 1: per-warp tiled, 2: block-shared tile (default), 3: warp-specialised producer / consumer pipeline
                                  // 2: one TMA-staged tile shared by a block's 32 consecutive queries (k-nearest)
 
     // host-side staging of the scene (flattened)
