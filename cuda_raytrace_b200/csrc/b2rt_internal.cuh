@@ -99,8 +99,9 @@ struct b2rt_ctx {
     float gather_target = 1.6f;  // first gather radius: sized to hold gather_target * k photons at the local density
     int gather_tcap = 1024;      // gather variant 2: positions in the shared tile (1024 -> 7 blocks per SM, 2048 -> 5)
     int gather_qt = 8;           // gather variant 2: consecutive queries that share one staged tile (8, 16 or 32)
-    int gather_variant = 2;      // 0: row-by-row scan, 1: per-warp tiled, 2: block-shared tile (default), 3: warp-specialised producer / consumer pipeline
-                                 // 2: one TMA-staged tile shared by a block's 32 consecutive queries (k-nearest)
+    int gather_variant = 2;      // 0: row-by-row scan with direct loads, 1: coarse table + TMA-staged tiles per warp,
+                                 // 2: one TMA-staged tile shared by a block's consecutive queries (default),
+                                 // 3: the same tiles through a producer / consumer warp pipeline
 
     // host-side staging of the scene (flattened)
     std::vector<float> h_verts;      // xyz
