@@ -2,13 +2,14 @@
 // Host-side only: argument checks, staging of host buffers, buffer management.
 #include "b2rt_internal.cuh"
 #include <string.h>
+#include <math.h>
 
 static int need_built(b2rt_ctx *ctx, const char *who) {
     if (!ctx->built) { ctx->err = std::string(who) + ": b2rt_build_accel has not been called"; return B2RT_E_STATE; }
     return B2RT_OK;
 }
 static int check_map(b2rt_ctx *ctx, int32_t map, const char *who) {
-    if (map != B2RT_MAP_CAUSTIC && map != B2RT_MAP_INDIRECT) { ctx->err = std::string(who) + ": bad map id"; return B2RT_E_ARG; }
+    if (map < B2RT_MAP_CAUSTIC || map > B2RT_MAP_RADIANCE) { ctx->err = std::string(who) + ": bad map id"; return B2RT_E_ARG; }
     return B2RT_OK;
 }
 static int status_check(b2rt_ctx *ctx) {
@@ -28,6 +29,7 @@ extern "C" {
 int b2rt_photons_clear(b2rt_ctx *ctx) {
     if (!ctx) return B2RT_E_ARG;
     for (PhotonMap &m : ctx->maps) { m.n = 0; m.n_paths = 0; m.grid_built = false; }
+    ctx->radiance_computed = false;
     return B2RT_OK;
 }
 
@@ -115,11 +117,12 @@ int b2rt_photons_upload(b2rt_ctx *ctx, int32_t map, const b2rt_photon *in, int64
         B2RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     }
     m.n = n; m.n_paths = n_paths; m.grid_built = false;
+    if (map == B2RT_MAP_RADIANCE) ctx->radiance_computed = false;    // alpha of uploaded radiance photons is rho_r
     return B2RT_OK;
 }
 
 void *b2rt_photons_device_ptr(b2rt_ctx *ctx, int32_t map) {
-    if (!ctx || (map != 0 && map != 1)) return nullptr;
+    if (!ctx || map < 0 || map > B2RT_MAP_RADIANCE) return nullptr;
     return ctx->maps[map].photons.p;
 }
 
@@ -204,6 +207,91 @@ int b2rt_gather_sets(b2rt_ctx *ctx, int32_t map, int64_t nqueries, const b2rt_qu
                      float max_dist2, int32_t *idx_out, int where) {
     if (ctx && !idx_out) { ctx->err = "gather_sets: idx_out is NULL"; return B2RT_E_ARG; }
     return gather_common(ctx, map, nqueries, queries, k, max_dist2, nullptr, nullptr, nullptr, idx_out, where);
+}
+
+// ---- final gathering (finalgather.cu) ----------------------------------------------------------------------------------
+int b2rt_photons_trace_fg(b2rt_ctx *ctx, int64_t first_path, int64_t n_paths, int32_t max_depth, int64_t n_stored[2]) {
+    if (!ctx) return B2RT_E_ARG;
+    if (first_path < 0 || n_paths < 0 || max_depth < 1 || max_depth > 64) { ctx->err = "photons_trace_fg: bad arguments"; return B2RT_E_ARG; }
+    int rc = need_built(ctx, "photons_trace_fg");
+    if (rc) return rc;
+    if (ctx->h_lights.empty()) { ctx->err = "photons_trace_fg: the scene has no lights"; return B2RT_E_STATE; }
+    B2RT_CUDA(ctx, cudaSetDevice(ctx->device));
+    rc = b2rt_photons_trace_fg_impl(ctx, first_path, n_paths, max_depth, n_stored);
+    if (rc) return rc;
+    return status_check(ctx);
+}
+
+int b2rt_irradiance(b2rt_ctx *ctx, int32_t map, int64_t nq, const b2rt_query *queries, int32_t k, float max_dist2,
+                    float *out_E, int where) {
+    if (!ctx) return B2RT_E_ARG;
+    int rc = check_map(ctx, map, "irradiance");
+    if (rc) return rc;
+    if (nq < 0 || (nq && (!queries || !out_E)) || !(max_dist2 > 0.f) || k < 1 || k > 224) {
+        ctx->err = "irradiance: bad arguments (1 <= k <= 224, max_dist2 > 0)"; return B2RT_E_ARG;
+    }
+    PhotonMap &m = ctx->maps[map];
+    if (!m.grid_built) { ctx->err = "irradiance: b2rt_photon_grid_build has not been called for this map"; return B2RT_E_STATE; }
+    if (nq == 0) return B2RT_OK;
+    B2RT_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (where == B2RT_DEVICE) return b2rt_irradiance_impl(ctx, map, nq, queries, k, max_dist2, out_E, false);
+    if (where != B2RT_HOST) { ctx->err = "irradiance: where must be B2RT_HOST or B2RT_DEVICE"; return B2RT_E_ARG; }
+    cudaStream_t st = ctx->stream;
+    B2RT_CUDA(ctx, ctx->d_queries.reserve((size_t)nq * sizeof(b2rt_query)));
+    B2RT_CUDA(ctx, ctx->d_q_rgb.reserve((size_t)nq * 12));
+    B2RT_CUDA(ctx, cudaMemcpyAsync(ctx->d_queries.p, queries, (size_t)nq * sizeof(b2rt_query), cudaMemcpyHostToDevice, st));
+    rc = b2rt_irradiance_impl(ctx, map, nq, ctx->d_queries.as<b2rt_query>(), k, max_dist2, ctx->d_q_rgb.as<float>(), false);
+    if (rc) return rc;
+    B2RT_CUDA(ctx, cudaMemcpyAsync(out_E, ctx->d_q_rgb.p, (size_t)nq * 12, cudaMemcpyDeviceToHost, st));
+    B2RT_CUDA(ctx, cudaStreamSynchronize(st));
+    return B2RT_OK;
+}
+
+int b2rt_radiance_compute(b2rt_ctx *ctx, int32_t nused, float max_dist2) {
+    if (!ctx) return B2RT_E_ARG;
+    if (nused < 1 || nused > 224 || !(max_dist2 > 0.f)) { ctx->err = "radiance_compute: bad arguments (1 <= nused <= 224)"; return B2RT_E_ARG; }
+    B2RT_CUDA(ctx, cudaSetDevice(ctx->device));
+    int rc = b2rt_radiance_compute_impl(ctx, nused, max_dist2);
+    if (rc) return rc;
+    B2RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return B2RT_OK;
+}
+
+int b2rt_radiance_lookup(b2rt_ctx *ctx, int64_t nq, const b2rt_query *queries, float *out_rgb, int32_t *out_idx, int where) {
+    if (!ctx) return B2RT_E_ARG;
+    if (nq < 0 || (nq && !queries)) { ctx->err = "radiance_lookup: bad arguments"; return B2RT_E_ARG; }
+    PhotonMap &m = ctx->maps[B2RT_MAP_RADIANCE];
+    if (!m.grid_built) { ctx->err = "radiance_lookup: the radiance-photon grid is not built (b2rt_radiance_compute)"; return B2RT_E_STATE; }
+    if (nq == 0) return B2RT_OK;
+    B2RT_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (where == B2RT_DEVICE) return b2rt_radiance_lookup_impl(ctx, nq, queries, out_rgb, out_idx);
+    if (where != B2RT_HOST) { ctx->err = "radiance_lookup: where must be B2RT_HOST or B2RT_DEVICE"; return B2RT_E_ARG; }
+    cudaStream_t st = ctx->stream;
+    B2RT_CUDA(ctx, ctx->d_queries.reserve((size_t)nq * sizeof(b2rt_query)));
+    B2RT_CUDA(ctx, ctx->d_q_rgb.reserve((size_t)nq * 12));
+    B2RT_CUDA(ctx, ctx->d_q_found.reserve((size_t)nq * 4));
+    B2RT_CUDA(ctx, cudaMemcpyAsync(ctx->d_queries.p, queries, (size_t)nq * sizeof(b2rt_query), cudaMemcpyHostToDevice, st));
+    int rc = b2rt_radiance_lookup_impl(ctx, nq, ctx->d_queries.as<b2rt_query>(), ctx->d_q_rgb.as<float>(), ctx->d_q_found.as<int32_t>());
+    if (rc) return rc;
+    if (out_rgb) B2RT_CUDA(ctx, cudaMemcpyAsync(out_rgb, ctx->d_q_rgb.p, (size_t)nq * 12, cudaMemcpyDeviceToHost, st));
+    if (out_idx) B2RT_CUDA(ctx, cudaMemcpyAsync(out_idx, ctx->d_q_found.p, (size_t)nq * 4, cudaMemcpyDeviceToHost, st));
+    B2RT_CUDA(ctx, cudaStreamSynchronize(st));
+    return B2RT_OK;
+}
+
+int b2rt_final_gather_set(b2rt_ctx *ctx, int32_t enable, int32_t gather_samples, float gather_angle_deg) {
+    if (!ctx) return B2RT_E_ARG;
+    if (enable && (gather_samples < 1 || gather_samples > 4096 || !(gather_angle_deg > 0.f) || !(gather_angle_deg < 90.f))) {
+        ctx->err = "final_gather_set: gather_samples in [1, 4096], gather_angle in (0, 90) degrees"; return B2RT_E_ARG;
+    }
+    ctx->fg_enable = enable ? 1 : 0;
+    if (enable) {
+        ctx->fg_samples = gather_samples;
+        // cos(Radians(ga)) (photonmap.cpp:296): float degrees -> float radians -> cos in double, rounded once
+        const float rad = (3.14159265358979323846f / 180.f) * gather_angle_deg;
+        ctx->fg_cos_angle = (float)cos((double)rad);
+    }
+    return B2RT_OK;
 }
 
 int b2rt_render_frame(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_params *fp, float *out_rgb, int where) {

@@ -135,7 +135,13 @@ struct b2rt_ctx {
     int sampler_type = B2RT_SAMPLER_RANDOM, sampler_nx = 1, sampler_ny = 1;   // b2rt_sampler_set
     int film_variant = 1;               // 1: shared-memory tiles (film_tile_kernel), 0: one thread per pixel (B2RT_FILM_VARIANT)
     size_t film_smem_opt_in = 0;
-    PhotonMap maps[2];       // B2RT_MAP_CAUSTIC, B2RT_MAP_INDIRECT
+    PhotonMap maps[4];       // B2RT_MAP_CAUSTIC, B2RT_MAP_INDIRECT, B2RT_MAP_DIRECT, B2RT_MAP_RADIANCE
+    // final gathering (finalgather.cu)
+    int fg_enable = 0, fg_samples = 32;                 // b2rt_final_gather_set
+    float fg_cos_angle = 0.98480775301220802f;          // cos(10 degrees)
+    bool radiance_computed = false;                     // maps[3].alpha holds Lo (true) or rho_r (false)
+    DevBuf d_fg_queries, d_fg_E, d_fg_Etmp, d_fg_idx, d_fg_r2, d_fg_found, d_fg_slots, d_fg_cnt, d_fg_cnt2;
+    DevBuf d_fg_dirs, d_fg_pend, d_fg_pq, d_fg_pidx, d_fg_flag;
     b2rt_accel_info info{};
 };
 
@@ -178,5 +184,12 @@ int b2rt_film_impl(b2rt_ctx *ctx, const b2rt_filter *f, const int32_t cells[4], 
 int b2rt_gather_impl(b2rt_ctx *ctx, int map, int64_t nq, const b2rt_query *d_queries, int k, float max_dist2,
                      float *d_rgb, float *d_r2, int32_t *d_found, int32_t *d_idx);
 void b2rt_fill_dscene(b2rt_ctx *ctx, DScene *sc);
+// final gathering (finalgather.cu)
+int b2rt_photons_trace_fg_impl(b2rt_ctx *ctx, int64_t first_path, int64_t n_paths, int max_depth, int64_t n_stored[2]);
+int b2rt_irradiance_impl(b2rt_ctx *ctx, int map, int64_t nq, const b2rt_query *d_queries, int k, float max_dist2,
+                         float *d_E, bool accumulate);
+int b2rt_radiance_compute_impl(b2rt_ctx *ctx, int nused, float max_dist2);
+int b2rt_radiance_lookup_impl(b2rt_ctx *ctx, int64_t nq, const b2rt_query *d_queries, float *d_rgb, int32_t *d_idx);
+int b2rt_final_gather_impl(b2rt_ctx *ctx, int64_t nq, const b2rt_query *d_queries, float max_dist2, float *d_rgb);
 // exclusive scan of n uint32 in place (single pass, small n helper used by build)
 int b2rt_exclusive_scan_u32(b2rt_ctx *ctx, uint32_t *d, int64_t n, uint32_t *d_total);

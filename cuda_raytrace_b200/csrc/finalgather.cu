@@ -1,0 +1,487 @@
+// Final gathering: pbrt's PhotonIntegrator with finalgather true, the integrator's default.
+// The reference's GPU code has no equivalent (its finalGatheringCamera, photon_mapping/gathering.cu:129-146, averages
+// the k-nearest estimate); what is followed here is pbrt-v2/src/integrators/photonmap.cpp:
+//   K15 fg_photon_kernel      :440-490  direct photons + radiance photons (u < 0.125 per deposit) of a path range
+//   K16 irradiance_kernel     :263-283  EPhoton from the k-nearest sets the gather kernel (K12) selects
+//       radiance_lo_kernel    :585-621  ComputeRadianceTask: Lo = INV_PI * rho_r * (E_direct + E_indirect + E_caustic)
+//   K17 radiance_lookup_kernel:156-172  nearest radiance photon with Dot(rp.n, n) > 0, unbounded radius (hash grid
+//                                       shells instead of pbrt's kd-tree; exact, b2rt_fg.cuh)
+//   K18 final_gather_kernel   :645-758  one warp per shading point: lane = gather ray (BSDF-sampled and photon-cone-sampled,
+//                                       power heuristic), traversal + radiance-photon lookup inline, fixed-order butterfly sum
+// Randomness is Philox(seed; pixel, sample | tree node, ray): an image tile is bit-identical on any GPU.
+#include "b2rt_shade.cuh"
+#include "b2rt_fg.cuh"
+#include <algorithm>
+
+namespace {
+
+constexpr int FG_THREADS = 128;
+constexpr int FG_NDIR = 50;              // nIndirSamplePhotons (photonmap.cpp:652)
+
+// ---- K15 ---------------------------------------------------------------------------------------------------------------
+// slots[(path - first) * (max_depth + 1) + j]: the path's direct photon (if any) first, then its radiance photons in
+// bounce order.  Same emission / bounce / roulette stream as photon_trace_kernel (photon.cu), so the paths are the very
+// paths whose caustic / indirect photons sit in maps 0 and 1; the radiance-photon draw is block 2 of the bounce counter,
+// which the path itself never reads.
+__global__ void __launch_bounds__(FG_THREADS)
+fg_photon_kernel(DScene sc, uint32_t seed_lo, uint32_t seed_hi, int64_t first_path, int64_t n_paths, int max_depth,
+                 b2rt_photon *__restrict__ slots, uint32_t *__restrict__ cnt_d, uint32_t *__restrict__ cnt_r, uint32_t *status) {
+    int64_t li = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (li >= n_paths) return;
+    const uint64_t path = (uint64_t)(first_path + li);
+    const uint32_t p_lo = (uint32_t)path, p_hi = (uint32_t)(path >> 32);
+    uint32_t nd = 0, nr = 0;
+    b2rt_photon *my = slots + li * (max_depth + 1);
+    u4 r0 = philox4x32_10(p_lo, p_hi, 0u, 0u, seed_lo, seed_hi);
+    u4 r1 = philox4x32_10(p_lo, p_hi, 0u, 1u, seed_lo, seed_hi);
+    f3 o, d, alpha;
+    float tmin;
+    bool alive = emit_photon(sc, u01(r0.x), u01(r0.y), u01(r0.z), u01(r1.x), u01(r1.y), o, d, tmin, alpha);
+    int n_isect = 0;
+    bool overflow = false;
+    while (alive) {
+        HitD h;
+        if (!traverse<false>(sc.nodes, sc.recs, sc.analytic, o.x, o.y, o.z, d.x, d.y, d.z, tmin, INFINITY, h, overflow))
+            break;
+        ++n_isect;
+        Surface s = make_surface(sc, h, o, d);
+        Mat m = load_material(sc, s.material);
+        f3 wo = -d;
+        if (m.type == B2RT_MAT_MATTE) {     // hasNonSpecular: a photon is deposited here (direct, indirect or caustic)
+            if (n_isect == 1) {
+                float4 *dst = reinterpret_cast<float4 *>(my);
+                dst[0] = make_float4(s.p.x, s.p.y, s.p.z, __uint_as_float(fg_oct_encode(wo)));
+                dst[1] = make_float4(alpha.x, alpha.y, alpha.z, __uint_as_float(p_lo));
+                nd = 1;
+            }
+            u4 rr = philox4x32_10(p_lo, p_hi, (uint32_t)n_isect, 2u, seed_lo, seed_hi);
+            if (u01(rr.x) < .125f) {
+                f3 n = dot3(s.n, wo) < 0.f ? -s.n : s.n;                        // Faceforward(dg.nn, -photonRay.d)
+                float4 *dst = reinterpret_cast<float4 *>(my + nd + nr);
+                dst[0] = make_float4(s.p.x, s.p.y, s.p.z, __uint_as_float(fg_oct_encode(n)));
+                dst[1] = make_float4(m.kd.x, m.kd.y, m.kd.z, __uint_as_float(p_lo));   // rho_r of the Lambertian lobe
+                ++nr;
+            }
+        }
+        if (n_isect >= max_depth) break;
+        u4 rb = philox4x32_10(p_lo, p_hi, (uint32_t)n_isect, 0u, seed_lo, seed_hi);
+        BsdfSample bs;
+        if (!sample_bsdf(s, m, wo, u01(rb.x), u01(rb.y), u01(rb.z), bs)) break;
+        if (is_black(bs.f) || bs.pdf == 0.f) break;
+        f3 anew = mk3(alpha.x * bs.f.x * bs.absdot / bs.pdf, alpha.y * bs.f.y * bs.absdot / bs.pdf,
+                      alpha.z * bs.f.z * bs.absdot / bs.pdf);
+        float cont = fminf(1.f, lum(anew) / lum(alpha));
+        if (u01(rb.w) > cont) break;
+        alpha = mk3(anew.x / cont, anew.y / cont, anew.z / cont);
+        o = s.p; d = bs.wi; tmin = s.ray_eps;
+    }
+    cnt_d[li] = nd;
+    cnt_r[li] = nr;
+    if (overflow) atomicAdd(status, 1u);
+}
+
+__global__ void __launch_bounds__(256)
+fg_compact_kernel(const b2rt_photon *__restrict__ slots, const uint32_t *__restrict__ off_d, const uint32_t *__restrict__ off_r,
+                  const uint32_t *__restrict__ tot, int64_t n_paths, int stride, b2rt_photon *__restrict__ out_d,
+                  b2rt_photon *__restrict__ out_r) {
+    int64_t li = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (li >= n_paths) return;
+    uint32_t od = off_d[li], orr = off_r[li];
+    uint32_t nd = ((li + 1 < n_paths) ? off_d[li + 1] : tot[0]) - od;
+    uint32_t nr = ((li + 1 < n_paths) ? off_r[li + 1] : tot[1]) - orr;
+    const float4 *src = reinterpret_cast<const float4 *>(slots + li * stride);
+    for (uint32_t j = 0; j < nd; ++j) {
+        float4 *dst = reinterpret_cast<float4 *>(out_d + od + j);
+        dst[0] = src[2 * j]; dst[1] = src[2 * j + 1];
+    }
+    for (uint32_t j = 0; j < nr; ++j) {
+        float4 *dst = reinterpret_cast<float4 *>(out_r + orr + j);
+        dst[0] = src[2 * (nd + j)]; dst[1] = src[2 * (nd + j) + 1];
+    }
+}
+
+// ---- K16 ---------------------------------------------------------------------------------------------------------------
+// EPhoton over the set K12 selected (idx: k entries per query, ascending (d2, index), -1 padded): E = sum of alpha over
+// the photons with Dot(n, wi) > 0, in that order, / (nPaths * md2 * M_PI) with pbrt's float * float * double product.
+__global__ void __launch_bounds__(256)
+irradiance_kernel(const b2rt_photon *__restrict__ sorted, const b2rt_query *__restrict__ queries, const int32_t *__restrict__ idx,
+                  const float *__restrict__ r2, const int32_t *__restrict__ found, int64_t nq, int k, float n_paths,
+                  float *__restrict__ E, int accumulate) {
+    int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= nq) return;
+    const float4 *Q = reinterpret_cast<const float4 *>(queries + q);
+    const float4 q0 = Q[0], q1 = Q[1];
+    const f3 n = mk3(q0.w, q1.x, q1.y);
+    f3 acc = mk3(0.f, 0.f, 0.f);
+    const int nf = found[q];
+    for (int j = 0; j < nf; ++j) {
+        const int32_t i = idx[q * k + j];
+        const float4 *pp = reinterpret_cast<const float4 *>(sorted + i);
+        const float4 A = __ldg(pp);
+        if (dot3(n, fg_oct_decode(__float_as_uint(A.w))) > 0.f) {
+            const float4 B = __ldg(pp + 1);
+            acc = acc + mk3(B.x, B.y, B.z);
+        }
+    }
+    f3 e = mk3(0.f, 0.f, 0.f);
+    if (nf > 0) {
+        const float den = (float)((double)(n_paths * r2[q]) * 3.14159265358979323846);
+        e = mk3(acc.x / den, acc.y / den, acc.z / den);
+    }
+    if (accumulate) { e.x = E[3 * q] + e.x; e.y = E[3 * q + 1] + e.y; e.z = E[3 * q + 2] + e.z; }
+    E[3 * q] = e.x; E[3 * q + 1] = e.y; E[3 * q + 2] = e.z;
+}
+
+// radiance photon i -> the query (p, n) its irradiance is estimated at
+__global__ void __launch_bounds__(256)
+radiance_queries_kernel(const b2rt_photon *__restrict__ rp, int64_t n, b2rt_query *__restrict__ q) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 A = reinterpret_cast<const float4 *>(rp + i)[0];
+    const f3 nn = fg_oct_decode(__float_as_uint(A.w));
+    float4 *dst = reinterpret_cast<float4 *>(q + i);
+    dst[0] = make_float4(A.x, A.y, A.z, nn.x);
+    dst[1] = make_float4(nn.y, nn.z, 0.f, 0.f);
+    dst[2] = make_float4(0.f, 0.f, 0.f, 0.f);
+}
+// rp.Lo += INV_PI * rho_r * E   (photonmap.cpp:608); rho_t is black for the Lambertian lobe
+__global__ void __launch_bounds__(256)
+radiance_lo_kernel(b2rt_photon *__restrict__ rp, const float *__restrict__ E, int64_t n) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float *a = rp[i].alpha;
+    const bool blk = a[0] == 0.f && a[1] == 0.f && a[2] == 0.f;
+    for (int c = 0; c < 3; ++c) a[c] = blk ? 0.f : (B2_INV_PI * a[c]) * E[3 * i + c];
+}
+
+// ---- K17 ---------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128)
+radiance_lookup_kernel(FgGrid g, const float4 *__restrict__ photons, const uint32_t *__restrict__ cell_start,
+                       const b2rt_query *__restrict__ queries, int64_t nq, float *__restrict__ out_rgb, int32_t *__restrict__ out_idx) {
+    int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= nq) return;
+    const float4 *Q = reinterpret_cast<const float4 *>(queries + q);
+    const float4 q0 = Q[0], q1 = Q[1];
+    float d2;
+    const int i = fg_radiance_nearest(g, photons, cell_start, mk3(q0.x, q0.y, q0.z), mk3(q0.w, q1.x, q1.y), d2);
+    if (out_idx) out_idx[q] = i;
+    if (out_rgb) {
+        float4 B = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (i >= 0) B = photons[2 * (size_t)i + 1];
+        out_rgb[3 * q] = B.x; out_rgb[3 * q + 1] = B.y; out_rgb[3 * q + 2] = B.z;
+    }
+}
+
+// ---- photon directions of the 50 nearest indirect photons: radius doubling for the queries that found fewer ------------
+__global__ void __launch_bounds__(256)
+fg_flag_kernel(const int32_t *__restrict__ found, int64_t nq, int need, uint32_t *__restrict__ flag) {
+    int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (q < nq) flag[q] = found[q] < need ? 1u : 0u;
+}
+__global__ void __launch_bounds__(256)
+fg_pending_kernel(const b2rt_query *__restrict__ queries, const int32_t *__restrict__ found, const uint32_t *__restrict__ off,
+                  int64_t nq, int need, b2rt_query *__restrict__ pq, uint32_t *__restrict__ pidx) {
+    int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= nq || found[q] >= need) return;
+    const uint32_t j = off[q];
+    const float4 *src = reinterpret_cast<const float4 *>(queries + q);
+    float4 *dst = reinterpret_cast<float4 *>(pq + j);
+    dst[0] = src[0]; dst[1] = src[1]; dst[2] = src[2];
+    pidx[j] = (uint32_t)q;
+}
+__global__ void __launch_bounds__(256)
+fg_scatter_kernel(const uint32_t *__restrict__ pidx, const int32_t *__restrict__ tidx, const int32_t *__restrict__ tfound,
+                  int64_t np, int k, int32_t *__restrict__ idx, int32_t *__restrict__ found) {
+    int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= np * k) return;
+    const int64_t j = t / k;
+    const int e = (int)(t % k);
+    const uint32_t q = pidx[j];
+    idx[(int64_t)q * k + e] = tidx[t];
+    if (e == 0) found[q] = tfound[j];
+}
+
+// ---- K18 ---------------------------------------------------------------------------------------------------------------
+struct FgArgs {
+    DScene sc;
+    FgGrid g;
+    const float4 *rad;                 // sorted radiance photons, float4 pairs
+    const uint32_t *rad_cells;
+    const b2rt_photon *ind;            // sorted indirect photons (directions for the cone sampling)
+    const int32_t *idx;                // [nq * FG_NDIR] nearest indirect photons per query
+    const int32_t *found;
+    const b2rt_query *queries;
+    int64_t nq;
+    int gs;                            // gather rays per strategy (pbrt: gatherSamples / 2)
+    float cos_angle, cone_pdf;
+    uint32_t k0, k1;
+    float *out_rgb;
+    uint32_t *status;
+};
+
+__global__ void __launch_bounds__(FG_THREADS)
+final_gather_kernel(const FgArgs A) {
+    __shared__ f3 s_dirs[FG_THREADS / 32][FG_NDIR];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t wstride = (int64_t)gridDim.x * (FG_THREADS / 32);
+    bool overflow = false;
+    for (int64_t q = (int64_t)blockIdx.x * (FG_THREADS / 32) + warp; q < A.nq; q += wstride) {
+        const float4 *Q = reinterpret_cast<const float4 *>(A.queries + q);
+        const float4 q0 = __ldg(Q), q1 = __ldg(Q + 1), q2 = __ldg(Q + 2);
+        const f3 p = mk3(q0.x, q0.y, q0.z), nf = mk3(q0.w, q1.x, q1.y), kd = mk3(q1.z, q1.w, q2.x);
+        const float ray_eps = q2.y;
+        const uint32_t gpix = __float_as_uint(q2.z), kc = __float_as_uint(q2.w);
+        const int nd = min(A.found[q], FG_NDIR);
+        __syncwarp();
+        for (int j = lane; j < nd; j += 32) {
+            const int32_t i = A.idx[q * FG_NDIR + j];
+            s_dirs[warp][j] = fg_oct_decode(__float_as_uint(__ldg(reinterpret_cast<const float4 *>(A.ind + i)).w));
+        }
+        __syncwarp();
+        f3 sn, tn;
+        fg_coordinate_system(nf, sn, tn);
+        const f3 fr = kd * B2_INV_PI;                                    // Lambertian f, throughput folded into kd
+        f3 accB = mk3(0.f, 0.f, 0.f), accC = mk3(0.f, 0.f, 0.f);
+        for (int base = 0; base < 2 * A.gs; base += 32) {
+            const int r = base + lane;
+            if (r >= 2 * A.gs) continue;
+            const bool cone = r >= A.gs;
+            const u4 u = philox4x32_10(gpix, kc, 0x200u + (uint32_t)r, 0u, A.k0, A.k1);
+            f3 wi;
+            float cosw;
+            if (!cone) {
+                // Lambertian::Sample_f: cosine hemisphere on wo's side (= nf's side), pdf = |cos| / pi
+                const f3 l = cosine_sample_hemisphere(u01(u.x), u01(u.y));
+                wi = mk3(sn.x * l.x + tn.x * l.y + nf.x * l.z, sn.y * l.x + tn.y * l.y + nf.y * l.z,
+                         sn.z * l.x + tn.z * l.y + nf.z * l.z);
+                cosw = dot3(wi, nf);
+                if (!(l.z > 0.f) || !(cosw > 0.f)) continue;
+            } else {
+                if (nd == 0) continue;
+                const int pn = min(nd - 1, (int)floorf(u01(u.z) * (float)nd));
+                const f3 z = s_dirs[warp][pn];
+                f3 vx, vy;
+                fg_coordinate_system(z, vx, vy);
+                wi = fg_sample_cone(u01(u.x), u01(u.y), A.cos_angle, vx, vy, z);
+                cosw = dot3(wi, nf);
+                if (!(cosw > 0.f)) continue;                                // bsdf->f(wo, wi) is black
+            }
+            HitD h;
+            if (!traverse<false>(A.sc.nodes, A.sc.recs, A.sc.analytic, p.x, p.y, p.z, wi.x, wi.y, wi.z, ray_eps, INFINITY, h,
+                                 overflow))
+                continue;
+            const Surface s = make_surface(A.sc, h, p, wi);
+            const f3 ng = dot3(s.n, -wi) < 0.f ? -s.n : s.n;               // Faceforward(nGather, -bounceRay.d)
+            float d2;
+            const int ri = fg_radiance_nearest(A.g, A.rad, A.rad_cells, s.p, ng, d2);
+            if (ri < 0) continue;
+            const float4 Lo = __ldg(A.rad + 2 * (size_t)ri + 1);
+            const float bsdf_pdf = fabsf(cosw) * B2_INV_PI;
+            const float photon_pdf = fg_photon_pdf(s_dirs[warp], nd, wi, A.cos_angle, A.cone_pdf);
+            const float absdot = fabsf(cosw);
+            if (!cone) {
+                const float wt = fg_power_heuristic(A.gs, bsdf_pdf, A.gs, photon_pdf);
+                const float w = absdot * wt / bsdf_pdf;
+                accB = accB + mk3(fr.x * Lo.x * w, fr.y * Lo.y * w, fr.z * Lo.z * w);
+            } else {
+                const float wt = fg_power_heuristic(A.gs, photon_pdf, A.gs, bsdf_pdf);
+                accC = accC + mk3(fr.x * Lo.x * absdot * wt / photon_pdf, fr.y * Lo.y * absdot * wt / photon_pdf,
+                                  fr.z * Lo.z * absdot * wt / photon_pdf);
+            }
+        }
+        __syncwarp();
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            accB.x += __shfl_xor_sync(0xffffffffu, accB.x, o); accB.y += __shfl_xor_sync(0xffffffffu, accB.y, o);
+            accB.z += __shfl_xor_sync(0xffffffffu, accB.z, o);
+            accC.x += __shfl_xor_sync(0xffffffffu, accC.x, o); accC.y += __shfl_xor_sync(0xffffffffu, accC.y, o);
+            accC.z += __shfl_xor_sync(0xffffffffu, accC.z, o);
+        }
+        if (lane == 0) {
+            const float g = (float)A.gs;
+            A.out_rgb[3 * q] = accB.x / g + accC.x / g;
+            A.out_rgb[3 * q + 1] = accB.y / g + accC.y / g;
+            A.out_rgb[3 * q + 2] = accB.z / g + accC.z / g;
+        }
+    }
+    if (overflow) atomicAdd(A.status, 1u);
+}
+
+FgGrid fg_grid_of(const PhotonMap &m) {
+    FgGrid g;
+    float mx = 0.f;
+    for (int a = 0; a < 3; ++a) {
+        g.lo[a] = m.grid.origin[a]; g.dims[a] = m.grid.dims[a];
+        float hi = m.grid.origin[a] + (float)m.grid.dims[a] * m.grid.cell_size;
+        mx = fmaxf(mx, fmaxf(fabsf(m.grid.origin[a]), fabsf(hi)));
+    }
+    g.cell = m.grid.cell_size; g.inv = m.grid.inv_cell;
+    g.slack = 1e-5f * mx + 1e-4f * m.grid.cell_size;
+    return g;
+}
+
+}  // namespace
+
+int b2rt_photons_reserve(b2rt_ctx *ctx, DevBuf &b, int64_t keep, int64_t want);
+
+int b2rt_photons_trace_fg_impl(b2rt_ctx *ctx, int64_t first_path, int64_t n_paths, int max_depth, int64_t n_stored[2]) {
+    cudaStream_t st = ctx->stream;
+    if (n_stored) n_stored[0] = n_stored[1] = 0;
+    if (n_paths == 0) return B2RT_OK;
+    if (n_paths > (1ll << 28)) { ctx->err = "photons_trace_fg: at most 2^28 paths per call"; return B2RT_E_ARG; }
+    DScene sc;
+    b2rt_fill_dscene(ctx, &sc);
+    const int stride = max_depth + 1;
+    B2RT_CUDA(ctx, ctx->d_fg_slots.reserve((size_t)n_paths * stride * sizeof(b2rt_photon)));
+    B2RT_CUDA(ctx, ctx->d_fg_cnt.reserve((size_t)n_paths * 4));
+    B2RT_CUDA(ctx, ctx->d_fg_cnt2.reserve((size_t)n_paths * 4));
+    uint32_t *cnt_d = ctx->d_fg_cnt.as<uint32_t>(), *cnt_r = ctx->d_fg_cnt2.as<uint32_t>();
+    uint32_t *counters = ctx->d_counters.as<uint32_t>();
+    fg_photon_kernel<<<(unsigned)((n_paths + FG_THREADS - 1) / FG_THREADS), FG_THREADS, 0, st>>>(
+        sc, (uint32_t)ctx->seed, (uint32_t)(ctx->seed >> 32), first_path, n_paths, max_depth,
+        ctx->d_fg_slots.as<b2rt_photon>(), cnt_d, cnt_r, counters + 8);
+    B2RT_LAUNCH_CHECK(ctx);
+    int rc = b2rt_exclusive_scan_u32(ctx, cnt_d, n_paths, counters + 32);
+    if (rc) return rc;
+    rc = b2rt_exclusive_scan_u32(ctx, cnt_r, n_paths, counters + 33);
+    if (rc) return rc;
+    uint32_t tot[2];
+    B2RT_CUDA(ctx, cudaMemcpyAsync(tot, counters + 32, 8, cudaMemcpyDeviceToHost, st));
+    B2RT_CUDA(ctx, cudaStreamSynchronize(st));
+    PhotonMap &md = ctx->maps[B2RT_MAP_DIRECT], &mr = ctx->maps[B2RT_MAP_RADIANCE];
+    if (ctx->radiance_computed) { ctx->err = "photons_trace_fg: radiance already computed; clear the photon maps first"; return B2RT_E_STATE; }
+    rc = b2rt_photons_reserve(ctx, md.photons, md.n, md.n + tot[0]);
+    if (rc) return rc;
+    rc = b2rt_photons_reserve(ctx, mr.photons, mr.n, mr.n + tot[1]);
+    if (rc) return rc;
+    fg_compact_kernel<<<(unsigned)((n_paths + 255) / 256), 256, 0, st>>>(
+        ctx->d_fg_slots.as<b2rt_photon>(), cnt_d, cnt_r, counters + 32, n_paths, stride,
+        md.photons.as<b2rt_photon>() + md.n, mr.photons.as<b2rt_photon>() + mr.n);
+    B2RT_LAUNCH_CHECK(ctx);
+    md.n += tot[0]; mr.n += tot[1];
+    md.n_paths += n_paths; mr.n_paths += n_paths;
+    md.grid_built = mr.grid_built = false;
+    if (n_stored) { n_stored[0] = tot[0]; n_stored[1] = tot[1]; }
+    return B2RT_OK;
+}
+
+// E (or E += with accumulate) for nq device queries against `map`; chunks keep the k-nearest index buffer bounded
+int b2rt_irradiance_impl(b2rt_ctx *ctx, int map, int64_t nq, const b2rt_query *d_queries, int k, float max_dist2,
+                         float *d_E, bool accumulate) {
+    PhotonMap &m = ctx->maps[map];
+    const int64_t chunk = 1 << 20;
+    const int64_t cq = std::min<int64_t>(nq, chunk);
+    B2RT_CUDA(ctx, ctx->d_fg_idx.reserve((size_t)cq * k * 4));
+    B2RT_CUDA(ctx, ctx->d_fg_r2.reserve((size_t)cq * 4));
+    B2RT_CUDA(ctx, ctx->d_fg_found.reserve((size_t)cq * 4));
+    for (int64_t q0 = 0; q0 < nq; q0 += chunk) {
+        const int64_t n = std::min<int64_t>(chunk, nq - q0);
+        int rc = b2rt_gather_impl(ctx, map, n, d_queries + q0, k, max_dist2, nullptr, ctx->d_fg_r2.as<float>(),
+                                  ctx->d_fg_found.as<int32_t>(), ctx->d_fg_idx.as<int32_t>());
+        if (rc) return rc;
+        irradiance_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(
+            m.sorted.as<b2rt_photon>(), d_queries + q0, ctx->d_fg_idx.as<int32_t>(), ctx->d_fg_r2.as<float>(),
+            ctx->d_fg_found.as<int32_t>(), n, k, (float)m.n_paths, d_E + 3 * q0, accumulate ? 1 : 0);
+        B2RT_LAUNCH_CHECK(ctx);
+    }
+    return B2RT_OK;
+}
+
+int b2rt_radiance_compute_impl(b2rt_ctx *ctx, int nused, float max_dist2) {
+    PhotonMap &mr = ctx->maps[B2RT_MAP_RADIANCE];
+    if (ctx->radiance_computed) { ctx->err = "radiance_compute: already computed for these radiance photons"; return B2RT_E_STATE; }
+    const int64_t n = mr.n;
+    if (n > 0) {
+        B2RT_CUDA(ctx, ctx->d_fg_queries.reserve((size_t)n * sizeof(b2rt_query)));
+        B2RT_CUDA(ctx, ctx->d_fg_E.reserve((size_t)n * 12));
+        B2RT_CUDA(ctx, cudaMemsetAsync(ctx->d_fg_E.p, 0, (size_t)n * 12, ctx->stream));
+        radiance_queries_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(mr.photons.as<b2rt_photon>(), n,
+                                                                                        ctx->d_fg_queries.as<b2rt_query>());
+        B2RT_LAUNCH_CHECK(ctx);
+        // E = EPhoton(direct) + EPhoton(indirect) + EPhoton(caustic), in pbrt's order (photonmap.cpp:600-605)
+        const int order[3] = {B2RT_MAP_DIRECT, B2RT_MAP_INDIRECT, B2RT_MAP_CAUSTIC};
+        for (int t = 0; t < 3; ++t) {
+            PhotonMap &m = ctx->maps[order[t]];
+            if (m.n == 0) continue;
+            if (!m.grid_built) { ctx->err = "radiance_compute: a non-empty photon map has no grid (b2rt_photon_grid_build)"; return B2RT_E_STATE; }
+            int rc = b2rt_irradiance_impl(ctx, order[t], n, ctx->d_fg_queries.as<b2rt_query>(), nused, max_dist2,
+                                          ctx->d_fg_E.as<float>(), true);
+            if (rc) return rc;
+        }
+        radiance_lo_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(mr.photons.as<b2rt_photon>(),
+                                                                                   ctx->d_fg_E.as<float>(), n);
+        B2RT_LAUNCH_CHECK(ctx);
+    }
+    ctx->radiance_computed = true;
+    mr.grid_built = false;
+    return b2rt_photon_grid_build_impl(ctx, B2RT_MAP_RADIANCE, 0.f, 0.f);
+}
+
+int b2rt_radiance_lookup_impl(b2rt_ctx *ctx, int64_t nq, const b2rt_query *d_queries, float *d_rgb, int32_t *d_idx) {
+    PhotonMap &mr = ctx->maps[B2RT_MAP_RADIANCE];
+    if (nq <= 0) return B2RT_OK;
+    radiance_lookup_kernel<<<(unsigned)((nq + 127) / 128), 128, 0, ctx->stream>>>(
+        fg_grid_of(mr), mr.sorted.as<float4>(), mr.cell_start.as<uint32_t>(), d_queries, nq, d_rgb, d_idx);
+    B2RT_LAUNCH_CHECK(ctx);
+    return B2RT_OK;
+}
+
+// the indirect term of the camera pass with final gathering: d_rgb[3 * nq]
+int b2rt_final_gather_impl(b2rt_ctx *ctx, int64_t nq, const b2rt_query *d_queries, float max_dist2, float *d_rgb) {
+    if (nq <= 0) return B2RT_OK;
+    cudaStream_t st = ctx->stream;
+    PhotonMap &mi = ctx->maps[B2RT_MAP_INDIRECT], &mr = ctx->maps[B2RT_MAP_RADIANCE];
+    const int k = FG_NDIR;
+    const int need = (int)std::min<int64_t>(k, mi.n);
+    B2RT_CUDA(ctx, ctx->d_fg_dirs.reserve((size_t)nq * k * 4));
+    B2RT_CUDA(ctx, ctx->d_fg_found.reserve((size_t)nq * 4));
+    B2RT_CUDA(ctx, ctx->d_fg_r2.reserve((size_t)nq * 4));
+    int32_t *idx = ctx->d_fg_dirs.as<int32_t>(), *found = ctx->d_fg_found.as<int32_t>();
+    int rc = b2rt_gather_impl(ctx, B2RT_MAP_INDIRECT, nq, d_queries, k, max_dist2, nullptr, ctx->d_fg_r2.as<float>(), found, idx);
+    if (rc) return rc;
+    // pbrt doubles the squared search radius until 50 photons are found (photonmap.cpp:655-660); only the queries that
+    // are still short are searched again
+    uint32_t *counters = ctx->d_counters.as<uint32_t>();
+    float md2 = max_dist2;
+    for (int it = 0; it < 40 && need > 0; ++it) {
+        B2RT_CUDA(ctx, ctx->d_fg_flag.reserve((size_t)nq * 4));
+        uint32_t *flag = ctx->d_fg_flag.as<uint32_t>();
+        fg_flag_kernel<<<(unsigned)((nq + 255) / 256), 256, 0, st>>>(found, nq, need, flag);
+        B2RT_LAUNCH_CHECK(ctx);
+        rc = b2rt_exclusive_scan_u32(ctx, flag, nq, counters + 34);
+        if (rc) return rc;
+        uint32_t np = 0;
+        B2RT_CUDA(ctx, cudaMemcpyAsync(&np, counters + 34, 4, cudaMemcpyDeviceToHost, st));
+        B2RT_CUDA(ctx, cudaStreamSynchronize(st));
+        if (np == 0) break;
+        md2 *= 2.f;
+        B2RT_CUDA(ctx, ctx->d_fg_pq.reserve((size_t)np * sizeof(b2rt_query)));
+        B2RT_CUDA(ctx, ctx->d_fg_pidx.reserve((size_t)np * 4));
+        B2RT_CUDA(ctx, ctx->d_fg_idx.reserve((size_t)np * k * 4));
+        B2RT_CUDA(ctx, ctx->d_fg_pend.reserve((size_t)np * 4));
+        fg_pending_kernel<<<(unsigned)((nq + 255) / 256), 256, 0, st>>>(d_queries, found, flag, nq, need,
+                                                                         ctx->d_fg_pq.as<b2rt_query>(), ctx->d_fg_pidx.as<uint32_t>());
+        B2RT_LAUNCH_CHECK(ctx);
+        rc = b2rt_gather_impl(ctx, B2RT_MAP_INDIRECT, np, ctx->d_fg_pq.as<b2rt_query>(), k, md2, nullptr, ctx->d_fg_r2.as<float>(),
+                              ctx->d_fg_pend.as<int32_t>(), ctx->d_fg_idx.as<int32_t>());
+        if (rc) return rc;
+        fg_scatter_kernel<<<(unsigned)(((int64_t)np * k + 255) / 256), 256, 0, st>>>(
+            ctx->d_fg_pidx.as<uint32_t>(), ctx->d_fg_idx.as<int32_t>(), ctx->d_fg_pend.as<int32_t>(), np, k, idx, found);
+        B2RT_LAUNCH_CHECK(ctx);
+    }
+    FgArgs A;
+    b2rt_fill_dscene(ctx, &A.sc);
+    A.g = fg_grid_of(mr);
+    A.rad = mr.sorted.as<float4>(); A.rad_cells = mr.cell_start.as<uint32_t>();
+    A.ind = mi.sorted.as<b2rt_photon>(); A.idx = idx; A.found = found; A.queries = d_queries; A.nq = nq;
+    A.gs = std::max(1, ctx->fg_samples / 2);
+    A.cos_angle = ctx->fg_cos_angle; A.cone_pdf = fg_cone_pdf(ctx->fg_cos_angle);
+    A.k0 = (uint32_t)ctx->seed ^ 0x46475448u; A.k1 = (uint32_t)(ctx->seed >> 32);      // 'FGTH' stream
+    A.out_rgb = d_rgb; A.status = counters + 8;
+    int64_t blocks = (nq + FG_THREADS / 32 - 1) / (FG_THREADS / 32);
+    const int64_t cap = (int64_t)ctx->sm_count * 8;
+    if (blocks > cap) blocks = cap;
+    final_gather_kernel<<<(unsigned)blocks, FG_THREADS, 0, st>>>(A);
+    B2RT_LAUNCH_CHECK(ctx);
+    return B2RT_OK;
+}

@@ -280,7 +280,7 @@ int b2rt_upload_tables(b2rt_ctx *ctx) {
 }
 
 // grow a photon array keeping its first `keep` photons
-static int photons_reserve(b2rt_ctx *ctx, DevBuf &b, int64_t keep, int64_t want) {
+int b2rt_photons_reserve(b2rt_ctx *ctx, DevBuf &b, int64_t keep, int64_t want) {
     size_t need = (size_t)want * sizeof(b2rt_photon);
     if (need <= b.cap) return B2RT_OK;
     size_t ncap = need + need / 2 + 4096;
@@ -336,9 +336,9 @@ int b2rt_photons_trace_impl(b2rt_ctx *ctx, int64_t first_path, int64_t n_paths, 
     B2RT_CUDA(ctx, cudaMemcpyAsync(tot, counters + 10, 8, cudaMemcpyDeviceToHost, st));
     B2RT_CUDA(ctx, cudaStreamSynchronize(st));
     PhotonMap &mc = ctx->maps[B2RT_MAP_CAUSTIC], &mi = ctx->maps[B2RT_MAP_INDIRECT];
-    rc = photons_reserve(ctx, mc.photons, mc.n, mc.n + tot[0]);
+    rc = b2rt_photons_reserve(ctx, mc.photons, mc.n, mc.n + tot[0]);
     if (rc) return rc;
-    rc = photons_reserve(ctx, mi.photons, mi.n, mi.n + tot[1]);
+    rc = b2rt_photons_reserve(ctx, mi.photons, mi.n, mi.n + tot[1]);
     if (rc) return rc;
     photon_compact_kernel<<<(unsigned)((n_paths + 255) / 256), 256, 0, st>>>(
         ctx->d_slots.as<b2rt_photon>(), cnt_c, cnt_i, counters + 10, n_paths, max_depth,

@@ -215,7 +215,10 @@ render_li_kernel(DScene sc, b2rt_camera cam, b2rt_frame_params fp, uint32_t seed
                     float4 *dst = reinterpret_cast<float4 *>(myq + nq);
                     dst[0] = make_float4(sf.p.x, sf.p.y, sf.p.z, nf.x);
                     dst[1] = make_float4(nf.y, nf.z, kd.x, kd.y);
-                    dst[2] = make_float4(kd.z, 0.f, 0.f, 0.f);
+                    // pad: what the final-gather stage needs to continue from this leaf (ray epsilon, and the Philox
+                    // counter words: pixel id, sample number | specular-tree node); K12 never reads it
+                    dst[2] = make_float4(kd.z, sf.ray_eps, __uint_as_float(gpix),
+                                         __uint_as_float((uint32_t)k | (nd.id << 22)));
                     ++nq;
                 } else dropped = true;
             }
@@ -353,6 +356,10 @@ int b2rt_render_impl(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_par
     if (any_spec) { int d = fp->max_specular_depth < 1 ? 1 : fp->max_specular_depth; slots = 1 << (d - 1 > 5 ? 5 : d - 1); }
     const bool use_c = fp->use_caustic && ctx->maps[0].grid_built && ctx->maps[0].n > 0;
     const bool use_i = fp->use_indirect && ctx->maps[1].grid_built && ctx->maps[1].n > 0;
+    const bool use_fg = use_i && ctx->fg_enable;
+    if (use_fg && !(ctx->radiance_computed && ctx->maps[B2RT_MAP_RADIANCE].grid_built)) {
+        ctx->err = "render_frame: final gathering is on but b2rt_radiance_compute has not been called"; return B2RT_E_STATE;
+    }
     b2rt_frame_params p = *fp;
     p.use_caustic = use_c; p.use_indirect = use_i;
     // pixel filter wider than the pixel: trace the sample cells around the crop window that reach into it, keep every
@@ -414,8 +421,11 @@ int b2rt_render_impl(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_par
                 rgb_c = ctx->d_q_rgb.as<float>();
             }
             if (use_i) {
-                rc = b2rt_gather_impl(ctx, 1, tot, ctx->d_queries.as<b2rt_query>(), fp->nused, fp->max_dist2,
-                                      ctx->d_q_rgb2.as<float>(), nullptr, nullptr, nullptr);
+                if (use_fg)       // one-bounce final gathering instead of the direct estimate (photonmap.cpp:645-758)
+                    rc = b2rt_final_gather_impl(ctx, tot, ctx->d_queries.as<b2rt_query>(), fp->max_dist2, ctx->d_q_rgb2.as<float>());
+                else
+                    rc = b2rt_gather_impl(ctx, 1, tot, ctx->d_queries.as<b2rt_query>(), fp->nused, fp->max_dist2,
+                                          ctx->d_q_rgb2.as<float>(), nullptr, nullptr, nullptr);
                 if (rc) return rc;
                 rgb_i = ctx->d_q_rgb2.as<float>();
             }

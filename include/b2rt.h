@@ -103,7 +103,10 @@ int b2rt_trace_any(b2rt_ctx *ctx, int64_t nrays, const b2rt_ray *rays, uint8_t *
 
 /* ---- photon pass: replaces photontracing_camera / photontracing_closest_hit (cuda_render/photon_mapping/
  * photontracing.cu:80-185) and the host-side CreatePhotonMap kd-tree build (photonmappingrenderer.cpp:150-180) -- */
-enum { B2RT_MAP_CAUSTIC = 0, B2RT_MAP_INDIRECT = 1 };
+enum { B2RT_MAP_CAUSTIC = 0, B2RT_MAP_INDIRECT = 1,
+       B2RT_MAP_DIRECT = 2,      /* final gathering only: photons of a path's FIRST diffuse hit (photonmap.cpp:468-472) */
+       B2RT_MAP_RADIANCE = 3 };  /* final gathering only: radiance photons; wi_oct holds the surface normal, alpha the
+                                    reflectance rho_r until b2rt_radiance_compute turns it into the outgoing radiance Lo */
 /* 32-byte photon (the reference's CudaPhoton is 40 B, photon_mapping/photonmapping.h:32-40).
  * wi_oct: incident direction, octahedral 2 x snorm16 (low half x, high half y); path = emitting path index. */
 typedef struct { float p[3]; uint32_t wi_oct; float alpha[3]; uint32_t path; } b2rt_photon;
@@ -154,6 +157,33 @@ int b2rt_gather(b2rt_ctx *ctx, int32_t map, int64_t nqueries, const b2rt_query *
  * idx_out[nqueries*k], -1 padded */
 int b2rt_gather_sets(b2rt_ctx *ctx, int32_t map, int64_t nqueries, const b2rt_query *queries, int32_t k,
                      float max_dist2, int32_t *idx_out, int where);
+
+/* ---- final gathering: replaces nothing in cuda_render (its finalGatheringCamera, photon_mapping/gathering.cu:129-146,
+ * only averages the k-nearest estimate); follows pbrt's PhotonIntegrator with finalgather true, the integrator's
+ * default (pbrt-v2/src/integrators/photonmap.cpp:468-490 radiance-photon creation, :585-621 ComputeRadianceTask,
+ * :263-283 EPhoton, :156-172 RadiancePhotonProcess, :645-758 the gather itself).  SURVEY.md 8(f) rank 3. ---------- */
+/* Re-trace paths [first_path, first_path + n_paths) (same Philox streams, hence the same paths as b2rt_photons_trace)
+ * and append (a) the direct photon of each path to B2RT_MAP_DIRECT and (b) a radiance photon at every deposit
+ * (direct, indirect or caustic) that draws u < 0.125 from the path's own stream to B2RT_MAP_RADIANCE, both in path
+ * order.  n_stored[0] = direct photons, n_stored[1] = radiance photons appended (may be NULL). */
+int b2rt_photons_trace_fg(b2rt_ctx *ctx, int64_t first_path, int64_t n_paths, int32_t max_depth, int64_t n_stored[2]);
+/* EPhoton: irradiance at (p, n) from the k nearest photons of `map` within sqrt(max_dist2):
+ * sum of alpha over the photons with Dot(n, wi) > 0, divided by (nPaths * md2 * pi).  out_E[3 * nqueries]. */
+int b2rt_irradiance(b2rt_ctx *ctx, int32_t map, int64_t nqueries, const b2rt_query *queries, int32_t k, float max_dist2,
+                    float *out_E, int where);
+/* ComputeRadianceTask: Lo = (INV_PI * rho_r) * (E_direct + E_indirect + E_caustic) for every radiance photon, from the
+ * maps whose grid is built, then the hash grid over the radiance photons.  Call once after the maps are complete. */
+int b2rt_radiance_compute(b2rt_ctx *ctx, int32_t nused, float max_dist2);
+/* RadiancePhotonProcess with an unbounded search radius: the nearest radiance photon (ties: lower sorted index) whose
+ * normal satisfies Dot(rp.n, n) > 0.  out_rgb[3 * nqueries] = its Lo (0 if none), out_idx[nqueries] = its index in the
+ * SORTED radiance-photon array or -1; either may be NULL.  Only p and n of the queries are read. */
+int b2rt_radiance_lookup(b2rt_ctx *ctx, int64_t nqueries, const b2rt_query *queries, float *out_rgb, int32_t *out_idx,
+                         int where);
+/* b2rt_render_frame's indirect term from now on: enable = 0, LPhoton on the indirect map (finalgather false);
+ * enable = 1, one-bounce final gathering with gather_samples rays per shading point (pbrt finalgathersamples, default
+ * 32: half BSDF-sampled, half sampled in cones of gather_angle_deg degrees, pbrt gatherangle default 10, around the
+ * directions of the 50 nearest indirect photons, combined with the power heuristic). */
+int b2rt_final_gather_set(b2rt_ctx *ctx, int32_t enable, int32_t gather_samples, float gather_angle_deg);
 
 /* ---- camera pass: replaces the four launches of PhotonMappingRenderer::render / SimpleRenderer::render
  * (cuda_render/photon_mapping/photonmappingrenderer.cpp:31-45,108-139,228-277; simple_render/simplerender.cpp:18-103)
