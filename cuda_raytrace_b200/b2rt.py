@@ -528,3 +528,53 @@ def _sample_positions(self, xres, yres, window, spp):
 
 Context.set_sampler = _set_sampler
 Context.sample_positions = _sample_positions
+
+
+# ---- final gathering (pbrt photonmap with finalgather true) ------------------------------------------
+SYMBOLS += ["b2rt_photons_trace_fg", "b2rt_irradiance", "b2rt_radiance_compute", "b2rt_radiance_lookup",
+            "b2rt_final_gather_set"]
+MAP_CAUSTIC, MAP_INDIRECT, MAP_DIRECT, MAP_RADIANCE = 0, 1, 2, 3
+
+
+def _photons_trace_fg(self, first_path, n_paths, max_depth=5):
+    """Direct photons (map 2) and radiance photons (map 3) of paths [first_path, first_path + n_paths)."""
+    st = (C.c_int64 * 2)()
+    self.lib.b2rt_photons_trace_fg.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_void_p]
+    self._ck(self.lib.b2rt_photons_trace_fg(self.h, int(first_path), int(n_paths), int(max_depth), st))
+    return st[0], st[1]
+
+
+def _irradiance(self, which, queries, k, max_dist2):
+    """pbrt EPhoton at the queries' (p, n): (nq, 3) float32."""
+    queries = np.ascontiguousarray(queries, QUERY_DTYPE)
+    E = np.zeros((len(queries), 3), np.float32)
+    self.lib.b2rt_irradiance.argtypes = [C.c_void_p, C.c_int32, C.c_int64, C.c_void_p, C.c_int32, C.c_float, C.c_void_p, C.c_int]
+    self._ck(self.lib.b2rt_irradiance(self.h, int(which), len(queries), _ptr(queries), int(k), float(max_dist2), _ptr(E), HOST))
+    return E
+
+
+def _radiance_compute(self, nused=50, max_dist=0.1):
+    self.lib.b2rt_radiance_compute.argtypes = [C.c_void_p, C.c_int32, C.c_float]
+    self._ck(self.lib.b2rt_radiance_compute(self.h, int(nused), float(np.float32(max_dist) * np.float32(max_dist))))
+
+
+def _radiance_lookup(self, queries):
+    """Nearest radiance photon facing each query's normal: (Lo (nq, 3), index into the sorted radiance photons or -1)."""
+    queries = np.ascontiguousarray(queries, QUERY_DTYPE)
+    rgb, idx = np.zeros((len(queries), 3), np.float32), np.zeros(len(queries), np.int32)
+    self.lib.b2rt_radiance_lookup.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+    self._ck(self.lib.b2rt_radiance_lookup(self.h, len(queries), _ptr(queries), _ptr(rgb), _ptr(idx), HOST))
+    return rgb, idx
+
+
+def _set_final_gather(self, enable=True, gather_samples=32, gather_angle=10.0):
+    """pbrt `"bool finalgather"`, `"integer finalgathersamples"`, `"float gatherangle"` of the photonmap integrator."""
+    self.lib.b2rt_final_gather_set.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_float]
+    self._ck(self.lib.b2rt_final_gather_set(self.h, 1 if enable else 0, int(gather_samples), float(gather_angle)))
+
+
+Context.photons_trace_fg = _photons_trace_fg
+Context.irradiance = _irradiance
+Context.radiance_compute = _radiance_compute
+Context.radiance_lookup = _radiance_lookup
+Context.set_final_gather = _set_final_gather

@@ -495,3 +495,6 @@ void port_gather(int64_t n, const port_photon *sorted, int64_t n_paths, int64_t 
     }
     free(keys);
 }
+
+/* final gathering (finalgather true): direct / radiance photons, EPhoton, radiance-photon lookup, the gather */
+#include "oracle_fg.h"
