@@ -250,6 +250,14 @@ def _bind_photon():
     lib.port_grid_build.restype = None
     lib.port_gather.argtypes = [i64, vp, i64, i64, vp, C.c_int, f, vp, vp, vp, vp]
     lib.port_gather.restype = None
+    lib.port_photon_trace_fg.argtypes = [C.POINTER(_CScene), C.c_uint64, i64, i64, C.c_int, vp, i64, C.POINTER(i64), vp, i64,
+                                         C.POINTER(i64)]
+    lib.port_irradiance.argtypes = [i64, vp, i64, i64, vp, C.c_int, f, vp]
+    lib.port_irradiance.restype = None
+    lib.port_radiance_lookup.argtypes = [i64, vp, i64, vp, vp, vp]
+    lib.port_radiance_lookup.restype = None
+    lib.port_final_gather.argtypes = [C.POINTER(_CScene), i64, vp, i64, vp, i64, vp, C.c_int, f, C.c_uint64, vp]
+    lib.port_final_gather.restype = None
     lib.port_sincos_quarter.argtypes = [f, C.POINTER(f), C.POINTER(f)]
     lib.port_sincos_quarter.restype = None
     lib.port_philox.argtypes = [C.c_uint32] * 6 + [vp]
@@ -315,6 +323,58 @@ class PortFullScene:
         return oc[: nc.value].copy(), oi[: ni.value].copy()
 
 
+def _pft_fg(self, seed, first_path, n_paths, max_depth=5):
+    """(direct photons, radiance photons) of the path range: port_photon_trace_fg."""
+    lib = _bind_photon()
+    cs, keep = self._cscene()
+    cap = n_paths * max_depth + 1
+    od, orr = np.zeros(cap, PHOTON_DTYPE), np.zeros(cap, PHOTON_DTYPE)
+    nd, nr = C.c_int64(0), C.c_int64(0)
+    rc = lib.port_photon_trace_fg(C.byref(cs), seed, first_path, n_paths, max_depth, _p(od), cap, C.byref(nd), _p(orr), cap,
+                                  C.byref(nr))
+    assert rc == 0, rc
+    del keep
+    return od[: nd.value].copy(), orr[: nr.value].copy()
+
+
+def _pfinal_gather(self, ind_sorted, rad_sorted, queries, gather_samples, cos_angle, seed):
+    """port_final_gather: (nq, 3) indirect radiance of the queries (12 floats each, pad = ray eps, pixel id, sample word)."""
+    lib = _bind_photon()
+    cs, keep = self._cscene()
+    ind = np.ascontiguousarray(ind_sorted, PHOTON_DTYPE)
+    rad = np.ascontiguousarray(rad_sorted, PHOTON_DTYPE)
+    q = np.ascontiguousarray(queries).view(np.float32).reshape(-1, 12)
+    rgb = np.zeros((len(q), 3), np.float32)
+    lib.port_final_gather(C.byref(cs), len(ind), _p(ind), len(rad), _p(rad), len(q), _p(q), max(1, gather_samples // 2),
+                          float(cos_angle), seed, _p(rgb))
+    del keep
+    return rgb
+
+
+PortFullScene.photon_trace_fg = _pft_fg
+PortFullScene.final_gather = _pfinal_gather
+
+
+def irradiance(sorted_photons, n_paths, queries, k, max_dist2):
+    """port_irradiance (pbrt EPhoton): (nq, 3)."""
+    lib = _bind_photon()
+    sp = np.ascontiguousarray(sorted_photons, PHOTON_DTYPE)
+    q = np.ascontiguousarray(queries).view(np.float32).reshape(-1, 12)
+    E = np.zeros((len(q), 3), np.float32)
+    lib.port_irradiance(len(sp), _p(sp), n_paths, len(q), _p(q), k, max_dist2, _p(E))
+    return E
+
+
+def radiance_lookup(radiance_photons, queries):
+    """port_radiance_lookup: (Lo (nq, 3), index or -1) of the nearest photon whose normal faces the query's."""
+    lib = _bind_photon()
+    rp = np.ascontiguousarray(radiance_photons, PHOTON_DTYPE)
+    q = np.ascontiguousarray(queries).view(np.float32).reshape(-1, 12)
+    rgb, idx = np.zeros((len(q), 3), np.float32), np.zeros(len(q), np.int32)
+    lib.port_radiance_lookup(len(rp), _p(rp), len(q), _p(q), _p(rgb), _p(idx))
+    return rgb, idx
+
+
 def grid_build(photons, cell_size=0.0, target_per_cell=0.0):
     lib = _bind_photon()
     photons = np.ascontiguousarray(photons, PHOTON_DTYPE)
@@ -369,6 +429,10 @@ class RefPhotonScene:
         lib.ref_pm_shoot.argtypes = [vp, i, i, i, i, vp, i64, vp, i64, vp, vp]
         lib.ref_pm_lphoton.argtypes = [i64, vp, i, i64, vp, i, f, vp]
         lib.ref_pm_lphoton.restype = None
+        lib.ref_pm_ephoton.argtypes = [i64, vp, i, i64, vp, i, f, vp]
+        lib.ref_pm_ephoton.restype = None
+        lib.ref_pm_radiance_lookup.argtypes = [i64, vp, i64, vp, vp]
+        lib.ref_pm_radiance_lookup.restype = None
         self.lib = lib
         self.h = C.c_void_p(lib.ref_pm_create())
         self.nprims = 0
@@ -433,6 +497,28 @@ class RefPhotonScene:
         out = np.zeros((len(q), 3), np.float32)
         self.lib.ref_pm_lphoton(len(ph), _p(ph), int(n_paths), len(q), _p(q), k, max_dist2, _p(out))
         return out
+
+
+def _ref_ephoton(self, photons9, n_paths, queries, k, max_dist2):
+    """The reference's own EPhoton over its own kd-tree: (nq, 3)."""
+    ph = np.ascontiguousarray(photons9, np.float32).reshape(-1, 9)
+    q = np.ascontiguousarray(queries).view(np.float32).reshape(-1, 12)
+    out = np.zeros((len(q), 3), np.float32)
+    self.lib.ref_pm_ephoton(len(ph), _p(ph), int(n_paths), len(q), _p(q), int(k), float(max_dist2), _p(out))
+    return out
+
+
+def _ref_radiance_lookup(self, photons9, queries):
+    """The reference's own KdTree<RadiancePhoton>::Lookup + RadiancePhotonProcess; photons9 = {p, n, Lo}: Lo found (nq, 3)."""
+    ph = np.ascontiguousarray(photons9, np.float32).reshape(-1, 9)
+    q = np.ascontiguousarray(queries).view(np.float32).reshape(-1, 12)
+    out = np.zeros((len(q), 3), np.float32)
+    self.lib.ref_pm_radiance_lookup(len(ph), _p(ph), len(q), _p(q), _p(out))
+    return out
+
+
+RefPhotonScene.ephoton = _ref_ephoton
+RefPhotonScene.radiance_lookup = _ref_radiance_lookup
 
 
 def oct_decode(w):

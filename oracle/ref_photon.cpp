@@ -194,4 +194,45 @@ void ref_pm_lphoton(int64_t n, const float *photons, int n_paths, int64_t nq, co
     delete map;
 }
 
+// pbrt's irradiance estimate on caller-supplied photons: KdTree<Photon> build + Lookup + EPhoton (photonmap.cpp:263-283).
+// photons: 9 floats each {p, alpha, wi}; queries: 12 floats {p, n, -, -}
+void ref_pm_ephoton(int64_t n, const float *photons, int n_paths, int64_t nq, const float *queries, int k,
+                    float max_dist2, float *E_out) {
+    std::vector<refpm::Photon> v((size_t)n);
+    for (int64_t i = 0; i < n; ++i) {
+        const float *p = photons + 9 * i;
+        v[i] = refpm::Photon(Point(p[0], p[1], p[2]), rgb(p + 3), Vector(p[6], p[7], p[8]));
+    }
+    KdTree<refpm::Photon> *map = n ? new KdTree<refpm::Photon>(v) : NULL;
+    std::vector<refpm::ClosePhoton> buf((size_t)(k > 0 ? k : 1));
+    for (int64_t q = 0; q < nq; ++q) {
+        const float *Q = queries + 12 * q;
+        Spectrum E = refpm::EPhoton(map, n_paths, k, &buf[0], max_dist2, Point(Q[0], Q[1], Q[2]), Normal(Q[3], Q[4], Q[5]));
+        E.ToRGB(E_out + 3 * q);
+    }
+    delete map;
+}
+
+// pbrt's radiance-photon lookup: KdTree<RadiancePhoton> + RadiancePhotonProcess with md2 = INFINITY, exactly as the
+// final gather calls it (photonmap.cpp:156-172, 688-693).  photons: 9 floats each {p, n, Lo}; out: Lo of the photon found
+void ref_pm_radiance_lookup(int64_t n, const float *photons, int64_t nq, const float *queries, float *rgb_out) {
+    std::vector<refpm::RadiancePhoton> v((size_t)n);
+    for (int64_t i = 0; i < n; ++i) {
+        const float *p = photons + 9 * i;
+        v[i] = refpm::RadiancePhoton(Point(p[0], p[1], p[2]), Normal(p[3], p[4], p[5]));
+        v[i].Lo = rgb(p + 6);
+    }
+    KdTree<refpm::RadiancePhoton> *map = n ? new KdTree<refpm::RadiancePhoton>(v) : NULL;
+    for (int64_t q = 0; q < nq; ++q) {
+        const float *Q = queries + 12 * q;
+        Normal nn(Q[3], Q[4], Q[5]);
+        refpm::RadiancePhotonProcess proc(nn);
+        float md2 = INFINITY;
+        if (map) map->Lookup(Point(Q[0], Q[1], Q[2]), proc, md2);
+        Spectrum L = proc.photon ? proc.photon->Lo : Spectrum(0.f);
+        L.ToRGB(rgb_out + 3 * q);
+    }
+    delete map;
+}
+
 }  // extern "C"

@@ -1,0 +1,30 @@
+// TEST INFRASTRUCTURE ONLY.  Compiles the __host__ __device__ arithmetic of csrc/b2rt_fg.cuh (the radiance-photon shell
+// search and the MIS helpers the final-gather kernel calls) for the HOST, so the CPU test suite can run the very code the
+// GPU runs against the C oracle without a GPU.  Never loaded by the product path.
+#include "../../cuda_raytrace_b200/csrc/b2rt_fg.cuh"
+
+extern "C" {
+// grid: lo[3], cell, inv, slack, dims[3];  photons: b2rt_photon[n] in grid order;  queries: 12 floats each
+void emu_radiance_nearest(const float *lo, float cell, float inv, float slack, const int *dims, const void *photons,
+                          const uint32_t *cell_start, long long nq, const float *queries, int *idx_out, float *d2_out) {
+    FgGrid g;
+    for (int a = 0; a < 3; ++a) { g.lo[a] = lo[a]; g.dims[a] = dims[a]; }
+    g.cell = cell; g.inv = inv; g.slack = slack;
+    for (long long q = 0; q < nq; ++q) {
+        const float *Q = queries + 12 * q;
+        float d2;
+        idx_out[q] = fg_radiance_nearest(g, (const float4 *)photons, cell_start, mk3(Q[0], Q[1], Q[2]), mk3(Q[3], Q[4], Q[5]), d2);
+        if (d2_out) d2_out[q] = d2;
+    }
+}
+float emu_cone_pdf(float cos_max) { return fg_cone_pdf(cos_max); }
+float emu_power_heuristic(int nf, float f, int ng, float g) { return fg_power_heuristic(nf, f, ng, g); }
+void emu_sample_cone(float u1, float u2, float cos_max, const float *z, float *out) {
+    f3 zz = mk3(z[0], z[1], z[2]), vx, vy;
+    fg_coordinate_system(zz, vx, vy);
+    f3 w = fg_sample_cone(u1, u2, cos_max, vx, vy, zz);
+    out[0] = w.x; out[1] = w.y; out[2] = w.z;
+}
+uint32_t emu_oct_encode(const float *v) { return fg_oct_encode(mk3(v[0], v[1], v[2])); }
+void emu_oct_decode(uint32_t w, float *o) { f3 v = fg_oct_decode(w); o[0] = v.x; o[1] = v.y; o[2] = v.z; }
+}
