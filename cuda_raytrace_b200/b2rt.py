@@ -532,7 +532,7 @@ Context.sample_positions = _sample_positions
 
 # ---- final gathering (pbrt photonmap with finalgather true) ------------------------------------------
 SYMBOLS += ["b2rt_photons_trace_fg", "b2rt_irradiance", "b2rt_radiance_compute", "b2rt_radiance_lookup",
-            "b2rt_final_gather_set"]
+            "b2rt_final_gather_set", "b2rt_final_gather"]
 MAP_CAUSTIC, MAP_INDIRECT, MAP_DIRECT, MAP_RADIANCE = 0, 1, 2, 3
 
 
@@ -573,6 +573,16 @@ def _set_final_gather(self, enable=True, gather_samples=32, gather_angle=10.0):
     self._ck(self.lib.b2rt_final_gather_set(self.h, 1 if enable else 0, int(gather_samples), float(gather_angle)))
 
 
+def _final_gather(self, queries, max_dist2):
+    """The camera pass's final gather at caller-supplied shading points (pad = ray eps, pixel id bits, sample word bits)."""
+    queries = np.ascontiguousarray(queries, QUERY_DTYPE)
+    rgb = np.zeros((len(queries), 3), np.float32)
+    self.lib.b2rt_final_gather.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_float, C.c_void_p, C.c_int]
+    self._ck(self.lib.b2rt_final_gather(self.h, len(queries), _ptr(queries), float(max_dist2), _ptr(rgb), HOST))
+    return rgb
+
+
+Context.final_gather = _final_gather
 Context.photons_trace_fg = _photons_trace_fg
 Context.irradiance = _irradiance
 Context.radiance_compute = _radiance_compute

@@ -279,6 +279,32 @@ int b2rt_radiance_lookup(b2rt_ctx *ctx, int64_t nq, const b2rt_query *queries, f
     return B2RT_OK;
 }
 
+int b2rt_final_gather(b2rt_ctx *ctx, int64_t nq, const b2rt_query *queries, float max_dist2, float *out_rgb, int where) {
+    if (!ctx) return B2RT_E_ARG;
+    if (nq < 0 || (nq && (!queries || !out_rgb)) || !(max_dist2 > 0.f)) { ctx->err = "final_gather: bad arguments"; return B2RT_E_ARG; }
+    int rc = need_built(ctx, "final_gather");
+    if (rc) return rc;
+    if (!ctx->maps[B2RT_MAP_INDIRECT].grid_built || !ctx->radiance_computed || !ctx->maps[B2RT_MAP_RADIANCE].grid_built) {
+        ctx->err = "final_gather: needs the indirect map's grid and b2rt_radiance_compute"; return B2RT_E_STATE;
+    }
+    if (nq == 0) return B2RT_OK;
+    B2RT_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    const b2rt_query *dq = queries;
+    float *d_rgb = out_rgb;
+    if (where != B2RT_DEVICE) {
+        if (where != B2RT_HOST) { ctx->err = "final_gather: where must be B2RT_HOST or B2RT_DEVICE"; return B2RT_E_ARG; }
+        B2RT_CUDA(ctx, ctx->d_queries.reserve((size_t)nq * sizeof(b2rt_query)));
+        B2RT_CUDA(ctx, ctx->d_q_rgb.reserve((size_t)nq * 12));
+        B2RT_CUDA(ctx, cudaMemcpyAsync(ctx->d_queries.p, queries, (size_t)nq * sizeof(b2rt_query), cudaMemcpyHostToDevice, st));
+        dq = ctx->d_queries.as<b2rt_query>(); d_rgb = ctx->d_q_rgb.as<float>();
+    }
+    rc = b2rt_final_gather_impl(ctx, nq, dq, max_dist2, d_rgb);
+    if (rc) return rc;
+    if (where != B2RT_DEVICE) B2RT_CUDA(ctx, cudaMemcpyAsync(out_rgb, d_rgb, (size_t)nq * 12, cudaMemcpyDeviceToHost, st));
+    return status_check(ctx);
+}
+
 int b2rt_final_gather_set(b2rt_ctx *ctx, int32_t enable, int32_t gather_samples, float gather_angle_deg) {
     if (!ctx) return B2RT_E_ARG;
     if (enable && (gather_samples < 1 || gather_samples > 4096 || !(gather_angle_deg > 0.f) || !(gather_angle_deg < 90.f))) {

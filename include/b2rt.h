@@ -185,6 +185,12 @@ int b2rt_radiance_lookup(b2rt_ctx *ctx, int64_t nqueries, const b2rt_query *quer
  * directions of the 50 nearest indirect photons, combined with the power heuristic). */
 int b2rt_final_gather_set(b2rt_ctx *ctx, int32_t enable, int32_t gather_samples, float gather_angle_deg);
 
+/* parity hook: the gather of b2rt_render_frame for caller-supplied shading points.  kd = rho * path throughput; the
+ * queries' pad carries what the camera pass leaves there: pad[0] = ray epsilon of the hit, pad[1] = bits of the pixel id,
+ * pad[2] = bits of (sample number | specular-tree node << 22) -- the Philox counter words of the point's gather rays.
+ * Needs the indirect map's grid and b2rt_radiance_compute.  out_rgb[3 * nqueries]. */
+int b2rt_final_gather(b2rt_ctx *ctx, int64_t nqueries, const b2rt_query *queries, float max_dist2, float *out_rgb, int where);
+
 /* ---- camera pass: replaces the four launches of PhotonMappingRenderer::render / SimpleRenderer::render
  * (cuda_render/photon_mapping/photonmappingrenderer.cpp:31-45,108-139,228-277; simple_render/simplerender.cpp:18-103)
  * including the CPU camera-ray loop (util/camera/pbrtcamera.cpp:57-122) and the CPU film loop. ------------------- */
