@@ -329,6 +329,7 @@ int b2rt_photons_trace_fg_impl(b2rt_ctx *ctx, int64_t first_path, int64_t n_path
     if (n_stored) n_stored[0] = n_stored[1] = 0;
     if (n_paths == 0) return B2RT_OK;
     if (n_paths > (1ll << 28)) { ctx->err = "photons_trace_fg: at most 2^28 paths per call"; return B2RT_E_ARG; }
+    if (ctx->radiance_computed) { ctx->err = "photons_trace_fg: radiance already computed; clear the photon maps first"; return B2RT_E_STATE; }
     DScene sc;
     b2rt_fill_dscene(ctx, &sc);
     const int stride = max_depth + 1;
@@ -349,7 +350,6 @@ int b2rt_photons_trace_fg_impl(b2rt_ctx *ctx, int64_t first_path, int64_t n_path
     B2RT_CUDA(ctx, cudaMemcpyAsync(tot, counters + 32, 8, cudaMemcpyDeviceToHost, st));
     B2RT_CUDA(ctx, cudaStreamSynchronize(st));
     PhotonMap &md = ctx->maps[B2RT_MAP_DIRECT], &mr = ctx->maps[B2RT_MAP_RADIANCE];
-    if (ctx->radiance_computed) { ctx->err = "photons_trace_fg: radiance already computed; clear the photon maps first"; return B2RT_E_STATE; }
     rc = b2rt_photons_reserve(ctx, md.photons, md.n, md.n + tot[0]);
     if (rc) return rc;
     rc = b2rt_photons_reserve(ctx, mr.photons, mr.n, mr.n + tot[1]);
@@ -414,6 +414,7 @@ int b2rt_radiance_compute_impl(b2rt_ctx *ctx, int nused, float max_dist2) {
     }
     ctx->radiance_computed = true;
     mr.grid_built = false;
+    if (n == 0) return B2RT_OK;          // no radiance photons: the gather has nothing to look up, the indirect term is zero
     return b2rt_photon_grid_build_impl(ctx, B2RT_MAP_RADIANCE, 0.f, 0.f);
 }
 

@@ -355,9 +355,11 @@ int b2rt_render_impl(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_par
     int slots = 1;
     if (any_spec) { int d = fp->max_specular_depth < 1 ? 1 : fp->max_specular_depth; slots = 1 << (d - 1 > 5 ? 5 : d - 1); }
     const bool use_c = fp->use_caustic && ctx->maps[0].grid_built && ctx->maps[0].n > 0;
-    const bool use_i = fp->use_indirect && ctx->maps[1].grid_built && ctx->maps[1].n > 0;
+    // final gathering with no radiance photon at all: nothing to look up, the indirect term is zero
+    const bool use_i = fp->use_indirect && ctx->maps[1].grid_built && ctx->maps[1].n > 0 &&
+                       !(ctx->fg_enable && ctx->radiance_computed && !ctx->maps[B2RT_MAP_RADIANCE].grid_built);
     const bool use_fg = use_i && ctx->fg_enable;
-    if (use_fg && !(ctx->radiance_computed && ctx->maps[B2RT_MAP_RADIANCE].grid_built)) {
+    if (use_fg && !ctx->radiance_computed) {
         ctx->err = "render_frame: final gathering is on but b2rt_radiance_compute has not been called"; return B2RT_E_STATE;
     }
     b2rt_frame_params p = *fp;
