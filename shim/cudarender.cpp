@@ -369,6 +369,10 @@ PhotonMappingRenderer::PhotonMappingRenderer(const ParamSet &params) {
     maxSpecularDepth = params.FindOneInt("maxspeculardepth", 5);
     maxPhotonDepth = params.FindOneInt("maxphotondepth", 5);
     maxDist = params.FindOneFloat("maxdist", .1f);
+    finalGather = params.FindOneBool("finalgather", true);          // pbrt's default is final gathering ON (photonmap.cpp:793)
+    gatherSamples = params.FindOneInt("finalgathersamples", 32);
+    if (PbrtOptions.quickRender) gatherSamples = max(1, gatherSamples / 4);   // photonmap.cpp:795
+    gatherAngle = params.FindOneFloat("gatherangle", 10.f);
 }
 
 void PhotonMappingRenderer::render(const Scene *scene, CudaRender *cr, Camera *camera) {
@@ -380,6 +384,17 @@ void PhotonMappingRenderer::render(const Scene *scene, CudaRender *cr, Camera *c
         for (int m = 0; m < 2; ++m) cr->check(b2rt_photon_grid_build(ctx, m, 0.f, 0.f), "b2rt_photon_grid_build");
         Info("CudaRender: %lld caustic photons from %lld paths, %lld indirect photons from %lld paths",
              (long long)stored[0], (long long)paths[0], (long long)stored[1], (long long)paths[1]);
+        const bool fg = finalGather && nIndirect > 0 && stored[1] > 0;
+        if (fg) {
+            // PhotonIntegrator::Preprocess with finalGather (photonmap.cpp:468-490, 383-399): direct photons and radiance
+            // photons of the paths that filled the indirect map, then ComputeRadianceTask + the radiance-photon map
+            int64_t st[2];
+            cr->check(b2rt_photons_trace_fg(ctx, 0, paths[1], maxPhotonDepth, st), "b2rt_photons_trace_fg");
+            cr->check(b2rt_photon_grid_build(ctx, B2RT_MAP_DIRECT, 0.f, 0.f), "b2rt_photon_grid_build");
+            cr->check(b2rt_radiance_compute(ctx, nUsed, maxDist * maxDist), "b2rt_radiance_compute");
+            Info("CudaRender: final gathering, %lld direct photons, %lld radiance photons", (long long)st[0], (long long)st[1]);
+        }
+        cr->check(b2rt_final_gather_set(ctx, fg ? 1 : 0, gatherSamples, gatherAngle), "b2rt_final_gather_set");
     }
     b2rt_camera cam = probeCamera(camera);
     b2rt_frame_params fp = frameParams(cam, cr->sampler());

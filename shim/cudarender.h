@@ -79,8 +79,9 @@ public:
     explicit PhotonMappingRenderer(const ParamSet &params);
     void render(const Scene *scene, CudaRender *cudarender, Camera *camera);
 private:
-    int nCaustic, nIndirect, nUsed, maxSpecularDepth, maxPhotonDepth;
-    float maxDist;
+    int nCaustic, nIndirect, nUsed, maxSpecularDepth, maxPhotonDepth, gatherSamples;
+    float maxDist, gatherAngle;
+    bool finalGather;
 };
 
 #endif

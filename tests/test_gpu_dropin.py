@@ -47,10 +47,22 @@ def test_dropin_photon_renderer_matches_cpu_photonmap(tmp_path):
     prm = ('"integer causticphotons" [20000] "integer indirectphotons" [300000] "integer nused" [100] "float maxdist" [0.4] '
            '"integer maxphotondepth" [5] "integer maxspeculardepth" [5]')
     gpu, cpu = _run(tmp_path, "photon", 'SurfaceIntegrator "photonmap" "bool finalgather" ["false"] ' + prm,
-                    'Renderer "photonmap" ' + prm, spp=64)
+                    'Renderer "photonmap" "bool finalgather" ["false"] ' + prm, spp=64)
     m = S.image_metrics(_block(gpu, 8), _block(cpu, 8))
     assert abs(m["bias_rel"]) < 0.01, m
     assert m["mean_rel"] < 0.03, m
+
+
+@pytest.mark.skipif(not os.path.exists(BIN), reason="shim/_build/pbrt_b2rt not built (needs /root/reference)")
+def test_dropin_photon_renderer_final_gathering_default(tmp_path):
+    """pbrt's DEFAULT photonmap mode (finalgather true, 32 gather samples, 10 degree cones) on both sides: the scene file
+    says nothing about final gathering and the drop-in follows the integrator's defaults (photonmap.cpp:793-796)."""
+    prm = ('"integer causticphotons" [20000] "integer indirectphotons" [300000] "integer nused" [100] "float maxdist" [0.4] '
+           '"integer maxphotondepth" [5] "integer maxspeculardepth" [5]')
+    gpu, cpu = _run(tmp_path, "photonfg", 'SurfaceIntegrator "photonmap" ' + prm, 'Renderer "photonmap" ' + prm, spp=64, res=64)
+    m = S.image_metrics(_block(gpu, 8), _block(cpu, 8))
+    assert abs(m["bias_rel"]) < 0.03, m
+    assert m["mean_rel"] < 0.06, m
 
 
 @pytest.mark.skipif(not os.path.exists(BIN), reason="shim/_build/pbrt_b2rt not built (needs /root/reference)")
