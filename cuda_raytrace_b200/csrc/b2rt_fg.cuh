@@ -5,7 +5,7 @@
 #pragma once
 #include "b2rt_device.cuh"
 
-struct FgGrid { float lo[3]; float cell, inv, slack; int dims[3]; };
+struct FgGrid { float lo[3]; float cell, inv, slack; int dims[3]; int cdims[3]; int c2dims[3]; };
 
 __host__ __device__ __forceinline__ f3 fg_normalize(f3 v) {      // pbrt Normalize (same arithmetic as normalize3)
     float inv = 1.f / sqrtf(v.x * v.x + v.y * v.y + v.z * v.z);
@@ -44,12 +44,74 @@ __host__ __device__ __forceinline__ uint32_t fg_f2u(float f) {
 
 // Nearest radiance photon whose normal faces n (Dot(rp.n, n) > 0), unbounded radius; ties go to the lower sorted index.
 // photons: the grid-sorted b2rt_photon array viewed as float4 pairs ({p.xyz, bits(oct normal)}, {Lo.rgb, -}).
-// The search walks Chebyshev shells of cells around the query's (clamped) cell.  After shell r every unseen photon lies
-// outside the box of cells [c - r, c + r]; faces of that box at or beyond the grid's edge have nothing behind them.  The
-// walk stops once the best squared distance is below (distance to the nearest remaining face - slack)^2, so the result
-// is the exact global nearest: identical to a brute-force scan.
+//
+// Phase 0 walks Chebyshev shells of FINE cells around the query's (clamped) cell, r = 0 .. FG_FINE_SHELLS.  After shell r
+// every unseen photon lies outside the box of cells [c - r, c + r]; faces of that box at or beyond the grid's edge have
+// nothing behind them.  The walk stops once the best squared distance is below (distance to the nearest remaining face -
+// slack)^2.  Most lookups end here (a gather ray that hits a wall finds a photon of that wall next to it).
+// Phase 1 serves the rest -- hits on specular objects, on surfaces no photon reached: the nearest facing photon may be
+// tens of cells away and a fine-cell walk would spend its time in empty space (r03a: 43 s per 960 x 540 frame).  It walks
+// shells of LEVEL-2 cells (16^3 fine cells) and descends only where the occupancy tables (coarse1: photons per 4^3 fine
+// cells, coarse2: per 16^3) are non-zero and the cell's box is not farther than the best photon so far: level-2 cell ->
+// its 4^3 level-1 cells -> their 16 fine rows (one contiguous photon range each).  Same stopping rule with the level-2
+// cell size.  Both phases only ever skip photons that cannot win, so the result is the exact global nearest: identical to
+// a brute-force scan (tests/test_oracle_fg_cpu.py runs this very code on the host against one).
+#define FG_FINE_SHELLS 2
+__host__ __device__ __forceinline__ void fg_scan_range(const float4 *__restrict__ photons, uint32_t i0, uint32_t i1, f3 p, f3 n,
+                                                       int &best, float &best_d2) {
+    for (uint32_t i = i0; i < i1; ++i) {
+        const float4 A = photons[2 * (size_t)i];
+        const float dx = A.x - p.x, dy = A.y - p.y, dz = A.z - p.z;
+        const float d2 = dx * dx + dy * dy + dz * dz;
+        if (d2 < best_d2 || (d2 == best_d2 && (int)i < best)) {
+            if (dot3(fg_oct_decode(fg_f2u(A.w)), n) > 0.f) { best = (int)i; best_d2 = d2; }
+        }
+    }
+}
+// lower bound of the squared distance from p to any photon binned in fine cells [i0, i1) per axis.  Faces on the grid's
+// edge are open (edge cells also hold the photons clamped into them); the slack covers the rounding of the binning.
+__host__ __device__ __forceinline__ float fg_box_d2(const FgGrid &g, const float *pa, int x0, int x1, int y0, int y1, int z0,
+                                                    int z1) {
+    const int i0[3] = {x0, y0, z0}, i1[3] = {x1, y1, z1};
+    float d2 = 0.f;
+    for (int a = 0; a < 3; ++a) {
+        float d = 0.f;
+        if (i0[a] > 0) d = fmaxf(d, (g.lo[a] + (float)i0[a] * g.cell) - pa[a] - g.slack);
+        if (i1[a] < g.dims[a]) d = fmaxf(d, pa[a] - (g.lo[a] + (float)i1[a] * g.cell) - g.slack);
+        d2 += d * d;
+    }
+    return d2;
+}
+// one level-2 cell (X, Y, Z): descend through the occupancy tables
+__host__ __device__ inline void fg_visit_level2(const FgGrid &g, const float4 *__restrict__ photons,
+                                                const uint32_t *__restrict__ cell_start, const uint32_t *__restrict__ coarse1,
+                                                const uint32_t *__restrict__ coarse2, const float *pa, f3 p, f3 n, int X, int Y,
+                                                int Z, int &best, float &best_d2) {
+    if (coarse2[((size_t)Z * g.c2dims[1] + Y) * g.c2dims[0] + X] == 0u) return;
+    if (fg_box_d2(g, pa, 16 * X, min(16 * X + 16, g.dims[0]), 16 * Y, min(16 * Y + 16, g.dims[1]), 16 * Z,
+                  min(16 * Z + 16, g.dims[2])) > best_d2)
+        return;
+    const int zb = min(4 * Z + 4, g.cdims[2]), yb = min(4 * Y + 4, g.cdims[1]), xb = min(4 * X + 4, g.cdims[0]);
+    for (int z1 = 4 * Z; z1 < zb; ++z1)
+        for (int y1 = 4 * Y; y1 < yb; ++y1)
+            for (int x1 = 4 * X; x1 < xb; ++x1) {
+                if (coarse1[((size_t)z1 * g.cdims[1] + y1) * g.cdims[0] + x1] == 0u) continue;
+                const int fx0 = 4 * x1, fx1 = min(fx0 + 4, g.dims[0]);
+                const int fy1 = min(4 * y1 + 4, g.dims[1]), fz1 = min(4 * z1 + 4, g.dims[2]);
+                if (fg_box_d2(g, pa, fx0, fx1, 4 * y1, fy1, 4 * z1, fz1) > best_d2) continue;
+                for (int z = 4 * z1; z < fz1; ++z)
+                    for (int y = 4 * y1; y < fy1; ++y) {
+                        const size_t row = ((size_t)z * g.dims[1] + y) * g.dims[0];
+                        const uint32_t i0 = cell_start[row + fx0], i1 = cell_start[row + fx1];
+                        if (i0 == i1) continue;
+                        if (fg_box_d2(g, pa, fx0, fx1, y, y + 1, z, z + 1) > best_d2) continue;
+                        fg_scan_range(photons, i0, i1, p, n, best, best_d2);
+                    }
+            }
+}
 __host__ __device__ inline int fg_radiance_nearest(const FgGrid &g, const float4 *__restrict__ photons,
-                                                  const uint32_t *__restrict__ cell_start, f3 p, f3 n, float &best_d2) {
+                                                  const uint32_t *__restrict__ cell_start, const uint32_t *__restrict__ coarse1,
+                                                  const uint32_t *__restrict__ coarse2, f3 p, f3 n, float &best_d2) {
     const float pa[3] = {p.x, p.y, p.z};
     int c[3];
     for (int a = 0; a < 3; ++a) {
@@ -61,7 +123,8 @@ __host__ __device__ inline int fg_radiance_nearest(const FgGrid &g, const float4
     for (int a = 0; a < 3; ++a) { rmax = max(rmax, c[a]); rmax = max(rmax, g.dims[a] - 1 - c[a]); }
     int best = -1;
     best_d2 = INFINITY;
-    for (int r = 0; r <= rmax; ++r) {
+    // ---- phase 0: fine shells -----------------------------------------------------------------------------------------
+    for (int r = 0; r <= min(rmax, FG_FINE_SHELLS); ++r) {
         const int z0 = max(c[2] - r, 0), z1 = min(c[2] + r, g.dims[2] - 1);
         const int y0 = max(c[1] - r, 0), y1 = min(c[1] + r, g.dims[1] - 1);
         const int x0 = max(c[0] - r, 0), x1 = min(c[0] + r, g.dims[0] - 1);
@@ -69,22 +132,14 @@ __host__ __device__ inline int fg_radiance_nearest(const FgGrid &g, const float4
             const bool zface = (z == c[2] - r) || (z == c[2] + r);
             for (int y = y0; y <= y1; ++y) {
                 const bool full = zface || (y == c[1] - r) || (y == c[1] + r);
-                const uint32_t row = ((uint32_t)z * (uint32_t)g.dims[1] + (uint32_t)y) * (uint32_t)g.dims[0];
+                const size_t row = ((size_t)z * g.dims[1] + y) * g.dims[0];
                 // full row of the shell: cells x0..x1 are one contiguous photon range; otherwise only the two end cells
                 for (int part = 0; part < (full ? 1 : 2); ++part) {
                     int xa, xb;
                     if (full) { xa = x0; xb = x1; }
                     else if (part == 0) { xa = xb = c[0] - r; if (xa < 0) continue; }
-                    else { xa = xb = c[0] + r; if (r == 0 || xa >= g.dims[0]) continue; }
-                    const uint32_t i0 = cell_start[row + (uint32_t)xa], i1 = cell_start[row + (uint32_t)xb + 1u];
-                    for (uint32_t i = i0; i < i1; ++i) {
-                        const float4 A = photons[2 * (size_t)i];
-                        const float dx = A.x - p.x, dy = A.y - p.y, dz = A.z - p.z;
-                        const float d2 = dx * dx + dy * dy + dz * dz;
-                        if (d2 < best_d2 || (d2 == best_d2 && (int)i < best)) {
-                            if (dot3(fg_oct_decode(fg_f2u(A.w)), n) > 0.f) { best = (int)i; best_d2 = d2; }
-                        }
-                    }
+                    else { xa = xb = c[0] + r; if (xa >= g.dims[0]) continue; }
+                    fg_scan_range(photons, cell_start[row + xa], cell_start[row + xb + 1], p, n, best, best_d2);
                 }
             }
         }
@@ -93,7 +148,40 @@ __host__ __device__ inline int fg_radiance_nearest(const FgGrid &g, const float4
             if (c[a] - r > 0) bound = fminf(bound, pa[a] - (g.lo[a] + (float)(c[a] - r) * g.cell));
             if (c[a] + r + 1 < g.dims[a]) bound = fminf(bound, (g.lo[a] + (float)(c[a] + r + 1) * g.cell) - pa[a]);
         }
-        if (bound == INFINITY) break;                     // the whole grid has been scanned
+        if (bound == INFINITY) return best;               // the whole grid has been scanned
+        bound -= g.slack;
+        if (best >= 0 && bound > 0.f && best_d2 < bound * bound) return best;
+    }
+    // ---- phase 1: level-2 shells, descent through the occupancy tables ----------------------------------------------------
+    int C[3];
+    for (int a = 0; a < 3; ++a) C[a] = c[a] >> 4;
+    int Rmax = 0;
+    for (int a = 0; a < 3; ++a) { Rmax = max(Rmax, C[a]); Rmax = max(Rmax, g.c2dims[a] - 1 - C[a]); }
+    const float cell2 = 16.f * g.cell;
+    for (int R = 0; R <= Rmax; ++R) {
+        const int Z0 = max(C[2] - R, 0), Z1 = min(C[2] + R, g.c2dims[2] - 1);
+        const int Y0 = max(C[1] - R, 0), Y1 = min(C[1] + R, g.c2dims[1] - 1);
+        const int X0 = max(C[0] - R, 0), X1 = min(C[0] + R, g.c2dims[0] - 1);
+        for (int Z = Z0; Z <= Z1; ++Z) {
+            const bool zface = (Z == C[2] - R) || (Z == C[2] + R);
+            for (int Y = Y0; Y <= Y1; ++Y) {
+                if (zface || (Y == C[1] - R) || (Y == C[1] + R)) {
+                    for (int X = X0; X <= X1; ++X)
+                        fg_visit_level2(g, photons, cell_start, coarse1, coarse2, pa, p, n, X, Y, Z, best, best_d2);
+                } else {
+                    if (C[0] - R >= 0)
+                        fg_visit_level2(g, photons, cell_start, coarse1, coarse2, pa, p, n, C[0] - R, Y, Z, best, best_d2);
+                    if (C[0] + R < g.c2dims[0])
+                        fg_visit_level2(g, photons, cell_start, coarse1, coarse2, pa, p, n, C[0] + R, Y, Z, best, best_d2);
+                }
+            }
+        }
+        float bound = INFINITY;
+        for (int a = 0; a < 3; ++a) {
+            if (C[a] - R > 0) bound = fminf(bound, pa[a] - (g.lo[a] + (float)(C[a] - R) * cell2));
+            if (C[a] + R + 1 < g.c2dims[a]) bound = fminf(bound, (g.lo[a] + (float)(C[a] + R + 1) * cell2) - pa[a]);
+        }
+        if (bound == INFINITY) break;
         bound -= g.slack;
         if (best >= 0 && bound > 0.f && best_d2 < bound * bound) break;
     }

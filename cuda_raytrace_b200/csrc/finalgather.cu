@@ -157,13 +157,14 @@ radiance_lo_kernel(b2rt_photon *__restrict__ rp, const float *__restrict__ E, in
 // ---- K17 ---------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(128)
 radiance_lookup_kernel(FgGrid g, const float4 *__restrict__ photons, const uint32_t *__restrict__ cell_start,
+                       const uint32_t *__restrict__ coarse1, const uint32_t *__restrict__ coarse2,
                        const b2rt_query *__restrict__ queries, int64_t nq, float *__restrict__ out_rgb, int32_t *__restrict__ out_idx) {
     int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= nq) return;
     const float4 *Q = reinterpret_cast<const float4 *>(queries + q);
     const float4 q0 = Q[0], q1 = Q[1];
     float d2;
-    const int i = fg_radiance_nearest(g, photons, cell_start, mk3(q0.x, q0.y, q0.z), mk3(q0.w, q1.x, q1.y), d2);
+    const int i = fg_radiance_nearest(g, photons, cell_start, coarse1, coarse2, mk3(q0.x, q0.y, q0.z), mk3(q0.w, q1.x, q1.y), d2);
     if (out_idx) out_idx[q] = i;
     if (out_rgb) {
         float4 B = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -206,7 +207,7 @@ struct FgArgs {
     DScene sc;
     FgGrid g;
     const float4 *rad;                 // sorted radiance photons, float4 pairs
-    const uint32_t *rad_cells;
+    const uint32_t *rad_cells, *rad_coarse1, *rad_coarse2;   // cell ranges and the two occupancy levels (4^3, 16^3 cells)
     const b2rt_photon *ind;            // sorted indirect photons (directions for the cone sampling)
     const int32_t *idx;                // [nq * FG_NDIR] nearest indirect photons per query
     const int32_t *found;
@@ -273,7 +274,7 @@ final_gather_kernel(const FgArgs A) {
             const Surface s = make_surface(A.sc, h, p, wi);
             const f3 ng = dot3(s.n, -wi) < 0.f ? -s.n : s.n;               // Faceforward(nGather, -bounceRay.d)
             float d2;
-            const int ri = fg_radiance_nearest(A.g, A.rad, A.rad_cells, s.p, ng, d2);
+            const int ri = fg_radiance_nearest(A.g, A.rad, A.rad_cells, A.rad_coarse1, A.rad_coarse2, s.p, ng, d2);
             if (ri < 0) continue;
             const float4 Lo = __ldg(A.rad + 2 * (size_t)ri + 1);
             const float bsdf_pdf = fabsf(cosw) * B2_INV_PI;
@@ -307,8 +308,23 @@ final_gather_kernel(const FgArgs A) {
     if (overflow) atomicAdd(A.status, 1u);
 }
 
+// level-2 occupancy: photons per 16^3 fine cells = sum over 4^3 entries of the grid's coarse table
+__global__ void __launch_bounds__(256)
+fg_coarse2_kernel(const uint32_t *__restrict__ coarse1, int cx, int cy, int cz, int c2x, int c2y, int c2z,
+                  uint32_t *__restrict__ coarse2) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= c2x * c2y * c2z) return;
+    const int X = i % c2x, Y = (i / c2x) % c2y, Z = i / (c2x * c2y);
+    uint32_t cnt = 0;
+    for (int z = 4 * Z; z < min(4 * Z + 4, cz); ++z)
+        for (int y = 4 * Y; y < min(4 * Y + 4, cy); ++y)
+            for (int x = 4 * X; x < min(4 * X + 4, cx); ++x) cnt += coarse1[((size_t)z * cy + y) * cx + x];
+    coarse2[i] = cnt;
+}
+
 FgGrid fg_grid_of(const PhotonMap &m) {
     FgGrid g;
+    for (int a = 0; a < 3; ++a) { g.cdims[a] = m.cdims[a]; g.c2dims[a] = (m.cdims[a] + 3) / 4; }
     float mx = 0.f;
     for (int a = 0; a < 3; ++a) {
         g.lo[a] = m.grid.origin[a]; g.dims[a] = m.grid.dims[a];
@@ -321,6 +337,19 @@ FgGrid fg_grid_of(const PhotonMap &m) {
 }
 
 }  // namespace
+
+// the level-2 occupancy table of the radiance-photon grid (rebuilt per call: a few microseconds, and the grid may have
+// been rebuilt through b2rt_photon_grid_build since)
+static int fg_prepare_radiance(b2rt_ctx *ctx, const FgGrid &g) {
+    PhotonMap &mr = ctx->maps[B2RT_MAP_RADIANCE];
+    const int n2 = g.c2dims[0] * g.c2dims[1] * g.c2dims[2];
+    B2RT_CUDA(ctx, ctx->d_fg_coarse2.reserve((size_t)n2 * 4));
+    fg_coarse2_kernel<<<(n2 + 255) / 256, 256, 0, ctx->stream>>>(mr.coarse.as<uint32_t>(), g.cdims[0], g.cdims[1], g.cdims[2],
+                                                                 g.c2dims[0], g.c2dims[1], g.c2dims[2],
+                                                                 ctx->d_fg_coarse2.as<uint32_t>());
+    B2RT_LAUNCH_CHECK(ctx);
+    return B2RT_OK;
+}
 
 int b2rt_photons_reserve(b2rt_ctx *ctx, DevBuf &b, int64_t keep, int64_t want);
 
@@ -421,8 +450,12 @@ int b2rt_radiance_compute_impl(b2rt_ctx *ctx, int nused, float max_dist2) {
 int b2rt_radiance_lookup_impl(b2rt_ctx *ctx, int64_t nq, const b2rt_query *d_queries, float *d_rgb, int32_t *d_idx) {
     PhotonMap &mr = ctx->maps[B2RT_MAP_RADIANCE];
     if (nq <= 0) return B2RT_OK;
+    const FgGrid g = fg_grid_of(mr);
+    int rc = fg_prepare_radiance(ctx, g);
+    if (rc) return rc;
     radiance_lookup_kernel<<<(unsigned)((nq + 127) / 128), 128, 0, ctx->stream>>>(
-        fg_grid_of(mr), mr.sorted.as<float4>(), mr.cell_start.as<uint32_t>(), d_queries, nq, d_rgb, d_idx);
+        g, mr.sorted.as<float4>(), mr.cell_start.as<uint32_t>(), mr.coarse.as<uint32_t>(), ctx->d_fg_coarse2.as<uint32_t>(),
+        d_queries, nq, d_rgb, d_idx);
     B2RT_LAUNCH_CHECK(ctx);
     return B2RT_OK;
 }
@@ -473,7 +506,10 @@ int b2rt_final_gather_impl(b2rt_ctx *ctx, int64_t nq, const b2rt_query *d_querie
     FgArgs A;
     b2rt_fill_dscene(ctx, &A.sc);
     A.g = fg_grid_of(mr);
+    rc = fg_prepare_radiance(ctx, A.g);
+    if (rc) return rc;
     A.rad = mr.sorted.as<float4>(); A.rad_cells = mr.cell_start.as<uint32_t>();
+    A.rad_coarse1 = mr.coarse.as<uint32_t>(); A.rad_coarse2 = ctx->d_fg_coarse2.as<uint32_t>();
     A.ind = mi.sorted.as<b2rt_photon>(); A.idx = idx; A.found = found; A.queries = d_queries; A.nq = nq;
     A.gs = std::max(1, ctx->fg_samples / 2);
     A.cos_angle = ctx->fg_cos_angle; A.cone_pdf = fg_cone_pdf(ctx->fg_cos_angle);

@@ -5,15 +5,20 @@
 
 extern "C" {
 // grid: lo[3], cell, inv, slack, dims[3];  photons: b2rt_photon[n] in grid order;  queries: 12 floats each
+// coarse1 / coarse2: photons per 4^3 / 16^3 fine cells, dims (d + 3) / 4 and ((d + 3) / 4 + 3) / 4, row-major x fastest
 void emu_radiance_nearest(const float *lo, float cell, float inv, float slack, const int *dims, const void *photons,
-                          const uint32_t *cell_start, long long nq, const float *queries, int *idx_out, float *d2_out) {
+                          const uint32_t *cell_start, const uint32_t *coarse1, const uint32_t *coarse2, long long nq,
+                          const float *queries, int *idx_out, float *d2_out) {
     FgGrid g;
-    for (int a = 0; a < 3; ++a) { g.lo[a] = lo[a]; g.dims[a] = dims[a]; }
+    for (int a = 0; a < 3; ++a) {
+        g.lo[a] = lo[a]; g.dims[a] = dims[a]; g.cdims[a] = (dims[a] + 3) / 4; g.c2dims[a] = (g.cdims[a] + 3) / 4;
+    }
     g.cell = cell; g.inv = inv; g.slack = slack;
     for (long long q = 0; q < nq; ++q) {
         const float *Q = queries + 12 * q;
         float d2;
-        idx_out[q] = fg_radiance_nearest(g, (const float4 *)photons, cell_start, mk3(Q[0], Q[1], Q[2]), mk3(Q[3], Q[4], Q[5]), d2);
+        idx_out[q] = fg_radiance_nearest(g, (const float4 *)photons, cell_start, coarse1, coarse2, mk3(Q[0], Q[1], Q[2]),
+                                         mk3(Q[3], Q[4], Q[5]), d2);
         if (d2_out) d2_out[q] = d2;
     }
 }

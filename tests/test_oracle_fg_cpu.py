@@ -36,7 +36,7 @@ def emu():
                        check=True, capture_output=True)
     lib = C.CDLL(so)
     vp, f = C.c_void_p, C.c_float
-    lib.emu_radiance_nearest.argtypes = [vp, f, f, f, vp, vp, vp, C.c_longlong, vp, vp, vp]
+    lib.emu_radiance_nearest.argtypes = [vp, f, f, f, vp, vp, vp, vp, vp, C.c_longlong, vp, vp, vp]
     lib.emu_radiance_nearest.restype = None
     lib.emu_cone_pdf.argtypes = [f]
     lib.emu_cone_pdf.restype = f
@@ -100,6 +100,21 @@ def test_fg_pieces_match_pbrt_live(fg):
     assert np.abs(E - Er).max() <= 2e-6 * np.abs(Er).max()
 
 
+def _block_sum4(a):
+    """sum over 4 x 4 x 4 blocks of a (z, y, x) array (the grid's coarse table, csrc/photon.cu grid_coarse_kernel)"""
+    pad = [(0, (-n) % 4) for n in a.shape]
+    a = np.pad(a, pad)
+    z, y, x = a.shape
+    return a.reshape(z // 4, 4, y // 4, 4, x // 4, 4).sum((1, 3, 5))
+
+
+def _occupancy(cell_start, dims):
+    cnt = np.diff(cell_start.astype(np.int64)).reshape(int(dims[2]), int(dims[1]), int(dims[0]))
+    c1 = _block_sum4(cnt)
+    c2 = _block_sum4(c1)
+    return np.ascontiguousarray(c1, np.uint32), np.ascontiguousarray(c2, np.uint32)
+
+
 def _emu_nearest(emu, g, queries, slack=None):
     lo, dims = np.asarray(g["origin"], np.float32), np.asarray(g["dims"], np.int32)
     hi = lo + dims * np.float32(g["cell_size"])
@@ -109,8 +124,10 @@ def _emu_nearest(emu, g, queries, slack=None):
     cs = np.ascontiguousarray(g["cell_start"], np.uint32)
     q = np.ascontiguousarray(queries, np.float32)
     idx, d2 = np.zeros(len(q), np.int32), np.zeros(len(q), np.float32)
+    c1, c2 = _occupancy(cs, dims)
     emu.emu_radiance_nearest(lo.ctypes.data, g["cell_size"], g["inv_cell"], slack, dims.ctypes.data, srt.ctypes.data,
-                             cs.ctypes.data, len(q), q.ctypes.data, idx.ctypes.data, d2.ctypes.data)
+                             cs.ctypes.data, c1.ctypes.data, c2.ctypes.data, len(q), q.ctypes.data, idx.ctypes.data,
+                             d2.ctypes.data)
     return idx, d2
 
 
