@@ -148,6 +148,25 @@ def shoot_sharded(ctx, n_paths, max_depth=5, caustic=True, indirect=True, group=
 _pinned_frames = {}
 
 
+def shoot_sharded_fg(ctx, n_paths, max_depth=5, nused=50, max_dist=0.1, group=None):
+    """Final gathering's second photon pass, sharded like the first: this rank re-traces its slice of [0, n_paths) for the
+    direct and radiance photons (b2rt_photons_trace_fg), both maps are assembled on every rank (rank-order concatenation
+    == the single-GPU arrays byte for byte), then every rank builds the grids and computes the radiance photons' Lo itself
+    (replicated, deterministic: the same bytes everywhere, and no exchange of per-photon results).  Call after
+    shoot_sharded + grid_build of maps 0 and 1.  Returns the stored counts (direct, radiance)."""
+    import torch.distributed as dist
+    from . import b2rt
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    first, count = path_range(n_paths, rank, world)
+    ctx.photons_trace_fg(first, count, max_depth=max_depth)
+    nd = assemble_map(ctx, b2rt.MAP_DIRECT, n_paths, group)
+    nr = assemble_map(ctx, b2rt.MAP_RADIANCE, n_paths, group)
+    if nd:
+        ctx.grid_build(b2rt.MAP_DIRECT)
+    ctx.radiance_compute(nused, max_dist)
+    return nd, nr
+
+
 def render_sharded(ctx, cam, group=None, **kw):
     """Each rank renders its bands (interleaved stripes, `stripes=` per rank, default up to 8 with at least 64 rows per band); rank 0 returns the composited
     (yres, xres, 3) image, the others None.  With NCCL the

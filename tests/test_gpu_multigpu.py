@@ -22,3 +22,4 @@ def test_two_rank_photon_maps_and_frame_match_single_gpu():
     assert "photon maps identical to single-GPU on all ranks: True" in out
     assert "BVH bytes identical across ranks: True" in out
     assert "banded frame identical to single-GPU frame: True" in out
+    assert "final gathering: direct / radiance photons (with Lo) and banded frame identical to single-GPU: True" in out

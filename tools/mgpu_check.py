@@ -68,9 +68,37 @@ if rank == 0:
     ok_filtered = bool(np.array_equal(full_f.view(np.uint32), np.asarray(img_f).view(np.uint32)))
     print("mitchell + lowdiscrepancy banded frame: %.2f ms on rank 0" % ((t1 - t0) * 1e3), flush=True)
 ctx.set_filter(None); ctx.set_sampler("random")
+# the same identities with final gathering: sharded second photon pass (direct + radiance photons), replicated Lo, banded
+# frame with the gather on (a smaller map keeps the single-GPU comparison frame short)
+n_fg = min(n_paths, 400_000)
+M.shoot_sharded(ctx, n_fg)
+ctx.grid_build(0); ctx.grid_build(1)
+M.shoot_sharded_fg(ctx, n_fg, nused=50, max_dist=0.1)
+ctx.set_final_gather(True, 32, 10.0)
+hs = hashlib.sha256()
+for which in (2, 3):
+    hs.update(ctx.photons_download(which).tobytes())
+fg_sharded_hash = hs.hexdigest()
+img_fg = M.render_sharded(ctx, cam, **kw)
+ctx.set_final_gather(False)
+ctx.photons_clear()
+ctx.photons_trace(0, n_fg); ctx.photons_trace_fg(0, n_fg)
+for which in (0, 1, 2):
+    ctx.grid_build(which)
+ctx.radiance_compute(50, 0.1)
+hs = hashlib.sha256()
+for which in (2, 3):
+    hs.update(ctx.photons_download(which).tobytes())
+fg_single_hash = hs.hexdigest()
+ctx.set_final_gather(True, 32, 10.0)
+full_fg = ctx.render_frame(cam, **kw)
+ctx.set_final_gather(False)
+ok_fg = fg_sharded_hash == fg_single_hash
+if rank == 0:
+    ok_fg = ok_fg and bool(np.array_equal(full_fg.view(np.uint32), np.asarray(img_fg).view(np.uint32)))
 acc = hashlib.sha256(np.ascontiguousarray(ctx.accel_download()["wide_nodes"]).tobytes()).hexdigest()
 objs = [None] * world
-dist.all_gather_object(objs, (sharded_hash, single_hash, acc))
+dist.all_gather_object(objs, (sharded_hash, single_hash, acc, ok_fg))
 if rank == 0:
     same_photons = all(o[0] == o[1] == objs[0][0] for o in objs)
     same_bvh = all(o[2] == objs[0][2] for o in objs)
@@ -78,6 +106,8 @@ if rank == 0:
     print("BVH bytes identical across ranks:", same_bvh)
     print("banded frame identical to single-GPU frame:", ok_img)
     print("banded mitchell-filtered, low-discrepancy frame identical to single-GPU frame:", ok_filtered)
-    assert same_photons and same_bvh and ok_img and ok_filtered
+    same_fg = all(o[3] for o in objs)
+    print("final gathering: direct / radiance photons (with Lo) and banded frame identical to single-GPU:", same_fg)
+    assert same_photons and same_bvh and ok_img and ok_filtered and same_fg
 ctx.close()
 dist.destroy_process_group()
