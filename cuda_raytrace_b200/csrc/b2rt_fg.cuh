@@ -52,7 +52,8 @@ __host__ __device__ __forceinline__ uint32_t fg_f2u(float f) {
 // Phase 1 serves the rest -- hits on specular objects, on surfaces no photon reached: the nearest facing photon may be
 // tens of cells away and a fine-cell walk would spend its time in empty space (r03a: 43 s per 960 x 540 frame).  It walks
 // shells of LEVEL-2 cells (16^3 fine cells) and descends only where the occupancy tables (coarse1: photons per 4^3 fine
-// cells, coarse2: per 16^3) are non-zero and the cell's box is not farther than the best photon so far: level-2 cell ->
+// cells, coarse2: per 16^3) are non-zero, the cell's normal bounds (nbox1 / nbox2, below) admit a photon that faces n and
+// the cell's box is not farther than the best photon so far: level-2 cell ->
 // its 4^3 level-1 cells -> their 16 fine rows (one contiguous photon range each).  Same stopping rule with the level-2
 // cell size.  Both phases only ever skip photons that cannot win, so the result is the exact global nearest: identical to
 // a brute-force scan (tests/test_oracle_fg_cpu.py runs this very code on the host against one).
@@ -82,12 +83,55 @@ __host__ __device__ __forceinline__ float fg_box_d2(const FgGrid &g, const float
     }
     return d2;
 }
+// Normal bounds: per level-1 / level-2 cell the componentwise min and max of its photons' normals (6 floats: lo.xyz,
+// hi.xyz).  No photon of the cell can face n when sum_a max(n_a * lo_a, n_a * hi_a) <= 0: every product and the two
+// additions are the ones dot3() performs on a photon of the cell with each factor replaced by its bound, and rounded
+// multiplication and addition are monotonic, so the photon's own dot product is <= 0 too and the scan would reject it.
+// Without this a query whose neighbourhood only holds photons facing away (a gather ray that hits a mirror ball next to
+// a wall) scans every one of them without ever tightening the search (r03b: 27 s per 960 x 540 frame).
+__host__ __device__ __forceinline__ bool fg_may_face(const float *__restrict__ nb, f3 n) {
+    const float b = fmaxf(n.x * nb[0], n.x * nb[3]) + fmaxf(n.y * nb[1], n.y * nb[4]) + fmaxf(n.z * nb[2], n.z * nb[5]);
+    return b > 0.f;
+}
+__host__ __device__ inline void fg_nbox_level1(const FgGrid &g, const float4 *__restrict__ photons,
+                                               const uint32_t *__restrict__ cell_start, int X, int Y, int Z, float *out) {
+    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    const int fx0 = 4 * X, fx1 = min(fx0 + 4, g.dims[0]);
+    for (int z = 4 * Z; z < min(4 * Z + 4, g.dims[2]); ++z)
+        for (int y = 4 * Y; y < min(4 * Y + 4, g.dims[1]); ++y) {
+            const size_t row = ((size_t)z * g.dims[1] + y) * g.dims[0];
+            for (uint32_t i = cell_start[row + fx0]; i < cell_start[row + fx1]; ++i) {
+                const f3 m = fg_oct_decode(fg_f2u(photons[2 * (size_t)i].w));
+                lo[0] = fminf(lo[0], m.x); lo[1] = fminf(lo[1], m.y); lo[2] = fminf(lo[2], m.z);
+                hi[0] = fmaxf(hi[0], m.x); hi[1] = fmaxf(hi[1], m.y); hi[2] = fmaxf(hi[2], m.z);
+            }
+        }
+    for (int a = 0; a < 3; ++a) { out[a] = lo[a]; out[3 + a] = hi[a]; }
+}
+__host__ __device__ inline void fg_nbox_level2(const FgGrid &g, const float *__restrict__ nbox1,
+                                               const uint32_t *__restrict__ coarse1, int X, int Y, int Z, float *out,
+                                               uint32_t *count) {
+    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    uint32_t cnt = 0;
+    for (int z = 4 * Z; z < min(4 * Z + 4, g.cdims[2]); ++z)
+        for (int y = 4 * Y; y < min(4 * Y + 4, g.cdims[1]); ++y)
+            for (int x = 4 * X; x < min(4 * X + 4, g.cdims[0]); ++x) {
+                const size_t i = ((size_t)z * g.cdims[1] + y) * g.cdims[0] + x;
+                if (coarse1[i] == 0u) continue;
+                cnt += coarse1[i];
+                for (int a = 0; a < 3; ++a) { lo[a] = fminf(lo[a], nbox1[6 * i + a]); hi[a] = fmaxf(hi[a], nbox1[6 * i + 3 + a]); }
+            }
+    for (int a = 0; a < 3; ++a) { out[a] = lo[a]; out[3 + a] = hi[a]; }
+    *count = cnt;
+}
 // one level-2 cell (X, Y, Z): descend through the occupancy tables
 __host__ __device__ inline void fg_visit_level2(const FgGrid &g, const float4 *__restrict__ photons,
                                                 const uint32_t *__restrict__ cell_start, const uint32_t *__restrict__ coarse1,
-                                                const uint32_t *__restrict__ coarse2, const float *pa, f3 p, f3 n, int X, int Y,
+                                                const uint32_t *__restrict__ coarse2, const float *__restrict__ nbox1,
+                                                const float *__restrict__ nbox2, const float *pa, f3 p, f3 n, int X, int Y,
                                                 int Z, int &best, float &best_d2) {
-    if (coarse2[((size_t)Z * g.c2dims[1] + Y) * g.c2dims[0] + X] == 0u) return;
+    const size_t i2 = ((size_t)Z * g.c2dims[1] + Y) * g.c2dims[0] + X;
+    if (coarse2[i2] == 0u || !fg_may_face(nbox2 + 6 * i2, n)) return;
     if (fg_box_d2(g, pa, 16 * X, min(16 * X + 16, g.dims[0]), 16 * Y, min(16 * Y + 16, g.dims[1]), 16 * Z,
                   min(16 * Z + 16, g.dims[2])) > best_d2)
         return;
@@ -95,7 +139,8 @@ __host__ __device__ inline void fg_visit_level2(const FgGrid &g, const float4 *_
     for (int z1 = 4 * Z; z1 < zb; ++z1)
         for (int y1 = 4 * Y; y1 < yb; ++y1)
             for (int x1 = 4 * X; x1 < xb; ++x1) {
-                if (coarse1[((size_t)z1 * g.cdims[1] + y1) * g.cdims[0] + x1] == 0u) continue;
+                const size_t i1c = ((size_t)z1 * g.cdims[1] + y1) * g.cdims[0] + x1;
+                if (coarse1[i1c] == 0u || !fg_may_face(nbox1 + 6 * i1c, n)) continue;
                 const int fx0 = 4 * x1, fx1 = min(fx0 + 4, g.dims[0]);
                 const int fy1 = min(4 * y1 + 4, g.dims[1]), fz1 = min(4 * z1 + 4, g.dims[2]);
                 if (fg_box_d2(g, pa, fx0, fx1, 4 * y1, fy1, 4 * z1, fz1) > best_d2) continue;
@@ -111,7 +156,8 @@ __host__ __device__ inline void fg_visit_level2(const FgGrid &g, const float4 *_
 }
 __host__ __device__ inline int fg_radiance_nearest(const FgGrid &g, const float4 *__restrict__ photons,
                                                   const uint32_t *__restrict__ cell_start, const uint32_t *__restrict__ coarse1,
-                                                  const uint32_t *__restrict__ coarse2, f3 p, f3 n, float &best_d2) {
+                                                  const uint32_t *__restrict__ coarse2, const float *__restrict__ nbox1,
+                                                  const float *__restrict__ nbox2, f3 p, f3 n, float &best_d2) {
     const float pa[3] = {p.x, p.y, p.z};
     int c[3];
     for (int a = 0; a < 3; ++a) {
@@ -167,12 +213,12 @@ __host__ __device__ inline int fg_radiance_nearest(const FgGrid &g, const float4
             for (int Y = Y0; Y <= Y1; ++Y) {
                 if (zface || (Y == C[1] - R) || (Y == C[1] + R)) {
                     for (int X = X0; X <= X1; ++X)
-                        fg_visit_level2(g, photons, cell_start, coarse1, coarse2, pa, p, n, X, Y, Z, best, best_d2);
+                        fg_visit_level2(g, photons, cell_start, coarse1, coarse2, nbox1, nbox2, pa, p, n, X, Y, Z, best, best_d2);
                 } else {
                     if (C[0] - R >= 0)
-                        fg_visit_level2(g, photons, cell_start, coarse1, coarse2, pa, p, n, C[0] - R, Y, Z, best, best_d2);
+                        fg_visit_level2(g, photons, cell_start, coarse1, coarse2, nbox1, nbox2, pa, p, n, C[0] - R, Y, Z, best, best_d2);
                     if (C[0] + R < g.c2dims[0])
-                        fg_visit_level2(g, photons, cell_start, coarse1, coarse2, pa, p, n, C[0] + R, Y, Z, best, best_d2);
+                        fg_visit_level2(g, photons, cell_start, coarse1, coarse2, nbox1, nbox2, pa, p, n, C[0] + R, Y, Z, best, best_d2);
                 }
             }
         }

@@ -158,13 +158,14 @@ radiance_lo_kernel(b2rt_photon *__restrict__ rp, const float *__restrict__ E, in
 __global__ void __launch_bounds__(128)
 radiance_lookup_kernel(FgGrid g, const float4 *__restrict__ photons, const uint32_t *__restrict__ cell_start,
                        const uint32_t *__restrict__ coarse1, const uint32_t *__restrict__ coarse2,
+                       const float *__restrict__ nbox1, const float *__restrict__ nbox2,
                        const b2rt_query *__restrict__ queries, int64_t nq, float *__restrict__ out_rgb, int32_t *__restrict__ out_idx) {
     int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= nq) return;
     const float4 *Q = reinterpret_cast<const float4 *>(queries + q);
     const float4 q0 = Q[0], q1 = Q[1];
     float d2;
-    const int i = fg_radiance_nearest(g, photons, cell_start, coarse1, coarse2, mk3(q0.x, q0.y, q0.z), mk3(q0.w, q1.x, q1.y), d2);
+    const int i = fg_radiance_nearest(g, photons, cell_start, coarse1, coarse2, nbox1, nbox2, mk3(q0.x, q0.y, q0.z), mk3(q0.w, q1.x, q1.y), d2);
     if (out_idx) out_idx[q] = i;
     if (out_rgb) {
         float4 B = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -208,6 +209,7 @@ struct FgArgs {
     FgGrid g;
     const float4 *rad;                 // sorted radiance photons, float4 pairs
     const uint32_t *rad_cells, *rad_coarse1, *rad_coarse2;   // cell ranges and the two occupancy levels (4^3, 16^3 cells)
+    const float *rad_nbox1, *rad_nbox2;                      // normal bounds of the two levels
     const b2rt_photon *ind;            // sorted indirect photons (directions for the cone sampling)
     const int32_t *idx;                // [nq * FG_NDIR] nearest indirect photons per query
     const int32_t *found;
@@ -274,7 +276,7 @@ final_gather_kernel(const FgArgs A) {
             const Surface s = make_surface(A.sc, h, p, wi);
             const f3 ng = dot3(s.n, -wi) < 0.f ? -s.n : s.n;               // Faceforward(nGather, -bounceRay.d)
             float d2;
-            const int ri = fg_radiance_nearest(A.g, A.rad, A.rad_cells, A.rad_coarse1, A.rad_coarse2, s.p, ng, d2);
+            const int ri = fg_radiance_nearest(A.g, A.rad, A.rad_cells, A.rad_coarse1, A.rad_coarse2, A.rad_nbox1, A.rad_nbox2, s.p, ng, d2);
             if (ri < 0) continue;
             const float4 Lo = __ldg(A.rad + 2 * (size_t)ri + 1);
             const float bsdf_pdf = fabsf(cosw) * B2_INV_PI;
@@ -308,18 +310,22 @@ final_gather_kernel(const FgArgs A) {
     if (overflow) atomicAdd(A.status, 1u);
 }
 
-// level-2 occupancy: photons per 16^3 fine cells = sum over 4^3 entries of the grid's coarse table
-__global__ void __launch_bounds__(256)
-fg_coarse2_kernel(const uint32_t *__restrict__ coarse1, int cx, int cy, int cz, int c2x, int c2y, int c2z,
-                  uint32_t *__restrict__ coarse2) {
+// search tables of the radiance-photon grid: normal bounds per level-1 cell (4^3 fine cells), then count + normal bounds
+// per level-2 cell (16^3 fine cells); arithmetic in b2rt_fg.cuh
+__global__ void __launch_bounds__(128)
+fg_nbox1_kernel(FgGrid g, const float4 *__restrict__ photons, const uint32_t *__restrict__ cell_start, float *__restrict__ nbox1) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= c2x * c2y * c2z) return;
-    const int X = i % c2x, Y = (i / c2x) % c2y, Z = i / (c2x * c2y);
-    uint32_t cnt = 0;
-    for (int z = 4 * Z; z < min(4 * Z + 4, cz); ++z)
-        for (int y = 4 * Y; y < min(4 * Y + 4, cy); ++y)
-            for (int x = 4 * X; x < min(4 * X + 4, cx); ++x) cnt += coarse1[((size_t)z * cy + y) * cx + x];
-    coarse2[i] = cnt;
+    if (i >= g.cdims[0] * g.cdims[1] * g.cdims[2]) return;
+    fg_nbox_level1(g, photons, cell_start, i % g.cdims[0], (i / g.cdims[0]) % g.cdims[1], i / (g.cdims[0] * g.cdims[1]),
+                   nbox1 + 6 * (size_t)i);
+}
+__global__ void __launch_bounds__(128)
+fg_level2_kernel(FgGrid g, const float *__restrict__ nbox1, const uint32_t *__restrict__ coarse1, float *__restrict__ nbox2,
+                 uint32_t *__restrict__ coarse2) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= g.c2dims[0] * g.c2dims[1] * g.c2dims[2]) return;
+    fg_nbox_level2(g, nbox1, coarse1, i % g.c2dims[0], (i / g.c2dims[0]) % g.c2dims[1], i / (g.c2dims[0] * g.c2dims[1]),
+                   nbox2 + 6 * (size_t)i, coarse2 + i);
 }
 
 FgGrid fg_grid_of(const PhotonMap &m) {
@@ -338,15 +344,19 @@ FgGrid fg_grid_of(const PhotonMap &m) {
 
 }  // namespace
 
-// the level-2 occupancy table of the radiance-photon grid (rebuilt per call: a few microseconds, and the grid may have
-// been rebuilt through b2rt_photon_grid_build since)
+// the search tables of the radiance-photon grid (rebuilt per call: one pass over the radiance photons' first 16 bytes, a
+// fraction of a millisecond, and the grid may have been rebuilt through b2rt_photon_grid_build since)
 static int fg_prepare_radiance(b2rt_ctx *ctx, const FgGrid &g) {
     PhotonMap &mr = ctx->maps[B2RT_MAP_RADIANCE];
-    const int n2 = g.c2dims[0] * g.c2dims[1] * g.c2dims[2];
+    const int n1 = g.cdims[0] * g.cdims[1] * g.cdims[2], n2 = g.c2dims[0] * g.c2dims[1] * g.c2dims[2];
+    B2RT_CUDA(ctx, ctx->d_fg_nbox1.reserve((size_t)n1 * 24));
+    B2RT_CUDA(ctx, ctx->d_fg_nbox2.reserve((size_t)n2 * 24));
     B2RT_CUDA(ctx, ctx->d_fg_coarse2.reserve((size_t)n2 * 4));
-    fg_coarse2_kernel<<<(n2 + 255) / 256, 256, 0, ctx->stream>>>(mr.coarse.as<uint32_t>(), g.cdims[0], g.cdims[1], g.cdims[2],
-                                                                 g.c2dims[0], g.c2dims[1], g.c2dims[2],
-                                                                 ctx->d_fg_coarse2.as<uint32_t>());
+    fg_nbox1_kernel<<<(n1 + 127) / 128, 128, 0, ctx->stream>>>(g, mr.sorted.as<float4>(), mr.cell_start.as<uint32_t>(),
+                                                               ctx->d_fg_nbox1.as<float>());
+    B2RT_LAUNCH_CHECK(ctx);
+    fg_level2_kernel<<<(n2 + 127) / 128, 128, 0, ctx->stream>>>(g, ctx->d_fg_nbox1.as<float>(), mr.coarse.as<uint32_t>(),
+                                                                ctx->d_fg_nbox2.as<float>(), ctx->d_fg_coarse2.as<uint32_t>());
     B2RT_LAUNCH_CHECK(ctx);
     return B2RT_OK;
 }
@@ -455,7 +465,7 @@ int b2rt_radiance_lookup_impl(b2rt_ctx *ctx, int64_t nq, const b2rt_query *d_que
     if (rc) return rc;
     radiance_lookup_kernel<<<(unsigned)((nq + 127) / 128), 128, 0, ctx->stream>>>(
         g, mr.sorted.as<float4>(), mr.cell_start.as<uint32_t>(), mr.coarse.as<uint32_t>(), ctx->d_fg_coarse2.as<uint32_t>(),
-        d_queries, nq, d_rgb, d_idx);
+        ctx->d_fg_nbox1.as<float>(), ctx->d_fg_nbox2.as<float>(), d_queries, nq, d_rgb, d_idx);
     B2RT_LAUNCH_CHECK(ctx);
     return B2RT_OK;
 }
@@ -510,6 +520,7 @@ int b2rt_final_gather_impl(b2rt_ctx *ctx, int64_t nq, const b2rt_query *d_querie
     if (rc) return rc;
     A.rad = mr.sorted.as<float4>(); A.rad_cells = mr.cell_start.as<uint32_t>();
     A.rad_coarse1 = mr.coarse.as<uint32_t>(); A.rad_coarse2 = ctx->d_fg_coarse2.as<uint32_t>();
+    A.rad_nbox1 = ctx->d_fg_nbox1.as<float>(); A.rad_nbox2 = ctx->d_fg_nbox2.as<float>();
     A.ind = mi.sorted.as<b2rt_photon>(); A.idx = idx; A.found = found; A.queries = d_queries; A.nq = nq;
     A.gs = std::max(1, ctx->fg_samples / 2);
     A.cos_angle = ctx->fg_cos_angle; A.cone_pdf = fg_cone_pdf(ctx->fg_cos_angle);

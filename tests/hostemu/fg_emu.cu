@@ -5,22 +5,33 @@
 
 extern "C" {
 // grid: lo[3], cell, inv, slack, dims[3];  photons: b2rt_photon[n] in grid order;  queries: 12 floats each
-// coarse1 / coarse2: photons per 4^3 / 16^3 fine cells, dims (d + 3) / 4 and ((d + 3) / 4 + 3) / 4, row-major x fastest
+// coarse1: photons per 4^3 fine cells (the grid's own coarse table), dims (d + 3) / 4, row-major x fastest.  The level-2
+// counts and both levels' normal bounds are built here with the functions the device kernels call.
 void emu_radiance_nearest(const float *lo, float cell, float inv, float slack, const int *dims, const void *photons,
-                          const uint32_t *cell_start, const uint32_t *coarse1, const uint32_t *coarse2, long long nq,
-                          const float *queries, int *idx_out, float *d2_out) {
+                          const uint32_t *cell_start, const uint32_t *coarse1, long long nq, const float *queries,
+                          int *idx_out, float *d2_out) {
     FgGrid g;
     for (int a = 0; a < 3; ++a) {
         g.lo[a] = lo[a]; g.dims[a] = dims[a]; g.cdims[a] = (dims[a] + 3) / 4; g.c2dims[a] = (g.cdims[a] + 3) / 4;
     }
     g.cell = cell; g.inv = inv; g.slack = slack;
+    const int n1 = g.cdims[0] * g.cdims[1] * g.cdims[2], n2 = g.c2dims[0] * g.c2dims[1] * g.c2dims[2];
+    float *nbox1 = new float[6 * (size_t)n1], *nbox2 = new float[6 * (size_t)n2];
+    uint32_t *coarse2 = new uint32_t[n2];
+    for (int i = 0; i < n1; ++i)
+        fg_nbox_level1(g, (const float4 *)photons, cell_start, i % g.cdims[0], (i / g.cdims[0]) % g.cdims[1],
+                       i / (g.cdims[0] * g.cdims[1]), nbox1 + 6 * (size_t)i);
+    for (int i = 0; i < n2; ++i)
+        fg_nbox_level2(g, nbox1, coarse1, i % g.c2dims[0], (i / g.c2dims[0]) % g.c2dims[1], i / (g.c2dims[0] * g.c2dims[1]),
+                       nbox2 + 6 * (size_t)i, coarse2 + i);
     for (long long q = 0; q < nq; ++q) {
         const float *Q = queries + 12 * q;
         float d2;
-        idx_out[q] = fg_radiance_nearest(g, (const float4 *)photons, cell_start, coarse1, coarse2, mk3(Q[0], Q[1], Q[2]),
-                                         mk3(Q[3], Q[4], Q[5]), d2);
+        idx_out[q] = fg_radiance_nearest(g, (const float4 *)photons, cell_start, coarse1, coarse2, nbox1, nbox2,
+                                         mk3(Q[0], Q[1], Q[2]), mk3(Q[3], Q[4], Q[5]), d2);
         if (d2_out) d2_out[q] = d2;
     }
+    delete[] nbox1; delete[] nbox2; delete[] coarse2;
 }
 float emu_cone_pdf(float cos_max) { return fg_cone_pdf(cos_max); }
 float emu_power_heuristic(int nf, float f, int ng, float g) { return fg_power_heuristic(nf, f, ng, g); }

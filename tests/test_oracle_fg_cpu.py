@@ -36,7 +36,7 @@ def emu():
                        check=True, capture_output=True)
     lib = C.CDLL(so)
     vp, f = C.c_void_p, C.c_float
-    lib.emu_radiance_nearest.argtypes = [vp, f, f, f, vp, vp, vp, vp, vp, C.c_longlong, vp, vp, vp]
+    lib.emu_radiance_nearest.argtypes = [vp, f, f, f, vp, vp, vp, vp, C.c_longlong, vp, vp, vp]
     lib.emu_radiance_nearest.restype = None
     lib.emu_cone_pdf.argtypes = [f]
     lib.emu_cone_pdf.restype = f
@@ -124,10 +124,9 @@ def _emu_nearest(emu, g, queries, slack=None):
     cs = np.ascontiguousarray(g["cell_start"], np.uint32)
     q = np.ascontiguousarray(queries, np.float32)
     idx, d2 = np.zeros(len(q), np.int32), np.zeros(len(q), np.float32)
-    c1, c2 = _occupancy(cs, dims)
+    c1, _ = _occupancy(cs, dims)
     emu.emu_radiance_nearest(lo.ctypes.data, g["cell_size"], g["inv_cell"], slack, dims.ctypes.data, srt.ctypes.data,
-                             cs.ctypes.data, c1.ctypes.data, c2.ctypes.data, len(q), q.ctypes.data, idx.ctypes.data,
-                             d2.ctypes.data)
+                             cs.ctypes.data, c1.ctypes.data, len(q), q.ctypes.data, idx.ctypes.data, d2.ctypes.data)
     return idx, d2
 
 
