@@ -1,6 +1,13 @@
 // TEST INFRASTRUCTURE ONLY.  Compiles the __host__ __device__ arithmetic of csrc/b2rt_fg.cuh (the radiance-photon shell
 // search and the MIS helpers the final-gather kernel calls) for the HOST, so the CPU test suite can run the very code the
 // GPU runs against the C oracle without a GPU.  Never loaded by the product path.
+// work counters of the lookup: [0] photons distance-tested, [1] level-2 cells looked at, [2] level-1 cells looked at
+static unsigned long long g_fg_stat[4];
+#ifdef __CUDA_ARCH__
+#define FG_STAT(counter, amount)
+#else
+#define FG_STAT(counter, amount) (g_fg_stat[counter] += (unsigned long long)(amount))
+#endif
 #include "../../cuda_raytrace_b200/csrc/b2rt_fg.cuh"
 
 extern "C" {
@@ -32,6 +39,9 @@ void emu_radiance_nearest(const float *lo, float cell, float inv, float slack, c
         if (d2_out) d2_out[q] = d2;
     }
     delete[] nbox1; delete[] nbox2; delete[] coarse2;
+}
+void emu_stat(unsigned long long *out, int reset) {
+    for (int i = 0; i < 4; ++i) { out[i] = g_fg_stat[i]; if (reset) g_fg_stat[i] = 0; }
 }
 float emu_cone_pdf(float cos_max) { return fg_cone_pdf(cos_max); }
 float emu_power_heuristic(int nf, float f, int ng, float g) { return fg_power_heuristic(nf, f, ng, g); }
