@@ -128,22 +128,38 @@ __host__ __device__ inline void fg_nbox_level2(const FgGrid &g, const float *__r
     for (int a = 0; a < 3; ++a) { out[a] = lo[a]; out[3 + a] = hi[a]; }
     *count = cnt;
 }
-// one level-2 cell (X, Y, Z): descend through the occupancy tables
+// min over the warp by (d2, index): every lane ends with the winner.  NL = 1 (one thread owns the lookup): nothing to do.
+template <int NL>
+__host__ __device__ __forceinline__ void fg_lanes_min(int &best, float &best_d2) {
+#ifdef __CUDA_ARCH__
+    if (NL > 1) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float od2 = __shfl_xor_sync(0xffffffffu, best_d2, o);
+            const int ob = __shfl_xor_sync(0xffffffffu, best, o);
+            if (ob >= 0 && (od2 < best_d2 || (od2 == best_d2 && (best < 0 || ob < best)))) { best_d2 = od2; best = ob; }
+        }
+    }
+#endif
+}
+// one level-2 cell (X, Y, Z): descend through the occupancy tables.  NL lanes share the cell: lane l takes the level-1
+// children l, l + NL, ... with a private best and the lanes agree on the minimum before they leave (all decisions up to
+// the children loop depend only on values every lane holds, so a warp stays converged around the shuffles).
+template <int NL>
 __host__ __device__ inline void fg_visit_level2(const FgGrid &g, const float4 *__restrict__ photons,
                                                 const uint32_t *__restrict__ cell_start, const uint32_t *__restrict__ coarse1,
                                                 const uint32_t *__restrict__ coarse2, const float *__restrict__ nbox1,
                                                 const float *__restrict__ nbox2, const float *pa, f3 p, f3 n, int X, int Y,
-                                                int Z, bool sample, int &best, float &best_d2) {
+                                                int Z, bool sample, int lane, int &best, float &best_d2) {
     const size_t i2 = ((size_t)Z * g.c2dims[1] + Y) * g.c2dims[0] + X;
     FG_STAT(1, 1);
     if (coarse2[i2] == 0u || !fg_may_face(nbox2 + 6 * i2, n)) return;
     if (fg_box_d2(g, pa, 16 * X, min(16 * X + 16, g.dims[0]), 16 * Y, min(16 * Y + 16, g.dims[1]), 16 * Z,
                   min(16 * Z + 16, g.dims[2])) > best_d2)
         return;
-    const int zb = min(4 * Z + 4, g.cdims[2]), yb = min(4 * Y + 4, g.cdims[1]), xb = min(4 * X + 4, g.cdims[0]);
-    for (int z1 = 4 * Z; z1 < zb; ++z1)
-        for (int y1 = 4 * Y; y1 < yb; ++y1)
-            for (int x1 = 4 * X; x1 < xb; ++x1) {
+    for (int k = lane; k < 64; k += NL) {
+                const int x1 = 4 * X + (k & 3), y1 = 4 * Y + ((k >> 2) & 3), z1 = 4 * Z + (k >> 4);
+                if (x1 >= g.cdims[0] || y1 >= g.cdims[1] || z1 >= g.cdims[2]) continue;
                 const size_t i1c = ((size_t)z1 * g.cdims[1] + y1) * g.cdims[0] + x1;
                 FG_STAT(2, 1);
                 if (coarse1[i1c] == 0u || !fg_may_face(nbox1 + 6 * i1c, n)) continue;
@@ -158,12 +174,12 @@ __host__ __device__ inline void fg_visit_level2(const FgGrid &g, const float4 *_
                         if (fg_box_d2(g, pa, fx0, fx1, y, y + 1, z, z + 1) > best_d2) continue;
                         fg_scan_range(photons, i0, sample ? i0 + 1u : i1, p, n, best, best_d2);
                     }
-            }
+    }
+    fg_lanes_min<NL>(best, best_d2);
 }
-__host__ __device__ inline int fg_radiance_nearest(const FgGrid &g, const float4 *__restrict__ photons,
-                                                  const uint32_t *__restrict__ cell_start, const uint32_t *__restrict__ coarse1,
-                                                  const uint32_t *__restrict__ coarse2, const float *__restrict__ nbox1,
-                                                  const float *__restrict__ nbox2, f3 p, f3 n, float &best_d2) {
+// phase 0; returns true when the lookup is finished (best / best_d2 final), false when phase 1 has to continue from them
+__host__ __device__ inline bool fg_radiance_phase0(const FgGrid &g, const float4 *__restrict__ photons,
+                                                   const uint32_t *__restrict__ cell_start, f3 p, f3 n, int &best, float &best_d2) {
     const float pa[3] = {p.x, p.y, p.z};
     int c[3];
     for (int a = 0; a < 3; ++a) {
@@ -173,7 +189,7 @@ __host__ __device__ inline int fg_radiance_nearest(const FgGrid &g, const float4
     }
     int rmax = 0;
     for (int a = 0; a < 3; ++a) { rmax = max(rmax, c[a]); rmax = max(rmax, g.dims[a] - 1 - c[a]); }
-    int best = -1;
+    best = -1;
     best_d2 = INFINITY;
     // ---- phase 0: fine shells -----------------------------------------------------------------------------------------
     for (int r = 0; r <= min(rmax, FG_FINE_SHELLS); ++r) {
@@ -200,13 +216,26 @@ __host__ __device__ inline int fg_radiance_nearest(const FgGrid &g, const float4
             if (c[a] - r > 0) bound = fminf(bound, pa[a] - (g.lo[a] + (float)(c[a] - r) * g.cell));
             if (c[a] + r + 1 < g.dims[a]) bound = fminf(bound, (g.lo[a] + (float)(c[a] + r + 1) * g.cell) - pa[a]);
         }
-        if (bound == INFINITY) return best;               // the whole grid has been scanned
+        if (bound == INFINITY) return true;               // the whole grid has been scanned
         bound -= g.slack;
-        if (best >= 0 && bound > 0.f && best_d2 < bound * bound) return best;
+        if (best >= 0 && bound > 0.f && best_d2 < bound * bound) return true;
     }
-    // ---- phase 1: level-2 shells, descent through the occupancy tables ----------------------------------------------------
+    return false;
+}
+// ---- phase 1: level-2 shells, descent through the occupancy tables; NL lanes work on ONE lookup (same p, n, best on all) ---
+template <int NL>
+__host__ __device__ inline void fg_radiance_phase1(const FgGrid &g, const float4 *__restrict__ photons,
+                                                   const uint32_t *__restrict__ cell_start, const uint32_t *__restrict__ coarse1,
+                                                   const uint32_t *__restrict__ coarse2, const float *__restrict__ nbox1,
+                                                   const float *__restrict__ nbox2, f3 p, f3 n, int lane, int &best,
+                                                   float &best_d2) {
+    const float pa[3] = {p.x, p.y, p.z};
     int C[3];
-    for (int a = 0; a < 3; ++a) C[a] = c[a] >> 4;
+    for (int a = 0; a < 3; ++a) {
+        float f = floorf((pa[a] - g.lo[a]) * g.inv);
+        f = fminf(fmaxf(f, 0.f), (float)(g.dims[a] - 1));
+        C[a] = (int)f >> 4;
+    }
     int Rmax = 0;
     for (int a = 0; a < 3; ++a) { Rmax = max(Rmax, C[a]); Rmax = max(Rmax, g.c2dims[a] - 1 - C[a]); }
     const float cell2 = 16.f * g.cell;
@@ -225,12 +254,12 @@ __host__ __device__ inline int fg_radiance_nearest(const FgGrid &g, const float4
             for (int Y = Y0; Y <= Y1; ++Y) {
                 if (zface || (Y == C[1] - R) || (Y == C[1] + R)) {
                     for (int X = X0; X <= X1; ++X)
-                        fg_visit_level2(g, photons, cell_start, coarse1, coarse2, nbox1, nbox2, pa, p, n, X, Y, Z, sample, best, best_d2);
+                        fg_visit_level2<NL>(g, photons, cell_start, coarse1, coarse2, nbox1, nbox2, pa, p, n, X, Y, Z, sample, lane, best, best_d2);
                 } else {
                     if (C[0] - R >= 0)
-                        fg_visit_level2(g, photons, cell_start, coarse1, coarse2, nbox1, nbox2, pa, p, n, C[0] - R, Y, Z, sample, best, best_d2);
+                        fg_visit_level2<NL>(g, photons, cell_start, coarse1, coarse2, nbox1, nbox2, pa, p, n, C[0] - R, Y, Z, sample, lane, best, best_d2);
                     if (C[0] + R < g.c2dims[0])
-                        fg_visit_level2(g, photons, cell_start, coarse1, coarse2, nbox1, nbox2, pa, p, n, C[0] + R, Y, Z, sample, best, best_d2);
+                        fg_visit_level2<NL>(g, photons, cell_start, coarse1, coarse2, nbox1, nbox2, pa, p, n, C[0] + R, Y, Z, sample, lane, best, best_d2);
                 }
             }
         }
@@ -244,6 +273,15 @@ __host__ __device__ inline int fg_radiance_nearest(const FgGrid &g, const float4
         if (best >= 0 && bound > 0.f && best_d2 < bound * bound) break;
     }
     }
+}
+// the whole lookup by one thread
+__host__ __device__ inline int fg_radiance_nearest(const FgGrid &g, const float4 *__restrict__ photons,
+                                                  const uint32_t *__restrict__ cell_start, const uint32_t *__restrict__ coarse1,
+                                                  const uint32_t *__restrict__ coarse2, const float *__restrict__ nbox1,
+                                                  const float *__restrict__ nbox2, f3 p, f3 n, float &best_d2) {
+    int best;
+    if (!fg_radiance_phase0(g, photons, cell_start, p, n, best, best_d2))
+        fg_radiance_phase1<1>(g, photons, cell_start, coarse1, coarse2, nbox1, nbox2, p, n, 0, best, best_d2);
     return best;
 }
 

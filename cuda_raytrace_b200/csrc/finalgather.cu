@@ -216,6 +216,7 @@ struct FgArgs {
     const b2rt_query *queries;
     int64_t nq;
     int gs;                            // gather rays per strategy (pbrt: gatherSamples / 2)
+    int coop;                          // far lookups: 0 = per lane, 1 = warp-cooperative
     float cos_angle, cone_pdf;
     uint32_t k0, k1;
     float *out_rgb;
@@ -246,50 +247,84 @@ final_gather_kernel(const FgArgs A) {
         const f3 fr = kd * B2_INV_PI;                                    // Lambertian f, throughput folded into kd
         f3 accB = mk3(0.f, 0.f, 0.f), accC = mk3(0.f, 0.f, 0.f);
         for (int base = 0; base < 2 * A.gs; base += 32) {
+            // no early exits in this body: with A.coop the lanes meet at the ballot below
             const int r = base + lane;
-            if (r >= 2 * A.gs) continue;
+            bool act = r < 2 * A.gs;
             const bool cone = r >= A.gs;
-            const u4 u = philox4x32_10(gpix, kc, 0x200u + (uint32_t)r, 0u, A.k0, A.k1);
-            f3 wi;
-            float cosw;
-            if (!cone) {
-                // Lambertian::Sample_f: cosine hemisphere on wo's side (= nf's side), pdf = |cos| / pi
-                const f3 l = cosine_sample_hemisphere(u01(u.x), u01(u.y));
-                wi = mk3(sn.x * l.x + tn.x * l.y + nf.x * l.z, sn.y * l.x + tn.y * l.y + nf.y * l.z,
-                         sn.z * l.x + tn.z * l.y + nf.z * l.z);
-                cosw = dot3(wi, nf);
-                if (!(l.z > 0.f) || !(cosw > 0.f)) continue;
-            } else {
-                if (nd == 0) continue;
-                const int pn = min(nd - 1, (int)floorf(u01(u.z) * (float)nd));
-                const f3 z = s_dirs[warp][pn];
-                f3 vx, vy;
-                fg_coordinate_system(z, vx, vy);
-                wi = fg_sample_cone(u01(u.x), u01(u.y), A.cos_angle, vx, vy, z);
-                cosw = dot3(wi, nf);
-                if (!(cosw > 0.f)) continue;                                // bsdf->f(wo, wi) is black
+            f3 wi = mk3(0.f, 0.f, 1.f);
+            float cosw = 0.f;
+            if (act) {
+                const u4 u = philox4x32_10(gpix, kc, 0x200u + (uint32_t)r, 0u, A.k0, A.k1);
+                if (!cone) {
+                    // Lambertian::Sample_f: cosine hemisphere on wo's side (= nf's side), pdf = |cos| / pi
+                    const f3 l = cosine_sample_hemisphere(u01(u.x), u01(u.y));
+                    wi = mk3(sn.x * l.x + tn.x * l.y + nf.x * l.z, sn.y * l.x + tn.y * l.y + nf.y * l.z,
+                             sn.z * l.x + tn.z * l.y + nf.z * l.z);
+                    cosw = dot3(wi, nf);
+                    act = (l.z > 0.f) && (cosw > 0.f);
+                } else if (nd == 0) {
+                    act = false;
+                } else {
+                    const int pn = min(nd - 1, (int)floorf(u01(u.z) * (float)nd));
+                    const f3 z = s_dirs[warp][pn];
+                    f3 vx, vy;
+                    fg_coordinate_system(z, vx, vy);
+                    wi = fg_sample_cone(u01(u.x), u01(u.y), A.cos_angle, vx, vy, z);
+                    cosw = dot3(wi, nf);
+                    act = cosw > 0.f;                                        // else bsdf->f(wo, wi) is black
+                }
             }
-            HitD h;
-            if (!traverse<false>(A.sc.nodes, A.sc.recs, A.sc.analytic, p.x, p.y, p.z, wi.x, wi.y, wi.z, ray_eps, INFINITY, h,
-                                 overflow))
-                continue;
-            const Surface s = make_surface(A.sc, h, p, wi);
-            const f3 ng = dot3(s.n, -wi) < 0.f ? -s.n : s.n;               // Faceforward(nGather, -bounceRay.d)
-            float d2;
-            const int ri = fg_radiance_nearest(A.g, A.rad, A.rad_cells, A.rad_coarse1, A.rad_coarse2, A.rad_nbox1, A.rad_nbox2, s.p, ng, d2);
-            if (ri < 0) continue;
-            const float4 Lo = __ldg(A.rad + 2 * (size_t)ri + 1);
-            const float bsdf_pdf = fabsf(cosw) * B2_INV_PI;
-            const float photon_pdf = fg_photon_pdf(s_dirs[warp], nd, wi, A.cos_angle, A.cone_pdf);
-            const float absdot = fabsf(cosw);
-            if (!cone) {
-                const float wt = fg_power_heuristic(A.gs, bsdf_pdf, A.gs, photon_pdf);
-                const float w = absdot * wt / bsdf_pdf;
-                accB = accB + mk3(fr.x * Lo.x * w, fr.y * Lo.y * w, fr.z * Lo.z * w);
-            } else {
-                const float wt = fg_power_heuristic(A.gs, photon_pdf, A.gs, bsdf_pdf);
-                accC = accC + mk3(fr.x * Lo.x * absdot * wt / photon_pdf, fr.y * Lo.y * absdot * wt / photon_pdf,
-                                  fr.z * Lo.z * absdot * wt / photon_pdf);
+            f3 hp = mk3(0.f, 0.f, 0.f), ng = mk3(0.f, 0.f, 1.f);
+            bool hit = false;
+            if (act) {
+                HitD h;
+                hit = traverse<false>(A.sc.nodes, A.sc.recs, A.sc.analytic, p.x, p.y, p.z, wi.x, wi.y, wi.z, ray_eps, INFINITY, h,
+                                      overflow);
+                if (hit) {
+                    const Surface s = make_surface(A.sc, h, p, wi);
+                    hp = s.p;
+                    ng = dot3(s.n, -wi) < 0.f ? -s.n : s.n;                 // Faceforward(nGather, -bounceRay.d)
+                }
+            }
+            // nearest radiance photon facing the hit: the near search per lane, the far search (hits on specular objects,
+            // on surfaces no photon reached) per lane or by the whole warp, one pending lookup after the other
+            int ri = -1;
+            float d2 = INFINITY;
+            bool far = false;
+            if (hit) far = !fg_radiance_phase0(A.g, A.rad, A.rad_cells, hp, ng, ri, d2);
+            if (A.coop) {
+                unsigned pend = __ballot_sync(0xffffffffu, far);
+                while (pend) {
+                    const int src = __ffs(pend) - 1;
+                    pend &= pend - 1u;
+                    const f3 qp = mk3(__shfl_sync(0xffffffffu, hp.x, src), __shfl_sync(0xffffffffu, hp.y, src),
+                                      __shfl_sync(0xffffffffu, hp.z, src));
+                    const f3 qn = mk3(__shfl_sync(0xffffffffu, ng.x, src), __shfl_sync(0xffffffffu, ng.y, src),
+                                      __shfl_sync(0xffffffffu, ng.z, src));
+                    int b = __shfl_sync(0xffffffffu, ri, src);
+                    float bd2 = __shfl_sync(0xffffffffu, d2, src);
+                    fg_radiance_phase1<32>(A.g, A.rad, A.rad_cells, A.rad_coarse1, A.rad_coarse2, A.rad_nbox1, A.rad_nbox2, qp, qn,
+                                           lane, b, bd2);
+                    if (lane == src) { ri = b; d2 = bd2; }
+                }
+            } else if (far) {
+                fg_radiance_phase1<1>(A.g, A.rad, A.rad_cells, A.rad_coarse1, A.rad_coarse2, A.rad_nbox1, A.rad_nbox2, hp, ng, 0, ri,
+                                      d2);
+            }
+            if (hit && ri >= 0) {
+                const float4 Lo = __ldg(A.rad + 2 * (size_t)ri + 1);
+                const float bsdf_pdf = fabsf(cosw) * B2_INV_PI;
+                const float photon_pdf = fg_photon_pdf(s_dirs[warp], nd, wi, A.cos_angle, A.cone_pdf);
+                const float absdot = fabsf(cosw);
+                if (!cone) {
+                    const float wt = fg_power_heuristic(A.gs, bsdf_pdf, A.gs, photon_pdf);
+                    const float w = absdot * wt / bsdf_pdf;
+                    accB = accB + mk3(fr.x * Lo.x * w, fr.y * Lo.y * w, fr.z * Lo.z * w);
+                } else {
+                    const float wt = fg_power_heuristic(A.gs, photon_pdf, A.gs, bsdf_pdf);
+                    accC = accC + mk3(fr.x * Lo.x * absdot * wt / photon_pdf, fr.y * Lo.y * absdot * wt / photon_pdf,
+                                      fr.z * Lo.z * absdot * wt / photon_pdf);
+                }
             }
         }
         __syncwarp();
@@ -523,6 +558,7 @@ int b2rt_final_gather_impl(b2rt_ctx *ctx, int64_t nq, const b2rt_query *d_querie
     A.rad_nbox1 = ctx->d_fg_nbox1.as<float>(); A.rad_nbox2 = ctx->d_fg_nbox2.as<float>();
     A.ind = mi.sorted.as<b2rt_photon>(); A.idx = idx; A.found = found; A.queries = d_queries; A.nq = nq;
     A.gs = std::max(1, ctx->fg_samples / 2);
+    A.coop = ctx->fg_variant == 1 ? 1 : 0;
     A.cos_angle = ctx->fg_cos_angle; A.cone_pdf = fg_cone_pdf(ctx->fg_cos_angle);
     A.k0 = (uint32_t)ctx->seed ^ 0x46475448u; A.k1 = (uint32_t)(ctx->seed >> 32);      // 'FGTH' stream
     A.out_rgb = d_rgb; A.status = counters + 8;

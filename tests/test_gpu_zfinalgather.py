@@ -154,6 +154,33 @@ def test_final_gather_matches_oracle(fctx, oracle_maps, computed, gs):
     assert err.max() <= 1e-5, (err.max(), float((_raw(got) == _raw(ref)).mean()))
 
 
+def test_final_gather_warp_cooperative_lookup_is_bit_identical(fctx, computed, monkeypatch):
+    """B2RT_FG_VARIANT=1: the far radiance-photon lookups of a warp's gather rays are worked through by all 32 lanes
+    together.  The lookup is exact either way, so the gather's output must not change by a bit."""
+    q = np.concatenate([_gather_queries(96, seed=31), _gather_queries(160, seed=32)])
+    # shading points whose gather rays mostly end on the glass / mirror spheres (far lookups): on the floor between them
+    q[96:, 0] = np.linspace(-0.8, 0.8, 160, dtype=np.float32)
+    q[96:, 1] = 0
+    q[96:, 2] = np.linspace(-0.6, 0.6, 160, dtype=np.float32)
+    q[96:, 3:6] = (0, 1, 0)
+    fctx.set_final_gather(True, 32, 10.0)
+    ref = fctx.final_gather(q.view(b2rt.QUERY_DTYPE).reshape(-1), float(MAXD2))
+    fctx.set_final_gather(False)
+    monkeypatch.setenv("B2RT_FG_VARIANT", "1")
+    with b2rt.Context(0, seed=G.SEED) as c:
+        S.fill_scene(c, S.cornell_scene())
+        c.build_accel()
+        c.photons_trace(0, F.FG_PATHS)
+        c.photons_trace_fg(0, F.FG_PATHS)
+        for m in (0, 1, 2):
+            c.grid_build(m)
+        c.radiance_compute(NUSED, 0.3)
+        c.set_final_gather(True, 32, 10.0)
+        got = c.final_gather(q.view(b2rt.QUERY_DTYPE).reshape(-1), float(MAXD2))
+        assert np.array_equal(_raw(c.photons_download(3)), _raw(computed))
+    assert np.abs(ref).max() > 0 and np.array_equal(_raw(got), _raw(ref))
+
+
 def test_final_gather_small_map_radius_doubling(built):
     """fewer than 50 indirect photons and queries far from them: the doubling search ends with every photon's direction"""
     sc = O.PortFullScene()
