@@ -87,8 +87,8 @@ __host__ __device__ __forceinline__ float fg_box_d2(const FgGrid &g, const float
     }
     return d2;
 }
-// Normal bounds: per level-1 / level-2 cell the componentwise min and max of its photons' normals (6 floats: lo.xyz,
-// hi.xyz).  No photon of the cell can face n when sum_a max(n_a * lo_a, n_a * hi_a) <= 0: every product and the two
+// Cell bounds: per level-1 / level-2 cell 12 floats, the componentwise min and max of its photons' normals (lo.xyz,
+// hi.xyz) and then of their positions.  No photon of the cell can face n when sum_a max(n_a * lo_a, n_a * hi_a) <= 0: every product and the two
 // additions are the ones dot3() performs on a photon of the cell with each factor replaced by its bound, and rounded
 // multiplication and addition are monotonic, so the photon's own dot product is <= 0 too and the scan would reject it.
 // Without this a query whose neighbourhood only holds photons facing away (a gather ray that hits a mirror ball next to
@@ -97,25 +97,39 @@ __host__ __device__ __forceinline__ bool fg_may_face(const float *__restrict__ n
     const float b = fmaxf(n.x * nb[0], n.x * nb[3]) + fmaxf(n.y * nb[1], n.y * nb[4]) + fmaxf(n.z * nb[2], n.z * nb[5]);
     return b > 0.f;
 }
+// squared distance from p to the bounding box of a cell's photon POSITIONS (pb = lo.xyz, hi.xyz): a lower bound of what
+// fg_scan_range computes for any photon of the cell (same operations on bounds, monotonic rounding).  Much tighter than
+// the cell's own box when the photons lie on a surface that crosses it: with the grid box, a query above a floor opens
+// every floor cell within sqrt(2 h cell) of the foot point, a hundred cells, however good its current best is.
+__host__ __device__ __forceinline__ float fg_pbox_d2(const float *__restrict__ pb, f3 p) {
+    const float dx = fmaxf(fmaxf(pb[0] - p.x, p.x - pb[3]), 0.f), dy = fmaxf(fmaxf(pb[1] - p.y, p.y - pb[4]), 0.f),
+                dz = fmaxf(fmaxf(pb[2] - p.z, p.z - pb[5]), 0.f);
+    return dx * dx + dy * dy + dz * dz;
+}
 __host__ __device__ inline void fg_nbox_level1(const FgGrid &g, const float4 *__restrict__ photons,
                                                const uint32_t *__restrict__ cell_start, int X, int Y, int Z, float *out) {
     float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    float plo[3] = {INFINITY, INFINITY, INFINITY}, phi[3] = {-INFINITY, -INFINITY, -INFINITY};
     const int fx0 = 4 * X, fx1 = min(fx0 + 4, g.dims[0]);
     for (int z = 4 * Z; z < min(4 * Z + 4, g.dims[2]); ++z)
         for (int y = 4 * Y; y < min(4 * Y + 4, g.dims[1]); ++y) {
             const size_t row = ((size_t)z * g.dims[1] + y) * g.dims[0];
             for (uint32_t i = cell_start[row + fx0]; i < cell_start[row + fx1]; ++i) {
-                const f3 m = fg_oct_decode(fg_f2u(photons[2 * (size_t)i].w));
+                const float4 A = photons[2 * (size_t)i];
+                const f3 m = fg_oct_decode(fg_f2u(A.w));
                 lo[0] = fminf(lo[0], m.x); lo[1] = fminf(lo[1], m.y); lo[2] = fminf(lo[2], m.z);
                 hi[0] = fmaxf(hi[0], m.x); hi[1] = fmaxf(hi[1], m.y); hi[2] = fmaxf(hi[2], m.z);
+                plo[0] = fminf(plo[0], A.x); plo[1] = fminf(plo[1], A.y); plo[2] = fminf(plo[2], A.z);
+                phi[0] = fmaxf(phi[0], A.x); phi[1] = fmaxf(phi[1], A.y); phi[2] = fmaxf(phi[2], A.z);
             }
         }
-    for (int a = 0; a < 3; ++a) { out[a] = lo[a]; out[3 + a] = hi[a]; }
+    for (int a = 0; a < 3; ++a) { out[a] = lo[a]; out[3 + a] = hi[a]; out[6 + a] = plo[a]; out[9 + a] = phi[a]; }
 }
 __host__ __device__ inline void fg_nbox_level2(const FgGrid &g, const float *__restrict__ nbox1,
                                                const uint32_t *__restrict__ coarse1, int X, int Y, int Z, float *out,
                                                uint32_t *count) {
     float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    float plo[3] = {INFINITY, INFINITY, INFINITY}, phi[3] = {-INFINITY, -INFINITY, -INFINITY};
     uint32_t cnt = 0;
     for (int z = 4 * Z; z < min(4 * Z + 4, g.cdims[2]); ++z)
         for (int y = 4 * Y; y < min(4 * Y + 4, g.cdims[1]); ++y)
@@ -123,9 +137,12 @@ __host__ __device__ inline void fg_nbox_level2(const FgGrid &g, const float *__r
                 const size_t i = ((size_t)z * g.cdims[1] + y) * g.cdims[0] + x;
                 if (coarse1[i] == 0u) continue;
                 cnt += coarse1[i];
-                for (int a = 0; a < 3; ++a) { lo[a] = fminf(lo[a], nbox1[6 * i + a]); hi[a] = fmaxf(hi[a], nbox1[6 * i + 3 + a]); }
+                for (int a = 0; a < 3; ++a) {
+                    lo[a] = fminf(lo[a], nbox1[12 * i + a]); hi[a] = fmaxf(hi[a], nbox1[12 * i + 3 + a]);
+                    plo[a] = fminf(plo[a], nbox1[12 * i + 6 + a]); phi[a] = fmaxf(phi[a], nbox1[12 * i + 9 + a]);
+                }
             }
-    for (int a = 0; a < 3; ++a) { out[a] = lo[a]; out[3 + a] = hi[a]; }
+    for (int a = 0; a < 3; ++a) { out[a] = lo[a]; out[3 + a] = hi[a]; out[6 + a] = plo[a]; out[9 + a] = phi[a]; }
     *count = cnt;
 }
 // min over the warp by (d2, index): every lane ends with the winner.  NL = 1 (one thread owns the lookup): nothing to do.
@@ -153,25 +170,24 @@ __host__ __device__ inline void fg_visit_level2(const FgGrid &g, const float4 *_
                                                 int Z, bool sample, int lane, int &best, float &best_d2) {
     const size_t i2 = ((size_t)Z * g.c2dims[1] + Y) * g.c2dims[0] + X;
     FG_STAT(1, 1);
-    if (coarse2[i2] == 0u || !fg_may_face(nbox2 + 6 * i2, n)) return;
-    if (fg_box_d2(g, pa, 16 * X, min(16 * X + 16, g.dims[0]), 16 * Y, min(16 * Y + 16, g.dims[1]), 16 * Z,
-                  min(16 * Z + 16, g.dims[2])) > best_d2)
-        return;
+    if (coarse2[i2] == 0u || !fg_may_face(nbox2 + 12 * i2, n)) return;
+    if (fg_pbox_d2(nbox2 + 12 * i2 + 6, p) > best_d2) return;
     for (int k = lane; k < 64; k += NL) {
                 const int x1 = 4 * X + (k & 3), y1 = 4 * Y + ((k >> 2) & 3), z1 = 4 * Z + (k >> 4);
                 if (x1 >= g.cdims[0] || y1 >= g.cdims[1] || z1 >= g.cdims[2]) continue;
                 const size_t i1c = ((size_t)z1 * g.cdims[1] + y1) * g.cdims[0] + x1;
                 FG_STAT(2, 1);
-                if (coarse1[i1c] == 0u || !fg_may_face(nbox1 + 6 * i1c, n)) continue;
+                if (coarse1[i1c] == 0u || !fg_may_face(nbox1 + 12 * i1c, n)) continue;
+                if (fg_pbox_d2(nbox1 + 12 * i1c + 6, p) > best_d2) continue;
                 const int fx0 = 4 * x1, fx1 = min(fx0 + 4, g.dims[0]);
                 const int fy1 = min(4 * y1 + 4, g.dims[1]), fz1 = min(4 * z1 + 4, g.dims[2]);
-                if (fg_box_d2(g, pa, fx0, fx1, 4 * y1, fy1, 4 * z1, fz1) > best_d2) continue;
                 for (int z = 4 * z1; z < fz1; ++z)
                     for (int y = 4 * y1; y < fy1; ++y) {
                         const size_t row = ((size_t)z * g.dims[1] + y) * g.dims[0];
                         const uint32_t i0 = cell_start[row + fx0], i1 = cell_start[row + fx1];
                         if (i0 == i1) continue;
                         if (fg_box_d2(g, pa, fx0, fx1, y, y + 1, z, z + 1) > best_d2) continue;
+                        FG_STAT(3, sample ? 1 : 0);
                         fg_scan_range(photons, i0, sample ? i0 + 1u : i1, p, n, best, best_d2);
                     }
     }
@@ -271,6 +287,27 @@ __host__ __device__ inline void fg_radiance_phase1(const FgGrid &g, const float4
         if (bound == INFINITY) break;
         bound -= g.slack;
         if (best >= 0 && bound > 0.f && best_d2 < bound * bound) break;
+    }
+    // between the sweeps: all photons of the 3 x 3 x 3 fine cells around the sampled winner.  The exact sweep has to open
+    // every admissible cell that reaches into the ball of the current best, i.e. a layer around the true nearest as thick
+    // as the sample's error; this brings the error from a couple of cells down to the local photon spacing.
+    if (sample && best >= 0) {
+        const float4 B = photons[2 * (size_t)best];
+        const float pb[3] = {B.x, B.y, B.z};
+        int cb[3];
+        for (int a = 0; a < 3; ++a) {
+            float f = floorf((pb[a] - g.lo[a]) * g.inv);
+            f = fminf(fmaxf(f, 0.f), (float)(g.dims[a] - 1));
+            cb[a] = (int)f;
+        }
+        const int xa = max(cb[0] - 1, 0), xb = min(cb[0] + 1, g.dims[0] - 1);
+        for (int k = lane; k < 9; k += NL) {
+            const int y = cb[1] - 1 + k % 3, z = cb[2] - 1 + k / 3;
+            if (y < 0 || z < 0 || y >= g.dims[1] || z >= g.dims[2]) continue;
+            const size_t row = ((size_t)z * g.dims[1] + y) * g.dims[0];
+            fg_scan_range(photons, cell_start[row + xa], cell_start[row + xb + 1], p, n, best, best_d2);
+        }
+        fg_lanes_min<NL>(best, best_d2);
     }
     }
 }

@@ -345,14 +345,14 @@ final_gather_kernel(const FgArgs A) {
     if (overflow) atomicAdd(A.status, 1u);
 }
 
-// search tables of the radiance-photon grid: normal bounds per level-1 cell (4^3 fine cells), then count + normal bounds
+// search tables of the radiance-photon grid: normal and position bounds per level-1 cell (4^3 fine cells), then count + normal bounds
 // per level-2 cell (16^3 fine cells); arithmetic in b2rt_fg.cuh
 __global__ void __launch_bounds__(128)
 fg_nbox1_kernel(FgGrid g, const float4 *__restrict__ photons, const uint32_t *__restrict__ cell_start, float *__restrict__ nbox1) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= g.cdims[0] * g.cdims[1] * g.cdims[2]) return;
     fg_nbox_level1(g, photons, cell_start, i % g.cdims[0], (i / g.cdims[0]) % g.cdims[1], i / (g.cdims[0] * g.cdims[1]),
-                   nbox1 + 6 * (size_t)i);
+                   nbox1 + 12 * (size_t)i);
 }
 __global__ void __launch_bounds__(128)
 fg_level2_kernel(FgGrid g, const float *__restrict__ nbox1, const uint32_t *__restrict__ coarse1, float *__restrict__ nbox2,
@@ -360,7 +360,7 @@ fg_level2_kernel(FgGrid g, const float *__restrict__ nbox1, const uint32_t *__re
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= g.c2dims[0] * g.c2dims[1] * g.c2dims[2]) return;
     fg_nbox_level2(g, nbox1, coarse1, i % g.c2dims[0], (i / g.c2dims[0]) % g.c2dims[1], i / (g.c2dims[0] * g.c2dims[1]),
-                   nbox2 + 6 * (size_t)i, coarse2 + i);
+                   nbox2 + 12 * (size_t)i, coarse2 + i);
 }
 
 FgGrid fg_grid_of(const PhotonMap &m) {
@@ -384,8 +384,8 @@ FgGrid fg_grid_of(const PhotonMap &m) {
 static int fg_prepare_radiance(b2rt_ctx *ctx, const FgGrid &g) {
     PhotonMap &mr = ctx->maps[B2RT_MAP_RADIANCE];
     const int n1 = g.cdims[0] * g.cdims[1] * g.cdims[2], n2 = g.c2dims[0] * g.c2dims[1] * g.c2dims[2];
-    B2RT_CUDA(ctx, ctx->d_fg_nbox1.reserve((size_t)n1 * 24));
-    B2RT_CUDA(ctx, ctx->d_fg_nbox2.reserve((size_t)n2 * 24));
+    B2RT_CUDA(ctx, ctx->d_fg_nbox1.reserve((size_t)n1 * 48));
+    B2RT_CUDA(ctx, ctx->d_fg_nbox2.reserve((size_t)n2 * 48));
     B2RT_CUDA(ctx, ctx->d_fg_coarse2.reserve((size_t)n2 * 4));
     fg_nbox1_kernel<<<(n1 + 127) / 128, 128, 0, ctx->stream>>>(g, mr.sorted.as<float4>(), mr.cell_start.as<uint32_t>(),
                                                                ctx->d_fg_nbox1.as<float>());

@@ -23,14 +23,14 @@ void emu_radiance_nearest(const float *lo, float cell, float inv, float slack, c
     }
     g.cell = cell; g.inv = inv; g.slack = slack;
     const int n1 = g.cdims[0] * g.cdims[1] * g.cdims[2], n2 = g.c2dims[0] * g.c2dims[1] * g.c2dims[2];
-    float *nbox1 = new float[6 * (size_t)n1], *nbox2 = new float[6 * (size_t)n2];
+    float *nbox1 = new float[12 * (size_t)n1], *nbox2 = new float[12 * (size_t)n2];
     uint32_t *coarse2 = new uint32_t[n2];
     for (int i = 0; i < n1; ++i)
         fg_nbox_level1(g, (const float4 *)photons, cell_start, i % g.cdims[0], (i / g.cdims[0]) % g.cdims[1],
-                       i / (g.cdims[0] * g.cdims[1]), nbox1 + 6 * (size_t)i);
+                       i / (g.cdims[0] * g.cdims[1]), nbox1 + 12 * (size_t)i);
     for (int i = 0; i < n2; ++i)
         fg_nbox_level2(g, nbox1, coarse1, i % g.c2dims[0], (i / g.c2dims[0]) % g.c2dims[1], i / (g.c2dims[0] * g.c2dims[1]),
-                       nbox2 + 6 * (size_t)i, coarse2 + i);
+                       nbox2 + 12 * (size_t)i, coarse2 + i);
     for (long long q = 0; q < nq; ++q) {
         const float *Q = queries + 12 * q;
         float d2;

@@ -52,8 +52,8 @@ def run(name, p, n):
     emu.emu_stat(st, 1)
     _, ref = O.radiance_lookup(srt, q[:200])
     assert np.array_equal(idx[:200], ref)
-    print("%-34s photons tested / query %9.1f   level-2 cells %7.1f   level-1 cells %7.1f   found dist (cells) %5.1f   %.1f us/query (host)"
-          % (name, st[0] / len(q), st[1] / len(q), st[2] / len(q), float(np.sqrt(d2[idx >= 0]).mean() / g["cell_size"]),
+    print("%-34s photons tested / query %9.1f   level-2 cells %7.1f   level-1 cells %7.1f   (sampled %6.1f)   found dist (cells) %5.1f   %.1f us/query (host)"
+          % (name, st[0] / len(q), st[1] / len(q), st[2] / len(q), st[3] / len(q), float(np.sqrt(d2[idx >= 0]).mean() / g["cell_size"]),
              (t1 - t0) / len(q) * 1e6))
 
 
@@ -67,3 +67,55 @@ for name, c in (("glass sphere", (0.4, 0.35, 0.3)), ("mirror sphere", (-0.45, 0.
 v = rng.normal(size=(nq, 3))
 v /= np.linalg.norm(v, axis=1, keepdims=True)
 run("inside the box, random normal", rng.uniform((-1.7, 0.05, -0.95), (1.7, 1.95, 0.95), (nq, 3)), v)
+
+# ---- the lookups of real gather rays: cosine-sampled rays from lit surface points, exhaustive closest hit ------------------
+ns = 6000
+pick = rng.integers(0, len(rad), ns)
+P0, N0 = rad["p"][pick].astype(np.float64), O.oct_decode(rad["wi_oct"][pick]).astype(np.float64)
+u1, u2 = rng.random(ns), rng.random(ns)
+rr, ph = np.sqrt(u1), 2 * np.pi * u2
+t1 = np.where(np.abs(N0[:, :1]) > 0.5, np.array([[0.0, 1.0, 0.0]]), np.array([[1.0, 0.0, 0.0]]))
+sn = np.cross(N0, t1); sn /= np.linalg.norm(sn, axis=1, keepdims=True)
+tn = np.cross(N0, sn)
+wi = sn * (rr * np.cos(ph))[:, None] + tn * (rr * np.sin(ph))[:, None] + N0 * np.sqrt(1 - u1)[:, None]
+rays = np.zeros((ns, 8), np.float32)
+rays[:, 0:3], rays[:, 3], rays[:, 4:7], rays[:, 7] = P0, 1e-3, wi, np.inf
+t, prim, _, _ = sc.geo.intersect(rays)
+hit = prim >= 0
+kind = np.asarray(sc.geo.kind, np.int32)
+hp = (P0 + wi * t[:, None].astype(np.float64))[hit]
+hk = kind[prim[hit]]
+ng = np.zeros_like(hp)
+verts, idx = np.asarray(sc.geo.verts, np.float64).reshape(-1, 3), np.asarray(sc.geo.idx, np.int64).reshape(-1, 3)
+tri = hk >= 0
+v = verts[idx[hk[tri]]]
+nt = np.cross(v[:, 2] - v[:, 0], v[:, 1] - v[:, 0])
+ng[tri] = nt / np.linalg.norm(nt, axis=1, keepdims=True)
+for c in ((0.4, 0.35, 0.3), (-0.45, 0.35, -0.3)):
+    on = (~tri) & (np.abs(np.linalg.norm(hp - np.asarray(c), axis=1) - 0.35) < 1e-3)
+    ng[on] = (hp[on] - np.asarray(c)) / 0.35
+disk = (~tri) & (np.linalg.norm(ng, axis=1) == 0)
+ng[disk] = (0, 0, 1)
+flip = np.einsum("ij,ij->i", ng, -wi[hit]) < 0
+ng[flip] *= -1
+print("gather rays: %d of %d hit; %.1f %% of the hits on the spheres, %.1f %% on the light's disk"
+      % (hit.sum(), ns, 100 * (~tri & ~disk).mean(), 100 * disk.mean()))
+run("gather-ray hits on matte triangles", hp[tri], ng[tri])
+if (~tri & ~disk).any():
+    run("gather-ray hits on the spheres", hp[~tri & ~disk], ng[~tri & ~disk])
+if disk.any():
+    run("gather-ray hits on the light's disk", hp[disk], ng[disk])
+
+if os.environ.get("FG_DEBUG"):
+    sel = np.where(~tri & ~disk)[0][:12]
+    for i in sel:
+        q = np.zeros((1, 12), np.float32); q[0, 0:3], q[0, 3:6] = hp[i], ng[i]
+        idx, d2 = np.zeros(1, np.int32), np.zeros(1, np.float32)
+        st = (C.c_ulonglong * 4)(); emu.emu_stat(st, 1)
+        emu.emu_radiance_nearest(lo.ctypes.data, g["cell_size"], g["inv_cell"], slack, dims.ctypes.data, srt.ctypes.data,
+                                 cs.ctypes.data, c1.ctypes.data, 1, q.ctypes.data, idx.ctypes.data, d2.ctypes.data)
+        emu.emu_stat(st, 1)
+        ph = srt[idx[0]]
+        print("p %s n %s -> photon p %s normal %s dist %.2f | tests %d l2 %d l1 %d sampled %d"
+              % (np.round(hp[i], 2), np.round(ng[i], 2), np.round(ph["p"], 2), np.round(O.oct_decode(np.array([ph["wi_oct"]]))[0], 2),
+                 np.sqrt(d2[0]), st[0], st[1], st[2], st[3]))

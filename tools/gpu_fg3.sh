@@ -1,5 +1,5 @@
 #!/bin/bash
-# Third GPU pass for final gathering (sampling sweep in the radiance-photon lookup).   usage: tools/gpu_fg3.sh <tag>
+# GPU pass for final gathering: whole GPU suite, fg stage timings of both lookup variants at two sizes, ncu launch list, smoke.   usage: tools/gpu_fg3.sh <tag>
 TAG=${1:-r03d}
 O=gpurun_out/$TAG
 mkdir -p $O
@@ -11,5 +11,4 @@ B2RT_FG_VARIANT=1 timeout 40 python tools/bench_fg.py 8000000 2000000 1920 1080 
 B2RT_FG_VARIANT=1 timeout 60 ncu --clock-control none --metrics gpu__time_duration.sum -c 600 --csv --log-file $O/launches_fg.csv \
     python tools/bench_fg.py 1000000 100000 960 540 32 1 > $O/ncu_fg.log 2>&1
 timeout 30 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" > $O/smoke.txt 2>&1
-timeout 80 python bench.py > $O/bench.json 2> $O/bench.err; echo "bench rc=$?" >> $O/bench.err
 ls -la $O
