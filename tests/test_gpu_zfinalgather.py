@@ -154,9 +154,11 @@ def test_final_gather_matches_oracle(fctx, oracle_maps, computed, gs):
     assert err.max() <= 1e-5, (err.max(), float((_raw(got) == _raw(ref)).mean()))
 
 
-def test_final_gather_warp_cooperative_lookup_is_bit_identical(fctx, computed, monkeypatch):
-    """B2RT_FG_VARIANT=1: the far radiance-photon lookups of a warp's gather rays are worked through by all 32 lanes
-    together.  The lookup is exact either way, so the gather's output must not change by a bit."""
+@pytest.mark.parametrize("variant", ["0", "1"])
+def test_final_gather_lookup_variants_are_bit_identical(fctx, computed, monkeypatch, variant):
+    """B2RT_FG_VARIANT: the far radiance-photon lookups of a warp's gather rays are done by each lane on its own (0) or
+    worked through by all 32 lanes together (1).  The lookup is exact either way, so the gather's output must not change
+    by a bit, whichever variant is the default."""
     q = np.concatenate([_gather_queries(96, seed=31), _gather_queries(160, seed=32)])
     # shading points whose gather rays mostly end on the glass / mirror spheres (far lookups): on the floor between them
     q[96:, 0] = np.linspace(-0.8, 0.8, 160, dtype=np.float32)
@@ -166,7 +168,7 @@ def test_final_gather_warp_cooperative_lookup_is_bit_identical(fctx, computed, m
     fctx.set_final_gather(True, 32, 10.0)
     ref = fctx.final_gather(q.view(b2rt.QUERY_DTYPE).reshape(-1), float(MAXD2))
     fctx.set_final_gather(False)
-    monkeypatch.setenv("B2RT_FG_VARIANT", "1")
+    monkeypatch.setenv("B2RT_FG_VARIANT", variant)
     with b2rt.Context(0, seed=G.SEED) as c:
         S.fill_scene(c, S.cornell_scene())
         c.build_accel()
