@@ -5,6 +5,9 @@
 #pragma once
 #include "b2rt_device.cuh"
 
+#ifndef FG_PHASE
+#define FG_PHASE(x)
+#endif
 #ifndef FG_STAT
 #define FG_STAT(counter, amount)          // tests/hostemu defines it to count the work of a lookup on the host
 #endif
@@ -61,6 +64,9 @@ __host__ __device__ __forceinline__ uint32_t fg_f2u(float f) {
 // cell size.  Both phases only ever skip photons that cannot win, so the result is the exact global nearest: identical to
 // a brute-force scan (tests/test_oracle_fg_cpu.py runs this very code on the host against one).
 #define FG_FINE_SHELLS 2
+#ifndef FG_REFINE_PASSES
+#define FG_REFINE_PASSES 1
+#endif
 __host__ __device__ __forceinline__ void fg_scan_range(const float4 *__restrict__ photons, uint32_t i0, uint32_t i1, f3 p, f3 n,
                                                        int &best, float &best_d2) {
     FG_STAT(0, i1 - i0);
@@ -159,6 +165,21 @@ __host__ __device__ __forceinline__ void fg_lanes_min(int &best, float &best_d2)
     }
 #endif
 }
+// lower bound for the photons of fine cells [x0, x1) x {y} x {z} inside a level-1 cell with position bounds pb: per axis a
+// photon lies in the grid interval AND in the cell's position interval, so its distance is at least the larger of the
+// two (a floor's photons all have y = 0: the row's grid box alone would put them up to a cell nearer than they are)
+__host__ __device__ __forceinline__ float fg_row_d2(const FgGrid &g, const float *pa, const float *__restrict__ pb, int x0, int x1,
+                                                    int y, int z) {
+    const int i0[3] = {x0, y, z}, i1[3] = {x1, y + 1, z + 1};
+    float d2 = 0.f;
+    for (int a = 0; a < 3; ++a) {
+        float d = fmaxf(fmaxf(pb[a] - pa[a], pa[a] - pb[3 + a]), 0.f);
+        if (i0[a] > 0) d = fmaxf(d, (g.lo[a] + (float)i0[a] * g.cell) - pa[a] - g.slack);
+        if (i1[a] < g.dims[a]) d = fmaxf(d, pa[a] - (g.lo[a] + (float)i1[a] * g.cell) - g.slack);
+        d2 += d * d;
+    }
+    return d2;
+}
 // one level-2 cell (X, Y, Z): descend through the occupancy tables.  NL lanes share the cell: lane l takes the level-1
 // children l, l + NL, ... with a private best and the lanes agree on the minimum before they leave (all decisions up to
 // the children loop depend only on values every lane holds, so a warp stays converged around the shuffles).
@@ -172,11 +193,30 @@ __host__ __device__ inline void fg_visit_level2(const FgGrid &g, const float4 *_
     FG_STAT(1, 1);
     if (coarse2[i2] == 0u || !fg_may_face(nbox2 + 12 * i2, n)) return;
     if (fg_pbox_d2(nbox2 + 12 * i2 + 6, p) > best_d2) return;
-    for (int k = lane; k < 64; k += NL) {
+    // One thread per lookup: open the admissible child whose position box is nearest first.  The nearest photon is most
+    // likely in it, and with best = its distance the tight boxes of the other children prune them without a distance test
+    // (raster order would scan every child that lies before it).  Lanes sharing a lookup take their children as they come.
+    int kfirst = -1;
+    if (NL == 1) {
+        float dmin = best_d2;
+        for (int k = 0; k < 64; ++k) {
+            const int x1 = 4 * X + (k & 3), y1 = 4 * Y + ((k >> 2) & 3), z1 = 4 * Z + (k >> 4);
+            if (x1 >= g.cdims[0] || y1 >= g.cdims[1] || z1 >= g.cdims[2]) continue;
+            const size_t i1c = ((size_t)z1 * g.cdims[1] + y1) * g.cdims[0] + x1;
+            FG_STAT(2, 1);
+            if (coarse1[i1c] == 0u || !fg_may_face(nbox1 + 12 * i1c, n)) continue;
+            const float d = fg_pbox_d2(nbox1 + 12 * i1c + 6, p);
+            if (d <= dmin) { if (d < dmin || kfirst < 0) { dmin = d; kfirst = k; } }
+        }
+        if (kfirst < 0) return;
+    }
+    for (int kk = (NL == 1 ? -1 : lane); kk < 64; kk += NL) {
+                const int k = kk < 0 ? kfirst : kk;
+                if (kk >= 0 && k == kfirst) continue;
                 const int x1 = 4 * X + (k & 3), y1 = 4 * Y + ((k >> 2) & 3), z1 = 4 * Z + (k >> 4);
                 if (x1 >= g.cdims[0] || y1 >= g.cdims[1] || z1 >= g.cdims[2]) continue;
                 const size_t i1c = ((size_t)z1 * g.cdims[1] + y1) * g.cdims[0] + x1;
-                FG_STAT(2, 1);
+                if (NL > 1) FG_STAT(2, 1);
                 if (coarse1[i1c] == 0u || !fg_may_face(nbox1 + 12 * i1c, n)) continue;
                 if (fg_pbox_d2(nbox1 + 12 * i1c + 6, p) > best_d2) continue;
                 const int fx0 = 4 * x1, fx1 = min(fx0 + 4, g.dims[0]);
@@ -186,7 +226,7 @@ __host__ __device__ inline void fg_visit_level2(const FgGrid &g, const float4 *_
                         const size_t row = ((size_t)z * g.dims[1] + y) * g.dims[0];
                         const uint32_t i0 = cell_start[row + fx0], i1 = cell_start[row + fx1];
                         if (i0 == i1) continue;
-                        if (fg_box_d2(g, pa, fx0, fx1, y, y + 1, z, z + 1) > best_d2) continue;
+                        if (fg_row_d2(g, pa, nbox1 + 12 * i1c + 6, fx0, fx1, y, z) > best_d2) continue;
                         FG_STAT(3, sample ? 1 : 0);
                         fg_scan_range(photons, i0, sample ? i0 + 1u : i1, p, n, best, best_d2);
                     }
@@ -207,6 +247,7 @@ __host__ __device__ inline bool fg_radiance_phase0(const FgGrid &g, const float4
     for (int a = 0; a < 3; ++a) { rmax = max(rmax, c[a]); rmax = max(rmax, g.dims[a] - 1 - c[a]); }
     best = -1;
     best_d2 = INFINITY;
+    FG_PHASE(0);
     // ---- phase 0: fine shells -----------------------------------------------------------------------------------------
     for (int r = 0; r <= min(rmax, FG_FINE_SHELLS); ++r) {
         const int z0 = max(c[2] - r, 0), z1 = min(c[2] + r, g.dims[2] - 1);
@@ -261,23 +302,38 @@ __host__ __device__ inline void fg_radiance_phase1(const FgGrid &g, const float4
     // order spends most of its tests on cells it would have skipped had it seen the near ones first: tools/fg_lookup_work.py.)
     for (int sweep = 0; sweep < 2; ++sweep) {
     const bool sample = sweep == 0;
+    FG_PHASE(sample ? 1 : 3);
     for (int R = 0; R <= Rmax; ++R) {
         const int Z0 = max(C[2] - R, 0), Z1 = min(C[2] + R, g.c2dims[2] - 1);
         const int Y0 = max(C[1] - R, 0), Y1 = min(C[1] + R, g.c2dims[1] - 1);
         const int X0 = max(C[0] - R, 0), X1 = min(C[0] + R, g.c2dims[0] - 1);
-        for (int Z = Z0; Z <= Z1; ++Z) {
-            const bool zface = (Z == C[2] - R) || (Z == C[2] + R);
-            for (int Y = Y0; Y <= Y1; ++Y) {
-                if (zface || (Y == C[1] - R) || (Y == C[1] + R)) {
-                    for (int X = X0; X <= X1; ++X)
-                        fg_visit_level2<NL>(g, photons, cell_start, coarse1, coarse2, nbox1, nbox2, pa, p, n, X, Y, Z, sample, lane, best, best_d2);
-                } else {
-                    if (C[0] - R >= 0)
-                        fg_visit_level2<NL>(g, photons, cell_start, coarse1, coarse2, nbox1, nbox2, pa, p, n, C[0] - R, Y, Z, sample, lane, best, best_d2);
-                    if (C[0] + R < g.c2dims[0])
-                        fg_visit_level2<NL>(g, photons, cell_start, coarse1, coarse2, nbox1, nbox2, pa, p, n, C[0] + R, Y, Z, sample, lane, best, best_d2);
+        // mode 0 finds the admissible cell of the shell whose position box is nearest and opens it first (see
+        // fg_visit_level2), mode 1 opens the others in raster order
+        int fX = -1, fY = -1, fZ = -1;
+        for (int mode = 0; mode < 2; ++mode) {
+            float dmin = best_d2;
+            for (int Z = Z0; Z <= Z1; ++Z) {
+                const bool zface = (Z == C[2] - R) || (Z == C[2] + R);
+                for (int Y = Y0; Y <= Y1; ++Y) {
+                    const bool full = zface || (Y == C[1] - R) || (Y == C[1] + R);
+                    for (int X = full ? X0 : max(C[0] - R, X0); X <= X1; ++X) {
+                        if (!full && X != C[0] - R && X != C[0] + R) {        // interior of the row: jump to its far end
+                            if (C[0] + R > X1 || X > C[0] + R) break;
+                            X = C[0] + R;
+                        }
+                        if (mode == 0) {
+                            const size_t i2 = ((size_t)Z * g.c2dims[1] + Y) * g.c2dims[0] + X;
+                            if (coarse2[i2] == 0u || !fg_may_face(nbox2 + 12 * i2, n)) continue;
+                            const float d = fg_pbox_d2(nbox2 + 12 * i2 + 6, p);
+                            if (d <= dmin && (d < dmin || fX < 0)) { dmin = d; fX = X; fY = Y; fZ = Z; }
+                        } else if (X != fX || Y != fY || Z != fZ) {
+                            fg_visit_level2<NL>(g, photons, cell_start, coarse1, coarse2, nbox1, nbox2, pa, p, n, X, Y, Z, sample, lane, best, best_d2);
+                        }
+                    }
                 }
             }
+            if (mode == 0 && fX >= 0)
+                fg_visit_level2<NL>(g, photons, cell_start, coarse1, coarse2, nbox1, nbox2, pa, p, n, fX, fY, fZ, sample, lane, best, best_d2);
         }
         float bound = INFINITY;
         for (int a = 0; a < 3; ++a) {
@@ -291,7 +347,9 @@ __host__ __device__ inline void fg_radiance_phase1(const FgGrid &g, const float4
     // between the sweeps: all photons of the 3 x 3 x 3 fine cells around the sampled winner.  The exact sweep has to open
     // every admissible cell that reaches into the ball of the current best, i.e. a layer around the true nearest as thick
     // as the sample's error; this brings the error from a couple of cells down to the local photon spacing.
-    if (sample && best >= 0) {
+    for (int pass = 0, prev = -1; sample && best >= 0 && best != prev && pass < FG_REFINE_PASSES; ++pass) {
+        prev = best;
+        FG_PHASE(2);
         const float4 B = photons[2 * (size_t)best];
         const float pb[3] = {B.x, B.y, B.z};
         int cb[3];

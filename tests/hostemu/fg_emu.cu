@@ -2,11 +2,16 @@
 // search and the MIS helpers the final-gather kernel calls) for the HOST, so the CPU test suite can run the very code the
 // GPU runs against the C oracle without a GPU.  Never loaded by the product path.
 // work counters of the lookup: [0] photons distance-tested, [1] level-2 cells looked at, [2] level-1 cells looked at
-static unsigned long long g_fg_stat[4];
+static unsigned long long g_fg_stat[4], g_fg_phase_tests[4];
+static int g_fg_phase;
 #ifdef __CUDA_ARCH__
 #define FG_STAT(counter, amount)
 #else
-#define FG_STAT(counter, amount) (g_fg_stat[counter] += (unsigned long long)(amount))
+#define FG_STAT(counter, amount) (g_fg_stat[counter] += (unsigned long long)(amount), (counter) == 0 ? (g_fg_phase_tests[g_fg_phase] += (unsigned long long)(amount)) : 0ull)
+#define FG_PHASE(x) (g_fg_phase = (x))
+#endif
+#ifndef FG_PHASE
+#define FG_PHASE(x)
 #endif
 #include "../../cuda_raytrace_b200/csrc/b2rt_fg.cuh"
 
@@ -39,6 +44,10 @@ void emu_radiance_nearest(const float *lo, float cell, float inv, float slack, c
         if (d2_out) d2_out[q] = d2;
     }
     delete[] nbox1; delete[] nbox2; delete[] coarse2;
+}
+// distance tests per phase of the lookup: fine shells, sampling sweep, refinement around the sampled winner, exact sweep
+void emu_phase_tests(unsigned long long *out, int reset) {
+    for (int i = 0; i < 4; ++i) { out[i] = g_fg_phase_tests[i]; if (reset) g_fg_phase_tests[i] = 0; }
 }
 void emu_stat(unsigned long long *out, int reset) {
     for (int i = 0; i < 4; ++i) { out[i] = g_fg_stat[i]; if (reset) g_fg_stat[i] = 0; }

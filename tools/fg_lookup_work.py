@@ -50,6 +50,10 @@ def run(name, p, n):
                              cs.ctypes.data, c1.ctypes.data, len(q), q.ctypes.data, idx.ctypes.data, d2.ctypes.data)
     t1 = time.perf_counter()
     emu.emu_stat(st, 1)
+    pt = (C.c_ulonglong * 4)()
+    emu.emu_phase_tests(pt, 1)
+    print("      distance tests per query by phase: fine shells %.1f, sampling sweep %.1f, refinement %.1f, exact sweep %.1f"
+          % tuple(v / len(q) for v in pt))
     _, ref = O.radiance_lookup(srt, q[:200])
     assert np.array_equal(idx[:200], ref)
     print("%-34s photons tested / query %9.1f   level-2 cells %7.1f   level-1 cells %7.1f   (sampled %6.1f)   found dist (cells) %5.1f   %.1f us/query (host)"
@@ -107,7 +111,7 @@ if disk.any():
     run("gather-ray hits on the light's disk", hp[disk], ng[disk])
 
 if os.environ.get("FG_DEBUG"):
-    sel = np.where(~tri & ~disk)[0][:12]
+    sel = np.where(~tri & ~disk)[0][:60]
     for i in sel:
         q = np.zeros((1, 12), np.float32); q[0, 0:3], q[0, 3:6] = hp[i], ng[i]
         idx, d2 = np.zeros(1, np.int32), np.zeros(1, np.float32)
