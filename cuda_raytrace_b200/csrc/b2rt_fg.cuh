@@ -234,8 +234,13 @@ __host__ __device__ inline void fg_visit_level2(const FgGrid &g, const float4 *_
     fg_lanes_min<NL>(best, best_d2);
 }
 // phase 0; returns true when the lookup is finished (best / best_d2 final), false when phase 1 has to continue from them
+// NL = 1: one thread owns the lookup.  NL = 32: the lanes of a warp share it (same p, n on all): they stride over the
+// photons of every row range with a private best and agree on the minimum after each shell, so the stopping rule sees the
+// same values on every lane and the warp stays converged.
+template <int NL>
 __host__ __device__ inline bool fg_radiance_phase0(const FgGrid &g, const float4 *__restrict__ photons,
-                                                   const uint32_t *__restrict__ cell_start, f3 p, f3 n, int &best, float &best_d2) {
+                                                   const uint32_t *__restrict__ cell_start, f3 p, f3 n, int lane, int &best,
+                                                   float &best_d2) {
     const float pa[3] = {p.x, p.y, p.z};
     int c[3];
     for (int a = 0; a < 3; ++a) {
@@ -264,10 +269,14 @@ __host__ __device__ inline bool fg_radiance_phase0(const FgGrid &g, const float4
                     if (full) { xa = x0; xb = x1; }
                     else if (part == 0) { xa = xb = c[0] - r; if (xa < 0) continue; }
                     else { xa = xb = c[0] + r; if (xa >= g.dims[0]) continue; }
-                    fg_scan_range(photons, cell_start[row + xa], cell_start[row + xb + 1], p, n, best, best_d2);
+                    const uint32_t i0 = cell_start[row + xa], i1 = cell_start[row + xb + 1];
+                    if (NL == 1) fg_scan_range(photons, i0, i1, p, n, best, best_d2);
+                    else
+                        for (uint32_t i = i0 + (uint32_t)lane; i < i1; i += NL) fg_scan_range(photons, i, i + 1u, p, n, best, best_d2);
                 }
             }
         }
+        fg_lanes_min<NL>(best, best_d2);
         float bound = INFINITY;
         for (int a = 0; a < 3; ++a) {
             if (c[a] - r > 0) bound = fminf(bound, pa[a] - (g.lo[a] + (float)(c[a] - r) * g.cell));
@@ -375,7 +384,7 @@ __host__ __device__ inline int fg_radiance_nearest(const FgGrid &g, const float4
                                                   const uint32_t *__restrict__ coarse2, const float *__restrict__ nbox1,
                                                   const float *__restrict__ nbox2, f3 p, f3 n, float &best_d2) {
     int best;
-    if (!fg_radiance_phase0(g, photons, cell_start, p, n, best, best_d2))
+    if (!fg_radiance_phase0<1>(g, photons, cell_start, p, n, 0, best, best_d2))
         fg_radiance_phase1<1>(g, photons, cell_start, coarse1, coarse2, nbox1, nbox2, p, n, 0, best, best_d2);
     return best;
 }

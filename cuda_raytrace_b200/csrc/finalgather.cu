@@ -216,7 +216,7 @@ struct FgArgs {
     const b2rt_query *queries;
     int64_t nq;
     int gs;                            // gather rays per strategy (pbrt: gatherSamples / 2)
-    int coop;                          // far lookups: 0 = per lane, 1 = warp-cooperative
+    int coop;                          // lookups: 0 = per lane, 1 = far ones warp-cooperative, 2 = all of them warp-cooperative
     float cos_angle, cone_pdf;
     uint32_t k0, k1;
     float *out_rgb;
@@ -291,8 +291,26 @@ final_gather_kernel(const FgArgs A) {
             int ri = -1;
             float d2 = INFINITY;
             bool far = false;
-            if (hit) far = !fg_radiance_phase0(A.g, A.rad, A.rad_cells, hp, ng, ri, d2);
-            if (A.coop) {
+            if (A.coop == 2) {
+                // every lookup of the warp's rays by all 32 lanes, one after the other: lanes = candidate photons
+                unsigned pend = __ballot_sync(0xffffffffu, hit);
+                while (pend) {
+                    const int src = __ffs(pend) - 1;
+                    pend &= pend - 1u;
+                    const f3 qp = mk3(__shfl_sync(0xffffffffu, hp.x, src), __shfl_sync(0xffffffffu, hp.y, src),
+                                      __shfl_sync(0xffffffffu, hp.z, src));
+                    const f3 qn = mk3(__shfl_sync(0xffffffffu, ng.x, src), __shfl_sync(0xffffffffu, ng.y, src),
+                                      __shfl_sync(0xffffffffu, ng.z, src));
+                    int b;
+                    float bd2;
+                    if (!fg_radiance_phase0<32>(A.g, A.rad, A.rad_cells, qp, qn, lane, b, bd2))
+                        fg_radiance_phase1<32>(A.g, A.rad, A.rad_cells, A.rad_coarse1, A.rad_coarse2, A.rad_nbox1, A.rad_nbox2, qp,
+                                               qn, lane, b, bd2);
+                    if (lane == src) { ri = b; d2 = bd2; }
+                }
+            } else if (hit) far = !fg_radiance_phase0<1>(A.g, A.rad, A.rad_cells, hp, ng, 0, ri, d2);
+            if (A.coop == 2) {
+            } else if (A.coop) {
                 unsigned pend = __ballot_sync(0xffffffffu, far);
                 while (pend) {
                     const int src = __ffs(pend) - 1;
@@ -558,7 +576,7 @@ int b2rt_final_gather_impl(b2rt_ctx *ctx, int64_t nq, const b2rt_query *d_querie
     A.rad_nbox1 = ctx->d_fg_nbox1.as<float>(); A.rad_nbox2 = ctx->d_fg_nbox2.as<float>();
     A.ind = mi.sorted.as<b2rt_photon>(); A.idx = idx; A.found = found; A.queries = d_queries; A.nq = nq;
     A.gs = std::max(1, ctx->fg_samples / 2);
-    A.coop = ctx->fg_variant == 1 ? 1 : 0;
+    A.coop = (ctx->fg_variant == 1 || ctx->fg_variant == 2) ? ctx->fg_variant : 0;
     A.cos_angle = ctx->fg_cos_angle; A.cone_pdf = fg_cone_pdf(ctx->fg_cos_angle);
     A.k0 = (uint32_t)ctx->seed ^ 0x46475448u; A.k1 = (uint32_t)(ctx->seed >> 32);      // 'FGTH' stream
     A.out_rgb = d_rgb; A.status = counters + 8;

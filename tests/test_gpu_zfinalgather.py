@@ -154,10 +154,10 @@ def test_final_gather_matches_oracle(fctx, oracle_maps, computed, gs):
     assert err.max() <= 1e-5, (err.max(), float((_raw(got) == _raw(ref)).mean()))
 
 
-@pytest.mark.parametrize("variant", ["0", "1"])
+@pytest.mark.parametrize("variant", ["0", "1", "2"])
 def test_final_gather_lookup_variants_are_bit_identical(fctx, computed, monkeypatch, variant):
     """B2RT_FG_VARIANT: the far radiance-photon lookups of a warp's gather rays are done by each lane on its own (0) or
-    worked through by all 32 lanes together (1).  The lookup is exact either way, so the gather's output must not change
+    worked through by all 32 lanes together (1), or every lookup is (2).  The lookup is exact either way, so the gather's output must not change
     by a bit, whichever variant is the default."""
     q = np.concatenate([_gather_queries(96, seed=31), _gather_queries(160, seed=32)])
     # shading points whose gather rays mostly end on the glass / mirror spheres (far lookups): on the floor between them
