@@ -81,3 +81,51 @@ def test_interleaved_stripes_partition_and_compose(yres, world, stripes):
     assert np.array_equal(np.concatenate(M.stripe_compose(parts, edges, world), 0), img)
     if stripes is None and yres >= 64 * world:
         assert min(b - a for a, b in zip(edges, edges[1:])) >= 64 - 1          # default: bands of (about) 64 rows or more
+
+
+def _fg_worker(rank, world, port, n_paths, q):
+    """One rank of the sharded second photon pass of final gathering, with the C oracle standing in for the GPU tracer:
+    trace this rank's slice of the path range, assemble both maps in rank order."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from oracle import oracle as O
+    from cuda_raytrace_b200 import scenes as S
+    sc = O.PortFullScene()
+    S.fill_scene(sc, S.cornell_scene())
+    first, count = M.path_range(n_paths, rank, world)
+    d, r = sc.photon_trace_fg(7, first, count)
+    out = []
+    for part in (d, r):
+        local = torch.from_numpy(np.ascontiguousarray(part).view(np.uint8).reshape(-1, 32).copy())
+        allp, counts = M.allgather_varlen(local)
+        out.append((allp.numpy().copy(), counts))
+    q.put((rank, out))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_sharded_final_gather_photon_pass_equals_single_rank(world):
+    """multigpu.shoot_sharded_fg's contract on CPU: direct and radiance photons traced by path-range slices and
+    concatenated in rank order are the single-rank arrays byte for byte (a path's photons depend only on seed and index)."""
+    from oracle import oracle as O
+    from cuda_raytrace_b200 import scenes as S
+    n_paths = 3001
+    port = 29300 + (os.getpid() + world * 13) % 250
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    ps = [ctx.Process(target=_fg_worker, args=(r, world, port, n_paths, q)) for r in range(world)]
+    for p in ps:
+        p.start()
+    res = [q.get(timeout=180) for _ in range(world)]
+    for p in ps:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    sc = O.PortFullScene()
+    S.fill_scene(sc, S.cornell_scene())
+    d, r = sc.photon_trace_fg(7, 0, n_paths)
+    assert len(d) > 1000 and len(r) > 200
+    for rank, out in res:
+        for (allp, counts), ref in zip(out, (d, r)):
+            assert sum(counts) == len(ref) and len(counts) == world
+            assert np.array_equal(allp, np.ascontiguousarray(ref).view(np.uint8).reshape(-1, 32))
