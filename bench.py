@@ -130,25 +130,48 @@ class ClockSampler:
                 "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
 
 
+def hit_parity(gpu_hits, gpu_occ, ref):
+    """The step's GPU results against what the reference's own BVHAccel returned for the same rays (the cpu_baseline leg
+    computes them anyway).  Bars (north star): hit distance bit-identical, primitive id identical except where two
+    primitives share the winning t exactly (a ray through a shared edge: pbrt keeps whichever its tree meets last, the
+    GPU the lower id) -- those are counted as ties, not mismatches."""
+    s1, s2 = ref["primary_stride"], ref["shadow_stride"]
+    gt = np.ascontiguousarray(gpu_hits[::s1, 0]).view(np.uint32)
+    gp = np.ascontiguousarray(gpu_hits[::s1, 1]).view(np.int32)
+    rt, rp = ref["t"].view(np.uint32), ref["prim"]
+    t_bad = gt != rt
+    p_bad = gp != rp
+    go = np.ascontiguousarray(gpu_occ[::s2])
+    return {"oracle": "pbrt-v2 BVHAccel::Intersect / IntersectP (oracle/_ref, the reference's own CPU path)",
+            "rays": int(len(rt) + len(go)), "primary_rays": int(len(rt)), "shadow_rays": int(len(go)),
+            "hits": int((rp >= 0).sum()), "t_mismatch": int(t_bad.sum()), "prim_mismatch": int((p_bad & t_bad).sum()),
+            "ties": int((p_bad & ~t_bad).sum()), "occluded_mismatch": int((go != ref["occ"]).sum()),
+            "ok": bool(not t_bad.any() and not (go != ref["occ"]).any())}
+
+
 def cpu_reference_step(P, idx, rays, shadow, nthreads, sample=None):
-    """The reference's CPU path on (a sample of) one step.  Returns dict(value Mrays/s, kind, cores, sample)."""
+    """The reference's CPU path on (a sample of) one step.  Returns dict(value Mrays/s, kind, cores, sample) and, for
+    the reference kind, the hits it computed (for hit_parity)."""
     from oracle import oracle as O
     if O.ref_available():
         rs = O.RefScene()
         rs.add_mesh(P, idx)
         build_s = rs.build()
         nth = nthreads or rs.num_cores()
-        r1 = rays if sample is None else rays[:: max(1, len(rays) // sample)]
-        r2 = shadow if sample is None else shadow[:: max(1, len(shadow) // sample)]
+        st1 = 1 if sample is None else max(1, len(rays) // sample)
+        st2 = 1 if sample is None else max(1, len(shadow) // sample)
+        r1, r2 = rays[::st1], shadow[::st2]
         rs.intersect(r1[: 20000], nth)                                   # warm the page cache / threads
-        _, _, _, s1 = rs.intersect(r1, nth)
-        _, s2 = rs.occluded(r2, nth)
+        t, prim, _, s1 = rs.intersect(r1, nth)
+        occ, s2 = rs.occluded(r2, nth)
         rs.close()
         n = len(r1) + len(r2)
         return {"value": n / (s1 + s2) / 1e6, "unit": "Mrays/s", "cores": nth, "kind": "reference",
                 "sample": "%d primary (BVHAccel::Intersect) + %d shadow (IntersectP) rays of the step, pbrt-v2 "
-                          "BVHAccel built in %.2f s (excluded)" % (len(r1), len(r2), build_s),
-                "closest_mrays": len(r1) / s1 / 1e6, "any_mrays": len(r2) / s2 / 1e6, "seconds": s1 + s2}
+                          "BVHAccel built in %.2f s (excluded); ranges of 4096 rays handed out by pbrt's own task "
+                          "queue (EnqueueTasks)" % (len(r1), len(r2), build_s),
+                "closest_mrays": len(r1) / s1 / 1e6, "any_mrays": len(r2) / s2 / 1e6, "seconds": s1 + s2,
+                "_hits": {"t": t, "prim": prim, "occ": occ, "primary_stride": st1, "shadow_stride": st2}}
     # port: exhaustive loop over all prims -- O(n_prims) per ray, so only a tiny sample
     ps = O.PortScene()
     ps.add_mesh(P, idx)
@@ -387,6 +410,7 @@ def main():
     barrier()
     # parity guard on the bench inputs themselves: device and host paths must agree bit for bit
     assert np.array_equal(h_hits.numpy().view(np.uint32), d_hits.cpu().numpy().view(np.uint32))
+    gpu_hits_np, gpu_occ_np = h_hits.numpy().copy(), h_occ.numpy().copy()      # the timed step's own results (rank's rays)
 
     times = torch.tensor([ms_total, ms_closest, ms_any, e2e_s * 1e3], dtype=torch.float64, device="cuda")
     counts = torch.tensor([n1, n2], dtype=torch.float64, device="cuda")
@@ -434,7 +458,12 @@ def main():
             line["photon_frame"] = extra
         if not args.no_cpu_baseline:
             smp = args.cpu_sample or None
-            line["cpu_baseline"] = cpu_reference_step(P, idx, rays, shadow, None, sample=smp)
+            cb = cpu_reference_step(P, idx, rays, shadow, None, sample=smp)
+            ref_hits = cb.pop("_hits", None)
+            line["cpu_baseline"] = cb
+            if ref_hits is not None:
+                # self-certifying headline: the hits of the timed step against the reference's answers for the same rays
+                line["parity"] = hit_parity(gpu_hits_np, gpu_occ_np, ref_hits)
         emit(line)
     if world > 1:
         dist.destroy_process_group()

@@ -140,6 +140,10 @@ class Context:
         if rc:
             raise B2rtError(rc, self.lib.b2rt_last_error(self.h).decode())
 
+    def last_error(self):
+        """message of the last failing or warning call (e.g. b2rt_photons_shoot giving up like pbrt does)"""
+        return self.lib.b2rt_last_error(self.h).decode()
+
     # ---- scene --------------------------------------------------------------------------------
     def add_mesh(self, P, idx, material=-1, arealight=-1):
         P = _f32(P, (-1, 3))

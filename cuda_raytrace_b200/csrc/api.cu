@@ -86,27 +86,14 @@ void b2rt_destroy(b2rt_ctx *ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
-    DevBuf *bufs[] = {&ctx->d_verts, &ctx->d_idx, &ctx->d_analytic, &ctx->d_prim_kind, &ctx->d_leaf_box,
-                      &ctx->d_scene_box, &ctx->d_keys, &ctx->d_vals, &ctx->d_keys_alt, &ctx->d_vals_alt,
-                      &ctx->d_hist, &ctx->d_bin_parent, &ctx->d_bin_child, &ctx->d_bin_box, &ctx->d_bin_flag,
-                      &ctx->d_bin_cost, &ctx->d_bin_count, &ctx->d_wide_tmp, &ctx->d_wide_flag,
-                      &ctx->d_wide_index, &ctx->d_queue_a, &ctx->d_queue_b, &ctx->d_counters,
-                      &ctx->d_wide_nodes, &ctx->d_prim_recs, &ctx->d_leaf_prims, &ctx->d_rays, &ctx->d_hits,
-                      &ctx->d_occ, &ctx->d_scan_tmp, &ctx->d_prim_material, &ctx->d_prim_light, &ctx->d_materials,
-                      &ctx->d_lights, &ctx->d_light_cdf, &ctx->d_slots, &ctx->d_cnt_c, &ctx->d_cnt_i, &ctx->d_grid_box,
-                      &ctx->d_queries, &ctx->d_q_rgb, &ctx->d_q_r2, &ctx->d_q_found, &ctx->d_q_idx,
-                      &ctx->d_samples, &ctx->d_qslots, &ctx->d_qcnt, &ctx->d_q_rgb2, &ctx->d_frame, &ctx->d_film_xy,
-                      &ctx->d_film_rgb};
-    for (PhotonMap &m : ctx->maps) {
-        m.photons.release(); m.sorted.release(); m.cell_start.release(); m.keys.release(); m.order.release(); m.pos4.release(); m.coarse.release();
-    }
-    for (DevBuf *b : bufs) b->release();
+    cudaStreamSynchronize(ctx->stream_in);
+    cudaStreamSynchronize(ctx->stream_out);
     cudaEventDestroy(ctx->ev0); cudaEventDestroy(ctx->ev1);
     cudaEventDestroy(ctx->evb0); cudaEventDestroy(ctx->evb1); cudaEventDestroy(ctx->evb_mid);
     cudaEventDestroy(ctx->ev_in); cudaEventDestroy(ctx->ev_k); cudaEventDestroy(ctx->ev_out);
     cudaStreamDestroy(ctx->stream_in); cudaStreamDestroy(ctx->stream_out);
     cudaStreamDestroy(ctx->stream);
-    delete ctx;
+    delete ctx;      // ~DevBuf frees every device buffer of the context and of its photon maps
 }
 
 const char *b2rt_last_error(b2rt_ctx *ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
@@ -266,28 +253,41 @@ static int trace_common(b2rt_ctx *ctx, int64_t nrays, const b2rt_ray *rays, b2rt
     else B2RT_CUDA(ctx, ctx->d_hits.reserve((size_t)nrays * sizeof(b2rt_hit)));
     // Chunked pipeline over three streams: the upload of chunk i+1, the traversal of chunk i and the download of
     // chunk i-1 overlap (PCIe is full duplex; with pinned caller memory the copies are asynchronous).
+    // The loop body is a lambda so that EVERY way out of it -- a failing CUDA call, a failing launch -- passes the join
+    // below: copies that still read the caller's `rays` or write its `hits` / `occ` must have drained before the
+    // caller sees the error and frees or reuses those buffers.
     const int64_t CH = ctx->host_chunk;
-    B2RT_CUDA(ctx, cudaEventRecord(ctx->ev_k, st));                 // everything queued so far on the main stream
-    B2RT_CUDA(ctx, cudaStreamWaitEvent(ctx->stream_in, ctx->ev_k, 0));
-    for (int64_t c0 = 0; c0 < nrays; c0 += CH) {
-        const int64_t cn = nrays - c0 < CH ? nrays - c0 : CH;
-        b2rt_ray *dr = ctx->d_rays.as<b2rt_ray>() + c0;
-        B2RT_CUDA(ctx, cudaMemcpyAsync(dr, rays + c0, (size_t)cn * sizeof(b2rt_ray), cudaMemcpyHostToDevice, ctx->stream_in));
-        B2RT_CUDA(ctx, cudaEventRecord(ctx->ev_in, ctx->stream_in));
-        B2RT_CUDA(ctx, cudaStreamWaitEvent(st, ctx->ev_in, 0));
-        int rc = any ? b2rt_trace_impl(ctx, cn, dr, nullptr, ctx->d_occ.as<uint8_t>() + c0, true)
-                     : b2rt_trace_impl(ctx, cn, dr, ctx->d_hits.as<b2rt_hit>() + c0, nullptr, false);
-        if (rc) return rc;
-        B2RT_CUDA(ctx, cudaEventRecord(ctx->ev_k, st));
-        B2RT_CUDA(ctx, cudaStreamWaitEvent(ctx->stream_out, ctx->ev_k, 0));
-        if (any)
-            B2RT_CUDA(ctx, cudaMemcpyAsync(occ + c0, ctx->d_occ.as<uint8_t>() + c0, (size_t)cn, cudaMemcpyDeviceToHost, ctx->stream_out));
-        else
-            B2RT_CUDA(ctx, cudaMemcpyAsync(hits + c0, ctx->d_hits.as<b2rt_hit>() + c0, (size_t)cn * sizeof(b2rt_hit),
-                                           cudaMemcpyDeviceToHost, ctx->stream_out));
+    auto pipeline = [&]() -> int {
+        B2RT_CUDA(ctx, cudaEventRecord(ctx->ev_k, st));                 // everything queued so far on the main stream
+        B2RT_CUDA(ctx, cudaStreamWaitEvent(ctx->stream_in, ctx->ev_k, 0));
+        for (int64_t c0 = 0; c0 < nrays; c0 += CH) {
+            const int64_t cn = nrays - c0 < CH ? nrays - c0 : CH;
+            b2rt_ray *dr = ctx->d_rays.as<b2rt_ray>() + c0;
+            B2RT_CUDA(ctx, cudaMemcpyAsync(dr, rays + c0, (size_t)cn * sizeof(b2rt_ray), cudaMemcpyHostToDevice, ctx->stream_in));
+            B2RT_CUDA(ctx, cudaEventRecord(ctx->ev_in, ctx->stream_in));
+            B2RT_CUDA(ctx, cudaStreamWaitEvent(st, ctx->ev_in, 0));
+            int rc = any ? b2rt_trace_impl(ctx, cn, dr, nullptr, ctx->d_occ.as<uint8_t>() + c0, true)
+                         : b2rt_trace_impl(ctx, cn, dr, ctx->d_hits.as<b2rt_hit>() + c0, nullptr, false);
+            if (rc) return rc;
+            B2RT_CUDA(ctx, cudaEventRecord(ctx->ev_k, st));
+            B2RT_CUDA(ctx, cudaStreamWaitEvent(ctx->stream_out, ctx->ev_k, 0));
+            if (any)
+                B2RT_CUDA(ctx, cudaMemcpyAsync(occ + c0, ctx->d_occ.as<uint8_t>() + c0, (size_t)cn, cudaMemcpyDeviceToHost, ctx->stream_out));
+            else
+                B2RT_CUDA(ctx, cudaMemcpyAsync(hits + c0, ctx->d_hits.as<b2rt_hit>() + c0, (size_t)cn * sizeof(b2rt_hit),
+                                               cudaMemcpyDeviceToHost, ctx->stream_out));
+        }
+        B2RT_CUDA(ctx, cudaEventRecord(ctx->ev_out, ctx->stream_out));
+        B2RT_CUDA(ctx, cudaStreamWaitEvent(st, ctx->ev_out, 0));
+        return B2RT_OK;
+    };
+    const int prc = pipeline();
+    if (prc) {
+        const std::string msg = ctx->err;
+        cudaStreamSynchronize(ctx->stream_in); cudaStreamSynchronize(st); cudaStreamSynchronize(ctx->stream_out);
+        ctx->err = msg;
+        return prc;
     }
-    B2RT_CUDA(ctx, cudaEventRecord(ctx->ev_out, ctx->stream_out));
-    B2RT_CUDA(ctx, cudaStreamWaitEvent(st, ctx->ev_out, 0));
     return check_status(ctx);
 }
 

@@ -55,6 +55,7 @@ int b2rt_photons_shoot(b2rt_ctx *ctx, int64_t n_caustic_wanted, int64_t n_indire
     int rc = b2rt_photons_clear(ctx);
     if (rc) return rc;
     int64_t first = 0;
+    bool gave_up = false;
     bool c_done = n_caustic_wanted == 0, i_done = n_indirect_wanted == 0;
     while (!(c_done && i_done)) {
         int flags = (c_done ? 0 : 1) | (i_done ? 0 : 2);
@@ -64,17 +65,23 @@ int b2rt_photons_shoot(b2rt_ctx *ctx, int64_t n_caustic_wanted, int64_t n_indire
         first += batch_paths;
         if (ctx->maps[0].n >= n_caustic_wanted) c_done = true;
         if (ctx->maps[1].n >= n_indirect_wanted) i_done = true;
-        // pbrt gives up when nothing is being stored (photonmap.cpp:527-537)
-        if (first > 500000 && ((!c_done && (ctx->maps[0].n == 0 || ctx->maps[0].n < first / 1024)) ||
-                               (!i_done && (ctx->maps[1].n == 0 || ctx->maps[1].n < first / 1024)))) {
-            ctx->err = "photons_shoot: unable to store enough photons, giving up";
-            return B2RT_E_STATE;
+        // pbrt gives up when nothing is being stored (photonmap.cpp:182-184, 526-537): after 500 000 paths a map that is
+        // still wanted and holds fewer than blockSize / 1024 = 4 photons (pbrt passes its block size, 4096, as `shot`,
+        // not the paths shot so far).  Like pbrt this is not fatal: it reports, ERASES every map and renders on
+        // without them -- a diffuse-only scene with the default causticphotons = 20000 ends up here in pbrt as well.
+        if (first > 500000 && ((!c_done && ctx->maps[0].n < 4) || (!i_done && ctx->maps[1].n < 4))) {
+            rc = b2rt_photons_clear(ctx);
+            if (rc) return rc;
+            ctx->err = "photons_shoot: unable to store enough photons, giving up (photon maps erased, as pbrt does)";
+            gave_up = true;
+            break;
         }
     }
     for (int m = 0; m < 2; ++m) {
         if (n_paths_out) n_paths_out[m] = ctx->maps[m].n_paths;
         if (n_stored_out) n_stored_out[m] = ctx->maps[m].n;
     }
+    (void)gave_up;       // reported through the counts (0 photons although some were wanted) and b2rt_last_error
     return B2RT_OK;
 }
 

@@ -11,7 +11,12 @@
 #ifndef FG_STAT
 #define FG_STAT(counter, amount)          // tests/hostemu defines it to count the work of a lookup on the host
 #endif
-struct FgGrid { float lo[3]; float cell, inv, slack; int dims[3]; int cdims[3]; int c2dims[3]; };
+// pstride / nrm: how the radiance photons are laid out for the lookup.  pstride = 2, nrm = NULL: the grid-sorted b2rt_photon
+// array itself (float4 pairs, the normal octahedral in the first one's w).  pstride = 1, nrm != NULL: the packed copies
+// fg_pack_kernel makes for the camera pass -- 16 bytes per distance test instead of a 32-byte record, and the normals
+// already decoded (fg_oct_decode + normalise were 18 % of the gather kernel's instructions, ncu r03g); same values, same bits.
+struct FgGrid { float lo[3]; float cell, inv, slack; int dims[3]; int cdims[3]; int c2dims[3]; int pstride; const float4 *nrm; };
+__host__ __device__ __forceinline__ f3 fg_photon_normal(const FgGrid &g, uint32_t i, float w);
 
 __host__ __device__ __forceinline__ f3 fg_normalize(f3 v) {      // pbrt Normalize (same arithmetic as normalize3)
     float inv = 1.f / sqrtf(v.x * v.x + v.y * v.y + v.z * v.z);
@@ -67,15 +72,19 @@ __host__ __device__ __forceinline__ uint32_t fg_f2u(float f) {
 #ifndef FG_REFINE_PASSES
 #define FG_REFINE_PASSES 1
 #endif
-__host__ __device__ __forceinline__ void fg_scan_range(const float4 *__restrict__ photons, uint32_t i0, uint32_t i1, f3 p, f3 n,
-                                                       int &best, float &best_d2) {
+__host__ __device__ __forceinline__ f3 fg_photon_normal(const FgGrid &g, uint32_t i, float w) {
+    if (g.nrm) { const float4 N = g.nrm[i]; return mk3(N.x, N.y, N.z); }
+    return fg_oct_decode(fg_f2u(w));
+}
+__host__ __device__ __forceinline__ void fg_scan_range(const FgGrid &g, const float4 *__restrict__ photons, uint32_t i0, uint32_t i1,
+                                                       f3 p, f3 n, int &best, float &best_d2) {
     FG_STAT(0, i1 - i0);
     for (uint32_t i = i0; i < i1; ++i) {
-        const float4 A = photons[2 * (size_t)i];
+        const float4 A = photons[(size_t)g.pstride * i];
         const float dx = A.x - p.x, dy = A.y - p.y, dz = A.z - p.z;
         const float d2 = dx * dx + dy * dy + dz * dz;
         if (d2 < best_d2 || (d2 == best_d2 && (int)i < best)) {
-            if (dot3(fg_oct_decode(fg_f2u(A.w)), n) > 0.f) { best = (int)i; best_d2 = d2; }
+            if (dot3(fg_photon_normal(g, i, A.w), n) > 0.f) { best = (int)i; best_d2 = d2; }
         }
     }
 }
@@ -121,8 +130,8 @@ __host__ __device__ inline void fg_nbox_level1(const FgGrid &g, const float4 *__
         for (int y = 4 * Y; y < min(4 * Y + 4, g.dims[1]); ++y) {
             const size_t row = ((size_t)z * g.dims[1] + y) * g.dims[0];
             for (uint32_t i = cell_start[row + fx0]; i < cell_start[row + fx1]; ++i) {
-                const float4 A = photons[2 * (size_t)i];
-                const f3 m = fg_oct_decode(fg_f2u(A.w));
+                const float4 A = photons[(size_t)g.pstride * i];
+                const f3 m = fg_photon_normal(g, i, A.w);
                 lo[0] = fminf(lo[0], m.x); lo[1] = fminf(lo[1], m.y); lo[2] = fminf(lo[2], m.z);
                 hi[0] = fmaxf(hi[0], m.x); hi[1] = fmaxf(hi[1], m.y); hi[2] = fmaxf(hi[2], m.z);
                 plo[0] = fminf(plo[0], A.x); plo[1] = fminf(plo[1], A.y); plo[2] = fminf(plo[2], A.z);
@@ -228,7 +237,7 @@ __host__ __device__ inline void fg_visit_level2(const FgGrid &g, const float4 *_
                         if (i0 == i1) continue;
                         if (fg_row_d2(g, pa, nbox1 + 12 * i1c + 6, fx0, fx1, y, z) > best_d2) continue;
                         FG_STAT(3, sample ? 1 : 0);
-                        fg_scan_range(photons, i0, sample ? i0 + 1u : i1, p, n, best, best_d2);
+                        fg_scan_range(g, photons, i0, sample ? i0 + 1u : i1, p, n, best, best_d2);
                     }
     }
     fg_lanes_min<NL>(best, best_d2);
@@ -270,9 +279,9 @@ __host__ __device__ inline bool fg_radiance_phase0(const FgGrid &g, const float4
                     else if (part == 0) { xa = xb = c[0] - r; if (xa < 0) continue; }
                     else { xa = xb = c[0] + r; if (xa >= g.dims[0]) continue; }
                     const uint32_t i0 = cell_start[row + xa], i1 = cell_start[row + xb + 1];
-                    if (NL == 1) fg_scan_range(photons, i0, i1, p, n, best, best_d2);
+                    if (NL == 1) fg_scan_range(g, photons, i0, i1, p, n, best, best_d2);
                     else
-                        for (uint32_t i = i0 + (uint32_t)lane; i < i1; i += NL) fg_scan_range(photons, i, i + 1u, p, n, best, best_d2);
+                        for (uint32_t i = i0 + (uint32_t)lane; i < i1; i += NL) fg_scan_range(g, photons, i, i + 1u, p, n, best, best_d2);
                 }
             }
         }
@@ -359,7 +368,7 @@ __host__ __device__ inline void fg_radiance_phase1(const FgGrid &g, const float4
     for (int pass = 0, prev = -1; sample && best >= 0 && best != prev && pass < FG_REFINE_PASSES; ++pass) {
         prev = best;
         FG_PHASE(2);
-        const float4 B = photons[2 * (size_t)best];
+        const float4 B = photons[(size_t)g.pstride * best];
         const float pb[3] = {B.x, B.y, B.z};
         int cb[3];
         for (int a = 0; a < 3; ++a) {
@@ -372,7 +381,7 @@ __host__ __device__ inline void fg_radiance_phase1(const FgGrid &g, const float4
             const int y = cb[1] - 1 + k % 3, z = cb[2] - 1 + k / 3;
             if (y < 0 || z < 0 || y >= g.dims[1] || z >= g.dims[2]) continue;
             const size_t row = ((size_t)z * g.dims[1] + y) * g.dims[0];
-            fg_scan_range(photons, cell_start[row + xa], cell_start[row + xb + 1], p, n, best, best_d2);
+            fg_scan_range(g, photons, cell_start[row + xa], cell_start[row + xb + 1], p, n, best, best_d2);
         }
         fg_lanes_min<NL>(best, best_d2);
     }

@@ -10,6 +10,17 @@
 
 struct DevBuf {
     void *p = nullptr; size_t cap = 0;
+    // owns its allocation: `delete ctx` (b2rt_destroy, with the context's device current) frees every buffer, including
+    // the ones added later -- an explicit release list in b2rt_destroy went stale once (the final-gather buffers leaked)
+    DevBuf() = default;
+    DevBuf(const DevBuf &) = delete;
+    DevBuf &operator=(const DevBuf &) = delete;
+    DevBuf(DevBuf &&o) noexcept : p(o.p), cap(o.cap) { o.p = nullptr; o.cap = 0; }
+    DevBuf &operator=(DevBuf &&o) noexcept {
+        if (this != &o) { release(); p = o.p; cap = o.cap; o.p = nullptr; o.cap = 0; }
+        return *this;
+    }
+    ~DevBuf() { release(); }
     // grow-only device buffer; returns cudaError
     cudaError_t reserve(size_t bytes) {
         if (bytes <= cap) return cudaSuccess;
@@ -64,6 +75,7 @@ struct PhotonMap {
     int64_t n_paths = 0;     // paths emitted while this map was still collecting (pbrt nCausticPaths / nIndirectPaths)
     // grid
     bool grid_built = false;
+    uint64_t grid_epoch = 0; // bumped by every grid build (tables derived from the grid check it)
     DevBuf sorted;           // b2rt_photon[n] in (cell key, path-order index) order
     DevBuf cell_start;       // uint32[n_cells+1]
     DevBuf keys, order;      // uint32[n] sorted cell keys / original indices (kept for parity downloads)
@@ -138,14 +150,15 @@ struct b2rt_ctx {
     PhotonMap maps[4];       // B2RT_MAP_CAUSTIC, B2RT_MAP_INDIRECT, B2RT_MAP_DIRECT, B2RT_MAP_RADIANCE
     // final gathering (finalgather.cu)
     int fg_enable = 0, fg_samples = 32;                 // b2rt_final_gather_set
-    int fg_variant = 0;                                 // far radiance-photon lookups of a warp's gather rays: 0 = each lane its
-                                                        // own, 1 = the 32 lanes work through them together, 2 = the 32 lanes
-                                                        // work through ALL lookups together (B2RT_FG_VARIANT); r03e / r03h on one
-                                                        // B200, 960 x 540: 345 / 392 / 409 ms per frame -> 0 is the default
+    int fg_variant = 3;                                 // 3 (default): trace / cell-sorted lookup / combine as separate launches;
+                                                        // 0: the fused warp-per-shading-point kernel (B2RT_FG_VARIANT, A/B)
     float fg_cos_angle = 0.98480775301220802f;          // cos(10 degrees)
     bool radiance_computed = false;                     // maps[3].alpha holds Lo (true) or rho_r (false)
     DevBuf d_fg_queries, d_fg_E, d_fg_Etmp, d_fg_idx, d_fg_r2, d_fg_found, d_fg_slots, d_fg_cnt, d_fg_cnt2;
     DevBuf d_fg_dirs, d_fg_pend, d_fg_pq, d_fg_pidx, d_fg_flag, d_fg_coarse2, d_fg_nbox1, d_fg_nbox2;
+    DevBuf d_fg_rpos, d_fg_rnrm;                        // packed {p, oct normal} / decoded normals of the sorted radiance photons
+    uint64_t fg_tables_epoch = 0;                       // grid_epoch of maps[3] the tables above were built for (0 = none)
+    DevBuf d_fg_rayrec, d_fg_rkeys, d_fg_rvals, d_fg_rkeys2, d_fg_rvals2, d_fg_ri;   // split gather pipeline, per gather ray
     b2rt_accel_info info{};
 };
 

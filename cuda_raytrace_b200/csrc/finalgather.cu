@@ -156,7 +156,7 @@ radiance_lo_kernel(b2rt_photon *__restrict__ rp, const float *__restrict__ E, in
 
 // ---- K17 ---------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(128)
-radiance_lookup_kernel(FgGrid g, const float4 *__restrict__ photons, const uint32_t *__restrict__ cell_start,
+radiance_lookup_kernel(FgGrid g, const float4 *__restrict__ pos, const float4 *__restrict__ photons, const uint32_t *__restrict__ cell_start,
                        const uint32_t *__restrict__ coarse1, const uint32_t *__restrict__ coarse2,
                        const float *__restrict__ nbox1, const float *__restrict__ nbox2,
                        const b2rt_query *__restrict__ queries, int64_t nq, float *__restrict__ out_rgb, int32_t *__restrict__ out_idx) {
@@ -165,7 +165,7 @@ radiance_lookup_kernel(FgGrid g, const float4 *__restrict__ photons, const uint3
     const float4 *Q = reinterpret_cast<const float4 *>(queries + q);
     const float4 q0 = Q[0], q1 = Q[1];
     float d2;
-    const int i = fg_radiance_nearest(g, photons, cell_start, coarse1, coarse2, nbox1, nbox2, mk3(q0.x, q0.y, q0.z), mk3(q0.w, q1.x, q1.y), d2);
+    const int i = fg_radiance_nearest(g, pos, cell_start, coarse1, coarse2, nbox1, nbox2, mk3(q0.x, q0.y, q0.z), mk3(q0.w, q1.x, q1.y), d2);
     if (out_idx) out_idx[q] = i;
     if (out_rgb) {
         float4 B = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -207,7 +207,8 @@ fg_scatter_kernel(const uint32_t *__restrict__ pidx, const int32_t *__restrict__
 struct FgArgs {
     DScene sc;
     FgGrid g;
-    const float4 *rad;                 // sorted radiance photons, float4 pairs
+    const float4 *rad;                 // sorted radiance photons, float4 pairs (the winner's Lo is read from here)
+    const float4 *rad_pos;             // what the lookup scans: rad itself (g.pstride 2) or the packed copy (g.pstride 1)
     const uint32_t *rad_cells, *rad_coarse1, *rad_coarse2;   // cell ranges and the two occupancy levels (4^3, 16^3 cells)
     const float *rad_nbox1, *rad_nbox2;                      // normal bounds of the two levels
     const b2rt_photon *ind;            // sorted indirect photons (directions for the cone sampling)
@@ -216,13 +217,88 @@ struct FgArgs {
     const b2rt_query *queries;
     int64_t nq;
     int gs;                            // gather rays per strategy (pbrt: gatherSamples / 2)
-    int coop;                          // lookups: 0 = per lane, 1 = far ones warp-cooperative, 2 = all of them warp-cooperative
     float cos_angle, cone_pdf;
     uint32_t k0, k1;
     float *out_rgb;
     uint32_t *status;
+    // split pipeline (default): per gather ray of the chunk
+    float4 *ray_recs;                  // [2 * nrays] {hit point, -} {facing normal of the hit, -}
+    uint32_t *ray_keys, *ray_vals;     // radiance-grid cell of the hit (n_cells = no hit) / ray index
+    int32_t *ray_ri;                   // nearest facing radiance photon of the ray's hit, -1 = none / no hit
+    uint32_t n_cells;
 };
 
+// Gather ray r of a shading point (photonmap.cpp:662-687 BSDF-sampled, :708-733 cone-sampled): lanes / rays [0, gs) sample
+// the Lambertian lobe, [gs, 2 gs) pick one of the nd photon directions and sample its cone.  Pure function of the query's
+// Philox words and r, so the trace and the combine launches of the split pipeline regenerate the very same direction.
+struct FgRay { f3 wi; float cosw; bool act, cone; };
+template <class DirOf>
+__device__ __forceinline__ FgRay fg_make_ray(uint32_t gpix, uint32_t kc, int r, int gs, int nd, f3 nf, f3 sn, f3 tn,
+                                             float cos_angle, uint32_t k0, uint32_t k1, DirOf dir_of) {
+    FgRay R;
+    R.act = r < 2 * gs;
+    R.cone = r >= gs;
+    R.wi = mk3(0.f, 0.f, 1.f);
+    R.cosw = 0.f;
+    if (R.act) {
+        const u4 u = philox4x32_10(gpix, kc, 0x200u + (uint32_t)r, 0u, k0, k1);
+        if (!R.cone) {
+            // Lambertian::Sample_f: cosine hemisphere on wo's side (= nf's side), pdf = |cos| / pi
+            const f3 l = cosine_sample_hemisphere(u01(u.x), u01(u.y));
+            R.wi = mk3(sn.x * l.x + tn.x * l.y + nf.x * l.z, sn.y * l.x + tn.y * l.y + nf.y * l.z,
+                       sn.z * l.x + tn.z * l.y + nf.z * l.z);
+            R.cosw = dot3(R.wi, nf);
+            R.act = (l.z > 0.f) && (R.cosw > 0.f);
+        } else if (nd == 0) {
+            R.act = false;
+        } else {
+            const int pn = min(nd - 1, (int)floorf(u01(u.z) * (float)nd));
+            const f3 z = dir_of(pn);
+            f3 vx, vy;
+            fg_coordinate_system(z, vx, vy);
+            R.wi = fg_sample_cone(u01(u.x), u01(u.y), cos_angle, vx, vy, z);
+            R.cosw = dot3(R.wi, nf);
+            R.act = R.cosw > 0.f;                                        // else bsdf->f(wo, wi) is black
+        }
+    }
+    return R;
+}
+// MIS-weighted contribution of one gather ray whose hit found the radiance photon with outgoing radiance Lo
+// (photonmap.cpp:689-706 / :735-754)
+__device__ __forceinline__ void fg_accumulate(const FgRay &R, f3 fr, float4 Lo, const f3 *dirs, int nd, int gs, float cos_angle,
+                                              float cone_pdf, f3 &accB, f3 &accC) {
+    const float bsdf_pdf = fabsf(R.cosw) * B2_INV_PI;
+    const float photon_pdf = fg_photon_pdf(dirs, nd, R.wi, cos_angle, cone_pdf);
+    const float absdot = fabsf(R.cosw);
+    if (!R.cone) {
+        const float wt = fg_power_heuristic(gs, bsdf_pdf, gs, photon_pdf);
+        const float w = absdot * wt / bsdf_pdf;
+        accB = accB + mk3(fr.x * Lo.x * w, fr.y * Lo.y * w, fr.z * Lo.z * w);
+    } else {
+        const float wt = fg_power_heuristic(gs, photon_pdf, gs, bsdf_pdf);
+        accC = accC + mk3(fr.x * Lo.x * absdot * wt / photon_pdf, fr.y * Lo.y * absdot * wt / photon_pdf,
+                          fr.z * Lo.z * absdot * wt / photon_pdf);
+    }
+}
+__device__ __forceinline__ void fg_warp_sum_store(f3 accB, f3 accC, int lane, int gs, float *out) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        accB.x += __shfl_xor_sync(0xffffffffu, accB.x, o); accB.y += __shfl_xor_sync(0xffffffffu, accB.y, o);
+        accB.z += __shfl_xor_sync(0xffffffffu, accB.z, o);
+        accC.x += __shfl_xor_sync(0xffffffffu, accC.x, o); accC.y += __shfl_xor_sync(0xffffffffu, accC.y, o);
+        accC.z += __shfl_xor_sync(0xffffffffu, accC.z, o);
+    }
+    if (lane == 0) {
+        const float g = (float)gs;
+        out[0] = accB.x / g + accC.x / g;
+        out[1] = accB.y / g + accC.y / g;
+        out[2] = accB.z / g + accC.z / g;
+    }
+}
+
+// B2RT_FG_VARIANT=0, the first version, kept as the A/B reference of the split pipeline below (identical bytes): one warp
+// per shading point, lane = gather ray, traversal and the radiance-photon lookup inline.  A warp's 32 lanes walk 32
+// unrelated lookups with their own trip counts: 2.9 of 32 threads active per instruction (ncu r03g), 344 ms for 960 x 540.
 __global__ void __launch_bounds__(FG_THREADS)
 final_gather_kernel(const FgArgs A) {
     __shared__ f3 s_dirs[FG_THREADS / 32][FG_NDIR];
@@ -246,121 +322,136 @@ final_gather_kernel(const FgArgs A) {
         fg_coordinate_system(nf, sn, tn);
         const f3 fr = kd * B2_INV_PI;                                    // Lambertian f, throughput folded into kd
         f3 accB = mk3(0.f, 0.f, 0.f), accC = mk3(0.f, 0.f, 0.f);
+        const f3 *dirs = s_dirs[warp];
         for (int base = 0; base < 2 * A.gs; base += 32) {
-            // no early exits in this body: with A.coop the lanes meet at the ballot below
-            const int r = base + lane;
-            bool act = r < 2 * A.gs;
-            const bool cone = r >= A.gs;
-            f3 wi = mk3(0.f, 0.f, 1.f);
-            float cosw = 0.f;
-            if (act) {
-                const u4 u = philox4x32_10(gpix, kc, 0x200u + (uint32_t)r, 0u, A.k0, A.k1);
-                if (!cone) {
-                    // Lambertian::Sample_f: cosine hemisphere on wo's side (= nf's side), pdf = |cos| / pi
-                    const f3 l = cosine_sample_hemisphere(u01(u.x), u01(u.y));
-                    wi = mk3(sn.x * l.x + tn.x * l.y + nf.x * l.z, sn.y * l.x + tn.y * l.y + nf.y * l.z,
-                             sn.z * l.x + tn.z * l.y + nf.z * l.z);
-                    cosw = dot3(wi, nf);
-                    act = (l.z > 0.f) && (cosw > 0.f);
-                } else if (nd == 0) {
-                    act = false;
-                } else {
-                    const int pn = min(nd - 1, (int)floorf(u01(u.z) * (float)nd));
-                    const f3 z = s_dirs[warp][pn];
-                    f3 vx, vy;
-                    fg_coordinate_system(z, vx, vy);
-                    wi = fg_sample_cone(u01(u.x), u01(u.y), A.cos_angle, vx, vy, z);
-                    cosw = dot3(wi, nf);
-                    act = cosw > 0.f;                                        // else bsdf->f(wo, wi) is black
-                }
-            }
-            f3 hp = mk3(0.f, 0.f, 0.f), ng = mk3(0.f, 0.f, 1.f);
-            bool hit = false;
-            if (act) {
-                HitD h;
-                hit = traverse<false>(A.sc.nodes, A.sc.recs, A.sc.analytic, p.x, p.y, p.z, wi.x, wi.y, wi.z, ray_eps, INFINITY, h,
-                                      overflow);
-                if (hit) {
-                    const Surface s = make_surface(A.sc, h, p, wi);
-                    hp = s.p;
-                    ng = dot3(s.n, -wi) < 0.f ? -s.n : s.n;                 // Faceforward(nGather, -bounceRay.d)
-                }
-            }
-            // nearest radiance photon facing the hit: the near search per lane, the far search (hits on specular objects,
-            // on surfaces no photon reached) per lane or by the whole warp, one pending lookup after the other
-            int ri = -1;
-            float d2 = INFINITY;
-            bool far = false;
-            if (A.coop == 2) {
-                // every lookup of the warp's rays by all 32 lanes, one after the other: lanes = candidate photons
-                unsigned pend = __ballot_sync(0xffffffffu, hit);
-                while (pend) {
-                    const int src = __ffs(pend) - 1;
-                    pend &= pend - 1u;
-                    const f3 qp = mk3(__shfl_sync(0xffffffffu, hp.x, src), __shfl_sync(0xffffffffu, hp.y, src),
-                                      __shfl_sync(0xffffffffu, hp.z, src));
-                    const f3 qn = mk3(__shfl_sync(0xffffffffu, ng.x, src), __shfl_sync(0xffffffffu, ng.y, src),
-                                      __shfl_sync(0xffffffffu, ng.z, src));
-                    int b;
-                    float bd2;
-                    if (!fg_radiance_phase0<32>(A.g, A.rad, A.rad_cells, qp, qn, lane, b, bd2))
-                        fg_radiance_phase1<32>(A.g, A.rad, A.rad_cells, A.rad_coarse1, A.rad_coarse2, A.rad_nbox1, A.rad_nbox2, qp,
-                                               qn, lane, b, bd2);
-                    if (lane == src) { ri = b; d2 = bd2; }
-                }
-            } else if (hit) far = !fg_radiance_phase0<1>(A.g, A.rad, A.rad_cells, hp, ng, 0, ri, d2);
-            if (A.coop == 2) {
-            } else if (A.coop) {
-                unsigned pend = __ballot_sync(0xffffffffu, far);
-                while (pend) {
-                    const int src = __ffs(pend) - 1;
-                    pend &= pend - 1u;
-                    const f3 qp = mk3(__shfl_sync(0xffffffffu, hp.x, src), __shfl_sync(0xffffffffu, hp.y, src),
-                                      __shfl_sync(0xffffffffu, hp.z, src));
-                    const f3 qn = mk3(__shfl_sync(0xffffffffu, ng.x, src), __shfl_sync(0xffffffffu, ng.y, src),
-                                      __shfl_sync(0xffffffffu, ng.z, src));
-                    int b = __shfl_sync(0xffffffffu, ri, src);
-                    float bd2 = __shfl_sync(0xffffffffu, d2, src);
-                    fg_radiance_phase1<32>(A.g, A.rad, A.rad_cells, A.rad_coarse1, A.rad_coarse2, A.rad_nbox1, A.rad_nbox2, qp, qn,
-                                           lane, b, bd2);
-                    if (lane == src) { ri = b; d2 = bd2; }
-                }
-            } else if (far) {
-                fg_radiance_phase1<1>(A.g, A.rad, A.rad_cells, A.rad_coarse1, A.rad_coarse2, A.rad_nbox1, A.rad_nbox2, hp, ng, 0, ri,
-                                      d2);
-            }
-            if (hit && ri >= 0) {
-                const float4 Lo = __ldg(A.rad + 2 * (size_t)ri + 1);
-                const float bsdf_pdf = fabsf(cosw) * B2_INV_PI;
-                const float photon_pdf = fg_photon_pdf(s_dirs[warp], nd, wi, A.cos_angle, A.cone_pdf);
-                const float absdot = fabsf(cosw);
-                if (!cone) {
-                    const float wt = fg_power_heuristic(A.gs, bsdf_pdf, A.gs, photon_pdf);
-                    const float w = absdot * wt / bsdf_pdf;
-                    accB = accB + mk3(fr.x * Lo.x * w, fr.y * Lo.y * w, fr.z * Lo.z * w);
-                } else {
-                    const float wt = fg_power_heuristic(A.gs, photon_pdf, A.gs, bsdf_pdf);
-                    accC = accC + mk3(fr.x * Lo.x * absdot * wt / photon_pdf, fr.y * Lo.y * absdot * wt / photon_pdf,
-                                      fr.z * Lo.z * absdot * wt / photon_pdf);
-                }
-            }
+            const FgRay R = fg_make_ray(__float_as_uint(q2.z), kc, base + lane, A.gs, nd, nf, sn, tn, A.cos_angle, A.k0, A.k1,
+                                        [dirs](int pn) { return dirs[pn]; });
+            (void)gpix;
+            if (!R.act) continue;
+            HitD h;
+            if (!traverse<false>(A.sc.nodes, A.sc.recs, A.sc.analytic, p.x, p.y, p.z, R.wi.x, R.wi.y, R.wi.z, ray_eps, INFINITY, h,
+                                 overflow))
+                continue;
+            const Surface s = make_surface(A.sc, h, p, R.wi);
+            const f3 ng = dot3(s.n, -R.wi) < 0.f ? -s.n : s.n;          // Faceforward(nGather, -bounceRay.d)
+            float d2;
+            const int ri = fg_radiance_nearest(A.g, A.rad_pos, A.rad_cells, A.rad_coarse1, A.rad_coarse2, A.rad_nbox1, A.rad_nbox2,
+                                               s.p, ng, d2);
+            if (ri >= 0)
+                fg_accumulate(R, fr, __ldg(A.rad + 2 * (size_t)ri + 1), dirs, nd, A.gs, A.cos_angle, A.cone_pdf, accB, accC);
         }
         __syncwarp();
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            accB.x += __shfl_xor_sync(0xffffffffu, accB.x, o); accB.y += __shfl_xor_sync(0xffffffffu, accB.y, o);
-            accB.z += __shfl_xor_sync(0xffffffffu, accB.z, o);
-            accC.x += __shfl_xor_sync(0xffffffffu, accC.x, o); accC.y += __shfl_xor_sync(0xffffffffu, accC.y, o);
-            accC.z += __shfl_xor_sync(0xffffffffu, accC.z, o);
-        }
-        if (lane == 0) {
-            const float g = (float)A.gs;
-            A.out_rgb[3 * q] = accB.x / g + accC.x / g;
-            A.out_rgb[3 * q + 1] = accB.y / g + accC.y / g;
-            A.out_rgb[3 * q + 2] = accB.z / g + accC.z / g;
-        }
+        fg_warp_sum_store(accB, accC, lane, A.gs, A.out_rgb + 3 * q);
     }
     if (overflow) atomicAdd(A.status, 1u);
+}
+
+// ---- the split pipeline (default): trace -> sort the hits by radiance-grid cell -> lookup -> combine -------------------------
+// What bounded the fused kernel was not memory but divergent issue: the lanes of a warp were the gather rays of one shading
+// point, their hits land all over the scene, and every lane ran its own shell walk.  Here the lookups are a launch of their
+// own over the hits SORTED BY THE CELL THEY FALL IN (K2): the lanes of a warp start in the same or neighbouring cells, walk
+// the same rows with the same trip counts and read the same photons (L1).  Every ray's arithmetic is unchanged, and the
+// combine launch sums in the same butterfly order, so the output is bit-identical to the fused kernel (tested).
+//
+// launch 1: one thread per gather ray (ray i of the chunk = query i / R, ray i % R): direction, traversal, hit record
+__global__ void __launch_bounds__(FG_THREADS)
+fg_trace_kernel(const FgArgs A, int64_t nrays, int R) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nrays) return;
+    const int64_t q = i / R;
+    const int r = (int)(i - q * R);
+    const float4 *Q = reinterpret_cast<const float4 *>(A.queries + q);
+    const float4 q0 = __ldg(Q), q1 = __ldg(Q + 1), q2 = __ldg(Q + 2);
+    const f3 p = mk3(q0.x, q0.y, q0.z), nf = mk3(q0.w, q1.x, q1.y);
+    const int nd = min(A.found[q], FG_NDIR);
+    f3 sn, tn;
+    fg_coordinate_system(nf, sn, tn);
+    const int32_t *qidx = A.idx + q * FG_NDIR;
+    const b2rt_photon *ind = A.ind;
+    const FgRay Ry = fg_make_ray(__float_as_uint(q2.z), __float_as_uint(q2.w), r, A.gs, nd, nf, sn, tn, A.cos_angle, A.k0, A.k1,
+                                 [qidx, ind](int pn) {
+                                     return fg_oct_decode(__float_as_uint(__ldg(reinterpret_cast<const float4 *>(ind + __ldg(qidx + pn))).w));
+                                 });
+    uint32_t key = A.n_cells;
+    bool overflow = false;
+    if (Ry.act) {
+        HitD h;
+        if (traverse<false>(A.sc.nodes, A.sc.recs, A.sc.analytic, p.x, p.y, p.z, Ry.wi.x, Ry.wi.y, Ry.wi.z, q2.y, INFINITY, h, overflow)) {
+            const Surface s = make_surface(A.sc, h, p, Ry.wi);
+            const f3 ng = dot3(s.n, -Ry.wi) < 0.f ? -s.n : s.n;          // Faceforward(nGather, -bounceRay.d)
+            A.ray_recs[2 * i] = make_float4(s.p.x, s.p.y, s.p.z, 0.f);
+            A.ray_recs[2 * i + 1] = make_float4(ng.x, ng.y, ng.z, 0.f);
+            // the fine cell the lookup starts from (fg_radiance_phase0 clamps the same way)
+            const float pa[3] = {s.p.x, s.p.y, s.p.z};
+            int c[3];
+            for (int a = 0; a < 3; ++a) {
+                float f = floorf((pa[a] - A.g.lo[a]) * A.g.inv);
+                f = fminf(fmaxf(f, 0.f), (float)(A.g.dims[a] - 1));
+                c[a] = (int)f;
+            }
+            key = ((uint32_t)c[2] * (uint32_t)A.g.dims[1] + (uint32_t)c[1]) * (uint32_t)A.g.dims[0] + (uint32_t)c[0];
+        }
+    }
+    A.ray_keys[i] = key;
+    A.ray_vals[i] = (uint32_t)i;
+    A.ray_ri[i] = -1;
+    if (overflow) atomicAdd(A.status, 1u);
+}
+// launch 2: thread j = the j-th hit in cell order
+__global__ void __launch_bounds__(FG_THREADS)
+fg_lookup_kernel(const FgArgs A, const uint32_t *__restrict__ keys, const uint32_t *__restrict__ vals, int64_t nrays) {
+    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= nrays || keys[j] >= A.n_cells) return;       // misses sort to the end
+    const uint32_t i = vals[j];
+    const float4 P = A.ray_recs[2 * (size_t)i], N = A.ray_recs[2 * (size_t)i + 1];
+    float d2;
+    A.ray_ri[i] = fg_radiance_nearest(A.g, A.rad_pos, A.rad_cells, A.rad_coarse1, A.rad_coarse2, A.rad_nbox1, A.rad_nbox2,
+                                      mk3(P.x, P.y, P.z), mk3(N.x, N.y, N.z), d2);
+}
+// launch 3: one warp per shading point, lane = gather ray, in the fused kernel's order
+__global__ void __launch_bounds__(FG_THREADS)
+fg_combine_kernel(const FgArgs A) {
+    __shared__ f3 s_dirs[FG_THREADS / 32][FG_NDIR];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t wstride = (int64_t)gridDim.x * (FG_THREADS / 32);
+    const int R = 2 * A.gs;
+    for (int64_t q = (int64_t)blockIdx.x * (FG_THREADS / 32) + warp; q < A.nq; q += wstride) {
+        const float4 *Q = reinterpret_cast<const float4 *>(A.queries + q);
+        const float4 q0 = __ldg(Q), q1 = __ldg(Q + 1), q2 = __ldg(Q + 2);
+        const f3 nf = mk3(q0.w, q1.x, q1.y), kd = mk3(q1.z, q1.w, q2.x);
+        const int nd = min(A.found[q], FG_NDIR);
+        __syncwarp();
+        for (int j = lane; j < nd; j += 32) {
+            const int32_t i = A.idx[q * FG_NDIR + j];
+            s_dirs[warp][j] = fg_oct_decode(__float_as_uint(__ldg(reinterpret_cast<const float4 *>(A.ind + i)).w));
+        }
+        __syncwarp();
+        f3 sn, tn;
+        fg_coordinate_system(nf, sn, tn);
+        const f3 fr = kd * B2_INV_PI;
+        f3 accB = mk3(0.f, 0.f, 0.f), accC = mk3(0.f, 0.f, 0.f);
+        const f3 *dirs = s_dirs[warp];
+        for (int base = 0; base < R; base += 32) {
+            const int r = base + lane;
+            const int ri = r < R ? A.ray_ri[q * R + r] : -1;
+            if (ri < 0) continue;
+            const FgRay Ry = fg_make_ray(__float_as_uint(q2.z), __float_as_uint(q2.w), r, A.gs, nd, nf, sn, tn, A.cos_angle, A.k0,
+                                         A.k1, [dirs](int pn) { return dirs[pn]; });
+            fg_accumulate(Ry, fr, __ldg(A.rad + 2 * (size_t)ri + 1), dirs, nd, A.gs, A.cos_angle, A.cone_pdf, accB, accC);
+        }
+        __syncwarp();
+        fg_warp_sum_store(accB, accC, lane, A.gs, A.out_rgb + 3 * q);
+    }
+}
+// packed copies of the sorted radiance photons for the lookups: {p, oct normal} and the decoded normal
+__global__ void __launch_bounds__(256)
+fg_pack_kernel(const float4 *__restrict__ sorted, int64_t n, float4 *__restrict__ pos, float4 *__restrict__ nrm) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 A = sorted[2 * i];
+    const f3 m = fg_oct_decode(__float_as_uint(A.w));
+    pos[i] = A;
+    nrm[i] = make_float4(m.x, m.y, m.z, 0.f);
 }
 
 // search tables of the radiance-photon grid: normal and position bounds per level-1 cell (4^3 fine cells), then count + normal bounds
@@ -392,25 +483,40 @@ FgGrid fg_grid_of(const PhotonMap &m) {
     }
     g.cell = m.grid.cell_size; g.inv = m.grid.inv_cell;
     g.slack = 1e-5f * mx + 1e-4f * m.grid.cell_size;
+    g.pstride = 2; g.nrm = nullptr;
     return g;
 }
 
 }  // namespace
 
-// the search tables of the radiance-photon grid (rebuilt per call: one pass over the radiance photons' first 16 bytes, a
-// fraction of a millisecond, and the grid may have been rebuilt through b2rt_photon_grid_build since)
-static int fg_prepare_radiance(b2rt_ctx *ctx, const FgGrid &g) {
+// The lookup's view of the radiance-photon grid: packed positions + decoded normals (fg_pack_kernel) and the search tables
+// of the two coarse levels.  Built once per grid build (grid_epoch), not per call: a frame runs the gather chunk by chunk.
+// On return g describes the packed layout and *pos points at the array the lookups scan.
+static int fg_prepare_radiance(b2rt_ctx *ctx, FgGrid &g, const float4 **pos) {
     PhotonMap &mr = ctx->maps[B2RT_MAP_RADIANCE];
     const int n1 = g.cdims[0] * g.cdims[1] * g.cdims[2], n2 = g.c2dims[0] * g.c2dims[1] * g.c2dims[2];
-    B2RT_CUDA(ctx, ctx->d_fg_nbox1.reserve((size_t)n1 * 48));
-    B2RT_CUDA(ctx, ctx->d_fg_nbox2.reserve((size_t)n2 * 48));
-    B2RT_CUDA(ctx, ctx->d_fg_coarse2.reserve((size_t)n2 * 4));
-    fg_nbox1_kernel<<<(n1 + 127) / 128, 128, 0, ctx->stream>>>(g, mr.sorted.as<float4>(), mr.cell_start.as<uint32_t>(),
-                                                               ctx->d_fg_nbox1.as<float>());
+    const bool fresh = ctx->fg_tables_epoch != mr.grid_epoch || mr.grid_epoch == 0;
+    if (fresh) {
+        B2RT_CUDA(ctx, ctx->d_fg_rpos.reserve((size_t)std::max<int64_t>(mr.n, 1) * 16));
+        B2RT_CUDA(ctx, ctx->d_fg_rnrm.reserve((size_t)std::max<int64_t>(mr.n, 1) * 16));
+        B2RT_CUDA(ctx, ctx->d_fg_nbox1.reserve((size_t)n1 * 48));
+        B2RT_CUDA(ctx, ctx->d_fg_nbox2.reserve((size_t)n2 * 48));
+        B2RT_CUDA(ctx, ctx->d_fg_coarse2.reserve((size_t)n2 * 4));
+    }
+    g.pstride = 1; g.nrm = ctx->d_fg_rnrm.as<float4>();
+    *pos = ctx->d_fg_rpos.as<float4>();
+    if (!fresh) return B2RT_OK;
+    if (mr.n > 0) {
+        fg_pack_kernel<<<(unsigned)((mr.n + 255) / 256), 256, 0, ctx->stream>>>(mr.sorted.as<float4>(), mr.n, ctx->d_fg_rpos.as<float4>(),
+                                                                                ctx->d_fg_rnrm.as<float4>());
+        B2RT_LAUNCH_CHECK(ctx);
+    }
+    fg_nbox1_kernel<<<(n1 + 127) / 128, 128, 0, ctx->stream>>>(g, *pos, mr.cell_start.as<uint32_t>(), ctx->d_fg_nbox1.as<float>());
     B2RT_LAUNCH_CHECK(ctx);
     fg_level2_kernel<<<(n2 + 127) / 128, 128, 0, ctx->stream>>>(g, ctx->d_fg_nbox1.as<float>(), mr.coarse.as<uint32_t>(),
                                                                 ctx->d_fg_nbox2.as<float>(), ctx->d_fg_coarse2.as<uint32_t>());
     B2RT_LAUNCH_CHECK(ctx);
+    ctx->fg_tables_epoch = mr.grid_epoch;
     return B2RT_OK;
 }
 
@@ -513,11 +619,12 @@ int b2rt_radiance_compute_impl(b2rt_ctx *ctx, int nused, float max_dist2) {
 int b2rt_radiance_lookup_impl(b2rt_ctx *ctx, int64_t nq, const b2rt_query *d_queries, float *d_rgb, int32_t *d_idx) {
     PhotonMap &mr = ctx->maps[B2RT_MAP_RADIANCE];
     if (nq <= 0) return B2RT_OK;
-    const FgGrid g = fg_grid_of(mr);
-    int rc = fg_prepare_radiance(ctx, g);
+    FgGrid g = fg_grid_of(mr);
+    const float4 *pos = nullptr;
+    int rc = fg_prepare_radiance(ctx, g, &pos);
     if (rc) return rc;
     radiance_lookup_kernel<<<(unsigned)((nq + 127) / 128), 128, 0, ctx->stream>>>(
-        g, mr.sorted.as<float4>(), mr.cell_start.as<uint32_t>(), mr.coarse.as<uint32_t>(), ctx->d_fg_coarse2.as<uint32_t>(),
+        g, pos, mr.sorted.as<float4>(), mr.cell_start.as<uint32_t>(), mr.coarse.as<uint32_t>(), ctx->d_fg_coarse2.as<uint32_t>(),
         ctx->d_fg_nbox1.as<float>(), ctx->d_fg_nbox2.as<float>(), d_queries, nq, d_rgb, d_idx);
     B2RT_LAUNCH_CHECK(ctx);
     return B2RT_OK;
@@ -569,21 +676,56 @@ int b2rt_final_gather_impl(b2rt_ctx *ctx, int64_t nq, const b2rt_query *d_querie
     FgArgs A;
     b2rt_fill_dscene(ctx, &A.sc);
     A.g = fg_grid_of(mr);
-    rc = fg_prepare_radiance(ctx, A.g);
+    rc = fg_prepare_radiance(ctx, A.g, &A.rad_pos);
     if (rc) return rc;
     A.rad = mr.sorted.as<float4>(); A.rad_cells = mr.cell_start.as<uint32_t>();
     A.rad_coarse1 = mr.coarse.as<uint32_t>(); A.rad_coarse2 = ctx->d_fg_coarse2.as<uint32_t>();
     A.rad_nbox1 = ctx->d_fg_nbox1.as<float>(); A.rad_nbox2 = ctx->d_fg_nbox2.as<float>();
-    A.ind = mi.sorted.as<b2rt_photon>(); A.idx = idx; A.found = found; A.queries = d_queries; A.nq = nq;
+    A.ind = mi.sorted.as<b2rt_photon>();
     A.gs = std::max(1, ctx->fg_samples / 2);
-    A.coop = (ctx->fg_variant == 1 || ctx->fg_variant == 2) ? ctx->fg_variant : 0;
     A.cos_angle = ctx->fg_cos_angle; A.cone_pdf = fg_cone_pdf(ctx->fg_cos_angle);
     A.k0 = (uint32_t)ctx->seed ^ 0x46475448u; A.k1 = (uint32_t)(ctx->seed >> 32);      // 'FGTH' stream
-    A.out_rgb = d_rgb; A.status = counters + 8;
-    int64_t blocks = (nq + FG_THREADS / 32 - 1) / (FG_THREADS / 32);
+    A.status = counters + 8;
+    A.ray_recs = nullptr; A.ray_keys = A.ray_vals = nullptr; A.ray_ri = nullptr;
+    A.n_cells = (uint32_t)mr.grid.n_cells;
     const int64_t cap = (int64_t)ctx->sm_count * 8;
-    if (blocks > cap) blocks = cap;
-    final_gather_kernel<<<(unsigned)blocks, FG_THREADS, 0, st>>>(A);
-    B2RT_LAUNCH_CHECK(ctx);
+    if (ctx->fg_variant == 0) {
+        A.idx = idx; A.found = found; A.queries = d_queries; A.nq = nq; A.out_rgb = d_rgb;
+        int64_t blocks = std::min(cap, (nq + FG_THREADS / 32 - 1) / (FG_THREADS / 32));
+        final_gather_kernel<<<(unsigned)blocks, FG_THREADS, 0, st>>>(A);
+        B2RT_LAUNCH_CHECK(ctx);
+        return B2RT_OK;
+    }
+    // split pipeline, in chunks of at most 2^26 gather rays (2 GB of hit records + 1.3 GB of sort buffers and results)
+    const int R = 2 * A.gs;
+    const int64_t cq = std::max<int64_t>(1, std::min<int64_t>(nq, (1ll << 26) / R));
+    const int64_t cr = cq * R;
+    B2RT_CUDA(ctx, ctx->d_fg_rayrec.reserve((size_t)cr * 32));
+    B2RT_CUDA(ctx, ctx->d_fg_rkeys.reserve((size_t)cr * 4));
+    B2RT_CUDA(ctx, ctx->d_fg_rvals.reserve((size_t)cr * 4));
+    B2RT_CUDA(ctx, ctx->d_fg_rkeys2.reserve((size_t)cr * 4));
+    B2RT_CUDA(ctx, ctx->d_fg_rvals2.reserve((size_t)cr * 4));
+    B2RT_CUDA(ctx, ctx->d_fg_ri.reserve((size_t)cr * 4));
+    A.ray_recs = ctx->d_fg_rayrec.as<float4>(); A.ray_keys = ctx->d_fg_rkeys.as<uint32_t>();
+    A.ray_vals = ctx->d_fg_rvals.as<uint32_t>(); A.ray_ri = ctx->d_fg_ri.as<int32_t>();
+    int key_bits = 1;
+    while (key_bits < 32 && (1ull << key_bits) <= (uint64_t)A.n_cells) ++key_bits;     // keys 0 .. n_cells inclusive
+    for (int64_t q0 = 0; q0 < nq; q0 += cq) {
+        const int64_t n = std::min<int64_t>(cq, nq - q0), nrays = n * R;
+        A.idx = idx + q0 * k; A.found = found + q0; A.queries = d_queries + q0; A.nq = n; A.out_rgb = d_rgb + 3 * q0;
+        fg_trace_kernel<<<(unsigned)((nrays + FG_THREADS - 1) / FG_THREADS), FG_THREADS, 0, st>>>(A, nrays, R);
+        B2RT_LAUNCH_CHECK(ctx);
+        bool in_alt = false;
+        rc = b2rt_sort_pairs_impl(ctx, nrays, A.ray_keys, A.ray_vals, ctx->d_fg_rkeys2.as<uint32_t>(), ctx->d_fg_rvals2.as<uint32_t>(),
+                                  key_bits, &in_alt);
+        if (rc) return rc;
+        const uint32_t *sk = in_alt ? ctx->d_fg_rkeys2.as<uint32_t>() : A.ray_keys;
+        const uint32_t *sv = in_alt ? ctx->d_fg_rvals2.as<uint32_t>() : A.ray_vals;
+        fg_lookup_kernel<<<(unsigned)((nrays + FG_THREADS - 1) / FG_THREADS), FG_THREADS, 0, st>>>(A, sk, sv, nrays);
+        B2RT_LAUNCH_CHECK(ctx);
+        int64_t blocks = std::min(cap, (n + FG_THREADS / 32 - 1) / (FG_THREADS / 32));
+        fg_combine_kernel<<<(unsigned)blocks, FG_THREADS, 0, st>>>(A);
+        B2RT_LAUNCH_CHECK(ctx);
+    }
     return B2RT_OK;
 }

@@ -538,5 +538,6 @@ int b2rt_photon_grid_build_impl(b2rt_ctx *ctx, int map, float cell_size, float t
     B2RT_CUDA(ctx, cudaEventSynchronize(ctx->evb1));
     B2RT_CUDA(ctx, cudaEventElapsedTime(&m.grid.build_ms, ctx->evb0, ctx->evb1));
     m.grid_built = true;
+    ++m.grid_epoch;
     return B2RT_OK;
 }

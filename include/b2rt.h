@@ -127,7 +127,10 @@ typedef struct {
 int b2rt_photons_trace(b2rt_ctx *ctx, int64_t first_path, int64_t n_paths, int32_t max_depth, int32_t flags,
                        int64_t n_stored[2]);
 /* pbrt's stopping rule (photonmap.cpp:521-576): shoot batches of `batch_paths` until each map holds at least the
- * wanted number of photons; a map stops collecting (and stops counting paths) once it is full. */
+ * wanted number of photons; a map stops collecting (and stops counting paths) once it is full.  pbrt's give-up rule
+ * (:182-184, :526-537) too: after 500 000 paths a wanted map that holds fewer than 4 photons ends the shooting, ALL maps
+ * are erased and the call still returns B2RT_OK -- n_stored_out is {0, 0} and b2rt_last_error() has the message; the
+ * frame then renders without photon maps, which is what pbrt does (e.g. a diffuse-only scene with causticphotons > 0). */
 int b2rt_photons_shoot(b2rt_ctx *ctx, int64_t n_caustic_wanted, int64_t n_indirect_wanted, int32_t max_depth,
                        int64_t batch_paths, int64_t n_paths_out[2], int64_t n_stored_out[2]);
 int b2rt_photons_clear(b2rt_ctx *ctx);

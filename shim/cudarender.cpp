@@ -381,6 +381,8 @@ void PhotonMappingRenderer::render(const Scene *scene, CudaRender *cr, Camera *c
         int64_t paths[2], stored[2];
         int64_t batch = 65536;
         cr->check(b2rt_photons_shoot(ctx, nCaustic, nIndirect, maxPhotonDepth, batch, paths, stored), "b2rt_photons_shoot");
+        if (stored[0] == 0 && stored[1] == 0)     // pbrt's give-up (photonmap.cpp:526-537): report, render without photon maps
+            Error("Unable to store enough photons.  Giving up.\n");
         for (int m = 0; m < 2; ++m) cr->check(b2rt_photon_grid_build(ctx, m, 0.f, 0.f), "b2rt_photon_grid_build");
         Info("CudaRender: %lld caustic photons from %lld paths, %lld indirect photons from %lld paths",
              (long long)stored[0], (long long)paths[0], (long long)stored[1], (long long)paths[1]);

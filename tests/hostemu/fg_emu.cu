@@ -19,10 +19,24 @@ extern "C" {
 // grid: lo[3], cell, inv, slack, dims[3];  photons: b2rt_photon[n] in grid order;  queries: 12 floats each
 // coarse1: photons per 4^3 fine cells (the grid's own coarse table), dims (d + 3) / 4, row-major x fastest.  The level-2
 // counts and both levels' normal bounds are built here with the functions the device kernels call.
-void emu_radiance_nearest(const float *lo, float cell, float inv, float slack, const int *dims, const void *photons,
-                          const uint32_t *cell_start, const uint32_t *coarse1, long long nq, const float *queries,
-                          int *idx_out, float *d2_out) {
+// packed != 0: run the lookup over the packed position array + decoded normals (the layout the camera pass uses)
+// instead of the sorted photon records; the answer must not change.
+void emu_radiance_nearest_layout(const float *lo, float cell, float inv, float slack, const int *dims, const void *photons_in,
+                                 const uint32_t *cell_start, const uint32_t *coarse1, long long nq, const float *queries,
+                                 int *idx_out, float *d2_out, long long n_photons, int packed) {
     FgGrid g;
+    g.pstride = 2; g.nrm = nullptr;
+    const void *photons = photons_in;
+    float4 *pos = nullptr, *nrm = nullptr;
+    if (packed) {
+        pos = new float4[n_photons > 0 ? n_photons : 1]; nrm = new float4[n_photons > 0 ? n_photons : 1];
+        for (long long i = 0; i < n_photons; ++i) {
+            pos[i] = ((const float4 *)photons_in)[2 * i];
+            const f3 m = fg_oct_decode(fg_f2u(pos[i].w));
+            nrm[i] = make_float4(m.x, m.y, m.z, 0.f);
+        }
+        g.pstride = 1; g.nrm = nrm; photons = pos;
+    }
     for (int a = 0; a < 3; ++a) {
         g.lo[a] = lo[a]; g.dims[a] = dims[a]; g.cdims[a] = (dims[a] + 3) / 4; g.c2dims[a] = (g.cdims[a] + 3) / 4;
     }
@@ -44,6 +58,12 @@ void emu_radiance_nearest(const float *lo, float cell, float inv, float slack, c
         if (d2_out) d2_out[q] = d2;
     }
     delete[] nbox1; delete[] nbox2; delete[] coarse2;
+    delete[] pos; delete[] nrm;
+}
+void emu_radiance_nearest(const float *lo, float cell, float inv, float slack, const int *dims, const void *photons,
+                          const uint32_t *cell_start, const uint32_t *coarse1, long long nq, const float *queries,
+                          int *idx_out, float *d2_out) {
+    emu_radiance_nearest_layout(lo, cell, inv, slack, dims, photons, cell_start, coarse1, nq, queries, idx_out, d2_out, 0, 0);
 }
 // distance tests per phase of the lookup: fine shells, sampling sweep, refinement around the sampled winner, exact sweep
 void emu_phase_tests(unsigned long long *out, int reset) {

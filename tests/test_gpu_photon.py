@@ -91,6 +91,34 @@ def test_shoot_follows_pbrt_stopping_rule(pctx):
     assert abs(nc / pc / gold["pbrt_caustic_per_path"] - 1) < 0.15
 
 
+def test_shoot_gives_up_like_pbrt(built):
+    """pbrt's unsuccessful() (photonmap.cpp:182-184, 526-537): after 500 000 paths a wanted map with fewer than
+    blockSize / 1024 = 4 photons ends the shooting and every map is erased -- no error, the frame renders without maps.
+    A diffuse-only scene can never store a caustic photon; a scene with sparse caustics must NOT give up."""
+    with b2rt.Context(0, seed=G.SEED) as c:
+        S.fill_scene(c, S.cornell_scene(spheres=False, boxes=True))
+        c.build_accel()
+        (pc, pi), (nc, ni) = c.photons_shoot(1000, 10_000_000, batch_paths=262144)
+        assert (nc, ni) == (0, 0) and "giving up" in c.last_error()
+        assert c.photons_count(1)[0] == 0
+        cam = b2rt.pbrt_camera((0, 1, 3.4), (0, 1, 0), (0, 1, 0), 40, 16, 16)
+        img = c.render_frame(cam, spp=1, nused=20, max_dist=0.3)          # still renders (direct lighting only)
+        assert np.isfinite(img).all() and img.max() > 0
+        # without a caustic request the same scene fills its indirect map
+        (pc, pi), (nc, ni) = c.photons_shoot(0, 20000, batch_paths=65536)
+        assert nc == 0 and ni >= 20000
+    with b2rt.Context(0, seed=G.SEED) as c:
+        # a tiny glass ball: a few caustic photons per 100 000 paths -- pbrt keeps shooting (>= 4 stored), so must we;
+        # the old rule (photons < paths shot / 1024) stopped here
+        desc = S.cornell_scene(spheres=False)
+        desc["shapes"].insert(5, ("sphere", *S.xf_translate(0.0, 0.03, 0.0), 0.03, 3))
+        desc["lights"] = [("disk", 6, (17.0, 12.0, 4.0), 4)]
+        S.fill_scene(c, desc)
+        c.build_accel()
+        (pc, pi), (nc, ni) = c.photons_shoot(40, 1000, batch_paths=262144)
+        assert nc >= 40 and pc > 500000 and nc < pc // 1024
+
+
 @pytest.mark.parametrize("cell", [0.0, 0.05, 0.3])
 def test_grid_bit_exact(pctx, oracle_photons, cell):
     pctx.photons_clear()

@@ -38,6 +38,8 @@ def emu():
     vp, f = C.c_void_p, C.c_float
     lib.emu_radiance_nearest.argtypes = [vp, f, f, f, vp, vp, vp, vp, C.c_longlong, vp, vp, vp]
     lib.emu_radiance_nearest.restype = None
+    lib.emu_radiance_nearest_layout.argtypes = [vp, f, f, f, vp, vp, vp, vp, C.c_longlong, vp, vp, vp, C.c_longlong, C.c_int]
+    lib.emu_radiance_nearest_layout.restype = None
     lib.emu_cone_pdf.argtypes = [f]
     lib.emu_cone_pdf.restype = f
     lib.emu_sample_cone.argtypes = [f, f, f, vp, vp]
@@ -115,7 +117,7 @@ def _occupancy(cell_start, dims):
     return np.ascontiguousarray(c1, np.uint32), np.ascontiguousarray(c2, np.uint32)
 
 
-def _emu_nearest(emu, g, queries, slack=None):
+def _emu_nearest(emu, g, queries, slack=None, packed=False):
     lo, dims = np.asarray(g["origin"], np.float32), np.asarray(g["dims"], np.int32)
     hi = lo + dims * np.float32(g["cell_size"])
     if slack is None:
@@ -125,8 +127,9 @@ def _emu_nearest(emu, g, queries, slack=None):
     q = np.ascontiguousarray(queries, np.float32)
     idx, d2 = np.zeros(len(q), np.int32), np.zeros(len(q), np.float32)
     c1, _ = _occupancy(cs, dims)
-    emu.emu_radiance_nearest(lo.ctypes.data, g["cell_size"], g["inv_cell"], slack, dims.ctypes.data, srt.ctypes.data,
-                             cs.ctypes.data, c1.ctypes.data, len(q), q.ctypes.data, idx.ctypes.data, d2.ctypes.data)
+    emu.emu_radiance_nearest_layout(lo.ctypes.data, g["cell_size"], g["inv_cell"], slack, dims.ctypes.data, srt.ctypes.data,
+                                    cs.ctypes.data, c1.ctypes.data, len(q), q.ctypes.data, idx.ctypes.data, d2.ctypes.data,
+                                    len(srt), 1 if packed else 0)
     return idx, d2
 
 
@@ -141,6 +144,16 @@ def test_device_shell_search_equals_brute_force(emu, fg, target):
     q[-40:-20, 0:3] = g["origin"] + np.float32(g["cell_size"]) * np.arange(20)[:, None].astype(np.float32)   # on cell faces
     idx, _ = _emu_nearest(emu, g, q)
     _, ref = O.radiance_lookup(g["sorted"], q)
+    assert np.array_equal(idx, ref)
+
+
+def test_packed_layout_returns_the_same_photon(emu, fg):
+    """The camera pass searches packed copies (16-byte positions + decoded normals) instead of the sorted records."""
+    _, rad = fg
+    g = O.grid_build(rad, 0.0, 1.0)
+    q = np.ascontiguousarray(F.lookup_queries(400, seed=21), np.float32)
+    ref, _ = _emu_nearest(emu, g, q)
+    idx, _ = _emu_nearest(emu, g, q, packed=True)
     assert np.array_equal(idx, ref)
 
 
