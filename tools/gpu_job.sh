@@ -1,0 +1,28 @@
+#!/bin/bash
+# One parametrised GPU-box job list (replaces the per-experiment scripts of round 1).
+# usage: tools/gpu_job.sh <tag> <job> [<job> ...]       outputs under gpurun_out/<tag>/
+# jobs: tests | tests:<pytest -k expr> | fgtests | bench | benchref | fg540 | fg1080 | photon | stages | cfg4 | smoke
+TAG=$1; shift
+O=gpurun_out/$TAG
+mkdir -p $O
+nvidia-smi --query-gpu=name,clocks.max.sm,memory.total --format=csv > $O/smi.txt 2>&1
+nproc > $O/nproc.txt
+for job in "$@"; do
+  case $job in
+    tests)    timeout 1700 python -m pytest tests -m gpu -x -q > $O/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> $O/pytest_gpu.log ;;
+    tests:*)  timeout 900 python -m pytest tests -m gpu -x -q -k "${job#tests:}" > $O/pytest_k.log 2>&1; echo "pytest rc=$?" >> $O/pytest_k.log ;;
+    fgtests)  timeout 600 python -m pytest tests/test_gpu_zfinalgather.py tests/test_gpu_photon.py -m gpu -x -q > $O/pytest_fg.log 2>&1; echo "pytest rc=$?" >> $O/pytest_fg.log ;;
+    smoke)    timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > $O/smoke.log 2>&1; echo "rc=$?" >> $O/smoke.log ;;
+    bench)    timeout 900 python bench.py > $O/bench.json 2> $O/bench.err; echo "bench rc=$?" >> $O/bench.err ;;
+    benchq)   timeout 600 python bench.py --steps 20 > $O/bench.json 2> $O/bench.err; echo "bench rc=$?" >> $O/bench.err ;;
+    benchref) timeout 600 python bench.py --impl reference --steps 5 --warmup 1 > $O/bench_ref.json 2> $O/bench_ref.err ;;
+    fg540)    timeout 300 python tools/bench_fg.py 1000000 100000 960 540 32 2 > $O/bench_fg_540.jsonl 2> $O/bench_fg_540.err; echo "rc=$?" >> $O/bench_fg_540.err ;;
+    fg540v0)  B2RT_FG_VARIANT=0 timeout 300 python tools/bench_fg.py 1000000 100000 960 540 32 1 > $O/bench_fg_540_v0.jsonl 2> $O/bench_fg_540_v0.err ;;
+    fg1080)   timeout 600 python tools/bench_fg.py 8000000 2000000 1920 1080 32 2 > $O/bench_fg_1080.jsonl 2> $O/bench_fg_1080.err; echo "rc=$?" >> $O/bench_fg_1080.err ;;
+    photon)   timeout 600 python tools/bench_photon.py > $O/photon.log 2>&1 ;;
+    stages)   timeout 600 python tools/bench_stages.py > $O/stages.json 2> $O/stages.err ;;
+    cfg4)     timeout 900 python tools/bench_cfg4.py > $O/cfg4.json 2> $O/cfg4.err ;;
+    *)        echo "unknown job $job" >> $O/jobs.err ;;
+  esac
+done
+ls -la $O
