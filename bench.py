@@ -36,11 +36,18 @@ if ROOT not in sys.path:
 # The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints "NCCL version ..." from C at
 # communicator creation, seen at N = 2), so keep a private copy of the real stdout for the JSON line and send
 # everything else that targets fd 1 to stderr.
-_JSON_OUT = os.fdopen(os.dup(1), "w")
-os.dup2(2, 1)
+_JSON_OUT = None
+
+
+def grab_stdout():
+    global _JSON_OUT
+    if _JSON_OUT is None:
+        _JSON_OUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
 
 
 def emit(line):
+    grab_stdout()
     _JSON_OUT.write(json.dumps(line) + "\n")
     _JSON_OUT.flush()
 
@@ -142,6 +149,26 @@ def hit_parity(gpu_hits, gpu_occ, ref):
     t_bad = gt != rt
     p_bad = gp != rp
     go = np.ascontiguousarray(gpu_occ[::s2])
+    out = _parity_counts(rt, rp, gt, gp, t_bad, p_bad, go, ref)
+    bad = np.nonzero(t_bad)[0]
+    if len(bad) and ref.get("brute") is not None:
+        # who is right where the two disagree: the exhaustive loop over ALL primitives with pbrt's own Shape::Intersect
+        # (renderers/aggregatetest.cpp:93-102) for exactly those rays.  pbrt's BVHAccel prunes with an unpadded box test
+        # (accelerators/bvh.cpp:126-148) and can drop a hit that lies on a box face; the GPU traversal pads its boxes.
+        bt, bp = ref["brute"](bad[:4096] * s1)
+        bt = bt.view(np.uint32)
+        out["disagreements_resolved_by_exhaustive_loop"] = {
+            "rays": int(len(bt)), "gpu_equals_exhaustive": int((gt[bad[:4096]] == bt).sum()),
+            "bvhaccel_equals_exhaustive": int((rt[bad[:4096]] == bt).sum()),
+            "first": [{"ray": int(i * s1), "gpu_t": float(gt[i:i + 1].view(np.float32)[0]), "gpu_prim": int(gp[i]),
+                       "bvhaccel_t": float(rt[i:i + 1].view(np.float32)[0]), "bvhaccel_prim": int(rp[i]),
+                       "exhaustive_t": float(bt[j:j + 1].view(np.float32)[0]), "exhaustive_prim": int(bp[j])}
+                      for j, i in enumerate(bad[:8])]}
+        out["ok"] = bool(out["occluded_mismatch"] == 0 and (gt[bad[:4096]] == bt).all() and len(bad) <= 4096)
+    return out
+
+
+def _parity_counts(rt, rp, gt, gp, t_bad, p_bad, go, ref):
     return {"oracle": "pbrt-v2 BVHAccel::Intersect / IntersectP (oracle/_ref, the reference's own CPU path)",
             "rays": int(len(rt) + len(go)), "primary_rays": int(len(rt)), "shadow_rays": int(len(go)),
             "hits": int((rp >= 0).sum()), "t_mismatch": int(t_bad.sum()), "prim_mismatch": int((p_bad & t_bad).sum()),
@@ -164,14 +191,18 @@ def cpu_reference_step(P, idx, rays, shadow, nthreads, sample=None):
         rs.intersect(r1[: 20000], nth)                                   # warm the page cache / threads
         t, prim, _, s1 = rs.intersect(r1, nth)
         occ, s2 = rs.occluded(r2, nth)
-        rs.close()
         n = len(r1) + len(r2)
+
+        def brute(ray_idx):          # keeps the pbrt scene alive for hit_parity; closed there
+            bt, bp, _ = rs.intersect_brute(rays[ray_idx], nth)
+            return bt, bp
         return {"value": n / (s1 + s2) / 1e6, "unit": "Mrays/s", "cores": nth, "kind": "reference",
                 "sample": "%d primary (BVHAccel::Intersect) + %d shadow (IntersectP) rays of the step, pbrt-v2 "
                           "BVHAccel built in %.2f s (excluded); ranges of 4096 rays handed out by pbrt's own task "
                           "queue (EnqueueTasks)" % (len(r1), len(r2), build_s),
                 "closest_mrays": len(r1) / s1 / 1e6, "any_mrays": len(r2) / s2 / 1e6, "seconds": s1 + s2,
-                "_hits": {"t": t, "prim": prim, "occ": occ, "primary_stride": st1, "shadow_stride": st2}}
+                "_hits": {"t": t, "prim": prim, "occ": occ, "primary_stride": st1, "shadow_stride": st2, "brute": brute,
+                          "close": rs.close}}
     # port: exhaustive loop over all prims -- O(n_prims) per ray, so only a tiny sample
     ps = O.PortScene()
     ps.add_mesh(P, idx)
@@ -280,6 +311,7 @@ def photon_frame_extra(local_rank, world, rank):
 
 
 def main():
+    grab_stdout()
     args = parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -464,6 +496,7 @@ def main():
             if ref_hits is not None:
                 # self-certifying headline: the hits of the timed step against the reference's answers for the same rays
                 line["parity"] = hit_parity(gpu_hits_np, gpu_occ_np, ref_hits)
+                ref_hits["close"]()
         emit(line)
     if world > 1:
         dist.destroy_process_group()

@@ -155,3 +155,38 @@ def test_no_cpu_fallback(built):
                 src = open(os.path.join(dirpath, f)).read()
                 for needle in ("import oracle", "from oracle", "liboracle", "libpbrt_oracle", "oracle_port.h"):
                     assert needle not in src, (f, needle)
+
+
+def test_bench_parity_block_against_reference():
+    """bench.py's self-certification: the step's hits against pbrt BVHAccel, disagreements resolved by the exhaustive
+    loop.  Here the 'GPU' side is the C port's exhaustive loop (the GPU parity tests prove GPU == port)."""
+    if not O.ref_available():
+        pytest.skip("oracle/_ref not built")
+    import importlib.util
+    import os
+    spec = importlib.util.spec_from_file_location("bench_mod", os.path.join(os.path.dirname(__file__), "..", "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    from cuda_raytrace_b200 import scenes as S
+    P, idx = S.heightfield_mesh(40, 40, None, seed=5)
+    rays = np.concatenate([S.pinhole_rays(64, 48), S.incoherent_rays(2000, [-1, -0.3, -1], [1, 0.6, 1])])
+    port = O.PortScene()
+    port.add_mesh(P, idx)
+    t, prim, b1, b2 = port.intersect(rays, nthreads=4)
+    shadow = S.shadow_rays(rays, t, prim, (0.5, 3.0, 0.5))
+    _, sprim, _, _ = port.intersect(shadow, nthreads=4)
+    hits = np.zeros((len(rays), 4), np.float32)
+    hits[:, 0] = t
+    hits[:, 1] = prim.astype(np.int32).view(np.float32)
+    cb = bench.cpu_reference_step(P, idx, rays, shadow, 2, sample=None)
+    ref = cb.pop("_hits")
+    par = bench.hit_parity(hits, (sprim >= 0).astype(np.uint8), ref)
+    ref["close"]()
+    assert par["ok"] and par["occluded_mismatch"] == 0 and par["primary_rays"] == len(rays), par
+    # corrupt one hit distance: the exhaustive loop must side against the 'GPU'
+    hits[np.nonzero(prim >= 0)[0][0], 0] *= 2
+    cb = bench.cpu_reference_step(P, idx, rays, shadow, 2, sample=None)
+    ref = cb.pop("_hits")
+    par = bench.hit_parity(hits, (sprim >= 0).astype(np.uint8), ref)
+    ref["close"]()
+    assert not par["ok"] and par["t_mismatch"] >= 1, par
