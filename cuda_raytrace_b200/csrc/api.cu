@@ -103,21 +103,32 @@ int b2rt_clear_scene(b2rt_ctx *ctx) {
     ctx->h_verts.clear(); ctx->h_idx.clear(); ctx->h_tri_prim.clear(); ctx->h_analytic.clear();
     ctx->h_analytic_prim.clear(); ctx->h_analytic_type.clear(); ctx->h_prim_material.clear();
     ctx->h_prim_light.clear(); ctx->h_materials.clear(); ctx->h_lights.clear();
+    ctx->h_vnormal.clear(); ctx->h_vuv.clear(); ctx->h_tri_flags.clear(); ctx->any_attr = false;
     ctx->n_prims = 0; ctx->built = false;
     return B2RT_OK;
 }
 
-int b2rt_add_mesh(b2rt_ctx *ctx, int32_t nverts, const float *P, int32_t ntris, const int32_t *idx,
-                  const float *N, const float *uv, int32_t material_id, int32_t arealight_id,
-                  int32_t *first_prim) {
+int b2rt_add_mesh_ex(b2rt_ctx *ctx, int32_t nverts, const float *P, int32_t ntris, const int32_t *idx,
+                     const float *N, const float *uv, int32_t material_id, int32_t arealight_id, int32_t flags,
+                     int32_t *first_prim) {
     if (!ctx) return B2RT_E_ARG;
     if (nverts < 0 || ntris < 0 || (nverts && !P) || (ntris && !idx)) { ctx->err = "add_mesh: bad sizes/pointers"; return B2RT_E_ARG; }
     if ((int64_t)ctx->n_prims + ntris >= (1ll << 28)) { ctx->err = "add_mesh: more than 2^28 primitives"; return B2RT_E_ARG; }
+    if (flags & ~B2RT_MESH_REVERSE) { ctx->err = "add_mesh: unknown flag bits"; return B2RT_E_ARG; }
     for (int64_t k = 0; k < 3ll * ntris; ++k)
         if (idx[k] < 0 || idx[k] >= nverts) { ctx->err = "add_mesh: vertex index out of range"; return B2RT_E_ARG; }
-    (void)N; (void)uv;  // shading attributes: consumed by the shade stage (not by traversal)
     int32_t vbase = (int32_t)(ctx->h_verts.size() / 3);
     ctx->h_verts.insert(ctx->h_verts.end(), P, P + 3ll * nverts);
+    // per-vertex normals / uv (K6, reference: cuda_render/util/shape/cudatrianglemesh.cpp:24-44 uploads them the same way)
+    const uint8_t fl = (uint8_t)((N ? 1 : 0) | (uv ? 2 : 0) | ((flags & B2RT_MESH_REVERSE) ? 4 : 0));
+    if (fl) ctx->any_attr = true;
+    if (ctx->any_attr) {
+        ctx->h_vnormal.resize(3 * (size_t)vbase, 0.f); ctx->h_vuv.resize(2 * (size_t)vbase, 0.f);
+        if (N) ctx->h_vnormal.insert(ctx->h_vnormal.end(), N, N + 3ll * nverts);
+        if (uv) ctx->h_vuv.insert(ctx->h_vuv.end(), uv, uv + 2ll * nverts);
+        ctx->h_vnormal.resize(3 * (size_t)(vbase + nverts), 0.f); ctx->h_vuv.resize(2 * (size_t)(vbase + nverts), 0.f);
+        ctx->h_tri_flags.resize(ctx->h_tri_prim.size(), 0);
+    }
     size_t ib = ctx->h_idx.size();
     ctx->h_idx.resize(ib + 3ll * ntris);
     for (int64_t k = 0; k < 3ll * ntris; ++k) ctx->h_idx[ib + k] = idx[k] + vbase;
@@ -127,8 +138,15 @@ int b2rt_add_mesh(b2rt_ctx *ctx, int32_t nverts, const float *P, int32_t ntris, 
         ctx->h_prim_material.push_back(material_id);
         ctx->h_prim_light.push_back(arealight_id);
     }
+    if (ctx->any_attr) ctx->h_tri_flags.resize(ctx->h_tri_prim.size(), fl);
     ctx->built = false;
     return B2RT_OK;
+}
+
+int b2rt_add_mesh(b2rt_ctx *ctx, int32_t nverts, const float *P, int32_t ntris, const int32_t *idx,
+                  const float *N, const float *uv, int32_t material_id, int32_t arealight_id,
+                  int32_t *first_prim) {
+    return b2rt_add_mesh_ex(ctx, nverts, P, ntris, idx, N, uv, material_id, arealight_id, 0, first_prim);
 }
 
 static int add_analytic(b2rt_ctx *ctx, int type, const float o2w[12], const float *w2o, float radius,

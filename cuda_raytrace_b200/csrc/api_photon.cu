@@ -327,6 +327,28 @@ int b2rt_final_gather_set(b2rt_ctx *ctx, int32_t enable, int32_t gather_samples,
     return B2RT_OK;
 }
 
+int b2rt_surface_at(b2rt_ctx *ctx, int64_t nrays, const b2rt_ray *rays, b2rt_surface *out, int where) {
+    if (!ctx) return B2RT_E_ARG;
+    if (nrays < 0 || (nrays && (!rays || !out))) { ctx->err = "surface_at: bad arguments"; return B2RT_E_ARG; }
+    int rc = need_built(ctx, "surface_at");
+    if (rc || nrays == 0) return rc;
+    B2RT_CUDA(ctx, cudaSetDevice(ctx->device));
+    const b2rt_ray *dr = rays;
+    b2rt_surface *d_out = out;
+    if (where != B2RT_DEVICE) {
+        if (where != B2RT_HOST) { ctx->err = "surface_at: where must be B2RT_HOST or B2RT_DEVICE"; return B2RT_E_ARG; }
+        B2RT_CUDA(ctx, ctx->d_rays.reserve((size_t)nrays * sizeof(b2rt_ray)));
+        B2RT_CUDA(ctx, ctx->d_samples.reserve((size_t)nrays * sizeof(b2rt_surface)));
+        B2RT_CUDA(ctx, cudaMemcpyAsync(ctx->d_rays.p, rays, (size_t)nrays * sizeof(b2rt_ray), cudaMemcpyHostToDevice, ctx->stream));
+        dr = ctx->d_rays.as<b2rt_ray>(); d_out = ctx->d_samples.as<b2rt_surface>();
+    }
+    rc = b2rt_surface_at_impl(ctx, nrays, dr, d_out);
+    if (rc) return rc;
+    if (where != B2RT_DEVICE)
+        B2RT_CUDA(ctx, cudaMemcpyAsync(out, d_out, (size_t)nrays * sizeof(b2rt_surface), cudaMemcpyDeviceToHost, ctx->stream));
+    return status_check(ctx);
+}
+
 int b2rt_render_frame(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_params *fp, float *out_rgb, int where) {
     if (!ctx) return B2RT_E_ARG;
     if (!cam || !fp || !out_rgb || fp->spp < 1 || fp->x0 < 0 || fp->y0 < 0 || fp->x1 > cam->xres || fp->y1 > cam->yres ||

@@ -135,6 +135,11 @@ struct DScene {
     const Light *lights;
     const float *light_cdf;         // n_lights+1 entries, cdf[0]=0, cdf[n]=1; then n_lights pdfs
     int32_t n_lights, n_materials;
+    // per-vertex shading attributes (K6).  tri_flags == NULL: no mesh of the scene has any (the common case; make_surface
+    // then never touches the rest).  prim_kind[prim] = triangle index; tri_flags[tri]: bit 0 normals, bit 1 uv, bit 2 flip.
+    const uint8_t *tri_flags;
+    const int32_t *prim_kind, *tri_idx;
+    const float *verts, *vnormal, *vuv;
 };
 
 struct RayD {           // per-ray constants

@@ -119,6 +119,11 @@ struct b2rt_ctx {
     std::vector<float> h_verts;      // xyz
     std::vector<int32_t> h_idx;      // 3 per tri, global vertex indices
     std::vector<int32_t> h_tri_prim; // global prim id of each triangle
+    // per-vertex shading attributes (world-space normals, uv) of the meshes that have them; sized like h_verts once any
+    // mesh brought one, empty otherwise.  h_tri_flags[tri]: bit 0 normals, bit 1 uv, bit 2 reversed orientation
+    std::vector<float> h_vnormal, h_vuv;
+    std::vector<uint8_t> h_tri_flags;
+    bool any_attr = false;
     std::vector<AnalyticPrim> h_analytic;
     std::vector<int32_t> h_analytic_prim;  // global prim id
     std::vector<int32_t> h_analytic_type;
@@ -130,6 +135,7 @@ struct b2rt_ctx {
     // device scene + accel
     bool built = false;
     DevBuf d_verts, d_idx, d_analytic, d_prim_kind;   // prim_kind[n_prims]: tri index or ~analytic index
+    DevBuf d_vnormal, d_vuv, d_tri_flags;             // uploaded only when any_attr
     DevBuf d_leaf_box;      // float[6*n] per-prim AABB (prim id order)
     DevBuf d_scene_box;     // uint32[12]: centroid bounds + scene bounds as ordered ints
     DevBuf d_keys, d_vals, d_keys_alt, d_vals_alt, d_hist;  // sort
@@ -193,6 +199,7 @@ int b2rt_photons_trace_impl(b2rt_ctx *ctx, int64_t first_path, int64_t n_paths, 
                             int64_t n_stored[2]);
 int b2rt_photon_grid_build_impl(b2rt_ctx *ctx, int map, float cell_size, float target_per_cell);
 int b2rt_render_impl(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_params *fp, float *d_out);
+int b2rt_surface_at_impl(b2rt_ctx *ctx, int64_t n, const b2rt_ray *d_rays, b2rt_surface *d_out);
 int b2rt_sample_positions_impl(b2rt_ctx *ctx, int xres, int yres, const int32_t window[4], int spp, float *d_xy);
 bool b2rt_filter_valid(const b2rt_filter *f);
 void b2rt_filter_halo(const b2rt_filter *f, int *hx, int *hy);

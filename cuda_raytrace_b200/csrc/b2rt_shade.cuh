@@ -11,25 +11,107 @@
 
 struct Surface {
     f3 p;        // world hit point  o + d*t
-    f3 n;        // geometric normal (= shading normal: per-vertex normals are not used, like the reference's
-                 // fallback when a mesh has none, cudatrianglemesh.cu:60-75)
-    f3 sn, tn;   // BSDF frame: sn = Normalize(dpdu) with (dpdu,dpdv) = CoordinateSystem(n), tn = Cross(n, sn)
+    f3 n;        // SHADING normal, BSDF::nn = dgShading.nn: the z axis of the BSDF frame, the cosine factors and the
+                 // Faceforward of the photon lookups (core/reflection.cpp:601-609, integrators/photonmap.cpp:624-638)
+    f3 ng;       // GEOMETRIC normal, dg.nn: which side wi / wo are on in BSDF::f (reflection.cpp:616), isect.Le, the
+                 // normals of radiance photons and gather hits (photonmap.cpp:481, :672).  Equal to n unless the mesh has
+                 // per-vertex normals.
+    f3 sn, tn;   // BSDF frame: sn = Normalize(dgShading.dpdu), tn = Cross(nn, sn)
+    float u, v;  // surface parametrisation (triangles with attributes only; 0 otherwise)
     float ray_eps;
     int32_t material, light;
 };
 
-// K6: from (slot, t) and the ray.  Triangle: n = Normalize(Cross(e2, e1)) which is what pbrt gets for meshes with
-// default/degenerate uv (shapes/trianglemesh.cpp:181-201: CoordinateSystem(Normalize(Cross(e2,e1)),..));
+// Triangle with per-vertex uv and / or normals, or one whose orientation is reversed: pbrt's Triangle::Intersect tail
+// (shapes/trianglemesh.cpp:181-201, the uv determinant and its CoordinateSystem fallback) and
+// Triangle::GetShadingGeometry (:311-389) followed by BSDF::BSDF, operation for operation (the reference's device code
+// for the same job: cuda_render/util/shape/cudatrianglemesh.cu:25-78).  Normals arrive in WORLD space (the caller applies
+// the mesh's object-to-world normal transform; pbrt applies it after the interpolation, the same value up to rounding
+// and the same bits for the identity).  flags: bit 0 the mesh has normals, bit 1 it has uv, bit 2 ReverseOrientation ^
+// TransformSwapsHandedness (core/diffgeom.cpp:52-54).  dndu / dndv only feed texture filtering and are not formed.
+static __device__ __noinline__ void tri_surface_attr(const DScene &sc, const HitD &h, int tri, int flags, Surface &s) {
+    const int i0 = sc.tri_idx[3 * tri], i1 = sc.tri_idx[3 * tri + 1], i2 = sc.tri_idx[3 * tri + 2];
+    const f3 p1 = mk3(sc.verts[3 * i0], sc.verts[3 * i0 + 1], sc.verts[3 * i0 + 2]);
+    const f3 p2 = mk3(sc.verts[3 * i1], sc.verts[3 * i1 + 1], sc.verts[3 * i1 + 2]);
+    const f3 p3 = mk3(sc.verts[3 * i2], sc.verts[3 * i2 + 1], sc.verts[3 * i2 + 2]);
+    float uv[3][2] = {{0.f, 0.f}, {1.f, 0.f}, {1.f, 1.f}};                  // Triangle::GetUVs defaults (trianglemesh.h:98-100)
+    if (flags & 2) {
+        uv[0][0] = sc.vuv[2 * i0]; uv[0][1] = sc.vuv[2 * i0 + 1];
+        uv[1][0] = sc.vuv[2 * i1]; uv[1][1] = sc.vuv[2 * i1 + 1];
+        uv[2][0] = sc.vuv[2 * i2]; uv[2][1] = sc.vuv[2 * i2 + 1];
+    }
+    const float du1 = uv[0][0] - uv[2][0], du2 = uv[1][0] - uv[2][0], dv1 = uv[0][1] - uv[2][1], dv2 = uv[1][1] - uv[2][1];
+    const f3 dp1 = p1 - p3, dp2 = p2 - p3;
+    const float determinant = du1 * dv2 - dv1 * du2;
+    f3 dpdu, dpdv;
+    if (determinant == 0.f) {
+        const f3 e1 = p2 - p1, e2 = p3 - p1;
+        coordinate_system(normalize3(cross3(e2, e1)), dpdu, dpdv);
+    } else {
+        const float invdet = 1.f / determinant;
+        dpdu = (dp1 * dv2 - dp2 * dv1) * invdet;
+        dpdv = (dp1 * -du2 + dp2 * du1) * invdet;
+    }
+    const float b0 = 1.f - h.b1 - h.b2;
+    s.u = b0 * uv[0][0] + h.b1 * uv[1][0] + h.b2 * uv[2][0];
+    s.v = b0 * uv[0][1] + h.b1 * uv[1][1] + h.b2 * uv[2][1];
+    s.ng = normalize3(cross3(dpdu, dpdv));
+    if (flags & 4) s.ng = s.ng * -1.f;
+    f3 sdpdu = dpdu;                        // dgShading.dpdu
+    s.n = s.ng;
+    if (flags & 1) {
+        float b[3];
+        const float A00 = uv[1][0] - uv[0][0], A01 = uv[2][0] - uv[0][0], A10 = uv[1][1] - uv[0][1], A11 = uv[2][1] - uv[0][1];
+        const float C0 = s.u - uv[0][0], C1 = s.v - uv[0][1];
+        const float det = A00 * A11 - A01 * A10;                               // SolveLinearSystem2x2 (core/transform.cpp:39-49)
+        bool ok = !(fabsf(det) < 1e-10f);
+        if (ok) {
+            b[1] = (A11 * C0 - A01 * C1) / det;
+            b[2] = (A00 * C1 - A10 * C0) / det;
+            ok = !(isnan(b[1]) || isnan(b[2]));
+        }
+        if (!ok) b[0] = b[1] = b[2] = 1.f / 3.f;
+        else b[0] = 1.f - b[1] - b[2];
+        const f3 n0 = mk3(sc.vnormal[3 * i0], sc.vnormal[3 * i0 + 1], sc.vnormal[3 * i0 + 2]);
+        const f3 n1 = mk3(sc.vnormal[3 * i1], sc.vnormal[3 * i1 + 1], sc.vnormal[3 * i1 + 2]);
+        const f3 n2 = mk3(sc.vnormal[3 * i2], sc.vnormal[3 * i2 + 1], sc.vnormal[3 * i2 + 2]);
+        const f3 ns = normalize3(n0 * b[0] + n1 * b[1] + n2 * b[2]);
+        f3 ss = normalize3(dpdu);
+        f3 ts = cross3(ss, ns);
+        if (ts.x * ts.x + ts.y * ts.y + ts.z * ts.z > 0.f) {
+            ts = normalize3(ts);
+            ss = cross3(ts, ns);
+        } else {
+            coordinate_system(ns, ss, ts);
+        }
+        sdpdu = ss;
+        s.n = normalize3(cross3(ss, ts));      // DifferentialGeometry ctor of dgShading (core/diffgeom.cpp:46)
+        if (flags & 4) s.n = s.n * -1.f;
+    }
+    s.sn = normalize3(sdpdu);
+    s.tn = cross3(s.n, s.sn);
+}
+
+// K6: from (slot, t) and the ray.  Triangle without attributes: n = Normalize(Cross(e2, e1)) which is what pbrt gets for
+// meshes with default/degenerate uv (shapes/trianglemesh.cpp:181-201: CoordinateSystem(Normalize(Cross(e2,e1)),..));
 // rayEpsilon = 1e-3*t (trianglemesh.cpp:224).  Sphere / disk: 5e-4*t (sphere.cpp:154, disk.cpp:100).
 __device__ __forceinline__ Surface make_surface(const DScene &sc, const HitD &h, f3 o, f3 d) {
     Surface s;
     s.p = o + d * h.t;
+    s.u = 0.f; s.v = 0.f;
     const float4 *pp = reinterpret_cast<const float4 *>(sc.recs + h.slot);
     float4 B = __ldg(pp + 1), C = __ldg(pp + 2);
     int type = __float_as_int(B.w);
+    s.material = sc.prim_material ? sc.prim_material[h.prim] : -1;
+    s.light = sc.prim_light ? sc.prim_light[h.prim] : -1;
     if (type == B2RT_PRIM_TRI) {
-        s.n = normalize3(cross3(mk3(C.x, C.y, C.z), mk3(B.x, B.y, B.z)));
         s.ray_eps = 1e-3f * h.t;
+        if (sc.tri_flags) {                                  // some mesh of the scene carries attributes
+            const int tri = sc.prim_kind[h.prim];
+            const int fl = sc.tri_flags[tri];
+            if (fl) { tri_surface_attr(sc, h, tri, fl, s); return s; }
+        }
+        s.n = normalize3(cross3(mk3(C.x, C.y, C.z), mk3(B.x, B.y, B.z)));
     } else {
         const AnalyticPrim &A = sc.analytic[__float_as_int(C.w)];
         f3 no;
@@ -38,12 +120,11 @@ __device__ __forceinline__ Surface make_surface(const DScene &sc, const HitD &h,
         s.n = normalize3(xf_normal(A.w2o, no));
         s.ray_eps = 5e-4f * h.t;
     }
+    s.ng = s.n;
     f3 dpdv;
     coordinate_system(s.n, s.sn, dpdv);
     s.sn = normalize3(s.sn);
     s.tn = cross3(s.n, s.sn);
-    s.material = sc.prim_material ? sc.prim_material[h.prim] : -1;
-    s.light = sc.prim_light ? sc.prim_light[h.prim] : -1;
     return s;
 }
 
@@ -110,7 +191,7 @@ __device__ __forceinline__ bool sample_bsdf(const Surface &s, const Mat &m, f3 w
         if (o.pdf == 0.f) return false;
         o.wi = to_world(s, wi);
         // f re-evaluated for non-specular lobes: reflection only when wi, wo on the same side of ng
-        bool same = dot3(o.wi, s.n) * dot3(woW, s.n) > 0.f;
+        bool same = dot3(o.wi, s.ng) * dot3(woW, s.ng) > 0.f;
         o.f = same ? m.kd * B2_INV_PI : mk3(0.f, 0.f, 0.f);
         o.specular = false;
     } else {

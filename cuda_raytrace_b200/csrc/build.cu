@@ -396,6 +396,11 @@ int b2rt_build_impl(b2rt_ctx *ctx) {
     B2RT_CUDA(ctx, up(ctx->d_verts, ctx->h_verts.data(), ctx->h_verts.size() * sizeof(float)));
     B2RT_CUDA(ctx, up(ctx->d_idx, ctx->h_idx.data(), ctx->h_idx.size() * sizeof(int32_t)));
     B2RT_CUDA(ctx, up(ctx->d_prim_kind, kind.data(), kind.size() * sizeof(int32_t)));
+    if (ctx->any_attr) {
+        B2RT_CUDA(ctx, up(ctx->d_vnormal, ctx->h_vnormal.data(), ctx->h_vnormal.size() * sizeof(float)));
+        B2RT_CUDA(ctx, up(ctx->d_vuv, ctx->h_vuv.data(), ctx->h_vuv.size() * sizeof(float)));
+        B2RT_CUDA(ctx, up(ctx->d_tri_flags, ctx->h_tri_flags.data(), ctx->h_tri_flags.size()));
+    }
     // analytic prims + their types packed in one buffer: [AnalyticPrim x m][int32 type x m]
     size_t m = ctx->h_analytic.size();
     std::vector<uint8_t> apack(m * sizeof(AnalyticPrim) + m * sizeof(int32_t) + 16);

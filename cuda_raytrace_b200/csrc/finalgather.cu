@@ -56,7 +56,7 @@ fg_photon_kernel(DScene sc, uint32_t seed_lo, uint32_t seed_hi, int64_t first_pa
             }
             u4 rr = philox4x32_10(p_lo, p_hi, (uint32_t)n_isect, 2u, seed_lo, seed_hi);
             if (u01(rr.x) < .125f) {
-                f3 n = dot3(s.n, wo) < 0.f ? -s.n : s.n;                        // Faceforward(dg.nn, -photonRay.d)
+                f3 n = dot3(s.ng, wo) < 0.f ? -s.ng : s.ng;                     // Faceforward(dg.nn, -photonRay.d)
                 float4 *dst = reinterpret_cast<float4 *>(my + nd + nr);
                 dst[0] = make_float4(s.p.x, s.p.y, s.p.z, __uint_as_float(fg_oct_encode(n)));
                 dst[1] = make_float4(m.kd.x, m.kd.y, m.kd.z, __uint_as_float(p_lo));   // rho_r of the Lambertian lobe
@@ -333,7 +333,7 @@ final_gather_kernel(const FgArgs A) {
                                  overflow))
                 continue;
             const Surface s = make_surface(A.sc, h, p, R.wi);
-            const f3 ng = dot3(s.n, -R.wi) < 0.f ? -s.n : s.n;          // Faceforward(nGather, -bounceRay.d)
+            const f3 ng = dot3(s.ng, -R.wi) < 0.f ? -s.ng : s.ng;          // Faceforward(nGather, -bounceRay.d)
             float d2;
             const int ri = fg_radiance_nearest(A.g, A.rad_pos, A.rad_cells, A.rad_coarse1, A.rad_coarse2, A.rad_nbox1, A.rad_nbox2,
                                                s.p, ng, d2);
@@ -378,7 +378,7 @@ fg_trace_kernel(const FgArgs A, int64_t nrays, int R) {
         HitD h;
         if (traverse<false>(A.sc.nodes, A.sc.recs, A.sc.analytic, p.x, p.y, p.z, Ry.wi.x, Ry.wi.y, Ry.wi.z, q2.y, INFINITY, h, overflow)) {
             const Surface s = make_surface(A.sc, h, p, Ry.wi);
-            const f3 ng = dot3(s.n, -Ry.wi) < 0.f ? -s.n : s.n;          // Faceforward(nGather, -bounceRay.d)
+            const f3 ng = dot3(s.ng, -Ry.wi) < 0.f ? -s.ng : s.ng;          // Faceforward(nGather, -bounceRay.d)
             A.ray_recs[2 * i] = make_float4(s.p.x, s.p.y, s.p.z, 0.f);
             A.ray_recs[2 * i + 1] = make_float4(ng.x, ng.y, ng.z, 0.f);
             // the fine cell the lookup starts from (fg_radiance_phase0 clamps the same way)

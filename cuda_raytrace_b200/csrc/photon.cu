@@ -226,6 +226,12 @@ void b2rt_fill_dscene(b2rt_ctx *ctx, DScene *sc) {
     sc->light_cdf = ctx->d_light_cdf.as<float>();
     sc->n_lights = (int32_t)ctx->h_lights.size();
     sc->n_materials = (int32_t)ctx->h_materials.size();
+    sc->tri_flags = ctx->any_attr ? ctx->d_tri_flags.as<uint8_t>() : nullptr;
+    sc->prim_kind = ctx->d_prim_kind.as<int32_t>();
+    sc->tri_idx = ctx->d_idx.as<int32_t>();
+    sc->verts = ctx->d_verts.as<float>();
+    sc->vnormal = ctx->d_vnormal.as<float>();
+    sc->vuv = ctx->d_vuv.as<float>();
 }
 
 // material / light tables -> device (called from b2rt_build_accel).  Light power CDF as pbrt's

@@ -110,7 +110,7 @@ __device__ f3 direct_lighting(const DScene &sc, const Surface &s, const Mat &m, 
                 f3 dl = Lt.p - s.p;
                 float d2 = dl.x * dl.x + dl.y * dl.y + dl.z * dl.z;
                 f3 wi = normalize3(dl);
-                bool same = dot3(wi, s.n) * dot3(wo, s.n) > 0.f;
+                bool same = dot3(wi, s.ng) * dot3(wo, s.ng) > 0.f;      // BSDF::f: sides by the geometric normal
                 if (!same) continue;
                 // visibility segment p -> lightPos: direction (lightPos - p), [rayEps, 1]
                 if (traverse<true>(sc.nodes, sc.recs, sc.analytic, s.p.x, s.p.y, s.p.z, dl.x, dl.y, dl.z, s.ray_eps, 1.f, h,
@@ -129,7 +129,7 @@ __device__ f3 direct_lighting(const DScene &sc, const Surface &s, const Mat &m, 
                 f3 wi = normalize3(dl);
                 float lpdf = disk_light_pdf(D, Lt, s.p, wi);
                 bool emits = dot3(Lt.n, -wi) > 0.f;
-                bool same = dot3(wi, s.n) * dot3(wo, s.n) > 0.f;
+                bool same = dot3(wi, s.ng) * dot3(wo, s.ng) > 0.f;      // BSDF::f: sides by the geometric normal
                 if (lpdf > 0.f && emits && same) {
                     if (!traverse<true>(sc.nodes, sc.recs, sc.analytic, s.p.x, s.p.y, s.p.z, dl.x, dl.y, dl.z, s.ray_eps,
                                         1.f - 1e-3f, h, overflow)) {
@@ -201,7 +201,7 @@ render_li_kernel(DScene sc, b2rt_camera cam, b2rt_frame_params fp, uint32_t seed
         Surface sf = make_surface(sc, h, nd.o, nd.d);
         Mat m = load_material(sc, sf.material);
         f3 wo = -nd.d;
-        if (sf.light >= 0 && sf.light < sc.n_lights && dot3(sf.n, wo) > 0.f) {     // isect.Le(wo): DiffuseAreaLight::L
+        if (sf.light >= 0 && sf.light < sc.n_lights && dot3(sf.ng, wo) > 0.f) {     // isect.Le(wo): DiffuseAreaLight::L
             const Light &Lg = sc.lights[sf.light];
             L = L + nd.T * mk3(Lg.rgb[0], Lg.rgb[1], Lg.rgb[2]);
         }
@@ -327,6 +327,38 @@ sample_positions_kernel(int xres, int yres, int x0, int y0, int cw, int spp, uin
 }
 
 }  // namespace
+
+// parity hook for K6: closest hit + the surface the shade stage derives from it, one thread per ray
+__global__ void __launch_bounds__(128)
+surface_at_kernel(DScene sc, const b2rt_ray *__restrict__ rays, int64_t n, b2rt_surface *__restrict__ out, uint32_t *status) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 *rp = reinterpret_cast<const float4 *>(rays + i);
+    const float4 a = __ldg(rp), b = __ldg(rp + 1);
+    HitD h;
+    bool overflow = false;
+    float4 *o = reinterpret_cast<float4 *>(out + i);
+    if (!traverse<false>(sc.nodes, sc.recs, sc.analytic, a.x, a.y, a.z, b.x, b.y, b.z, a.w, b.w, h, overflow)) {
+        for (int k = 0; k < 4; ++k) o[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        o[4] = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
+    } else {
+        const Surface s = make_surface(sc, h, mk3(a.x, a.y, a.z), mk3(b.x, b.y, b.z));
+        o[0] = make_float4(s.p.x, s.p.y, s.p.z, h.t);
+        o[1] = make_float4(s.ng.x, s.ng.y, s.ng.z, s.u);
+        o[2] = make_float4(s.n.x, s.n.y, s.n.z, s.v);
+        o[3] = make_float4(s.sn.x, s.sn.y, s.sn.z, s.ray_eps);
+        o[4] = make_float4(s.tn.x, s.tn.y, s.tn.z, __int_as_float(h.prim));
+    }
+    if (overflow) atomicAdd(status, 1u);
+}
+int b2rt_surface_at_impl(b2rt_ctx *ctx, int64_t n, const b2rt_ray *d_rays, b2rt_surface *d_out) {
+    if (n <= 0) return B2RT_OK;
+    DScene sc;
+    b2rt_fill_dscene(ctx, &sc);
+    surface_at_kernel<<<(unsigned)((n + 127) / 128), 128, 0, ctx->stream>>>(sc, d_rays, n, d_out, ctx->d_counters.as<uint32_t>() + 8);
+    B2RT_LAUNCH_CHECK(ctx);
+    return B2RT_OK;
+}
 
 int b2rt_sample_positions_impl(b2rt_ctx *ctx, int xres, int yres, const int32_t window[4], int spp, float *d_xy) {
     SamplerD sm = {ctx->sampler_type, ctx->sampler_nx, ctx->sampler_ny};

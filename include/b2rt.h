@@ -68,6 +68,15 @@ int  b2rt_device_count(void);
 int b2rt_add_mesh(b2rt_ctx *ctx, int32_t nverts, const float *P, int32_t ntris, const int32_t *idx,
                   const float *N, const float *uv, int32_t material_id, int32_t arealight_id,
                   int32_t *first_prim);
+/* The same with orientation flags.  N (3 floats per vertex, WORLD space: the caller applies the mesh's object-to-world
+ * normal transform) and uv (2 per vertex) are pbrt's "N" and "uv" / "st" mesh parameters: a hit then carries the
+ * interpolated shading normal and the (dpdu, dpdv) frame of the uv parametrisation exactly as Triangle::Intersect +
+ * Triangle::GetShadingGeometry + BSDF::BSDF form them (pbrt-v2/src/shapes/trianglemesh.cpp:181-201, 311-389; reference
+ * device code cuda_render/util/shape/cudatrianglemesh.cu:25-78). */
+enum { B2RT_MESH_REVERSE = 1 };   /* pbrt ReverseOrientation ^ TransformSwapsHandedness: flips the normals (core/diffgeom.cpp:52-54) */
+int b2rt_add_mesh_ex(b2rt_ctx *ctx, int32_t nverts, const float *P, int32_t ntris, const int32_t *idx,
+                     const float *N, const float *uv, int32_t material_id, int32_t arealight_id, int32_t flags,
+                     int32_t *first_prim);
 /* o2w, w2o: row-major 3x4 object->world and its inverse exactly as pbrt holds them
  * (cuda_render/util/shape/cudasphere.cpp:15-40); w2o may be NULL (then it is computed here). */
 int b2rt_add_sphere(b2rt_ctx *ctx, const float o2w[12], const float *w2o, float radius, int32_t material_id,
@@ -100,6 +109,14 @@ int b2rt_accel_download(b2rt_ctx *ctx, uint32_t *morton, int32_t *prim_order, in
 int b2rt_trace_closest(b2rt_ctx *ctx, int64_t nrays, const b2rt_ray *rays, b2rt_hit *hits, int where);
 int b2rt_trace_any(b2rt_ctx *ctx, int64_t nrays, const b2rt_ray *rays, uint8_t *occluded, int where);
 
+
+/* parity hook for the hit attributes (K6): closest hit of every ray + what the shade stage derives from it -- replaces the
+ * attribute half of trianglemesh_intersect / sphere_intersect / disk_intersect (cuda_render/util/shape/cudatrianglemesh.cu:
+ * 25-78).  prim = -1 on a miss (the other fields are then 0).  ng = geometric normal dg.nn, n / sn / tn = the BSDF frame
+ * (nn, sn, tn of core/reflection.cpp:601-609) built from the shading geometry. */
+typedef struct { float p[3]; float t; float ng[3]; float u; float n[3]; float v; float sn[3]; float ray_eps; float tn[3];
+                 int32_t prim; } b2rt_surface;     /* 80 bytes */
+int b2rt_surface_at(b2rt_ctx *ctx, int64_t nrays, const b2rt_ray *rays, b2rt_surface *out, int where);
 
 /* ---- photon pass: replaces photontracing_camera / photontracing_closest_hit (cuda_render/photon_mapping/
  * photontracing.cu:80-185) and the host-side CreatePhotonMap kd-tree build (photonmappingrenderer.cpp:150-180) -- */
