@@ -17,6 +17,10 @@ LIGHT_POINT, LIGHT_DISK_AREA = 0, 1
 
 RAY_DTYPE = np.dtype([("o", np.float32, 3), ("tmin", np.float32), ("d", np.float32, 3), ("tmax", np.float32)])
 HIT_DTYPE = np.dtype([("t", np.float32), ("prim", np.int32), ("b1", np.float32), ("b2", np.float32)])
+SURFACE_DTYPE = np.dtype([("p", np.float32, 3), ("t", np.float32), ("ng", np.float32, 3), ("u", np.float32),
+                          ("n", np.float32, 3), ("v", np.float32), ("sn", np.float32, 3), ("ray_eps", np.float32),
+                          ("tn", np.float32, 3), ("prim", np.int32)])      # == b2rt_surface
+MESH_REVERSE = 1
 
 
 class AccelInfo(C.Structure):
@@ -36,7 +40,7 @@ SYMBOLS = [
     "b2rt_create", "b2rt_destroy", "b2rt_last_error", "b2rt_device_count", "b2rt_add_mesh", "b2rt_add_sphere",
     "b2rt_add_disk", "b2rt_add_material", "b2rt_add_light", "b2rt_clear_scene", "b2rt_build_accel",
     "b2rt_accel_info_get", "b2rt_accel_download", "b2rt_trace_closest", "b2rt_trace_any", "b2rt_sort_pairs",
-    "b2rt_sync", "b2rt_timer_start", "b2rt_timer_stop", "b2rt_launch_count", "b2rt_stream", "b2rt_host_alloc", "b2rt_host_free",
+    "b2rt_add_mesh_ex", "b2rt_surface_at", "b2rt_sync", "b2rt_timer_start", "b2rt_timer_stop", "b2rt_launch_count", "b2rt_stream", "b2rt_host_alloc", "b2rt_host_free",
 ]
 
 _lib = None
@@ -68,6 +72,8 @@ def load():
     lib.b2rt_accel_info_get.argtypes = [vp, C.POINTER(AccelInfo)]
     lib.b2rt_accel_download.argtypes = [vp] + [vp] * 7
     lib.b2rt_trace_closest.argtypes = [vp, i64, vp, vp, C.c_int]
+    lib.b2rt_add_mesh_ex.argtypes = [vp, i32, vp, i32, vp, vp, vp, i32, i32, i32, ip]
+    lib.b2rt_surface_at.argtypes = [vp, i64, vp, vp, C.c_int]
     lib.b2rt_trace_any.argtypes = [vp, i64, vp, vp, C.c_int]
     lib.b2rt_sort_pairs.argtypes = [vp, i64, vp, vp, C.c_int]
     lib.b2rt_sync.argtypes = [vp]
@@ -145,13 +151,26 @@ class Context:
         return self.lib.b2rt_last_error(self.h).decode()
 
     # ---- scene --------------------------------------------------------------------------------
-    def add_mesh(self, P, idx, material=-1, arealight=-1):
+    def add_mesh(self, P, idx, material=-1, arealight=-1, N=None, uv=None, reverse=False):
+        """N: per-vertex normals in WORLD space, uv: per-vertex (u, v) -- pbrt's "N" / "uv" mesh parameters;
+        reverse: pbrt ReverseOrientation ^ TransformSwapsHandedness."""
         P = _f32(P, (-1, 3))
         idx = np.ascontiguousarray(idx, dtype=np.int32).reshape(-1, 3)
+        N = None if N is None else _f32(N, (-1, 3))
+        uv = None if uv is None else _f32(uv, (-1, 2))
+        if (N is not None and len(N) != len(P)) or (uv is not None and len(uv) != len(P)):
+            raise ValueError("add_mesh: N / uv need one entry per vertex")
         first = C.c_int32()
-        self._ck(self.lib.b2rt_add_mesh(self.h, len(P), _ptr(P), len(idx), _ptr(idx), None, None, material,
-                                        arealight, C.byref(first)))
+        self._ck(self.lib.b2rt_add_mesh_ex(self.h, len(P), _ptr(P), len(idx), _ptr(idx), _ptr(N), _ptr(uv), material,
+                                           arealight, MESH_REVERSE if reverse else 0, C.byref(first)))
         return first.value
+
+    def surface_at(self, rays):
+        """closest hit + the hit attributes the shade stage derives (b2rt_surface_at): SURFACE_DTYPE per ray"""
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
+        out = np.zeros(len(rays), SURFACE_DTYPE)
+        self._ck(self.lib.b2rt_surface_at(self.h, len(rays), _ptr(rays), _ptr(out), HOST))
+        return out
 
     def add_sphere(self, o2w, radius, w2o=None, material=-1, arealight=-1):
         o2w = _f32(o2w, (12,))

@@ -302,3 +302,29 @@ def image_metrics(img, ref):
     mb = b.mean()
     return {"mean_rel": float(np.abs(a - b).mean() / mb), "rmse_rel": float(np.sqrt(((a - b) ** 2).mean()) / mb),
             "bias_rel": float((a.mean() - mb) / mb)}
+
+
+def sphere_mesh(nu=24, nv=12, radius=0.5, center=(0.0, 0.0, 0.0), seed=None):
+    """Latitude / longitude sphere as an indexed mesh with per-vertex normals (exact sphere normals: the mesh shades
+    smooth) and uv = (phi / 2 pi, theta / pi) -- pbrt's "N" and "uv" mesh parameters.  The poles are rings of
+    coincident vertices so that every triangle has three distinct uv.  seed: shuffle the triangle order."""
+    th = np.linspace(0.0, np.pi, nv + 1)
+    ph = np.linspace(0.0, 2.0 * np.pi, nu + 1)
+    T, Ph = np.meshgrid(th, ph, indexing="ij")
+    n = np.stack([np.sin(T) * np.cos(Ph), np.cos(T), np.sin(T) * np.sin(Ph)], -1).reshape(-1, 3)
+    n /= np.linalg.norm(n, axis=1, keepdims=True)
+    P = (np.asarray(center, np.float64) + radius * n).astype(np.float32)
+    uv = np.stack([Ph / (2.0 * np.pi), T / np.pi], -1).reshape(-1, 2).astype(np.float32)
+    idx = []
+    for i in range(nv):
+        for j in range(nu):
+            a, b = i * (nu + 1) + j, i * (nu + 1) + j + 1
+            c, d = a + nu + 1, b + nu + 1
+            if i > 0:
+                idx.append((a, b, c))
+            if i < nv - 1:
+                idx.append((b, d, c))
+    idx = np.asarray(idx, np.int32)
+    if seed is not None:
+        idx = idx[np.random.default_rng(seed).permutation(len(idx))]
+    return P, idx, n.astype(np.float32), uv

@@ -65,8 +65,11 @@ class PortScene:
         self.idx = np.zeros((0, 3), np.int32)
         self.kind = []
         self.analytic = []
+        self.vnormal = np.zeros((0, 3), np.float32)     # per-vertex attributes, zero where a mesh has none
+        self.vuv = np.zeros((0, 2), np.float32)
+        self.tri_flags = np.zeros(0, np.uint8)          # bit 0 normals, bit 1 uv, bit 2 reversed orientation
 
-    def add_mesh(self, P, idx):
+    def add_mesh(self, P, idx, N=None, uv=None, reverse=False):
         P = np.ascontiguousarray(P, np.float32).reshape(-1, 3)
         idx = np.ascontiguousarray(idx, np.int32).reshape(-1, 3)
         first = len(self.kind)
@@ -74,7 +77,19 @@ class PortScene:
         self.idx = np.concatenate([self.idx, idx + len(self.verts)]).astype(np.int32)
         self.verts = np.concatenate([self.verts, P]).astype(np.float32)
         self.kind.extend(range(t0, t0 + len(idx)))
+        fl = (1 if N is not None else 0) | (2 if uv is not None else 0) | (4 if reverse else 0)
+        self.vnormal = np.concatenate([self.vnormal, np.zeros((len(P), 3), np.float32) if N is None else
+                                       np.asarray(N, np.float32).reshape(-1, 3)]).astype(np.float32)
+        self.vuv = np.concatenate([self.vuv, np.zeros((len(P), 2), np.float32) if uv is None else
+                                   np.asarray(uv, np.float32).reshape(-1, 2)]).astype(np.float32)
+        self.tri_flags = np.concatenate([self.tri_flags, np.full(len(idx), fl, np.uint8)])
         return first
+
+    def _attr_arrays(self):
+        """(vnormal, vuv, tri_flags) or (None, None, None) when no mesh has attributes"""
+        if not self.tri_flags.any():
+            return None, None, None
+        return np.ascontiguousarray(self.vnormal), np.ascontiguousarray(self.vuv), np.ascontiguousarray(self.tri_flags)
 
     def _add_analytic(self, o2w, w2o, radius, height, inner, typ):
         rec = np.zeros(28, np.float32)
@@ -169,6 +184,9 @@ class RefScene:
         lib.ref_intersect_brute.argtypes = [vp, i64, vp, vp, vp, vp, C.c_int]
         lib.ref_intersect_brute.restype = d
         lib.ref_num_cores.restype = C.c_int
+        lib.ref_scene_add_mesh_attr.argtypes = [vp, C.c_int, vp, C.c_int, vp, vp, vp, C.c_int]
+        lib.ref_surface.argtypes = [vp, i64, vp, vp, C.c_int]
+        lib.ref_surface.restype = None
         self.lib = lib
         self.h = C.c_void_p(lib.ref_scene_create())
         self.build_seconds = None
@@ -177,6 +195,22 @@ class RefScene:
         P = np.ascontiguousarray(P, np.float32).reshape(-1, 3)
         idx = np.ascontiguousarray(idx, np.int32).reshape(-1, 3)
         return self.lib.ref_scene_add_mesh(self.h, len(P), _p(P), len(idx), _p(idx))
+
+    def add_mesh_attr(self, P, idx, N=None, uv=None, reverse=False):
+        """pbrt TriangleMesh with "N" / "uv" (identity object-to-world, so N is in world space) and ReverseOrientation"""
+        P = np.ascontiguousarray(P, np.float32).reshape(-1, 3)
+        idx = np.ascontiguousarray(idx, np.int32).reshape(-1, 3)
+        N = None if N is None else np.ascontiguousarray(N, np.float32).reshape(-1, 3)
+        uv = None if uv is None else np.ascontiguousarray(uv, np.float32).reshape(-1, 2)
+        return self.lib.ref_scene_add_mesh_attr(self.h, len(P), _p(P), len(idx), _p(idx), _p(N), _p(uv), 1 if reverse else 0)
+
+    def surface_at(self, rays, nthreads=1):
+        """pbrt's own hit attributes: BVHAccel::Intersect, Intersection::GetBSDF (Triangle::GetShadingGeometry) and the
+        BSDF's (nn, sn, tn) frame.  SURFACE_DTYPE per ray."""
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
+        out = np.zeros(len(rays), SURFACE_DTYPE)
+        self.lib.ref_surface(self.h, len(rays), _p(rays), _p(out), nthreads)
+        return out
 
     def add_sphere(self, o2w, w2o, radius):
         o2w = np.ascontiguousarray(o2w, np.float32).reshape(12)
@@ -231,12 +265,17 @@ class RefScene:
 
 # ---- photon pass / grid / estimator restatements (oracle_photon.c) ----------------------------------------------------
 PHOTON_DTYPE = np.dtype([("p", np.float32, 3), ("wi_oct", np.uint32), ("alpha", np.float32, 3), ("path", np.uint32)])
+# == b2rt_surface (include/b2rt.h): hit point, t, geometric normal, u, shading normal (BSDF nn), v, sn, ray epsilon, tn, prim
+SURFACE_DTYPE = np.dtype([("p", np.float32, 3), ("t", np.float32), ("ng", np.float32, 3), ("u", np.float32),
+                          ("n", np.float32, 3), ("v", np.float32), ("sn", np.float32, 3), ("ray_eps", np.float32),
+                          ("tn", np.float32, 3), ("prim", np.int32)])
 
 
 class _CScene(C.Structure):
     _fields_ = [("nprims", C.c_int32), ("kind", C.c_void_p), ("verts", C.c_void_p), ("idx", C.c_void_p),
                 ("analytic", C.c_void_p), ("prim_material", C.c_void_p), ("nmaterials", C.c_int32),
-                ("materials", C.c_void_p), ("nlights", C.c_int32), ("lights", C.c_void_p)]
+                ("materials", C.c_void_p), ("nlights", C.c_int32), ("lights", C.c_void_p),
+                ("vnormal", C.c_void_p), ("vuv", C.c_void_p), ("tri_flags", C.c_void_p)]
 
 
 def _bind_photon():
@@ -258,6 +297,8 @@ def _bind_photon():
     lib.port_radiance_lookup.restype = None
     lib.port_final_gather.argtypes = [C.POINTER(_CScene), i64, vp, i64, vp, i64, vp, C.c_int, f, C.c_uint64, vp]
     lib.port_final_gather.restype = None
+    lib.port_surface_at.argtypes = [C.POINTER(_CScene), i64, vp, vp]
+    lib.port_surface_at.restype = None
     lib.port_sincos_quarter.argtypes = [f, C.POINTER(f), C.POINTER(f)]
     lib.port_sincos_quarter.restype = None
     lib.port_philox.argtypes = [C.c_uint32] * 6 + [vp]
@@ -281,8 +322,8 @@ class PortFullScene:
         self.materials.append([float(mtype), *map(float, rgb), *map(float, kt), float(ior)])
         return len(self.materials) - 1
 
-    def add_mesh(self, P, idx, material=-1, arealight=-1):
-        first = self.geo.add_mesh(P, idx)
+    def add_mesh(self, P, idx, material=-1, arealight=-1, N=None, uv=None, reverse=False):
+        first = self.geo.add_mesh(P, idx, N, uv, reverse)
         self.prim_material.extend([material] * len(np.asarray(idx).reshape(-1, 3)))
         return first
 
@@ -304,10 +345,24 @@ class PortFullScene:
         pm = np.asarray(self.prim_material, np.int32)
         mats = np.asarray(self.materials, np.float32).reshape(-1, 8)
         lights = np.asarray(self.lights, np.float32).reshape(-1, 8)
-        keep = (kind, verts, idx, an, pm, mats, lights)
-        cs = _CScene(len(kind), _p(kind).value, _p(verts).value, _p(idx).value, _p(an).value, _p(pm).value, len(mats),
-                     _p(mats).value if len(mats) else None, len(lights), _p(lights).value if len(lights) else None)
+        vn, vuv, tf = self.geo._attr_arrays()
+        keep = (kind, verts, idx, an, pm, mats, lights, vn, vuv, tf)
+        cs = _CScene(len(kind), _p(kind).value, _p(verts).value, _p(idx).value, _p(an).value,
+                     _p(pm).value if len(pm) else None, len(mats),
+                     _p(mats).value if len(mats) else None, len(lights), _p(lights).value if len(lights) else None,
+                     _p(vn).value if vn is not None else None, _p(vuv).value if vuv is not None else None,
+                     _p(tf).value if tf is not None else None)
         return cs, keep
+
+    def surface_at(self, rays):
+        """port_surface_at: closest hit + hit attributes, SURFACE_DTYPE per ray"""
+        lib = _bind_photon()
+        cs, keep = self._cscene()
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
+        out = np.zeros(len(rays), SURFACE_DTYPE)
+        lib.port_surface_at(C.byref(cs), len(rays), _p(rays), _p(out))
+        del keep
+        return out
 
     def photon_trace(self, seed, first_path, n_paths, max_depth=5, caustic=True, indirect=True):
         lib = _bind_photon()

@@ -71,7 +71,7 @@ int port_photon_trace_fg(const port_scene *sc, uint64_t seed, int64_t first_path
                 uint32_t rr[4];
                 philox(p_lo, p_hi, (uint32_t)n_isect, 2u, k0, k1, rr);
                 if (u01(rr[0]) < .125f) {
-                    v3 n = vdot(s.n, wo) < 0.f ? vneg(s.n) : s.n;
+                    v3 n = vdot(s.ng, wo) < 0.f ? vneg(s.ng) : s.ng;
                     port_photon ph;
                     ph.p[0] = s.p.x; ph.p[1] = s.p.y; ph.p[2] = s.p.z; ph.wi_oct = oct_encode(n);
                     ph.alpha[0] = m.kd.x; ph.alpha[1] = m.kd.y; ph.alpha[2] = m.kd.z; ph.path = p_lo;
@@ -214,7 +214,7 @@ void port_final_gather(const port_scene *sc, int64_t n_ind, const port_photon *i
             }
             osurf s; int prim;
             if (!closest(sc, p, wi, ray_eps, &s, &prim)) continue;
-            v3 ng = vdot(s.n, vneg(wi)) < 0.f ? vneg(s.n) : s.n;
+            v3 ng = vdot(s.ng, vneg(wi)) < 0.f ? vneg(s.ng) : s.ng;
             int64_t ri = radiance_nearest(n_rad, rad, s.p, ng);
             if (ri < 0) continue;
             v3 Lo = V(rad[ri].alpha[0], rad[ri].alpha[1], rad[ri].alpha[2]);

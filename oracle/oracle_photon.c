@@ -133,22 +133,84 @@ static v3 xfn(const float *w2o, v3 n) {   /* Normal transform = transpose of the
              w2o[2] * n.x + w2o[6] * n.y + w2o[10] * n.z);
 }
 
-typedef struct { v3 p, n, sn, tn; float ray_eps; } osurf;
+typedef struct { v3 p, n, ng, sn, tn; float ray_eps, u, v, t; } osurf;   /* n = shading normal (BSDF nn), ng = geometric dg.nn */
+static inline v3 vsub(v3 a, v3 b) { return V(a.x - b.x, a.y - b.y, a.z - b.z); }
+/* triangle with per-vertex normals / uv / reversed orientation: pbrt shapes/trianglemesh.cpp:181-201 (dpdu, dpdv from the uv
+ * determinant or CoordinateSystem), :311-389 (GetShadingGeometry), core/diffgeom.cpp:46-54, core/reflection.cpp:601-609 */
+static void tri_attr(const port_scene *sc, int tri, int fl, float b1, float b2, osurf *s) {
+    const int32_t *vi = sc->idx + 3 * (int64_t)tri;
+    const float *q1 = sc->verts + 3 * (int64_t)vi[0], *q2 = sc->verts + 3 * (int64_t)vi[1], *q3 = sc->verts + 3 * (int64_t)vi[2];
+    const v3 p1 = V(q1[0], q1[1], q1[2]), p2 = V(q2[0], q2[1], q2[2]), p3 = V(q3[0], q3[1], q3[2]);
+    float uv[3][2] = {{0.f, 0.f}, {1.f, 0.f}, {1.f, 1.f}};
+    if (fl & 2)
+        for (int j = 0; j < 3; ++j) { uv[j][0] = sc->vuv[2 * (int64_t)vi[j]]; uv[j][1] = sc->vuv[2 * (int64_t)vi[j] + 1]; }
+    const float du1 = uv[0][0] - uv[2][0], du2 = uv[1][0] - uv[2][0], dv1 = uv[0][1] - uv[2][1], dv2 = uv[1][1] - uv[2][1];
+    const v3 dp1 = vsub(p1, p3), dp2 = vsub(p2, p3);
+    const float determinant = du1 * dv2 - dv1 * du2;
+    v3 dpdu, dpdv;
+    if (determinant == 0.f) {
+        coord_system(vnormalize(vcross(vsub(p3, p1), vsub(p2, p1))), &dpdu, &dpdv);
+    } else {
+        const float invdet = 1.f / determinant;
+        dpdu = vscale(vsub(vscale(dp1, dv2), vscale(dp2, dv1)), invdet);
+        dpdv = vscale(vadd(vscale(dp1, -du2), vscale(dp2, du1)), invdet);
+    }
+    const float b0 = 1.f - b1 - b2;
+    s->u = b0 * uv[0][0] + b1 * uv[1][0] + b2 * uv[2][0];
+    s->v = b0 * uv[0][1] + b1 * uv[1][1] + b2 * uv[2][1];
+    s->ng = vnormalize(vcross(dpdu, dpdv));
+    if (fl & 4) s->ng = vscale(s->ng, -1.f);
+    v3 sdpdu = dpdu;
+    s->n = s->ng;
+    if (fl & 1) {
+        float b[3];
+        const float A00 = uv[1][0] - uv[0][0], A01 = uv[2][0] - uv[0][0], A10 = uv[1][1] - uv[0][1], A11 = uv[2][1] - uv[0][1];
+        const float C0 = s->u - uv[0][0], C1 = s->v - uv[0][1];
+        const float det = A00 * A11 - A01 * A10;
+        int ok = !(fabsf(det) < 1e-10f);
+        if (ok) {
+            b[1] = (A11 * C0 - A01 * C1) / det;
+            b[2] = (A00 * C1 - A10 * C0) / det;
+            ok = !(isnan(b[1]) || isnan(b[2]));
+        }
+        if (!ok) b[0] = b[1] = b[2] = 1.f / 3.f;
+        else b[0] = 1.f - b[1] - b[2];
+        const float *m0 = sc->vnormal + 3 * (int64_t)vi[0], *m1 = sc->vnormal + 3 * (int64_t)vi[1], *m2 = sc->vnormal + 3 * (int64_t)vi[2];
+        const v3 ns = vnormalize(vadd(vadd(vscale(V(m0[0], m0[1], m0[2]), b[0]), vscale(V(m1[0], m1[1], m1[2]), b[1])),
+                                      vscale(V(m2[0], m2[1], m2[2]), b[2])));
+        v3 ss = vnormalize(dpdu);
+        v3 ts = vcross(ss, ns);
+        if (ts.x * ts.x + ts.y * ts.y + ts.z * ts.z > 0.f) {
+            ts = vnormalize(ts);
+            ss = vcross(ts, ns);
+        } else {
+            coord_system(ns, &ss, &ts);
+        }
+        sdpdu = ss;
+        s->n = vnormalize(vcross(ss, ts));
+        if (fl & 4) s->n = vscale(s->n, -1.f);
+    }
+    s->sn = vnormalize(sdpdu);
+    s->tn = vcross(s->n, s->sn);
+}
 /* exhaustive closest hit (min t, min prim id) + hit attributes */
-static int closest(const port_scene *sc, v3 o, v3 d, float tmin, osurf *s, int *prim_out) {
-    float ray[8] = {o.x, o.y, o.z, tmin, d.x, d.y, d.z, INFINITY};
+static int closest_range(const port_scene *sc, v3 o, v3 d, float tmin, float tmax, osurf *s, int *prim_out) {
+    float ray[8] = {o.x, o.y, o.z, tmin, d.x, d.y, d.z, tmax};
     float t, b1, b2; int32_t prim;
     port_intersect_brute(sc->nprims, sc->kind, sc->verts, sc->idx, sc->analytic, 1, ray, &t, &prim, &b1, &b2, 1);
     if (prim < 0) return 0;
     *prim_out = prim;
     s->p = vadd(o, vscale(d, t));
+    s->t = t; s->u = 0.f; s->v = 0.f;
     int k = sc->kind[prim];
     if (k >= 0) {
+        s->ray_eps = 1e-3f * t;
+        const int fl = sc->tri_flags ? sc->tri_flags[k] : 0;
+        if (fl) { tri_attr(sc, k, fl, b1, b2, s); return 1; }
         const int32_t *vi = sc->idx + 3 * (int64_t)k;
         const float *p1 = sc->verts + 3 * (int64_t)vi[0], *p2 = sc->verts + 3 * (int64_t)vi[1], *p3 = sc->verts + 3 * (int64_t)vi[2];
         v3 e1 = V(p2[0] - p1[0], p2[1] - p1[1], p2[2] - p1[2]), e2 = V(p3[0] - p1[0], p3[1] - p1[1], p3[2] - p1[2]);
         s->n = vnormalize(vcross(e2, e1));
-        s->ray_eps = 1e-3f * t;
     } else {
         const float *A = sc->analytic + 28 * (int64_t)(~k);
         v3 no;
@@ -156,11 +218,33 @@ static int closest(const port_scene *sc, v3 o, v3 d, float tmin, osurf *s, int *
         s->n = vnormalize(xfn(A + 12, no));
         s->ray_eps = 5e-4f * t;
     }
+    s->ng = s->n;
     v3 dpdv;
     coord_system(s->n, &s->sn, &dpdv);
     s->sn = vnormalize(s->sn);
     s->tn = vcross(s->n, s->sn);
     return 1;
+}
+static int closest(const port_scene *sc, v3 o, v3 d, float tmin, osurf *s, int *prim_out) {
+    return closest_range(sc, o, d, tmin, INFINITY, s, prim_out);
+}
+void port_surface_at(const port_scene *sc, int64_t nrays, const float *rays, float *out) {
+    for (int64_t i = 0; i < nrays; ++i) {
+        const float *r = rays + 8 * i;
+        float *o = out + 20 * i;
+        osurf s; int prim = -1;
+        memset(o, 0, 80);
+        if (!closest_range(sc, V(r[0], r[1], r[2]), V(r[4], r[5], r[6]), r[3], r[7], &s, &prim)) {
+            int32_t m1 = -1; memcpy(o + 19, &m1, 4);
+            continue;
+        }
+        o[0] = s.p.x; o[1] = s.p.y; o[2] = s.p.z; o[3] = s.t;
+        o[4] = s.ng.x; o[5] = s.ng.y; o[6] = s.ng.z; o[7] = s.u;
+        o[8] = s.n.x; o[9] = s.n.y; o[10] = s.n.z; o[11] = s.v;
+        o[12] = s.sn.x; o[13] = s.sn.y; o[14] = s.sn.z; o[15] = s.ray_eps;
+        o[16] = s.tn.x; o[17] = s.tn.y; o[18] = s.tn.z;
+        int32_t pi = prim; memcpy(o + 19, &pi, 4);
+    }
 }
 static v3 to_local(const osurf *s, v3 v) { return V(vdot(v, s->sn), vdot(v, s->tn), vdot(v, s->n)); }
 static v3 to_world(const osurf *s, v3 v) {
@@ -190,7 +274,7 @@ static int sample_bsdf(const osurf *s, const omat *m, v3 woW, float u1, float u2
         o->pdf = (wo.z * wi.z > 0.f) ? fabsf(wi.z) * O_INV_PI : 0.f;
         if (o->pdf == 0.f) return 0;
         o->wi = to_world(s, wi);
-        int same = vdot(o->wi, s->n) * vdot(woW, s->n) > 0.f;
+        int same = vdot(o->wi, s->ng) * vdot(woW, s->ng) > 0.f;
         o->f = same ? vscale(m->kd, O_INV_PI) : V(0, 0, 0);
         o->specular = 0;
     } else {

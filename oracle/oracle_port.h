@@ -32,7 +32,14 @@ typedef struct {
     const int32_t *prim_material;   /* per prim, -1 = default grey matte 0.5 */
     int32_t nmaterials; const float *materials;   /* 8 floats each: type(0 matte,1 mirror,2 glass), kd/kr[3], kt[3], ior */
     int32_t nlights; const float *lights;         /* 8 floats each: type(0 point,1 disk area), p[3], rgb[3], prim */
+    /* per-vertex shading attributes (may all be NULL): world-space normals 3 / vertex, uv 2 / vertex, and per TRIANGLE
+     * flags: bit 0 the mesh has normals, bit 1 uv, bit 2 reversed orientation (same meaning as csrc/b2rt_shade.cuh) */
+    const float *vnormal; const float *vuv; const uint8_t *tri_flags;
 } port_scene;
+/* hit attributes (K6): closest hit of each ray + pbrt's Triangle::Intersect tail, Triangle::GetShadingGeometry and
+ * BSDF::BSDF (shapes/trianglemesh.cpp:181-201, 311-389; core/reflection.cpp:601-609).  out: 20 floats per ray laid out as
+ * b2rt_surface {p, t, ng, u, n, v, sn, ray_eps, tn, bits(prim)}; prim = -1 and zeros on a miss. */
+void port_surface_at(const port_scene *sc, int64_t nrays, const float *rays, float *out);
 typedef struct { float p[3]; uint32_t wi_oct; float alpha[3]; uint32_t path; } port_photon;   /* == b2rt_photon */
 void port_philox(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1, uint32_t out[4]);
 void port_sincos_quarter(float q, float *s, float *c);

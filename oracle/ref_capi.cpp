@@ -25,6 +25,9 @@
 #include "primitive.h"
 #include "intersection.h"
 #include "paramset.h"
+#include "reflection.h"
+#include "memory.h"
+#include <string.h>
 #include <atomic>
 #include <thread>
 #include <vector>
@@ -115,6 +118,21 @@ int ref_scene_add_mesh(void *h, int nverts, const float *P, int ntris, const int
     return first;
 }
 
+// the same with pbrt's "N" and "uv" mesh parameters and ReverseOrientation (identity object-to-world: N is world space)
+int ref_scene_add_mesh_attr(void *h, int nverts, const float *P, int ntris, const int *idx, const float *N,
+                            const float *uv, int reverse) {
+    RefScene *s = (RefScene *)h;
+    Transform *I = new Transform();
+    s->xforms.push_back(I);
+    Reference<Shape> mesh = new TriangleMesh(I, I, reverse != 0, ntris, nverts, idx, (const Point *)P,
+                                             (const Normal *)N, NULL, uv, Reference<Texture<float> >());
+    std::vector<Reference<Shape> > tris;
+    mesh->Refine(tris);
+    int first = (int)s->shapes.size();
+    for (size_t i = 0; i < tris.size(); ++i) s->push(tris[i]);
+    return first;
+}
+
 int ref_scene_add_sphere(void *h, const float o2w[12], const float w2o[12], float radius) {
     RefScene *s = (RefScene *)h;
     Transform *t, *ti;
@@ -175,6 +193,37 @@ double ref_intersect(void *h, int64_t nrays, const float *rays, float *t_out, in
         }
     });
     return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+}
+
+// Hit attributes as pbrt forms them: Intersection::GetBSDF runs Shape::GetShadingGeometry and MatteMaterial::GetBSDF,
+// i.e. BSDF(dgShading, dgGeom.nn) (core/reflection.cpp:601-609).  The BSDF's frame is private; LocalToWorld of the unit
+// axes returns sn, tn, nn (x * 1 + y * 0 + z * 0: exact up to the sign of a zero).  out: 20 floats per ray = b2rt_surface.
+void ref_surface(void *h, int64_t nrays, const float *rays, float *out, int nthreads) {
+    RefScene *s = (RefScene *)h;
+    parallel_for(nrays, nthreads, [=](int64_t lo, int64_t hi) {
+        MemoryArena arena;
+        for (int64_t i = lo; i < hi; ++i) {
+            const float *r = rays + 8 * i;
+            float *o = out + 20 * i;
+            for (int k = 0; k < 20; ++k) o[k] = 0.f;
+            Ray ray(Point(r[0], r[1], r[2]), Vector(r[4], r[5], r[6]), r[3], r[7]);
+            Intersection isect;
+            int prim = -1;
+            if (s->accel->Intersect(ray, &isect)) {
+                prim = s->id2prim.find(isect.shapeId)->second;
+                BSDF *bsdf = isect.GetBSDF(RayDifferential(ray), arena);
+                const Vector sn = bsdf->LocalToWorld(Vector(1, 0, 0)), tn = bsdf->LocalToWorld(Vector(0, 1, 0)),
+                             nn = bsdf->LocalToWorld(Vector(0, 0, 1));
+                o[0] = isect.dg.p.x; o[1] = isect.dg.p.y; o[2] = isect.dg.p.z; o[3] = ray.maxt;
+                o[4] = isect.dg.nn.x; o[5] = isect.dg.nn.y; o[6] = isect.dg.nn.z; o[7] = isect.dg.u;
+                o[8] = nn.x; o[9] = nn.y; o[10] = nn.z; o[11] = isect.dg.v;
+                o[12] = sn.x; o[13] = sn.y; o[14] = sn.z; o[15] = isect.rayEpsilon;
+                o[16] = tn.x; o[17] = tn.y; o[18] = tn.z;
+                arena.FreeAll();
+            }
+            memcpy(o + 19, &prim, 4);
+        }
+    });
 }
 
 double ref_intersectp(void *h, int64_t nrays, const float *rays, unsigned char *occ, int nthreads) {
