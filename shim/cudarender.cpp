@@ -27,6 +27,7 @@
 #include "samplers/stratified.h"
 #include "samplers/lowdiscrepancy.h"
 #include "filters/box.h"
+#include "cameras/perspective.h"
 #include "filters/triangle.h"
 #include "filters/gaussian.h"
 #include "filters/mitchell.h"
@@ -41,10 +42,15 @@ public:
     static int nverts(const TriangleMesh *m) { return m->nverts; }
     static const int *indices(const TriangleMesh *m) { return m->vertexIndex; }
     static const Point *points(const TriangleMesh *m) { return m->p; }     // already in world space (trianglemesh.cpp:69-71)
+    static const Normal *normals(const TriangleMesh *m) { return m->n; }   // OBJECT space, NULL if the mesh has none
+    static const float *uvs(const TriangleMesh *m) { return m->uvs; }
+    static bool hasTangents(const TriangleMesh *m) { return m->s != NULL; }
+    static bool hasAlpha(const TriangleMesh *m) { return m->alphaTexture.GetPtr() != NULL; }
 };
 class CudaSphere {
 public:
     static float radius(const Sphere *s) { return s->radius; }
+    static bool partial(const Sphere *s) { return s->zmin > -s->radius || s->zmax < s->radius || s->phiMax < 2.f * M_PI; }
 };
 class CudaDisk {
 public:
@@ -146,6 +152,14 @@ int CudaRender::materialId(const Material *material) {
             Warning("CudaRender: material not supported, using grey matte");        // cudamaterial.cpp:20
             type = B2RT_MAT_MATTE;
         }
+        // lobes that are not translated (the glossy lobe of plastic / uber / substrate, Oren-Nayar roughness ...): say so,
+        // as the reference does for whole materials it cannot translate (cudamaterial.cpp:20)
+        const int translated = type == B2RT_MAT_GLASS ? 2 : 1;
+        if (bsdf->NumComponents() > translated)
+            Warning("CudaRender: material has %d BxDF lobes, the CUDA renderer keeps %d (%s); the others are dropped",
+                    bsdf->NumComponents(), translated,
+                    type == B2RT_MAT_MATTE ? "Lambertian" : type == B2RT_MAT_GLASS ? "specular reflection + transmission"
+                                                                                   : "specular reflection");
         check(b2rt_add_material(ctx_, type, kd, kt, ior, &id), "b2rt_add_material");
     }
     materialCache_[material] = id;
@@ -157,14 +171,20 @@ int CudaRender::submit(const ShapeRec &r, const Transform *extra, int lightIndex
     int prim = -1;
     const int al = lightIndex;      // b2rt area-light id == pbrt light index (lights are added in scene->lights order)
     if (r.kind == 0) {
-        std::vector<float> P = r.P;
-        if (extra)
+        std::vector<float> P = r.P, N = r.N;
+        if (extra) {
             for (size_t i = 0; i + 2 < P.size(); i += 3) {
                 Point q = (*extra)(Point(P[i], P[i + 1], P[i + 2]));
                 P[i] = q.x; P[i + 1] = q.y; P[i + 2] = q.z;
             }
-        check(b2rt_add_mesh(ctx_, (int)(P.size() / 3), P.data(), (int)(r.idx.size() / 3), r.idx.data(), NULL, NULL,
-                            r.material, al, &prim), "b2rt_add_mesh");
+            for (size_t i = 0; i + 2 < N.size(); i += 3) {           // TransformedPrimitive: normals by the instance transform
+                Normal q = (*extra)(Normal(N[i], N[i + 1], N[i + 2]));
+                N[i] = q.x; N[i + 1] = q.y; N[i + 2] = q.z;
+            }
+        }
+        check(b2rt_add_mesh_ex(ctx_, (int)(P.size() / 3), P.data(), (int)(r.idx.size() / 3), r.idx.data(),
+                               N.empty() ? NULL : N.data(), r.uv.empty() ? NULL : r.uv.data(), r.material, al,
+                               r.reverse ? B2RT_MESH_REVERSE : 0, &prim), "b2rt_add_mesh_ex");
     } else {
         float o2w[12], w2o[12];
         memcpy(o2w, r.o2w, sizeof(o2w)); memcpy(w2o, r.w2o, sizeof(w2o));
@@ -187,6 +207,7 @@ void CudaRender::createCudaShape(const std::string &name, Reference<Shape> &shap
                                  int lightIndex) {
     ShapeRec r;
     r.radius = r.height = r.inner = 0.f;
+    r.reverse = false;
     if (name == "trianglemesh") {
         const TriangleMesh *m = static_cast<const TriangleMesh *>(shape.GetPtr());
         r.kind = 0;
@@ -194,9 +215,26 @@ void CudaRender::createCudaShape(const std::string &name, Reference<Shape> &shap
         r.P.resize(3 * (size_t)CudaTriangleMesh::nverts(m));
         for (int i = 0; i < CudaTriangleMesh::nverts(m); ++i) { r.P[3 * i] = p[i].x; r.P[3 * i + 1] = p[i].y; r.P[3 * i + 2] = p[i].z; }
         r.idx.assign(CudaTriangleMesh::indices(m), CudaTriangleMesh::indices(m) + 3 * (size_t)CudaTriangleMesh::ntris(m));
+        // per-vertex attributes (reference: cudatrianglemesh.cpp:24-44 uploads "N" and "uv" the same way).  pbrt keeps N in
+        // OBJECT space and transforms the interpolated normal (trianglemesh.cpp:338-341); the library takes world space.
+        const int nv = CudaTriangleMesh::nverts(m);
+        if (const Normal *n = CudaTriangleMesh::normals(m)) {
+            r.N.resize(3 * (size_t)nv);
+            for (int i = 0; i < nv; ++i) {
+                Normal w = (*shape->ObjectToWorld)(n[i]);
+                r.N[3 * i] = w.x; r.N[3 * i + 1] = w.y; r.N[3 * i + 2] = w.z;
+            }
+        }
+        if (const float *uv = CudaTriangleMesh::uvs(m)) r.uv.assign(uv, uv + 2 * (size_t)nv);
+        r.reverse = shape->ReverseOrientation ^ shape->TransformSwapsHandedness;       // core/diffgeom.cpp:52-54
+        if (CudaTriangleMesh::hasTangents(m)) Warning("CudaRender: per-vertex tangents \"S\" of a triangle mesh are ignored");
+        if (CudaTriangleMesh::hasAlpha(m)) Warning("CudaRender: alpha textures are not supported (cudatrianglemesh.cu:66), mesh is opaque");
     } else if (name == "sphere") {
         const Sphere *s = static_cast<const Sphere *>(shape.GetPtr());
         r.kind = 1; r.radius = CudaSphere::radius(s);
+        if (CudaSphere::partial(s))
+            Warning("CudaRender: partial sphere (zmin / zmax / phimax) rendered as a full sphere, like the reference's device "
+                    "code (cuda_render/util/shape/cudasphere.cu:27-72)");
     } else if (name == "disk") {
         const Disk *d = static_cast<const Disk *>(shape.GetPtr());
         r.kind = 2; r.radius = CudaDisk::radius(d); r.height = CudaDisk::height(d); r.inner = CudaDisk::inner(d);
@@ -261,6 +299,18 @@ void CudaRender::Render(const Scene *scene) {
 // any projective pbrt camera with lensradius 0 works without friend access (cameras/perspective.cpp:81-114).
 static b2rt_camera probeCamera(const Camera *camera) {
     const int W = camera->film->xResolution, H = camera->film->yResolution;
+    // what the library's camera is: a pinhole (b2rt_camera).  Say so when the scene's camera is something else instead of
+    // silently rendering a different picture (the reference uploads pbrt's own rays, pbrtcamera.cpp:57-122, so it follows
+    // any camera; depth of field there costs a CPU ray loop per frame).
+    if (const ProjectiveCamera *pc = dynamic_cast<const ProjectiveCamera *>(camera)) {
+        if (pc->lensRadius > 0.f)
+            Warning("CudaRender: \"lensradius\" %g ignored, the CUDA renderer's camera is a pinhole (no depth of field)", pc->lensRadius);
+        if (!dynamic_cast<const PerspectiveCamera *>(camera))
+            Warning("CudaRender: only the perspective camera is translated; this projective camera is rendered as a pinhole "
+                    "through its centre ray");
+    } else {
+        Warning("CudaRender: camera type not translated, rendered as a pinhole fitted to its corner rays");
+    }
     struct { float x, y; } pts[4] = {{W * .5f, H * .5f}, {0, 0}, {(float)W, 0}, {0, (float)H}};
     Vector d[4]; Point o;
     for (int i = 0; i < 4; ++i) {
@@ -363,6 +413,14 @@ void SimpleRenderer::render(const Scene *, CudaRender *cr, Camera *camera) {
 }
 
 PhotonMappingRenderer::PhotonMappingRenderer(const ParamSet &params) {
+    // pbrt hands the hook the parameters of the `Renderer` line only (RenderOptions::MakeRenderer, core/api.cpp:1245-1253):
+    // a scene that configures `SurfaceIntegrator "photonmap" "integer indirectphotons" [...]` and is run with -c gets the
+    // defaults below unless the same parameters are repeated on a Renderer line.  Not silently.
+    if (params.ints.empty() && params.floats.empty() && params.bools.empty())
+        Warning("CudaRender: no photon-mapping parameters on the Renderer line; SurfaceIntegrator parameters are not visible "
+                "to the CUDA renderer (core/api.cpp:1249), using pbrt's photonmap defaults (causticphotons 20000, "
+                "indirectphotons 100000, nused 50, maxdist 0.1, finalgather true).  Repeat them as "
+                "Renderer \"cuda\" \"integer indirectphotons\" [...] to set them.");
     nCaustic = params.FindOneInt("causticphotons", 20000);          // names and defaults: photonmap.cpp:784-801
     nIndirect = params.FindOneInt("indirectphotons", 100000);
     nUsed = params.FindOneInt("nused", 50);

@@ -51,6 +51,8 @@ private:
     struct ShapeRec {                 // one flattened shape, kept so that object instances can be replayed
         int kind;                     // 0 mesh, 1 sphere, 2 disk
         std::vector<float> P; std::vector<int> idx;
+        std::vector<float> N, uv;     // per-vertex world-space normals / uv of a mesh (empty: none)
+        bool reverse;                 // ReverseOrientation ^ TransformSwapsHandedness
         float o2w[12], w2o[12], radius, height, inner;
         int material;
     };
