@@ -222,7 +222,11 @@ def fill_scene(target, desc):
     for si, sh in enumerate(desc["shapes"]):
         al = light_of_shape.get(si, -1)
         if sh[0] == "mesh":
-            first.append(target.add_mesh(sh[1], sh[2], material=mids[sh[3]], arealight=al))
+            if len(sh) > 4:       # per-vertex normals / uv (world space here: descriptions with an o2w are for to_pbrt only)
+                assert len(sh) < 7 or sh[6] is None
+                first.append(target.add_mesh(sh[1], sh[2], material=mids[sh[3]], arealight=al, N=sh[4], uv=sh[5] if len(sh) > 5 else None))
+            else:
+                first.append(target.add_mesh(sh[1], sh[2], material=mids[sh[3]], arealight=al))
         elif sh[0] == "sphere":
             first.append(target.add_sphere(sh[1], sh[3], w2o=sh[2], material=mids[sh[4]], arealight=al))
         else:
@@ -272,9 +276,18 @@ def to_pbrt(desc, eye, look, up, fov, xres, yres, spp, integrator, filename, ren
             l = light_of_shape[si]
             L.append('  AreaLightSource "diffuse" "rgb L" [%g %g %g] "integer nsamples" [%d]' % (*l[2], l[3]))
         if sh[0] == "mesh":
-            L.append('  Shape "trianglemesh" "integer indices" [%s] "point P" [%s]' % (
+            # optional per-vertex attributes: ("mesh", P, idx, material, N, uv[, o2w]) -- with o2w, P and N are in object
+            # space and the file carries the transform (pbrt transforms P at load time and N per hit)
+            extra = ""
+            if len(sh) > 4 and sh[4] is not None:
+                extra += ' "normal N" [%s]' % " ".join("%.9g" % v for v in np.asarray(sh[4], np.float64).reshape(-1))
+            if len(sh) > 5 and sh[5] is not None:
+                extra += ' "float uv" [%s]' % " ".join("%.9g" % v for v in np.asarray(sh[5], np.float64).reshape(-1))
+            if len(sh) > 6 and sh[6] is not None:
+                L.append("  Transform [%s]" % _m16(sh[6]))
+            L.append('  Shape "trianglemesh" "integer indices" [%s] "point P" [%s]%s' % (
                 " ".join(str(int(v)) for v in np.asarray(sh[2]).reshape(-1)),
-                " ".join("%.9g" % v for v in np.asarray(sh[1], np.float64).reshape(-1))))
+                " ".join("%.9g" % v for v in np.asarray(sh[1], np.float64).reshape(-1)), extra))
         elif sh[0] == "sphere":
             L.append('  Transform [%s]\n  Shape "sphere" "float radius" [%g]' % (_m16(sh[1]), sh[3]))
         else:

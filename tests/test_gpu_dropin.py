@@ -15,13 +15,14 @@ BIN = os.path.join(ROOT, "shim", "_build", "pbrt_b2rt")
 EYE, LOOK, UP, FOV = (0, 1, 3.4), (0, 1, 0), (0, 1, 0), 40
 
 
-def _run(tmp_path, name, integrator, renderer, spp, res=96, pixelfilter='"box"', sampler="lowdiscrepancy"):
+def _run(tmp_path, name, integrator, renderer, spp, res=96, pixelfilter='"box"', sampler="lowdiscrepancy", desc=None):
     out = {}
+    desc = desc or S.cornell_scene(boxes=True)
     for tag, flag in (("gpu", ["-c"]), ("cpu", [])):
         pf = str(tmp_path / ("%s_%s.pfm" % (name, tag)))
         scene = str(tmp_path / ("%s_%s.pbrt" % (name, tag)))
         with open(scene, "w") as f:
-            f.write(S.to_pbrt(S.cornell_scene(boxes=True), EYE, LOOK, UP, FOV, res, res, spp, integrator, pf, renderer=renderer,
+            f.write(S.to_pbrt(desc, EYE, LOOK, UP, FOV, res, res, spp, integrator, pf, renderer=renderer,
                               pixelfilter=pixelfilter, sampler=sampler))
         r = subprocess.run([BIN, "--quiet"] + flag + [scene], capture_output=True, text=True, timeout=600)
         assert r.returncode == 0, r.stderr[-2000:]
@@ -94,3 +95,27 @@ def test_dropin_follows_the_scene_sampler(tmp_path, sampler):
     m = S.image_metrics(_block(gpu, 8), _block(cpu, 8))
     assert abs(m["bias_rel"]) < 0.005, m
     assert m["mean_rel"] < 0.012, m
+
+
+@pytest.mark.skipif(not os.path.exists(BIN), reason="shim/_build/pbrt_b2rt not built (needs /root/reference)")
+def test_dropin_mesh_with_vertex_normals_and_uv(tmp_path):
+    """a `Shape "trianglemesh"` with `"normal N"` and `"float uv"` under a non-uniform object transform.
+    The shim reads TriangleMesh::n / uvs through the fork's friend declaration, applies the object-to-world NORMAL
+    transform (inverse transpose) and hands both to b2rt_add_mesh_ex; pbrt's CPU path interpolates the shading normal in
+    Triangle::GetShadingGeometry.  A coarse ball (12 x 6) makes the difference between smooth and faceted shading large:
+    the GPU image must match pbrt's smooth image and must NOT match pbrt's image of the same mesh without normals."""
+    integ = 'SurfaceIntegrator "directlighting" "integer maxdepth" [5]'
+    P, idx, N, uv = S.sphere_mesh(12, 6, 1.0, (0.0, 0.0, 0.0))
+    o2w = [0.45, 0, 0, 0.0, 0, 0.6, 0, 0.6, 0, 0, 0.45, 0.1]        # Translate(0, .6, .1) Scale(.45, .6, .45): an ellipsoid
+    desc = S.cornell_scene(spheres=False)
+    desc["shapes"].append(("mesh", P, idx, 0, N, uv, o2w))
+    gpu, cpu = _run(tmp_path, "smooth", integ, "simple", spp=256, res=96, desc=desc)
+    flat = S.cornell_scene(spheres=False)
+    flat["shapes"].append(("mesh", P, idx, 0, None, None, o2w))
+    _, cpu_flat = _run(tmp_path, "flat", integ, "simple", spp=256, res=96, desc=flat)
+    m = S.image_metrics(_block(gpu, 4), _block(cpu, 4))
+    assert abs(m["bias_rel"]) < 0.005 and m["mean_rel"] < 0.015, m
+    ball = (slice(40, 88), slice(28, 68))                            # the ellipsoid's pixels
+    mb = S.image_metrics(_block(gpu[ball], 4), _block(cpu[ball], 4))
+    mf = S.image_metrics(_block(gpu[ball], 4), _block(cpu_flat[ball], 4))
+    assert mb["mean_rel"] < 0.015 and mf["mean_rel"] > 2 * mb["mean_rel"], (mb, mf)
