@@ -8,6 +8,7 @@
 // contiguous sub-tile, lanes rank by __match_any_sync + popc of lower lanes).  Equal keys keep
 // their input order, so with value = original index ties break by index.
 #include "b2rt_internal.cuh"
+#include <algorithm>
 
 namespace {
 
@@ -153,6 +154,177 @@ radix_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__res
     }
 }
 
+// ---- one-sweep variant (default): ONE histogram pass for all digits + one scatter launch per digit --------------------
+// After Adinets & Merrill, "Onesweep" (2022), restated for this tile / ranking scheme.  The three-launch pass above reads
+// the keys twice per pass and round-trips a per-block histogram through memory and a multi-launch scan: 20 P bytes per
+// pair and ~5 launches per pass where 4 + 16 P bytes and one launch are needed (68 B/pair for P = 4).  Here
+//   * onesweep_hist_kernel reads the keys once and counts every digit of every pass (P x 256 global counters);
+//   * onesweep_scatter_kernel does one pass per launch.  A block takes the next tile from a global ticket counter (so a
+//     block only ever waits for tiles that were handed out before its own: they are running or done, no deadlock whatever
+//     the launch order of blocks), ranks its 4096 keys exactly as radix_scatter_kernel does, publishes its 256 digit counts
+//     and finds its own start per digit by DECOUPLED LOOK-BACK over the tiles before it: state word = flag << 30 | value,
+//     flag 1 = the tile's own count, flag 2 = inclusive prefix over all tiles up to it.  Thread d walks digit d.
+// Determinism: the output position of a key is (keys with a smaller digit) + (same digit in earlier TILES) + (its stable
+// rank inside the tile) -- integers that do not depend on which block ran the tile or when.  Stability as before.
+constexpr uint32_t OS_FLAG_AGG = 1u << 30, OS_FLAG_INC = 2u << 30, OS_VALUE = (1u << 30) - 1u;
+constexpr int OS_MAX_PASSES = 4;
+
+__global__ void __launch_bounds__(SORT_THREADS)
+onesweep_hist_kernel(const uint32_t *__restrict__ keys, int64_t n, int passes, uint32_t *__restrict__ ghist) {
+    __shared__ uint32_t sh[OS_MAX_PASSES][RADIX];
+    for (int i = threadIdx.x; i < OS_MAX_PASSES * RADIX; i += SORT_THREADS) (&sh[0][0])[i] = 0;
+    __syncthreads();
+    // The top digit of a short key takes few values (a 26-bit cell key: 4): plain shared atomics would serialise 32-way
+    // inside every warp.  Its count is aggregated per warp first (match.any, the leader adds the group size); the lower
+    // digits are spread out and take the atomic directly.  Whole warps iterate together (`ok` masks the tail).
+    const bool vec_ok = (reinterpret_cast<uintptr_t>(keys) & 15) == 0;
+    const int64_t n4 = vec_ok ? n / 4 : 0;
+    const uint4 *kp = reinterpret_cast<const uint4 *>(keys);
+    const int lane = threadIdx.x & 31, top = passes - 1;
+    const int64_t stride = (int64_t)gridDim.x * SORT_THREADS;
+    auto count = [&](uint32_t k, bool ok) {
+        for (int p = 0; p < top; ++p)
+            if (ok) atomicAdd(&sh[p][(k >> (8 * p)) & 0xff], 1u);
+        const uint32_t d = ok ? ((k >> (8 * top)) & 0xff) : 0x100u;
+        const uint32_t peers = __match_any_sync(0xffffffffu, d);
+        if (ok && lane == __ffs(peers) - 1) atomicAdd(&sh[top][d], (uint32_t)__popc(peers));
+    };
+    const int64_t start = (int64_t)blockIdx.x * SORT_THREADS + (threadIdx.x & ~31);      // the warp's first index
+    for (int64_t w = start; w < n4; w += stride) {
+        const int64_t i = w + lane;
+        const bool ok = i < n4;
+        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+        if (ok) v = __ldg(kp + i);
+        count(v.x, ok); count(v.y, ok); count(v.z, ok); count(v.w, ok);
+    }
+    for (int64_t w = 4 * n4 + start; w < n; w += stride) {
+        const int64_t i = w + lane;
+        const bool ok = i < n;
+        count(ok ? keys[i] : 0u, ok);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < passes * RADIX; i += SORT_THREADS) {
+        const uint32_t c = (&sh[0][0])[i];
+        if (c) atomicAdd(&ghist[i], c);
+    }
+}
+
+__global__ void __launch_bounds__(SORT_THREADS, 4)
+onesweep_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__restrict__ vals_in,
+                        uint32_t *__restrict__ keys_out, uint32_t *__restrict__ vals_out, int64_t n, int shift,
+                        const uint32_t *__restrict__ ghist /* [256] of this pass */, uint32_t *__restrict__ state /* [tiles][256] */,
+                        uint32_t *__restrict__ ticket) {
+    __shared__ uint32_t sh[SORT_WARPS][RADIX];
+    __shared__ uint32_t s_off[RADIX];
+    __shared__ uint32_t s_gadj[RADIX];
+    __shared__ uint32_t s_wsum[SORT_WARPS];
+    __shared__ uint32_t s_key[SORT_TILE], s_val[SORT_TILE];
+    __shared__ uint32_t s_tile;
+    for (int i = threadIdx.x; i < SORT_WARPS * RADIX; i += SORT_THREADS) (&sh[0][0])[i] = 0;
+    if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
+    __syncthreads();
+    const uint32_t tile = s_tile;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t lt = (1u << lane) - 1u;
+    const int64_t tile0 = (int64_t)tile * SORT_TILE;
+    const int64_t base = tile0 + warp * (32 * SORT_ITEMS);
+    const int tile_n = (int)(n - tile0 < SORT_TILE ? n - tile0 : SORT_TILE);
+
+    uint32_t k[SORT_ITEMS], rank[SORT_ITEMS], peers[SORT_ITEMS];
+#pragma unroll
+    for (int r = 0; r < SORT_ITEMS; ++r) {
+        int64_t i = base + r * 32 + lane;
+        k[r] = i < n ? keys_in[i] : 0u;
+    }
+#pragma unroll
+    for (int r = 0; r < SORT_ITEMS; ++r) {
+        const bool ok = base + r * 32 + lane < n;
+        const uint32_t d = ok ? ((k[r] >> shift) & 0xff) : 0x100u;
+        peers[r] = __match_any_sync(0xffffffffu, d);
+    }
+#pragma unroll
+    for (int r = 0; r < SORT_ITEMS; ++r) {
+        const bool ok = base + r * 32 + lane < n;
+        const uint32_t d = (k[r] >> shift) & 0xff;
+        const int leader = __ffs(peers[r]) - 1;
+        uint32_t before = 0;
+        if (lane == leader && ok) {
+            before = sh[warp][d];
+            sh[warp][d] = before + __popc(peers[r]);
+        }
+        before = __shfl_sync(0xffffffffu, before, leader);
+        rank[r] = before + __popc(peers[r] & lt);
+        __syncwarp();
+    }
+    __syncthreads();
+    {
+        const int d = threadIdx.x;          // SORT_THREADS == RADIX: thread d owns digit d
+        uint32_t run = 0;
+#pragma unroll
+        for (int w = 0; w < SORT_WARPS; ++w) {
+            uint32_t c = sh[w][d];
+            sh[w][d] = run;
+            run += c;
+        }
+        // publish this tile's count of digit d at once, then look back
+        volatile uint32_t *st = state;
+        const size_t me = (size_t)tile * RADIX + d;
+        if (tile == 0) st[me] = OS_FLAG_INC | run;
+        else st[me] = OS_FLAG_AGG | run;
+        // block-wide exclusive scans over the digits: of the tile's counts (slot of digit d in the shared tile) and of
+        // the global histogram (first output position of digit d)
+        uint32_t inc = run, ginc = ghist[d];
+        const uint32_t gcount = ginc;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t t = __shfl_up_sync(0xffffffffu, inc, o), g = __shfl_up_sync(0xffffffffu, ginc, o);
+            if (lane >= o) { inc += t; ginc += g; }
+        }
+        __shared__ uint32_t s_gsum[SORT_WARPS];
+        if (lane == 31) { s_wsum[warp] = inc; s_gsum[warp] = ginc; }
+        __syncthreads();
+        uint32_t wbase = 0, gbase = 0;
+#pragma unroll
+        for (int w = 0; w < SORT_WARPS; ++w)
+            if (w < warp) { wbase += s_wsum[w]; gbase += s_gsum[w]; }
+        const uint32_t off = wbase + inc - run;
+        const uint32_t gfirst = gbase + ginc - gcount;
+        uint32_t excl = 0;                                  // digit d in the tiles before this one
+        if (tile > 0) {
+            size_t j = me - RADIX;
+            for (;;) {
+                const uint32_t v = st[j];
+                const uint32_t f = v & ~OS_VALUE;
+                if (f == 0u) continue;                      // not published yet: that tile is running, poll again
+                excl += v & OS_VALUE;
+                if (f == OS_FLAG_INC) break;
+                j -= RADIX;
+            }
+            st[me] = OS_FLAG_INC | (excl + run);
+        }
+        s_off[d] = off;
+        s_gadj[d] = gfirst + excl - off;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < SORT_ITEMS; ++r) {
+        int64_t i = base + r * 32 + lane;
+        if (i < n) {
+            uint32_t d = (k[r] >> shift) & 0xff;
+            uint32_t lp = s_off[d] + sh[warp][d] + rank[r];
+            s_key[lp] = k[r];
+            s_val[lp] = vals_in[i];
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < tile_n; i += SORT_THREADS) {
+        uint32_t key = s_key[i];
+        uint32_t pos = s_gadj[(key >> shift) & 0xff] + (uint32_t)i;
+        keys_out[pos] = key;
+        vals_out[pos] = s_val[i];
+    }
+}
+
 // ---- exclusive scan (reduce-then-scan, recursive) ------------------------------------------------
 constexpr int SCAN_THREADS = 512;
 constexpr int SCAN_ITEMS = 8;
@@ -243,9 +415,30 @@ int b2rt_sort_pairs_impl(b2rt_ctx *ctx, int64_t n, uint32_t *keys, uint32_t *val
     if (n >= (1ll << 32)) { ctx->err = "sort: n must be < 2^32"; return B2RT_E_ARG; }
     int passes = (key_bits + 7) / 8;
     int nblocks = (int)((n + SORT_TILE - 1) / SORT_TILE);
+    uint32_t *kin = keys, *vin = vals, *kout = keys_alt, *vout = vals_alt;
+    if (ctx->sort_variant == 1 && n < (1ll << 30) && passes <= OS_MAX_PASSES) {
+        // one-sweep: [passes * 256 digit counts][passes tickets, padded to 64][passes * tiles * 256 look-back states]
+        const size_t head = (size_t)OS_MAX_PASSES * RADIX + 64;
+        const size_t words = head + (size_t)passes * nblocks * RADIX;
+        B2RT_CUDA(ctx, ctx->d_hist.reserve(words * sizeof(uint32_t)));
+        uint32_t *ghist = ctx->d_hist.as<uint32_t>(), *tickets = ghist + OS_MAX_PASSES * RADIX, *states = ghist + head;
+        B2RT_CUDA(ctx, cudaMemsetAsync(ghist, 0, words * sizeof(uint32_t), ctx->stream));
+        const int hblocks = (int)std::min<int64_t>((n + 4 * SORT_THREADS - 1) / (4 * SORT_THREADS), (int64_t)ctx->sm_count * 8);
+        onesweep_hist_kernel<<<hblocks, SORT_THREADS, 0, ctx->stream>>>(kin, n, passes, ghist);
+        B2RT_LAUNCH_CHECK(ctx);
+        for (int p = 0; p < passes; ++p) {
+            onesweep_scatter_kernel<<<nblocks, SORT_THREADS, 0, ctx->stream>>>(kin, vin, kout, vout, n, 8 * p, ghist + p * RADIX,
+                                                                              states + (size_t)p * nblocks * RADIX, tickets + p);
+            B2RT_LAUNCH_CHECK(ctx);
+            uint32_t *t;
+            t = kin; kin = kout; kout = t;
+            t = vin; vin = vout; vout = t;
+        }
+        *result_in_alt = (passes & 1) != 0;
+        return B2RT_OK;
+    }
     B2RT_CUDA(ctx, ctx->d_hist.reserve((size_t)RADIX * nblocks * sizeof(uint32_t)));
     uint32_t *hist = ctx->d_hist.as<uint32_t>();
-    uint32_t *kin = keys, *vin = vals, *kout = keys_alt, *vout = vals_alt;
     for (int p = 0; p < passes; ++p) {
         int shift = 8 * p;
         radix_hist_kernel<<<nblocks, SORT_THREADS, 0, ctx->stream>>>(kin, n, shift, hist, nblocks);

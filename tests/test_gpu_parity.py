@@ -7,7 +7,7 @@ import torch
 
 from helpers import CASES, load_golden, case_scene, fill, fill_ctx, bits
 from oracle import oracle as O
-from cuda_raytrace_b200 import scenes as S
+from cuda_raytrace_b200 import b2rt, scenes as S
 
 pytestmark = pytest.mark.gpu
 
@@ -34,6 +34,37 @@ def test_sort_pairs_matches_stable_sort(ctx, n, bits_):
     assert np.array_equal(dk.cpu().numpy().view(np.uint32), keys[order])
     ek, ev = O.sort_pairs(keys, vals, bits_)
     assert np.array_equal(ev, dv.cpu().numpy().view(np.uint32))
+
+
+@pytest.mark.parametrize("variant", ["0", "1"])
+def test_sort_skewed_keys_both_schedules(built, monkeypatch, variant):
+    """B2RT_SORT_VARIANT: 1 = one-sweep (one histogram pass, one look-back scatter launch per digit), 0 = the three-launch
+    pass.  Key sets that stress the look-back and the histogram: all keys equal (every tile waits on one digit chain),
+    four distinct top digits (a short cell key), already sorted, reversed, and a ragged last tile."""
+    monkeypatch.setenv("B2RT_SORT_VARIANT", variant)
+    rng = np.random.default_rng(7)
+    with b2rt.Context(0, seed=1) as c:
+        for n, kind, bits_ in [(300_001, "equal", 32), (1_000_003, "top4", 26), (262_144, "sorted", 32),
+                               (262_145, "reversed", 32), (4_000_000, "cells", 22), (70_000, "byte", 8)]:
+            if kind == "equal":
+                keys = np.full(n, 0xdeadbeef, np.uint32)
+            elif kind == "top4":
+                keys = rng.integers(0, 1 << 26, n, dtype=np.uint64).astype(np.uint32)
+            elif kind == "sorted":
+                keys = np.sort(rng.integers(0, 1 << 32, n, dtype=np.uint64).astype(np.uint32))
+            elif kind == "reversed":
+                keys = np.sort(rng.integers(0, 1 << 32, n, dtype=np.uint64).astype(np.uint32))[::-1].copy()
+            elif kind == "cells":
+                keys = (rng.normal(0.5, 0.05, n).clip(0, 1) * ((1 << 22) - 1)).astype(np.uint32)       # clustered cell ids
+            else:
+                keys = rng.integers(0, 256, n, dtype=np.uint64).astype(np.uint32)
+            vals = np.arange(n, dtype=np.uint32)
+            dk, dv = _dev(keys.view(np.int32)), _dev(vals.view(np.int32))
+            c.sort_pairs_device(n, dk.data_ptr(), dv.data_ptr(), bits_)
+            c.sync()
+            order = np.argsort(keys, kind="stable")
+            assert np.array_equal(dv.cpu().numpy().view(np.uint32), order.astype(np.uint32)), (kind, variant)
+            assert np.array_equal(dk.cpu().numpy().view(np.uint32), keys[order]), (kind, variant)
 
 
 # ---- K1/K3/K4: builder topology, bit-exact against the CPU restatement ----------------------------------

@@ -21,6 +21,7 @@ for job in "$@"; do
     fg1080)   timeout 600 python tools/bench_fg.py 8000000 2000000 1920 1080 32 2 > $O/bench_fg_1080.jsonl 2> $O/bench_fg_1080.err; echo "rc=$?" >> $O/bench_fg_1080.err ;;
     photon)   timeout 600 python tools/bench_photon.py > $O/photon.log 2>&1 ;;
     stages)   timeout 600 python tools/bench_stages.py > $O/stages.json 2> $O/stages.err ;;
+    stages0)  B2RT_SORT_VARIANT=0 timeout 600 python tools/bench_stages.py > $O/stages_sort_variant0.json 2> $O/stages0.err ;;
     cfg4)     timeout 900 python tools/bench_cfg4.py > $O/cfg4.json 2> $O/cfg4.err ;;
     *)        echo "unknown job $job" >> $O/jobs.err ;;
   esac
