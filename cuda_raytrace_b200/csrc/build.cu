@@ -278,6 +278,73 @@ wide_collapse_level_kernel(const int32_t *__restrict__ queue_in, int nq, int n,
         if (is_openable(c[k], n, collapse)) queue_out[atomicAdd(out_count, 1u)] = c[k];
 }
 
+// The same collapse without levels and without the host: ONE launch works through a global queue of wide roots.
+// A thread claims queue slot i (atomic ticket), waits until the slot holds a node (or until everything is done), collapses
+// that root exactly as wide_collapse_level_kernel does and appends the openable children.  `pending` counts roots that are
+// queued or in work; whoever brings it to zero raises `done`.  Progress never depends on a block that is not resident yet:
+// every queued root is claimed by a thread that is already running (a waiting one, or one that takes its next ticket), so
+// the grid size only bounds the parallelism.  The queue order is scheduling-dependent but never reaches the output: a
+// root's children are a function of the binary tree alone and node indices come from the prefix sum over wide_flag.
+// The level-synchronous form cost one launch, one 4-byte download and one stream synchronisation per level (15 levels for
+// the 1 M-triangle scene: ~0.4 of the 1.0 ms build).
+// ctl[0] = next ticket, ctl[1] = queue tail, ctl[2] = pending, ctl[3] = done, ctl[5] = deepest level reached
+__global__ void __launch_bounds__(128)
+wide_collapse_queue_kernel(int n, const int32_t *__restrict__ child, const float *__restrict__ box,
+                           const uint8_t *__restrict__ collapse, WideTmp *__restrict__ tmp,
+                           uint32_t *__restrict__ wide_flag, int32_t *queue, uint8_t *level, uint32_t *ctl) {
+    volatile int32_t *vq = queue;
+    volatile uint32_t *vctl = ctl;
+    volatile uint8_t *vlevel = level;
+    for (;;) {
+        const uint32_t slot = atomicAdd(&ctl[0], 1u);
+        if (slot >= (uint32_t)(n - 1)) return;              // there are at most n - 1 internal nodes
+        int root;
+        while ((root = vq[slot]) < 0)
+            if (vctl[3]) return;
+        __threadfence();
+        const int lvl = vlevel[root];
+        int c[4]; int m = 2;
+        c[0] = child[2 * root]; c[1] = child[2 * root + 1]; c[2] = -1; c[3] = -1;
+        while (m < 4) {
+            int best = -1; float best_area = -1.f;
+            for (int k = 0; k < m; ++k) {
+                if (!is_openable(c[k], n, collapse)) continue;
+                float a = box_area(box + 6 * (int64_t)c[k]);
+                if (a > best_area) { best_area = a; best = k; }   // first max wins: deterministic
+            }
+            if (best < 0) break;
+            int node = c[best];
+            for (int k = m; k > best + 1; --k) c[k] = c[k - 1];
+            c[best] = child[2 * node]; c[best + 1] = child[2 * node + 1];
+            ++m;
+        }
+        WideTmp t;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) t.c[k] = c[k];
+        tmp[root] = t;
+        wide_flag[root] = 1u;
+        atomicMax(&ctl[5], (uint32_t)lvl);
+        int open[4], no = 0;
+        for (int k = 0; k < m; ++k)
+            if (is_openable(c[k], n, collapse)) open[no++] = c[k];
+        if (no > 0) {
+            const uint32_t at = atomicAdd(&ctl[1], (uint32_t)no);
+            for (int k = 0; k < no; ++k) vlevel[open[k]] = (uint8_t)min(lvl + 1, 255);
+            __threadfence();                                    // levels before the queue entries that announce them
+            for (int k = 0; k < no; ++k) vq[at + k] = open[k];
+        }
+        // this root is finished and `no` new ones are queued
+        const uint32_t before = atomicAdd(&ctl[2], (uint32_t)(no - 1));
+        if (before + (uint32_t)(no - 1) == 0u) { __threadfence(); vctl[3] = 1u; }
+    }
+}
+__global__ void wide_collapse_queue_init_kernel(int32_t *queue, uint8_t *level, uint32_t *ctl, const uint8_t *collapse) {
+    // queue = {root 0} unless the whole tree collapsed into one leaf (then there is nothing to do)
+    const bool any = !collapse[0];
+    ctl[0] = 0u; ctl[1] = any ? 1u : 0u; ctl[2] = any ? 1u : 0u; ctl[3] = any ? 0u : 1u; ctl[5] = 0u;
+    if (any) { level[0] = 1; queue[0] = 0; }
+}
+
 // Absolute margin added to every child box stored in a wide node: 2^-21 of the largest root-box coordinate (~4 ulps at
 // scene scale).  A slab test cannot follow a ray that runs exactly IN the plane shared by two sibling boxes (a ray
 // through a mesh vertex, an axis-parallel ray along a wall): the interval of one of the two boxes ends at exactly 0 and
@@ -451,6 +518,8 @@ int b2rt_build_impl(b2rt_ctx *ctx) {
         B2RT_LAUNCH_CHECK(ctx);
     } else {
         const int grid = (n + 255) / 256;
+        uint32_t sb[12];
+        bool have_sb = false;
         init_scene_box_kernel<<<1, 32, 0, st>>>(scene_box);
         B2RT_LAUNCH_CHECK(ctx);
         prim_bounds_kernel<<<grid, 256, 0, st>>>(ctx->d_verts.as<float>(), ctx->d_idx.as<int32_t>(),
@@ -491,60 +560,62 @@ int b2rt_build_impl(b2rt_ctx *ctx) {
             refit_kernel<<<grid, 256, 0, st>>>(leaf_box, vals, n, parent, child, range, bin_box, cost, flag,
                                                collapse);
             B2RT_LAUNCH_CHECK(ctx);
+            // greedy collapse to 4-wide nodes: one persistent launch over a device-side queue, the node order from a
+            // prefix sum over wide_flag; then ONE host read for everything the host needs (root collapsed?, node count,
+            // depth, SAH cost, root box) -- the build used to synchronise ~17 times
+            uint32_t *wide_flag = ctx->d_wide_flag.as<uint32_t>();
+            uint32_t *wide_index = ctx->d_wide_index.as<uint32_t>();
+            uint32_t *counter = ctx->d_counters.as<uint32_t>();
+            int32_t *qa = ctx->d_queue_a.as<int32_t>();
+            uint8_t *level = (uint8_t *)ctx->d_queue_b.p;
+            uint32_t *ctl = counter + 40;
+            B2RT_CUDA(ctx, cudaMemsetAsync(wide_flag, 0, (size_t)nn * 4, st));
+            B2RT_CUDA(ctx, cudaMemsetAsync(qa, 0xff, (size_t)nn * 4, st));
+            wide_collapse_queue_init_kernel<<<1, 1, 0, st>>>(qa, level, ctl, collapse);
+            B2RT_LAUNCH_CHECK(ctx);
+            {
+                int64_t blocks = ((int64_t)(n - 1) + 127) / 128;
+                const int64_t cap = (int64_t)ctx->sm_count * 8;
+                if (blocks > cap) blocks = cap;
+                wide_collapse_queue_kernel<<<(unsigned)blocks, 128, 0, st>>>(n, child, bin_box, collapse, ctx->d_wide_tmp.as<WideTmp>(),
+                                                                             wide_flag, qa, level, ctl);
+                B2RT_LAUNCH_CHECK(ctx);
+            }
+            B2RT_CUDA(ctx, cudaMemcpyAsync(wide_index, wide_flag, (size_t)(n - 1) * 4, cudaMemcpyDeviceToDevice, st));
+            rc = b2rt_exclusive_scan_u32(ctx, wide_index, n - 1, counter + 4);
+            if (rc) return rc;
             uint8_t root_collapsed = 0;
+            uint32_t total = 0, deepest = 0;
+            float c0 = 0.f, rootbox[6];
             B2RT_CUDA(ctx, cudaMemcpyAsync(&root_collapsed, collapse, 1, cudaMemcpyDeviceToHost, st));
+            B2RT_CUDA(ctx, cudaMemcpyAsync(&total, counter + 4, 4, cudaMemcpyDeviceToHost, st));
+            B2RT_CUDA(ctx, cudaMemcpyAsync(&deepest, ctl + 5, 4, cudaMemcpyDeviceToHost, st));
+            B2RT_CUDA(ctx, cudaMemcpyAsync(&c0, cost, 4, cudaMemcpyDeviceToHost, st));
+            B2RT_CUDA(ctx, cudaMemcpyAsync(rootbox, bin_box, 24, cudaMemcpyDeviceToHost, st));
+            B2RT_CUDA(ctx, cudaMemcpyAsync(sb, scene_box, sizeof(sb), cudaMemcpyDeviceToHost, st));
+            have_sb = true;
             B2RT_CUDA(ctx, cudaStreamSynchronize(st));
             if (root_collapsed) {
                 B2RT_CUDA(ctx, ctx->d_wide_nodes.reserve(sizeof(WideNode)));
                 wide_single_kernel<<<1, 32, 0, st>>>(n, bin_box, ctx->d_wide_nodes.as<WideNode>());
                 B2RT_LAUNCH_CHECK(ctx);
             } else {
-                // level-synchronous greedy collapse; the queues are only work lists (their order does
-                // not reach the output: node indices come from the prefix sum over wide_flag)
-                uint32_t *wide_flag = ctx->d_wide_flag.as<uint32_t>();
-                uint32_t *wide_index = ctx->d_wide_index.as<uint32_t>();
-                uint32_t *counter = ctx->d_counters.as<uint32_t>();
-                int32_t *qa = ctx->d_queue_a.as<int32_t>(), *qb = ctx->d_queue_b.as<int32_t>();
-                B2RT_CUDA(ctx, cudaMemsetAsync(wide_flag, 0, (size_t)nn * 4, st));
-                B2RT_CUDA(ctx, cudaMemsetAsync(qa, 0, 4, st));  // queue = {root 0}
-                uint32_t nq = 1;
-                depth = 0;
-                while (nq > 0) {
-                    ++depth;
-                    B2RT_CUDA(ctx, cudaMemsetAsync(counter, 0, 4, st));
-                    wide_collapse_level_kernel<<<(nq + 127) / 128, 128, 0, st>>>(
-                        qa, (int)nq, n, child, bin_box, collapse, ctx->d_wide_tmp.as<WideTmp>(), wide_flag, qb,
-                        counter);
-                    B2RT_LAUNCH_CHECK(ctx);
-                    B2RT_CUDA(ctx, cudaMemcpyAsync(&nq, counter, 4, cudaMemcpyDeviceToHost, st));
-                    B2RT_CUDA(ctx, cudaStreamSynchronize(st));
-                    std::swap(qa, qb);
-                }
-                B2RT_CUDA(ctx, cudaMemcpyAsync(wide_index, wide_flag, (size_t)(n - 1) * 4,
-                                               cudaMemcpyDeviceToDevice, st));
-                rc = b2rt_exclusive_scan_u32(ctx, wide_index, n - 1, counter + 4);
-                if (rc) return rc;
-                uint32_t total = 0;
-                B2RT_CUDA(ctx, cudaMemcpyAsync(&total, counter + 4, 4, cudaMemcpyDeviceToHost, st));
-                B2RT_CUDA(ctx, cudaStreamSynchronize(st));
                 n_wide = (int)total;
+                depth = (int)deepest;
                 B2RT_CUDA(ctx, ctx->d_wide_nodes.reserve((size_t)n_wide * sizeof(WideNode)));
                 wide_emit_kernel<<<(n - 1 + 127) / 128, 128, 0, st>>>(
                     n, ctx->d_wide_tmp.as<WideTmp>(), wide_flag, wide_index, bin_box, range, collapse,
                     ctx->d_wide_nodes.as<WideNode>());
                 B2RT_LAUNCH_CHECK(ctx);
             }
-            float c0 = 0.f, rootbox[6];
-            B2RT_CUDA(ctx, cudaMemcpyAsync(&c0, cost, 4, cudaMemcpyDeviceToHost, st));
-            B2RT_CUDA(ctx, cudaMemcpyAsync(rootbox, bin_box, 24, cudaMemcpyDeviceToHost, st));
-            B2RT_CUDA(ctx, cudaStreamSynchronize(st));
             float dx = rootbox[3] - rootbox[0], dy = rootbox[4] - rootbox[1], dz = rootbox[5] - rootbox[2];
             float ra = 2.f * (dx * dy + dy * dz + dz * dx);
             info.sah_cost = ra > 0.f ? c0 / ra : 0.f;
         }
-        uint32_t sb[12];
-        B2RT_CUDA(ctx, cudaMemcpyAsync(sb, scene_box, sizeof(sb), cudaMemcpyDeviceToHost, st));
-        B2RT_CUDA(ctx, cudaStreamSynchronize(st));
+        if (!have_sb) {
+            B2RT_CUDA(ctx, cudaMemcpyAsync(sb, scene_box, sizeof(sb), cudaMemcpyDeviceToHost, st));
+            B2RT_CUDA(ctx, cudaStreamSynchronize(st));
+        }
         for (int a = 0; a < 6; ++a) {
             uint32_t o = sb[6 + a];
             uint32_t b = (o & 0x80000000u) ? (o & 0x7fffffffu) : ~o;
