@@ -189,6 +189,11 @@ struct b2rt_ctx {
         }                                                                                 \
     } while (0)
 
+// where a GPU's freshly traced photons go: its slice of the two maps' arrays on each of the n GPUs of the box (n = 1: the
+// local arrays).  a / b = caustic / indirect (photon pass), direct / radiance (final-gathering pass).
+#define B2RT_MAX_GPUS 16
+struct PhotonDst { b2rt_photon *a[B2RT_MAX_GPUS]; b2rt_photon *b[B2RT_MAX_GPUS]; int n; };
+
 // ---- stage entry points (host functions, each enqueues on ctx->stream) -----------------------
 int b2rt_sort_pairs_impl(b2rt_ctx *ctx, int64_t n, uint32_t *keys, uint32_t *vals, uint32_t *keys_alt,
                          uint32_t *vals_alt, int key_bits, bool *result_in_alt);
@@ -199,8 +204,15 @@ struct DScene;
 int b2rt_upload_tables(b2rt_ctx *ctx);
 int b2rt_photons_trace_impl(b2rt_ctx *ctx, int64_t first_path, int64_t n_paths, int max_depth, int flags,
                             int64_t n_stored[2]);
+int b2rt_photons_trace_begin(b2rt_ctx *ctx, int64_t first_path, int64_t n_paths, int max_depth, int flags, uint32_t tot[2]);
+int b2rt_photons_trace_commit(b2rt_ctx *ctx, int64_t n_paths, int max_depth, const PhotonDst &dst);
+int b2rt_photons_trace_fg_begin(b2rt_ctx *ctx, int64_t first_path, int64_t n_paths, int max_depth, uint32_t tot[2]);
+int b2rt_photons_trace_fg_commit(b2rt_ctx *ctx, int64_t n_paths, int max_depth, const PhotonDst &dst);
+int b2rt_photons_reserve(b2rt_ctx *ctx, DevBuf &b, int64_t keep, int64_t want);
 int b2rt_photon_grid_build_impl(b2rt_ctx *ctx, int map, float cell_size, float target_per_cell);
 int b2rt_render_impl(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_params *fp, float *d_out);
+int b2rt_render_pixels_impl(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_params *fp, const uint32_t *d_pixmap,
+                            int64_t n_map, float *d_out);
 int b2rt_surface_at_impl(b2rt_ctx *ctx, int64_t n, const b2rt_ray *d_rays, b2rt_surface *d_out);
 int b2rt_sample_positions_impl(b2rt_ctx *ctx, int xres, int yres, const int32_t window[4], int spp, float *d_xy);
 bool b2rt_filter_valid(const b2rt_filter *f);

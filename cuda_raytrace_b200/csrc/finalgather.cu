@@ -82,21 +82,27 @@ fg_photon_kernel(DScene sc, uint32_t seed_lo, uint32_t seed_hi, int64_t first_pa
 
 __global__ void __launch_bounds__(256)
 fg_compact_kernel(const b2rt_photon *__restrict__ slots, const uint32_t *__restrict__ off_d, const uint32_t *__restrict__ off_r,
-                  const uint32_t *__restrict__ tot, int64_t n_paths, int stride, b2rt_photon *__restrict__ out_d,
-                  b2rt_photon *__restrict__ out_r) {
+                  const uint32_t *__restrict__ tot, int64_t n_paths, int stride, const PhotonDst dst) {
     int64_t li = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (li >= n_paths) return;
     uint32_t od = off_d[li], orr = off_r[li];
     uint32_t nd = ((li + 1 < n_paths) ? off_d[li + 1] : tot[0]) - od;
     uint32_t nr = ((li + 1 < n_paths) ? off_r[li + 1] : tot[1]) - orr;
     const float4 *src = reinterpret_cast<const float4 *>(slots + li * stride);
+    // like photon_compact_kernel: the slice goes to its place in the arrays of every GPU (peer stores over NVLink)
     for (uint32_t j = 0; j < nd; ++j) {
-        float4 *dst = reinterpret_cast<float4 *>(out_d + od + j);
-        dst[0] = src[2 * j]; dst[1] = src[2 * j + 1];
+        const float4 a = src[2 * j], b = src[2 * j + 1];
+        for (int g = 0; g < dst.n; ++g) {
+            float4 *d = reinterpret_cast<float4 *>(dst.a[g] + od + j);
+            d[0] = a; d[1] = b;
+        }
     }
     for (uint32_t j = 0; j < nr; ++j) {
-        float4 *dst = reinterpret_cast<float4 *>(out_r + orr + j);
-        dst[0] = src[2 * (nd + j)]; dst[1] = src[2 * (nd + j) + 1];
+        const float4 a = src[2 * (nd + j)], b = src[2 * (nd + j) + 1];
+        for (int g = 0; g < dst.n; ++g) {
+            float4 *d = reinterpret_cast<float4 *>(dst.b[g] + orr + j);
+            d[0] = a; d[1] = b;
+        }
     }
 }
 
@@ -520,11 +526,9 @@ static int fg_prepare_radiance(b2rt_ctx *ctx, FgGrid &g, const float4 **pos) {
     return B2RT_OK;
 }
 
-int b2rt_photons_reserve(b2rt_ctx *ctx, DevBuf &b, int64_t keep, int64_t want);
-
-int b2rt_photons_trace_fg_impl(b2rt_ctx *ctx, int64_t first_path, int64_t n_paths, int max_depth, int64_t n_stored[2]) {
+int b2rt_photons_trace_fg_begin(b2rt_ctx *ctx, int64_t first_path, int64_t n_paths, int max_depth, uint32_t tot[2]) {
     cudaStream_t st = ctx->stream;
-    if (n_stored) n_stored[0] = n_stored[1] = 0;
+    tot[0] = tot[1] = 0;
     if (n_paths == 0) return B2RT_OK;
     if (n_paths > (1ll << 28)) { ctx->err = "photons_trace_fg: at most 2^28 paths per call"; return B2RT_E_ARG; }
     if (ctx->radiance_computed) { ctx->err = "photons_trace_fg: radiance already computed; clear the photon maps first"; return B2RT_E_STATE; }
@@ -544,18 +548,34 @@ int b2rt_photons_trace_fg_impl(b2rt_ctx *ctx, int64_t first_path, int64_t n_path
     if (rc) return rc;
     rc = b2rt_exclusive_scan_u32(ctx, cnt_r, n_paths, counters + 33);
     if (rc) return rc;
-    uint32_t tot[2];
     B2RT_CUDA(ctx, cudaMemcpyAsync(tot, counters + 32, 8, cudaMemcpyDeviceToHost, st));
     B2RT_CUDA(ctx, cudaStreamSynchronize(st));
+    return B2RT_OK;
+}
+int b2rt_photons_trace_fg_commit(b2rt_ctx *ctx, int64_t n_paths, int max_depth, const PhotonDst &dst) {
+    if (n_paths == 0) return B2RT_OK;
+    fg_compact_kernel<<<(unsigned)((n_paths + 255) / 256), 256, 0, ctx->stream>>>(
+        ctx->d_fg_slots.as<b2rt_photon>(), ctx->d_fg_cnt.as<uint32_t>(), ctx->d_fg_cnt2.as<uint32_t>(),
+        ctx->d_counters.as<uint32_t>() + 32, n_paths, max_depth + 1, dst);
+    B2RT_LAUNCH_CHECK(ctx);
+    return B2RT_OK;
+}
+
+int b2rt_photons_trace_fg_impl(b2rt_ctx *ctx, int64_t first_path, int64_t n_paths, int max_depth, int64_t n_stored[2]) {
+    if (n_stored) n_stored[0] = n_stored[1] = 0;
+    if (n_paths == 0) return B2RT_OK;
+    uint32_t tot[2];
+    int rc = b2rt_photons_trace_fg_begin(ctx, first_path, n_paths, max_depth, tot);
+    if (rc) return rc;
     PhotonMap &md = ctx->maps[B2RT_MAP_DIRECT], &mr = ctx->maps[B2RT_MAP_RADIANCE];
     rc = b2rt_photons_reserve(ctx, md.photons, md.n, md.n + tot[0]);
     if (rc) return rc;
     rc = b2rt_photons_reserve(ctx, mr.photons, mr.n, mr.n + tot[1]);
     if (rc) return rc;
-    fg_compact_kernel<<<(unsigned)((n_paths + 255) / 256), 256, 0, st>>>(
-        ctx->d_fg_slots.as<b2rt_photon>(), cnt_d, cnt_r, counters + 32, n_paths, stride,
-        md.photons.as<b2rt_photon>() + md.n, mr.photons.as<b2rt_photon>() + mr.n);
-    B2RT_LAUNCH_CHECK(ctx);
+    PhotonDst dst;
+    dst.n = 1; dst.a[0] = md.photons.as<b2rt_photon>() + md.n; dst.b[0] = mr.photons.as<b2rt_photon>() + mr.n;
+    rc = b2rt_photons_trace_fg_commit(ctx, n_paths, max_depth, dst);
+    if (rc) return rc;
     md.n += tot[0]; mr.n += tot[1];
     md.n_paths += n_paths; mr.n_paths += n_paths;
     md.grid_built = mr.grid_built = false;

@@ -191,11 +191,14 @@ photon_trace_regen_kernel(DScene sc, uint32_t seed_lo, uint32_t seed_hi, int64_t
 
 __global__ void photon_pool_reset_kernel(unsigned long long *pool) { *pool = 0ull; }
 
-// place the deposits in path order: out_c[off_c[path] + 0..nc), out_i[off_i[path] + 0..ni)
+// place the deposits in path order: out_c[off_c[path] + 0..nc), out_i[off_i[path] + 0..ni).
+// The compaction IS the exchange step of the multi-GPU photon pass: dst holds the position of this GPU's slice in the
+// photon arrays of EVERY GPU of the box (dst.n of them; peer pointers, the stores travel over NVLink / NVSwitch), so the
+// photon maps are assembled by the kernel that produces them -- no send buffer, no collective afterwards, no copies.
 __global__ void __launch_bounds__(256)
 photon_compact_kernel(const b2rt_photon *__restrict__ slots, const uint32_t *__restrict__ off_c,
                       const uint32_t *__restrict__ off_i, const uint32_t *__restrict__ tot, int64_t n_paths,
-                      int max_depth, b2rt_photon *__restrict__ out_c, b2rt_photon *__restrict__ out_i) {
+                      int max_depth, const PhotonDst dst) {
     int64_t li = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (li >= n_paths) return;
     uint32_t oc = off_c[li], oi = off_i[li];
@@ -203,12 +206,18 @@ photon_compact_kernel(const b2rt_photon *__restrict__ slots, const uint32_t *__r
     uint32_t ni = ((li + 1 < n_paths) ? off_i[li + 1] : tot[1]) - oi;
     const float4 *src = reinterpret_cast<const float4 *>(slots + li * max_depth);
     for (uint32_t j = 0; j < nc; ++j) {
-        float4 *dst = reinterpret_cast<float4 *>(out_c + oc + j);
-        dst[0] = src[2 * j]; dst[1] = src[2 * j + 1];
+        const float4 a = src[2 * j], b = src[2 * j + 1];
+        for (int g = 0; g < dst.n; ++g) {
+            float4 *d = reinterpret_cast<float4 *>(dst.a[g] + oc + j);
+            d[0] = a; d[1] = b;
+        }
     }
     for (uint32_t j = 0; j < ni; ++j) {
-        float4 *dst = reinterpret_cast<float4 *>(out_i + oi + j);
-        dst[0] = src[2 * (nc + j)]; dst[1] = src[2 * (nc + j) + 1];
+        const float4 a = src[2 * (nc + j)], b = src[2 * (nc + j) + 1];
+        for (int g = 0; g < dst.n; ++g) {
+            float4 *d = reinterpret_cast<float4 *>(dst.b[g] + oi + j);
+            d[0] = a; d[1] = b;
+        }
     }
 }
 
@@ -300,10 +309,12 @@ int b2rt_photons_reserve(b2rt_ctx *ctx, DevBuf &b, int64_t keep, int64_t want) {
     return B2RT_OK;
 }
 
-int b2rt_photons_trace_impl(b2rt_ctx *ctx, int64_t first_path, int64_t n_paths, int max_depth, int flags,
-                            int64_t n_stored[2]) {
+// Photon pass in two steps so that several GPUs can meet in the middle (multi.cu): `begin` traces the paths into per-path
+// slots, scans the per-path counts and returns how many photons each map gains; `commit` compacts them to wherever the
+// caller says -- the local arrays (single GPU) or this GPU's slice of every GPU's arrays.
+int b2rt_photons_trace_begin(b2rt_ctx *ctx, int64_t first_path, int64_t n_paths, int max_depth, int flags, uint32_t tot[2]) {
     cudaStream_t st = ctx->stream;
-    if (n_stored) n_stored[0] = n_stored[1] = 0;
+    tot[0] = tot[1] = 0;
     if (n_paths == 0) return B2RT_OK;
     if (n_paths > (1ll << 30)) { ctx->err = "photons_trace: at most 2^30 paths per call"; return B2RT_E_ARG; }
     DScene sc;
@@ -338,18 +349,35 @@ int b2rt_photons_trace_impl(b2rt_ctx *ctx, int64_t first_path, int64_t n_paths, 
     if (rc) return rc;
     rc = b2rt_exclusive_scan_u32(ctx, cnt_i, n_paths, counters + 11);
     if (rc) return rc;
-    uint32_t tot[2];
     B2RT_CUDA(ctx, cudaMemcpyAsync(tot, counters + 10, 8, cudaMemcpyDeviceToHost, st));
     B2RT_CUDA(ctx, cudaStreamSynchronize(st));
+    return B2RT_OK;
+}
+int b2rt_photons_trace_commit(b2rt_ctx *ctx, int64_t n_paths, int max_depth, const PhotonDst &dst) {
+    if (n_paths == 0) return B2RT_OK;
+    photon_compact_kernel<<<(unsigned)((n_paths + 255) / 256), 256, 0, ctx->stream>>>(
+        ctx->d_slots.as<b2rt_photon>(), ctx->d_cnt_c.as<uint32_t>(), ctx->d_cnt_i.as<uint32_t>(),
+        ctx->d_counters.as<uint32_t>() + 10, n_paths, max_depth, dst);
+    B2RT_LAUNCH_CHECK(ctx);
+    return B2RT_OK;
+}
+
+int b2rt_photons_trace_impl(b2rt_ctx *ctx, int64_t first_path, int64_t n_paths, int max_depth, int flags,
+                            int64_t n_stored[2]) {
+    if (n_stored) n_stored[0] = n_stored[1] = 0;
+    if (n_paths == 0) return B2RT_OK;
+    uint32_t tot[2];
+    int rc = b2rt_photons_trace_begin(ctx, first_path, n_paths, max_depth, flags, tot);
+    if (rc) return rc;
     PhotonMap &mc = ctx->maps[B2RT_MAP_CAUSTIC], &mi = ctx->maps[B2RT_MAP_INDIRECT];
     rc = b2rt_photons_reserve(ctx, mc.photons, mc.n, mc.n + tot[0]);
     if (rc) return rc;
     rc = b2rt_photons_reserve(ctx, mi.photons, mi.n, mi.n + tot[1]);
     if (rc) return rc;
-    photon_compact_kernel<<<(unsigned)((n_paths + 255) / 256), 256, 0, st>>>(
-        ctx->d_slots.as<b2rt_photon>(), cnt_c, cnt_i, counters + 10, n_paths, max_depth,
-        mc.photons.as<b2rt_photon>() + mc.n, mi.photons.as<b2rt_photon>() + mi.n);
-    B2RT_LAUNCH_CHECK(ctx);
+    PhotonDst dst;
+    dst.n = 1; dst.a[0] = mc.photons.as<b2rt_photon>() + mc.n; dst.b[0] = mi.photons.as<b2rt_photon>() + mi.n;
+    rc = b2rt_photons_trace_commit(ctx, n_paths, max_depth, dst);
+    if (rc) return rc;
     mc.n += tot[0]; mi.n += tot[1];
     if (flags & 1) mc.n_paths += n_paths;
     if (flags & 2) mi.n_paths += n_paths;

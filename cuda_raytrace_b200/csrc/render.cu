@@ -168,14 +168,19 @@ struct TreeNode { f3 o, d; float tmin; f3 T; int depth; uint32_t id; };
 __global__ void __launch_bounds__(RENDER_THREADS)
 render_li_kernel(DScene sc, b2rt_camera cam, b2rt_frame_params fp, uint32_t seed_lo, uint32_t seed_hi, int64_t first_sample,
                  int64_t n_samples, int slots, float *__restrict__ sample_rgb, b2rt_query *__restrict__ qslots,
-                 uint32_t *__restrict__ qcnt, uint32_t *status, float2 *__restrict__ sample_xy, SamplerD sm) {
+                 uint32_t *__restrict__ qcnt, uint32_t *status, float2 *__restrict__ sample_xy, SamplerD sm,
+                 const uint32_t *__restrict__ pixmap) {
     int64_t ls = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (ls >= n_samples) return;
     const int64_t s = first_sample + ls;
     const int cw = fp.x1 - fp.x0;
     const int64_t pix = s / fp.spp;
     const int k = (int)(s % fp.spp);
-    const int px = fp.x0 + (int)(pix % cw), py = fp.y0 + (int)(pix / cw);
+    int px = fp.x0 + (int)(pix % cw), py = fp.y0 + (int)(pix / cw);
+    if (pixmap) {               // this GPU's pixels of a frame shared by several (image tiles): x | y << 16
+        const uint32_t pm = __ldg(pixmap + pix);
+        px = (int)(pm & 0xffffu); py = (int)(pm >> 16);
+    }
     const uint32_t gpix = global_pixel_id(px, py, cam.xres, cam.yres);
     const uint32_t k0 = seed_lo ^ 0x43414d52u, k1 = seed_hi;                     // 'CAMR' stream
     const float2 off = pixel_offset(sm, gpix, (uint32_t)k, k0, k1);
@@ -276,7 +281,8 @@ query_compact_kernel(const b2rt_query *__restrict__ qslots, const uint32_t *__re
 __global__ void __launch_bounds__(256)
 film_resolve_kernel(const float *__restrict__ sample_rgb, const uint32_t *__restrict__ qoff, const uint32_t *__restrict__ qtot,
                     const float *__restrict__ rgb_c, const float *__restrict__ rgb_i, int64_t n_samples, int spp,
-                    int64_t first_pixel, int64_t n_pixels, float *__restrict__ out_rgb) {
+                    int64_t first_pixel, int64_t n_pixels, float *__restrict__ out_rgb, const uint32_t *__restrict__ pixmap,
+                    int xres) {
     int64_t lp = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (lp >= n_pixels) return;
     f3 acc = mk3(0.f, 0.f, 0.f);
@@ -292,7 +298,12 @@ film_resolve_kernel(const float *__restrict__ sample_rgb, const uint32_t *__rest
         acc = acc + L;
     }
     float inv = 1.f / (float)spp;
-    float *o = out_rgb + 3 * (first_pixel + lp);
+    int64_t at = first_pixel + lp;
+    if (pixmap) {               // tile pixel: straight to its place in the WHOLE image, which may live on another GPU
+        const uint32_t pm = __ldg(pixmap + at);      // (the composite on GPU 0 is this store, over NVLink)
+        at = (int64_t)(pm >> 16) * xres + (int64_t)(pm & 0xffffu);
+    }
+    float *o = out_rgb + 3 * at;
     o[0] = acc.x * inv; o[1] = acc.y * inv; o[2] = acc.z * inv;
 }
 
@@ -376,6 +387,13 @@ int b2rt_sample_positions_impl(b2rt_ctx *ctx, int xres, int yres, const int32_t 
 
 // d_out: device buffer of (x1-x0)*(y1-y0)*3 floats, crop-window row-major
 int b2rt_render_impl(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_params *fp, float *d_out) {
+    return b2rt_render_pixels_impl(ctx, cam, fp, nullptr, 0, d_out);
+}
+// The same for an arbitrary pixel list (d_pixmap[n_map], x | y << 16, on this device): the multi-GPU frame's image tiles.
+// d_out is then the WHOLE xres * yres * 3 image (possibly a peer pointer) and every pixel is stored at its own place.
+// Box filter of radius <= 0.5 only (a wider filter needs the halo cells of every tile; multi.cu uses row bands then).
+int b2rt_render_pixels_impl(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_params *fp, const uint32_t *d_pixmap,
+                            int64_t n_map, float *d_out) {
     cudaStream_t st = ctx->stream;
     DScene sc;
     b2rt_fill_dscene(ctx, &sc);
@@ -401,6 +419,7 @@ int b2rt_render_impl(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_par
     // default) keeps the direct per-pixel mean below.
     const b2rt_filter &flt = ctx->film_filter;
     const bool filtered = !(flt.type == B2RT_FILTER_BOX && flt.xwidth <= 0.5f && flt.ywidth <= 0.5f);
+    if (filtered && d_pixmap) { ctx->err = "render_pixels: pixel lists need the box filter"; return B2RT_E_STATE; }
     if (filtered) {
         int hx, hy;
         b2rt_filter_halo(&flt, &hx, &hy);
@@ -411,7 +430,8 @@ int b2rt_render_impl(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_par
     if (sm.type == B2RT_SAMPLER_STRATIFIED && (int64_t)sm.nx * sm.ny != fp->spp) {
         ctx->err = "render_frame: stratified sampler needs xsamples * ysamples == spp"; return B2RT_E_ARG;
     }
-    const int64_t n_cells = (int64_t)(p.x1 - p.x0) * (p.y1 - p.y0);
+    const int64_t n_cells = d_pixmap ? n_map : (int64_t)(p.x1 - p.x0) * (p.y1 - p.y0);
+    if (n_cells <= 0) return B2RT_OK;
     if (filtered) {
         B2RT_CUDA(ctx, ctx->d_film_xy.reserve((size_t)n_cells * fp->spp * 8));
         B2RT_CUDA(ctx, ctx->d_film_rgb.reserve((size_t)n_cells * fp->spp * 12));
@@ -435,7 +455,7 @@ int b2rt_render_impl(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_par
         render_li_kernel<<<(unsigned)((ns + RENDER_THREADS - 1) / RENDER_THREADS), RENDER_THREADS, 0, st>>>(
             sc, *cam, p, (uint32_t)ctx->seed, (uint32_t)(ctx->seed >> 32), p0 * fp->spp, ns, slots,
             ctx->d_samples.as<float>(), ctx->d_qslots.as<b2rt_query>(), qcnt, counters + 8,
-            filtered ? ctx->d_film_xy.as<float2>() + p0 * fp->spp : nullptr, sm);
+            filtered ? ctx->d_film_xy.as<float2>() + p0 * fp->spp : nullptr, sm, d_pixmap);
         B2RT_LAUNCH_CHECK(ctx);
         int rc = b2rt_exclusive_scan_u32(ctx, qcnt, ns, counters + 12);
         if (rc) return rc;
@@ -469,7 +489,8 @@ int b2rt_render_impl(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_par
                 ctx->d_samples.as<float>(), qcnt, counters + 12, rgb_c, rgb_i, ns, ctx->d_film_rgb.as<float>() + 3 * p0 * fp->spp);
         else
             film_resolve_kernel<<<(unsigned)((np + 255) / 256), 256, 0, st>>>(ctx->d_samples.as<float>(), qcnt, counters + 12,
-                                                                              rgb_c, rgb_i, ns, fp->spp, p0, np, d_out);
+                                                                              rgb_c, rgb_i, ns, fp->spp, p0, np, d_out, d_pixmap,
+                                                                              cam->xres);
         B2RT_LAUNCH_CHECK(ctx);
     }
     if (filtered) {

@@ -1,0 +1,143 @@
+"""Image parity against the reference's CPU renderer on the BASELINE configs, at the north star's bar: mean relative error
+<= 1 %, RMSE <= 0.5 % (metric family of pbrt-v2/src/tools/exrdiff.cpp:73-103).
+
+  python tools/converged_parity.py --ref   build container only (needs oracle/_ref/pbrt, i.e. /root/reference): renders
+                                           the reference images with pbrt-v2 and stores them in tests/golden/converged.npz
+  python tools/converged_parity.py --gpu   GPU box: renders the same scenes through libb2rt and prints one JSON line per
+                                           case (tests/test_gpu_converged.py asserts the bars on the same function)
+
+Cases
+  cfg1_as_stated   BASELINE configs[0] to the letter: Cornell box (two matte boxes), photonmap, causticphotons 0,
+                   indirectphotons 200000, nused 50, maxdist 0.3, finalgather false, 512 x 512, lowdiscrepancy 4 spp.
+                   NOT a converged image on either side: 4 spp and a 50-photon estimate from ONE photon map.  Reported with
+                   its noise floor (pbrt against pbrt with another pixel sampler); no bar is asserted on it.
+  cfg1_converged   the same scene, film and integrator driven to convergence on both sides: 256 spp, 4 M indirect photons
+                   and the estimate over ALL photons within maxdist 0.1 (pbrt: nused larger than any disc holds, so its heap
+                   never fills and LPhoton keeps maxdist; b2rt: nused <= 0).  Same estimator, residual noise ~0.3 %.
+  cfg3_converged   480 x 270 cut (same camera, same aspect) of BASELINE configs[2]: Cornell + glass and mirror spheres,
+                   2 M caustic + 4 M indirect photons, all photons within maxdist 0.05, 256 spp.
+pbrt shoots until the wanted photon counts are stored (photonmap.cpp:521-576); b2rt_photons_shoot follows the same rule."""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from cuda_raytrace_b200 import scenes as S   # noqa: E402
+
+GOLD = os.path.join(ROOT, "tests", "golden", "converged.npz")
+EYE, LOOK, UP, FOV = (0, 1, 3.4), (0, 1, 0), (0, 1, 0), 40
+BIG = 400000            # "nused" that no disc of the converged cases reaches: pbrt's lookup degenerates to fixed radius
+
+CASES = {
+    "cfg1_as_stated": dict(scene=dict(spheres=False, boxes=True), res=(512, 512), spp=4, nc=0, ni=200000, nused=50, maxdist=0.3,
+                           fixed=False, seeds=1),
+    "cfg1_converged": dict(scene=dict(spheres=False, boxes=True), res=(512, 512), spp=256, nc=0, ni=4000000, nused=BIG,
+                           maxdist=0.1, fixed=True, seeds=2),
+    "cfg3_converged": dict(scene=dict(spheres=True, wide=1.78), res=(480, 270), spp=256, nc=2000000, ni=4000000, nused=BIG,
+                           maxdist=0.05, fixed=True, seeds=2),
+}
+
+
+def integrator(c):
+    return ('SurfaceIntegrator "photonmap" "integer causticphotons" [%d] "integer indirectphotons" [%d] "integer nused" [%d] '
+            '"float maxdist" [%g] "bool finalgather" ["false"] "integer maxphotondepth" [5] "integer maxspeculardepth" [5]'
+            % (c["nc"], c["ni"], c["nused"], c["maxdist"]))
+
+
+def exrdiff_metrics(img, ref):
+    """pbrt-v2/src/tools/exrdiff.cpp:73-103 on RGB: avg delta %, RMS % (= 100 * sqrt(MSE), absolute as exrdiff prints it),
+    fractions of channels off by more than 0.5 % / 5 %; plus the mean relative error and the RMSE relative to the mean."""
+    a, b = np.asarray(img, np.float64), np.asarray(ref, np.float64)
+    m = S.image_metrics(a, b)
+    nz = ~((a == 0) & (b == 0))
+    with np.errstate(divide="ignore", invalid="ignore"):
+        d = np.abs(b - a) / np.where(b != 0, b, 1e-30)
+    return {"mean_rel_err_pct": 100 * m["mean_rel"], "rmse_rel_to_mean_pct": 100 * m["rmse_rel"],
+            "exrdiff_rms_pct": 100 * float(np.sqrt(((a - b) ** 2).mean())), "exrdiff_avg_delta_pct": 100 * m["bias_rel"],
+            "exrdiff_small_diff_frac": float(((d > .005) & nz).mean()), "exrdiff_big_diff_frac": float(((d > .05) & nz).mean())}
+
+
+def run_pbrt(name, c, sampler, tmp, ncores):
+    pf = os.path.join(tmp, "%s_%s.pfm" % (name, sampler))
+    scene = os.path.join(tmp, "%s_%s.pbrt" % (name, sampler))
+    with open(scene, "w") as f:
+        f.write(S.to_pbrt(S.cornell_scene(**c["scene"]), EYE, LOOK, UP, FOV, c["res"][0], c["res"][1], c["spp"], integrator(c), pf,
+                          sampler=sampler))
+    t = time.time()
+    subprocess.run([os.path.join(ROOT, "oracle", "_ref", "pbrt"), "--quiet", "--ncores", str(ncores), scene], check=True,
+                   capture_output=True)
+    return S.read_pfm(pf), time.time() - t
+
+
+def make_ref(only, ncores):
+    tmp = os.path.join(ROOT, "gpurun_out", "converged_ref")
+    os.makedirs(tmp, exist_ok=True)
+    out = dict(np.load(GOLD)) if os.path.exists(GOLD) else {}
+    for name, c in CASES.items():
+        if only and name not in only:
+            continue
+        img, secs = run_pbrt(name, c, "lowdiscrepancy", tmp, ncores)
+        out[name] = img.astype(np.float32)
+        out[name + "_seconds"] = np.float64(secs)
+        print(name, "pbrt %.1f s on %d cores, mean %.5f" % (secs, ncores, img.mean()), flush=True)
+        if name == "cfg1_as_stated":
+            # noise floor of the as-stated configuration: the reference against itself with another pixel sampler (the photon
+            # map is the same in both runs -- pbrt's photon RNG is seeded by constants -- so this floor has NO photon-map
+            # term; the GPU comparison does)
+            alt, _ = run_pbrt(name, c, "stratified", tmp, ncores)
+            out[name + "_floor"] = np.array(json.dumps(exrdiff_metrics(alt, img)))
+            print("  floor", out[name + "_floor"], flush=True)
+        np.savez_compressed(GOLD, **out)
+
+
+def gpu_image(name, c, device=0):
+    """the case through libb2rt: mean over c['seeds'] independent photon maps / sample sets"""
+    from cuda_raytrace_b200 import b2rt
+    acc, info = None, {}
+    for seed in range(c["seeds"]):
+        with b2rt.Context(device, seed=101 + seed) as ctx:
+            S.fill_scene(ctx, S.cornell_scene(**c["scene"]))
+            ctx.build_accel()
+            ctx.set_sampler("lowdiscrepancy")
+            t0 = time.time()
+            (pc, pi), (nc, ni) = ctx.photons_shoot(c["nc"], c["ni"], batch_paths=1 << 20)
+            for m in (0, 1):
+                ctx.grid_build(m)
+            cam = b2rt.pbrt_camera(EYE, LOOK, UP, FOV, c["res"][0], c["res"][1])
+            img = ctx.render_frame(cam, spp=c["spp"], nused=0 if c["fixed"] else c["nused"], max_dist=c["maxdist"],
+                                   caustic=c["nc"] > 0, indirect=c["ni"] > 0)
+            info = {"photons": [int(nc), int(ni)], "paths": [int(pc), int(pi)], "seconds_per_seed": time.time() - t0}
+        acc = img.astype(np.float64) if acc is None else acc + img
+    return (acc / c["seeds"]).astype(np.float32), info
+
+
+def compare_gpu(name, device=0):
+    gold = np.load(GOLD)
+    c = CASES[name]
+    img, info = gpu_image(name, c, device)
+    res = {"case": name, "config": {k: v for k, v in c.items() if k != "scene"}, "gpu": info,
+           "pbrt_seconds": float(gold[name + "_seconds"]), "metrics": exrdiff_metrics(img, gold[name])}
+    if name + "_floor" in gold:
+        res["pbrt_vs_pbrt_other_sampler"] = json.loads(str(gold[name + "_floor"]))
+    return res, img
+
+
+if __name__ == "__main__":
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--ref", action="store_true")
+    ap.add_argument("--gpu", action="store_true")
+    ap.add_argument("--cases", nargs="*", default=None)
+    ap.add_argument("--ncores", type=int, default=os.cpu_count())
+    a = ap.parse_args()
+    if a.ref:
+        make_ref(a.cases, a.ncores)
+    if a.gpu:
+        for nm in (a.cases or CASES):
+            r, _ = compare_gpu(nm)
+            print(json.dumps(r), flush=True)
