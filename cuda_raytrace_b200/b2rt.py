@@ -611,3 +611,148 @@ Context.irradiance = _irradiance
 Context.radiance_compute = _radiance_compute
 Context.radiance_lookup = _radiance_lookup
 Context.set_final_gather = _set_final_gather
+
+
+# ---- several GPUs of one box in ONE process (csrc/multi.cu, include/b2rt.h "b2rt_multi_*") ------------------------------
+SYMBOLS += ["b2rt_multi_create", "b2rt_multi_destroy", "b2rt_multi_last_error", "b2rt_multi_count", "b2rt_multi_ctx",
+            "b2rt_multi_info", "b2rt_multi_stats_get", "b2rt_multi_build_accel", "b2rt_multi_photons_clear",
+            "b2rt_multi_photons_trace", "b2rt_multi_photons_shoot", "b2rt_multi_photons_trace_fg",
+            "b2rt_multi_photon_grid_build", "b2rt_multi_radiance_compute", "b2rt_multi_final_gather_set",
+            "b2rt_multi_sampler_set", "b2rt_multi_film_set_filter", "b2rt_multi_render_frame"]
+EXCHANGE_MODES = {0: "fused peer stores", 1: "nccl broadcast", 2: "peer copies"}
+
+
+class MultiStats(C.Structure):
+    _fields_ = [("trace_ms", C.c_float), ("reserve_ms", C.c_float), ("exchange_ms", C.c_float), ("grid_ms", C.c_float),
+                ("render_ms", C.c_float), ("exchange_bytes", C.c_int64), ("passes", C.c_int32)]
+
+
+class _BorrowedContext(Context):
+    """A per-device context owned by a MultiContext: same methods, never destroyed from here."""
+
+    def __init__(self, lib, handle):
+        self.lib, self.h = lib, C.c_void_p(handle)
+
+    def close(self):
+        self.h = None
+
+    __del__ = close
+
+
+class MultiContext:
+    """n GPUs behind one object.  `ctxs` are the per-device contexts (scene ingestion: the same add_* calls on each, or
+    fill(lambda ctx: ...)); the photon passes, grids and frames below are sharded by the library."""
+
+    def __init__(self, ngpus, seed=0, devices=None):
+        self.lib = load()
+        L, vp, i32, i64, f = self.lib, C.c_void_p, C.c_int32, C.c_int64, C.c_float
+        L.b2rt_multi_create.argtypes = [C.c_int, vp, C.c_uint64, C.POINTER(vp)]
+        L.b2rt_multi_destroy.argtypes = [vp]
+        L.b2rt_multi_destroy.restype = None
+        L.b2rt_multi_last_error.argtypes = [vp]
+        L.b2rt_multi_last_error.restype = C.c_char_p
+        L.b2rt_multi_count.argtypes = [vp]
+        L.b2rt_multi_ctx.argtypes = [vp, C.c_int]
+        L.b2rt_multi_ctx.restype = vp
+        L.b2rt_multi_info.argtypes = [vp, C.POINTER(i32), C.POINTER(i32)]
+        L.b2rt_multi_stats_get.argtypes = [vp, C.POINTER(MultiStats), C.c_int]
+        L.b2rt_multi_build_accel.argtypes = [vp]
+        L.b2rt_multi_photons_clear.argtypes = [vp]
+        L.b2rt_multi_photons_trace.argtypes = [vp, i64, i64, i32, i32, vp]
+        L.b2rt_multi_photons_shoot.argtypes = [vp, i64, i64, i32, i64, vp, vp]
+        L.b2rt_multi_photons_trace_fg.argtypes = [vp, i64, i64, i32, vp]
+        L.b2rt_multi_photon_grid_build.argtypes = [vp, i32, f, f]
+        L.b2rt_multi_radiance_compute.argtypes = [vp, i32, f]
+        L.b2rt_multi_final_gather_set.argtypes = [vp, i32, i32, f]
+        L.b2rt_multi_sampler_set.argtypes = [vp, i32, i32, i32]
+        L.b2rt_multi_film_set_filter.argtypes = [vp, vp]
+        L.b2rt_multi_render_frame.argtypes = [vp, C.POINTER(Camera), C.POINTER(FrameParams), vp, C.c_int]
+        dev = None if devices is None else (C.c_int * ngpus)(*devices)
+        h = vp()
+        rc = L.b2rt_multi_create(ngpus, dev, seed, C.byref(h))
+        if rc:
+            raise B2rtError(rc, L.b2rt_last_error(None).decode())
+        self.h = h
+        self.ctxs = [_BorrowedContext(L, L.b2rt_multi_ctx(h, i)) for i in range(ngpus)]
+
+    def close(self):
+        if getattr(self, "h", None):
+            for c in self.ctxs:
+                c.close()
+            self.lib.b2rt_multi_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _ck(self, rc):
+        if rc:
+            raise B2rtError(rc, self.lib.b2rt_multi_last_error(self.h).decode())
+
+    def fill(self, fn):
+        """fn(ctx) on every per-device context (scene ingestion); returns the list of results"""
+        return [fn(c) for c in self.ctxs]
+
+    def info(self):
+        p, e = C.c_int32(), C.c_int32()
+        self._ck(self.lib.b2rt_multi_info(self.h, C.byref(p), C.byref(e)))
+        return {"gpus": len(self.ctxs), "peer_access": bool(p.value), "exchange": EXCHANGE_MODES.get(e.value, str(e.value))}
+
+    def stats(self, reset=False):
+        s = MultiStats()
+        self._ck(self.lib.b2rt_multi_stats_get(self.h, C.byref(s), 1 if reset else 0))
+        return {k: getattr(s, k) for k, _ in MultiStats._fields_}
+
+    def build_accel(self):
+        self._ck(self.lib.b2rt_multi_build_accel(self.h))
+        return self.ctxs[0].accel_info()
+
+    def photons_clear(self):
+        self._ck(self.lib.b2rt_multi_photons_clear(self.h))
+
+    def photons_trace(self, first_path, n_paths, max_depth=5, caustic=True, indirect=True):
+        st = (C.c_int64 * 2)()
+        self._ck(self.lib.b2rt_multi_photons_trace(self.h, first_path, n_paths, max_depth,
+                                                   (1 if caustic else 0) | (2 if indirect else 0), st))
+        return st[0], st[1]
+
+    def photons_shoot(self, n_caustic, n_indirect, max_depth=5, batch_paths=65536):
+        npaths, nst = (C.c_int64 * 2)(), (C.c_int64 * 2)()
+        self._ck(self.lib.b2rt_multi_photons_shoot(self.h, n_caustic, n_indirect, max_depth, batch_paths, npaths, nst))
+        return (npaths[0], npaths[1]), (nst[0], nst[1])
+
+    def photons_trace_fg(self, first_path, n_paths, max_depth=5):
+        st = (C.c_int64 * 2)()
+        self._ck(self.lib.b2rt_multi_photons_trace_fg(self.h, int(first_path), int(n_paths), int(max_depth), st))
+        return st[0], st[1]
+
+    def grid_build(self, which, cell_size=0.0, target_per_cell=0.0):
+        self._ck(self.lib.b2rt_multi_photon_grid_build(self.h, which, cell_size, target_per_cell))
+
+    def radiance_compute(self, nused=50, max_dist=0.1):
+        self._ck(self.lib.b2rt_multi_radiance_compute(self.h, int(nused), float(np.float32(max_dist) * np.float32(max_dist))))
+
+    def set_final_gather(self, enable=True, gather_samples=32, gather_angle=10.0):
+        self._ck(self.lib.b2rt_multi_final_gather_set(self.h, 1 if enable else 0, int(gather_samples), float(gather_angle)))
+
+    def set_sampler(self, name="random", xsamples=1, ysamples=1):
+        self._ck(self.lib.b2rt_multi_sampler_set(self.h, SAMPLERS[name] if isinstance(name, str) else int(name), int(xsamples),
+                                                 int(ysamples)))
+
+    def set_filter(self, flt=None):
+        self._ck(self.lib.b2rt_multi_film_set_filter(self.h, C.byref(flt) if flt is not None else None))
+
+    def render_frame(self, cam, spp=1, max_specular_depth=5, nused=50, max_dist=0.1, caustic=True, indirect=True,
+                     direct=True, window=None, out=None):
+        x0, x1, y0, y1 = window if window else (0, cam.xres, 0, cam.yres)
+        fp = FrameParams(spp, max_specular_depth, nused, float(np.float32(max_dist) * np.float32(max_dist)), int(caustic),
+                         int(indirect), int(direct), x0, x1, y0, y1)
+        if out is None:
+            out = np.zeros((y1 - y0, x1 - x0, 3), np.float32)
+        self._ck(self.lib.b2rt_multi_render_frame(self.h, C.byref(cam), C.byref(fp), _ptr(out), HOST))
+        return out

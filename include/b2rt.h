@@ -260,6 +260,49 @@ int b2rt_film_set_filter(b2rt_ctx *ctx, const b2rt_filter *filter);
 int b2rt_film_reconstruct(b2rt_ctx *ctx, const b2rt_filter *filter, const int32_t cells[4], int32_t spp, const float *xy,
                           const float *rgb, const int32_t pixels[4], float *out_rgb, int where);
 
+/* ---- several GPUs of one box behind the same single-threaded boundary (the reference has no multi-GPU
+ * path, one implicit device: cuda_render/cudarender.cpp:17-36).  One process, one context per device, one worker thread
+ * per device inside the library.  Results are bit-identical to the single-GPU calls for any GPU count:
+ *   - photon passes: the path range is cut into one contiguous slice per GPU; the compaction kernel of each GPU stores
+ *     its photons at their final position in the photon arrays of EVERY GPU (peer stores over NVLink: compute and exchange
+ *     in one kernel).  B2RT_MGPU_EXCHANGE=nccl selects a grouped ncclBroadcast per slice instead (libnccl.so.2 is dlopen'ed),
+ *     =copy one cudaMemcpyPeerAsync per slice (also the fallback without peer access).
+ *   - grids, radiance photons: replicated (deterministic, same bytes everywhere).
+ *   - camera pass: 64 x 64 image tiles, tile t on GPU t mod n, each GPU renders its tiles in one pass and stores the
+ *     pixels straight into the frame on GPU 0; pixel filters wider than a pixel use one row band per GPU instead.
+ * Scene, sampler, filter and final-gather settings are per context: call b2rt_add_* / b2rt_add_material / ... on
+ * b2rt_multi_ctx(m, i) for every i (same calls, same order), or the b2rt_multi_*_set helpers. */
+typedef struct b2rt_multi b2rt_multi;
+typedef struct {
+    float   trace_ms, reserve_ms, exchange_ms;   /* wall clock of the three steps of the sharded photon passes (summed) */
+    float   grid_ms, render_ms;
+    int64_t exchange_bytes;                      /* bytes of photons every GPU holds after the passes (all slices) */
+    int32_t passes;
+} b2rt_multi_stats;
+int  b2rt_multi_create(int ngpus, const int *devices /* NULL: 0 .. ngpus-1 */, uint64_t seed, b2rt_multi **out);
+void b2rt_multi_destroy(b2rt_multi *m);
+const char *b2rt_multi_last_error(b2rt_multi *m);
+int  b2rt_multi_count(b2rt_multi *m);
+b2rt_ctx *b2rt_multi_ctx(b2rt_multi *m, int i);
+/* peer_access: 1 if every pair of the devices has peer access; exchange_mode: 0 fused peer stores, 1 NCCL, 2 peer copies */
+int  b2rt_multi_info(b2rt_multi *m, int32_t *peer_access, int32_t *exchange_mode);
+int  b2rt_multi_stats_get(b2rt_multi *m, b2rt_multi_stats *out, int reset);
+int  b2rt_multi_build_accel(b2rt_multi *m);                     /* every device builds the same deterministic BVH */
+int  b2rt_multi_photons_clear(b2rt_multi *m);
+/* as b2rt_photons_trace / _shoot / _trace_fg; afterwards EVERY context holds the complete maps */
+int  b2rt_multi_photons_trace(b2rt_multi *m, int64_t first_path, int64_t n_paths, int32_t max_depth, int32_t flags,
+                              int64_t n_stored[2]);
+int  b2rt_multi_photons_shoot(b2rt_multi *m, int64_t n_caustic_wanted, int64_t n_indirect_wanted, int32_t max_depth,
+                              int64_t batch_paths, int64_t n_paths_out[2], int64_t n_stored_out[2]);
+int  b2rt_multi_photons_trace_fg(b2rt_multi *m, int64_t first_path, int64_t n_paths, int32_t max_depth, int64_t n_stored[2]);
+int  b2rt_multi_photon_grid_build(b2rt_multi *m, int32_t map, float cell_size, float target_per_cell);
+int  b2rt_multi_radiance_compute(b2rt_multi *m, int32_t nused, float max_dist2);
+int  b2rt_multi_final_gather_set(b2rt_multi *m, int32_t enable, int32_t gather_samples, float gather_angle_deg);
+int  b2rt_multi_sampler_set(b2rt_multi *m, int32_t type, int32_t xsamples, int32_t ysamples);
+int  b2rt_multi_film_set_filter(b2rt_multi *m, const b2rt_filter *filter);
+/* as b2rt_render_frame; where = B2RT_HOST, or B2RT_DEVICE for a buffer on the FIRST device of the group */
+int  b2rt_multi_render_frame(b2rt_multi *m, const b2rt_camera *cam, const b2rt_frame_params *fp, float *out_rgb, int where);
+
 /* generic device sort exposed for tests/bench of the hand-written radix sort (K2):
  * stable LSD sort of (key32,value32) pairs on `key_bits` low bits; device pointers only. */
 int b2rt_sort_pairs(b2rt_ctx *ctx, int64_t n, uint32_t *keys, uint32_t *vals, int key_bits);

@@ -11,6 +11,7 @@ for job in "$@"; do
   case $job in
     tests)    timeout 1700 python -m pytest tests -m gpu -x -q > $O/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> $O/pytest_gpu.log ;;
     tests:*)  timeout 900 python -m pytest tests -m gpu -x -q -k "${job#tests:}" > $O/pytest_k.log 2>&1; echo "pytest rc=$?" >> $O/pytest_k.log ;;
+    multitests) timeout 900 python -m pytest tests/test_gpu_multi_capi.py -m gpu -x -q > $O/pytest_multi.log 2>&1; echo "pytest rc=$?" >> $O/pytest_multi.log ;;
     fgtests)  timeout 600 python -m pytest tests/test_gpu_zfinalgather.py tests/test_gpu_photon.py -m gpu -x -q > $O/pytest_fg.log 2>&1; echo "pytest rc=$?" >> $O/pytest_fg.log ;;
     smoke)    timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > $O/smoke.log 2>&1; echo "rc=$?" >> $O/smoke.log ;;
     bench)    timeout 900 python bench.py > $O/bench.json 2> $O/bench.err; echo "bench rc=$?" >> $O/bench.err ;;
