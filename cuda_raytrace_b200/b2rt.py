@@ -614,7 +614,7 @@ Context.set_final_gather = _set_final_gather
 
 
 # ---- several GPUs of one box in ONE process (csrc/multi.cu, include/b2rt.h "b2rt_multi_*") ------------------------------
-SYMBOLS += ["b2rt_multi_create", "b2rt_multi_destroy", "b2rt_multi_last_error", "b2rt_multi_count", "b2rt_multi_ctx",
+SYMBOLS += ["b2rt_multi_create", "b2rt_multi_resize", "b2rt_multi_destroy", "b2rt_multi_last_error", "b2rt_multi_count", "b2rt_multi_ctx",
             "b2rt_multi_info", "b2rt_multi_stats_get", "b2rt_multi_build_accel", "b2rt_multi_photons_clear",
             "b2rt_multi_photons_trace", "b2rt_multi_photons_shoot", "b2rt_multi_photons_trace_fg",
             "b2rt_multi_photon_grid_build", "b2rt_multi_radiance_compute", "b2rt_multi_final_gather_set",
@@ -693,6 +693,13 @@ class MultiContext:
     def _ck(self, rc):
         if rc:
             raise B2rtError(rc, self.lib.b2rt_multi_last_error(self.h).decode())
+
+    def resize(self, ngpus, devices=None):
+        """grow the group; the new contexts copy context 0's scene and settings (then build_accel again)"""
+        self.lib.b2rt_multi_resize.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        dev = None if devices is None else (C.c_int * ngpus)(*devices)
+        self._ck(self.lib.b2rt_multi_resize(self.h, ngpus, dev))
+        self.ctxs = [_BorrowedContext(self.lib, self.lib.b2rt_multi_ctx(self.h, i)) for i in range(ngpus)]
 
     def fill(self, fn):
         """fn(ctx) on every per-device context (scene ingestion); returns the list of results"""

@@ -263,6 +263,8 @@ int status_all(b2rt_multi *m) {
 
 extern "C" {
 
+int b2rt_multi_photons_clear(b2rt_multi *m);
+
 int b2rt_multi_create(int ngpus, const int *devices, uint64_t seed, b2rt_multi **out) {
     if (!out || ngpus < 1 || ngpus > B2RT_MAX_GPUS) return B2RT_E_ARG;
     *out = nullptr;
@@ -317,6 +319,54 @@ int b2rt_multi_create(int ngpus, const int *devices, uint64_t seed, b2rt_multi *
     return B2RT_OK;
 }
 
+// Grow the group to ngpus devices: the new contexts get a copy of context 0's scene (everything b2rt_add_* staged on the
+// host side), of its materials, lights, sampler, filter and final-gather settings -- so a caller that learns the GPU
+// count late (the pbrt drop-in reads "integer gpus" from the Renderer line after the scene has been parsed) ingests
+// the scene once.  Call b2rt_multi_build_accel afterwards.  Photon maps are not copied (cleared on all).
+int b2rt_multi_resize(b2rt_multi *m, int ngpus, const int *devices) {
+    if (!m || ngpus < m->n || ngpus > B2RT_MAX_GPUS) { if (m) m->err = "multi_resize: can only grow, up to 16 devices"; return B2RT_E_ARG; }
+    if (ngpus == m->n) return B2RT_OK;
+    if (m->exchange == EXCH_NCCL) { m->err = "multi_resize: not with the NCCL exchange (communicators are created for a fixed group)"; return B2RT_E_STATE; }
+    const b2rt_ctx *c0 = m->ctx[0];
+    const int old = m->n;
+    for (int i = old; i < ngpus; ++i) {
+        const int d = devices ? devices[i] : i;
+        b2rt_ctx *c = nullptr;
+        int rc = b2rt_create(d, c0->seed, &c);
+        if (rc) { m->err = b2rt_last_error(nullptr); return rc; }
+        c->h_verts = c0->h_verts; c->h_idx = c0->h_idx; c->h_tri_prim = c0->h_tri_prim; c->h_analytic = c0->h_analytic;
+        c->h_analytic_prim = c0->h_analytic_prim; c->h_analytic_type = c0->h_analytic_type;
+        c->h_prim_material = c0->h_prim_material; c->h_prim_light = c0->h_prim_light;
+        c->h_materials = c0->h_materials; c->h_lights = c0->h_lights;
+        c->h_vnormal = c0->h_vnormal; c->h_vuv = c0->h_vuv; c->h_tri_flags = c0->h_tri_flags; c->any_attr = c0->any_attr;
+        c->n_prims = c0->n_prims;
+        c->film_filter = c0->film_filter; c->sampler_type = c0->sampler_type; c->sampler_nx = c0->sampler_nx; c->sampler_ny = c0->sampler_ny;
+        c->fg_enable = c0->fg_enable; c->fg_samples = c0->fg_samples; c->fg_cos_angle = c0->fg_cos_angle;
+        m->ctx.push_back(c); m->dev.push_back(d);
+    }
+    m->n = ngpus;
+    for (int i = 0; i < ngpus; ++i)
+        for (int j = 0; j < ngpus; ++j) {
+            if (i == j || m->dev[i] == m->dev[j] || (i < old && j < old)) continue;
+            int can = 0;
+            cudaDeviceCanAccessPeer(&can, m->dev[i], m->dev[j]);
+            if (!can) { m->peer = false; continue; }
+            cudaSetDevice(m->dev[i]);
+            cudaError_t e = cudaDeviceEnablePeerAccess(m->dev[j], 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) m->peer = false;
+            cudaGetLastError();
+        }
+    for (int i = old; i < ngpus; ++i) {
+        m->workers.push_back(new Worker());
+        m->pixmaps.push_back(new DevBuf()); m->pixmap_n.push_back(0);
+        m->bands.push_back(new DevBuf());
+        m->workers[i]->th = std::thread(worker_main, m, i);
+    }
+    m->pm_xres = m->pm_yres = 0;           // tile ownership changes with the GPU count
+    b2rt_multi_photons_clear(m);
+    return B2RT_OK;
+}
+
 void b2rt_multi_destroy(b2rt_multi *m) {
     if (!m) return;
     for (Worker *w : m->workers) {
@@ -336,6 +386,7 @@ void b2rt_multi_destroy(b2rt_multi *m) {
     delete m;
 }
 
+int b2rt_multi_photons_clear(b2rt_multi *m);
 const char *b2rt_multi_last_error(b2rt_multi *m) { return m ? m->err.c_str() : b2rt_last_error(nullptr); }
 int b2rt_multi_count(b2rt_multi *m) { return m ? m->n : 0; }
 b2rt_ctx *b2rt_multi_ctx(b2rt_multi *m, int i) { return (m && i >= 0 && i < m->n) ? m->ctx[i] : nullptr; }

@@ -280,6 +280,9 @@ typedef struct {
     int32_t passes;
 } b2rt_multi_stats;
 int  b2rt_multi_create(int ngpus, const int *devices /* NULL: 0 .. ngpus-1 */, uint64_t seed, b2rt_multi **out);
+/* grow the group: the new contexts receive a copy of context 0's staged scene, materials, lights and settings, so the
+ * scene is ingested once even when the GPU count is learnt late; call b2rt_multi_build_accel afterwards */
+int  b2rt_multi_resize(b2rt_multi *m, int ngpus, const int *devices);
 void b2rt_multi_destroy(b2rt_multi *m);
 const char *b2rt_multi_last_error(b2rt_multi *m);
 int  b2rt_multi_count(b2rt_multi *m);

@@ -88,25 +88,45 @@ static void m34(const Matrix4x4 &m, float out[12]) {
 }
 static void rgb3(const Spectrum &s, float out[3]) { s.ToRGB(out); }
 
-CudaRender::CudaRender() : ctx_(NULL), renderer_(NULL), sampler_(NULL), camera_(NULL) {
+CudaRender::CudaRender() : multi_(NULL), ctx_(NULL), renderer_(NULL), sampler_(NULL), camera_(NULL) {
     int device = 0;
     if (const char *e = getenv("B2RT_DEVICE")) device = atoi(e);
     uint64_t seed = 0;
     if (const char *e = getenv("B2RT_SEED")) seed = strtoull(e, NULL, 0);
-    int rc = b2rt_create(device, seed, &ctx_);
+    // a group of ONE GPU while the scene is parsed; Render() grows it when the Renderer line asks for more
+    int rc = b2rt_multi_create(1, &device, seed, &multi_);
     if (rc) Severe("CudaRender: %s", b2rt_last_error(NULL));      // no CPU fallback: abort like cudashape.cpp:32
+    ctx_ = b2rt_multi_ctx(multi_, 0);
 }
 
 CudaRender::~CudaRender() {
     delete renderer_;
     delete sampler_;
     delete camera_;
-    b2rt_destroy(ctx_);
+    b2rt_multi_destroy(multi_);
     if (gCudaRender == this) gCudaRender = NULL;
 }
 
 void CudaRender::check(int rc, const char *what) {
     if (rc) Severe("CudaRender: %s failed: %s", what, b2rt_last_error(ctx_));
+}
+void CudaRender::checkMulti(int rc, const char *what) {
+    if (rc) Severe("CudaRender: %s failed: %s", what, b2rt_multi_last_error(multi_));
+}
+
+// "integer gpus" (SURVEY 8(e)): how many GPUs of the box the frame is spread over
+static int gpusParam(const ParamSet &params) {
+    int def = 1;
+    if (const char *e = getenv("B2RT_GPUS")) def = atoi(e);
+    int g = params.FindOneInt("gpus", def);
+    // B2RT_GPUS_ON_ONE_DEVICE: test hook, the group is made of several contexts on the first device (a one-GPU box still
+    // runs the sharded photon pass, the tile lists and the composite)
+    const int have = getenv("B2RT_GPUS_ON_ONE_DEVICE") ? 16 : b2rt_device_count();
+    if (g <= 0 || g > have) {
+        if (g > have) Warning("CudaRender: \"gpus\" %d but %d visible, using %d", g, have, have);
+        g = have;
+    }
+    return g < 1 ? 1 : g;
 }
 
 void CudaRender::createRenderer(Sampler *sampler, Camera *camera, const ParamSet &params, const std::string &name) {
@@ -290,7 +310,17 @@ void CudaRender::Render(const Scene *scene) {
             check(b2rt_add_light(ctx_, B2RT_LIGHT_POINT, p, rgb, -1, 1, &id), "b2rt_add_light");
         }
     }
-    check(b2rt_build_accel(ctx_), "b2rt_build_accel");
+    if (renderer_->gpus > 1) {
+        // the other GPUs get a copy of the scene, lights and materials staged in the first context
+        int first = 0;
+        if (const char *e = getenv("B2RT_DEVICE")) first = atoi(e);
+        std::vector<int> devs;
+        const int have = b2rt_device_count();
+        for (int i = 0; i < renderer_->gpus; ++i) devs.push_back(getenv("B2RT_GPUS_ON_ONE_DEVICE") ? first : (first + i) % have);
+        checkMulti(b2rt_multi_resize(multi_, renderer_->gpus, devs.data()), "b2rt_multi_resize");
+        Info("CudaRender: %d GPUs", renderer_->gpus);
+    }
+    checkMulti(b2rt_multi_build_accel(multi_), "b2rt_multi_build_accel");
     renderer_->render(scene, this, camera_);
 }
 
@@ -336,9 +366,9 @@ static b2rt_camera probeCamera(const Camera *camera) {
 // private as well (film/image.h:66, filters/gaussian.h:52, mitchell.h:61, sinc.h:59); this file is compiled with
 // -fno-access-control (shim/Makefile) so the shim can read them without touching the reference's headers.
 // Hands the filter to the library; returns the ImageFilm, or NULL for a film type the shim does not know.
-static ImageFilm *useFilmFilter(b2rt_ctx *ctx, Camera *camera) {
+static ImageFilm *useFilmFilter(b2rt_multi *ctx, Camera *camera) {
     ImageFilm *film = dynamic_cast<ImageFilm *>(camera->film);
-    if (!film || !film->filter) { b2rt_film_set_filter(ctx, NULL); return NULL; }
+    if (!film || !film->filter) { b2rt_multi_film_set_filter(ctx, NULL); return NULL; }
     Filter *f = film->filter;
     b2rt_filter bf;
     bf.type = B2RT_FILTER_BOX; bf.xwidth = f->xWidth; bf.ywidth = f->yWidth; bf.p0 = bf.p1 = 0.f;
@@ -347,7 +377,7 @@ static ImageFilm *useFilmFilter(b2rt_ctx *ctx, Camera *camera) {
     else if (MitchellFilter *m = dynamic_cast<MitchellFilter *>(f)) { bf.type = B2RT_FILTER_MITCHELL; bf.p0 = m->B; bf.p1 = m->C; }
     else if (LanczosSincFilter *l = dynamic_cast<LanczosSincFilter *>(f)) { bf.type = B2RT_FILTER_SINC; bf.p0 = l->tau; }
     else if (!dynamic_cast<BoxFilter *>(f)) Warning("CudaRender: unknown pixel filter, reconstructing with a box of its widths");
-    if (b2rt_film_set_filter(ctx, &bf) != B2RT_OK) { b2rt_film_set_filter(ctx, NULL); return NULL; }
+    if (b2rt_multi_film_set_filter(ctx, &bf) != B2RT_OK) { b2rt_multi_film_set_filter(ctx, NULL); return NULL; }
     return film;
 }
 
@@ -381,13 +411,13 @@ static void writeFilm(Camera *camera, ImageFilm *film, const std::vector<float> 
 // The scene's `Sampler`: its pattern inside the pixel is reproduced on the GPU (b2rt_sampler_set) instead of pulling
 // every CameraSample through Sampler::GetMoreSamples on the CPU as the reference does (pbrtcamera.cpp:57-122).
 // stratified's strata counts are private members (samplers/stratified.h:56; this file has -fno-access-control).
-static void useSampler(b2rt_ctx *ctx, Sampler *sampler) {
+static void useSampler(b2rt_multi *ctx, Sampler *sampler) {
     int rc = B2RT_OK;
     if (StratifiedSampler *st = dynamic_cast<StratifiedSampler *>(sampler))
-        rc = b2rt_sampler_set(ctx, B2RT_SAMPLER_STRATIFIED, st->xPixelSamples, st->yPixelSamples);
-    else if (dynamic_cast<LDSampler *>(sampler)) rc = b2rt_sampler_set(ctx, B2RT_SAMPLER_LOWDISCREPANCY, 1, 1);
-    else rc = b2rt_sampler_set(ctx, B2RT_SAMPLER_RANDOM, 1, 1);       // "random" and the samplers the GPU path has no pattern for
-    if (rc != B2RT_OK) b2rt_sampler_set(ctx, B2RT_SAMPLER_RANDOM, 1, 1);
+        rc = b2rt_multi_sampler_set(ctx, B2RT_SAMPLER_STRATIFIED, st->xPixelSamples, st->yPixelSamples);
+    else if (dynamic_cast<LDSampler *>(sampler)) rc = b2rt_multi_sampler_set(ctx, B2RT_SAMPLER_LOWDISCREPANCY, 1, 1);
+    else rc = b2rt_multi_sampler_set(ctx, B2RT_SAMPLER_RANDOM, 1, 1);       // "random" and the samplers the GPU path has no pattern for
+    if (rc != B2RT_OK) b2rt_multi_sampler_set(ctx, B2RT_SAMPLER_RANDOM, 1, 1);
 }
 
 static b2rt_frame_params frameParams(const b2rt_camera &cam, Sampler *sampler) {
@@ -400,15 +430,15 @@ static b2rt_frame_params frameParams(const b2rt_camera &cam, Sampler *sampler) {
     return fp;
 }
 
-SimpleRenderer::SimpleRenderer(const ParamSet &) {}
+SimpleRenderer::SimpleRenderer(const ParamSet &params) { gpus = gpusParam(params); }
 
 void SimpleRenderer::render(const Scene *, CudaRender *cr, Camera *camera) {
     b2rt_camera cam = probeCamera(camera);
     b2rt_frame_params fp = frameParams(cam, cr->sampler());
     std::vector<float> img((size_t)cam.xres * cam.yres * 3);
-    ImageFilm *film = useFilmFilter(cr->ctx(), camera);
-    useSampler(cr->ctx(), cr->sampler());
-    cr->check(b2rt_render_frame(cr->ctx(), &cam, &fp, img.data(), B2RT_HOST), "b2rt_render_frame");
+    ImageFilm *film = useFilmFilter(cr->multi(), camera);
+    useSampler(cr->multi(), cr->sampler());
+    cr->checkMulti(b2rt_multi_render_frame(cr->multi(), &cam, &fp, img.data(), B2RT_HOST), "b2rt_multi_render_frame");
     writeFilm(camera, film, img);
 }
 
@@ -431,17 +461,19 @@ PhotonMappingRenderer::PhotonMappingRenderer(const ParamSet &params) {
     gatherSamples = params.FindOneInt("finalgathersamples", 32);
     if (PbrtOptions.quickRender) gatherSamples = max(1, gatherSamples / 4);   // photonmap.cpp:795
     gatherAngle = params.FindOneFloat("gatherangle", 10.f);
+    gpus = gpusParam(params);
 }
 
 void PhotonMappingRenderer::render(const Scene *scene, CudaRender *cr, Camera *camera) {
-    b2rt_ctx *ctx = cr->ctx();
+    b2rt_multi *mg = cr->multi();
     if (scene->lights.size() > 0 && (nCaustic > 0 || nIndirect > 0)) {
         int64_t paths[2], stored[2];
-        int64_t batch = 65536;
-        cr->check(b2rt_photons_shoot(ctx, nCaustic, nIndirect, maxPhotonDepth, batch, paths, stored), "b2rt_photons_shoot");
+        int64_t batch = 262144;           // the same for every GPU count: the stopping rule counts whole batches, and the
+                                          // image must not depend on "gpus"
+        cr->checkMulti(b2rt_multi_photons_shoot(mg, nCaustic, nIndirect, maxPhotonDepth, batch, paths, stored), "b2rt_multi_photons_shoot");
         if (stored[0] == 0 && stored[1] == 0)     // pbrt's give-up (photonmap.cpp:526-537): report, render without photon maps
             Error("Unable to store enough photons.  Giving up.\n");
-        for (int m = 0; m < 2; ++m) cr->check(b2rt_photon_grid_build(ctx, m, 0.f, 0.f), "b2rt_photon_grid_build");
+        for (int m = 0; m < 2; ++m) cr->checkMulti(b2rt_multi_photon_grid_build(mg, m, 0.f, 0.f), "b2rt_multi_photon_grid_build");
         Info("CudaRender: %lld caustic photons from %lld paths, %lld indirect photons from %lld paths",
              (long long)stored[0], (long long)paths[0], (long long)stored[1], (long long)paths[1]);
         const bool fg = finalGather && nIndirect > 0 && stored[1] > 0;
@@ -449,20 +481,20 @@ void PhotonMappingRenderer::render(const Scene *scene, CudaRender *cr, Camera *c
             // PhotonIntegrator::Preprocess with finalGather (photonmap.cpp:468-490, 383-399): direct photons and radiance
             // photons of the paths that filled the indirect map, then ComputeRadianceTask + the radiance-photon map
             int64_t st[2];
-            cr->check(b2rt_photons_trace_fg(ctx, 0, paths[1], maxPhotonDepth, st), "b2rt_photons_trace_fg");
-            cr->check(b2rt_photon_grid_build(ctx, B2RT_MAP_DIRECT, 0.f, 0.f), "b2rt_photon_grid_build");
-            cr->check(b2rt_radiance_compute(ctx, nUsed, maxDist * maxDist), "b2rt_radiance_compute");
+            cr->checkMulti(b2rt_multi_photons_trace_fg(mg, 0, paths[1], maxPhotonDepth, st), "b2rt_multi_photons_trace_fg");
+            cr->checkMulti(b2rt_multi_photon_grid_build(mg, B2RT_MAP_DIRECT, 0.f, 0.f), "b2rt_multi_photon_grid_build");
+            cr->checkMulti(b2rt_multi_radiance_compute(mg, nUsed, maxDist * maxDist), "b2rt_multi_radiance_compute");
             Info("CudaRender: final gathering, %lld direct photons, %lld radiance photons", (long long)st[0], (long long)st[1]);
         }
-        cr->check(b2rt_final_gather_set(ctx, fg ? 1 : 0, gatherSamples, gatherAngle), "b2rt_final_gather_set");
+        cr->checkMulti(b2rt_multi_final_gather_set(mg, fg ? 1 : 0, gatherSamples, gatherAngle), "b2rt_multi_final_gather_set");
     }
     b2rt_camera cam = probeCamera(camera);
     b2rt_frame_params fp = frameParams(cam, cr->sampler());
     fp.max_specular_depth = maxSpecularDepth; fp.nused = nUsed; fp.max_dist2 = maxDist * maxDist;
     fp.use_caustic = nCaustic > 0; fp.use_indirect = nIndirect > 0;
     std::vector<float> img((size_t)cam.xres * cam.yres * 3);
-    ImageFilm *film = useFilmFilter(ctx, camera);
-    useSampler(ctx, cr->sampler());
-    cr->check(b2rt_render_frame(ctx, &cam, &fp, img.data(), B2RT_HOST), "b2rt_render_frame");
+    ImageFilm *film = useFilmFilter(mg, camera);
+    useSampler(mg, cr->sampler());
+    cr->checkMulti(b2rt_multi_render_frame(mg, &cam, &fp, img.data(), B2RT_HOST), "b2rt_multi_render_frame");
     writeFilm(camera, film, img);
 }

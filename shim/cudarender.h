@@ -19,7 +19,9 @@ class CudaRender;
 // generated on the device, so the pbrt Camera itself is handed over)
 class CudaRenderer {
 public:
+    CudaRenderer() : gpus(1) {}
     virtual ~CudaRenderer() {}
+    int gpus;            // "integer gpus" of the Renderer line (default: $B2RT_GPUS, else 1; <= 0: every visible GPU)
     virtual void render(const Scene *scene, CudaRender *cudarender, Camera *camera) = 0;
 };
 
@@ -41,7 +43,9 @@ public:
                          std::vector<Reference<Primitive> > *currentInstance, const Material *material, int lightIndex);
     void objectInstance(std::vector<Reference<Primitive> > *key, const Transform &transform);
 
-    b2rt_ctx *ctx() { return ctx_; }
+    b2rt_ctx *ctx() { return ctx_; }           // context of the first GPU: scene ingestion goes here
+    b2rt_multi *multi() { return multi_; }     // the GPU group every pass runs on (one GPU unless "integer gpus" says more)
+    void checkMulti(int rc, const char *what);
     Sampler *sampler() { return sampler_; }
     // area-light prims: pbrt light index (position in scene->lights) -> b2rt primitive id of its disk
     const std::map<int, int> &lightPrims() const { return lightPrims_; }
@@ -58,6 +62,7 @@ private:
     };
     int materialId(const Material *m);
     int submit(const ShapeRec &r, const Transform *extra, int lightIndex);
+    b2rt_multi *multi_;
     b2rt_ctx *ctx_;
     CudaRenderer *renderer_;
     Sampler *sampler_;

@@ -119,3 +119,26 @@ def test_dropin_mesh_with_vertex_normals_and_uv(tmp_path):
     mb = S.image_metrics(_block(gpu[ball], 4), _block(cpu[ball], 4))
     mf = S.image_metrics(_block(gpu[ball], 4), _block(cpu_flat[ball], 4))
     assert mb["mean_rel"] < 0.015 and mf["mean_rel"] > 2 * mb["mean_rel"], (mb, mf)
+
+
+@pytest.mark.skipif(not os.path.exists(BIN), reason="shim/_build/pbrt_b2rt not built (needs /root/reference)")
+def test_dropin_integer_gpus_gives_the_same_image(tmp_path, monkeypatch):
+    """`Renderer "photonmap" "integer gpus" [3]`: the shim grows its GPU group (b2rt_multi_resize copies the parsed scene),
+    shoots the photons sharded, renders image tiles and composites on the first GPU -- the PFM must be byte-identical to
+    the one-GPU run.  On a box with fewer GPUs the group is built from contexts on one device (B2RT_GPUS_ON_ONE_DEVICE)."""
+    import torch
+    if torch.cuda.device_count() < 3:
+        monkeypatch.setenv("B2RT_GPUS_ON_ONE_DEVICE", "1")
+    prm = ('"integer causticphotons" [5000] "integer indirectphotons" [100000] "integer nused" [50] "float maxdist" [0.3] '
+           '"bool finalgather" ["false"]')
+    imgs = []
+    for g in (1, 3):
+        pf = str(tmp_path / ("gpus%d.pfm" % g))
+        scene = str(tmp_path / ("gpus%d.pbrt" % g))
+        with open(scene, "w") as f:
+            f.write(S.to_pbrt(S.cornell_scene(), EYE, LOOK, UP, FOV, 160, 100, 4, 'SurfaceIntegrator "photonmap" ' + prm, pf,
+                              renderer='Renderer "photonmap" "integer gpus" [%d] %s' % (g, prm)))
+        r = subprocess.run([BIN, "--quiet", "-c", scene], capture_output=True, text=True, timeout=600, env=dict(os.environ))
+        assert r.returncode == 0, r.stderr[-2000:]
+        imgs.append(S.read_pfm(pf))
+    assert imgs[0].max() > 0 and np.array_equal(imgs[0], imgs[1])

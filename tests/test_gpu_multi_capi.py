@@ -108,3 +108,17 @@ def test_multi_ragged_and_empty_slices(built):
         assert [m.ctxs[3].photons_download(k).tobytes() for k in (0, 1)] == want
         with pytest.raises(b2rt.B2rtError):
             m.photons_trace(0, 10, max_depth=0)
+
+
+def test_multi_resize_copies_the_scene(single):
+    """the drop-in's order of events: the scene goes into ONE context while the file is parsed, the GPU count arrives with
+    the Renderer line; b2rt_multi_resize clones the staged scene and settings into the new contexts"""
+    desc, cam, ref = single
+    with b2rt.MultiContext(1, seed=3, devices=[0]) as m:
+        S.fill_scene(m.ctxs[0], desc)
+        m.resize(3, devices=[0, 0, 0])
+        m.build_accel()
+        m.photons_trace(0, N_PATHS)
+        assert [m.ctxs[2].photons_download(k).tobytes() for k in (0, 1)] == ref["maps"]
+        m.grid_build(0); m.grid_build(1)
+        assert np.array_equal(m.render_frame(cam, spp=2, nused=40, max_dist=0.15), ref["box"])
