@@ -105,8 +105,10 @@ struct b2rt_ctx {
     int trace_pool_flip = 0;     // which of the two ray-pool counters the next speculative-kernel launch uses
     int trace_chunk = 32;        // persistent: consecutive rays a warp takes from the pool per atomicAdd
     int64_t host_chunk = 1 << 18; // rays per chunk of the host-buffer pipeline (B2RT_HOST_CHUNK)
-    int sort_variant = 1;        // K2: 1 = one-sweep (one histogram pass + one look-back scatter launch per digit), 0 = the
-                                 // three-launch pass (histogram, scan, scatter); B2RT_SORT_VARIANT
+    int sort_variant = 1;        // K2: 1 = one-sweep (one histogram pass + one look-back scatter launch per digit) for inputs
+                                 // below 2^22 pairs, the three-launch pass (histogram, scan, scatter) above; 2 = one-sweep
+                                 // always, 0 = never; B2RT_SORT_VARIANT
+    int sort_rank = 0;           // in-tile ranking: 0 = leader + shuffle, 1 = shared atomic ticket + REDUX min (B2RT_SORT_RANK)
     int photon_variant = 1;      // 0: one thread per path, 1: resident grid with path regeneration
     int photon_blocks_per_sm = 0;
     int gather_blocks_per_sm[4] = {0, 0, 0, 0};

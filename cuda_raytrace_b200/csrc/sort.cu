@@ -65,7 +65,7 @@ radix_hist_kernel(const uint32_t *__restrict__ keys, int64_t n, int shift, uint3
 __global__ void __launch_bounds__(SORT_THREADS, 4)
 radix_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__restrict__ vals_in,
                      uint32_t *__restrict__ keys_out, uint32_t *__restrict__ vals_out, int64_t n, int shift,
-                     const uint32_t *__restrict__ scanned_hist, int nblocks) {
+                     const uint32_t *__restrict__ scanned_hist, int nblocks, int rank_mode) {
     __shared__ uint32_t sh[SORT_WARPS][RADIX];  // first: running warp histogram; then: exclusive count of earlier warps
     __shared__ uint32_t s_off[RADIX];           // first tile slot of digit d
     __shared__ uint32_t s_gadj[RADIX];          // global position of digit d's first element minus s_off[d]
@@ -93,19 +93,34 @@ radix_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__res
         const uint32_t d = ok ? ((k[r] >> shift) & 0xff) : 0x100u;
         peers[r] = __match_any_sync(0xffffffffu, d);
     }
+    if (rank_mode == 0) {
 #pragma unroll
-    for (int r = 0; r < SORT_ITEMS; ++r) {
-        const bool ok = base + r * 32 + lane < n;
-        const uint32_t d = (k[r] >> shift) & 0xff;
-        const int leader = __ffs(peers[r]) - 1;
-        uint32_t before = 0;
-        if (lane == leader && ok) {
-            before = sh[warp][d];
-            sh[warp][d] = before + __popc(peers[r]);
+        for (int r = 0; r < SORT_ITEMS; ++r) {
+            const bool ok = base + r * 32 + lane < n;
+            const uint32_t d = (k[r] >> shift) & 0xff;
+            const int leader = __ffs(peers[r]) - 1;
+            uint32_t before = 0;
+            if (lane == leader && ok) {
+                before = sh[warp][d];
+                sh[warp][d] = before + __popc(peers[r]);
+            }
+            before = __shfl_sync(0xffffffffu, before, leader);
+            rank[r] = before + __popc(peers[r] & lt);
+            __syncwarp();
         }
-        before = __shfl_sync(0xffffffffu, before, leader);
-        rank[r] = before + __popc(peers[r] & lt);
-        __syncwarp();
+    } else {
+        // B2RT_SORT_RANK=1: every lane takes a ticket with a shared-memory atomic (a warp's atomics on one address are
+        // applied in instruction order, so item r is counted before item r + 1: stability); the lanes of a digit group get
+        // consecutive tickets in some order, the group's first ticket is their minimum (REDUX over the peer mask) and the
+        // stable rank inside the group is the number of lower lanes.  No leader election, no shuffle, no warp barrier.
+#pragma unroll
+        for (int r = 0; r < SORT_ITEMS; ++r) {
+            const bool ok = base + r * 32 + lane < n;
+            const uint32_t d = ok ? ((k[r] >> shift) & 0xff) : 0u;
+            const uint32_t mine = ok ? atomicAdd(&sh[warp][d], 1u) : 0u;
+            const uint32_t first = __reduce_min_sync(peers[r], mine);
+            rank[r] = first + __popc(peers[r] & lt);
+        }
     }
     __syncthreads();
     // thread d: per-warp counts of digit d -> exclusive over warps; block total -> exclusive scan over the digits
@@ -213,7 +228,7 @@ __global__ void __launch_bounds__(SORT_THREADS, 4)
 onesweep_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__restrict__ vals_in,
                         uint32_t *__restrict__ keys_out, uint32_t *__restrict__ vals_out, int64_t n, int shift,
                         const uint32_t *__restrict__ ghist /* [256] of this pass */, uint32_t *__restrict__ state /* [tiles][256] */,
-                        uint32_t *__restrict__ ticket) {
+                        uint32_t *__restrict__ ticket, int rank_mode) {
     __shared__ uint32_t sh[SORT_WARPS][RADIX];
     __shared__ uint32_t s_off[RADIX];
     __shared__ uint32_t s_gadj[RADIX];
@@ -242,19 +257,34 @@ onesweep_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__
         const uint32_t d = ok ? ((k[r] >> shift) & 0xff) : 0x100u;
         peers[r] = __match_any_sync(0xffffffffu, d);
     }
+    if (rank_mode == 0) {
 #pragma unroll
-    for (int r = 0; r < SORT_ITEMS; ++r) {
-        const bool ok = base + r * 32 + lane < n;
-        const uint32_t d = (k[r] >> shift) & 0xff;
-        const int leader = __ffs(peers[r]) - 1;
-        uint32_t before = 0;
-        if (lane == leader && ok) {
-            before = sh[warp][d];
-            sh[warp][d] = before + __popc(peers[r]);
+        for (int r = 0; r < SORT_ITEMS; ++r) {
+            const bool ok = base + r * 32 + lane < n;
+            const uint32_t d = (k[r] >> shift) & 0xff;
+            const int leader = __ffs(peers[r]) - 1;
+            uint32_t before = 0;
+            if (lane == leader && ok) {
+                before = sh[warp][d];
+                sh[warp][d] = before + __popc(peers[r]);
+            }
+            before = __shfl_sync(0xffffffffu, before, leader);
+            rank[r] = before + __popc(peers[r] & lt);
+            __syncwarp();
         }
-        before = __shfl_sync(0xffffffffu, before, leader);
-        rank[r] = before + __popc(peers[r] & lt);
-        __syncwarp();
+    } else {
+        // B2RT_SORT_RANK=1: every lane takes a ticket with a shared-memory atomic (a warp's atomics on one address are
+        // applied in instruction order, so item r is counted before item r + 1: stability); the lanes of a digit group get
+        // consecutive tickets in some order, the group's first ticket is their minimum (REDUX over the peer mask) and the
+        // stable rank inside the group is the number of lower lanes.  No leader election, no shuffle, no warp barrier.
+#pragma unroll
+        for (int r = 0; r < SORT_ITEMS; ++r) {
+            const bool ok = base + r * 32 + lane < n;
+            const uint32_t d = ok ? ((k[r] >> shift) & 0xff) : 0u;
+            const uint32_t mine = ok ? atomicAdd(&sh[warp][d], 1u) : 0u;
+            const uint32_t first = __reduce_min_sync(peers[r], mine);
+            rank[r] = first + __popc(peers[r] & lt);
+        }
     }
     __syncthreads();
     {
@@ -416,7 +446,12 @@ int b2rt_sort_pairs_impl(b2rt_ctx *ctx, int64_t n, uint32_t *keys, uint32_t *val
     int passes = (key_bits + 7) / 8;
     int nblocks = (int)((n + SORT_TILE - 1) / SORT_TILE);
     uint32_t *kin = keys, *vin = vals, *kout = keys_alt, *vout = vals_alt;
-    if (ctx->sort_variant == 1 && n < (1ll << 30) && passes <= OS_MAX_PASSES) {
+    // Measured on B200 (profiles/r04c_stage_rooflines*.json): one-sweep wins while the sort is launch-bound (2^20 pairs: 0.115
+    // against 0.138 ms) and loses for large inputs (2^26: 3.2 against 2.5 ms) -- at ~40 tiles per microsecond the per-digit
+    // look-back (one thread walks one digit's chain, one L2 round trip per predecessor) cannot keep up and the tiles
+    // convoy.  sort_variant 1 = one-sweep below 2^22 pairs, 2 = always, 0 = never.
+    const bool onesweep = ctx->sort_variant == 2 || (ctx->sort_variant == 1 && n < (1ll << 22));
+    if (onesweep && n < (1ll << 30) && passes <= OS_MAX_PASSES) {
         // one-sweep: [passes * 256 digit counts][passes tickets, padded to 64][passes * tiles * 256 look-back states]
         const size_t head = (size_t)OS_MAX_PASSES * RADIX + 64;
         const size_t words = head + (size_t)passes * nblocks * RADIX;
@@ -428,7 +463,7 @@ int b2rt_sort_pairs_impl(b2rt_ctx *ctx, int64_t n, uint32_t *keys, uint32_t *val
         B2RT_LAUNCH_CHECK(ctx);
         for (int p = 0; p < passes; ++p) {
             onesweep_scatter_kernel<<<nblocks, SORT_THREADS, 0, ctx->stream>>>(kin, vin, kout, vout, n, 8 * p, ghist + p * RADIX,
-                                                                              states + (size_t)p * nblocks * RADIX, tickets + p);
+                                                                              states + (size_t)p * nblocks * RADIX, tickets + p, ctx->sort_rank);
             B2RT_LAUNCH_CHECK(ctx);
             uint32_t *t;
             t = kin; kin = kout; kout = t;
@@ -446,7 +481,7 @@ int b2rt_sort_pairs_impl(b2rt_ctx *ctx, int64_t n, uint32_t *keys, uint32_t *val
         int rc = b2rt_exclusive_scan_u32(ctx, hist, (int64_t)RADIX * nblocks, nullptr);
         if (rc) return rc;
         radix_scatter_kernel<<<nblocks, SORT_THREADS, 0, ctx->stream>>>(kin, vin, kout, vout, n, shift, hist,
-                                                                        nblocks);
+                                                                        nblocks, ctx->sort_rank);
         B2RT_LAUNCH_CHECK(ctx);
         uint32_t *t;
         t = kin; kin = kout; kout = t;
