@@ -60,7 +60,6 @@ int b2rt_create(int device, uint64_t seed, b2rt_ctx **out) {
     if (const char *v = getenv("B2RT_TRACE_CHUNK")) ctx->trace_chunk = atoi(v);
     if (const char *v = getenv("B2RT_GATHER_VARIANT")) ctx->gather_variant = atoi(v);
     if (const char *v = getenv("B2RT_SORT_VARIANT")) ctx->sort_variant = atoi(v);
-    if (const char *v = getenv("B2RT_SORT_RANK")) ctx->sort_rank = atoi(v);
     if (const char *v = getenv("B2RT_PHOTON_VARIANT")) ctx->photon_variant = atoi(v);
     if (const char *v = getenv("B2RT_FG_VARIANT")) ctx->fg_variant = atoi(v);
     if (const char *v = getenv("B2RT_TRACE_SORT")) ctx->trace_sort = atoi(v);

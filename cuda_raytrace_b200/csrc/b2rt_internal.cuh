@@ -108,9 +108,9 @@ struct b2rt_ctx {
     int sort_variant = 1;        // K2: 1 = one-sweep (one histogram pass + one look-back scatter launch per digit) for inputs
                                  // below 2^22 pairs, the three-launch pass (histogram, scan, scatter) above; 2 = one-sweep
                                  // always, 0 = never; B2RT_SORT_VARIANT
-    int sort_rank = 0;           // in-tile ranking: 0 = leader + shuffle, 1 = shared atomic ticket + REDUX min (B2RT_SORT_RANK)
     int photon_variant = 1;      // 0: one thread per path, 1: resident grid with path regeneration
     int photon_blocks_per_sm = 0;
+    int collapse_blocks_per_sm = 0;   // occupancy of the cooperative wide-collapse kernel (build.cu)
     int gather_blocks_per_sm[4] = {0, 0, 0, 0};
     float gather_target = 1.6f;  // first gather radius: sized to hold gather_target * k photons at the local density
     int gather_tcap = 1024;      // gather variant 2: positions in the shared tile (1024 -> 7 blocks per SM, 2048 -> 5)

@@ -11,6 +11,8 @@
 // Every float result below is order-independent (min/max) or evaluated in one fixed order, and every
 // index comes from integer prefix sums, so the output bytes are identical across runs and GPUs.
 #include "b2rt_internal.cuh"
+#include <cooperative_groups.h>
+namespace cg = cooperative_groups;
 #include <math.h>
 
 namespace {
@@ -278,71 +280,82 @@ wide_collapse_level_kernel(const int32_t *__restrict__ queue_in, int nq, int n,
         if (is_openable(c[k], n, collapse)) queue_out[atomicAdd(out_count, 1u)] = c[k];
 }
 
-// The same collapse without levels and without the host: ONE launch works through a global queue of wide roots.
-// A thread claims queue slot i (atomic ticket), waits until the slot holds a node (or until everything is done), collapses
-// that root exactly as wide_collapse_level_kernel does and appends the openable children.  `pending` counts roots that are
-// queued or in work; whoever brings it to zero raises `done`.  Progress never depends on a block that is not resident yet:
-// every queued root is claimed by a thread that is already running (a waiting one, or one that takes its next ticket), so
-// the grid size only bounds the parallelism.  The queue order is scheduling-dependent but never reaches the output: a
-// root's children are a function of the binary tree alone and node indices come from the prefix sum over wide_flag.
-// The level-synchronous form cost one launch, one 4-byte download and one stream synchronisation per level (15 levels for
-// the 1 M-triangle scene: ~0.4 of the 1.0 ms build).
-// ctl[0] = next ticket, ctl[1] = queue tail, ctl[2] = pending, ctl[3] = done, ctl[5] = deepest level reached
-__global__ void __launch_bounds__(128)
-wide_collapse_queue_kernel(int n, const int32_t *__restrict__ child, const float *__restrict__ box,
-                           const uint8_t *__restrict__ collapse, WideTmp *__restrict__ tmp,
-                           uint32_t *__restrict__ wide_flag, int32_t *queue, uint8_t *level, uint32_t *ctl) {
-    volatile int32_t *vq = queue;
-    volatile uint32_t *vctl = ctl;
-    volatile uint8_t *vlevel = level;
+// The same collapse without the host: ONE cooperative launch walks the levels itself, grid.sync() between them.  The
+// level-synchronous host loop cost one launch, one 4-byte download and one stream synchronisation per level (15 levels
+// for the 1 M-triangle scene).  A first device-side version (r04c) used a single work queue with a ticket, a tail and a
+// pending counter: three same-address atomics per wide node, 568 us for 266 k nodes -- slower than the host loop.  Here the
+// only shared counter is the next level's queue tail, bumped once per warp (ballot + prefix over the lanes' child counts).
+// The queue order is scheduling-dependent but never reaches the output: a root's children are a function of the binary
+// tree alone and node indices come from the prefix sum over wide_flag.
+// ctl[0], ctl[1] = sizes of queue A / B, ctl[5] = number of levels
+__global__ void __launch_bounds__(256)
+wide_collapse_coop_kernel(int n, const int32_t *__restrict__ child, const float *__restrict__ box,
+                          const uint8_t *__restrict__ collapse, WideTmp *__restrict__ tmp,
+                          uint32_t *__restrict__ wide_flag, int32_t *qa, int32_t *qb, uint32_t *ctl) {
+    cg::grid_group grid = cg::this_grid();
+    const int lane = threadIdx.x & 31;
+    const int64_t gsize = (int64_t)gridDim.x * blockDim.x;
+    int cur = 0, levels = 0;
     for (;;) {
-        const uint32_t slot = atomicAdd(&ctl[0], 1u);
-        if (slot >= (uint32_t)(n - 1)) return;              // there are at most n - 1 internal nodes
-        int root;
-        while ((root = vq[slot]) < 0)
-            if (vctl[3]) return;
-        __threadfence();
-        const int lvl = vlevel[root];
-        int c[4]; int m = 2;
-        c[0] = child[2 * root]; c[1] = child[2 * root + 1]; c[2] = -1; c[3] = -1;
-        while (m < 4) {
-            int best = -1; float best_area = -1.f;
-            for (int k = 0; k < m; ++k) {
-                if (!is_openable(c[k], n, collapse)) continue;
-                float a = box_area(box + 6 * (int64_t)c[k]);
-                if (a > best_area) { best_area = a; best = k; }   // first max wins: deterministic
-            }
-            if (best < 0) break;
-            int node = c[best];
-            for (int k = m; k > best + 1; --k) c[k] = c[k - 1];
-            c[best] = child[2 * node]; c[best + 1] = child[2 * node + 1];
-            ++m;
-        }
-        WideTmp t;
+        const uint32_t nq = ((volatile uint32_t *)ctl)[cur];
+        if (nq == 0) break;
+        ++levels;
+        const int32_t *qin = cur ? qb : qa;
+        int32_t *qout = cur ? qa : qb;
+        // whole warps iterate together (the ballot below needs every lane)
+        for (int64_t w = (int64_t)blockIdx.x * blockDim.x + (threadIdx.x & ~31); w < (int64_t)nq; w += gsize) {
+            const int64_t qi = w + lane;
+            int open[4], no = 0;
+            if (qi < (int64_t)nq) {
+                const int root = qin[qi];
+                int c[4]; int m = 2;
+                c[0] = child[2 * root]; c[1] = child[2 * root + 1]; c[2] = -1; c[3] = -1;
+                while (m < 4) {
+                    int best = -1; float best_area = -1.f;
+                    for (int k = 0; k < m; ++k) {
+                        if (!is_openable(c[k], n, collapse)) continue;
+                        float a = box_area(box + 6 * (int64_t)c[k]);
+                        if (a > best_area) { best_area = a; best = k; }   // first max wins: deterministic
+                    }
+                    if (best < 0) break;
+                    int node = c[best];
+                    for (int k = m; k > best + 1; --k) c[k] = c[k - 1];
+                    c[best] = child[2 * node]; c[best + 1] = child[2 * node + 1];
+                    ++m;
+                }
+                WideTmp t;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) t.c[k] = c[k];
-        tmp[root] = t;
-        wide_flag[root] = 1u;
-        atomicMax(&ctl[5], (uint32_t)lvl);
-        int open[4], no = 0;
-        for (int k = 0; k < m; ++k)
-            if (is_openable(c[k], n, collapse)) open[no++] = c[k];
-        if (no > 0) {
-            const uint32_t at = atomicAdd(&ctl[1], (uint32_t)no);
-            for (int k = 0; k < no; ++k) vlevel[open[k]] = (uint8_t)min(lvl + 1, 255);
-            __threadfence();                                    // levels before the queue entries that announce them
-            for (int k = 0; k < no; ++k) vq[at + k] = open[k];
+                for (int k = 0; k < 4; ++k) t.c[k] = c[k];
+                tmp[root] = t;
+                wide_flag[root] = 1u;
+                for (int k = 0; k < m; ++k)
+                    if (is_openable(c[k], n, collapse)) open[no++] = c[k];
+            }
+            // one atomic per warp: exclusive prefix of the lanes' child counts
+            int inc = no;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                int t = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o) inc += t;
+            }
+            const int total = __shfl_sync(0xffffffffu, inc, 31);
+            uint32_t at = 0;
+            if (lane == 31 && total > 0) at = atomicAdd(&ctl[cur ^ 1], (uint32_t)total);
+            at = __shfl_sync(0xffffffffu, at, 31) + (uint32_t)(inc - no);
+            for (int k = 0; k < no; ++k) qout[at + k] = open[k];
         }
-        // this root is finished and `no` new ones are queued
-        const uint32_t before = atomicAdd(&ctl[2], (uint32_t)(no - 1));
-        if (before + (uint32_t)(no - 1) == 0u) { __threadfence(); vctl[3] = 1u; }
+        grid.sync();
+        if (blockIdx.x == 0 && threadIdx.x == 0) ((volatile uint32_t *)ctl)[cur] = 0u;     // empty for the level after next
+        cur ^= 1;
+        grid.sync();
     }
+    if (blockIdx.x == 0 && threadIdx.x == 0) ctl[5] = (uint32_t)levels;
 }
-__global__ void wide_collapse_queue_init_kernel(int32_t *queue, uint8_t *level, uint32_t *ctl, const uint8_t *collapse) {
-    // queue = {root 0} unless the whole tree collapsed into one leaf (then there is nothing to do)
+__global__ void wide_collapse_init_kernel(int32_t *qa, uint32_t *ctl, const uint8_t *collapse) {
+    // queue A = {root 0} unless the whole tree collapsed into one leaf (then there is nothing to do)
     const bool any = !collapse[0];
-    ctl[0] = 0u; ctl[1] = any ? 1u : 0u; ctl[2] = any ? 1u : 0u; ctl[3] = any ? 0u : 1u; ctl[5] = 0u;
-    if (any) { level[0] = 1; queue[0] = 0; }
+    ctl[0] = any ? 1u : 0u; ctl[1] = 0u; ctl[5] = 0u;
+    if (any) qa[0] = 0;
 }
 
 // Absolute margin added to every child box stored in a wide node: 2^-21 of the largest root-box coordinate (~4 ulps at
@@ -566,19 +579,25 @@ int b2rt_build_impl(b2rt_ctx *ctx) {
             uint32_t *wide_flag = ctx->d_wide_flag.as<uint32_t>();
             uint32_t *wide_index = ctx->d_wide_index.as<uint32_t>();
             uint32_t *counter = ctx->d_counters.as<uint32_t>();
-            int32_t *qa = ctx->d_queue_a.as<int32_t>();
-            uint8_t *level = (uint8_t *)ctx->d_queue_b.p;
+            int32_t *qa = ctx->d_queue_a.as<int32_t>(), *qb = ctx->d_queue_b.as<int32_t>();
             uint32_t *ctl = counter + 40;
             B2RT_CUDA(ctx, cudaMemsetAsync(wide_flag, 0, (size_t)nn * 4, st));
-            B2RT_CUDA(ctx, cudaMemsetAsync(qa, 0xff, (size_t)nn * 4, st));
-            wide_collapse_queue_init_kernel<<<1, 1, 0, st>>>(qa, level, ctl, collapse);
+            wide_collapse_init_kernel<<<1, 1, 0, st>>>(qa, ctl, collapse);
             B2RT_LAUNCH_CHECK(ctx);
             {
-                int64_t blocks = ((int64_t)(n - 1) + 127) / 128;
-                const int64_t cap = (int64_t)ctx->sm_count * 8;
-                if (blocks > cap) blocks = cap;
-                wide_collapse_queue_kernel<<<(unsigned)blocks, 128, 0, st>>>(n, child, bin_box, collapse, ctx->d_wide_tmp.as<WideTmp>(),
-                                                                             wide_flag, qa, level, ctl);
+                if (ctx->collapse_blocks_per_sm == 0) {
+                    B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx->collapse_blocks_per_sm, wide_collapse_coop_kernel, 256, 0));
+                    if (ctx->collapse_blocks_per_sm < 1) ctx->collapse_blocks_per_sm = 1;
+                }
+                // every block must be resident (grid.sync); more than 4 per SM only adds to the barrier
+                int64_t blocks = (int64_t)ctx->sm_count * std::min(ctx->collapse_blocks_per_sm, 4);
+                const int64_t want = ((int64_t)(n - 1) + 255) / 256;
+                if (blocks > want) blocks = want;
+                WideTmp *wtmp = ctx->d_wide_tmp.as<WideTmp>();
+                int nn_ = n;
+                const int32_t *child_ = child; const float *box_ = bin_box; const uint8_t *col_ = collapse;
+                void *args[] = {&nn_, &child_, &box_, &col_, &wtmp, &wide_flag, &qa, &qb, &ctl};
+                B2RT_CUDA(ctx, cudaLaunchCooperativeKernel((const void *)wide_collapse_coop_kernel, dim3((unsigned)blocks), dim3(256), args, 0, st));
                 B2RT_LAUNCH_CHECK(ctx);
             }
             B2RT_CUDA(ctx, cudaMemcpyAsync(wide_index, wide_flag, (size_t)(n - 1) * 4, cudaMemcpyDeviceToDevice, st));

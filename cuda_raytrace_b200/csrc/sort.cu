@@ -65,7 +65,7 @@ radix_hist_kernel(const uint32_t *__restrict__ keys, int64_t n, int shift, uint3
 __global__ void __launch_bounds__(SORT_THREADS, 4)
 radix_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__restrict__ vals_in,
                      uint32_t *__restrict__ keys_out, uint32_t *__restrict__ vals_out, int64_t n, int shift,
-                     const uint32_t *__restrict__ scanned_hist, int nblocks, int rank_mode) {
+                     const uint32_t *__restrict__ scanned_hist, int nblocks) {
     __shared__ uint32_t sh[SORT_WARPS][RADIX];  // first: running warp histogram; then: exclusive count of earlier warps
     __shared__ uint32_t s_off[RADIX];           // first tile slot of digit d
     __shared__ uint32_t s_gadj[RADIX];          // global position of digit d's first element minus s_off[d]
@@ -93,34 +93,19 @@ radix_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__res
         const uint32_t d = ok ? ((k[r] >> shift) & 0xff) : 0x100u;
         peers[r] = __match_any_sync(0xffffffffu, d);
     }
-    if (rank_mode == 0) {
 #pragma unroll
-        for (int r = 0; r < SORT_ITEMS; ++r) {
-            const bool ok = base + r * 32 + lane < n;
-            const uint32_t d = (k[r] >> shift) & 0xff;
-            const int leader = __ffs(peers[r]) - 1;
-            uint32_t before = 0;
-            if (lane == leader && ok) {
-                before = sh[warp][d];
-                sh[warp][d] = before + __popc(peers[r]);
-            }
-            before = __shfl_sync(0xffffffffu, before, leader);
-            rank[r] = before + __popc(peers[r] & lt);
-            __syncwarp();
+    for (int r = 0; r < SORT_ITEMS; ++r) {
+        const bool ok = base + r * 32 + lane < n;
+        const uint32_t d = (k[r] >> shift) & 0xff;
+        const int leader = __ffs(peers[r]) - 1;
+        uint32_t before = 0;
+        if (lane == leader && ok) {
+            before = sh[warp][d];
+            sh[warp][d] = before + __popc(peers[r]);
         }
-    } else {
-        // B2RT_SORT_RANK=1: every lane takes a ticket with a shared-memory atomic (a warp's atomics on one address are
-        // applied in instruction order, so item r is counted before item r + 1: stability); the lanes of a digit group get
-        // consecutive tickets in some order, the group's first ticket is their minimum (REDUX over the peer mask) and the
-        // stable rank inside the group is the number of lower lanes.  No leader election, no shuffle, no warp barrier.
-#pragma unroll
-        for (int r = 0; r < SORT_ITEMS; ++r) {
-            const bool ok = base + r * 32 + lane < n;
-            const uint32_t d = ok ? ((k[r] >> shift) & 0xff) : 0u;
-            const uint32_t mine = ok ? atomicAdd(&sh[warp][d], 1u) : 0u;
-            const uint32_t first = __reduce_min_sync(peers[r], mine);
-            rank[r] = first + __popc(peers[r] & lt);
-        }
+        before = __shfl_sync(0xffffffffu, before, leader);
+        rank[r] = before + __popc(peers[r] & lt);
+        __syncwarp();
     }
     __syncthreads();
     // thread d: per-warp counts of digit d -> exclusive over warps; block total -> exclusive scan over the digits
@@ -179,6 +164,8 @@ radix_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__res
 //     the launch order of blocks), ranks its 4096 keys exactly as radix_scatter_kernel does, publishes its 256 digit counts
 //     and finds its own start per digit by DECOUPLED LOOK-BACK over the tiles before it: state word = flag << 30 | value,
 //     flag 1 = the tile's own count, flag 2 = inclusive prefix over all tiles up to it.  Thread d walks digit d.
+// (Tried and dropped, r04d: ranking by shared-memory atomic tickets + REDUX min over the peer mask instead of leader +
+// shuffle -- same bytes, 2x slower at every size: 5.9 against 2.9 ms at 2^26.)
 // Determinism: the output position of a key is (keys with a smaller digit) + (same digit in earlier TILES) + (its stable
 // rank inside the tile) -- integers that do not depend on which block ran the tile or when.  Stability as before.
 constexpr uint32_t OS_FLAG_AGG = 1u << 30, OS_FLAG_INC = 2u << 30, OS_VALUE = (1u << 30) - 1u;
@@ -228,7 +215,7 @@ __global__ void __launch_bounds__(SORT_THREADS, 4)
 onesweep_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__restrict__ vals_in,
                         uint32_t *__restrict__ keys_out, uint32_t *__restrict__ vals_out, int64_t n, int shift,
                         const uint32_t *__restrict__ ghist /* [256] of this pass */, uint32_t *__restrict__ state /* [tiles][256] */,
-                        uint32_t *__restrict__ ticket, int rank_mode) {
+                        uint32_t *__restrict__ ticket) {
     __shared__ uint32_t sh[SORT_WARPS][RADIX];
     __shared__ uint32_t s_off[RADIX];
     __shared__ uint32_t s_gadj[RADIX];
@@ -257,34 +244,19 @@ onesweep_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__
         const uint32_t d = ok ? ((k[r] >> shift) & 0xff) : 0x100u;
         peers[r] = __match_any_sync(0xffffffffu, d);
     }
-    if (rank_mode == 0) {
 #pragma unroll
-        for (int r = 0; r < SORT_ITEMS; ++r) {
-            const bool ok = base + r * 32 + lane < n;
-            const uint32_t d = (k[r] >> shift) & 0xff;
-            const int leader = __ffs(peers[r]) - 1;
-            uint32_t before = 0;
-            if (lane == leader && ok) {
-                before = sh[warp][d];
-                sh[warp][d] = before + __popc(peers[r]);
-            }
-            before = __shfl_sync(0xffffffffu, before, leader);
-            rank[r] = before + __popc(peers[r] & lt);
-            __syncwarp();
+    for (int r = 0; r < SORT_ITEMS; ++r) {
+        const bool ok = base + r * 32 + lane < n;
+        const uint32_t d = (k[r] >> shift) & 0xff;
+        const int leader = __ffs(peers[r]) - 1;
+        uint32_t before = 0;
+        if (lane == leader && ok) {
+            before = sh[warp][d];
+            sh[warp][d] = before + __popc(peers[r]);
         }
-    } else {
-        // B2RT_SORT_RANK=1: every lane takes a ticket with a shared-memory atomic (a warp's atomics on one address are
-        // applied in instruction order, so item r is counted before item r + 1: stability); the lanes of a digit group get
-        // consecutive tickets in some order, the group's first ticket is their minimum (REDUX over the peer mask) and the
-        // stable rank inside the group is the number of lower lanes.  No leader election, no shuffle, no warp barrier.
-#pragma unroll
-        for (int r = 0; r < SORT_ITEMS; ++r) {
-            const bool ok = base + r * 32 + lane < n;
-            const uint32_t d = ok ? ((k[r] >> shift) & 0xff) : 0u;
-            const uint32_t mine = ok ? atomicAdd(&sh[warp][d], 1u) : 0u;
-            const uint32_t first = __reduce_min_sync(peers[r], mine);
-            rank[r] = first + __popc(peers[r] & lt);
-        }
+        before = __shfl_sync(0xffffffffu, before, leader);
+        rank[r] = before + __popc(peers[r] & lt);
+        __syncwarp();
     }
     __syncthreads();
     {
@@ -463,7 +435,7 @@ int b2rt_sort_pairs_impl(b2rt_ctx *ctx, int64_t n, uint32_t *keys, uint32_t *val
         B2RT_LAUNCH_CHECK(ctx);
         for (int p = 0; p < passes; ++p) {
             onesweep_scatter_kernel<<<nblocks, SORT_THREADS, 0, ctx->stream>>>(kin, vin, kout, vout, n, 8 * p, ghist + p * RADIX,
-                                                                              states + (size_t)p * nblocks * RADIX, tickets + p, ctx->sort_rank);
+                                                                              states + (size_t)p * nblocks * RADIX, tickets + p);
             B2RT_LAUNCH_CHECK(ctx);
             uint32_t *t;
             t = kin; kin = kout; kout = t;
@@ -481,7 +453,7 @@ int b2rt_sort_pairs_impl(b2rt_ctx *ctx, int64_t n, uint32_t *keys, uint32_t *val
         int rc = b2rt_exclusive_scan_u32(ctx, hist, (int64_t)RADIX * nblocks, nullptr);
         if (rc) return rc;
         radix_scatter_kernel<<<nblocks, SORT_THREADS, 0, ctx->stream>>>(kin, vin, kout, vout, n, shift, hist,
-                                                                        nblocks, ctx->sort_rank);
+                                                                        nblocks);
         B2RT_LAUNCH_CHECK(ctx);
         uint32_t *t;
         t = kin; kin = kout; kout = t;

@@ -247,8 +247,18 @@ def _m16(o2w):
 
 
 def to_pbrt(desc, eye, look, up, fov, xres, yres, spp, integrator, filename, renderer=None, sampler="lowdiscrepancy",
-            pixelfilter='"box"'):
-    """integrator: the full `SurfaceIntegrator ...` line.  Only features the reference's GPU path translates are used."""
+            pixelfilter='"box"', world_rotate_y=0.0):
+    """integrator: the full `SurfaceIntegrator ...` line.  Only features the reference's GPU path translates are used.
+    world_rotate_y (degrees): the whole world AND the camera are turned about the y axis -- the same picture in expectation,
+    but pbrt's constant-seeded random streams (photon directions, light samples) then produce different paths: an
+    independent realisation of the reference renderer (tools/converged_parity.py averages several)."""
+    rot = ""
+    if world_rotate_y:
+        a = np.deg2rad(world_rotate_y)
+        R = np.array([[np.cos(a), 0, np.sin(a)], [0, 1, 0], [-np.sin(a), 0, np.cos(a)]])      # pbrt Rotate(theta, y)
+        eye, look, up = R @ np.asarray(eye, float), R @ np.asarray(look, float), R @ np.asarray(up, float)
+        rot = "Rotate %.9g 0 1 0" % world_rotate_y
+    xf = "ConcatTransform" if world_rotate_y else "Transform"
     L = ["LookAt %g %g %g  %g %g %g  %g %g %g" % (*eye, *look, *up),
          'Camera "perspective" "float fov" [%g]' % fov,
          'Film "image" "integer xresolution" [%d] "integer yresolution" [%d] "string filename" ["%s"]' % (xres, yres, filename),
@@ -258,6 +268,8 @@ def to_pbrt(desc, eye, look, up, fov, xres, yres, spp, integrator, filename, ren
     if renderer:
         L.append(renderer if renderer.startswith("Renderer") else 'Renderer "%s"' % renderer)
     L.append("WorldBegin")
+    if rot:
+        L.append(rot)
     light_of_shape = {l[1]: l for l in desc["lights"] if l[0] == "disk"}
     for l in desc["lights"]:
         if l[0] == "point":
@@ -284,15 +296,15 @@ def to_pbrt(desc, eye, look, up, fov, xres, yres, spp, integrator, filename, ren
             if len(sh) > 5 and sh[5] is not None:
                 extra += ' "float uv" [%s]' % " ".join("%.9g" % v for v in np.asarray(sh[5], np.float64).reshape(-1))
             if len(sh) > 6 and sh[6] is not None:
-                L.append("  Transform [%s]" % _m16(sh[6]))
+                L.append("  %s [%s]" % (xf, _m16(sh[6])))
             L.append('  Shape "trianglemesh" "integer indices" [%s] "point P" [%s]%s' % (
                 " ".join(str(int(v)) for v in np.asarray(sh[2]).reshape(-1)),
                 " ".join("%.9g" % v for v in np.asarray(sh[1], np.float64).reshape(-1)), extra))
         elif sh[0] == "sphere":
-            L.append('  Transform [%s]\n  Shape "sphere" "float radius" [%g]' % (_m16(sh[1]), sh[3]))
+            L.append('  %s [%s]\n  Shape "sphere" "float radius" [%g]' % (xf, _m16(sh[1]), sh[3]))
         else:
-            L.append('  Transform [%s]\n  Shape "disk" "float height" [%g] "float radius" [%g] "float innerradius" [%g]' % (
-                _m16(sh[1]), sh[3], sh[4], sh[5]))
+            L.append('  %s [%s]\n  Shape "disk" "float height" [%g] "float radius" [%g] "float innerradius" [%g]' % (
+                xf, _m16(sh[1]), sh[3], sh[4], sh[5]))
         L.append("AttributeEnd")
     L.append("WorldEnd")
     return "\n".join(L) + "\n"

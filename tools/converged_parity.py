@@ -11,12 +11,16 @@ Cases
                    indirectphotons 200000, nused 50, maxdist 0.3, finalgather false, 512 x 512, lowdiscrepancy 4 spp.
                    NOT a converged image on either side: 4 spp and a 50-photon estimate from ONE photon map.  Reported with
                    its noise floor (pbrt against pbrt with another pixel sampler); no bar is asserted on it.
-  cfg1_converged   the same scene, film and integrator driven to convergence on both sides: 256 spp, 4 M indirect photons
-                   and the estimate over ALL photons within maxdist 0.1 (pbrt: nused larger than any disc holds, so its heap
-                   never fills and LPhoton keeps maxdist; b2rt: nused <= 0).  Same estimator, residual noise ~0.3 %.
+  cfg1_converged   the same scene, film and integrator (kNN estimate, nused 200 of 500 k indirect photons) driven to
+                   convergence on both sides by AVERAGING 16 independent realisations of 256 spp each.
   cfg3_converged   480 x 270 cut (same camera, same aspect) of BASELINE configs[2]: Cornell + glass and mirror spheres,
-                   0.2 M caustic + 4 M indirect photons, all photons within maxdist 0.05, 256 spp (more caustic photons
-                   would put more than `BIG` of them into one disc at the focus of the glass ball).
+                   100 k caustic + 500 k indirect photons, nused 64, maxdist 0.1 as stated; 16 realisations of 256 spp.
+Why realisations and not one big photon map: the estimate's noise is set by nused, and neither renderer can raise it far
+-- pbrt's MemoryArena never reuses blocks above 32 KB, so nused > 2048 leaks ~0.6 MB per camera sample (64 GB in 30 s,
+measured), and b2rt's selection buffers end at 224.  pbrt seeds every random stream with constants, so a second run gives
+the same photons; turning the whole world and the camera about the y axis (scenes.to_pbrt world_rotate_y) keeps the
+picture but makes the world-space photon directions of DiffuseAreaLight::Sample_L hit different geometry: independent
+photon maps.  b2rt takes a different seed per realisation.
 pbrt shoots until the wanted photon counts are stored (photonmap.cpp:521-576); b2rt_photons_shoot follows the same rule."""
 import argparse
 import json
@@ -33,18 +37,13 @@ from cuda_raytrace_b200 import scenes as S   # noqa: E402
 
 GOLD = os.path.join(ROOT, "tests", "golden", "converged.npz")
 EYE, LOOK, UP, FOV = (0, 1, 3.4), (0, 1, 0), (0, 1, 0), 40
-BIG = 40000             # "nused" that no disc of the converged cases reaches: pbrt's lookup degenerates to fixed radius.
-                        # (pbrt allocates nused ClosePhotons per estimate from an arena it frees once per 256-sample batch:
-                        # 400000 took 10 GB and was killed; 40000 is 8x the mean disc population.  --gpu verifies the
-                        # assumption: it reports the largest number of photons any sampled disc holds.)
-
 CASES = {
     "cfg1_as_stated": dict(scene=dict(spheres=False, boxes=True), res=(512, 512), spp=4, nc=0, ni=200000, nused=50, maxdist=0.3,
-                           fixed=False, seeds=1),
-    "cfg1_converged": dict(scene=dict(spheres=False, boxes=True), res=(512, 512), spp=256, nc=0, ni=4000000, nused=BIG,
-                           maxdist=0.1, fixed=True, seeds=2),
-    "cfg3_converged": dict(scene=dict(spheres=True, wide=1.78), res=(480, 270), spp=256, nc=200000, ni=4000000, nused=BIG,
-                           maxdist=0.05, fixed=True, seeds=2),
+                           realisations=1),
+    "cfg1_converged": dict(scene=dict(spheres=False, boxes=True), res=(512, 512), spp=256, nc=0, ni=500000, nused=200,
+                           maxdist=0.3, realisations=16),
+    "cfg3_converged": dict(scene=dict(spheres=True, wide=1.78), res=(480, 270), spp=256, nc=100000, ni=500000, nused=64,
+                           maxdist=0.1, realisations=16),
 }
 
 
@@ -67,12 +66,12 @@ def exrdiff_metrics(img, ref):
             "exrdiff_small_diff_frac": float(((d > .005) & nz).mean()), "exrdiff_big_diff_frac": float(((d > .05) & nz).mean())}
 
 
-def run_pbrt(name, c, sampler, tmp, ncores):
-    pf = os.path.join(tmp, "%s_%s.pfm" % (name, sampler))
-    scene = os.path.join(tmp, "%s_%s.pbrt" % (name, sampler))
+def run_pbrt(name, c, sampler, tmp, ncores, rotate=0.0):
+    pf = os.path.join(tmp, "%s_%s_%g.pfm" % (name, sampler, rotate))
+    scene = os.path.join(tmp, "%s_%s_%g.pbrt" % (name, sampler, rotate))
     with open(scene, "w") as f:
         f.write(S.to_pbrt(S.cornell_scene(**c["scene"]), EYE, LOOK, UP, FOV, c["res"][0], c["res"][1], c["spp"], integrator(c), pf,
-                          sampler=sampler))
+                          sampler=sampler, world_rotate_y=rotate))
     t = time.time()
     subprocess.run([os.path.join(ROOT, "oracle", "_ref", "pbrt"), "--quiet", "--ncores", str(ncores), scene], check=True,
                    capture_output=True)
@@ -86,10 +85,21 @@ def make_ref(only, ncores):
     for name, c in CASES.items():
         if only and name not in only:
             continue
-        img, secs = run_pbrt(name, c, "lowdiscrepancy", tmp, ncores)
-        out[name] = img.astype(np.float32)
+        K = c["realisations"]
+        acc, secs, first = None, 0.0, None
+        for k in range(K):
+            one, t = run_pbrt(name, c, "lowdiscrepancy", tmp, ncores, rotate=(360.0 * k / K + (11.0 if k else 0.0)) if K > 1 else 0.0)
+            acc = one.astype(np.float64) if acc is None else acc + one
+            first = one if first is None else first
+            secs += t
+            if k:       # how far a single realisation is from the running mean: the noise the averaging removes
+                print("  realisation %d: %.1f s, vs mean so far" % (k, t), exrdiff_metrics(one, acc / (k + 1)), flush=True)
+        img = (acc / K).astype(np.float32)
+        out[name] = img
         out[name + "_seconds"] = np.float64(secs)
-        print(name, "pbrt %.1f s on %d cores, mean %.5f" % (secs, ncores, img.mean()), flush=True)
+        if K > 1:
+            out[name + "_single_vs_mean"] = np.array(json.dumps(exrdiff_metrics(first, img)))
+        print(name, "pbrt %.1f s on %d cores (%d realisations), mean %.5f" % (secs, ncores, K, img.mean()), flush=True)
         if name == "cfg1_as_stated":
             # noise floor of the as-stated configuration: the reference against itself with another pixel sampler (the photon
             # map is the same in both runs -- pbrt's photon RNG is seeded by constants -- so this floor has NO photon-map
@@ -101,33 +111,28 @@ def make_ref(only, ncores):
 
 
 def gpu_image(name, c, device=0):
-    """the case through libb2rt: mean over c['seeds'] independent photon maps / sample sets"""
+    """the case through libb2rt: mean over c['realisations'] independent photon maps / sample sets (one seed each)"""
     from cuda_raytrace_b200 import b2rt
-    acc, info = None, {}
-    for seed in range(c["seeds"]):
+    acc, info, first = None, {}, None
+    for seed in range(c["realisations"]):
         with b2rt.Context(device, seed=101 + seed) as ctx:
             S.fill_scene(ctx, S.cornell_scene(**c["scene"]))
             ctx.build_accel()
             ctx.set_sampler("lowdiscrepancy")
             t0 = time.time()
-            (pc, pi), (nc, ni) = ctx.photons_shoot(c["nc"], c["ni"], batch_paths=1 << 20)
+            (pc, pi), (nc, ni) = ctx.photons_shoot(c["nc"], c["ni"], batch_paths=1 << 18)
             for m in (0, 1):
                 ctx.grid_build(m)
             cam = b2rt.pbrt_camera(EYE, LOOK, UP, FOV, c["res"][0], c["res"][1])
-            img = ctx.render_frame(cam, spp=c["spp"], nused=0 if c["fixed"] else c["nused"], max_dist=c["maxdist"],
-                                   caustic=c["nc"] > 0, indirect=c["ni"] > 0)
-            info = {"photons": [int(nc), int(ni)], "paths": [int(pc), int(pi)], "seconds_per_seed": time.time() - t0}
-            if c["fixed"] and seed == 0:
-                # certify the fixed-radius reading of pbrt's lookup: no disc around a visible point may hold `nused` photons
-                rays = S.pinhole_rays(c["res"][0] // 4, c["res"][1] // 4, eye=EYE, look=LOOK, fov=FOV)
-                sf = ctx.surface_at(rays)
-                sf = sf[sf["prim"] >= 0]
-                q = np.zeros(len(sf), b2rt.QUERY_DTYPE)
-                q["p"], q["n"], q["kd"] = sf["p"], sf["n"], 0.5
-                info["max_photons_in_a_disc"] = [int(ctx.gather(m, q, 0, c["maxdist"] ** 2)[2].max()) if n else 0
-                                                 for m, n in ((0, nc), (1, ni))]
+            img = ctx.render_frame(cam, spp=c["spp"], nused=c["nused"], max_dist=c["maxdist"], caustic=c["nc"] > 0,
+                                   indirect=c["ni"] > 0)
+            info = {"photons": [int(nc), int(ni)], "paths": [int(pc), int(pi)], "seconds_per_realisation": time.time() - t0}
         acc = img.astype(np.float64) if acc is None else acc + img
-    return (acc / c["seeds"]).astype(np.float32), info
+        first = img if first is None else first
+    mean = (acc / c["realisations"]).astype(np.float32)
+    if c["realisations"] > 1:
+        info["single_vs_mean"] = exrdiff_metrics(first, mean)
+    return mean, info
 
 
 def compare_gpu(name, device=0):
@@ -138,6 +143,8 @@ def compare_gpu(name, device=0):
            "pbrt_seconds": float(gold[name + "_seconds"]), "metrics": exrdiff_metrics(img, gold[name])}
     if name + "_floor" in gold:
         res["pbrt_vs_pbrt_other_sampler"] = json.loads(str(gold[name + "_floor"]))
+    if name + "_single_vs_mean" in gold:
+        res["pbrt_single_realisation_vs_its_mean"] = json.loads(str(gold[name + "_single_vs_mean"]))
     return res, img
 
 

@@ -22,8 +22,6 @@ for job in "$@"; do
     fg1080)   timeout 600 python tools/bench_fg.py 8000000 2000000 1920 1080 32 2 > $O/bench_fg_1080.jsonl 2> $O/bench_fg_1080.err; echo "rc=$?" >> $O/bench_fg_1080.err ;;
     photon)   timeout 600 python tools/bench_photon.py > $O/photon.log 2>&1 ;;
     stages)   timeout 600 python tools/bench_stages.py > $O/stages.json 2> $O/stages.err ;;
-    stagesr)  B2RT_SORT_RANK=1 timeout 600 python tools/bench_stages.py > $O/stages_sort_rank1.json 2> $O/stagesr.err ;;
-    stages0r) B2RT_SORT_VARIANT=0 B2RT_SORT_RANK=1 timeout 600 python tools/bench_stages.py > $O/stages_sort_variant0_rank1.json 2> $O/stages0r.err ;;
     buildlist) python tools/bench_stages.py 20 > $O/plain_stages.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $O/launches_stages.csv python tools/bench_stages.py 20 > $O/ncu_stages.log 2>&1 ;;
     stages0)  B2RT_SORT_VARIANT=0 timeout 600 python tools/bench_stages.py > $O/stages_sort_variant0.json 2> $O/stages0.err ;;
     cfg4)     timeout 900 python tools/bench_cfg4.py > $O/cfg4.json 2> $O/cfg4.err ;;
