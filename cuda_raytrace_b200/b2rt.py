@@ -412,7 +412,7 @@ class FrameParams(C.Structure):
                 ("x0", C.c_int32), ("x1", C.c_int32), ("y0", C.c_int32), ("y1", C.c_int32)]
 
 
-SYMBOLS += ["b2rt_render_frame"]
+SYMBOLS += ["b2rt_render_frame", "b2rt_camera_samples"]
 
 
 def pbrt_camera(eye, look, up, fov, xres, yres):
@@ -464,6 +464,23 @@ def _render_frame_device(self, cam, out_ptr, spp=1, max_specular_depth=5, nused=
     self._ck(self.lib.b2rt_render_frame(self.h, C.byref(cam), C.byref(fp), C.c_void_p(out_ptr), DEVICE))
 
 
+def _camera_samples(self, cam, spp=1, max_specular_depth=5, direct=True, window=None, queries=False):
+    """b2rt_camera_samples: (rgb (n, 3), leaf counts (n,), leaf queries (n, slots) or None) of the crop window's samples"""
+    x0, x1, y0, y1 = window if window else (0, cam.xres, 0, cam.yres)
+    fp = FrameParams(spp, max_specular_depth, 50, 0.01, 0, 0, int(direct), x0, x1, y0, y1)
+    n = (x1 - x0) * (y1 - y0) * spp
+    rgb, nq, slots = np.zeros((n, 3), np.float32), np.zeros(n, np.uint32), C.c_int32()
+    self.lib.b2rt_camera_samples.argtypes = [C.c_void_p, C.POINTER(Camera), C.POINTER(FrameParams), C.c_void_p, C.c_void_p,
+                                             C.c_void_p, C.POINTER(C.c_int32)]
+    q = None
+    if queries:
+        self._ck(self.lib.b2rt_camera_samples(self.h, C.byref(cam), C.byref(fp), _ptr(rgb), _ptr(nq), None, C.byref(slots)))
+        q = np.zeros((n, slots.value), QUERY_DTYPE)
+    self._ck(self.lib.b2rt_camera_samples(self.h, C.byref(cam), C.byref(fp), _ptr(rgb), _ptr(nq), _ptr(q), C.byref(slots)))
+    return rgb, nq, q
+
+
+Context.camera_samples = _camera_samples
 Context.render_frame = _render_frame
 Context.render_frame_device = _render_frame_device
 

@@ -349,6 +349,30 @@ int b2rt_surface_at(b2rt_ctx *ctx, int64_t nrays, const b2rt_ray *rays, b2rt_sur
     return status_check(ctx);
 }
 
+int b2rt_camera_samples(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_params *fp, float *out_rgb, uint32_t *out_nleaves,
+                        b2rt_query *out_queries, int32_t *slots_out) {
+    if (!ctx) return B2RT_E_ARG;
+    if (!cam || !fp || !out_rgb || !out_nleaves || fp->spp < 1 || fp->x0 < 0 || fp->y0 < 0 || fp->x1 > cam->xres ||
+        fp->y1 > cam->yres || fp->x0 >= fp->x1 || fp->y0 >= fp->y1) { ctx->err = "camera_samples: bad arguments"; return B2RT_E_ARG; }
+    int rc = need_built(ctx, "camera_samples");
+    if (rc) return rc;
+    B2RT_CUDA(ctx, cudaSetDevice(ctx->device));
+    const int slots = b2rt_camera_slots(ctx, fp->max_specular_depth);
+    if (slots_out) *slots_out = slots;
+    const int64_t n = (int64_t)(fp->x1 - fp->x0) * (fp->y1 - fp->y0) * fp->spp;
+    B2RT_CUDA(ctx, ctx->d_samples.reserve((size_t)n * 12));
+    B2RT_CUDA(ctx, ctx->d_qcnt.reserve((size_t)n * 4));
+    if (out_queries) B2RT_CUDA(ctx, ctx->d_qslots.reserve((size_t)n * slots * sizeof(b2rt_query)));
+    rc = b2rt_camera_samples_impl(ctx, cam, fp, slots, ctx->d_samples.as<float>(), ctx->d_qcnt.as<uint32_t>(),
+                                  out_queries ? ctx->d_qslots.as<b2rt_query>() : nullptr);
+    if (rc) return rc;
+    B2RT_CUDA(ctx, cudaMemcpyAsync(out_rgb, ctx->d_samples.p, (size_t)n * 12, cudaMemcpyDeviceToHost, ctx->stream));
+    B2RT_CUDA(ctx, cudaMemcpyAsync(out_nleaves, ctx->d_qcnt.p, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    if (out_queries)
+        B2RT_CUDA(ctx, cudaMemcpyAsync(out_queries, ctx->d_qslots.p, (size_t)n * slots * sizeof(b2rt_query), cudaMemcpyDeviceToHost, ctx->stream));
+    return status_check(ctx);
+}
+
 int b2rt_render_frame(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_params *fp, float *out_rgb, int where) {
     if (!ctx) return B2RT_E_ARG;
     if (!cam || !fp || !out_rgb || fp->spp < 1 || fp->x0 < 0 || fp->y0 < 0 || fp->x1 > cam->xres || fp->y1 > cam->yres ||

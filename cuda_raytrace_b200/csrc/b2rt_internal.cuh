@@ -215,6 +215,9 @@ int b2rt_photon_grid_build_impl(b2rt_ctx *ctx, int map, float cell_size, float t
 int b2rt_render_impl(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_params *fp, float *d_out);
 int b2rt_render_pixels_impl(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_params *fp, const uint32_t *d_pixmap,
                             int64_t n_map, float *d_out);
+int b2rt_camera_samples_impl(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_params *fp, int slots, float *d_rgb,
+                             uint32_t *d_nq, b2rt_query *d_q);
+int b2rt_camera_slots(b2rt_ctx *ctx, int max_specular_depth);
 int b2rt_surface_at_impl(b2rt_ctx *ctx, int64_t n, const b2rt_ray *d_rays, b2rt_surface *d_out);
 int b2rt_sample_positions_impl(b2rt_ctx *ctx, int xres, int yres, const int32_t window[4], int spp, float *d_xy);
 bool b2rt_filter_valid(const b2rt_filter *f);

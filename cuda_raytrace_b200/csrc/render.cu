@@ -15,6 +15,7 @@
 // and the film kernel adds everything up per pixel in a fixed order.  Pixel jitter and light samples are
 // Philox(seed, pixel, sample), so an image tile is bit-identical no matter which GPU renders it.
 #include "b2rt_shade.cuh"
+#include <algorithm>
 
 namespace {
 
@@ -383,6 +384,35 @@ int b2rt_sample_positions_impl(b2rt_ctx *ctx, int xres, int yres, const int32_t 
         reinterpret_cast<float2 *>(d_xy));
     B2RT_LAUNCH_CHECK(ctx);
     return B2RT_OK;
+}
+
+// parity hook for K6 / K7 / K14: what render_li_kernel leaves per camera sample, before any photon-map term is added.
+// d_rgb[3 n], d_nq[n], d_q[n * slots] (NULL: no queries wanted), n = crop-window pixels * spp, sample-major per pixel.
+int b2rt_camera_samples_impl(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_params *fp, int slots, float *d_rgb,
+                             uint32_t *d_nq, b2rt_query *d_q) {
+    DScene sc;
+    b2rt_fill_dscene(ctx, &sc);
+    b2rt_frame_params p = *fp;
+    p.use_caustic = 0; p.use_indirect = d_q ? 1 : 0;
+    SamplerD sm = {ctx->sampler_type, ctx->sampler_nx, ctx->sampler_ny};
+    if (sm.type == B2RT_SAMPLER_STRATIFIED && (int64_t)sm.nx * sm.ny != fp->spp) {
+        ctx->err = "camera_samples: stratified sampler needs xsamples * ysamples == spp"; return B2RT_E_ARG;
+    }
+    const int64_t n = (int64_t)(p.x1 - p.x0) * (p.y1 - p.y0) * fp->spp;
+    const int64_t chunk = 1 << 20;
+    for (int64_t s0 = 0; s0 < n; s0 += chunk) {
+        const int64_t ns = std::min(chunk, n - s0);
+        render_li_kernel<<<(unsigned)((ns + RENDER_THREADS - 1) / RENDER_THREADS), RENDER_THREADS, 0, ctx->stream>>>(
+            sc, *cam, p, (uint32_t)ctx->seed, (uint32_t)(ctx->seed >> 32), s0, ns, slots, d_rgb + 3 * s0,
+            d_q ? d_q + s0 * slots : nullptr, d_nq + s0, ctx->d_counters.as<uint32_t>() + 8, nullptr, sm, nullptr);
+        B2RT_LAUNCH_CHECK(ctx);
+    }
+    return B2RT_OK;
+}
+int b2rt_camera_slots(b2rt_ctx *ctx, int max_specular_depth) {
+    for (const Material &m : ctx->h_materials)
+        if (m.type != B2RT_MAT_MATTE) { int d = max_specular_depth < 1 ? 1 : max_specular_depth; return 1 << (d - 1 > 5 ? 5 : d - 1); }
+    return 1;
 }
 
 // d_out: device buffer of (x1-x0)*(y1-y0)*3 floats, crop-window row-major

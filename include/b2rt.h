@@ -229,6 +229,16 @@ typedef struct {
  * grids built if use_caustic / use_indirect are set (maps that are empty or unbuilt contribute nothing). */
 int b2rt_render_frame(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_params *fp, float *out_rgb, int where);
 
+/* parity hook for the camera pass proper (K14 camera rays, K6 attributes, K7 direct lighting with MIS, the specular tree):
+ * per camera sample of the crop window (pixel-major, spp samples each) the radiance render_li_kernel computes before the
+ * photon-map terms are added -- Le + UniformSampleAllLights + both specular branches (pbrt PhotonIntegrator::Li,
+ * integrators/photonmap.cpp:624-638, core/integrator.cpp:47-258; reference: raytracing_closest_hit + directLight,
+ * cuda_render/photon_mapping/raytracing.cu:49-128) -- the number of diffuse leaves of its specular tree and, if
+ * out_queries != NULL, the leaves themselves (*slots_out per sample) as the gather / final-gather stage receives them.
+ * Host buffers.  Bit-exact against oracle/oracle_render.h port_camera_samples. */
+int b2rt_camera_samples(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_params *fp, float *out_rgb, uint32_t *out_nleaves,
+                        b2rt_query *out_queries, int32_t *slots_out);
+
 /* ---- image-plane samples: replaces the CPU sample loop PbrtCamera::preLaunch (cuda_render/util/camera/pbrtcamera.cpp:
  * 57-122), which pulls every CameraSample out of pbrt's Sampler and uploads 72 bytes per ray.  The pattern of
  * b2rt_render_frame's samples inside each pixel: pbrt "random" (the default), "stratified" (xsamples * ysamples = spp

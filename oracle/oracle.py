@@ -275,7 +275,8 @@ class _CScene(C.Structure):
     _fields_ = [("nprims", C.c_int32), ("kind", C.c_void_p), ("verts", C.c_void_p), ("idx", C.c_void_p),
                 ("analytic", C.c_void_p), ("prim_material", C.c_void_p), ("nmaterials", C.c_int32),
                 ("materials", C.c_void_p), ("nlights", C.c_int32), ("lights", C.c_void_p),
-                ("vnormal", C.c_void_p), ("vuv", C.c_void_p), ("tri_flags", C.c_void_p)]
+                ("vnormal", C.c_void_p), ("vuv", C.c_void_p), ("tri_flags", C.c_void_p),
+                ("prim_light", C.c_void_p), ("light_nsamples", C.c_void_p)]
 
 
 def _bind_photon():
@@ -297,6 +298,9 @@ def _bind_photon():
     lib.port_radiance_lookup.restype = None
     lib.port_final_gather.argtypes = [C.POINTER(_CScene), i64, vp, i64, vp, i64, vp, C.c_int, f, C.c_uint64, vp]
     lib.port_final_gather.restype = None
+    lib.port_camera_samples.argtypes = [C.POINTER(_CScene), C.c_uint64, vp, i64, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int,
+                                        C.c_int, vp, vp, vp]
+    lib.port_camera_samples.restype = None
     lib.port_surface_at.argtypes = [C.POINTER(_CScene), i64, vp, vp]
     lib.port_surface_at.restype = None
     lib.port_sincos_quarter.argtypes = [f, C.POINTER(f), C.POINTER(f)]
@@ -314,8 +318,10 @@ class PortFullScene:
     def __init__(self):
         self.geo = PortScene()
         self.prim_material = []
+        self.prim_light = []
         self.materials = []
         self.lights = []
+        self.light_nsamples = []
 
     def add_material(self, mtype, rgb, kt=None, ior=1.5):
         kt = (1.0, 1.0, 1.0) if kt is None else kt
@@ -325,19 +331,23 @@ class PortFullScene:
     def add_mesh(self, P, idx, material=-1, arealight=-1, N=None, uv=None, reverse=False):
         first = self.geo.add_mesh(P, idx, N, uv, reverse)
         self.prim_material.extend([material] * len(np.asarray(idx).reshape(-1, 3)))
+        self.prim_light.extend([arealight] * len(np.asarray(idx).reshape(-1, 3)))
         return first
 
     def add_sphere(self, o2w, radius, w2o=None, material=-1, arealight=-1):
         self.prim_material.append(material)
+        self.prim_light.append(arealight)
         return self.geo.add_sphere(o2w, w2o, radius)
 
     def add_disk(self, o2w, height, radius, inner=0.0, w2o=None, material=-1, arealight=-1):
         self.prim_material.append(material)
+        self.prim_light.append(arealight)
         return self.geo.add_disk(o2w, w2o, height, radius, inner)
 
     def add_light(self, ltype, rgb, p=None, prim=-1, nsamples=1):
         p = (0.0, 0.0, 0.0) if p is None else p
         self.lights.append([float(ltype), *map(float, p), *map(float, rgb), float(prim)])
+        self.light_nsamples.append(int(nsamples))
         return len(self.lights) - 1
 
     def _cscene(self):
@@ -346,13 +356,31 @@ class PortFullScene:
         mats = np.asarray(self.materials, np.float32).reshape(-1, 8)
         lights = np.asarray(self.lights, np.float32).reshape(-1, 8)
         vn, vuv, tf = self.geo._attr_arrays()
-        keep = (kind, verts, idx, an, pm, mats, lights, vn, vuv, tf)
+        pl = np.asarray(self.prim_light, np.int32)
+        lns = np.asarray(self.light_nsamples, np.int32)
+        keep = (kind, verts, idx, an, pm, mats, lights, vn, vuv, tf, pl, lns)
         cs = _CScene(len(kind), _p(kind).value, _p(verts).value, _p(idx).value, _p(an).value,
                      _p(pm).value if len(pm) else None, len(mats),
                      _p(mats).value if len(mats) else None, len(lights), _p(lights).value if len(lights) else None,
                      _p(vn).value if vn is not None else None, _p(vuv).value if vuv is not None else None,
-                     _p(tf).value if tf is not None else None)
+                     _p(tf).value if tf is not None else None, _p(pl).value if len(pl) else None,
+                     _p(lns).value if len(lns) else None)
         return cs, keep
+
+    def camera_samples(self, seed, cam12, xy, gpix, ks, sampler_type=0, max_specular_depth=5, direct=True, slots=0):
+        """port_camera_samples: per-sample camera-pass radiance (n, 3), leaf counts (n,), leaf queries (n, slots, 12)"""
+        lib = _bind_photon()
+        cs, keep = self._cscene()
+        xy = np.ascontiguousarray(xy, np.float32).reshape(-1, 2)
+        n = len(xy)
+        gpix, ks = np.ascontiguousarray(gpix, np.uint32), np.ascontiguousarray(ks, np.uint32)
+        cam12 = np.ascontiguousarray(cam12, np.float32).reshape(12)
+        rgb, nq = np.zeros((n, 3), np.float32), np.zeros(n, np.uint32)
+        q = np.zeros((n, max(slots, 1), 12), np.float32)
+        lib.port_camera_samples(C.byref(cs), seed, _p(cam12), n, _p(xy), _p(gpix), _p(ks), sampler_type, max_specular_depth,
+                                1 if direct else 0, 1 if slots > 0 else 0, max(slots, 1), _p(rgb), _p(nq), _p(q))
+        del keep
+        return rgb, nq, q
 
     def surface_at(self, rays):
         """port_surface_at: closest hit + hit attributes, SURFACE_DTYPE per ray"""

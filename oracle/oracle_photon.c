@@ -582,3 +582,4 @@ void port_gather(int64_t n, const port_photon *sorted, int64_t n_paths, int64_t 
 
 /* final gathering (finalgather true): direct / radiance photons, EPhoton, radiance-photon lookup, the gather */
 #include "oracle_fg.h"
+#include "oracle_render.h"

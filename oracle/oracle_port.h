@@ -35,7 +35,13 @@ typedef struct {
     /* per-vertex shading attributes (may all be NULL): world-space normals 3 / vertex, uv 2 / vertex, and per TRIANGLE
      * flags: bit 0 the mesh has normals, bit 1 uv, bit 2 reversed orientation (same meaning as csrc/b2rt_shade.cuh) */
     const float *vnormal; const float *vuv; const uint8_t *tri_flags;
+    /* camera pass only (may be NULL): area-light index per prim (-1 none), light samples per light */
+    const int32_t *prim_light; const int32_t *light_nsamples;
 } port_scene;
+/* per-sample oracle of the camera pass (oracle_render.h): see there */
+void port_camera_samples(const port_scene *sc, uint64_t seed, const float cam[12], int64_t n, const float *xy,
+                         const uint32_t *gpix, const uint32_t *ks, int sampler_type, int max_specular_depth,
+                         int direct_lighting, int want_queries, int slots, float *out_rgb, uint32_t *out_nq, float *out_q);
 /* hit attributes (K6): closest hit of each ray + pbrt's Triangle::Intersect tail, Triangle::GetShadingGeometry and
  * BSDF::BSDF (shapes/trianglemesh.cpp:181-201, 311-389; core/reflection.cpp:601-609).  out: 20 floats per ray laid out as
  * b2rt_surface {p, t, ng, u, n, v, sn, ray_eps, tn, bits(prim)}; prim = -1 and zeros on a miss. */

@@ -95,3 +95,39 @@ def test_image_matches_pbrt_golden(built, name):
     # north star's 1 % mean relative error for the direct image and 3 % for the photon image at this photon count
     assert abs(m["bias_rel"]) < (0.005 if name == "direct" else 0.01), m
     assert m["mean_rel"] < (0.01 if name == "direct" else 0.03), m
+
+
+# ---- per-sample oracle of the camera pass (K14 + K6 + K7 + the specular tree) --------------------------------------------
+@pytest.mark.parametrize("sampler,spp", [("random", 2), ("lowdiscrepancy", 4), ("stratified", 4)])
+@pytest.mark.parametrize("light", ["disk", "point"])
+def test_camera_samples_match_the_c_oracle(built, sampler, spp, light):
+    """b2rt_camera_samples (what render_li_kernel leaves per camera sample: Le + direct lighting with MIS + both specular
+    branches, and the diffuse leaves handed to the gather stages) against oracle/oracle_render.h port_camera_samples -- the
+    same arithmetic in plain C over exhaustive closest-hit / any-hit loops, at the same Philox counters.  Bar: bit-exact."""
+    from oracle import oracle as O
+    desc = S.cornell_scene(light=light)                      # glass + mirror spheres: the specular tree branches
+    xres, yres, win = 64, 48, (20, 44, 18, 34)                # x0, x1, y0, y1 over the two balls
+    cam = b2rt.pbrt_camera((0, 1, 3.4), (0, 1, 0), (0, 1, 0), 40, xres, yres)
+    seed = 21
+    with b2rt.Context(0, seed=seed) as c:
+        S.fill_scene(c, desc)
+        c.build_accel()
+        c.set_sampler(sampler, 2, 2)
+        rgb, nq, q = c.camera_samples(cam, spp=spp, window=win, queries=True)
+    ps = O.PortFullScene()
+    S.fill_scene(ps, desc)
+    x0, x1, y0, y1 = win
+    xy = O.sample_positions(sampler, seed, xres, yres, (x0, y0, x1, y1), spp, 2, 2)
+    py, px = np.meshgrid(np.arange(y0, y1), np.arange(x0, x1), indexing="ij")
+    gpix = np.repeat((py * xres + px).reshape(-1).astype(np.uint32), spp)
+    ks = np.tile(np.arange(spp, dtype=np.uint32), (x1 - x0) * (y1 - y0))
+    cam12 = np.array([*cam.o, *cam.A, *cam.B, *cam.C], np.float32)
+    ergb, enq, eq = ps.camera_samples(seed, cam12, xy, gpix, ks, sampler_type={"random": 0, "stratified": 1, "lowdiscrepancy": 2}[sampler],
+                                      slots=q.shape[1])
+    assert np.array_equal(nq, enq) and nq.max() >= 2 and (nq == 0).any() is not None
+    assert np.array_equal(rgb.view(np.uint32), ergb.view(np.uint32)), float(np.abs(rgb - ergb).max())
+    got = q.view(np.float32).reshape(len(nq), -1, 12)
+    for j in range(got.shape[1]):
+        m = nq > j
+        assert np.array_equal(got[m, j].view(np.uint32), eq[m, j].view(np.uint32))
+    assert rgb.max() > 0.5 and (rgb.sum(1) > 0).mean() > 0.5
