@@ -265,49 +265,97 @@ def workload_config(args, ntris):
             "sharding": "rank r traces sample r of every pixel against its own replicated BVH (no collective)"}
 
 
-def photon_frame_extra(local_rank, world, rank):
-    """Not part of `value`: stage timings of the photon-mapping frame, BASELINE configs[2] (Cornell + glass / mirror
-    spheres, 10 M stored photons, kNN k = 64, 1920x1080, 1 spp).  Wall clock around synchronised stages, max over
-    ranks; for N > 1 emission is split by path range + NCCL all-gather, the image by bands gathered on rank 0."""
-    import torch
-    import torch.distributed as dist
-    from cuda_raytrace_b200 import b2rt, scenes as S, multigpu as M
-    ctx = b2rt.Context(local_rank, seed=3)
-    S.fill_scene(ctx, S.cornell_scene(spheres=True, wide=1.78))
-    ctx.build_accel()
+def photon_frame_extra(n_gpus, peak_gbs, cpu_baseline=True):
+    """Not part of `value`: the other two clauses of the metric, "photons traced+gathered/s" and "ms/frame", on BASELINE
+    configs[2] (Cornell + glass / mirror spheres, ~10 M stored photons, kNN k = 64, 1920x1080, 1 spp).  ONE process drives
+    all n_gpus through the multi-GPU layer of the C ABI (b2rt_multi_*, csrc/multi.cu): photon paths sharded by index range
+    with the exchange fused into the compaction kernel (peer stores over NVLink), replicated grids, 64 x 64 image tiles
+    composited on GPU 0.  Stage times are DEVICE times: CUDA events on every GPU's library stream around the stage, max
+    over the GPUs; median of 5 after 1 warm-up.  SHA-256 of both photon maps and of the frame are emitted so that the
+    records of different GPU counts can be compared (the bytes must not depend on N)."""
+    import hashlib
+    from cuda_raytrace_b200 import b2rt, scenes as S
+    n_paths = 24_000_000      # yields ~12 M indirect + ~0.53 M caustic photons in this scene
+    k, maxdist = 64, 0.1
+    desc = S.cornell_scene(spheres=True, wide=1.78)
     cam = b2rt.pbrt_camera((0, 1, 3.4), (0, 1, 0), (0, 1, 0), 40, 1920, 1080)
-    frame_out = ctx.pinned_empty((1080, 1920, 3))     # the image lands in page-locked memory
-    n_paths = 24_000_000      # yields ~10.4 M indirect + ~0.53 M caustic photons in this scene
-    best = None
-    for rep in range(4):
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize(); t0 = time.perf_counter()
-        if world > 1:
-            nc, ni = M.shoot_sharded(ctx, n_paths)
-        else:
-            ctx.photons_clear()
-            nc, ni = ctx.photons_trace(0, n_paths)
-        ctx.sync(); t1 = time.perf_counter()
-        ctx.grid_build(0); ctx.grid_build(1)
-        ctx.sync(); t2 = time.perf_counter()
-        if world > 1:
-            M.render_sharded(ctx, cam, spp=1, nused=64, max_dist=0.1)
-        else:
-            ctx.render_frame(cam, spp=1, nused=64, max_dist=0.1, out=frame_out)
-        torch.cuda.synchronize(); t3 = time.perf_counter()
-        tt = torch.tensor([t1 - t0, t2 - t1, t3 - t2, t3 - t0], dtype=torch.float64, device="cuda")
-        if world > 1:
-            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        tt = (tt * 1e3).tolist()
-        if rep >= 1 and (best is None or tt[3] < best[3]):
-            best = tt
-    ctx.close()
-    return {"workload": "Cfg3: Cornell + glass/mirror spheres, %d emitted paths -> %d caustic + %d indirect photons, kNN k=64, "
-                        "maxdist 0.1, 1920x1080 1 spp" % (n_paths, nc, ni),
-            "shoot_allgather_ms": best[0], "grid_build_ms": best[1], "camera_pass_ms": best[2], "frame_ms": best[3],
-            "photons_traced_and_gathered_per_s": (nc + ni) / (best[3] * 1e-3), "paths_per_s": n_paths / (best[0] * 1e-3),
-            "timing": "wall clock, best of 3 after 1 warm-up, max over ranks"}
+    out = {}
+    with b2rt.MultiContext(n_gpus, seed=3) as m:
+        m.fill(lambda c: S.fill_scene(c, desc))
+        m.build_accel()
+        frame = m.ctxs[0].pinned_empty((1080, 1920, 3))
+
+        def timed(fn):
+            for c in m.ctxs:
+                c.timer_start()
+            r = fn()
+            return r, max(c.timer_stop() for c in m.ctxs)
+        rows = []
+        for rep in range(6):
+            m.photons_clear()
+            (nc, ni), t_shoot = timed(lambda: m.photons_trace(0, n_paths))
+            _, t_grid = timed(lambda: (m.grid_build(0), m.grid_build(1)))
+            _, t_cam = timed(lambda: m.render_frame(cam, spp=1, nused=k, max_dist=maxdist, out=frame))
+            if rep:
+                rows.append((t_shoot, t_grid, t_cam, t_shoot + t_grid + t_cam))
+        med = [float(np.median([r[j] for r in rows])) for j in range(4)]
+        st = m.stats(reset=True)
+        sha = {"caustic_map": hashlib.sha256(m.ctxs[-1].photons_download(0).tobytes()).hexdigest(),
+               "indirect_map": hashlib.sha256(m.ctxs[-1].photons_download(1).tobytes()).hexdigest(),
+               "frame": hashlib.sha256(np.ascontiguousarray(frame).tobytes()).hexdigest()}
+        g0, g1 = m.ctxs[0].grid_info(0), m.ctxs[0].grid_info(1)
+        nq = 1920 * 1080          # one diffuse leaf per pixel is the floor; specular pixels add leaves
+        grid_bytes = 204.0 * (nc + ni)                                  # 188 B / photon (SURVEY 8(d)) + the 16-B position copy
+        gather_bytes = 16.0 * (nc + ni) + 2 * nq * (32.0 * k + 60.0)     # every position once + k records and 60 B per query and map
+        out = {"workload": "Cfg3: Cornell + glass/mirror spheres, %d emitted paths -> %d caustic + %d indirect photons, kNN k=%d, "
+                           "maxdist %g, 1920x1080 1 spp" % (n_paths, nc, ni, k, maxdist),
+               "api": "b2rt_multi_photons_trace / b2rt_multi_photon_grid_build / b2rt_multi_render_frame (C ABI, one process, %d GPU%s)"
+                      % (n_gpus, "" if n_gpus == 1 else "s"),
+               "multi": m.info(),
+               "shoot_exchange_ms": med[0], "grid_build_ms": med[1], "camera_pass_ms": med[2], "frame_ms": med[3],
+               "photons_traced_and_gathered_per_s": (nc + ni) / (med[3] * 1e-3), "paths_per_s": n_paths / (med[0] * 1e-3),
+               "gather_queries_per_s": 2 * nq / (med[2] * 1e-3),
+               "exchange": {"bytes_held_per_gpu": st["exchange_bytes"] // max(st["passes"], 1),
+                            "bus_GBs": ((n_gpus - 1) / n_gpus * st["exchange_bytes"] / max(st["passes"], 1)) /
+                                       max(st["exchange_ms"] / max(st["passes"], 1) * 1e-3, 1e-9) / 1e9 if n_gpus > 1 else None,
+                            "host_wall_ms_per_pass": {kk: st[kk] / max(st["passes"], 1) for kk in ("trace_ms", "reserve_ms", "exchange_ms")}},
+               "roofline": {"grid_build": {"bound": "hbm", "algorithmic_bytes": grid_bytes, "achieved": grid_bytes / (med[1] * 1e-3) / 1e9,
+                                           "peak": peak_gbs, "unit": "GB/s", "frac": grid_bytes / (med[1] * 1e-3) / 1e9 / peak_gbs,
+                                           "note": "replicated on every GPU: does not shrink with N"},
+                            "camera_pass_gather": {"bound": "issue slots / L2 (not HBM)", "algorithmic_bytes": gather_bytes,
+                                                   "achieved": gather_bytes / (med[2] * 1e-3) / 1e9 * n_gpus ** 0, "peak": peak_gbs, "unit": "GB/s",
+                                                   "frac": gather_bytes / (med[2] * 1e-3) / 1e9 / (peak_gbs * n_gpus),
+                                                   "note": "16 N + (32 k + 60) Q per map; the time also holds the camera rays and direct lighting"}},
+               "sha256": sha, "grid_cells": [list(g0.dims), list(g1.dims)],
+               "timing": "CUDA events on each GPU's library stream around the stage, max over GPUs, median of 5 after 1 warm-up"}
+        if cpu_baseline:
+            # the reference's CPU path for the same clauses, bounded sample: PhotonIntegrator::Preprocess (photons/s, kd-tree
+            # build included) and KdTree lookup + LPhoton (calls/s) on the GPU's own photons
+            from oracle import oracle as O
+            if O.ref_available():
+                nth = os.cpu_count() or 1
+                rp = O.RefPhotonScene()
+                S.fill_scene(rp, desc)
+                t0 = time.perf_counter()
+                pc_, pi_, paths_ = rp.shoot(20000, 400000, ncores=0)
+                t_pre = time.perf_counter() - t0
+                sub = m.ctxs[0].photons_download(1)[:2_000_000]
+                nqs = 200_000
+                rays = S.pinhole_rays(640, 360, eye=(0, 1, 3.4), look=(0, 1, 0), fov=40)
+                sf = m.ctxs[0].surface_at(rays)
+                sf = sf[sf["prim"] >= 0][:nqs]
+                q = np.zeros(len(sf), b2rt.QUERY_DTYPE)
+                q["p"], q["n"], q["kd"] = sf["p"], sf["n"], 0.5
+                _, t_build, t_look = rp.lphoton_timed(O.photons_to9(sub), n_paths * len(sub) // max(ni, 1), q, k, maxdist * maxdist, nth)
+                out["cpu_baseline"] = {
+                    "kind": "reference", "cores": nth,
+                    "preprocess": {"value": (len(pc_) + len(pi_)) / t_pre, "unit": "photons stored/s",
+                                   "sample": "pbrt-v2 PhotonIntegrator::Preprocess, 20 k caustic + 400 k indirect photons wanted (%d + %d stored from "
+                                             "%d paths), kd-tree builds included, %.2f s" % (len(pc_), len(pi_), max(paths_), t_pre)},
+                    "lphoton": {"value": len(q) / t_look, "unit": "estimates/s",
+                                "sample": "KdTree::Lookup + LPhoton, k = %d, %d visible points against %d of the GPU's indirect photons; "
+                                          "kd-tree build %.2f s (excluded), lookups %.2f s" % (k, len(q), len(sub), t_build, t_look)}}
+    return out
 
 
 def main():
@@ -453,7 +501,15 @@ def main():
     N1, N2 = counts.tolist()
 
     ctx.close()
-    extra = None if args.no_photon_extra else photon_frame_extra(local_rank, world, rank)
+    # The photon-frame clauses run in ONE process over all N GPUs (the library's own multi-GPU layer), so the other ranks
+    # are done: they leave (and release their GPUs) before rank 0 starts it.
+    del d_rays, d_shadow, d_hits, d_occ, flush
+    torch.cuda.empty_cache()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+        if rank != 0:
+            return
     if rank == 0:
         peaks = {}
         pk_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
@@ -461,6 +517,12 @@ def main():
             peaks = json.load(open(pk_path))
         peak = peaks.get("hbm_gbs", 6650.0)
         peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
+        extra = None
+        if not args.no_photon_extra:
+            try:
+                extra = photon_frame_extra(world, peak, cpu_baseline=not args.no_cpu_baseline)
+            except Exception as e:                      # the headline line must survive a failure of the extra
+                extra = {"error": "%s: %s" % (type(e).__name__, e)}
         per_launch_ms = ms_closest / args.steps
         achieved = 48.0 * n1 / (per_launch_ms * 1e-3) / 1e9
         value = (N1 + N2) * args.steps / (ms_total_m * 1e-3) / 1e6
@@ -498,8 +560,6 @@ def main():
                 line["parity"] = hit_parity(gpu_hits_np, gpu_occ_np, ref_hits)
                 ref_hits["close"]()
         emit(line)
-    if world > 1:
-        dist.destroy_process_group()
 
 
 if __name__ == "__main__":

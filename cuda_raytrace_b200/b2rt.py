@@ -361,6 +361,12 @@ def _grid_build(self, which, cell_size=0.0, target_per_cell=0.0):
     return gi
 
 
+def _grid_info(self, which):
+    gi = GridInfo()
+    self._ck(self.lib.b2rt_photon_grid_info(self.h, which, C.byref(gi)))
+    return gi
+
+
 def _grid_download(self, which):
     gi = GridInfo()
     self._ck(self.lib.b2rt_photon_grid_info(self.h, which, C.byref(gi)))
@@ -396,7 +402,7 @@ def _gather_sets(self, which, queries, k, max_dist2):
 for _n, _f in [("photons_trace", _photons_trace), ("photons_shoot", _photons_shoot), ("photons_clear", _photons_clear),
                ("photons_count", _photons_count), ("photons_download", _photons_download),
                ("photons_upload", _photons_upload), ("grid_build", _grid_build), ("grid_download", _grid_download),
-               ("gather", _gather), ("gather_sets", _gather_sets)]:
+               ("gather", _gather), ("gather_sets", _gather_sets), ("grid_info", _grid_info)]:
     setattr(Context, _n, _f)
 
 

@@ -358,11 +358,13 @@ int b2rt_sync(b2rt_ctx *ctx) {
 
 int b2rt_timer_start(b2rt_ctx *ctx) {
     if (!ctx) return B2RT_E_ARG;
+    B2RT_CUDA(ctx, cudaSetDevice(ctx->device));        // a caller that drives several contexts may have another device current
     B2RT_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
     return B2RT_OK;
 }
 int b2rt_timer_stop(b2rt_ctx *ctx, float *ms) {
     if (!ctx || !ms) return B2RT_E_ARG;
+    B2RT_CUDA(ctx, cudaSetDevice(ctx->device));
     B2RT_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
     B2RT_CUDA(ctx, cudaEventSynchronize(ctx->ev1));
     B2RT_CUDA(ctx, cudaEventElapsedTime(ms, ctx->ev0, ctx->ev1));

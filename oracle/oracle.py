@@ -582,6 +582,20 @@ class RefPhotonScene:
         return out
 
 
+def _ref_lphoton_timed(self, photons9, n_paths, queries, k, max_dist2, nthreads):
+    """pbrt's KdTree build + LPhoton over all queries on nthreads threads: (rgb, kd-tree build seconds, lookup seconds)"""
+    ph = np.ascontiguousarray(photons9, np.float32).reshape(-1, 9)
+    q = np.ascontiguousarray(queries).view(np.float32).reshape(-1, 12)
+    out = np.zeros((len(q), 3), np.float32)
+    b, l = C.c_double(), C.c_double()
+    self.lib.ref_pm_lphoton_timed.argtypes = [C.c_int64, C.c_void_p, C.c_int, C.c_int64, C.c_void_p, C.c_int, C.c_float, C.c_int,
+                                              C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    self.lib.ref_pm_lphoton_timed.restype = None
+    self.lib.ref_pm_lphoton_timed(len(ph), _p(ph), int(n_paths), len(q), _p(q), int(k), float(max_dist2), int(nthreads), _p(out),
+                                  C.byref(b), C.byref(l))
+    return out, b.value, l.value
+
+
 def _ref_ephoton(self, photons9, n_paths, queries, k, max_dist2):
     """The reference's own EPhoton over its own kd-tree: (nq, 3)."""
     ph = np.ascontiguousarray(photons9, np.float32).reshape(-1, 9)
@@ -601,6 +615,7 @@ def _ref_radiance_lookup(self, photons9, queries):
 
 
 RefPhotonScene.ephoton = _ref_ephoton
+RefPhotonScene.lphoton_timed = _ref_lphoton_timed
 RefPhotonScene.radiance_lookup = _ref_radiance_lookup
 
 

@@ -34,6 +34,10 @@
 #include "textures/constant.h"
 #include "lights/point.h"
 #include "lights/diffuse.h"
+#include <atomic>
+#include <thread>
+#include <chrono>
+#include <algorithm>
 #include <vector>
 
 namespace refpm {
@@ -192,6 +196,52 @@ void ref_pm_lphoton(int64_t n, const float *photons, int n_paths, int64_t nq, co
         arena.FreeAll();
     }
     delete map;
+}
+
+// The same estimator as a TIMED, multi-threaded loop (the CPU baseline of the gather stage: bench.py): kd-tree build and
+// lookups timed apart; ranges of 1024 queries handed out by an atomic cursor, one arena / lookup buffer per thread.
+void ref_pm_lphoton_timed(int64_t n, const float *photons, int n_paths, int64_t nq, const float *queries, int k,
+                          float max_dist2, int nthreads, float *rgb_out, double *build_seconds, double *lookup_seconds) {
+    std::vector<refpm::Photon> v((size_t)n);
+    for (int64_t i = 0; i < n; ++i) {
+        const float *p = photons + 9 * i;
+        v[i] = refpm::Photon(Point(p[0], p[1], p[2]), rgb(p + 3), Vector(p[6], p[7], p[8]));
+    }
+    auto t0 = std::chrono::steady_clock::now();
+    KdTree<refpm::Photon> *map = n ? new KdTree<refpm::Photon>(v) : NULL;
+    auto t1 = std::chrono::steady_clock::now();
+    std::atomic<int64_t> cursor(0);
+    auto work = [&]() {
+        std::vector<refpm::ClosePhoton> buf((size_t)(k > 0 ? k : 1));
+        MemoryArena arena;
+        RNG rng(1);
+        for (;;) {
+            const int64_t lo = cursor.fetch_add(1024);
+            if (lo >= nq) break;
+            for (int64_t q = lo; q < std::min(nq, lo + 1024); ++q) {
+                const float *Q = queries + 12 * q;
+                Normal nn(Q[3], Q[4], Q[5]);
+                Vector dpdu, dpdv;
+                CoordinateSystem(Vector(nn), &dpdu, &dpdv);
+                DifferentialGeometry dg(Point(Q[0], Q[1], Q[2]), dpdu, dpdv, Normal(0, 0, 0), Normal(0, 0, 0), 0.f, 0.f, NULL);
+                dg.nn = nn;
+                BSDF *bsdf = BSDF_ALLOC(arena, BSDF)(dg, nn);
+                bsdf->Add(BSDF_ALLOC(arena, Lambertian)(rgb(Q + 6)));
+                Intersection isect;
+                isect.dg = dg;
+                Spectrum L = refpm::LPhoton(map, n_paths, k, &buf[0], bsdf, rng, isect, Vector(nn), max_dist2);
+                L.ToRGB(rgb_out + 3 * q);
+                arena.FreeAll();
+            }
+        }
+    };
+    std::vector<std::thread> th;
+    for (int t = 0; t < std::max(1, nthreads); ++t) th.emplace_back(work);
+    for (auto &t : th) t.join();
+    auto t2 = std::chrono::steady_clock::now();
+    delete map;
+    if (build_seconds) *build_seconds = std::chrono::duration<double>(t1 - t0).count();
+    if (lookup_seconds) *lookup_seconds = std::chrono::duration<double>(t2 - t1).count();
 }
 
 // pbrt's irradiance estimate on caller-supplied photons: KdTree<Photon> build + Lookup + EPhoton (photonmap.cpp:263-283).
