@@ -16,6 +16,10 @@ for job in "$@"; do
     smoke)    timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > $O/smoke.log 2>&1; echo "rc=$?" >> $O/smoke.log ;;
     bench)    timeout 900 python bench.py > $O/bench.json 2> $O/bench.err; echo "bench rc=$?" >> $O/bench.err ;;
     benchq)   timeout 600 python bench.py --steps 20 > $O/bench.json 2> $O/bench.err; echo "bench rc=$?" >> $O/bench.err ;;
+    bench2)   timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29533 bench.py --gpus 2 --steps 50 > $O/bench_n2.json 2> $O/bench_n2.err; echo "rc=$?" >> $O/bench_n2.err ;;
+    bench4)   timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node 4 --master-addr 127.0.0.1 --master-port 29534 bench.py --gpus 4 --steps 50 > $O/bench_n4.json 2> $O/bench_n4.err; echo "rc=$?" >> $O/bench_n4.err ;;
+    bench8)   timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29538 bench.py --gpus 8 --steps 50 > $O/bench_n8.json 2> $O/bench_n8.err; echo "rc=$?" >> $O/bench_n8.err ;;
+    topo)     nvidia-smi topo -m > $O/topo.txt 2>&1 ;;
     benchref) timeout 600 python bench.py --impl reference --steps 5 --warmup 1 > $O/bench_ref.json 2> $O/bench_ref.err ;;
     fg540)    timeout 300 python tools/bench_fg.py 1000000 100000 960 540 32 2 > $O/bench_fg_540.jsonl 2> $O/bench_fg_540.err; echo "rc=$?" >> $O/bench_fg_540.err ;;
     fg540v0)  B2RT_FG_VARIANT=0 timeout 300 python tools/bench_fg.py 1000000 100000 960 540 32 1 > $O/bench_fg_540_v0.jsonl 2> $O/bench_fg_540_v0.err ;;
