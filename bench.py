@@ -337,11 +337,11 @@ def photon_frame_extra(n_gpus, peak_gbs, cpu_baseline=True):
                 rp = O.RefPhotonScene()
                 S.fill_scene(rp, desc)
                 t0 = time.perf_counter()
-                pc_, pi_, paths_ = rp.shoot(20000, 400000, ncores=0)
+                pc_, pi_, paths_ = rp.shoot(100000, 4000000, ncores=0)
                 t_pre = time.perf_counter() - t0
-                sub = m.ctxs[0].photons_download(1)[:2_000_000]
-                nqs = 200_000
-                rays = S.pinhole_rays(640, 360, eye=(0, 1, 3.4), look=(0, 1, 0), fov=40)
+                sub = m.ctxs[0].photons_download(1)[:4_000_000]
+                nqs = 2_000_000
+                rays = S.pinhole_rays(1920, 1080, eye=(0, 1, 3.4), look=(0, 1, 0), fov=40)
                 sf = m.ctxs[0].surface_at(rays)
                 sf = sf[sf["prim"] >= 0][:nqs]
                 q = np.zeros(len(sf), b2rt.QUERY_DTYPE)
@@ -350,7 +350,7 @@ def photon_frame_extra(n_gpus, peak_gbs, cpu_baseline=True):
                 out["cpu_baseline"] = {
                     "kind": "reference", "cores": nth,
                     "preprocess": {"value": (len(pc_) + len(pi_)) / t_pre, "unit": "photons stored/s",
-                                   "sample": "pbrt-v2 PhotonIntegrator::Preprocess, 20 k caustic + 400 k indirect photons wanted (%d + %d stored from "
+                                   "sample": "pbrt-v2 PhotonIntegrator::Preprocess, 100 k caustic + 4 M indirect photons wanted (%d + %d stored from "
                                              "%d paths), kd-tree builds included, %.2f s" % (len(pc_), len(pi_), max(paths_), t_pre)},
                     "lphoton": {"value": len(q) / t_look, "unit": "estimates/s",
                                 "sample": "KdTree::Lookup + LPhoton, k = %d, %d visible points against %d of the GPU's indirect photons; "
