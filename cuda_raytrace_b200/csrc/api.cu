@@ -63,6 +63,7 @@ int b2rt_create(int device, uint64_t seed, b2rt_ctx **out) {
     if (const char *v = getenv("B2RT_PHOTON_VARIANT")) ctx->photon_variant = atoi(v);
     if (const char *v = getenv("B2RT_FG_VARIANT")) ctx->fg_variant = atoi(v);
     if (const char *v = getenv("B2RT_TRACE_SORT")) ctx->trace_sort = atoi(v);
+    if (const char *v = getenv("B2RT_TRACE_PLANES")) ctx->trace_planes = atoi(v);
     if (const char *v = getenv("B2RT_FILM_VARIANT")) ctx->film_variant = atoi(v);
     if (const char *v = getenv("B2RT_GATHER_QT")) ctx->gather_qt = atoi(v);
     if (const char *v = getenv("B2RT_GATHER_TCAP")) ctx->gather_tcap = atoi(v);

@@ -14,6 +14,7 @@
 // Node boxes are tested conservatively (padded slab test) so the tree never hides a primitive that
 // the exhaustive loop (renderers/aggregatetest.cpp:93-102) would accept.
 #include "b2rt_device.cuh"
+#include <type_traits>
 
 namespace {
 
@@ -205,8 +206,14 @@ trace_persistent_kernel(const WideNode *__restrict__ nodes, const PrimRec *__res
 // Box tests only prune; accepted primitives and their (t, b1, b2) are computed by the same expressions, so the
 // results are bit-identical to the other variants.
 // SORT: 2 = children visited in full near-to-far order, 1 = nearest first, the rest in slot order, 0 = slot order
-template <bool ANY, int SORT>
-__global__ void __launch_bounds__(PT_THREADS)
+// PL (B2RT_TRACE_PLANES, default on): the near and far plane of every slab are picked by the SIGN of the ray direction --
+// as the ADDRESS of the 16-byte load, lo or hi array of the node -- instead of min / max per child: the same entry and exit
+// distances (rounded subtraction and multiplication are monotonic, so (lo - o) * id <= (hi - o) * id for id >= 0 and the
+// reverse for id < 0, with the clamped reciprocal also for d = +-0) with 6 instead of 12 FMNMX per child.  ncu r04i: the
+// ALU pipe (min / max, selects, compares) is the busiest pipe of this kernel, 48 / 54 % of its peak at 18 / 21.6 active
+// threads per instruction.
+template <bool ANY, int SORT, bool PL>
+__global__ void __launch_bounds__(PT_THREADS, ANY ? 8 : 7)
 trace_spec_kernel(const WideNode *__restrict__ nodes, const PrimRec *__restrict__ recs,
                   const AnalyticPrim *__restrict__ analytic, const b2rt_ray *__restrict__ rays,
                   b2rt_hit *__restrict__ hits, uint8_t *__restrict__ occ, int64_t nrays,
@@ -222,6 +229,7 @@ trace_spec_kernel(const WideNode *__restrict__ nodes, const PrimRec *__restrict_
 
     RayD r;
     float idx = 0.f, idy = 0.f, idz = 0.f;
+    int sg_ = 0;                            // PL: bit a set = direction component a is negative (near plane = hi array)
     float best_t = 0.f, best_b1 = 0.f, best_b2 = 0.f;
     int best_prim = 0x7fffffff;
     bool found = false, active = false, exhausted = false;
@@ -251,6 +259,7 @@ trace_spec_kernel(const WideNode *__restrict__ nodes, const PrimRec *__restrict_
                 r.dx = r1.x; r.dy = r1.y; r.dz = r1.z;
                 r.ddx = r1.x; r.ddy = r1.y; r.ddz = r1.z;
                 idx = slab_rcp(r1.x); idy = slab_rcp(r1.y); idz = slab_rcp(r1.z);
+                if (PL) sg_ = (signbit(idx) ? 1 : 0) | (signbit(idy) ? 2 : 0) | (signbit(idz) ? 4 : 0);
                 best_t = r1.w; best_prim = 0x7fffffff; best_b1 = 0.f; best_b2 = 0.f;
                 found = false; sp = 0; cur = 0; leaf = NONE; my = i; active = true;
             }
@@ -265,8 +274,11 @@ trace_spec_kernel(const WideNode *__restrict__ nodes, const PrimRec *__restrict_
             // ---- node loop: descend; park the first leaf met and keep going until the whole warp has one ---------
             while (cur >= 0 && cur != NONE) {
                 const float4 *np = reinterpret_cast<const float4 *>(nodes + cur);
-                const float4 lox = __ldg(np), hix = __ldg(np + 1), loy = __ldg(np + 2), hiy = __ldg(np + 3),
-                             loz = __ldg(np + 4), hiz = __ldg(np + 5);
+                // PL: lox / loy / loz hold the NEAR planes, hix / hiy / hiz the FAR ones (picked by the load address)
+                const int nx_ = sg_ & 1, ny_ = 2 + ((sg_ >> 1) & 1), nz_ = 4 + ((sg_ >> 2) & 1);
+                const float4 lox = __ldg(np + (PL ? nx_ : 0)), hix = __ldg(np + (PL ? (nx_ ^ 1) : 1)),
+                             loy = __ldg(np + (PL ? ny_ : 2)), hiy = __ldg(np + (PL ? (ny_ ^ 1) : 3)),
+                             loz = __ldg(np + (PL ? nz_ : 4)), hiz = __ldg(np + (PL ? (nz_ ^ 1) : 5));
                 const int4 ch = __ldg(reinterpret_cast<const int4 *>(np + 6));
                 float tn[4]; int32_t cr[4];
                 const float lx[4] = {lox.x, lox.y, lox.z, lox.w}, hx[4] = {hix.x, hix.y, hix.z, hix.w};
@@ -278,8 +290,10 @@ trace_spec_kernel(const WideNode *__restrict__ nodes, const PrimRec *__restrict_
                     const float t0x = (lx[k] - r.ox) * idx, t1x = (hx[k] - r.ox) * idx;
                     const float t0y = (ly[k] - r.oy) * idy, t1y = (hy[k] - r.oy) * idy;
                     const float t0z = (lz[k] - r.oz) * idz, t1z = (hz[k] - r.oz) * idz;
-                    const float tnear = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), r.tmin));
-                    const float tfar = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), best_t));
+                    const float tnear = PL ? fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, r.tmin))
+                                           : fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), r.tmin));
+                    const float tfar = PL ? fminf(fminf(t1x, t1y), fminf(t1z, best_t))
+                                          : fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), best_t));
                     const float tn_p = __fmaf_rn(fabsf(tnear), -2e-6f, tnear);      // conservative pad, one FFMA each
                     const float tf_p = __fmaf_rn(fabsf(tfar), 2e-6f, tfar);
                     const bool h = (tn_p <= tf_p) && (cr[k] != B2RT_CHILD_EMPTY);
@@ -376,8 +390,8 @@ int b2rt_trace_impl(b2rt_ctx *ctx, int64_t n, const b2rt_ray *d_rays, b2rt_hit *
         // persistent grid: every SM holds as many blocks as the occupancy calculator allows
         int &per_sm = ctx->pt_blocks_per_sm[(spec ? 2 : 0) + (any_hit ? 1 : 0)];
         if (per_sm == 0 && spec) {
-            if (any_hit) B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_spec_kernel<true, 0>, PT_THREADS, 0));
-            else B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_spec_kernel<false, 2>, PT_THREADS, 0));
+            if (any_hit) B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_spec_kernel<true, 0, true>, PT_THREADS, 0));
+            else B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_spec_kernel<false, 2, true>, PT_THREADS, 0));
             if (per_sm < 1) per_sm = 1;
         }
         if (per_sm == 0) {
@@ -403,10 +417,14 @@ int b2rt_trace_impl(b2rt_ctx *ctx, int64_t n, const b2rt_ray *d_rays, b2rt_hit *
             // default (trace_sort < 0): closest-hit rays visit children near to far; any-hit rays take them in slot order
             // (no sorting network: +9 % / +5 % on the 1 M / 8 M-triangle shadow rays, run r02b; for closest-hit rays slot
             // order costs 25-35 % and nearest-first-only is +2 % / -5 %)
-            auto kern = any_hit ? trace_spec_kernel<true, 0> : trace_spec_kernel<false, 2>;
-            if (ctx->trace_sort == 2) kern = any_hit ? trace_spec_kernel<true, 2> : trace_spec_kernel<false, 2>;
-            if (ctx->trace_sort == 1) kern = any_hit ? trace_spec_kernel<true, 1> : trace_spec_kernel<false, 1>;
-            if (ctx->trace_sort == 0) kern = any_hit ? trace_spec_kernel<true, 0> : trace_spec_kernel<false, 0>;
+            const int so = ctx->trace_sort < 0 ? (any_hit ? 0 : 2) : ctx->trace_sort;
+            auto pick = [&](auto planes) {
+                constexpr bool P = decltype(planes)::value;
+                if (so == 2) return any_hit ? trace_spec_kernel<true, 2, P> : trace_spec_kernel<false, 2, P>;
+                if (so == 1) return any_hit ? trace_spec_kernel<true, 1, P> : trace_spec_kernel<false, 1, P>;
+                return any_hit ? trace_spec_kernel<true, 0, P> : trace_spec_kernel<false, 0, P>;
+            };
+            auto kern = ctx->trace_planes ? pick(std::true_type()) : pick(std::false_type());
             kern<<<(unsigned)blocks, PT_THREADS, 0, ctx->stream>>>(nodes, recs, an, d_rays, any_hit ? nullptr : d_hits,
                                                                    any_hit ? d_occ : nullptr, n, pool, ctx->trace_refill,
                                                                    chunk, status, next_pool);

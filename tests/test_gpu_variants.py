@@ -11,7 +11,8 @@ from oracle import oracle as O
 from cuda_raytrace_b200 import b2rt, scenes as S
 
 pytestmark = pytest.mark.gpu
-_KEYS = ("B2RT_TRACE_VARIANT", "B2RT_TRACE_REFILL", "B2RT_TRACE_CHUNK", "B2RT_PHOTON_VARIANT", "B2RT_GATHER_VARIANT")
+_KEYS = ("B2RT_TRACE_VARIANT", "B2RT_TRACE_REFILL", "B2RT_TRACE_CHUNK", "B2RT_PHOTON_VARIANT", "B2RT_GATHER_VARIANT",
+         "B2RT_TRACE_PLANES", "B2RT_TRACE_SORT")
 
 
 def _ctx(seed, **env):
@@ -50,6 +51,8 @@ def terrain(built):
     dict(B2RT_TRACE_VARIANT=1), dict(B2RT_TRACE_VARIANT=1, B2RT_TRACE_REFILL=20),
     dict(B2RT_TRACE_VARIANT=2), dict(B2RT_TRACE_VARIANT=2, B2RT_TRACE_REFILL=12),
     dict(B2RT_TRACE_VARIANT=2, B2RT_TRACE_REFILL=32, B2RT_TRACE_CHUNK=96),
+    dict(B2RT_TRACE_VARIANT=2, B2RT_TRACE_PLANES=0), dict(B2RT_TRACE_VARIANT=2, B2RT_TRACE_PLANES=1, B2RT_TRACE_SORT=1),
+    dict(B2RT_TRACE_VARIANT=2, B2RT_TRACE_PLANES=1, B2RT_TRACE_SORT=0),
 ], ids=lambda e: "-".join("%s%s" % (k.split("_")[-1].lower(), v) for k, v in e.items()))
 def test_traversal_variants_match_oracle(terrain, env):
     P, idx, rays, (t, prim, b1, b2) = terrain
