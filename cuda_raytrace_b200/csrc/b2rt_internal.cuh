@@ -103,7 +103,8 @@ struct b2rt_ctx {
     int pt_blocks_per_sm[4] = {0, 0, 0, 0};
     int trace_sort = -1;         // variant 2 child order: 2 = near to far, 1 = nearest first only, 0 = slot order, < 0 = 2 for closest / 0 for any hit
     int trace_planes = 1;        // variant 2: near / far slab planes picked by the ray's direction signs (load address) instead
-                                 // of min / max per child (B2RT_TRACE_PLANES=0: the min / max form)
+                                 // of min / max per child: 1 = closest-hit rays only (default), 2 = any-hit rays too, 0 = never
+                                 // (B2RT_TRACE_PLANES)
     int trace_pool_flip = 0;     // which of the two ray-pool counters the next speculative-kernel launch uses
     int trace_chunk = 32;        // persistent: consecutive rays a warp takes from the pool per atomicAdd
     int64_t host_chunk = 1 << 18; // rays per chunk of the host-buffer pipeline (B2RT_HOST_CHUNK)

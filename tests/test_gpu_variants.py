@@ -51,7 +51,7 @@ def terrain(built):
     dict(B2RT_TRACE_VARIANT=1), dict(B2RT_TRACE_VARIANT=1, B2RT_TRACE_REFILL=20),
     dict(B2RT_TRACE_VARIANT=2), dict(B2RT_TRACE_VARIANT=2, B2RT_TRACE_REFILL=12),
     dict(B2RT_TRACE_VARIANT=2, B2RT_TRACE_REFILL=32, B2RT_TRACE_CHUNK=96),
-    dict(B2RT_TRACE_VARIANT=2, B2RT_TRACE_PLANES=0), dict(B2RT_TRACE_VARIANT=2, B2RT_TRACE_PLANES=1, B2RT_TRACE_SORT=1),
+    dict(B2RT_TRACE_VARIANT=2, B2RT_TRACE_PLANES=0), dict(B2RT_TRACE_VARIANT=2, B2RT_TRACE_PLANES=2, B2RT_TRACE_SORT=1),
     dict(B2RT_TRACE_VARIANT=2, B2RT_TRACE_PLANES=1, B2RT_TRACE_SORT=0),
 ], ids=lambda e: "-".join("%s%s" % (k.split("_")[-1].lower(), v) for k, v in e.items()))
 def test_traversal_variants_match_oracle(terrain, env):
