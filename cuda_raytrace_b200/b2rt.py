@@ -577,7 +577,7 @@ Context.sample_positions = _sample_positions
 
 
 # ---- final gathering (pbrt photonmap with finalgather true) ------------------------------------------
-SYMBOLS += ["b2rt_photons_trace_fg", "b2rt_irradiance", "b2rt_radiance_compute", "b2rt_radiance_lookup",
+SYMBOLS += ["b2rt_fg_deposit_limits", "b2rt_multi_fg_deposit_limits", "b2rt_photons_trace_fg", "b2rt_irradiance", "b2rt_radiance_compute", "b2rt_radiance_lookup",
             "b2rt_final_gather_set", "b2rt_final_gather"]
 MAP_CAUSTIC, MAP_INDIRECT, MAP_DIRECT, MAP_RADIANCE = 0, 1, 2, 3
 
@@ -588,6 +588,12 @@ def _photons_trace_fg(self, first_path, n_paths, max_depth=5):
     self.lib.b2rt_photons_trace_fg.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_void_p]
     self._ck(self.lib.b2rt_photons_trace_fg(self.h, int(first_path), int(n_paths), int(max_depth), st))
     return st[0], st[1]
+
+
+def _fg_deposit_limits(self, caustic_paths=-1, indirect_paths=-1):
+    """pbrt's depositedPhoton rule for the final-gathering photon pass (b2rt_fg_deposit_limits); -1 = no limit"""
+    self.lib.b2rt_fg_deposit_limits.argtypes = [C.c_void_p, C.c_int64, C.c_int64]
+    self._ck(self.lib.b2rt_fg_deposit_limits(self.h, int(caustic_paths), int(indirect_paths)))
 
 
 def _irradiance(self, which, queries, k, max_dist2):
@@ -630,6 +636,7 @@ def _final_gather(self, queries, max_dist2):
 
 Context.final_gather = _final_gather
 Context.photons_trace_fg = _photons_trace_fg
+Context.fg_deposit_limits = _fg_deposit_limits
 Context.irradiance = _irradiance
 Context.radiance_compute = _radiance_compute
 Context.radiance_lookup = _radiance_lookup

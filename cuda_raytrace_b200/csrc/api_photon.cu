@@ -312,6 +312,13 @@ int b2rt_final_gather(b2rt_ctx *ctx, int64_t nq, const b2rt_query *queries, floa
     return status_check(ctx);
 }
 
+int b2rt_fg_deposit_limits(b2rt_ctx *ctx, int64_t caustic_paths, int64_t indirect_paths) {
+    if (!ctx) return B2RT_E_ARG;
+    ctx->fg_lim_c = caustic_paths < 0 ? INT64_MAX : caustic_paths;
+    ctx->fg_lim_i = indirect_paths < 0 ? INT64_MAX : indirect_paths;
+    return B2RT_OK;
+}
+
 int b2rt_final_gather_set(b2rt_ctx *ctx, int32_t enable, int32_t gather_samples, float gather_angle_deg) {
     if (!ctx) return B2RT_E_ARG;
     if (enable && (gather_samples < 1 || gather_samples > 4096 || !(gather_angle_deg > 0.f) || !(gather_angle_deg < 90.f))) {

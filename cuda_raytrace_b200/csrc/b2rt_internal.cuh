@@ -166,6 +166,7 @@ struct b2rt_ctx {
     int fg_variant = 3;                                 // 3 (default): trace / cell-sorted lookup / combine as separate launches;
                                                         // 0: the fused warp-per-shading-point kernel (B2RT_FG_VARIANT, A/B)
     float fg_cos_angle = 0.98480775301220802f;          // cos(10 degrees)
+    int64_t fg_lim_c = INT64_MAX, fg_lim_i = INT64_MAX; // b2rt_fg_deposit_limits
     bool radiance_computed = false;                     // maps[3].alpha holds Lo (true) or rho_r (false)
     DevBuf d_fg_queries, d_fg_E, d_fg_Etmp, d_fg_idx, d_fg_r2, d_fg_found, d_fg_slots, d_fg_cnt, d_fg_cnt2;
     DevBuf d_fg_dirs, d_fg_pend, d_fg_pq, d_fg_pidx, d_fg_flag, d_fg_coarse2, d_fg_nbox1, d_fg_nbox2;

@@ -25,7 +25,8 @@ constexpr int FG_NDIR = 50;              // nIndirSamplePhotons (photonmap.cpp:6
 // which the path itself never reads.
 __global__ void __launch_bounds__(FG_THREADS)
 fg_photon_kernel(DScene sc, uint32_t seed_lo, uint32_t seed_hi, int64_t first_path, int64_t n_paths, int max_depth,
-                 b2rt_photon *__restrict__ slots, uint32_t *__restrict__ cnt_d, uint32_t *__restrict__ cnt_r, uint32_t *status) {
+                 b2rt_photon *__restrict__ slots, uint32_t *__restrict__ cnt_d, uint32_t *__restrict__ cnt_r, uint32_t *status,
+                 int64_t lim_c, int64_t lim_i) {
     int64_t li = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (li >= n_paths) return;
     const uint64_t path = (uint64_t)(first_path + li);
@@ -38,7 +39,7 @@ fg_photon_kernel(DScene sc, uint32_t seed_lo, uint32_t seed_hi, int64_t first_pa
     float tmin;
     bool alive = emit_photon(sc, u01(r0.x), u01(r0.y), u01(r0.z), u01(r1.x), u01(r1.y), o, d, tmin, alpha);
     int n_isect = 0;
-    bool overflow = false;
+    bool overflow = false, specular_path = true;
     while (alive) {
         HitD h;
         if (!traverse<false>(sc.nodes, sc.recs, sc.analytic, o.x, o.y, o.z, d.x, d.y, d.z, tmin, INFINITY, h, overflow))
@@ -47,7 +48,11 @@ fg_photon_kernel(DScene sc, uint32_t seed_lo, uint32_t seed_hi, int64_t first_pa
         Surface s = make_surface(sc, h, o, d);
         Mat m = load_material(sc, s.material);
         f3 wo = -d;
-        if (m.type == B2RT_MAT_MATTE) {     // hasNonSpecular: a photon is deposited here (direct, indirect or caustic)
+        // pbrt's depositedPhoton (photonmap.cpp:455-490): a caustic-type hit is a deposit only while the caustic map still
+        // collects (path < lim_c), a direct / indirect one while the indirect map does (path < lim_i); b2rt_fg_deposit_limits
+        const bool caustic_hit = specular_path && n_isect > 1;
+        const bool deposited = caustic_hit ? ((int64_t)path < lim_c) : ((int64_t)path < lim_i);
+        if (m.type == B2RT_MAT_MATTE && deposited) {     // hasNonSpecular: a photon is deposited here (direct, indirect or caustic)
             if (n_isect == 1) {
                 float4 *dst = reinterpret_cast<float4 *>(my);
                 dst[0] = make_float4(s.p.x, s.p.y, s.p.z, __uint_as_float(fg_oct_encode(wo)));
@@ -73,6 +78,7 @@ fg_photon_kernel(DScene sc, uint32_t seed_lo, uint32_t seed_hi, int64_t first_pa
         float cont = fminf(1.f, lum(anew) / lum(alpha));
         if (u01(rb.w) > cont) break;
         alpha = mk3(anew.x / cont, anew.y / cont, anew.z / cont);
+        specular_path = specular_path && bs.specular;
         o = s.p; d = bs.wi; tmin = s.ray_eps;
     }
     cnt_d[li] = nd;
@@ -542,7 +548,7 @@ int b2rt_photons_trace_fg_begin(b2rt_ctx *ctx, int64_t first_path, int64_t n_pat
     uint32_t *counters = ctx->d_counters.as<uint32_t>();
     fg_photon_kernel<<<(unsigned)((n_paths + FG_THREADS - 1) / FG_THREADS), FG_THREADS, 0, st>>>(
         sc, (uint32_t)ctx->seed, (uint32_t)(ctx->seed >> 32), first_path, n_paths, max_depth,
-        ctx->d_fg_slots.as<b2rt_photon>(), cnt_d, cnt_r, counters + 8);
+        ctx->d_fg_slots.as<b2rt_photon>(), cnt_d, cnt_r, counters + 8, ctx->fg_lim_c, ctx->fg_lim_i);
     B2RT_LAUNCH_CHECK(ctx);
     int rc = b2rt_exclusive_scan_u32(ctx, cnt_d, n_paths, counters + 32);
     if (rc) return rc;

@@ -496,6 +496,11 @@ int b2rt_multi_radiance_compute(b2rt_multi *m, int32_t nused, float max_dist2) {
     });
 }
 
+int b2rt_multi_fg_deposit_limits(b2rt_multi *m, int64_t caustic_paths, int64_t indirect_paths) {
+    if (!m) return B2RT_E_ARG;
+    for (b2rt_ctx *c : m->ctx) b2rt_fg_deposit_limits(c, caustic_paths, indirect_paths);
+    return B2RT_OK;
+}
 int b2rt_multi_final_gather_set(b2rt_multi *m, int32_t enable, int32_t gather_samples, float gather_angle_deg) {
     if (!m) return B2RT_E_ARG;
     for (b2rt_ctx *c : m->ctx) {

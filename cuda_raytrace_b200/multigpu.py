@@ -196,7 +196,8 @@ def render_sharded(ctx, cam, group=None, **kw):
         ctx.render_frame_device(cam, band[at:].data_ptr(), window=(0, cam.xres, by0, by1), **kw)   # synchronous on return
         at += by1 - by0
     parts = [torch.empty_like(band) for _ in range(world)] if rank == 0 else None
-    dist.gather(band, parts, dst=0, group=group)
+    # `dst` is a GLOBAL rank: translate the group's rank 0 (a sub-group need not contain global rank 0)
+    dist.gather(band, parts, dst=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
     if rank != 0:
         return None
     img = torch.cat(stripe_compose(parts, edges, world), 0)

@@ -187,6 +187,12 @@ int b2rt_gather_sets(b2rt_ctx *ctx, int32_t map, int64_t nqueries, const b2rt_qu
  * (direct, indirect or caustic) that draws u < 0.125 from the path's own stream to B2RT_MAP_RADIANCE, both in path
  * order.  n_stored[0] = direct photons, n_stored[1] = radiance photons appended (may be NULL). */
 int b2rt_photons_trace_fg(b2rt_ctx *ctx, int64_t first_path, int64_t n_paths, int32_t max_depth, int64_t n_stored[2]);
+/* pbrt only creates a radiance photon (and a direct photon) where a photon was actually DEPOSITED (depositedPhoton,
+ * photonmap.cpp:455-490): a caustic-type hit (all-specular path, > 1 intersection) counts while the caustic map is still
+ * collecting, i.e. for paths < caustic_paths; a direct / indirect hit for paths < indirect_paths.  The two numbers are
+ * n_paths_out of b2rt_photons_shoot; pass them before b2rt_photons_trace_fg over [0, max of the two).  Negative = no limit
+ * (the default: every matte hit of the traced paths counts). */
+int b2rt_fg_deposit_limits(b2rt_ctx *ctx, int64_t caustic_paths, int64_t indirect_paths);
 /* EPhoton: irradiance at (p, n) from the k nearest photons of `map` within sqrt(max_dist2):
  * sum of alpha over the photons with Dot(n, wi) > 0, divided by (nPaths * md2 * pi).  out_E[3 * nqueries]. */
 int b2rt_irradiance(b2rt_ctx *ctx, int32_t map, int64_t nqueries, const b2rt_query *queries, int32_t k, float max_dist2,
@@ -310,6 +316,7 @@ int  b2rt_multi_photons_shoot(b2rt_multi *m, int64_t n_caustic_wanted, int64_t n
 int  b2rt_multi_photons_trace_fg(b2rt_multi *m, int64_t first_path, int64_t n_paths, int32_t max_depth, int64_t n_stored[2]);
 int  b2rt_multi_photon_grid_build(b2rt_multi *m, int32_t map, float cell_size, float target_per_cell);
 int  b2rt_multi_radiance_compute(b2rt_multi *m, int32_t nused, float max_dist2);
+int  b2rt_multi_fg_deposit_limits(b2rt_multi *m, int64_t caustic_paths, int64_t indirect_paths);
 int  b2rt_multi_final_gather_set(b2rt_multi *m, int32_t enable, int32_t gather_samples, float gather_angle_deg);
 int  b2rt_multi_sampler_set(b2rt_multi *m, int32_t type, int32_t xsamples, int32_t ysamples);
 int  b2rt_multi_film_set_filter(b2rt_multi *m, const b2rt_filter *filter);

@@ -406,15 +406,21 @@ class PortFullScene:
         return oc[: nc.value].copy(), oi[: ni.value].copy()
 
 
-def _pft_fg(self, seed, first_path, n_paths, max_depth=5):
-    """(direct photons, radiance photons) of the path range: port_photon_trace_fg."""
+def _pft_fg(self, seed, first_path, n_paths, max_depth=5, limits=(-1, -1)):
+    """(direct photons, radiance photons) of the path range: port_photon_trace_fg.  limits = (caustic_paths, indirect_paths)
+    of pbrt's depositedPhoton rule (-1: none)."""
     lib = _bind_photon()
+    lib.port_fg_deposit_limits.argtypes = [C.c_int64, C.c_int64]
+    lib.port_fg_deposit_limits.restype = None
+    big = 2 ** 63 - 1
+    lib.port_fg_deposit_limits(big if limits[0] < 0 else limits[0], big if limits[1] < 0 else limits[1])
     cs, keep = self._cscene()
     cap = n_paths * max_depth + 1
     od, orr = np.zeros(cap, PHOTON_DTYPE), np.zeros(cap, PHOTON_DTYPE)
     nd, nr = C.c_int64(0), C.c_int64(0)
     rc = lib.port_photon_trace_fg(C.byref(cs), seed, first_path, n_paths, max_depth, _p(od), cap, C.byref(nd), _p(orr), cap,
                                   C.byref(nr))
+    lib.port_fg_deposit_limits(big, big)
     assert rc == 0, rc
     del keep
     return od[: nd.value].copy(), orr[: nr.value].copy()

@@ -13,6 +13,10 @@
 /* photonmap.cpp:440-490 with finalgather true: the direct photon (first diffuse hit) of every path and a radiance photon
  * (p, Faceforward(nn, wo), rho_r) at every deposit that draws u < .125f.  The draw is Philox block 2 of the bounce
  * counter: the path's own stream (blocks 0, 1) is untouched, so the paths are those of port_photon_trace. */
+/* deposit limits (pbrt's depositedPhoton, photonmap.cpp:455-490): a caustic-type hit only counts as a deposit while the
+ * caustic map is still collecting (path < lim_c), a direct / indirect one while the indirect map is (path < lim_i) */
+static int64_t g_fg_lim_c = INT64_MAX, g_fg_lim_i = INT64_MAX;
+void port_fg_deposit_limits(int64_t lim_c, int64_t lim_i) { g_fg_lim_c = lim_c; g_fg_lim_i = lim_i; }
 int port_photon_trace_fg(const port_scene *sc, uint64_t seed, int64_t first_path, int64_t n_paths, int max_depth,
                          port_photon *out_d, int64_t cap_d, int64_t *n_d, port_photon *out_r, int64_t cap_r,
                          int64_t *n_r) {
@@ -53,14 +57,16 @@ int port_photon_trace_fg(const port_scene *sc, uint64_t seed, int64_t first_path
         float ad = fabsf(vdot(Nl, d)), den = pdf * light_pdf;
         v3 alpha = V(ad * Le.x / den, ad * Le.y / den, ad * Le.z / den);
         if (black(alpha)) continue;
-        int n_isect = 0;
+        int n_isect = 0, specular_path = 1;
         for (;;) {
             osurf s; int prim;
             if (!closest(sc, o, d, tmin, &s, &prim)) break;
             ++n_isect;
             omat m = get_material(sc, prim);
             v3 wo = vneg(d);
-            if (m.type == 0) {
+            const int caustic_hit = specular_path && n_isect > 1;
+            const int deposited = caustic_hit ? ((int64_t)path < g_fg_lim_c) : ((int64_t)path < g_fg_lim_i);
+            if (m.type == 0 && deposited) {
                 if (n_isect == 1) {
                     port_photon ph;
                     ph.p[0] = s.p.x; ph.p[1] = s.p.y; ph.p[2] = s.p.z; ph.wi_oct = oct_encode(wo);
@@ -90,6 +96,7 @@ int port_photon_trace_fg(const port_scene *sc, uint64_t seed, int64_t first_path
             float cont = fminf(1.f, lumin(anew) / lumin(alpha));
             if (u01(rb[3]) > cont) break;
             alpha = V(anew.x / cont, anew.y / cont, anew.z / cont);
+            specular_path = specular_path && bs.specular;
             o = s.p; d = bs.wi; tmin = s.ray_eps;
         }
     }

@@ -481,7 +481,11 @@ void PhotonMappingRenderer::render(const Scene *scene, CudaRender *cr, Camera *c
             // PhotonIntegrator::Preprocess with finalGather (photonmap.cpp:468-490, 383-399): direct photons and radiance
             // photons of the paths that filled the indirect map, then ComputeRadianceTask + the radiance-photon map
             int64_t st[2];
-            cr->checkMulti(b2rt_multi_photons_trace_fg(mg, 0, paths[1], maxPhotonDepth, st), "b2rt_multi_photons_trace_fg");
+            // pbrt's depositedPhoton rule: direct / indirect hits count while the indirect map collected (paths[1]), caustic
+            // hits while the caustic map did (paths[0]); it keeps making radiance photons until BOTH maps are full
+            cr->checkMulti(b2rt_multi_fg_deposit_limits(mg, paths[0], paths[1]), "b2rt_multi_fg_deposit_limits");
+            const int64_t fgPaths = paths[0] > paths[1] ? paths[0] : paths[1];
+            cr->checkMulti(b2rt_multi_photons_trace_fg(mg, 0, fgPaths, maxPhotonDepth, st), "b2rt_multi_photons_trace_fg");
             cr->checkMulti(b2rt_multi_photon_grid_build(mg, B2RT_MAP_DIRECT, 0.f, 0.f), "b2rt_multi_photon_grid_build");
             cr->checkMulti(b2rt_multi_radiance_compute(mg, nUsed, maxDist * maxDist), "b2rt_multi_radiance_compute");
             Info("CudaRender: final gathering, %lld direct photons, %lld radiance photons", (long long)st[0], (long long)st[1]);

@@ -56,6 +56,29 @@ def test_fg_photons_bit_exact(fctx, oracle_maps):
     assert np.array_equal(_raw(fctx.photons_download(1)), _raw(om[1]))
 
 
+def test_fg_deposit_limits_follow_pbrt(built):
+    """pbrt's depositedPhoton (photonmap.cpp:455-490): with limits (caustic_paths, indirect_paths) a caustic-type hit makes a
+    radiance photon only on paths below the first, direct / indirect hits (and the direct photon) only below the second."""
+    sc = O.PortFullScene()
+    S.fill_scene(sc, S.cornell_scene())
+    n = 30000
+    with b2rt.Context(0, seed=G.SEED) as c:
+        S.fill_scene(c, S.cornell_scene())
+        c.build_accel()
+        for lim in ((12000, 20000), (30000, 9000), (0, 0)):
+            c.photons_clear()
+            c.fg_deposit_limits(*lim)
+            c.photons_trace_fg(0, n)
+            d, r = sc.photon_trace_fg(G.SEED, 0, n, limits=lim)
+            assert np.array_equal(_raw(c.photons_download(2)), _raw(d)) and np.array_equal(_raw(c.photons_download(3)), _raw(r))
+            assert (d["path"] < lim[1]).all() and (r["path"] < max(lim)).all()
+        c.fg_deposit_limits(-1, -1)
+        c.photons_clear()
+        c.photons_trace_fg(0, n)
+        d0, r0 = sc.photon_trace_fg(G.SEED, 0, n)
+        assert np.array_equal(_raw(c.photons_download(3)), _raw(r0)) and len(r0) > len(r)
+
+
 def test_fg_photons_independent_of_path_range_split(built, oracle_maps):
     _, om = oracle_maps
     with b2rt.Context(0, seed=G.SEED) as c:
