@@ -9,7 +9,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb2rt.so")
+LIB_PATH = os.environ.get("B2RT_LIB") or os.path.join(_HERE, "libb2rt.so")     # B2RT_LIB: e.g. the -DB2RT_STATS build
 
 HOST, DEVICE = 0, 1
 MAT_MATTE, MAT_MIRROR, MAT_GLASS = 0, 1, 2
@@ -40,7 +40,7 @@ SYMBOLS = [
     "b2rt_create", "b2rt_destroy", "b2rt_last_error", "b2rt_device_count", "b2rt_add_mesh", "b2rt_add_sphere",
     "b2rt_add_disk", "b2rt_add_material", "b2rt_add_light", "b2rt_clear_scene", "b2rt_build_accel",
     "b2rt_accel_info_get", "b2rt_accel_download", "b2rt_trace_closest", "b2rt_trace_any", "b2rt_sort_pairs",
-    "b2rt_add_mesh_ex", "b2rt_surface_at", "b2rt_sync", "b2rt_timer_start", "b2rt_timer_stop", "b2rt_launch_count", "b2rt_stream", "b2rt_host_alloc", "b2rt_host_free",
+    "b2rt_add_mesh_ex", "b2rt_surface_at", "b2rt_trace_stats", "b2rt_sync", "b2rt_timer_start", "b2rt_timer_stop", "b2rt_launch_count", "b2rt_stream", "b2rt_host_alloc", "b2rt_host_free",
 ]
 
 _lib = None
@@ -145,6 +145,14 @@ class Context:
     def _ck(self, rc):
         if rc:
             raise B2rtError(rc, self.lib.b2rt_last_error(self.h).decode())
+
+    def trace_stats(self, reset=True):
+        """(wide nodes fetched, primitive records tested) by the traversal kernel; needs the -DB2RT_STATS library
+        (B2RT_LIB=.../libb2rt_stats.so)"""
+        a, b = C.c_uint64(), C.c_uint64()
+        self.lib.b2rt_trace_stats.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.c_int]
+        self._ck(self.lib.b2rt_trace_stats(self.h, C.byref(a), C.byref(b), 1 if reset else 0))
+        return a.value, b.value
 
     def last_error(self):
         """message of the last failing or warning call (e.g. b2rt_photons_shoot giving up like pbrt does)"""

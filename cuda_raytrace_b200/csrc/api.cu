@@ -318,6 +318,27 @@ int b2rt_trace_any(b2rt_ctx *ctx, int64_t nrays, const b2rt_ray *rays, uint8_t *
     return trace_common(ctx, nrays, rays, nullptr, occluded, where, true);
 }
 
+// -DB2RT_STATS build only (make -C cuda_raytrace_b200/csrc stats -> libb2rt_stats.so): wide nodes fetched and primitive
+// records tested by the traversal kernel since the last reset; SURVEY 8(d) asks for the L2 -> SM bytes per ray they imply
+// (nodes * 128 + prims * 48).  The regular build returns B2RT_E_STATE.
+int b2rt_trace_stats(b2rt_ctx *ctx, uint64_t *nodes, uint64_t *prims, int reset) {
+    if (!ctx) return B2RT_E_ARG;
+#ifdef B2RT_STATS
+    B2RT_CUDA(ctx, cudaSetDevice(ctx->device));
+    unsigned long long v[2] = {0, 0};
+    B2RT_CUDA(ctx, cudaMemcpyAsync(v, ctx->d_counters.as<uint32_t>() + 24, 16, cudaMemcpyDeviceToHost, ctx->stream));
+    B2RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (reset) B2RT_CUDA(ctx, cudaMemsetAsync(ctx->d_counters.as<uint32_t>() + 24, 0, 16, ctx->stream));
+    if (nodes) *nodes = v[0];
+    if (prims) *prims = v[1];
+    return B2RT_OK;
+#else
+    (void)nodes; (void)prims; (void)reset;
+    ctx->err = "trace_stats: this library was built without -DB2RT_STATS (make -C cuda_raytrace_b200/csrc stats)";
+    return B2RT_E_STATE;
+#endif
+}
+
 int b2rt_sort_pairs(b2rt_ctx *ctx, int64_t n, uint32_t *keys, uint32_t *vals, int key_bits) {
     if (!ctx) return B2RT_E_ARG;
     if (n < 0 || key_bits < 1 || key_bits > 32 || (n && (!keys || !vals))) { ctx->err = "sort_pairs: bad arguments"; return B2RT_E_ARG; }

@@ -229,6 +229,9 @@ trace_spec_kernel(const WideNode *__restrict__ nodes, const PrimRec *__restrict_
 
     RayD r;
     float idx = 0.f, idy = 0.f, idz = 0.f;
+#ifdef B2RT_STATS
+    uint32_t st_nodes = 0, st_prims = 0;    // -DB2RT_STATS: wide nodes fetched / primitive records tested by this lane
+#endif
     int sg_ = 0;                            // PL: bit a set = direction component a is negative (near plane = hi array)
     float best_t = 0.f, best_b1 = 0.f, best_b2 = 0.f;
     int best_prim = 0x7fffffff;
@@ -274,6 +277,9 @@ trace_spec_kernel(const WideNode *__restrict__ nodes, const PrimRec *__restrict_
             // ---- node loop: descend; park the first leaf met and keep going until the whole warp has one ---------
             while (cur >= 0 && cur != NONE) {
                 const float4 *np = reinterpret_cast<const float4 *>(nodes + cur);
+#ifdef B2RT_STATS
+                ++st_nodes;
+#endif
                 // PL: lox / loy / loz hold the NEAR planes, hix / hiy / hiz the FAR ones (picked by the load address)
                 const int nx_ = sg_ & 1, ny_ = 2 + ((sg_ >> 1) & 1), nz_ = 4 + ((sg_ >> 2) & 1);
                 const float4 lox = __ldg(np + (PL ? nx_ : 0)), hix = __ldg(np + (PL ? (nx_ ^ 1) : 1)),
@@ -334,6 +340,9 @@ trace_spec_kernel(const WideNode *__restrict__ nodes, const PrimRec *__restrict_
                 for (uint32_t s = first; s < first + cnt; ++s) {
                     const float4 *pp = reinterpret_cast<const float4 *>(recs + s);
                     const float4 A = __ldg(pp), B = __ldg(pp + 1), C = __ldg(pp + 2);
+#ifdef B2RT_STATS
+                    ++st_prims;
+#endif
                     const int prim = __float_as_int(A.w);
                     const int type = __float_as_int(B.w);
                     float t, b1 = 0.f, b2 = 0.f;
@@ -371,6 +380,14 @@ trace_spec_kernel(const WideNode *__restrict__ nodes, const PrimRec *__restrict_
         }
         __syncwarp();
     }
+#ifdef B2RT_STATS
+    // one pair of 64-bit adds per warp: d_counters words 24-27
+    for (int o = 16; o > 0; o >>= 1) { st_nodes += __shfl_xor_sync(0xffffffffu, st_nodes, o); st_prims += __shfl_xor_sync(0xffffffffu, st_prims, o); }
+    if (lane == 0) {
+        atomicAdd(reinterpret_cast<unsigned long long *>(status + 16), (unsigned long long)st_nodes);
+        atomicAdd(reinterpret_cast<unsigned long long *>(status + 18), (unsigned long long)st_prims);
+    }
+#endif
 #undef PT_PUSH
 #undef PT_POP
 }

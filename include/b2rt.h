@@ -323,6 +323,11 @@ int  b2rt_multi_film_set_filter(b2rt_multi *m, const b2rt_filter *filter);
 /* as b2rt_render_frame; where = B2RT_HOST, or B2RT_DEVICE for a buffer on the FIRST device of the group */
 int  b2rt_multi_render_frame(b2rt_multi *m, const b2rt_camera *cam, const b2rt_frame_params *fp, float *out_rgb, int where);
 
+/* traversal work counters: wide nodes fetched and primitive records tested by b2rt_trace_* since the last
+ * reset -- L2 -> SM bytes per ray = (nodes * 128 + prims * 48) / rays.  Only in the -DB2RT_STATS build (libb2rt_stats.so,
+ * `make -C cuda_raytrace_b200/csrc stats`; tools/trace_stats.py); the regular library returns B2RT_E_STATE. */
+int b2rt_trace_stats(b2rt_ctx *ctx, uint64_t *nodes, uint64_t *prims, int reset);
+
 /* generic device sort exposed for tests/bench of the hand-written radix sort (K2):
  * stable LSD sort of (key32,value32) pairs on `key_bits` low bits; device pointers only. */
 int b2rt_sort_pairs(b2rt_ctx *ctx, int64_t n, uint32_t *keys, uint32_t *vals, int key_bits);

@@ -26,6 +26,7 @@ for job in "$@"; do
     saninit)  python -c "import __graft_entry__ as g; g.smoke()" > $O/plain_smoke.log 2>&1 && timeout 1500 compute-sanitizer --tool initcheck --log-file $O/sanitizer_initcheck.txt python -c "import __graft_entry__ as g; g.smoke()" > $O/san_initcheck_run.log 2>&1; echo "rc=$?" >> $O/san_initcheck_run.log ;;
     topo)     nvidia-smi topo -m > $O/topo.txt 2>&1 ;;
     abplanes) for v in 0 1 0 1; do B2RT_TRACE_PLANES=$v timeout 300 python bench.py --steps 100 --no-cpu-baseline --no-photon-extra > $O/bench_planes$v.json 2>> $O/abplanes.err; python -c "import json;d=json.load(open('$O/bench_planes$v.json'));print('planes',$v,d['value'],d['closest_hit_mrays'],d['any_hit_mrays'],d['incoherent_closest_hit_mrays'])" >> $O/abplanes.txt; done ;;
+    tracestats) timeout 300 python tools/trace_stats.py > $O/trace_stats.json 2> $O/trace_stats.err ;;
     benchref) timeout 600 python bench.py --impl reference --steps 5 --warmup 1 > $O/bench_ref.json 2> $O/bench_ref.err ;;
     fg540)    timeout 300 python tools/bench_fg.py 1000000 100000 960 540 32 2 > $O/bench_fg_540.jsonl 2> $O/bench_fg_540.err; echo "rc=$?" >> $O/bench_fg_540.err ;;
     fg540v0)  B2RT_FG_VARIANT=0 timeout 300 python tools/bench_fg.py 1000000 100000 960 540 32 1 > $O/bench_fg_540_v0.jsonl 2> $O/bench_fg_540_v0.err ;;
