@@ -583,7 +583,9 @@ int b2rt_photons_trace_fg_impl(b2rt_ctx *ctx, int64_t first_path, int64_t n_path
     rc = b2rt_photons_trace_fg_commit(ctx, n_paths, max_depth, dst);
     if (rc) return rc;
     md.n += tot[0]; mr.n += tot[1];
-    md.n_paths += n_paths; mr.n_paths += n_paths;
+    // nDirectPaths only counts the paths shot while the indirect map was collecting (photonmap.cpp:546-553)
+    md.n_paths += std::max<int64_t>(0, std::min<int64_t>(first_path + n_paths, ctx->fg_lim_i) - first_path);
+    mr.n_paths += n_paths;
     md.grid_built = mr.grid_built = false;
     if (n_stored) { n_stored[0] = tot[0]; n_stored[1] = tot[1]; }
     return B2RT_OK;

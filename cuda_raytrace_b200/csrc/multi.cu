@@ -441,6 +441,9 @@ int b2rt_multi_photons_trace_fg(b2rt_multi *m, int64_t first_path, int64_t n_pat
                       [&](int i, int64_t cnt, const PhotonDst &dst) { return b2rt_photons_trace_fg_commit(m->ctx[i], cnt, max_depth, dst); },
                       n_stored);
     if (rc) return rc;
+    // nDirectPaths only counts the paths shot while the indirect map was collecting (sharded_pass added n_paths)
+    const int64_t counted = std::max<int64_t>(0, std::min<int64_t>(first_path + n_paths, m->ctx[0]->fg_lim_i) - first_path);
+    for (b2rt_ctx *c : m->ctx) c->maps[B2RT_MAP_DIRECT].n_paths += counted - n_paths;
     return status_all(m);
 }
 

@@ -72,6 +72,7 @@ def test_fg_deposit_limits_follow_pbrt(built):
             d, r = sc.photon_trace_fg(G.SEED, 0, n, limits=lim)
             assert np.array_equal(_raw(c.photons_download(2)), _raw(d)) and np.array_equal(_raw(c.photons_download(3)), _raw(r))
             assert (d["path"] < lim[1]).all() and (r["path"] < max(lim)).all()
+            assert c.photons_count(2)[1] == min(n, lim[1])            # nDirectPaths: paths shot while the indirect map collected
         c.fg_deposit_limits(-1, -1)
         c.photons_clear()
         c.photons_trace_fg(0, n)
