@@ -40,7 +40,7 @@ SYMBOLS = [
     "b2rt_create", "b2rt_destroy", "b2rt_last_error", "b2rt_device_count", "b2rt_add_mesh", "b2rt_add_sphere",
     "b2rt_add_disk", "b2rt_add_material", "b2rt_add_light", "b2rt_clear_scene", "b2rt_build_accel",
     "b2rt_accel_info_get", "b2rt_accel_download", "b2rt_trace_closest", "b2rt_trace_any", "b2rt_sort_pairs",
-    "b2rt_add_mesh_ex", "b2rt_surface_at", "b2rt_trace_stats", "b2rt_sync", "b2rt_timer_start", "b2rt_timer_stop", "b2rt_launch_count", "b2rt_stream", "b2rt_host_alloc", "b2rt_host_free",
+    "b2rt_add_mesh_ex", "b2rt_surface_at", "b2rt_trace_stats", "b2rt_add_spot_light", "b2rt_add_distant_light", "b2rt_sync", "b2rt_timer_start", "b2rt_timer_stop", "b2rt_launch_count", "b2rt_stream", "b2rt_host_alloc", "b2rt_host_free",
 ]
 
 _lib = None
@@ -207,6 +207,22 @@ class Context:
         p = None if p is None else _f32(p, (3,))
         l = C.c_int32()
         self._ck(self.lib.b2rt_add_light(self.h, ltype, _ptr(p), _ptr(rgb), prim, nsamples, C.byref(l)))
+        return l.value
+
+    def add_spot_light(self, l2w, w2l, rgb, cos_total, cos_falloff):
+        """pbrt SpotLight: LightToWorld / WorldToLight (3x4 row-major, +z = axis), I, cos(coneangle), cos(coneangle - delta)"""
+        l2w, w2l, rgb = _f32(l2w, (12,)), _f32(w2l, (12,)), _f32(rgb, (3,))
+        l = C.c_int32()
+        self.lib.b2rt_add_spot_light.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.POINTER(C.c_int32)]
+        self._ck(self.lib.b2rt_add_spot_light(self.h, _ptr(l2w), _ptr(w2l), _ptr(rgb), cos_total, cos_falloff, C.byref(l)))
+        return l.value
+
+    def add_distant_light(self, dir_to_light, rgb):
+        """pbrt DistantLight: unit direction TO the light, radiance L"""
+        d, rgb = _f32(dir_to_light, (3,)), _f32(rgb, (3,))
+        l = C.c_int32()
+        self.lib.b2rt_add_distant_light.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_int32)]
+        self._ck(self.lib.b2rt_add_distant_light(self.h, _ptr(d), _ptr(rgb), C.byref(l)))
         return l.value
 
     def clear_scene(self):

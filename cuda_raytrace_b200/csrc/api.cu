@@ -199,6 +199,7 @@ int b2rt_add_light(b2rt_ctx *ctx, int32_t type, const float p[3], const float rg
     if (!ctx) return B2RT_E_ARG;
     if (type < B2RT_LIGHT_POINT || type > B2RT_LIGHT_DISK_AREA || !rgb) { ctx->err = "add_light: bad arguments"; return B2RT_E_ARG; }
     Light l;
+    memset(&l, 0, sizeof(l));
     l.type = type;
     if (p) memcpy(l.p, p, 12); else l.p[0] = l.p[1] = l.p[2] = 0.f;
     memcpy(l.rgb, rgb, 12);
@@ -208,12 +209,45 @@ int b2rt_add_light(b2rt_ctx *ctx, int32_t type, const float p[3], const float rg
     return B2RT_OK;
 }
 
+int b2rt_add_spot_light(b2rt_ctx *ctx, const float l2w[12], const float w2l[12], const float rgb[3], float cos_total_width,
+                        float cos_falloff_start, int32_t *light_id) {
+    if (!ctx) return B2RT_E_ARG;
+    if (!l2w || !w2l || !rgb || !(cos_total_width < cos_falloff_start || cos_total_width == cos_falloff_start)) {
+        ctx->err = "add_spot_light: bad arguments"; return B2RT_E_ARG;
+    }
+    Light l;
+    memset(&l, 0, sizeof(l));
+    l.type = B2RT_LIGHT_SPOT;
+    l.p[0] = l2w[3]; l.p[1] = l2w[7]; l.p[2] = l2w[11];                     // LightToWorld(Point(0, 0, 0))
+    memcpy(l.rgb, rgb, 12);
+    for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) { l.l2w[3 * r + c] = l2w[4 * r + c]; l.w2l[3 * r + c] = w2l[4 * r + c]; }
+    l.cos_total = cos_total_width; l.cos_falloff = cos_falloff_start;
+    l.prim = -1; l.nsamples = 1; l.analytic = -1; l.n[2] = 1.f;
+    if (light_id) *light_id = (int32_t)ctx->h_lights.size();
+    ctx->h_lights.push_back(l);
+    return B2RT_OK;
+}
+
+int b2rt_add_distant_light(b2rt_ctx *ctx, const float dir_to_light[3], const float rgb[3], int32_t *light_id) {
+    if (!ctx) return B2RT_E_ARG;
+    if (!dir_to_light || !rgb) { ctx->err = "add_distant_light: bad arguments"; return B2RT_E_ARG; }
+    Light l;
+    memset(&l, 0, sizeof(l));
+    l.type = B2RT_LIGHT_DISTANT;
+    memcpy(l.rgb, rgb, 12);
+    memcpy(l.n, dir_to_light, 12);
+    l.prim = -1; l.nsamples = 1; l.analytic = -1;
+    if (light_id) *light_id = (int32_t)ctx->h_lights.size();
+    ctx->h_lights.push_back(l);
+    return B2RT_OK;
+}
+
 int b2rt_build_accel(b2rt_ctx *ctx) {
     if (!ctx) return B2RT_E_ARG;
     B2RT_CUDA(ctx, cudaSetDevice(ctx->device));
-    int rc = b2rt_upload_tables(ctx);
+    int rc = b2rt_build_impl(ctx);
     if (rc) return rc;
-    return b2rt_build_impl(ctx);
+    return b2rt_upload_tables(ctx);          // after the build: distant lights need the scene bounds
 }
 
 int b2rt_accel_info_get(b2rt_ctx *ctx, b2rt_accel_info *info) {

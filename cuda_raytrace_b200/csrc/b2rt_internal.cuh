@@ -66,7 +66,10 @@ struct AnalyticPrim {
 struct Material { int32_t type; float kd[3]; float kt[3]; float ior; };
 // analytic/area/n are derived at build time for disk area lights: analytic = index into the analytic table,
 // area = Disk::Area() (shapes/disk.cpp:132-135), n = Normalize(ObjectToWorld(Normal(0,0,1))) (disk.cpp:154)
-struct Light { int32_t type; float p[3]; float rgb[3]; int32_t prim; int32_t nsamples; int32_t analytic; float area; float n[3]; };
+// spot: p = position, l2w / w2l = rotation parts of LightToWorld / WorldToLight, the two cone cosines.  distant: n = direction
+// TO the light, wc / wr = bounding sphere of the scene box (BBox::BoundingSphere), filled in when the tables are uploaded.
+struct Light { int32_t type; float p[3]; float rgb[3]; int32_t prim; int32_t nsamples; int32_t analytic; float area; float n[3];
+               float l2w[9], w2l[9]; float cos_total, cos_falloff; float wc[3], wr; };
 
 // one photon map (caustic or indirect): photons in path order as traced, then the hash-grid built over them
 struct PhotonMap {

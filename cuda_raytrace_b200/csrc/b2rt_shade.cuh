@@ -222,6 +222,16 @@ __device__ __forceinline__ bool sample_bsdf(const Surface &s, const Mat &m, f3 w
 
 // ---- lights ------------------------------------------------------------------------------------------------------
 struct LightD { int type; f3 p, rgb; int prim; int nsamples; int analytic; float area; f3 n; };
+// SpotLight::Falloff (lights/spot.cpp:60-70): w in world space, pointing away from the light
+__device__ __forceinline__ float spot_falloff(const Light &L, f3 w) {
+    f3 wl = normalize3(mk3(L.w2l[0] * w.x + L.w2l[1] * w.y + L.w2l[2] * w.z, L.w2l[3] * w.x + L.w2l[4] * w.y + L.w2l[5] * w.z,
+                           L.w2l[6] * w.x + L.w2l[7] * w.y + L.w2l[8] * w.z));
+    const float costheta = wl.z;
+    if (costheta < L.cos_total) return 0.f;
+    if (costheta > L.cos_falloff) return 1.f;
+    const float delta = (costheta - L.cos_total) / (L.cos_falloff - L.cos_total);
+    return delta * delta * delta * delta;
+}
 __device__ __forceinline__ LightD load_light(const DScene &sc, int i) {
     const Light &L = sc.lights[i];
     LightD l;
@@ -264,6 +274,34 @@ __device__ __forceinline__ bool emit_photon(const DScene &sc, float u0, float u1
         d = uniform_sample_sphere(u1, u2);
         Nl = d; tmin = 0.f;
         pdf = 1.f / (4.f * B2_PI);
+        Le = L.rgb;
+    } else if (L.type == B2RT_LIGHT_SPOT) {
+        // SpotLight::Sample_L (lights/spot.cpp:112-121): UniformSampleCone in light space (core/montecarlo.cpp:405-410)
+        const Light &G = sc.lights[li];
+        const float costheta = (1.f - u1) + u1 * G.cos_total;
+        const float sintheta = sqrtf(1.f - costheta * costheta);
+        float sn, cs;
+        b2_sincos_quarter(4.f * u2, sn, cs);
+        const f3 v = mk3(cs * sintheta, sn * sintheta, costheta);
+        o = L.p;
+        d = mk3(G.l2w[0] * v.x + G.l2w[1] * v.y + G.l2w[2] * v.z, G.l2w[3] * v.x + G.l2w[4] * v.y + G.l2w[5] * v.z,
+                G.l2w[6] * v.x + G.l2w[7] * v.y + G.l2w[8] * v.z);
+        Nl = d; tmin = 0.f;
+        pdf = (float)(1.0 / ((double)(2.f) * 3.14159265358979323846 * (double)(1.f - G.cos_total)));      // UniformConePdf
+        Le = L.rgb * spot_falloff(G, d);
+    } else if (L.type == B2RT_LIGHT_DISTANT) {
+        // DistantLight::Sample_L (lights/distant.cpp:84-105): a disk of the scene's bounding radius facing the light
+        const Light &G = sc.lights[li];
+        f3 v1, v2;
+        coordinate_system(L.n, v1, v2);
+        float d1, d2;
+        concentric_sample_disk(u1, u2, d1, d2);
+        const f3 wc = mk3(G.wc[0], G.wc[1], G.wc[2]);
+        const f3 pdisk = wc + (v1 * d1 + v2 * d2) * G.wr;
+        o = pdisk + L.n * G.wr;
+        d = -L.n;
+        Nl = d; tmin = 0.f;
+        pdf = (float)(1.0 / (3.14159265358979323846 * (double)G.wr * (double)G.wr));
         Le = L.rgb;
     } else {
         const AnalyticPrim &D = sc.analytic[L.analytic];

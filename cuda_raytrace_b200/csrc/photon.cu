@@ -256,11 +256,22 @@ int b2rt_upload_tables(b2rt_ctx *ctx) {
     std::vector<float> power(nl), cdf(2 * nl + 2, 0.f);
     for (size_t i = 0; i < nl; ++i) {
         Light &L = ctx->h_lights[i];
-        L.analytic = -1; L.area = 0.f; L.n[0] = L.n[1] = 0.f; L.n[2] = 1.f;
+        L.analytic = -1; L.area = 0.f;
+        if (L.type != B2RT_LIGHT_DISTANT) { L.n[0] = L.n[1] = 0.f; L.n[2] = 1.f; }
         float P[3];
         if (L.type == B2RT_LIGHT_POINT) {
             float f = (float)(4.f * M_PI);
             for (int c = 0; c < 3; ++c) P[c] = f * L.rgb[c];
+        } else if (L.type == B2RT_LIGHT_SPOT) {                  // SpotLight::Power (lights/spot.cpp:72-75)
+            float f = (float)M_PI, g = 1.f - .5f * (L.cos_falloff + L.cos_total);
+            for (int c = 0; c < 3; ++c) P[c] = L.rgb[c] * 2.f * f * g;
+        } else if (L.type == B2RT_LIGHT_DISTANT) {               // DistantLight::Power over BBox::BoundingSphere of the scene
+            const float *b = ctx->info.bounds;
+            float d2 = 0.f;
+            for (int a = 0; a < 3; ++a) { L.wc[a] = .5f * b[a] + .5f * b[3 + a]; float d = L.wc[a] - b[3 + a]; d2 += d * d; }
+            L.wr = sqrtf(d2);
+            float f = (float)M_PI;
+            for (int c = 0; c < 3; ++c) P[c] = L.rgb[c] * f * L.wr * L.wr;
         } else {
             int a = -1;
             for (size_t k = 0; k < ctx->h_analytic_prim.size(); ++k)

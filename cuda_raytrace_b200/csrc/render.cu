@@ -94,10 +94,11 @@ __device__ f3 direct_lighting(const DScene &sc, const Surface &s, const Mat &m, 
     const bool pattern = sm.type != B2RT_SAMPLER_RANDOM && node == 1u;
     for (int li = 0; li < sc.n_lights; ++li) {
         LightD Lt = load_light(sc, li);
-        const int ns = Lt.type == B2RT_LIGHT_POINT ? 1 : max(Lt.nsamples, 1);
+        const bool delta = Lt.type != B2RT_LIGHT_DISK_AREA;           // point, spot, distant: one sample, no MIS
+        const int ns = delta ? 1 : max(Lt.nsamples, 1);
         f3 Ld = mk3(0.f, 0.f, 0.f);
         u4 scr = {0u, 0u, 0u, 0u};
-        if (pattern && Lt.type != B2RT_LIGHT_POINT) scr = philox4x32_10(c0, 0xfffffffeu, (uint32_t)li, 0u, k0, k1);
+        if (pattern && !delta) scr = philox4x32_10(c0, 0xfffffffeu, (uint32_t)li, 0u, k0, k1);
         for (int j = 0; j < ns; ++j) {
             u4 r = philox4x32_10(c0, c1, node, 0x100u + (uint32_t)(li * 64 + j), k0, k1);
             float u_l1 = u01(r.x), u_l2 = u01(r.y), u_b1 = u01(r.z), u_b2 = u01(r.w);
@@ -106,20 +107,36 @@ __device__ f3 direct_lighting(const DScene &sc, const Surface &s, const Mat &m, 
                 u_l1 = ld_vdc(n, scr.x); u_l2 = ld_sobol2(n, scr.y); u_b1 = ld_vdc(n, scr.z); u_b2 = ld_sobol2(n, scr.w);
             }
             HitD h;
-            if (Lt.type == B2RT_LIGHT_POINT) {
-                // PointLight::Sample_L (lights/point.cpp:50-57): delta light, no MIS
+            if (Lt.type == B2RT_LIGHT_DISTANT) {
+                // DistantLight::Sample_L (lights/distant.cpp:48-55): wi = lightDir, Li = L, visibility ray to infinity
+                const f3 wi = Lt.n;
+                if (!(dot3(wi, s.ng) * dot3(wo, s.ng) > 0.f)) continue;
+                if (traverse<true>(sc.nodes, sc.recs, sc.analytic, s.p.x, s.p.y, s.p.z, wi.x, wi.y, wi.z, s.ray_eps, INFINITY, h,
+                                   overflow))
+                    continue;
+                const float w = fabsf(dot3(wi, s.n));
+                Ld = Ld + mk3(f_lambert.x * Lt.rgb.x * w, f_lambert.y * Lt.rgb.y * w, f_lambert.z * Lt.rgb.z * w);
+                continue;
+            }
+            if (delta) {
+                // PointLight / SpotLight::Sample_L (lights/point.cpp:50-57, lights/spot.cpp:50-57): delta light, no MIS
                 f3 dl = Lt.p - s.p;
                 float d2 = dl.x * dl.x + dl.y * dl.y + dl.z * dl.z;
                 f3 wi = normalize3(dl);
                 bool same = dot3(wi, s.ng) * dot3(wo, s.ng) > 0.f;      // BSDF::f: sides by the geometric normal
                 if (!same) continue;
+                f3 I = Lt.rgb;
+                if (Lt.type == B2RT_LIGHT_SPOT) {
+                    const float fo = spot_falloff(sc.lights[li], -wi);
+                    if (fo == 0.f) continue;
+                    I = I * fo;
+                }
                 // visibility segment p -> lightPos: direction (lightPos - p), [rayEps, 1]
                 if (traverse<true>(sc.nodes, sc.recs, sc.analytic, s.p.x, s.p.y, s.p.z, dl.x, dl.y, dl.z, s.ray_eps, 1.f, h,
                                    overflow))
                     continue;
                 float w = fabsf(dot3(wi, s.n));     // / lightPdf (= 1)
-                Ld = Ld + mk3(f_lambert.x * (Lt.rgb.x / d2) * w, f_lambert.y * (Lt.rgb.y / d2) * w,
-                              f_lambert.z * (Lt.rgb.z / d2) * w);
+                Ld = Ld + mk3(f_lambert.x * (I.x / d2) * w, f_lambert.y * (I.y / d2) * w, f_lambert.z * (I.z / d2) * w);
                 continue;
             }
             const AnalyticPrim &D = sc.analytic[Lt.analytic];

@@ -208,9 +208,51 @@ def cornell_scene(spheres=True, boxes=False, wide=1.0, light="disk"):
     if light == "disk":
         shapes.append(("disk", *xf_disk_down(0.0, 1.98, 0.0), 0.0, 0.3, 0.0, 0))
         lights.append(("disk", len(shapes) - 1, (17.0, 12.0, 4.0), 4))
+    elif light == "spot":           # pbrt `LightSource "spot"` under the ceiling, looking down at the floor
+        lights.append(spot_light((0.2, 1.9, 0.1), (0.0, 0.0, 0.0), 50.0, 10.0, (9.0, 8.0, 7.0)))
+    elif light == "distant":        # pbrt `LightSource "distant"` shining in through the open front of the box
+        lights.append(distant_light((0.4, 0.9, 3.0), (0.0, 0.6, 0.0), (2.5, 2.5, 2.0)))
+    elif light == "mixed":          # one of each delta light
+        lights.append(("point", (-0.5, 1.7, 0.3), (1.5, 1.5, 1.5)))
+        lights.append(spot_light((0.2, 1.9, 0.1), (0.0, 0.0, 0.0), 50.0, 10.0, (9.0, 8.0, 7.0)))
+        lights.append(distant_light((0.4, 0.9, 3.0), (0.0, 0.6, 0.0), (2.5, 2.5, 2.0)))
     else:
         lights.append(("point", (0.0, 1.9, 0.0), (3.0, 3.0, 3.0)))
     return {"materials": mats, "shapes": shapes, "lights": lights}
+
+
+def _coordinate_system(v1):
+    """pbrt CoordinateSystem (core/geometry.h:508-518) in float32"""
+    v1 = np.asarray(v1, np.float32)
+    if abs(v1[0]) > abs(v1[1]):
+        inv = np.float32(1) / np.sqrt(v1[0] * v1[0] + v1[2] * v1[2], dtype=np.float32)
+        v2 = np.array([-v1[2] * inv, 0, v1[0] * inv], np.float32)
+    else:
+        inv = np.float32(1) / np.sqrt(v1[1] * v1[1] + v1[2] * v1[2], dtype=np.float32)
+        v2 = np.array([0, v1[2] * inv, -v1[1] * inv], np.float32)
+    return v2, np.cross(v1.astype(np.float64), v2.astype(np.float64)).astype(np.float32)
+
+
+def spot_light(frm, to, coneangle, conedelta, rgb):
+    """("spot", l2w, w2l, rgb, cos_total_width, cos_falloff_start, from, to, coneangle, conedelta): pbrt CreateSpotLight
+    (lights/spot.cpp:78-101) with an identity CTM -- LightToWorld = Translate(from) * Inverse(dirToZ)"""
+    frm, to = np.asarray(frm, np.float32), np.asarray(to, np.float32)
+    d = (to - frm).astype(np.float32)
+    d = (d / np.sqrt((d * d).sum(dtype=np.float32), dtype=np.float32)).astype(np.float32)
+    du, dv = _coordinate_system(d)
+    R = np.stack([du, dv, d], 1).astype(np.float32)                 # columns: light x, y, z axes in world space
+    l2w = np.concatenate([R, frm[:, None]], 1).astype(np.float32)
+    w2l = np.concatenate([R.T, (-R.T.astype(np.float64) @ frm.astype(np.float64))[:, None].astype(np.float32)], 1).astype(np.float32)
+    ct = np.float32(np.cos(np.float32(np.radians(np.float32(coneangle)))))
+    cf = np.float32(np.cos(np.float32(np.radians(np.float32(coneangle - conedelta)))))
+    return ("spot", l2w.reshape(-1), w2l.reshape(-1), tuple(rgb), float(ct), float(cf), tuple(frm), tuple(to), coneangle, conedelta)
+
+
+def distant_light(frm, to, rgb):
+    """("distant", dir_to_light, rgb, from, to): pbrt CreateDistantLight (lights/distant.cpp:65-73), lightDir = Normalize(from - to)"""
+    d = (np.asarray(frm, np.float32) - np.asarray(to, np.float32)).astype(np.float32)
+    d = (d * (np.float32(1) / np.sqrt((d * d).sum(dtype=np.float32), dtype=np.float32))).astype(np.float32)
+    return ("distant", tuple(float(x) for x in d), tuple(rgb), tuple(frm), tuple(to))
 
 
 def fill_scene(target, desc):
@@ -234,6 +276,10 @@ def fill_scene(target, desc):
     for l in desc["lights"]:
         if l[0] == "disk":
             target.add_light(1, l[2], prim=first[l[1]], nsamples=l[3])
+        elif l[0] == "spot":
+            target.add_spot_light(l[1], l[2], l[3], l[4], l[5])
+        elif l[0] == "distant":
+            target.add_distant_light(l[1], l[2])
         else:
             target.add_light(0, l[2], p=l[1])
     return first
@@ -274,6 +320,12 @@ def to_pbrt(desc, eye, look, up, fov, xres, yres, spp, integrator, filename, ren
     for l in desc["lights"]:
         if l[0] == "point":
             L.append('LightSource "point" "point from" [%g %g %g] "rgb I" [%g %g %g]' % (*l[1], *l[2]))
+        elif l[0] == "spot":
+            L.append('LightSource "spot" "point from" [%.9g %.9g %.9g] "point to" [%.9g %.9g %.9g] "float coneangle" [%g] '
+                     '"float conedeltaangle" [%g] "rgb I" [%g %g %g]' % (*l[6], *l[7], l[8], l[9], *l[3]))
+        elif l[0] == "distant":
+            L.append('LightSource "distant" "point from" [%.9g %.9g %.9g] "point to" [%.9g %.9g %.9g] "rgb L" [%g %g %g]'
+                     % (*l[3], *l[4], *l[2]))
     for si, sh in enumerate(desc["shapes"]):
         mid = sh[3] if sh[0] == "mesh" else (sh[4] if sh[0] == "sphere" else sh[6])
         t, kd, kt, ior = desc["materials"][mid]

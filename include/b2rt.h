@@ -43,7 +43,7 @@ typedef struct { float t; int32_t prim; float b1, b2; } b2rt_hit;
 /* materials / lights: the subset cuda_render translates (util/material/cudamaterial.cpp:8-21,
  * util/light/cudalight.cpp:16-71) */
 enum { B2RT_MAT_MATTE = 0, B2RT_MAT_MIRROR = 1, B2RT_MAT_GLASS = 2 };
-enum { B2RT_LIGHT_POINT = 0, B2RT_LIGHT_DISK_AREA = 1 };
+enum { B2RT_LIGHT_POINT = 0, B2RT_LIGHT_DISK_AREA = 1, B2RT_LIGHT_SPOT = 2, B2RT_LIGHT_DISTANT = 3 };
 
 typedef struct {
     int32_t n_prims, n_tris, n_wide_nodes, n_leaf_slots;
@@ -89,6 +89,13 @@ int b2rt_add_material(b2rt_ctx *ctx, int32_t type, const float rgb_kd_or_kr[3], 
 /* point: p = position, rgb = I.  disk area: rgb = L, prim = the disk primitive, nsamples. */
 int b2rt_add_light(b2rt_ctx *ctx, int32_t type, const float p[3], const float rgb[3], int32_t prim,
                    int32_t nsamples, int32_t *light_id);
+/* pbrt SpotLight (lights/spot.cpp:40-121; the reference's cudalight.cpp:61-71 only warns): l2w / w2l = the light's
+ * LightToWorld and its inverse (row-major 3x4; the light looks along its +z), rgb = I, cos_total_width / cos_falloff_start =
+ * the two cosines pbrt derives from "coneangle" and "conedeltaangle".  pbrt DistantLight (lights/distant.cpp:40-105):
+ * dir_to_light = Normalize(LightToWorld(from - to)), rgb = L; its emission disk follows the scene bounds at build time. */
+int b2rt_add_spot_light(b2rt_ctx *ctx, const float l2w[12], const float w2l[12], const float rgb[3], float cos_total_width,
+                        float cos_falloff_start, int32_t *light_id);
+int b2rt_add_distant_light(b2rt_ctx *ctx, const float dir_to_light[3], const float rgb[3], int32_t *light_id);
 int b2rt_clear_scene(b2rt_ctx *ctx);
 
 /* ---- acceleration structure: replaces OptiX "Sbvh"/"Bvh" (cudarender.cpp:44,50) ---------------- */

@@ -276,7 +276,8 @@ class _CScene(C.Structure):
                 ("analytic", C.c_void_p), ("prim_material", C.c_void_p), ("nmaterials", C.c_int32),
                 ("materials", C.c_void_p), ("nlights", C.c_int32), ("lights", C.c_void_p),
                 ("vnormal", C.c_void_p), ("vuv", C.c_void_p), ("tri_flags", C.c_void_p),
-                ("prim_light", C.c_void_p), ("light_nsamples", C.c_void_p)]
+                ("prim_light", C.c_void_p), ("light_nsamples", C.c_void_p),
+                ("light_ext", C.c_void_p), ("world_bounds", C.c_void_p)]
 
 
 def _bind_photon():
@@ -322,6 +323,8 @@ class PortFullScene:
         self.materials = []
         self.lights = []
         self.light_nsamples = []
+        self.light_ext = []
+        self.world_bounds = None      # scene box for distant lights: set from the GPU's accel_info().bounds (set_world_bounds)
 
     def add_material(self, mtype, rgb, kt=None, ior=1.5):
         kt = (1.0, 1.0, 1.0) if kt is None else kt
@@ -348,7 +351,28 @@ class PortFullScene:
         p = (0.0, 0.0, 0.0) if p is None else p
         self.lights.append([float(ltype), *map(float, p), *map(float, rgb), float(prim)])
         self.light_nsamples.append(int(nsamples))
+        self.light_ext.append(np.zeros(24, np.float32))
         return len(self.lights) - 1
+
+    def add_spot_light(self, l2w, w2l, rgb, cos_total, cos_falloff):
+        l2w, w2l = np.asarray(l2w, np.float32).reshape(3, 4), np.asarray(w2l, np.float32).reshape(3, 4)
+        ext = np.zeros(24, np.float32)
+        ext[0:9], ext[9:18], ext[18], ext[19] = l2w[:, :3].reshape(-1), w2l[:, :3].reshape(-1), cos_total, cos_falloff
+        self.lights.append([2.0, *map(float, l2w[:, 3]), *map(float, rgb), -1.0])
+        self.light_nsamples.append(1)
+        self.light_ext.append(ext)
+        return len(self.lights) - 1
+
+    def add_distant_light(self, dir_to_light, rgb):
+        ext = np.zeros(24, np.float32)
+        ext[20:23] = np.asarray(dir_to_light, np.float32)
+        self.lights.append([3.0, 0.0, 0.0, 0.0, *map(float, rgb), -1.0])
+        self.light_nsamples.append(1)
+        self.light_ext.append(ext)
+        return len(self.lights) - 1
+
+    def set_world_bounds(self, bounds6):
+        self.world_bounds = np.ascontiguousarray(bounds6, np.float32).reshape(6)
 
     def _cscene(self):
         kind, verts, idx, an = self.geo._arrays()
@@ -358,13 +382,16 @@ class PortFullScene:
         vn, vuv, tf = self.geo._attr_arrays()
         pl = np.asarray(self.prim_light, np.int32)
         lns = np.asarray(self.light_nsamples, np.int32)
-        keep = (kind, verts, idx, an, pm, mats, lights, vn, vuv, tf, pl, lns)
+        lext = np.ascontiguousarray(np.concatenate(self.light_ext)) if self.light_ext else None
+        wb = self.world_bounds
+        keep = (kind, verts, idx, an, pm, mats, lights, vn, vuv, tf, pl, lns, lext, wb)
         cs = _CScene(len(kind), _p(kind).value, _p(verts).value, _p(idx).value, _p(an).value,
                      _p(pm).value if len(pm) else None, len(mats),
                      _p(mats).value if len(mats) else None, len(lights), _p(lights).value if len(lights) else None,
                      _p(vn).value if vn is not None else None, _p(vuv).value if vuv is not None else None,
                      _p(tf).value if tf is not None else None, _p(pl).value if len(pl) else None,
-                     _p(lns).value if len(lns) else None)
+                     _p(lns).value if len(lns) else None, _p(lext).value if lext is not None else None,
+                     _p(wb).value if wb is not None else None)
         return cs, keep
 
     def camera_samples(self, seed, cam12, xy, gpix, ks, sampler_type=0, max_specular_depth=5, direct=True, slots=0):

@@ -37,22 +37,7 @@ int port_photon_trace_fg(const port_scene *sc, uint64_t seed, int64_t first_path
         float light_pdf = cdf[sc->nlights + 1 + lsel];
         const olight *Ls = &L[lsel];
         v3 o, d, Nl, Le; float tmin, pdf;
-        if (Ls->type == 0) {
-            o = Ls->p; d = uniform_sphere(u01(r0[1]), u01(r0[2])); Nl = d; tmin = 0.f;
-            pdf = 1.f / (4.f * O_PI); Le = Ls->rgb;
-        } else {
-            const float *D = sc->analytic + 28 * (int64_t)Ls->analytic;
-            float x, y;
-            concentric_disk(u01(r0[1]), u01(r0[2]), &x, &y);
-            x *= D[24]; y *= D[24];
-            xfp(D, V(x, y, D[25]), &o);
-            Nl = Ls->n;
-            d = uniform_sphere(u01(r1[0]), u01(r1[1]));
-            if (vdot(d, Nl) < 0.f) d = vscale(d, -1.f);
-            tmin = 1e-3f;
-            pdf = (1.f / Ls->area) * O_INV_TWOPI;
-            Le = (vdot(Nl, d) > 0.f) ? Ls->rgb : V(0, 0, 0);
-        }
+        o_emit(sc, Ls, r0, r1, &o, &d, &Nl, &Le, &tmin, &pdf);
         if (pdf == 0.f || black(Le)) continue;
         float ad = fabsf(vdot(Nl, d)), den = pdf * light_pdf;
         v3 alpha = V(ad * Le.x / den, ad * Le.y / den, ad * Le.z / den);

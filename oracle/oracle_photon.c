@@ -337,7 +337,17 @@ static v3 oct_decode(uint32_t w) {
 }
 
 /* ---- lights + emission ------------------------------------------------------------------------------------------ */
-typedef struct { int type; v3 p, rgb; int analytic; float area; v3 n; } olight;
+typedef struct { int type; v3 p, rgb; int analytic; float area; v3 n; const float *ext; v3 wc; float wr; } olight;
+/* SpotLight::Falloff (lights/spot.cpp:60-70) */
+static float spot_falloff(const olight *L, v3 w) {
+    const float *m = L->ext + 9;
+    v3 wl = vnormalize(V(m[0] * w.x + m[1] * w.y + m[2] * w.z, m[3] * w.x + m[4] * w.y + m[5] * w.z, m[6] * w.x + m[7] * w.y + m[8] * w.z));
+    float costheta = wl.z, ct = L->ext[18], cf = L->ext[19];
+    if (costheta < ct) return 0.f;
+    if (costheta > cf) return 1.f;
+    float delta = (costheta - ct) / (cf - ct);
+    return delta * delta * delta * delta;
+}
 static void derive_lights(const port_scene *sc, olight *L, float *cdf /* 2n+2 */) {
     int n = sc->nlights;
     float power[64];
@@ -345,10 +355,22 @@ static void derive_lights(const port_scene *sc, olight *L, float *cdf /* 2n+2 */
         const float *l = sc->lights + 8 * i;
         L[i].type = (int)l[0]; L[i].p = V(l[1], l[2], l[3]); L[i].rgb = V(l[4], l[5], l[6]);
         L[i].analytic = -1; L[i].area = 0.f; L[i].n = V(0, 0, 1);
+        L[i].ext = sc->light_ext ? sc->light_ext + 24 * i : NULL; L[i].wc = V(0, 0, 0); L[i].wr = 0.f;
         v3 P;
         if (L[i].type == 0) {
             float f = (float)(4.f * M_PI);                       /* PointLight::Power, lights/point.cpp:60-62 */
             P = V(f * L[i].rgb.x, f * L[i].rgb.y, f * L[i].rgb.z);
+        } else if (L[i].type == 2) {                             /* SpotLight::Power, lights/spot.cpp:72-75 */
+            float f = (float)M_PI, g = 1.f - .5f * (L[i].ext[19] + L[i].ext[18]);
+            P = V(L[i].rgb.x * 2.f * f * g, L[i].rgb.y * 2.f * f * g, L[i].rgb.z * 2.f * f * g);
+        } else if (L[i].type == 3) {                             /* DistantLight::Power over BBox::BoundingSphere */
+            const float *b = sc->world_bounds;
+            float c[3], d2 = 0.f;
+            for (int a = 0; a < 3; ++a) { c[a] = .5f * b[a] + .5f * b[3 + a]; float d = c[a] - b[3 + a]; d2 += d * d; }
+            L[i].wc = V(c[0], c[1], c[2]); L[i].wr = sqrtf(d2);
+            L[i].n = V(L[i].ext[20], L[i].ext[21], L[i].ext[22]);
+            float f = (float)M_PI;
+            P = V(L[i].rgb.x * f * L[i].wr * L[i].wr, L[i].rgb.y * f * L[i].wr * L[i].wr, L[i].rgb.z * f * L[i].wr * L[i].wr);
         } else {
             int prim = (int)l[7];
             int a = ~sc->kind[prim];
@@ -367,6 +389,52 @@ static void derive_lights(const port_scene *sc, olight *L, float *cdf /* 2n+2 */
     float fi = cdf[n];
     for (int i = 1; i <= n; ++i) cdf[i] = fi > 0.f ? cdf[i] / fi : (float)i / (float)n;
     for (int i = 0; i < n; ++i) cdf[n + 1 + i] = fi > 0.f ? power[i] / (fi * (float)n) : 1.f / (float)n;
+}
+
+/* Light::Sample_L for photon emission: point (lights/point.cpp:80-88), diffuse disk (lights/diffuse.cpp:89-101), spot
+ * (lights/spot.cpp:112-121), distant (lights/distant.cpp:84-105).  r0 / r1: the path's first two Philox blocks. */
+static void o_emit(const port_scene *sc, const olight *Ls, const uint32_t r0[4], const uint32_t r1[4], v3 *o, v3 *d, v3 *Nl,
+                   v3 *Le, float *tmin, float *pdf) {
+    if (Ls->type == 0) {
+        *o = Ls->p; *d = uniform_sphere(u01(r0[1]), u01(r0[2])); *Nl = *d; *tmin = 0.f;
+        *pdf = 1.f / (4.f * O_PI); *Le = Ls->rgb;
+    } else if (Ls->type == 2) {
+        const float u1 = u01(r0[1]), u2 = u01(r0[2]), ct = Ls->ext[18];
+        const float costheta = (1.f - u1) + u1 * ct;
+        const float sintheta = sqrtf(1.f - costheta * costheta);
+        float sn, cs;
+        port_sincos_quarter(4.f * u2, &sn, &cs);
+        const v3 v = V(cs * sintheta, sn * sintheta, costheta);
+        const float *m = Ls->ext;
+        *o = Ls->p;
+        *d = V(m[0] * v.x + m[1] * v.y + m[2] * v.z, m[3] * v.x + m[4] * v.y + m[5] * v.z, m[6] * v.x + m[7] * v.y + m[8] * v.z);
+        *Nl = *d; *tmin = 0.f;
+        *pdf = (float)(1.0 / ((double)(2.f) * 3.14159265358979323846 * (double)(1.f - ct)));
+        *Le = vscale(Ls->rgb, spot_falloff(Ls, *d));
+    } else if (Ls->type == 3) {
+        v3 v1, v2;
+        coord_system(Ls->n, &v1, &v2);
+        float d1, d2;
+        concentric_disk(u01(r0[1]), u01(r0[2]), &d1, &d2);
+        const v3 pdisk = vadd(Ls->wc, vscale(vadd(vscale(v1, d1), vscale(v2, d2)), Ls->wr));
+        *o = vadd(pdisk, vscale(Ls->n, Ls->wr));
+        *d = vneg(Ls->n);
+        *Nl = *d; *tmin = 0.f;
+        *pdf = (float)(1.0 / (3.14159265358979323846 * (double)Ls->wr * (double)Ls->wr));
+        *Le = Ls->rgb;
+    } else {
+        const float *D = sc->analytic + 28 * (int64_t)Ls->analytic;
+        float x, y;
+        concentric_disk(u01(r0[1]), u01(r0[2]), &x, &y);
+        x *= D[24]; y *= D[24];
+        xfp(D, V(x, y, D[25]), o);
+        *Nl = Ls->n;
+        *d = uniform_sphere(u01(r1[0]), u01(r1[1]));
+        if (vdot(*d, *Nl) < 0.f) *d = vscale(*d, -1.f);
+        *tmin = 1e-3f;
+        *pdf = (1.f / Ls->area) * O_INV_TWOPI;
+        *Le = (vdot(*Nl, *d) > 0.f) ? Ls->rgb : V(0, 0, 0);
+    }
 }
 
 int port_photon_trace(const port_scene *sc, uint64_t seed, int64_t first_path, int64_t n_paths, int max_depth,
@@ -391,22 +459,7 @@ int port_photon_trace(const port_scene *sc, uint64_t seed, int64_t first_path, i
         float light_pdf = cdf[sc->nlights + 1 + lsel];
         const olight *Ls = &L[lsel];
         v3 o, d, Nl, Le; float tmin, pdf;
-        if (Ls->type == 0) {
-            o = Ls->p; d = uniform_sphere(u01(r0[1]), u01(r0[2])); Nl = d; tmin = 0.f;
-            pdf = 1.f / (4.f * O_PI); Le = Ls->rgb;
-        } else {
-            const float *D = sc->analytic + 28 * (int64_t)Ls->analytic;
-            float x, y;
-            concentric_disk(u01(r0[1]), u01(r0[2]), &x, &y);
-            x *= D[24]; y *= D[24];
-            xfp(D, V(x, y, D[25]), &o);
-            Nl = Ls->n;
-            d = uniform_sphere(u01(r1[0]), u01(r1[1]));
-            if (vdot(d, Nl) < 0.f) d = vscale(d, -1.f);
-            tmin = 1e-3f;
-            pdf = (1.f / Ls->area) * O_INV_TWOPI;
-            Le = (vdot(Nl, d) > 0.f) ? Ls->rgb : V(0, 0, 0);
-        }
+        o_emit(sc, Ls, r0, r1, &o, &d, &Nl, &Le, &tmin, &pdf);
         if (pdf == 0.f || black(Le)) continue;
         float ad = fabsf(vdot(Nl, d)), den = pdf * light_pdf;
         v3 alpha = V(ad * Le.x / den, ad * Le.y / den, ad * Le.z / den);

@@ -37,6 +37,9 @@ typedef struct {
     const float *vnormal; const float *vuv; const uint8_t *tri_flags;
     /* camera pass only (may be NULL): area-light index per prim (-1 none), light samples per light */
     const int32_t *prim_light; const int32_t *light_nsamples;
+    /* spot / distant lights (types 2 / 3; may be NULL): 24 floats per light {l2w[9], w2l[9], cos_total, cos_falloff,
+     * dir_to_light[3], pad}; world_bounds[6] = the scene box the distant light's emission disk is derived from */
+    const float *light_ext; const float *world_bounds;
 } port_scene;
 /* per-sample oracle of the camera pass (oracle_render.h): see there */
 void port_camera_samples(const port_scene *sc, uint64_t seed, const float cam[12], int64_t n, const float *xy,

@@ -46,10 +46,11 @@ static v3 r_direct(const port_scene *sc, const olight *Ls, const osurf *s, const
     for (int li = 0; li < sc->nlights; ++li) {
         const olight *Lt = &Ls[li];
         const int light_prim = (int)sc->lights[8 * li + 7];
-        const int ns = Lt->type == 0 ? 1 : (sc->light_nsamples && sc->light_nsamples[li] > 1 ? sc->light_nsamples[li] : 1);
+        const int delta = Lt->type != 1;                  /* point, spot, distant */
+        const int ns = delta ? 1 : (sc->light_nsamples && sc->light_nsamples[li] > 1 ? sc->light_nsamples[li] : 1);
         v3 Ld = V(0, 0, 0);
         uint32_t scr[4] = {0, 0, 0, 0};
-        if (pattern && Lt->type != 0) philox(c0, 0xfffffffeu, (uint32_t)li, 0u, k0, k1, scr);
+        if (pattern && !delta) philox(c0, 0xfffffffeu, (uint32_t)li, 0u, k0, k1, scr);
         for (int j = 0; j < ns; ++j) {
             uint32_t r[4];
             philox(c0, c1, node, 0x100u + (uint32_t)(li * 64 + j), k0, k1, r);
@@ -58,14 +59,28 @@ static v3 r_direct(const port_scene *sc, const olight *Ls, const osurf *s, const
                 const uint32_t n = c1 * (uint32_t)ns + (uint32_t)j;
                 u_l1 = port_vdc(n, scr[0]); u_l2 = port_sobol2(n, scr[1]); u_b1 = port_vdc(n, scr[2]); u_b2 = port_sobol2(n, scr[3]);
             }
-            if (Lt->type == 0) {
+            if (Lt->type == 3) {                  /* DistantLight::Sample_L (lights/distant.cpp:48-55) */
+                v3 wi = Lt->n;
+                if (!(vdot(wi, s->ng) * vdot(wo, s->ng) > 0.f)) continue;
+                if (r_occluded(sc, s->p, wi, s->ray_eps, INFINITY)) continue;
+                float w = fabsf(vdot(wi, s->n));
+                Ld = vadd(Ld, V(f_lambert.x * Lt->rgb.x * w, f_lambert.y * Lt->rgb.y * w, f_lambert.z * Lt->rgb.z * w));
+                continue;
+            }
+            if (delta) {                          /* PointLight / SpotLight::Sample_L */
                 v3 dl = vsub(Lt->p, s->p);
                 float d2 = dl.x * dl.x + dl.y * dl.y + dl.z * dl.z;
                 v3 wi = vnormalize(dl);
                 if (!(vdot(wi, s->ng) * vdot(wo, s->ng) > 0.f)) continue;
+                v3 I = Lt->rgb;
+                if (Lt->type == 2) {
+                    float fo = spot_falloff(Lt, vneg(wi));
+                    if (fo == 0.f) continue;
+                    I = vscale(I, fo);
+                }
                 if (r_occluded(sc, s->p, dl, s->ray_eps, 1.f)) continue;
                 float w = fabsf(vdot(wi, s->n));
-                Ld = vadd(Ld, V(f_lambert.x * (Lt->rgb.x / d2) * w, f_lambert.y * (Lt->rgb.y / d2) * w, f_lambert.z * (Lt->rgb.z / d2) * w));
+                Ld = vadd(Ld, V(f_lambert.x * (I.x / d2) * w, f_lambert.y * (I.y / d2) * w, f_lambert.z * (I.z / d2) * w));
                 continue;
             }
             const float *D = sc->analytic + 28 * (int64_t)Lt->analytic;

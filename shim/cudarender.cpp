@@ -28,6 +28,8 @@
 #include "samplers/lowdiscrepancy.h"
 #include "filters/box.h"
 #include "cameras/perspective.h"
+#include "lights/spot.h"
+#include "lights/distant.h"
 #include "filters/triangle.h"
 #include "filters/gaussian.h"
 #include "filters/mitchell.h"
@@ -304,6 +306,18 @@ void CudaRender::Render(const Scene *scene) {
             } else {
                 check(b2rt_add_light(ctx_, B2RT_LIGHT_DISK_AREA, NULL, rgb, it->second, l->nSamples, &id), "b2rt_add_light");
             }
+        } else if (const SpotLight *sl = dynamic_cast<const SpotLight *>(l)) {
+            // SpotLight keeps everything private without a friend line (lights/spot.h:57-61; the reference only warns for
+            // it, cudalight.cpp:61-71); this file is compiled with -fno-access-control
+            float l2w[12], w2l[12];
+            m34(sl->LightToWorld.GetMatrix(), l2w);
+            m34(sl->WorldToLight.GetMatrix(), w2l);
+            rgb3(sl->Intensity, rgb);
+            check(b2rt_add_spot_light(ctx_, l2w, w2l, rgb, sl->cosTotalWidth, sl->cosFalloffStart, &id), "b2rt_add_spot_light");
+        } else if (const DistantLight *dl = dynamic_cast<const DistantLight *>(l)) {
+            float d[3] = {dl->lightDir.x, dl->lightDir.y, dl->lightDir.z};
+            rgb3(dl->L, rgb);
+            check(b2rt_add_distant_light(ctx_, d, rgb, &id), "b2rt_add_distant_light");
         } else {
             Warning("CudaRender: light %d has a type the CUDA renderer does not translate, treated as black", (int)i);
             rgb[0] = rgb[1] = rgb[2] = 0.f;

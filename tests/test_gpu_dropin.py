@@ -142,3 +142,21 @@ def test_dropin_integer_gpus_gives_the_same_image(tmp_path, monkeypatch):
         assert r.returncode == 0, r.stderr[-2000:]
         imgs.append(S.read_pfm(pf))
     assert imgs[0].max() > 0 and np.array_equal(imgs[0], imgs[1])
+
+
+@pytest.mark.skipif(not os.path.exists(BIN), reason="shim/_build/pbrt_b2rt not built (needs /root/reference)")
+@pytest.mark.parametrize("light", ["spot", "distant"])
+def test_dropin_spot_and_distant_lights(tmp_path, light):
+    """`LightSource "spot"` / `"distant"` in the scene file (the reference's GPU path skips both with a warning): direct
+    lighting and photon map against pbrt's CPU renderer on the same file."""
+    desc = S.cornell_scene(boxes=True, light=light)
+    gpu, cpu = _run(tmp_path, light + "_direct", 'SurfaceIntegrator "directlighting" "integer maxdepth" [5]', "simple", spp=64,
+                    res=64, desc=desc)
+    m = S.image_metrics(_block(gpu, 8), _block(cpu, 8))
+    assert abs(m["bias_rel"]) < 0.005 and m["mean_rel"] < 0.012, m
+    prm = ('"integer causticphotons" [10000] "integer indirectphotons" [200000] "integer nused" [100] "float maxdist" [0.4] '
+           '"bool finalgather" ["false"]')
+    gpu, cpu = _run(tmp_path, light + "_photon", 'SurfaceIntegrator "photonmap" ' + prm, 'Renderer "photonmap" ' + prm, spp=16,
+                    res=64, desc=desc)
+    m = S.image_metrics(_block(gpu, 8), _block(cpu, 8))
+    assert abs(m["bias_rel"]) < 0.015 and m["mean_rel"] < 0.04, m

@@ -131,3 +131,37 @@ def test_camera_samples_match_the_c_oracle(built, sampler, spp, light):
         m = nq > j
         assert np.array_equal(got[m, j].view(np.uint32), eq[m, j].view(np.uint32))
     assert rgb.max() > 0.5 and (rgb.sum(1) > 0).mean() > 0.5
+
+
+# ---- spot and distant lights (the reference's cudalight.cpp:61-71 only warns for them) -----------------
+@pytest.mark.parametrize("light", ["spot", "distant", "mixed"])
+def test_delta_lights_photons_and_camera_samples_match_the_c_oracle(built, light):
+    """pbrt SpotLight / DistantLight (lights/spot.cpp, lights/distant.cpp): photon emission (cone / scene-sized disk), light
+    power for the emission CDF, and direct lighting -- photons and per-sample camera-pass radiance bit-exact against the C port."""
+    from oracle import oracle as O
+    desc = S.cornell_scene(light=light)
+    seed, n_paths = 17, 20000
+    cam = b2rt.pbrt_camera((0, 1, 3.4), (0, 1, 0), (0, 1, 0), 40, 48, 48)
+    win = (8, 40, 10, 42)
+    with b2rt.Context(0, seed=seed) as c:
+        S.fill_scene(c, desc)
+        info = c.build_accel()
+        c.photons_trace(0, n_paths)
+        gc, gi = c.photons_download(0), c.photons_download(1)
+        rgb, nq, q = c.camera_samples(cam, spp=2, window=win, queries=True)
+    ps = O.PortFullScene()
+    S.fill_scene(ps, desc)
+    ps.set_world_bounds(np.array(list(info.bounds), np.float32))
+    oc, oi = ps.photon_trace(seed, 0, n_paths)
+    assert len(oi) > 2000
+    assert np.array_equal(gc.view(np.uint32), oc.view(np.uint32)) and np.array_equal(gi.view(np.uint32), oi.view(np.uint32))
+    x0, x1, y0, y1 = win
+    xy = O.sample_positions("random", seed, 48, 48, (x0, y0, x1, y1), 2)
+    py, px = np.meshgrid(np.arange(y0, y1), np.arange(x0, x1), indexing="ij")
+    gpix = np.repeat((py * 48 + px).reshape(-1).astype(np.uint32), 2)
+    ks = np.tile(np.arange(2, dtype=np.uint32), (x1 - x0) * (y1 - y0))
+    cam12 = np.array([*cam.o, *cam.A, *cam.B, *cam.C], np.float32)
+    ergb, enq, _ = ps.camera_samples(seed, cam12, xy, gpix, ks, slots=q.shape[1])
+    assert np.array_equal(nq, enq)
+    assert np.array_equal(rgb.view(np.uint32), ergb.view(np.uint32)), float(np.abs(rgb - ergb).max())
+    assert rgb.max() > 0.05
