@@ -673,7 +673,7 @@ SYMBOLS += ["b2rt_multi_create", "b2rt_multi_resize", "b2rt_multi_destroy", "b2r
             "b2rt_multi_photons_trace", "b2rt_multi_photons_shoot", "b2rt_multi_photons_trace_fg",
             "b2rt_multi_photon_grid_build", "b2rt_multi_radiance_compute", "b2rt_multi_final_gather_set",
             "b2rt_multi_sampler_set", "b2rt_multi_film_set_filter", "b2rt_multi_render_frame"]
-EXCHANGE_MODES = {0: "fused peer stores", 1: "nccl broadcast", 2: "peer copies"}
+EXCHANGE_MODES = {0: "fused peer stores", 1: "nccl broadcast", 2: "peer copies", 3: "push kernel"}
 
 
 class MultiStats(C.Structure):

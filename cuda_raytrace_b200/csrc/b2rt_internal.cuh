@@ -218,6 +218,7 @@ int b2rt_photons_trace_commit(b2rt_ctx *ctx, int64_t n_paths, int max_depth, con
 int b2rt_photons_trace_fg_begin(b2rt_ctx *ctx, int64_t first_path, int64_t n_paths, int max_depth, uint32_t tot[2]);
 int b2rt_photons_trace_fg_commit(b2rt_ctx *ctx, int64_t n_paths, int max_depth, const PhotonDst &dst);
 int b2rt_photons_reserve(b2rt_ctx *ctx, DevBuf &b, int64_t keep, int64_t want);
+int b2rt_photons_push(b2rt_ctx *ctx, const b2rt_photon *src, int64_t n_photons, const PhotonDst &dst);   // dst.a[0 .. n): peers
 int b2rt_photon_grid_build_impl(b2rt_ctx *ctx, int map, float cell_size, float target_per_cell);
 int b2rt_render_impl(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_params *fp, float *d_out);
 int b2rt_render_pixels_impl(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_params *fp, const uint32_t *d_pixmap,

@@ -71,7 +71,7 @@ struct Worker {
     int rc = 0;
 };
 
-enum { EXCH_FUSED = 0, EXCH_NCCL = 1, EXCH_COPY = 2 };
+enum { EXCH_FUSED = 0, EXCH_NCCL = 1, EXCH_COPY = 2, EXCH_PUSH = 3 };
 
 }  // namespace
 
@@ -173,7 +173,7 @@ int sharded_pass(b2rt_multi *m, int64_t first, int64_t n_paths, int mapA, int ma
     });
     if (rc) return rc;
     const double t2 = now_ms();
-    const int mode = (m->exchange == EXCH_FUSED && !m->peer && G > 1) ? EXCH_COPY : m->exchange;
+    const int mode = ((m->exchange == EXCH_FUSED || m->exchange == EXCH_PUSH) && !m->peer && G > 1) ? EXCH_COPY : m->exchange;
     rc = parallel(m, [&](int i) -> int {
         b2rt_ctx *c = m->ctx[i];
         int64_t lo, cnt;
@@ -192,6 +192,23 @@ int sharded_pass(b2rt_multi *m, int64_t first, int64_t n_paths, int mapA, int ma
         }
         int r = commit(i, cnt, dst);
         if (r) return r;
+        if (mode == EXCH_PUSH) {
+            // local slice -> the same place in every peer's array, one coalesced copy kernel per map
+            const int maps[2] = {mapA, mapB};
+            const int64_t *offs[2] = {offA, offB};
+            const int64_t bases[2] = {baseA, baseB};
+            for (int t = 0; t < 2; ++t) {
+                const int64_t np = offs[t][i + 1] - offs[t][i];
+                PhotonDst peers;
+                peers.n = 0;
+                for (int k = 1; k < G; ++k) {
+                    const int g = (i + k) % G;
+                    peers.a[peers.n++] = m->ctx[g]->maps[maps[t]].photons.as<b2rt_photon>() + bases[t] + offs[t][i];
+                }
+                r = b2rt_photons_push(c, c->maps[maps[t]].photons.as<b2rt_photon>() + bases[t] + offs[t][i], np, peers);
+                if (r) return r;
+            }
+        }
         if (mode == EXCH_COPY) {
             for (int k = 1; k < G; ++k) {           // staggered so that not everybody targets the same peer first
                 const int g = (i + k) % G;
@@ -297,6 +314,7 @@ int b2rt_multi_create(int ngpus, const int *devices, uint64_t seed, b2rt_multi *
     if (const char *v = getenv("B2RT_MGPU_EXCHANGE")) {
         if (!strcmp(v, "nccl")) m->exchange = EXCH_NCCL;
         else if (!strcmp(v, "copy")) m->exchange = EXCH_COPY;
+        else if (!strcmp(v, "push")) m->exchange = EXCH_PUSH;
         else m->exchange = EXCH_FUSED;
     }
     if (m->exchange == EXCH_NCCL && ngpus > 1) {
@@ -394,7 +412,7 @@ b2rt_ctx *b2rt_multi_ctx(b2rt_multi *m, int i) { return (m && i >= 0 && i < m->n
 int b2rt_multi_info(b2rt_multi *m, int32_t *peer_access, int32_t *exchange_mode) {
     if (!m) return B2RT_E_ARG;
     if (peer_access) *peer_access = m->peer ? 1 : 0;
-    if (exchange_mode) *exchange_mode = (m->exchange == EXCH_FUSED && !m->peer && m->n > 1) ? EXCH_COPY : m->exchange;
+    if (exchange_mode) *exchange_mode = ((m->exchange == EXCH_FUSED || m->exchange == EXCH_PUSH) && !m->peer && m->n > 1) ? EXCH_COPY : m->exchange;
     return B2RT_OK;
 }
 

@@ -320,6 +320,25 @@ int b2rt_photons_reserve(b2rt_ctx *ctx, DevBuf &b, int64_t keep, int64_t want) {
     return B2RT_OK;
 }
 
+// B2RT_MGPU_EXCHANGE=push: the slice was compacted into this GPU's own array; a grid-stride copy stores it into the same
+// place of the peers' arrays, 16 bytes per thread and destination: whole 512-byte lines per warp over NVLink where the
+// compaction kernel's peer stores are 32-byte pieces at path-dependent offsets.
+__global__ void __launch_bounds__(256)
+photon_push_kernel(const float4 *__restrict__ src, int64_t n16, const PhotonDst dst) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (int64_t)gridDim.x * blockDim.x) {
+        const float4 v = src[i];
+        for (int g = 0; g < dst.n; ++g) reinterpret_cast<float4 *>(dst.a[g])[i] = v;
+    }
+}
+int b2rt_photons_push(b2rt_ctx *ctx, const b2rt_photon *src, int64_t n_photons, const PhotonDst &dst) {
+    if (n_photons <= 0 || dst.n <= 0) return B2RT_OK;
+    const int64_t n16 = n_photons * 2;
+    const int64_t blocks = std::min<int64_t>((n16 + 255) / 256, (int64_t)ctx->sm_count * 8);
+    photon_push_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(reinterpret_cast<const float4 *>(src), n16, dst);
+    B2RT_LAUNCH_CHECK(ctx);
+    return B2RT_OK;
+}
+
 // Photon pass in two steps so that several GPUs can meet in the middle (multi.cu): `begin` traces the paths into per-path
 // slots, scans the per-path counts and returns how many photons each map gains; `commit` compacts them to wherever the
 // caller says -- the local arrays (single GPU) or this GPU's slice of every GPU's arrays.

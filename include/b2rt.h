@@ -310,7 +310,8 @@ void b2rt_multi_destroy(b2rt_multi *m);
 const char *b2rt_multi_last_error(b2rt_multi *m);
 int  b2rt_multi_count(b2rt_multi *m);
 b2rt_ctx *b2rt_multi_ctx(b2rt_multi *m, int i);
-/* peer_access: 1 if every pair of the devices has peer access; exchange_mode: 0 fused peer stores, 1 NCCL, 2 peer copies */
+/* peer_access: 1 if every pair of the devices has peer access; exchange_mode: 0 fused peer stores, 1 NCCL, 2 peer copies,
+ * 3 push kernel (B2RT_MGPU_EXCHANGE=push: local compaction, then one coalesced copy kernel stores the slice into the peers) */
 int  b2rt_multi_info(b2rt_multi *m, int32_t *peer_access, int32_t *exchange_mode);
 int  b2rt_multi_stats_get(b2rt_multi *m, b2rt_multi_stats *out, int reset);
 int  b2rt_multi_build_accel(b2rt_multi *m);                     /* every device builds the same deterministic BVH */

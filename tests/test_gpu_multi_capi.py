@@ -55,7 +55,7 @@ def single(built):
     return desc, cam, out
 
 
-@pytest.mark.parametrize("mode", ["fused", "copy", "nccl"])
+@pytest.mark.parametrize("mode", ["fused", "push", "copy", "nccl"])
 @pytest.mark.parametrize("group", _groups(), ids=[g[0] for g in _groups()])
 def test_multi_matches_single_context(single, group, mode, monkeypatch):
     desc, cam, ref = single

@@ -24,6 +24,7 @@ for job in "$@"; do
     sanmem)   python -c "import __graft_entry__ as g; g.smoke()" > $O/plain_smoke.log 2>&1 && timeout 1500 compute-sanitizer --tool memcheck --log-file $O/sanitizer_memcheck.txt python -c "import __graft_entry__ as g; g.smoke()" > $O/san_memcheck_run.log 2>&1; echo "rc=$?" >> $O/san_memcheck_run.log ;;
     sanrace)  python -c "import __graft_entry__ as g; g.smoke()" > $O/plain_smoke.log 2>&1 && timeout 1500 compute-sanitizer --tool racecheck --log-file $O/sanitizer_racecheck.txt python -c "import __graft_entry__ as g; g.smoke()" > $O/san_racecheck_run.log 2>&1; echo "rc=$?" >> $O/san_racecheck_run.log ;;
     saninit)  python -c "import __graft_entry__ as g; g.smoke()" > $O/plain_smoke.log 2>&1 && timeout 1500 compute-sanitizer --tool initcheck --log-file $O/sanitizer_initcheck.txt python -c "import __graft_entry__ as g; g.smoke()" > $O/san_initcheck_run.log 2>&1; echo "rc=$?" >> $O/san_initcheck_run.log ;;
+    exch:*)   timeout 600 python tools/bench_exchange.py ${job#exch:} > $O/exchange_n${job#exch:}.jsonl 2> $O/exchange.err ;;
     topo)     nvidia-smi topo -m > $O/topo.txt 2>&1 ;;
     abplanes) for v in 0 1 0 1; do B2RT_TRACE_PLANES=$v timeout 300 python bench.py --steps 100 --no-cpu-baseline --no-photon-extra > $O/bench_planes$v.json 2>> $O/abplanes.err; python -c "import json;d=json.load(open('$O/bench_planes$v.json'));print('planes',$v,d['value'],d['closest_hit_mrays'],d['any_hit_mrays'],d['incoherent_closest_hit_mrays'])" >> $O/abplanes.txt; done ;;
     tracestats) timeout 300 python tools/trace_stats.py > $O/trace_stats.json 2> $O/trace_stats.err ;;
