@@ -122,8 +122,7 @@ struct b2rt_ctx {
     int gather_tcap = 1024;      // gather variant 2: positions in the shared tile (1024 -> 7 blocks per SM, 2048 -> 5)
     int gather_qt = 8;           // gather variant 2: consecutive queries that share one staged tile (8, 16 or 32)
     int gather_variant = 2;      // 0: row-by-row scan with direct loads, 1: coarse table + TMA-staged tiles per warp,
-                                 // 2: one TMA-staged tile shared by a block's consecutive queries (default),
-                                 // 3: the same tiles through a producer / consumer warp pipeline
+                                 // 2: one TMA-staged tile shared by a block's consecutive queries (default)
 
     // host-side staging of the scene (flattened)
     std::vector<float> h_verts;      // xyz

@@ -894,209 +894,11 @@ gather_block_kernel(const GatherArgs A) {
 }
 
 
-// ---- warp-specialised pipeline variant (B2RT_GATHER_VARIANT=3) --------------------------------------------------------
-// Same tiles and the same per-query work as gather_block_kernel, but the phases no longer run in lock step: warp 0 is
-// a PRODUCER that prepares tile t+1 (radii, union box, row bounds, prefix sums, cp.async.bulk into the other half of a
-// double-buffered shared tile) while the GP_CONS consumer warps scan tile t.  Hand-over by mbarriers: full[b] (producer's
-// arrive.expect_tx + the TMA transaction bytes) and empty[b] (one arrive per consumer warp once it has finished the tile,
-// fall-backs included).  ncu of the lock-step kernel: 1.2-1.7 warps per issue stalled at the block barrier and
-// issue-active ~50 % - the latency of phases A-C was exposed once per tile.
-// Measured (run r02u): identical bytes, but SLOWER than the lock-step kernel - camera pass 19.1 ms against 15.9 ms.  The
-// per-query work is a chain of short dependent steps (ballot, popc, shared store, REDUX) that needs many resident
-// warps; at 96 registers the pipeline keeps 4 blocks x 4 consumer warps per SM against 28 scanning warps of the
-// lock-step kernel, and the hidden set-up latency does not buy that back (5 blocks at 72 registers: 19.5 ms).  Kept as
-// an A/B schedule, not the default.
-constexpr int GP_CONS = 4;
-constexpr int GP_THREADS = 32 * (GP_CONS + 1);
-constexpr int GP_QT = 2 * GP_CONS;
-constexpr int GP_TCAP = 1024;
-constexpr int GP_RPL = 8;                       // rows per producer lane: union boxes of up to 256 rows
-static_assert(GP_CONS * G2_STAGE <= GP_TCAP, "fallback staging slices must fit in one tile buffer");
+// (A warp-specialised producer / consumer version of the same tiles -- one producer warp TMA-staging tile t + 1 into a
+// double-buffered shared tile while four consumer warps scan tile t, hand-over by full / empty mbarriers -- was built in round
+// 1 as B2RT_GATHER_VARIANT=3: identical bytes, but 19.1 against 15.9 ms for the camera pass, because the
+// per-query work wants many resident warps.  Removed in round 2; the code is in the history at commit 4f8443c.)
 
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-
-__global__ void __launch_bounds__(GP_THREADS, 4)
-gather_pipe_kernel(const GatherArgs A) {
-    __shared__ __align__(128) float4 s_tile[2][GP_TCAP];
-    __shared__ uint64_t s_cand[GP_CONS][GATHER_CAP];
-    __shared__ float4 s_q[2][GP_QT];
-    __shared__ uint32_t s_T[2];
-    __shared__ int s_ok[2];
-    __shared__ __align__(8) uint64_t s_full[2], s_empty[2], s_wbar[GP_CONS];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const Gather2Grid &g = A.g;
-    const uint32_t lt = (1u << lane) - 1u;
-    if (tid == 0) {
-        mbar_init(smem_addr(&s_full[0]), 1); mbar_init(smem_addr(&s_full[1]), 1);
-        mbar_init(smem_addr(&s_empty[0]), GP_CONS); mbar_init(smem_addr(&s_empty[1]), GP_CONS);
-        for (int w = 0; w < GP_CONS; ++w) mbar_init(smem_addr(&s_wbar[w]), 1);
-    }
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    __syncthreads();
-    const int64_t ntiles = (A.nq + GP_QT - 1) / GP_QT;
-
-    if (warp == 0) {
-        // =============================== producer ===============================
-        uint32_t it = 0;
-        for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
-            const int b = (int)(it & 1u);
-            const uint32_t full = smem_addr(&s_full[b]), empty = smem_addr(&s_empty[b]), tile_a = smem_addr(s_tile[b]);
-            mbar_wait(empty, ((it >> 1) & 1u) ^ 1u);            // the consumers are done with this buffer (passes at once the first two times)
-            const int64_t q0 = tile * GP_QT;
-            const int nqt = (int)(A.nq - q0 < GP_QT ? A.nq - q0 : GP_QT);
-            // ---- A: per-query radius and cell box, union over the tile ------------------------------------------
-            int lo[3] = {0x7fffffff, 0x7fffffff, 0x7fffffff}, hi[3] = {-1, -1, -1};
-            if (lane < nqt) {
-                const float4 a0 = __ldg(reinterpret_cast<const float4 *>(A.queries + q0 + lane));
-                const float pa[3] = {a0.x, a0.y, a0.z};
-                int C[3], cf[3];
-#pragma unroll
-                for (int a = 0; a < 3; ++a) {
-                    cf[a] = min(max((int)floorf((pa[a] - g.lo[a]) * g.inv), 0), g.dims[a] - 1);
-                    C[a] = cf[a] >> G2_SHIFT;
-                }
-                uint32_t n8 = 0;
-#pragma unroll
-                for (int c = 0; c < 8; ++c) {
-                    const int o[3] = {c & 1, (c >> 1) & 1, c >> 2};
-                    int P[3];
-                    bool in = true;
-#pragma unroll
-                    for (int a = 0; a < 3; ++a) {
-                        P[a] = C[a] - ((cf[a] & (G2_C - 1)) < G2_C / 2 ? 1 : 0) + o[a];
-                        in = in && P[a] >= 0 && P[a] < g.cdims[a];
-                    }
-                    if (in) n8 += __ldg(A.coarse + ((int64_t)P[2] * g.cdims[1] + P[1]) * g.cdims[0] + P[0]);
-                }
-                float r2_try = A.max_dist2;
-                if (n8 > 0) r2_try = fminf((A.target * 64.f * B2_INV_PI) * (float)A.k * g.cell * g.cell / (float)n8, A.max_dist2);
-                const float r = sqrtf(r2_try) * 1.0001f + g.slack;
-#pragma unroll
-                for (int a = 0; a < 3; ++a) {
-                    lo[a] = min(max((int)floorf((pa[a] - r - g.lo[a]) * g.inv), 0), g.dims[a] - 1);
-                    hi[a] = min(max((int)floorf((pa[a] + r - g.lo[a]) * g.inv), 0), g.dims[a] - 1);
-                }
-                s_q[b][lane] = make_float4(pa[0], pa[1], pa[2], r2_try);
-            }
-#pragma unroll
-            for (int a = 0; a < 3; ++a) {
-                lo[a] = __reduce_min_sync(0xffffffffu, lo[a]);
-                hi[a] = __reduce_max_sync(0xffffffffu, hi[a]);
-            }
-            const int x0 = lo[0], y0 = lo[1], z0 = lo[2], x1 = hi[0], ny = hi[1] - lo[1] + 1, nz = hi[2] - lo[2] + 1;
-            const int R = ny * nz;
-            bool tile_ok = R <= 32 * GP_RPL;
-            // ---- B: row j * 32 + lane of the union box for j < GP_RPL, offsets in row order ----------------------
-            uint32_t rb_[GP_RPL], rn_[GP_RPL], off_[GP_RPL], T = 0;
-            if (tile_ok) {
-#pragma unroll
-                for (int j = 0; j < GP_RPL; ++j) {
-                    const int row = j * 32 + lane;
-                    rb_[j] = 0; rn_[j] = 0;
-                    if (row < R) {
-                        const int z = z0 + row / ny, y = y0 + row % ny;
-                        const int64_t rb = ((int64_t)z * g.dims[1] + y) * g.dims[0];
-                        const uint32_t s0 = __ldg(A.cell_start + rb + x0), e0 = __ldg(A.cell_start + rb + x1 + 1);
-                        rb_[j] = s0; rn_[j] = e0 - s0;
-                    }
-                }
-#pragma unroll
-                for (int j = 0; j < GP_RPL; ++j) {
-                    if (j * 32 >= R) { off_[j] = T; continue; }
-                    uint32_t inc = rn_[j];
-#pragma unroll
-                    for (int o = 1; o < 32; o <<= 1) {
-                        const uint32_t up = __shfl_up_sync(0xffffffffu, inc, o);
-                        if (lane >= o) inc += up;
-                    }
-                    off_[j] = T + inc - rn_[j];
-                    T += __shfl_sync(0xffffffffu, inc, 31);
-                }
-                tile_ok = T <= GP_TCAP;
-            }
-            if (lane == 0) { s_T[b] = T; s_ok[b] = tile_ok ? 1 : 0; }
-            __syncwarp();
-            // ---- C: stage every run into this buffer; the consumers are released by full[b] ---------------------
-            if (tile_ok && T > 0) {
-                if (lane == 0) mbar_expect_tx(full, T * 16u);
-#pragma unroll
-                for (int j = 0; j < GP_RPL; ++j)
-                    if (rn_[j]) tma_bulk_g2s(tile_a + off_[j] * 16u, A.pos4 + rb_[j], rn_[j] * 16u, full);
-            } else if (lane == 0) {
-                mbar_arrive(full);
-            }
-        }
-        return;
-    }
-
-    // =============================== consumers ===============================
-    const int cw = warp - 1;
-    uint64_t *cand = s_cand[cw];
-    const uint32_t wbar = smem_addr(&s_wbar[cw]);
-    uint32_t wphase = 0, it = 0;
-    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
-        const int b = (int)(it & 1u);
-        mbar_wait(smem_addr(&s_full[b]), (it >> 1) & 1u);
-        const int64_t q0 = tile * GP_QT;
-        const int nqt = (int)(A.nq - q0 < GP_QT ? A.nq - q0 : GP_QT);
-        const uint32_t T = s_T[b];
-        const bool tile_ok = s_ok[b] != 0;
-        const float4 *tilep = s_tile[b];
-        uint32_t failed = 0;
-        for (int j = 0; j < GP_QT / GP_CONS; ++j) {
-            const int qi = cw + j * GP_CONS;
-            if (qi >= nqt) break;
-            if (!tile_ok) { failed |= 1u << j; continue; }
-            const float4 qv = s_q[b][qi];
-            uint64_t bound = (uint64_t)__float_as_uint(qv.w) << 32;
-            int count = 0;
-            for (uint32_t i0 = 0; i0 < T; i0 += 32) {
-                const uint32_t i = i0 + lane;
-                bool pass = false;
-                uint64_t key = 0;
-                if (i < T) {
-                    const float4 pa = tilep[i];
-                    const float dx = pa.x - qv.x, dy = pa.y - qv.y, dz = pa.z - qv.z;
-                    const float d2 = dx * dx + dy * dy + dz * dz;
-                    key = ((uint64_t)__float_as_uint(d2) << 32) | __float_as_uint(pa.w);
-                    pass = key < bound;
-                }
-                const uint32_t m = __ballot_sync(0xffffffffu, pass);
-                if (m) {
-                    if (pass) cand[CI(count + __popc(m & lt))] = key;
-                    count += __popc(m);
-                    __syncwarp();
-                    if (count > GATHER_CAP - 32) { bound = warp_keep(cand, count, A.k, lane); count = A.k; }
-                }
-            }
-            if (count >= A.k || qv.w >= A.max_dist2) {
-                const float4 *qp = reinterpret_cast<const float4 *>(A.queries + q0 + qi);
-                const float4 a0 = __ldg(qp), a1 = __ldg(qp + 1), a2 = __ldg(qp + 2);
-                gather_finish<true>(A, q0 + qi, mk3(a0.w, a1.x, a1.y), mk3(a1.z, a1.w, a2.x), cand, count, mk3(0.f, 0.f, 0.f), 0, lane,
-                                    true);                      // rows were staged in ascending cell order
-            } else {
-                failed |= 1u << j;
-            }
-        }
-        // fall-backs stage into a private slice of THIS tile buffer, so every consumer must be done scanning it first
-        fence_proxy_async_smem();
-        asm volatile("bar.sync 1, %0;" ::"n"(GP_CONS * 32) : "memory");
-        if (failed) {
-            for (int j = 0; j < GP_QT / GP_CONS; ++j) {
-                if (!((failed >> j) & 1u)) continue;
-                const int qi = cw + j * GP_CONS;
-                const float r2_next = tile_ok ? s_q[b][qi].w * 4.f : -1.f;
-                gather_query_warp<true>(A, q0 + qi, r2_next, cand, s_tile[b] + cw * G2_STAGE,
-                                        smem_addr(s_tile[b]) + (uint32_t)(cw * G2_STAGE) * 16u, wbar, wphase, lane);
-            }
-        }
-        fence_proxy_async_smem();               // this warp's generic reads of the buffer before the producer's next async writes
-        __syncwarp();
-        if (lane == 0) mbar_arrive(smem_addr(&s_empty[b]));
-    }
-}
 
 }  // namespace
 
@@ -1134,16 +936,7 @@ int b2rt_gather_impl(b2rt_ctx *ctx, int map, int64_t nq, const b2rt_query *d_que
         A.pos4 = m.pos4.as<float4>(); A.photons = m.sorted.as<b2rt_photon>(); A.cell_start = m.cell_start.as<uint32_t>();
         A.coarse = m.coarse.as<uint32_t>(); A.g = g2; A.queries = d_queries; A.nq = nq; A.k = k; A.max_dist2 = max_dist2;
         A.n_paths = npaths; A.target = ctx->gather_target; A.out_rgb = d_rgb; A.out_r2 = d_r2; A.out_found = d_found; A.idx_out = d_idx;
-        if (k > 0 && ctx->gather_variant == 3) {
-            int &bsm = ctx->gather_blocks_per_sm[3];
-            if (bsm == 0) {
-                B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bsm, gather_pipe_kernel, GP_THREADS, 0));
-                if (bsm < 1) bsm = 1;
-            }
-            int64_t nb = (nq + GP_QT - 1) / GP_QT;
-            if (nb > (int64_t)ctx->sm_count * bsm) nb = (int64_t)ctx->sm_count * bsm;
-            gather_pipe_kernel<<<(unsigned)nb, GP_THREADS, 0, ctx->stream>>>(A);
-        } else if (k > 0 && ctx->gather_variant == 2) {
+        if (k > 0 && ctx->gather_variant >= 2) {
             const int qt = ctx->gather_qt == 32 ? 32 : (ctx->gather_qt == 16 ? 16 : 8);
             // default: 1024-position tile, 7 blocks per SM (r01z sweep: camera pass 15.9 ms against 17.2 ms with 2048 / 5)
             void (*kern)(const GatherArgs) = gather_block_kernel<8, 1024, 7>;
