@@ -287,7 +287,8 @@ wide_collapse_level_kernel(const int32_t *__restrict__ queue_in, int nq, int n,
 // only shared counter is the next level's queue tail, bumped once per warp (ballot + prefix over the lanes' child counts).
 // The queue order is scheduling-dependent but never reaches the output: a root's children are a function of the binary
 // tree alone and node indices come from the prefix sum over wide_flag.
-// ctl[0], ctl[1] = sizes of queue A / B, ctl[5] = number of levels
+// ctl[0 .. 2] = queue sizes of levels L, L + 1, L + 2 in rotation (the third one is zeroed while level L runs, so one
+// grid.sync per level is enough), ctl[5] = number of levels
 __global__ void __launch_bounds__(256)
 wide_collapse_coop_kernel(int n, const int32_t *__restrict__ child, const float *__restrict__ box,
                           const uint8_t *__restrict__ collapse, WideTmp *__restrict__ tmp,
@@ -297,9 +298,11 @@ wide_collapse_coop_kernel(int n, const int32_t *__restrict__ child, const float 
     const int64_t gsize = (int64_t)gridDim.x * blockDim.x;
     int cur = 0, levels = 0;
     for (;;) {
-        const uint32_t nq = ((volatile uint32_t *)ctl)[cur];
+        const int c0 = levels % 3, c1 = (levels + 1) % 3, c2 = (levels + 2) % 3;
+        const uint32_t nq = ((volatile uint32_t *)ctl)[c0];
         if (nq == 0) break;
         ++levels;
+        if (blockIdx.x == 0 && threadIdx.x == 0) ((volatile uint32_t *)ctl)[c2] = 0u;     // the level after next starts empty
         const int32_t *qin = cur ? qb : qa;
         int32_t *qout = cur ? qa : qb;
         // whole warps iterate together (the ballot below needs every lane)
@@ -340,12 +343,10 @@ wide_collapse_coop_kernel(int n, const int32_t *__restrict__ child, const float 
             }
             const int total = __shfl_sync(0xffffffffu, inc, 31);
             uint32_t at = 0;
-            if (lane == 31 && total > 0) at = atomicAdd(&ctl[cur ^ 1], (uint32_t)total);
+            if (lane == 31 && total > 0) at = atomicAdd(&ctl[c1], (uint32_t)total);
             at = __shfl_sync(0xffffffffu, at, 31) + (uint32_t)(inc - no);
             for (int k = 0; k < no; ++k) qout[at + k] = open[k];
         }
-        grid.sync();
-        if (blockIdx.x == 0 && threadIdx.x == 0) ((volatile uint32_t *)ctl)[cur] = 0u;     // empty for the level after next
         cur ^= 1;
         grid.sync();
     }
@@ -354,7 +355,7 @@ wide_collapse_coop_kernel(int n, const int32_t *__restrict__ child, const float 
 __global__ void wide_collapse_init_kernel(int32_t *qa, uint32_t *ctl, const uint8_t *collapse) {
     // queue A = {root 0} unless the whole tree collapsed into one leaf (then there is nothing to do)
     const bool any = !collapse[0];
-    ctl[0] = any ? 1u : 0u; ctl[1] = 0u; ctl[5] = 0u;
+    ctl[0] = any ? 1u : 0u; ctl[1] = 0u; ctl[2] = 0u; ctl[5] = 0u;
     if (any) qa[0] = 0;
 }
 
@@ -589,8 +590,8 @@ int b2rt_build_impl(b2rt_ctx *ctx) {
                     B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx->collapse_blocks_per_sm, wide_collapse_coop_kernel, 256, 0));
                     if (ctx->collapse_blocks_per_sm < 1) ctx->collapse_blocks_per_sm = 1;
                 }
-                // every block must be resident (grid.sync); more than 4 per SM only adds to the barrier
-                int64_t blocks = (int64_t)ctx->sm_count * std::min(ctx->collapse_blocks_per_sm, 4);
+                // every block must be resident (grid.sync); more than 2 per SM only adds to the barrier
+                int64_t blocks = (int64_t)ctx->sm_count * std::min(ctx->collapse_blocks_per_sm, 2);
                 const int64_t want = ((int64_t)(n - 1) + 255) / 256;
                 if (blocks > want) blocks = want;
                 WideTmp *wtmp = ctx->d_wide_tmp.as<WideTmp>();
