@@ -8,8 +8,11 @@
 //                 per-GPU photon counts, and then the COMPACTION kernel of GPU g writes g's photons to their final
 //                 position in the photon arrays of ALL GPUs: peer stores over NVLink / NVSwitch, compute and exchange in
 //                 one kernel, no send buffer, no staging copy, no collective afterwards.  Rank-order concatenation of
-//                 path-ordered slices = the single-GPU array byte for byte.  Two other exchange modes for A/B and for
-//                 boxes without peer access: B2RT_MGPU_EXCHANGE=nccl (local compaction in place, then one grouped
+//                 path-ordered slices = the single-GPU array byte for byte.  That single-kernel form is B2RT_MGPU_EXCHANGE=fused;
+//                 the DEFAULT is `push`: the compaction writes the local array and a second kernel stores the finished
+//                 slice into the peers with whole 512-byte lines per warp (r04r on 8 x B200: 0.66 against 1.33 ms, the
+//                 compaction's own peer stores being 32-byte pieces at path-dependent offsets).  Two more modes for A/B and
+//                 for boxes without peer access: B2RT_MGPU_EXCHANGE=nccl (local compaction in place, then one grouped
 //                 ncclBroadcast per slice straight between the final arrays; libnccl is dlopen'ed, never linked) and
 //                 =copy (cudaMemcpyPeerAsync per slice).
 //   grids         replicated: every GPU builds the same deterministic grid over the same bytes.  (A partition of the
@@ -81,7 +84,8 @@ struct b2rt_multi {
     std::vector<int> dev;
     std::vector<Worker *> workers;
     bool peer = false;              // every pair of devices has peer access enabled
-    int exchange = EXCH_FUSED;
+    int exchange = EXCH_PUSH;       // r04r, 8 x B200, 400 MB of photons: push 0.66 ms (528 GB/s bus), peer copies 0.63, NCCL 1.11,
+                                    // stores from inside the compaction kernel 1.33 (32-byte pieces at path-dependent offsets)
     Nccl nccl;
     std::vector<ncclComm_t> comms;
     std::string err;
@@ -164,8 +168,12 @@ int sharded_pass(b2rt_multi *m, int64_t first, int64_t n_paths, int mapA, int ma
     for (int i = 0; i < G; ++i) { offA[i + 1] = offA[i] + tot[2 * i]; offB[i + 1] = offB[i] + tot[2 * i + 1]; }
     const int64_t baseA = m->ctx[0]->maps[mapA].n, baseB = m->ctx[0]->maps[mapB].n;
     if (baseA + offA[G] >= (1ll << 32) || baseB + offB[G] >= (1ll << 32)) { m->err = "photon pass: a map would exceed 2^32 photons"; return B2RT_E_ARG; }
-    // every device makes room for the whole pass
-    rc = parallel(m, [&](int i) -> int {
+    // every device makes room for the whole pass (a phase of its own only when some array has to grow)
+    bool grow = false;
+    for (int i = 0; i < G; ++i)
+        grow = grow || m->ctx[i]->maps[mapA].photons.cap < (size_t)(baseA + offA[G]) * sizeof(b2rt_photon) ||
+               m->ctx[i]->maps[mapB].photons.cap < (size_t)(baseB + offB[G]) * sizeof(b2rt_photon);
+    if (grow) rc = parallel(m, [&](int i) -> int {
         b2rt_ctx *c = m->ctx[i];
         int r = b2rt_photons_reserve(c, c->maps[mapA].photons, baseA, baseA + offA[G]);
         if (r) return r;
@@ -224,8 +232,7 @@ int sharded_pass(b2rt_multi *m, int64_t first, int64_t n_paths, int mapA, int ma
                 }
             }
         }
-        B2RT_CUDA(c, cudaStreamSynchronize(c->stream));
-        return B2RT_OK;
+        return b2rt_sync(c);            // stream sync + the traversal-overflow status word
     });
     if (rc) return rc;
     if (mode == EXCH_NCCL && G > 1) {
@@ -272,10 +279,6 @@ int check_state(b2rt_multi *m, const char *who) {
     return B2RT_OK;
 }
 
-int status_all(b2rt_multi *m) {
-    return parallel(m, [&](int i) -> int { return b2rt_sync(m->ctx[i]); });
-}
-
 }  // namespace
 
 extern "C" {
@@ -315,7 +318,7 @@ int b2rt_multi_create(int ngpus, const int *devices, uint64_t seed, b2rt_multi *
         if (!strcmp(v, "nccl")) m->exchange = EXCH_NCCL;
         else if (!strcmp(v, "copy")) m->exchange = EXCH_COPY;
         else if (!strcmp(v, "push")) m->exchange = EXCH_PUSH;
-        else m->exchange = EXCH_FUSED;
+        else if (!strcmp(v, "fused")) m->exchange = EXCH_FUSED;
     }
     if (m->exchange == EXCH_NCCL && ngpus > 1) {
         bool ok = m->nccl.load();
@@ -324,7 +327,7 @@ int b2rt_multi_create(int ngpus, const int *devices, uint64_t seed, b2rt_multi *
             ok = m->nccl.CommInitAll(m->comms.data(), ngpus, m->dev.data()) == 0;
             if (!ok) m->comms.clear();
         }
-        if (!ok) m->exchange = m->peer ? EXCH_FUSED : EXCH_COPY;       // reported by b2rt_multi_info
+        if (!ok) m->exchange = m->peer ? EXCH_PUSH : EXCH_COPY;        // reported by b2rt_multi_info
     }
     for (int i = 0; i < ngpus; ++i) {
         m->workers.push_back(new Worker());
@@ -445,8 +448,7 @@ int b2rt_multi_photons_trace(b2rt_multi *m, int64_t first_path, int64_t n_paths,
                       [&](int i, int64_t lo, int64_t cnt, uint32_t *tot) { return b2rt_photons_trace_begin(m->ctx[i], lo, cnt, max_depth, flags, tot); },
                       [&](int i, int64_t cnt, const PhotonDst &dst) { return b2rt_photons_trace_commit(m->ctx[i], cnt, max_depth, dst); },
                       n_stored);
-    if (rc) return rc;
-    return status_all(m);
+    return rc;
 }
 
 int b2rt_multi_photons_trace_fg(b2rt_multi *m, int64_t first_path, int64_t n_paths, int32_t max_depth, int64_t n_stored[2]) {
@@ -462,7 +464,7 @@ int b2rt_multi_photons_trace_fg(b2rt_multi *m, int64_t first_path, int64_t n_pat
     // nDirectPaths only counts the paths shot while the indirect map was collecting (sharded_pass added n_paths)
     const int64_t counted = std::max<int64_t>(0, std::min<int64_t>(first_path + n_paths, m->ctx[0]->fg_lim_i) - first_path);
     for (b2rt_ctx *c : m->ctx) c->maps[B2RT_MAP_DIRECT].n_paths += counted - n_paths;
-    return status_all(m);
+    return B2RT_OK;
 }
 
 // pbrt's stopping rule over sharded batches: the same loop as b2rt_photons_shoot, every batch cut over the GPUs
