@@ -33,6 +33,7 @@ for job in "$@"; do
     fg540v0)  B2RT_FG_VARIANT=0 timeout 300 python tools/bench_fg.py 1000000 100000 960 540 32 1 > $O/bench_fg_540_v0.jsonl 2> $O/bench_fg_540_v0.err ;;
     fg1080)   timeout 600 python tools/bench_fg.py 8000000 2000000 1920 1080 32 2 > $O/bench_fg_1080.jsonl 2> $O/bench_fg_1080.err; echo "rc=$?" >> $O/bench_fg_1080.err ;;
     photon)   timeout 600 python tools/bench_photon.py > $O/photon.log 2>&1 ;;
+    converged) timeout 900 python tools/converged_parity.py --gpu > $O/converged.jsonl 2> $O/converged.err ;;
     stages)   timeout 600 python tools/bench_stages.py > $O/stages.json 2> $O/stages.err ;;
     buildlist) python tools/bench_stages.py 20 > $O/plain_stages.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $O/launches_stages.csv python tools/bench_stages.py 20 > $O/ncu_stages.log 2>&1 ;;
     stages0)  B2RT_SORT_VARIANT=0 timeout 600 python tools/bench_stages.py > $O/stages_sort_variant0.json 2> $O/stages0.err ;;
