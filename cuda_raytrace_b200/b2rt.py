@@ -12,6 +12,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("B2RT_LIB") or os.path.join(_HERE, "libb2rt.so")     # B2RT_LIB: e.g. the -DB2RT_STATS build
 
 HOST, DEVICE = 0, 1
+SORT_NOALLOC_MAX = 1 << 20          # B2RT_SORT_NOALLOC_MAX (include/b2rt.h)
 MAT_MATTE, MAT_MIRROR, MAT_GLASS = 0, 1, 2
 LIGHT_POINT, LIGHT_DISK_AREA = 0, 1
 
@@ -39,7 +40,7 @@ class B2rtError(RuntimeError):
 SYMBOLS = [
     "b2rt_create", "b2rt_destroy", "b2rt_last_error", "b2rt_device_count", "b2rt_add_mesh", "b2rt_add_sphere",
     "b2rt_add_disk", "b2rt_add_material", "b2rt_add_light", "b2rt_clear_scene", "b2rt_build_accel",
-    "b2rt_accel_info_get", "b2rt_accel_download", "b2rt_trace_closest", "b2rt_trace_any", "b2rt_sort_pairs",
+    "b2rt_accel_info_get", "b2rt_accel_download", "b2rt_trace_closest", "b2rt_trace_any", "b2rt_sort_pairs", "b2rt_sort_pairs_noalloc",
     "b2rt_add_mesh_ex", "b2rt_surface_at", "b2rt_trace_stats", "b2rt_add_spot_light", "b2rt_add_distant_light", "b2rt_sync", "b2rt_timer_start", "b2rt_timer_stop", "b2rt_launch_count", "b2rt_stream", "b2rt_host_alloc", "b2rt_host_free",
 ]
 
@@ -76,6 +77,7 @@ def load():
     lib.b2rt_surface_at.argtypes = [vp, i64, vp, vp, C.c_int]
     lib.b2rt_trace_any.argtypes = [vp, i64, vp, vp, C.c_int]
     lib.b2rt_sort_pairs.argtypes = [vp, i64, vp, vp, C.c_int]
+    lib.b2rt_sort_pairs_noalloc.argtypes = [vp, i64, vp, vp, C.c_int]
     lib.b2rt_sync.argtypes = [vp]
     lib.b2rt_timer_start.argtypes = [vp]
     lib.b2rt_timer_stop.argtypes = [vp, fp]
@@ -275,6 +277,10 @@ class Context:
 
     def sort_pairs_device(self, n, keys_ptr, vals_ptr, key_bits=32):
         self._ck(self.lib.b2rt_sort_pairs(self.h, n, C.c_void_p(keys_ptr), C.c_void_p(vals_ptr), key_bits))
+
+    def sort_pairs_noalloc_device(self, n, keys_ptr, vals_ptr, key_bits=32):
+        """b2rt_sort_pairs_noalloc: scratch in the library's static device array, n <= SORT_NOALLOC_MAX, no cudaMalloc."""
+        self._ck(self.lib.b2rt_sort_pairs_noalloc(self.h, n, C.c_void_p(keys_ptr), C.c_void_p(vals_ptr), key_bits))
 
     # ---- timing -------------------------------------------------------------------------------
     def sync(self):

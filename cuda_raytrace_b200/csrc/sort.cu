@@ -9,6 +9,8 @@
 // their input order, so with value = original index ties break by index.
 #include "b2rt_internal.cuh"
 #include <algorithm>
+#include <mutex>
+#include <utility>
 
 namespace {
 
@@ -460,5 +462,108 @@ int b2rt_sort_pairs_impl(b2rt_ctx *ctx, int64_t n, uint32_t *keys, uint32_t *val
         t = vin; vin = vout; vout = t;
     }
     *result_in_alt = (passes & 1) != 0;
+    return B2RT_OK;
+}
+
+// ---- b2rt_sort_pairs_noalloc: the same sort with its scratch in a static device array ---------------------------------------
+// For callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  No counterpart
+// in the reference.  Same kernels, same schedule choice (ctx->sort_variant) and
+// therefore the same bytes as b2rt_sort_pairs; only where the ping-pong arrays, histograms / look-back states and scan
+// temporaries live differs: g_noalloc_scratch below, a file-scope array that every GPU that loads the library holds until
+// the process exits (9.1 MB).  This path calls no cudaMalloc / cudaFree / DevBuf::reserve.
+//
+// The array's name is only a host-side stand-in in host code, not a device address: the address the kernels receive comes
+// from cudaGetSymbolAddress, taken once per device with that device current (noalloc_scratch_ptr).
+// Every call on a device shares the array: two calls that overlap on the GPU (different streams / contexts of one device)
+// race.  The array keeps the previous call's contents; what must start at zero (the one-sweep digit counts, tickets and
+// look-back states) is cleared by a cudaMemsetAsync in every call, everything else is written before it is read.
+namespace {
+
+constexpr int64_t NOALLOC_MAX_PAIRS = B2RT_SORT_NOALLOC_MAX;                      // 2^20 pairs
+constexpr int64_t NOALLOC_TILES = (NOALLOC_MAX_PAIRS + SORT_TILE - 1) / SORT_TILE;
+constexpr size_t NOALLOC_OS_HEAD = (size_t)OS_MAX_PASSES * RADIX + 64;           // digit counts + tickets (one-sweep)
+// hist region: max(one-sweep: head + passes * tiles * 256 states, three-launch: 256 * tiles block histograms)
+constexpr size_t NOALLOC_HIST_WORDS = NOALLOC_OS_HEAD + (size_t)OS_MAX_PASSES * NOALLOC_TILES * RADIX;
+constexpr size_t NOALLOC_SCAN_WORDS = 256;      // scan of 256 * tiles <= 65536 words: 16 block sums + one level above, padded
+constexpr size_t NOALLOC_OFF_KEYS = 0, NOALLOC_OFF_VALS = (size_t)NOALLOC_MAX_PAIRS,
+                 NOALLOC_OFF_HIST = 2 * (size_t)NOALLOC_MAX_PAIRS, NOALLOC_OFF_SCAN = NOALLOC_OFF_HIST + NOALLOC_HIST_WORDS,
+                 NOALLOC_WORDS = NOALLOC_OFF_SCAN + NOALLOC_SCAN_WORDS;
+static_assert((int64_t)RADIX * NOALLOC_TILES <= (int64_t)SCAN_TILE * 64, "scan temporaries sized for two levels");
+
+static __device__ __align__(256) uint32_t g_noalloc_scratch[NOALLOC_WORDS];
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+std::mutex g_noalloc_mu;
+uint32_t *g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {};      // device address of g_noalloc_scratch on device i, nullptr = not resolved
+
+// once per device, with that device current
+int noalloc_scratch_ptr(b2rt_ctx *ctx, uint32_t **out) {
+    if (ctx->device < 0 || ctx->device >= NOALLOC_MAX_DEVICES) { ctx->err = "sort_pairs_noalloc: device index out of range"; return B2RT_E_ARG; }
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_ptr[ctx->device]) {
+        B2RT_CUDA(ctx, cudaSetDevice(ctx->device));
+        void *p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess || !p) {
+            ctx->err = std::string("sort_pairs_noalloc: cudaGetSymbolAddress(g_noalloc_scratch): ") + cudaGetErrorString(e);
+            return B2RT_E_CUDA;
+        }
+        g_noalloc_ptr[ctx->device] = static_cast<uint32_t *>(p);
+    }
+    *out = g_noalloc_ptr[ctx->device];
+    return B2RT_OK;
+}
+
+}  // namespace
+
+int b2rt_sort_pairs_noalloc(b2rt_ctx *ctx, int64_t n, uint32_t *keys, uint32_t *vals, int key_bits) {
+    if (!ctx) return B2RT_E_ARG;
+    if (n < 0 || key_bits < 1 || key_bits > 32 || (n && (!keys || !vals))) { ctx->err = "sort_pairs_noalloc: bad arguments"; return B2RT_E_ARG; }
+    if (n > NOALLOC_MAX_PAIRS) {
+        ctx->err = "sort_pairs_noalloc: n = " + std::to_string((long long)n) + " pairs exceeds the static scratch (B2RT_SORT_NOALLOC_MAX = " +
+                   std::to_string((long long)NOALLOC_MAX_PAIRS) + " pairs); use b2rt_sort_pairs";
+        return B2RT_E_ARG;
+    }
+    uint32_t *scratch = nullptr;
+    int rc = noalloc_scratch_ptr(ctx, &scratch);       // n = 0: the per-device set-up only
+    if (rc) return rc;
+    if (n <= 1) return B2RT_OK;
+    B2RT_CUDA(ctx, cudaSetDevice(ctx->device));
+    uint32_t *keys_alt = scratch + NOALLOC_OFF_KEYS, *vals_alt = scratch + NOALLOC_OFF_VALS, *hist = scratch + NOALLOC_OFF_HIST,
+             *scan_tmp = scratch + NOALLOC_OFF_SCAN;
+    const int passes = (key_bits + 7) / 8;
+    const int nblocks = (int)((n + SORT_TILE - 1) / SORT_TILE);
+    uint32_t *kin = keys, *vin = vals, *kout = keys_alt, *vout = vals_alt;
+    const bool onesweep = ctx->sort_variant == 2 || (ctx->sort_variant == 1 && n < (1ll << 22));     // as b2rt_sort_pairs_impl
+    if (onesweep) {
+        const size_t words = NOALLOC_OS_HEAD + (size_t)passes * nblocks * RADIX;
+        uint32_t *ghist = hist, *tickets = hist + OS_MAX_PASSES * RADIX, *states = hist + NOALLOC_OS_HEAD;
+        B2RT_CUDA(ctx, cudaMemsetAsync(ghist, 0, words * sizeof(uint32_t), ctx->stream));      // the last call's counts and flags
+        const int hblocks = (int)std::min<int64_t>((n + 4 * SORT_THREADS - 1) / (4 * SORT_THREADS), (int64_t)ctx->sm_count * 8);
+        onesweep_hist_kernel<<<hblocks, SORT_THREADS, 0, ctx->stream>>>(kin, n, passes, ghist);
+        B2RT_LAUNCH_CHECK(ctx);
+        for (int p = 0; p < passes; ++p) {
+            onesweep_scatter_kernel<<<nblocks, SORT_THREADS, 0, ctx->stream>>>(kin, vin, kout, vout, n, 8 * p, ghist + p * RADIX,
+                                                                              states + (size_t)p * nblocks * RADIX, tickets + p);
+            B2RT_LAUNCH_CHECK(ctx);
+            std::swap(kin, kout);
+            std::swap(vin, vout);
+        }
+    } else {
+        for (int p = 0; p < passes; ++p) {
+            radix_hist_kernel<<<nblocks, SORT_THREADS, 0, ctx->stream>>>(kin, n, 8 * p, hist, nblocks);      // writes all 256 * nblocks words
+            B2RT_LAUNCH_CHECK(ctx);
+            rc = scan_rec(ctx, hist, (int64_t)RADIX * nblocks, scan_tmp, nullptr);
+            if (rc) return rc;
+            radix_scatter_kernel<<<nblocks, SORT_THREADS, 0, ctx->stream>>>(kin, vin, kout, vout, n, 8 * p, hist, nblocks);
+            B2RT_LAUNCH_CHECK(ctx);
+            std::swap(kin, kout);
+            std::swap(vin, vout);
+        }
+    }
+    if (passes & 1) {       // an odd number of passes leaves the result in the scratch: copy it home (stream-ordered, no allocation)
+        B2RT_CUDA(ctx, cudaMemcpyAsync(keys, keys_alt, (size_t)n * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+        B2RT_CUDA(ctx, cudaMemcpyAsync(vals, vals_alt, (size_t)n * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+    }
     return B2RT_OK;
 }

@@ -339,6 +339,17 @@ int b2rt_trace_stats(b2rt_ctx *ctx, uint64_t *nodes, uint64_t *prims, int reset)
 /* generic device sort exposed for tests/bench of the hand-written radix sort (K2):
  * stable LSD sort of (key32,value32) pairs on `key_bits` low bits; device pointers only. */
 int b2rt_sort_pairs(b2rt_ctx *ctx, int64_t n, uint32_t *keys, uint32_t *vals, int key_bits);
+/* The same sort for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  No counterpart in the reference.  Allocates nothing: the ping-pong
+ * arrays, histograms / look-back states and scan temporaries live in a static device array inside the library (9.1 MB that
+ * every GPU that loads libb2rt.so holds until the process exits), so n is limited to B2RT_SORT_NOALLOC_MAX pairs -- larger
+ * n returns B2RT_E_ARG with a message.  Same kernels and schedule as b2rt_sort_pairs, hence the same bytes; device pointers
+ * only; asynchronous on the context stream.  All calls on one device share the array: calls that overlap on the GPU
+ * (two contexts / streams of one device) race, and the array keeps the previous call's contents (the call clears what it
+ * needs at zero itself).  n = 0 does the once-per-device set-up only (cudaGetSymbolAddress of the array): call it once
+ * before a graph capture. */
+#define B2RT_SORT_NOALLOC_MAX (1 << 20)
+int b2rt_sort_pairs_noalloc(b2rt_ctx *ctx, int64_t n, uint32_t *keys, uint32_t *vals, int key_bits);
 
 /* ---- pinned host buffers ---------------------------------------------------------------------- */
 /* Page-locked host memory for the B2RT_HOST calls (rays in, hits / images out): with pageable memory the driver
