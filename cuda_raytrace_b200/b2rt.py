@@ -41,7 +41,7 @@ SYMBOLS = [
     "b2rt_create", "b2rt_destroy", "b2rt_last_error", "b2rt_device_count", "b2rt_add_mesh", "b2rt_add_sphere",
     "b2rt_add_disk", "b2rt_add_material", "b2rt_add_light", "b2rt_clear_scene", "b2rt_build_accel",
     "b2rt_accel_info_get", "b2rt_accel_download", "b2rt_trace_closest", "b2rt_trace_any", "b2rt_sort_pairs", "b2rt_sort_pairs_noalloc",
-    "b2rt_add_mesh_ex", "b2rt_surface_at", "b2rt_trace_stats", "b2rt_add_spot_light", "b2rt_add_distant_light", "b2rt_sync", "b2rt_timer_start", "b2rt_timer_stop", "b2rt_launch_count", "b2rt_stream", "b2rt_host_alloc", "b2rt_host_free",
+    "b2rt_add_mesh_ex", "b2rt_surface_at", "b2rt_object_begin", "b2rt_object_end", "b2rt_add_instance", "b2rt_instance_info", "b2rt_trace_stats", "b2rt_add_spot_light", "b2rt_add_distant_light", "b2rt_sync", "b2rt_timer_start", "b2rt_timer_stop", "b2rt_launch_count", "b2rt_stream", "b2rt_host_alloc", "b2rt_host_free",
 ]
 
 _lib = None
@@ -229,6 +229,34 @@ class Context:
 
     def clear_scene(self):
         self._ck(self.lib.b2rt_clear_scene(self.h))
+
+    # ---- objects / instances (two-level BVH) ------------------------------------------------------
+    def object_begin(self):
+        """the add_mesh / add_sphere / add_disk calls until object_end() define an object (ids local to it)"""
+        o = C.c_int32()
+        self.lib.b2rt_object_begin.argtypes = [C.c_void_p, C.POINTER(C.c_int32)]
+        self._ck(self.lib.b2rt_object_begin(self.h, C.byref(o)))
+        return o.value
+
+    def object_end(self):
+        self.lib.b2rt_object_end.argtypes = [C.c_void_p]
+        self._ck(self.lib.b2rt_object_end(self.h))
+
+    def add_instance(self, obj, o2w, w2o=None):
+        """place object `obj` under the instance-to-world transform o2w (3x4 row-major); returns the instance id"""
+        o2w = _f32(o2w, (12,))
+        w2o = None if w2o is None else _f32(w2o, (12,))
+        k = C.c_int32()
+        self.lib.b2rt_add_instance.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.POINTER(C.c_int32)]
+        self._ck(self.lib.b2rt_add_instance(self.h, obj, _ptr(o2w), _ptr(w2o), C.byref(k)))
+        return k.value
+
+    def instance_info(self, k):
+        """(first global primitive id, primitive count, object id) of instance k; after build_accel"""
+        a, b, c = C.c_int32(), C.c_int32(), C.c_int32()
+        self.lib.b2rt_instance_info.argtypes = [C.c_void_p, C.c_int32] + [C.POINTER(C.c_int32)] * 3
+        self._ck(self.lib.b2rt_instance_info(self.h, k, C.byref(a), C.byref(b), C.byref(c)))
+        return a.value, b.value, c.value
 
     # ---- accel --------------------------------------------------------------------------------
     def build_accel(self):

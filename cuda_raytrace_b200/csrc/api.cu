@@ -84,6 +84,101 @@ int b2rt_create(int device, uint64_t seed, b2rt_ctx **out) {
     return B2RT_OK;
 }
 
+// ---- objects (two-level BVH): child contexts that share the parent's device and stream --------------------------------
+static void destroy_object(b2rt_ctx *c) {
+    if (!c) return;
+    cudaEventDestroy(c->evb0); cudaEventDestroy(c->evb1); cudaEventDestroy(c->evb_mid);
+    delete c;
+}
+static b2rt_ctx *new_object(b2rt_ctx *ctx) {
+    b2rt_ctx *c = new b2rt_ctx();
+    c->device = ctx->device; c->seed = ctx->seed; c->sm_count = ctx->sm_count; c->stream = ctx->stream; c->parent = ctx;
+    c->sort_variant = ctx->sort_variant;
+    if (cudaSetDevice(ctx->device) != cudaSuccess || cudaEventCreate(&c->evb0) != cudaSuccess || cudaEventCreate(&c->evb1) != cudaSuccess ||
+        cudaEventCreate(&c->evb_mid) != cudaSuccess || c->d_counters.reserve(256) != cudaSuccess ||
+        cudaMemsetAsync(c->d_counters.p, 0, 256, ctx->stream) != cudaSuccess) {
+        ctx->err = std::string("object_begin: ") + cudaGetErrorString(cudaGetLastError());
+        destroy_object(c);
+        return nullptr;
+    }
+    return c;
+}
+
+// everything b2rt_add_* / b2rt_object_* / b2rt_add_instance staged on the host side of src -> dst (b2rt_multi_resize)
+static void copy_staging(const b2rt_ctx *c0, b2rt_ctx *c) {
+    c->h_verts = c0->h_verts; c->h_idx = c0->h_idx; c->h_tri_prim = c0->h_tri_prim; c->h_analytic = c0->h_analytic;
+    c->h_analytic_prim = c0->h_analytic_prim; c->h_analytic_type = c0->h_analytic_type;
+    c->h_prim_material = c0->h_prim_material; c->h_prim_light = c0->h_prim_light;
+    c->h_materials = c0->h_materials; c->h_lights = c0->h_lights;
+    c->h_vnormal = c0->h_vnormal; c->h_vuv = c0->h_vuv; c->h_tri_flags = c0->h_tri_flags; c->any_attr = c0->any_attr;
+    c->n_prims = c0->n_prims;
+    c->built = false;
+}
+}  // extern "C"
+int b2rt_copy_staged_scene(const b2rt_ctx *src, b2rt_ctx *dst) {
+    copy_staging(src, dst);
+    for (b2rt_ctx *c : dst->objects) destroy_object(c);
+    dst->objects.clear(); dst->cur_object = nullptr;
+    for (const b2rt_ctx *o : src->objects) {
+        b2rt_ctx *c = new_object(dst);
+        if (!c) return B2RT_E_CUDA;
+        copy_staging(o, c);
+        dst->objects.push_back(c);
+    }
+    dst->h_instances = src->h_instances;
+    return B2RT_OK;
+}
+extern "C" {
+
+int b2rt_object_begin(b2rt_ctx *ctx, int32_t *object_id) {
+    if (!ctx) return B2RT_E_ARG;
+    if (ctx->parent || ctx->cur_object) { ctx->err = "object_begin: objects do not nest (pbrt: core/api.cpp:1107-1110)"; return B2RT_E_STATE; }
+    b2rt_ctx *c = new_object(ctx);
+    if (!c) return B2RT_E_CUDA;
+    if (object_id) *object_id = (int32_t)ctx->objects.size();
+    ctx->objects.push_back(c);
+    ctx->cur_object = c;
+    return B2RT_OK;
+}
+
+int b2rt_object_end(b2rt_ctx *ctx) {
+    if (!ctx) return B2RT_E_ARG;
+    if (!ctx->cur_object) { ctx->err = "object_end: no object is open"; return B2RT_E_STATE; }
+    ctx->cur_object = nullptr;
+    return B2RT_OK;
+}
+
+int b2rt_add_instance(b2rt_ctx *ctx, int32_t object_id, const float o2w[12], const float *w2o, int32_t *instance_id) {
+    if (!ctx) return B2RT_E_ARG;
+    if (ctx->cur_object) { ctx->err = "add_instance: not inside an object definition (pbrt: core/api.cpp:1143-1146)"; return B2RT_E_STATE; }
+    if (object_id < 0 || object_id >= (int32_t)ctx->objects.size() || !o2w) { ctx->err = "add_instance: bad arguments"; return B2RT_E_ARG; }
+    if (ctx->objects[object_id]->n_prims == 0) { ctx->err = "add_instance: the object has no primitives"; return B2RT_E_ARG; }
+    if ((int64_t)ctx->n_prims + 1 >= (1ll << 28)) { ctx->err = "add_instance: more than 2^28 items"; return B2RT_E_ARG; }
+    b2rt_ctx::HostInstance H;
+    memcpy(H.o2w, o2w, sizeof(H.o2w));
+    if (w2o) memcpy(H.w2o, w2o, sizeof(H.w2o));
+    else if (invert34(o2w, H.w2o)) { ctx->err = "add_instance: singular transform"; return B2RT_E_ARG; }
+    H.object = object_id;
+    H.item = ctx->n_prims++;
+    ctx->h_prim_material.push_back(-1);
+    ctx->h_prim_light.push_back(-1);
+    if (instance_id) *instance_id = (int32_t)ctx->h_instances.size();
+    ctx->h_instances.push_back(H);
+    ctx->built = false;
+    return B2RT_OK;
+}
+
+int b2rt_instance_info(b2rt_ctx *ctx, int32_t instance_id, int32_t *first_prim, int32_t *n_prims, int32_t *object_id) {
+    if (!ctx) return B2RT_E_ARG;
+    if (!ctx->built) { ctx->err = "instance_info: no acceleration structure built"; return B2RT_E_STATE; }
+    if (instance_id < 0 || instance_id >= (int32_t)ctx->h_instances.size()) { ctx->err = "instance_info: bad instance id"; return B2RT_E_ARG; }
+    const int o = ctx->h_instances[instance_id].object;
+    if (first_prim) *first_prim = ctx->h_instance_base[instance_id];
+    if (n_prims) *n_prims = ctx->objects[o]->n_prims;
+    if (object_id) *object_id = o;
+    return B2RT_OK;
+}
+
 void b2rt_destroy(b2rt_ctx *ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
@@ -95,6 +190,7 @@ void b2rt_destroy(b2rt_ctx *ctx) {
     cudaEventDestroy(ctx->ev_in); cudaEventDestroy(ctx->ev_k); cudaEventDestroy(ctx->ev_out);
     cudaStreamDestroy(ctx->stream_in); cudaStreamDestroy(ctx->stream_out);
     cudaStreamDestroy(ctx->stream);
+    for (b2rt_ctx *c : ctx->objects) destroy_object(c);
     delete ctx;      // ~DevBuf frees every device buffer of the context and of its photon maps
 }
 
@@ -107,6 +203,8 @@ int b2rt_clear_scene(b2rt_ctx *ctx) {
     ctx->h_prim_light.clear(); ctx->h_materials.clear(); ctx->h_lights.clear();
     ctx->h_vnormal.clear(); ctx->h_vuv.clear(); ctx->h_tri_flags.clear(); ctx->any_attr = false;
     ctx->n_prims = 0; ctx->built = false;
+    for (b2rt_ctx *c : ctx->objects) destroy_object(c);
+    ctx->objects.clear(); ctx->cur_object = nullptr; ctx->h_instances.clear(); ctx->h_instance_base.clear(); ctx->n_virtual_prims = 0;
     return B2RT_OK;
 }
 
@@ -114,6 +212,12 @@ int b2rt_add_mesh_ex(b2rt_ctx *ctx, int32_t nverts, const float *P, int32_t ntri
                      const float *N, const float *uv, int32_t material_id, int32_t arealight_id, int32_t flags,
                      int32_t *first_prim) {
     if (!ctx) return B2RT_E_ARG;
+    if (ctx->cur_object) {              // inside b2rt_object_begin / _end: the mesh belongs to the object, ids are local to it
+        if (arealight_id >= 0) { ctx->err = "add_mesh: area lights are not supported inside objects (pbrt: core/api.cpp:1009-1011)"; return B2RT_E_ARG; }
+        int rc = b2rt_add_mesh_ex(ctx->cur_object, nverts, P, ntris, idx, N, uv, material_id, -1, flags, first_prim);
+        if (rc) ctx->err = ctx->cur_object->err;
+        return rc;
+    }
     if (nverts < 0 || ntris < 0 || (nverts && !P) || (ntris && !idx)) { ctx->err = "add_mesh: bad sizes/pointers"; return B2RT_E_ARG; }
     if ((int64_t)ctx->n_prims + ntris >= (1ll << 28)) { ctx->err = "add_mesh: more than 2^28 primitives"; return B2RT_E_ARG; }
     if (flags & ~B2RT_MESH_REVERSE) { ctx->err = "add_mesh: unknown flag bits"; return B2RT_E_ARG; }
@@ -154,6 +258,12 @@ int b2rt_add_mesh(b2rt_ctx *ctx, int32_t nverts, const float *P, int32_t ntris, 
 static int add_analytic(b2rt_ctx *ctx, int type, const float o2w[12], const float *w2o, float radius,
                         float height, float inner, int32_t material_id, int32_t arealight_id, int32_t *prim) {
     if (!ctx) return B2RT_E_ARG;
+    if (ctx->cur_object) {
+        if (arealight_id >= 0) { ctx->err = "add_sphere/disk: area lights are not supported inside objects (pbrt: core/api.cpp:1009-1011)"; return B2RT_E_ARG; }
+        int rc = add_analytic(ctx->cur_object, type, o2w, w2o, radius, height, inner, material_id, -1, prim);
+        if (rc) ctx->err = ctx->cur_object->err;
+        return rc;
+    }
     if (!o2w || !(radius > 0.f)) { ctx->err = "add_sphere/disk: bad arguments"; return B2RT_E_ARG; }
     AnalyticPrim a;
     memcpy(a.o2w, o2w, sizeof(a.o2w));

@@ -124,30 +124,13 @@ __host__ __device__ __forceinline__ f3 uniform_sample_sphere(float u1, float u2)
     return mk3(r * c, r * s, z);
 }
 
-// ---- device view of the scene -------------------------------------------------------------------------------------
-struct DScene {
-    const WideNode *nodes;
-    const PrimRec *recs;            // leaf-slot order
-    const AnalyticPrim *analytic;
-    const int32_t *prim_material;   // per global prim id, -1 = none (default grey matte 0.5, cudamaterial.cpp:20)
-    const int32_t *prim_light;      // per global prim id, -1 = not an area light
-    const Material *materials;
-    const Light *lights;
-    const float *light_cdf;         // n_lights+1 entries, cdf[0]=0, cdf[n]=1; then n_lights pdfs
-    int32_t n_lights, n_materials;
-    // per-vertex shading attributes (K6).  tri_flags == NULL: no mesh of the scene has any (the common case; make_surface
-    // then never touches the rest).  prim_kind[prim] = triangle index; tri_flags[tri]: bit 0 normals, bit 1 uv, bit 2 flip.
-    const uint8_t *tri_flags;
-    const int32_t *prim_kind, *tri_idx;
-    const float *verts, *vnormal, *vuv;
-};
-
 struct RayD {           // per-ray constants
     float ox, oy, oz, dx, dy, dz, tmin;
     double ddx, ddy, ddz;   // direction widened once (pbrt's Cross works in double)
 };
 
-struct HitD { float t; int32_t prim; float b1, b2; int32_t slot; };
+// slot: leaf-record slot of the hit primitive (in the object's records for an instanced hit); inst: instance index or -1
+struct HitD { float t; int32_t prim; float b1, b2; int32_t slot; int32_t inst; };
 
 // returns true and writes t,b1,b2 if pbrt's Triangle::Intersect (shapes/trianglemesh.cpp:146-179) would accept
 // on [tmin, tmax]
@@ -269,6 +252,114 @@ __device__ __forceinline__ bool tri_test_nobranch(const RayD &r, const float4 &A
     return ok;
 }
 
+// ---- object instances: the second level of the two-level BVH ---------------------------------------------------------
+// Replaces the OptiX Transform node the reference hangs every ObjectInstance under (cuda_render/cudarender.cpp:88-103) and
+// follows pbrt's TransformedPrimitive::Intersect (core/primitive.cpp:95-103): the ray is taken into the instance's space
+// by Transform::operator()(Ray) -- origin as a point, direction as a vector, NOT renormalised, so t is the same parameter
+// in both spaces and [tmin, tmax] carry over -- and the object's own tree is searched there with the very same primitive
+// arithmetic.  t therefore equals what pbrt computes for the instanced shape bit for bit.
+__device__ __forceinline__ const InstanceRec *instance_of(const float4 &A) {
+    return reinterpret_cast<const InstanceRec *>(((uint64_t)__float_as_uint(A.y) << 32) | (uint64_t)__float_as_uint(A.x));
+}
+__device__ __forceinline__ void instance_ray(const InstanceRec *__restrict__ I, float ox, float oy, float oz, float dx, float dy,
+                                             float dz, float tmin, RayD &r) {
+    float m[12];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const float4 row = __ldg(reinterpret_cast<const float4 *>(I->w2o) + k);
+        m[4 * k] = row.x; m[4 * k + 1] = row.y; m[4 * k + 2] = row.z; m[4 * k + 3] = row.w;
+    }
+    xf_point(m, ox, oy, oz, r.ox, r.oy, r.oz);
+    xf_vec(m, dx, dy, dz, r.dx, r.dy, r.dz);
+    r.tmin = tmin;
+    r.ddx = r.dx; r.ddy = r.dy; r.ddz = r.dz;
+}
+
+// Closest (or any) accepted primitive of one instance on [r.tmin, tmax].  Plain if-if loop with a private stack: it is
+// entered from divergent code (one lane of a warp may be here while its neighbours test triangles), so it does not
+// cooperate across the warp.  Same conservative node test, same winner rule (min t, then min id) as the top level; the id
+// returned is local to the object.
+template <bool ANY>
+static __device__ __noinline__ bool instance_test(const RayD &rw, const InstanceRec *__restrict__ I, float tmax, float &t_out,
+                                                  float &b1_out, float &b2_out, int &prim_out, int &slot_out, bool &overflow) {
+    RayD r;
+    instance_ray(I, rw.ox, rw.oy, rw.oz, rw.dx, rw.dy, rw.dz, rw.tmin, r);
+    const WideNode *__restrict__ nodes = I->nodes;
+    const PrimRec *__restrict__ recs = I->recs;
+    const AnalyticPrim *__restrict__ analytic = I->analytic;
+    const float idx = slab_rcp(r.dx), idy = slab_rcp(r.dy), idz = slab_rcp(r.dz);
+    float best_t = tmax, best_b1 = 0.f, best_b2 = 0.f;
+    int best_prim = 0x7fffffff, best_slot = -1;
+    bool found = false;
+    int32_t stack[B2RT_STACK_SIZE];
+    int sp = 0;
+    int32_t cur = 0;
+    for (;;) {
+        if (cur >= 0) {
+            const float4 *np = reinterpret_cast<const float4 *>(nodes + cur);
+            const float4 lox = __ldg(np), hix = __ldg(np + 1), loy = __ldg(np + 2), hiy = __ldg(np + 3), loz = __ldg(np + 4),
+                         hiz = __ldg(np + 5);
+            const int4 ch = __ldg(reinterpret_cast<const int4 *>(np + 6));
+            float tn[4]; int32_t cr[4];
+            const float lx[4] = {lox.x, lox.y, lox.z, lox.w}, hx[4] = {hix.x, hix.y, hix.z, hix.w};
+            const float ly[4] = {loy.x, loy.y, loy.z, loy.w}, hy[4] = {hiy.x, hiy.y, hiy.z, hiy.w};
+            const float lz[4] = {loz.x, loz.y, loz.z, loz.w}, hz[4] = {hiz.x, hiz.y, hiz.z, hiz.w};
+            cr[0] = ch.x; cr[1] = ch.y; cr[2] = ch.z; cr[3] = ch.w;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                float t0x = (lx[k] - r.ox) * idx, t1x = (hx[k] - r.ox) * idx;
+                float t0y = (ly[k] - r.oy) * idy, t1y = (hy[k] - r.oy) * idy;
+                float t0z = (lz[k] - r.oz) * idz, t1z = (hz[k] - r.oz) * idz;
+                float tnear = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), r.tmin));
+                float tfar = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), best_t));
+                float tn_p = __fmaf_rn(fabsf(tnear), -2e-6f, tnear);
+                float tf_p = __fmaf_rn(fabsf(tfar), 2e-6f, tfar);
+                bool h = (tn_p <= tf_p) && (cr[k] != B2RT_CHILD_EMPTY);
+                tn[k] = h ? tnear : INFINITY;
+            }
+#define B2RT_CSWAP(a, b)                                                                  \
+    if (tn[b] < tn[a]) { float tt = tn[a]; tn[a] = tn[b]; tn[b] = tt; int32_t cc = cr[a]; cr[a] = cr[b]; cr[b] = cc; }
+            B2RT_CSWAP(0, 1) B2RT_CSWAP(2, 3) B2RT_CSWAP(0, 2) B2RT_CSWAP(1, 3) B2RT_CSWAP(1, 2)
+#undef B2RT_CSWAP
+            const int nhit = (tn[0] < INFINITY) + (tn[1] < INFINITY) + (tn[2] < INFINITY) + (tn[3] < INFINITY);
+            if (nhit == 0) {
+                if (sp == 0) break;
+                cur = stack[--sp];
+                continue;
+            }
+            if (sp + 3 > B2RT_STACK_SIZE) { overflow = true; break; }
+            if (nhit > 3) stack[sp++] = cr[3];
+            if (nhit > 2) stack[sp++] = cr[2];
+            if (nhit > 1) stack[sp++] = cr[1];
+            cur = cr[0];
+        } else {
+            const uint32_t ref = (uint32_t)cur & 0x7fffffffu;
+            const uint32_t first = ref >> 3, cnt = (ref & 7u) + 1u;
+            for (uint32_t s = first; s < first + cnt; ++s) {
+                const float4 *pp = reinterpret_cast<const float4 *>(recs + s);
+                const float4 A = __ldg(pp), B = __ldg(pp + 1), C = __ldg(pp + 2);
+                const int prim = __float_as_int(A.w);
+                const int type = __float_as_int(B.w);
+                float t, b1 = 0.f, b2 = 0.f;
+                bool h;
+                if (type == B2RT_PRIM_TRI) h = tri_test_nobranch(r, A, B, C, best_t, t, b1, b2);
+                else if (type == B2RT_PRIM_SPHERE) h = sphere_test(r, analytic[__float_as_int(C.w)], best_t, t);
+                else h = disk_test(r, analytic[__float_as_int(C.w)], best_t, t);
+                if (h) {
+                    if (ANY) { found = true; break; }
+                    if (t < best_t || prim < best_prim) {
+                        best_t = t; best_prim = prim; best_b1 = b1; best_b2 = b2; best_slot = (int)s; found = true;
+                    }
+                }
+            }
+            if ((ANY && found) || sp == 0) break;
+            cur = stack[--sp];
+        }
+    }
+    t_out = best_t; b1_out = best_b1; b2_out = best_b2; prim_out = best_prim; slot_out = best_slot;
+    return found;
+}
+
 // Wide-BVH traversal of one ray, inlined into the photon and camera kernels.  Winner among all accepted primitives is
 // (min t, then min primitive id): order-independent, so the answer does not depend on tree shape or visiting order.
 // Node boxes are tested conservatively (padded slab test) so the tree never hides a primitive that the exhaustive loop
@@ -289,7 +380,7 @@ __device__ __forceinline__ bool traverse(const WideNode *__restrict__ nodes, con
     constexpr int32_t NONE = B2RT_CHILD_EMPTY;      // "nothing": never a valid node index or leaf reference
 
     float best_t = tmax;
-    int best_prim = 0x7fffffff, best_slot = -1;
+    int best_prim = 0x7fffffff, best_slot = -1, best_inst = -1;
     float best_b1 = 0.f, best_b2 = 0.f;
     bool found = false;
 
@@ -361,13 +452,20 @@ __device__ __forceinline__ bool traverse(const WideNode *__restrict__ nodes, con
                 int type = __float_as_int(B.w);
                 float t, b1 = 0.f, b2 = 0.f;
                 bool h;
+                int hslot = (int)s, hinst = -1;
                 if (type == B2RT_PRIM_TRI) h = tri_test_nobranch(r, A, B, C, best_t, t, b1, b2);
                 else if (type == B2RT_PRIM_SPHERE) h = sphere_test(r, analytic[__float_as_int(C.w)], best_t, t);
-                else h = disk_test(r, analytic[__float_as_int(C.w)], best_t, t);
+                else if (type == B2RT_PRIM_DISK) h = disk_test(r, analytic[__float_as_int(C.w)], best_t, t);
+                else {                                      // object instance: search its tree in its own space
+                    int lprim;
+                    h = instance_test<ANY>(r, instance_of(A), best_t, t, b1, b2, lprim, hslot, overflow);
+                    prim += lprim;                          // A.w of an instance record = its first global id
+                    hinst = __float_as_int(C.w);
+                }
                 if (h) {
                     if (ANY) { found = true; break; }
                     if (t < best_t || prim < best_prim) {   // t <= best_t is guaranteed by the test
-                        best_t = t; best_prim = prim; best_b1 = b1; best_b2 = b2; best_slot = (int)s; found = true;
+                        best_t = t; best_prim = prim; best_b1 = b1; best_b2 = b2; best_slot = hslot; best_inst = hinst; found = true;
                     }
                 }
             }
@@ -381,6 +479,6 @@ __device__ __forceinline__ bool traverse(const WideNode *__restrict__ nodes, con
     }
     hit.t = found ? best_t : INFINITY;
     hit.prim = found ? best_prim : -1;
-    hit.b1 = best_b1; hit.b2 = best_b2; hit.slot = best_slot;
+    hit.b1 = best_b1; hit.b2 = best_b2; hit.slot = best_slot; hit.inst = best_inst;
     return found;
 }

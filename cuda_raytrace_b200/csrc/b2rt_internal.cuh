@@ -50,6 +50,7 @@ static_assert(sizeof(WideNode) == 128, "wide node must be one cache line");
 #define B2RT_PRIM_TRI 0
 #define B2RT_PRIM_SPHERE 1
 #define B2RT_PRIM_DISK 2
+#define B2RT_PRIM_INSTANCE 3     // top-level tree only: one record per object instance (two-level BVH), see InstanceRec
 
 // Leaf-ordered primitive record, 48 B = 3 x float4:
 //   a = {p1.xyz, bits(prim id)}   b = {e1.xyz, bits(type)}   c = {e2.xyz, bits(analytic index)}
@@ -63,6 +64,24 @@ struct AnalyticPrim {
     float radius, height, inner, pad;
 };
 
+// One instance of an object (pbrt ObjectInstance -> TransformedPrimitive, core/primitive.cpp:95-120; the reference's OptiX
+// Transform node over a Group, cuda_render/cudarender.cpp:88-103).  The object's own BVH (built once, in the object's space)
+// is shared by all its instances; nothing is flattened.  An instance occupies the global primitive ids
+// [prim_base, prim_base + n_prims): prim_base + the primitive's id inside the object.
+// Its top-level leaf record: a = {lo32(ptr), hi32(ptr), 0, bits(prim_base)}, b.w = B2RT_PRIM_INSTANCE, c.w = instance index;
+// ptr = device address of this record, so the traversal kernels need no extra argument.
+struct DScene;
+struct __align__(16) InstanceRec {
+    float o2w[12], w2o[12];          // instance-to-world and its inverse, row-major 3x4, exactly as pbrt holds them
+    const WideNode *nodes;           // the object's tree / records / analytic table (device pointers)
+    const PrimRec *recs;
+    const AnalyticPrim *analytic;
+    const DScene *object;            // the object's scene view for the shade stage (attributes, per-prim materials)
+    int32_t prim_base, n_prims, object_id, pad;
+    float box[6];                    // the object's AABB in its own space (lo.xyz, hi.xyz)
+};
+static_assert(sizeof(InstanceRec) % 16 == 0, "instance_ray reads the transform rows as float4");
+
 struct Material { int32_t type; float kd[3]; float kt[3]; float ior; };
 // analytic/area/n are derived at build time for disk area lights: analytic = index into the analytic table,
 // area = Disk::Area() (shapes/disk.cpp:132-135), n = Normalize(ObjectToWorld(Normal(0,0,1))) (disk.cpp:154)
@@ -70,6 +89,28 @@ struct Material { int32_t type; float kd[3]; float kt[3]; float ior; };
 // TO the light, wc / wr = bounding sphere of the scene box (BBox::BoundingSphere), filled in when the tables are uploaded.
 struct Light { int32_t type; float p[3]; float rgb[3]; int32_t prim; int32_t nsamples; int32_t analytic; float area; float n[3];
                float l2w[9], w2l[9]; float cos_total, cos_falloff; float wc[3], wr; };
+
+// ---- device view of the scene -------------------------------------------------------------------------------------
+struct DScene {
+    const WideNode *nodes;
+    const PrimRec *recs;            // leaf-slot order
+    const AnalyticPrim *analytic;
+    const int32_t *prim_material;   // per global prim id, -1 = none (default grey matte 0.5, cudamaterial.cpp:20)
+    const int32_t *prim_light;      // per global prim id, -1 = not an area light
+    const Material *materials;
+    const Light *lights;
+    const float *light_cdf;         // n_lights+1 entries, cdf[0]=0, cdf[n]=1; then n_lights pdfs
+    int32_t n_lights, n_materials;
+    // per-vertex shading attributes (K6).  tri_flags == NULL: no mesh of the scene has any (the common case; make_surface
+    // then never touches the rest).  prim_kind[prim] = triangle index; tri_flags[tri]: bit 0 normals, bit 1 uv, bit 2 flip.
+    const uint8_t *tri_flags;
+    const int32_t *prim_kind, *tri_idx;
+    const float *verts, *vnormal, *vuv;
+    // object instances (two-level BVH): NULL / 0 without instances.  A hit with HitD::inst >= 0 lies in instances[inst];
+    // its attributes come from instances[inst].object (the object's own scene view), transformed to world space.
+    const InstanceRec *instances;
+    int32_t n_instances;
+};
 
 // one photon map (caustic or indirect): photons in path order as traced, then the hash-grid built over them
 struct PhotonMap {
@@ -139,7 +180,17 @@ struct b2rt_ctx {
     std::vector<int32_t> h_prim_material, h_prim_light;
     std::vector<Material> h_materials;
     std::vector<Light> h_lights;
-    int32_t n_prims = 0;
+    int32_t n_prims = 0;             // items of THIS context's tree: primitives and (top level only) one item per instance
+    // objects and instances (two-level BVH).  An object is a child context (own staging, own tree, same stream) that the
+    // b2rt_add_* calls between b2rt_object_begin / _end fill; instances live in the parent only.
+    std::vector<b2rt_ctx *> objects;
+    b2rt_ctx *cur_object = nullptr;  // != nullptr between b2rt_object_begin and b2rt_object_end
+    b2rt_ctx *parent = nullptr;      // set in an object's context
+    struct HostInstance { float o2w[12], w2o[12]; int32_t object; int32_t item; };
+    std::vector<HostInstance> h_instances;
+    std::vector<int32_t> h_instance_base;   // global id of each instance's first primitive (assigned by the build)
+    int64_t n_virtual_prims = 0;     // n_prims + the primitives of all instances = the size of the global id space
+    DevBuf d_instances, d_objects;   // InstanceRec[n_instances], DScene[n_objects]
 
     // device scene + accel
     bool built = false;
@@ -206,6 +257,7 @@ struct PhotonDst { b2rt_photon *a[B2RT_MAX_GPUS]; b2rt_photon *b[B2RT_MAX_GPUS];
 int b2rt_sort_pairs_impl(b2rt_ctx *ctx, int64_t n, uint32_t *keys, uint32_t *vals, uint32_t *keys_alt,
                          uint32_t *vals_alt, int key_bits, bool *result_in_alt);
 int b2rt_build_impl(b2rt_ctx *ctx);
+int b2rt_copy_staged_scene(const b2rt_ctx *src, b2rt_ctx *dst);
 int b2rt_trace_impl(b2rt_ctx *ctx, int64_t n, const b2rt_ray *d_rays, b2rt_hit *d_hits, uint8_t *d_occ,
                     bool any_hit);
 struct DScene;

@@ -29,7 +29,13 @@ struct Surface {
 // the mesh's object-to-world normal transform; pbrt applies it after the interpolation, the same value up to rounding
 // and the same bits for the identity).  flags: bit 0 the mesh has normals, bit 1 it has uv, bit 2 ReverseOrientation ^
 // TransformSwapsHandedness (core/diffgeom.cpp:52-54).  dndu / dndv only feed texture filtering and are not formed.
-static __device__ __noinline__ void tri_surface_attr(const DScene &sc, const HitD &h, int tri, int flags, Surface &s) {
+// I != NULL: the triangle belongs to an object instance.  pbrt's TransformedPrimitive::Intersect takes dg.nn (as a normal),
+// dpdu and dpdv (as vectors) to world space BEFORE the shading geometry is formed, and GetShadingGeometry receives the whole
+// object-to-world chain for the interpolated normal (core/primitive.cpp:104-117, shapes/trianglemesh.cpp:338): the
+// Gram-Schmidt step below then runs in world space, which is not the same as transforming its object-space result when the
+// instance transform is not rigid.
+static __device__ __noinline__ void tri_surface_attr(const DScene &sc, const HitD &h, int tri, int flags, Surface &s,
+                                                     const InstanceRec *I = nullptr) {
     const int i0 = sc.tri_idx[3 * tri], i1 = sc.tri_idx[3 * tri + 1], i2 = sc.tri_idx[3 * tri + 2];
     const f3 p1 = mk3(sc.verts[3 * i0], sc.verts[3 * i0 + 1], sc.verts[3 * i0 + 2]);
     const f3 p2 = mk3(sc.verts[3 * i1], sc.verts[3 * i1 + 1], sc.verts[3 * i1 + 2]);
@@ -57,6 +63,11 @@ static __device__ __noinline__ void tri_surface_attr(const DScene &sc, const Hit
     s.v = b0 * uv[0][1] + h.b1 * uv[1][1] + h.b2 * uv[2][1];
     s.ng = normalize3(cross3(dpdu, dpdv));
     if (flags & 4) s.ng = s.ng * -1.f;
+    if (I) {
+        s.ng = normalize3(xf_normal(I->w2o, s.ng));
+        xf_vec(I->o2w, dpdu.x, dpdu.y, dpdu.z, dpdu.x, dpdu.y, dpdu.z);
+        xf_vec(I->o2w, dpdv.x, dpdv.y, dpdv.z, dpdv.x, dpdv.y, dpdv.z);
+    }
     f3 sdpdu = dpdu;                        // dgShading.dpdu
     s.n = s.ng;
     if (flags & 1) {
@@ -75,7 +86,9 @@ static __device__ __noinline__ void tri_surface_attr(const DScene &sc, const Hit
         const f3 n0 = mk3(sc.vnormal[3 * i0], sc.vnormal[3 * i0 + 1], sc.vnormal[3 * i0 + 2]);
         const f3 n1 = mk3(sc.vnormal[3 * i1], sc.vnormal[3 * i1 + 1], sc.vnormal[3 * i1 + 2]);
         const f3 n2 = mk3(sc.vnormal[3 * i2], sc.vnormal[3 * i2 + 1], sc.vnormal[3 * i2 + 2]);
-        const f3 ns = normalize3(n0 * b[0] + n1 * b[1] + n2 * b[2]);
+        f3 nsum = n0 * b[0] + n1 * b[1] + n2 * b[2];
+        if (I) nsum = xf_normal(I->w2o, nsum);
+        const f3 ns = normalize3(nsum);
         f3 ss = normalize3(dpdu);
         f3 ts = cross3(ss, ns);
         if (ts.x * ts.x + ts.y * ts.y + ts.z * ts.z > 0.f) {
@@ -92,10 +105,18 @@ static __device__ __noinline__ void tri_surface_attr(const DScene &sc, const Hit
     s.tn = cross3(s.n, s.sn);
 }
 
-// K6: from (slot, t) and the ray.  Triangle without attributes: n = Normalize(Cross(e2, e1)) which is what pbrt gets for
-// meshes with default/degenerate uv (shapes/trianglemesh.cpp:181-201: CoordinateSystem(Normalize(Cross(e2,e1)),..));
+// K6: from (slot, t) and the ray.  Triangle without attributes: pbrt's default uv (0,0), (1,0), (1,1) have determinant 1, so
+// Triangle::Intersect forms dpdu = p2 - p1 and dpdv = p3 - p2 (shapes/trianglemesh.cpp:181-201, up to the rounding of its
+// dp1 / dp2 sums) and dg.nn = Normalize(Cross(dpdu, dpdv)) = the direction of Cross(e1, e2): the winding decides the side,
+// which matters for glass meshes (entering / leaving, core/reflection.cpp:147-151).  Here from the record's edges: n =
+// Normalize(Cross(e1, e2)), sn = Normalize(e1).  (Until round 2 this was Cross(e2, e1) + CoordinateSystem -- pbrt's
+// degenerate-uv fallback, the opposite side; found by the instancing tests against pbrt's own attributes.)
 // rayEpsilon = 1e-3*t (trianglemesh.cpp:224).  Sphere / disk: 5e-4*t (sphere.cpp:154, disk.cpp:100).
-__device__ __forceinline__ Surface make_surface(const DScene &sc, const HitD &h, f3 o, f3 d) {
+// I != NULL (h.prim then local to the object, sc = the object's scene view, o / d the ray in the instance's space): the
+// attributes are formed in the object's space exactly as for a top-level primitive and then taken to world space the way
+// TransformedPrimitive::Intersect does -- p as a point, the normal by the inverse transpose and renormalised, dpdu as a
+// vector (core/primitive.cpp:104-117); rayEpsilon stays the shape's.
+__device__ __forceinline__ Surface make_surface_impl(const DScene &sc, const HitD &h, f3 o, f3 d, const InstanceRec *I) {
     Surface s;
     s.p = o + d * h.t;
     s.u = 0.f; s.v = 0.f;
@@ -103,29 +124,56 @@ __device__ __forceinline__ Surface make_surface(const DScene &sc, const HitD &h,
     float4 B = __ldg(pp + 1), C = __ldg(pp + 2);
     int type = __float_as_int(B.w);
     s.material = sc.prim_material ? sc.prim_material[h.prim] : -1;
-    s.light = sc.prim_light ? sc.prim_light[h.prim] : -1;
+    s.light = (!I && sc.prim_light) ? sc.prim_light[h.prim] : -1;     // pbrt: no area lights inside instances (core/api.cpp:1009-1011)
+    if (I) xf_point(I->o2w, s.p.x, s.p.y, s.p.z, s.p.x, s.p.y, s.p.z);
     if (type == B2RT_PRIM_TRI) {
         s.ray_eps = 1e-3f * h.t;
         if (sc.tri_flags) {                                  // some mesh of the scene carries attributes
             const int tri = sc.prim_kind[h.prim];
             const int fl = sc.tri_flags[tri];
-            if (fl) { tri_surface_attr(sc, h, tri, fl, s); return s; }
+            if (fl) { tri_surface_attr(sc, h, tri, fl, s, I); return s; }
         }
-        s.n = normalize3(cross3(mk3(C.x, C.y, C.z), mk3(B.x, B.y, B.z)));
+        s.n = normalize3(cross3(mk3(B.x, B.y, B.z), mk3(C.x, C.y, C.z)));
+        s.sn = mk3(B.x, B.y, B.z);
     } else {
         const AnalyticPrim &A = sc.analytic[__float_as_int(C.w)];
         f3 no;
-        if (type == B2RT_PRIM_SPHERE) xf_point(A.w2o, s.p.x, s.p.y, s.p.z, no.x, no.y, no.z);
-        else no = mk3(0.f, 0.f, 1.f);
+        if (type == B2RT_PRIM_SPHERE) {
+            const f3 po = I ? o + d * h.t : s.p;             // the hit point in the space the sphere's transform starts from
+            xf_point(A.w2o, po.x, po.y, po.z, no.x, no.y, no.z);
+        } else no = mk3(0.f, 0.f, 1.f);
         s.n = normalize3(xf_normal(A.w2o, no));
         s.ray_eps = 5e-4f * h.t;
+        f3 dpdv;
+        coordinate_system(s.n, s.sn, dpdv);
+    }
+    if (I) {
+        s.n = normalize3(xf_normal(I->w2o, s.n));
+        xf_vec(I->o2w, s.sn.x, s.sn.y, s.sn.z, s.sn.x, s.sn.y, s.sn.z);
     }
     s.ng = s.n;
-    f3 dpdv;
-    coordinate_system(s.n, s.sn, dpdv);
     s.sn = normalize3(s.sn);
     s.tn = cross3(s.n, s.sn);
     return s;
+}
+
+// hit inside an object instance: the ray goes into the instance's space as the traversal took it there (instance_ray)
+static __device__ __noinline__ Surface make_surface_instanced(const DScene &sc, const HitD &h, f3 o, f3 d) {
+    const InstanceRec *I = sc.instances + h.inst;
+    RayD r;
+    instance_ray(I, o.x, o.y, o.z, d.x, d.y, d.z, 0.f, r);
+    HitD lh = h;
+    lh.prim = h.prim - I->prim_base;
+    lh.inst = -1;
+    const DScene *os = I->object;
+    DScene osc = *os;
+    osc.materials = sc.materials; osc.n_materials = sc.n_materials;
+    return make_surface_impl(osc, lh, mk3(r.ox, r.oy, r.oz), mk3(r.dx, r.dy, r.dz), I);
+}
+
+__device__ __forceinline__ Surface make_surface(const DScene &sc, const HitD &h, f3 o, f3 d) {
+    if (h.inst >= 0) return make_surface_instanced(sc, h, o, d);
+    return make_surface_impl(sc, h, o, d, nullptr);
 }
 
 __device__ __forceinline__ f3 to_local(const Surface &s, f3 v) { return mk3(dot3(v, s.sn), dot3(v, s.tn), dot3(v, s.n)); }

@@ -42,8 +42,8 @@ __device__ __forceinline__ void xform_point(const float *m, float x, float y, fl
 __global__ void __launch_bounds__(256)
 prim_bounds_kernel(const float *__restrict__ verts, const int32_t *__restrict__ idx,
                    const int32_t *__restrict__ prim_kind, const AnalyticPrim *__restrict__ analytic,
-                   const int32_t *__restrict__ analytic_type, int n, float *__restrict__ leaf_box,
-                   uint32_t *__restrict__ scene_box) {
+                   const int32_t *__restrict__ analytic_type, const InstanceRec *__restrict__ instances, int n,
+                   float *__restrict__ leaf_box, uint32_t *__restrict__ scene_box) {
     int p = blockIdx.x * blockDim.x + threadIdx.x;
     float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
     bool ok = p < n;
@@ -56,6 +56,21 @@ prim_bounds_kernel(const float *__restrict__ verts, const int32_t *__restrict__ 
                 const float *v = verts + 3 * (int64_t)t[k];
 #pragma unroll
                 for (int a = 0; a < 3; ++a) { lo[a] = fminf(lo[a], v[a]); hi[a] = fmaxf(hi[a], v[a]); }
+            }
+        } else if ((~kind) & 0x40000000) {
+            // object instance: the object's box through the instance transform (8 corners), padded like the analytic boxes
+            const InstanceRec &I = instances[(~kind) & 0x3fffffff];
+            for (int c = 0; c < 8; ++c) {
+                float x, y, z;
+                xform_point(I.o2w, I.box[(c & 1) ? 3 : 0], I.box[(c & 2) ? 4 : 1], I.box[(c & 4) ? 5 : 2], x, y, z);
+                float q[3] = {x, y, z};
+#pragma unroll
+                for (int a = 0; a < 3; ++a) { lo[a] = fminf(lo[a], q[a]); hi[a] = fmaxf(hi[a], q[a]); }
+            }
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                float pad = 1e-5f * fmaxf(fmaxf(fabsf(lo[a]), fabsf(hi[a])), hi[a] - lo[a]);
+                lo[a] -= pad; hi[a] += pad;
             }
         } else {
             const AnalyticPrim &A = analytic[~kind];
@@ -432,8 +447,8 @@ __global__ void wide_single_kernel(int n, const float *__restrict__ box_root, Wi
 __global__ void __launch_bounds__(256)
 prim_records_kernel(const float *__restrict__ verts, const int32_t *__restrict__ idx,
                     const int32_t *__restrict__ prim_kind, const int32_t *__restrict__ analytic_type,
-                    const uint32_t *__restrict__ vals, int n, PrimRec *__restrict__ recs,
-                    int32_t *__restrict__ leaf_prims) {
+                    const InstanceRec *__restrict__ instances, const uint32_t *__restrict__ vals, int n,
+                    PrimRec *__restrict__ recs, int32_t *__restrict__ leaf_prims) {
     int j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= n) return;
     int p = (int)vals[j];
@@ -447,6 +462,12 @@ prim_records_kernel(const float *__restrict__ verts, const int32_t *__restrict__
         r.a = make_float4(p1[0], p1[1], p1[2], __int_as_float(p));
         r.b = make_float4(p2[0] - p1[0], p2[1] - p1[1], p2[2] - p1[2], __int_as_float(B2RT_PRIM_TRI));
         r.c = make_float4(p3[0] - p1[0], p3[1] - p1[1], p3[2] - p1[2], __int_as_float(0));
+    } else if ((~kind) & 0x40000000) {
+        const int k = (~kind) & 0x3fffffff;
+        const uint64_t ptr = reinterpret_cast<uint64_t>(instances + k);     // the record carries the instance's address
+        r.a = make_float4(__uint_as_float((uint32_t)ptr), __uint_as_float((uint32_t)(ptr >> 32)), 0.f, __int_as_float(instances[k].prim_base));
+        r.b = make_float4(0, 0, 0, __int_as_float(B2RT_PRIM_INSTANCE));
+        r.c = make_float4(0, 0, 0, __int_as_float(k));
     } else {
         r.a = make_float4(0, 0, 0, __int_as_float(p));
         r.b = make_float4(0, 0, 0, __int_as_float(analytic_type[~kind]));
@@ -467,6 +488,44 @@ int b2rt_build_impl(b2rt_ctx *ctx) {
     std::vector<int32_t> kind(n);
     for (size_t t = 0; t < ctx->h_tri_prim.size(); ++t) kind[ctx->h_tri_prim[t]] = (int32_t)t;
     for (size_t a = 0; a < ctx->h_analytic_prim.size(); ++a) kind[ctx->h_analytic_prim[a]] = ~(int32_t)a;
+    // two-level BVH: every object (child context: same device, same stream) builds its own tree in its own space first;
+    // an instance is one item of this tree whose leaf record points at the InstanceRec uploaded below
+    const size_t n_inst = ctx->h_instances.size();
+    std::vector<InstanceRec> irec(n_inst);
+    ctx->h_instance_base.assign(n_inst, 0);
+    ctx->n_virtual_prims = n;
+    if (n_inst || !ctx->objects.empty()) {
+        if (ctx->cur_object) { ctx->err = "build_accel: b2rt_object_end is missing"; return B2RT_E_STATE; }
+        std::vector<char> used(ctx->objects.size(), 0);
+        for (size_t k = 0; k < n_inst; ++k) used[ctx->h_instances[k].object] = 1;
+        for (size_t o = 0; o < ctx->objects.size(); ++o) {
+            b2rt_ctx *c = ctx->objects[o];
+            if (!used[o] || c->built) continue;
+            c->sort_variant = ctx->sort_variant;
+            int rc = b2rt_build_impl(c);
+            if (!rc) rc = b2rt_upload_tables(c);
+            if (rc) { ctx->err = "object " + std::to_string(o) + ": " + c->err; return rc; }
+        }
+        B2RT_CUDA(ctx, ctx->d_objects.reserve(std::max<size_t>(ctx->objects.size(), 1) * sizeof(DScene)));
+        B2RT_CUDA(ctx, ctx->d_instances.reserve(std::max<size_t>(n_inst, 1) * sizeof(InstanceRec)));
+        for (size_t k = 0; k < n_inst; ++k) {
+            const b2rt_ctx::HostInstance &H = ctx->h_instances[k];
+            const b2rt_ctx *c = ctx->objects[H.object];
+            InstanceRec &I = irec[k];
+            memcpy(I.o2w, H.o2w, sizeof(I.o2w)); memcpy(I.w2o, H.w2o, sizeof(I.w2o));
+            I.nodes = c->d_wide_nodes.as<WideNode>(); I.recs = c->d_prim_recs.as<PrimRec>(); I.analytic = c->d_analytic.as<AnalyticPrim>();
+            I.object = ctx->d_objects.as<DScene>() + H.object;
+            I.prim_base = (int32_t)ctx->n_virtual_prims; I.n_prims = c->n_prims; I.object_id = H.object; I.pad = 0;
+            memcpy(I.box, c->info.bounds, sizeof(I.box));
+            ctx->h_instance_base[k] = I.prim_base;
+            ctx->n_virtual_prims += c->n_prims;
+            if (ctx->n_virtual_prims >= (1ll << 31)) { ctx->err = "build_accel: more than 2^31 instanced primitives"; return B2RT_E_ARG; }
+            kind[H.item] = ~(int32_t)(0x40000000 | (int32_t)k);
+        }
+        if (n_inst)
+            B2RT_CUDA(ctx, cudaMemcpyAsync(ctx->d_instances.p, irec.data(), n_inst * sizeof(InstanceRec), cudaMemcpyHostToDevice, st));
+    }
+    const InstanceRec *d_inst = ctx->d_instances.as<InstanceRec>();
     auto up = [&](DevBuf &b, const void *src, size_t bytes) -> cudaError_t {
         cudaError_t e = b.reserve(bytes ? bytes : 16);
         if (e != cudaSuccess || !bytes) return e;
@@ -537,7 +596,7 @@ int b2rt_build_impl(b2rt_ctx *ctx) {
         init_scene_box_kernel<<<1, 32, 0, st>>>(scene_box);
         B2RT_LAUNCH_CHECK(ctx);
         prim_bounds_kernel<<<grid, 256, 0, st>>>(ctx->d_verts.as<float>(), ctx->d_idx.as<int32_t>(),
-                                                 ctx->d_prim_kind.as<int32_t>(), d_an, d_an_type, n, leaf_box,
+                                                 ctx->d_prim_kind.as<int32_t>(), d_an, d_an_type, d_inst, n, leaf_box,
                                                  scene_box);
         B2RT_LAUNCH_CHECK(ctx);
         morton_kernel<<<grid, 256, 0, st>>>(leaf_box, scene_box, n, ctx->d_keys.as<uint32_t>(),
@@ -551,7 +610,7 @@ int b2rt_build_impl(b2rt_ctx *ctx) {
         uint32_t *keys = ctx->d_keys.as<uint32_t>(), *vals = ctx->d_vals.as<uint32_t>();
 
         prim_records_kernel<<<grid, 256, 0, st>>>(ctx->d_verts.as<float>(), ctx->d_idx.as<int32_t>(),
-                                                  ctx->d_prim_kind.as<int32_t>(), d_an_type, vals, n,
+                                                  ctx->d_prim_kind.as<int32_t>(), d_an_type, d_inst, vals, n,
                                                   ctx->d_prim_recs.as<PrimRec>(), ctx->d_leaf_prims.as<int32_t>());
         B2RT_LAUNCH_CHECK(ctx);
 

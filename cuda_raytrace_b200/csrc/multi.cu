@@ -355,12 +355,8 @@ int b2rt_multi_resize(b2rt_multi *m, int ngpus, const int *devices) {
         b2rt_ctx *c = nullptr;
         int rc = b2rt_create(d, c0->seed, &c);
         if (rc) { m->err = b2rt_last_error(nullptr); return rc; }
-        c->h_verts = c0->h_verts; c->h_idx = c0->h_idx; c->h_tri_prim = c0->h_tri_prim; c->h_analytic = c0->h_analytic;
-        c->h_analytic_prim = c0->h_analytic_prim; c->h_analytic_type = c0->h_analytic_type;
-        c->h_prim_material = c0->h_prim_material; c->h_prim_light = c0->h_prim_light;
-        c->h_materials = c0->h_materials; c->h_lights = c0->h_lights;
-        c->h_vnormal = c0->h_vnormal; c->h_vuv = c0->h_vuv; c->h_tri_flags = c0->h_tri_flags; c->any_attr = c0->any_attr;
-        c->n_prims = c0->n_prims;
+        rc = b2rt_copy_staged_scene(c0, c);      // meshes, analytic shapes, objects and instances, materials, lights
+        if (rc) { m->err = c->err; b2rt_destroy(c); return rc; }
         c->film_filter = c0->film_filter; c->sampler_type = c0->sampler_type; c->sampler_nx = c0->sampler_nx; c->sampler_ny = c0->sampler_ny;
         c->fg_enable = c0->fg_enable; c->fg_samples = c0->fg_samples; c->fg_cos_angle = c0->fg_cos_angle;
         m->ctx.push_back(c); m->dev.push_back(d);

@@ -241,6 +241,8 @@ void b2rt_fill_dscene(b2rt_ctx *ctx, DScene *sc) {
     sc->verts = ctx->d_verts.as<float>();
     sc->vnormal = ctx->d_vnormal.as<float>();
     sc->vuv = ctx->d_vuv.as<float>();
+    sc->instances = ctx->h_instances.empty() ? nullptr : ctx->d_instances.as<InstanceRec>();
+    sc->n_instances = (int32_t)ctx->h_instances.size();
 }
 
 // material / light tables -> device (called from b2rt_build_accel).  Light power CDF as pbrt's
@@ -301,6 +303,15 @@ int b2rt_upload_tables(b2rt_ctx *ctx) {
     B2RT_CUDA(ctx, up(ctx->d_materials, ctx->h_materials.data(), ctx->h_materials.size() * sizeof(Material)));
     B2RT_CUDA(ctx, up(ctx->d_lights, ctx->h_lights.data(), nl * sizeof(Light)));
     B2RT_CUDA(ctx, up(ctx->d_light_cdf, cdf.data(), cdf.size() * sizeof(float)));
+    // scene views of the objects for the shade stage of instanced hits: their own geometry / attribute / per-primitive
+    // material arrays, this context's material table (InstanceRec::object points into d_objects, reserved by the build)
+    std::vector<DScene> osc(ctx->objects.size());
+    for (size_t o = 0; o < ctx->objects.size(); ++o) {
+        b2rt_fill_dscene(ctx->objects[o], &osc[o]);
+        osc[o].materials = ctx->d_materials.as<Material>(); osc[o].n_materials = (int32_t)ctx->h_materials.size();
+        osc[o].prim_light = nullptr; osc[o].lights = nullptr; osc[o].light_cdf = nullptr; osc[o].n_lights = 0;
+    }
+    if (!osc.empty()) B2RT_CUDA(ctx, up(ctx->d_objects, osc.data(), osc.size() * sizeof(DScene)));
     B2RT_CUDA(ctx, cudaStreamSynchronize(st));
     return B2RT_OK;
 }

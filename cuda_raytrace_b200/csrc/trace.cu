@@ -160,13 +160,20 @@ trace_persistent_kernel(const WideNode *__restrict__ nodes, const PrimRec *__res
                 for (uint32_t s = first; s < first + cnt; ++s) {
                     const float4 *pp = reinterpret_cast<const float4 *>(recs + s);
                     const float4 A = __ldg(pp), B = __ldg(pp + 1), C = __ldg(pp + 2);
-                    const int prim = __float_as_int(A.w);
+                    int prim = __float_as_int(A.w);
                     const int type = __float_as_int(B.w);
                     float t, b1 = 0.f, b2 = 0.f;
                     bool h;
                     if (type == B2RT_PRIM_TRI) h = tri_test(r, A, B, C, best_t, t, b1, b2);
                     else if (type == B2RT_PRIM_SPHERE) h = sphere_test(r, analytic[__float_as_int(C.w)], best_t, t);
-                    else h = disk_test(r, analytic[__float_as_int(C.w)], best_t, t);
+                    else if (type == B2RT_PRIM_DISK) h = disk_test(r, analytic[__float_as_int(C.w)], best_t, t);
+                    else {                                  // object instance (two-level BVH): b2rt_device.cuh instance_test
+                        int lprim, lslot;
+                        bool iovf = false;
+                        h = instance_test<ANY>(r, instance_of(A), best_t, t, b1, b2, lprim, lslot, iovf);
+                        prim += lprim;
+                        if (iovf) atomicAdd(status, 1u);
+                    }
                     if (h) {
                         if (ANY) { found = true; break; }
                         if (t < best_t || prim < best_prim) {
@@ -343,13 +350,20 @@ trace_spec_kernel(const WideNode *__restrict__ nodes, const PrimRec *__restrict_
 #ifdef B2RT_STATS
                     ++st_prims;
 #endif
-                    const int prim = __float_as_int(A.w);
+                    int prim = __float_as_int(A.w);
                     const int type = __float_as_int(B.w);
                     float t, b1 = 0.f, b2 = 0.f;
                     bool h;
                     if (type == B2RT_PRIM_TRI) h = tri_test_nobranch(r, A, B, C, best_t, t, b1, b2);
                     else if (type == B2RT_PRIM_SPHERE) h = sphere_test(r, analytic[__float_as_int(C.w)], best_t, t);
-                    else h = disk_test(r, analytic[__float_as_int(C.w)], best_t, t);
+                    else if (type == B2RT_PRIM_DISK) h = disk_test(r, analytic[__float_as_int(C.w)], best_t, t);
+                    else {                                  // object instance (two-level BVH): b2rt_device.cuh instance_test
+                        int lprim, lslot;
+                        bool iovf = false;
+                        h = instance_test<ANY>(r, instance_of(A), best_t, t, b1, b2, lprim, lslot, iovf);
+                        prim += lprim;
+                        if (iovf) atomicAdd(status, 1u);
+                    }
                     if (h) {
                         if (ANY) { found = true; break; }
                         if (t < best_t || prim < best_prim) {

@@ -293,8 +293,9 @@ def _m16(o2w):
 
 
 def to_pbrt(desc, eye, look, up, fov, xres, yres, spp, integrator, filename, renderer=None, sampler="lowdiscrepancy",
-            pixelfilter='"box"', world_rotate_y=0.0):
+            pixelfilter='"box"', world_rotate_y=0.0, extra_world=""):
     """integrator: the full `SurfaceIntegrator ...` line.  Only features the reference's GPU path translates are used.
+    extra_world: raw text appended inside the world block.
     world_rotate_y (degrees): the whole world AND the camera are turned about the y axis -- the same picture in expectation,
     but pbrt's constant-seeded random streams (photon directions, light samples) then produce different paths: an
     independent realisation of the reference renderer (tools/converged_parity.py averages several)."""
@@ -358,6 +359,8 @@ def to_pbrt(desc, eye, look, up, fov, xres, yres, spp, integrator, filename, ren
             L.append('  %s [%s]\n  Shape "disk" "float height" [%g] "float radius" [%g] "float innerradius" [%g]' % (
                 xf, _m16(sh[1]), sh[3], sh[4], sh[5]))
         L.append("AttributeEnd")
+    if extra_world:                 # raw scene text (ObjectBegin / ObjectInstance blocks of the instancing tests)
+        L.append(extra_world)
     L.append("WorldEnd")
     return "\n".join(L) + "\n"
 
@@ -405,3 +408,119 @@ def sphere_mesh(nu=24, nv=12, radius=0.5, center=(0.0, 0.0, 0.0), seed=None):
     if seed is not None:
         idx = idx[np.random.default_rng(seed).permutation(len(idx))]
     return P, idx, n.astype(np.float32), uv
+
+
+# ---- object instances (two-level BVH) ----------------------------------------------------------------------------------
+def xf_compose(*ms):
+    """product of 3x4 row-major affine transforms (applied right to left), float64 -> float32, with its inverse"""
+    M = np.eye(4)
+    for m in ms:
+        M = M @ np.vstack([np.asarray(m, np.float64).reshape(3, 4), [0, 0, 0, 1]])
+    return M[:3].astype(np.float32).reshape(12), np.linalg.inv(M)[:3].astype(np.float32).reshape(12)
+
+
+def xf_rotate_scale(axis, deg, scale, t):
+    """T(t) * R(axis, deg) * S(scale): (o2w, w2o) as float32[12]"""
+    a = np.asarray(axis, np.float64); a /= np.linalg.norm(a)
+    c, s = np.cos(np.radians(deg)), np.sin(np.radians(deg))
+    K = np.array([[0, -a[2], a[1]], [a[2], 0, -a[0]], [-a[1], a[0], 0]])
+    R = np.eye(3) * c + s * K + (1 - c) * np.outer(a, a)
+    M = np.eye(4); M[:3, :3] = R @ np.diag(np.broadcast_to(np.asarray(scale, np.float64), 3)); M[:3, 3] = t
+    return M[:3].astype(np.float32).reshape(12), np.linalg.inv(M)[:3].astype(np.float32).reshape(12)
+
+
+def instanced_scene(n_inst=10, seed=5, exact=False, attrs=True):
+    """World: a ground heightfield and one analytic sphere.  Object 0: a smooth sphere mesh (per-vertex normals + uv when
+    attrs) over a flat-shaded heightfield patch.  Object 1: an analytic sphere, a disk and a small mesh.  n_inst instances of
+    the two objects under rotations, non-uniform scales and translations.
+    exact=True: mesh-only objects with vertices on a 2^-10 grid and integer translations only -- every instance-space
+    operation is then exact and the two-level scene returns the same bits as its flattened copy.
+    Returns {"world": [shape...], "objects": [[shape...], ...], "instances": [(object, o2w, w2o), ...]} with shapes
+    ("mesh", P, idx, N, uv) | ("sphere", o2w, w2o, radius) | ("disk", o2w, w2o, height, radius, inner)."""
+    rng = np.random.default_rng(seed)
+    q = (lambda a: (np.round(np.asarray(a, np.float64) * 1024.0) / 1024.0).astype(np.float32)) if exact else (lambda a: np.asarray(a, np.float32))
+    Pg, ig = heightfield_mesh(16, 16, None, seed=seed + 1)
+    Pg = Pg.copy(); Pg[:, 1] = Pg[:, 1] * 0.3 - 0.8; Pg[:, [0, 2]] *= 4.0
+    world = [("mesh", q(Pg), ig, None, None)]
+    if not exact:
+        o2w, w2o = xf_translate(-2.5, 0.2, 1.0)
+        world.append(("sphere", o2w, w2o, 0.45))
+    P, idx, N, uv = sphere_mesh(16, 8, 0.4, (0.0, 0.3, 0.0), seed=seed + 2)
+    Ph, ih = heightfield_mesh(6, 6, None, seed=seed + 3)
+    Ph = Ph.copy(); Ph[:, 1] = Ph[:, 1] * 0.2 - 0.2; Ph[:, [0, 2]] *= 0.5
+    use = attrs and not exact
+    obj0 = [("mesh", q(P), idx, N if use else None, uv if use else None), ("mesh", q(Ph), ih, None, None)]
+    objects = [obj0]
+    if not exact:
+        so2w, sw2o = xf_rotate_scale((1, 2, 0.5), 25.0, (1.0, 1.0, 1.0), (0.1, 0.25, 0.0))
+        do2w, dw2o = xf_rotate_scale((1, 0, 0), -90.0, (1.0, 1.0, 1.0), (0.0, -0.1, 0.0))
+        Pm, im = heightfield_mesh(4, 4, None, seed=seed + 4)
+        Pm = Pm.copy(); Pm[:, 1] = Pm[:, 1] * 0.15 + 0.55; Pm[:, [0, 2]] *= 0.35
+        objects.append([("sphere", so2w, sw2o, 0.3), ("disk", do2w, dw2o, 0.0, 0.5, 0.1), ("mesh", Pm.astype(np.float32), im, None, None)])
+    inst = []
+    for k in range(n_inst):
+        o = int(k % len(objects))
+        if exact:
+            t = rng.integers(-3, 4, 3).astype(np.float64); t[1] = float(rng.integers(0, 3))
+            o2w, w2o = xf_translate(*t)
+        else:
+            t = rng.uniform(-3.0, 3.0, 3); t[1] = rng.uniform(-0.3, 1.2)
+            sc = rng.uniform(0.5, 1.6, 3) if k % 3 else np.full(3, rng.uniform(0.6, 1.4))
+            if k % 5 == 4:
+                sc[0] = -sc[0]                     # a mirroring instance (swaps handedness)
+            o2w, w2o = xf_rotate_scale(rng.normal(size=3), rng.uniform(0, 360), sc, t)
+        inst.append((o, o2w, w2o))
+    return {"world": world, "objects": objects, "instances": inst}
+
+
+def _add_shape(target, sh, style):
+    if sh[0] == "mesh":
+        kw = {}
+        if sh[3] is not None: kw["N"] = sh[3]
+        if sh[4] is not None: kw["uv"] = sh[4]
+        if style == "ref":
+            return target.add_mesh_attr(sh[1], sh[2], sh[3], sh[4]) if kw else target.add_mesh(sh[1], sh[2])
+        return target.add_mesh(sh[1], sh[2], **kw)
+    if sh[0] == "sphere":
+        return target.add_sphere(sh[1], sh[3], w2o=sh[2]) if style == "b2rt" else target.add_sphere(sh[1], sh[2], sh[3])
+    return target.add_disk(sh[1], sh[3], sh[4], sh[5], w2o=sh[2]) if style == "b2rt" else target.add_disk(sh[1], sh[2], sh[3], sh[4], sh[5])
+
+
+def fill_instanced(target, desc, style="b2rt"):
+    """style "b2rt": b2rt.Context signatures (add_sphere(o2w, radius, w2o=)); "port" / "ref": oracle.PortInstancedScene /
+    oracle.RefScene (add_sphere(o2w, w2o, radius)).  World shapes first, then the objects, then the instances."""
+    for sh in desc["world"]:
+        _add_shape(target, sh, style)
+    ids = []
+    for shapes in desc["objects"]:
+        ids.append(target.object_begin())
+        for sh in shapes:
+            _add_shape(target, sh, style)
+        target.object_end()
+    return [target.add_instance(ids[o], o2w, w2o) if style != "b2rt" else target.add_instance(ids[o], o2w, w2o=w2o)
+            for (o, o2w, w2o) in desc["instances"]]
+
+
+def flatten_instanced(desc):
+    """the same scene with every instance written out as world-space shapes (what the drop-in used to do): world shapes,
+    then instance 0's shapes, instance 1's, ...  Points by the float32 expression of pbrt's Transform (exact for the
+    `exact` scenes), normals by the inverse transpose, analytic shapes by composing the matrices."""
+    def xf_point32(m, x, y, z):          # pbrt Transform(Point) in binary32, one rounding per operation, left to right
+        m = np.asarray(m, np.float32).reshape(12)
+        return (m[0] * x + m[1] * y + m[2] * z + m[3], m[4] * x + m[5] * y + m[6] * z + m[7], m[8] * x + m[9] * y + m[10] * z + m[11])
+    out = list(desc["world"])
+    for (o, o2w, w2o) in desc["instances"]:
+        for sh in desc["objects"][o]:
+            if sh[0] == "mesh":
+                P = np.asarray(sh[1], np.float32)
+                x, y, z = xf_point32(o2w, P[:, 0], P[:, 1], P[:, 2])
+                N = None
+                if sh[3] is not None:
+                    n = np.asarray(sh[3], np.float32); m = np.asarray(w2o, np.float32).reshape(3, 4)
+                    N = np.stack([m[0, 0] * n[:, 0] + m[1, 0] * n[:, 1] + m[2, 0] * n[:, 2], m[0, 1] * n[:, 0] + m[1, 1] * n[:, 1] + m[2, 1] * n[:, 2],
+                                  m[0, 2] * n[:, 0] + m[1, 2] * n[:, 1] + m[2, 2] * n[:, 2]], -1).astype(np.float32)
+                out.append(("mesh", np.stack([x, y, z], -1).astype(np.float32), sh[2], N, sh[4]))
+            else:
+                a, b = xf_compose(o2w, sh[1])
+                out.append((sh[0], a, b) + tuple(sh[3:]))
+    return out

@@ -98,6 +98,23 @@ int b2rt_add_spot_light(b2rt_ctx *ctx, const float l2w[12], const float w2l[12],
 int b2rt_add_distant_light(b2rt_ctx *ctx, const float dir_to_light[3], const float rgb[3], int32_t *light_id);
 int b2rt_clear_scene(b2rt_ctx *ctx);
 
+/* ---- object instancing without flattening: replaces CudaRender::assembleObject / objectInstance, which hang every pbrt
+ * ObjectInstance under an OptiX Transform node over the object's own Group (cuda_render/cudarender.cpp:38-103).  Here: a
+ * two-level BVH.  The shapes added between b2rt_object_begin and b2rt_object_end form an OBJECT with a tree of its own,
+ * built once in the space the shapes are given in (pbrt: the CTM inside ObjectBegin / ObjectEnd); primitive ids returned by
+ * the b2rt_add_* calls in between are local to the object, area lights are refused (as pbrt does, core/api.cpp:1009-1011),
+ * material ids refer to the context's material table.  b2rt_add_instance places the object under the instance-to-world
+ * transform o2w (w2o = its inverse as pbrt holds it; NULL: computed here): nothing is copied, rays are taken into the
+ * instance's space as pbrt's TransformedPrimitive::Intersect does (core/primitive.cpp:95-120: origin as a point,
+ * direction as a vector, not renormalised, so t carries over) and the hit attributes come back to world space the same way.
+ * Hit ids: the items of the top-level tree (primitives and instances, in submission order) take the ids [0, n_items); the
+ * primitives of instance k then take [first_prim_k, first_prim_k + n_prims of its object), in instance order after
+ * n_items -- b2rt_instance_info after b2rt_build_accel.  Objects do not nest (pbrt: core/api.cpp:1107-1110, 1143-1146). */
+int b2rt_object_begin(b2rt_ctx *ctx, int32_t *object_id);
+int b2rt_object_end(b2rt_ctx *ctx);
+int b2rt_add_instance(b2rt_ctx *ctx, int32_t object_id, const float o2w[12], const float *w2o, int32_t *instance_id);
+int b2rt_instance_info(b2rt_ctx *ctx, int32_t instance_id, int32_t *first_prim, int32_t *n_prims, int32_t *object_id);
+
 /* ---- acceleration structure: replaces OptiX "Sbvh"/"Bvh" (cudarender.cpp:44,50) ---------------- */
 int b2rt_build_accel(b2rt_ctx *ctx);
 int b2rt_accel_info_get(b2rt_ctx *ctx, b2rt_accel_info *info);

@@ -138,6 +138,114 @@ class PortScene:
         return box
 
 
+def xf_point32(m, x, y, z):
+    """pbrt Transform::operator()(Point) for an affine 3x4 matrix in binary32, one rounding per operation, summed left to
+    right (core/transform.h:  m00*x + m01*y + m02*z + m03) -- the same expression as csrc/b2rt_device.cuh xf_point"""
+    m = np.asarray(m, np.float32).reshape(12)
+    return (m[0] * x + m[1] * y + m[2] * z + m[3], m[4] * x + m[5] * y + m[6] * z + m[7], m[8] * x + m[9] * y + m[10] * z + m[11])
+
+
+def xf_vec32(m, x, y, z):
+    m = np.asarray(m, np.float32).reshape(12)
+    return (m[0] * x + m[1] * y + m[2] * z, m[4] * x + m[5] * y + m[6] * z, m[8] * x + m[9] * y + m[10] * z)
+
+
+class PortInstancedScene:
+    """Oracle of the two-level scene (b2rt_object_begin / b2rt_add_instance), layered over the exhaustive C loop: pbrt's
+    TransformedPrimitive::Intersect (core/primitive.cpp:95-103) takes the ray into the instance's space with
+    Transform::operator()(Ray) -- origin as a point, direction as a vector, tmin / tmax unchanged -- and intersects the
+    object there.  Ids as in include/b2rt.h: items (world primitives and instances, submission order) first, then the
+    primitives of instance 0, instance 1, ...  Winner = (min t, then min id)."""
+
+    def __init__(self):
+        self.world = PortScene()
+        self.objects = []
+        self.instances = []          # (object, o2w, w2o, item id)
+        self._cur = None
+        self.n_items = 0
+
+    def object_begin(self):
+        self.objects.append(PortScene())
+        self._cur = self.objects[-1]
+        return len(self.objects) - 1
+
+    def object_end(self):
+        self._cur = None
+
+    def _target(self):
+        return self._cur if self._cur is not None else self.world
+
+    def add_mesh(self, P, idx, **kw):
+        if self._cur is not None:
+            return self._cur.add_mesh(P, idx, **kw)
+        first = self.n_items
+        self.world.add_mesh(P, idx, **kw)
+        self._item_of_world = getattr(self, "_item_of_world", [])
+        self._item_of_world.extend(range(first, first + len(np.asarray(idx).reshape(-1, 3))))
+        self.n_items += len(np.asarray(idx).reshape(-1, 3))
+        return first
+
+    def _add_one(self, fn, *a):
+        if self._cur is not None:
+            return fn(self._cur, *a)
+        fn(self.world, *a)
+        self._item_of_world = getattr(self, "_item_of_world", [])
+        self._item_of_world.append(self.n_items)
+        self.n_items += 1
+        return self.n_items - 1
+
+    def add_sphere(self, o2w, w2o, radius):
+        return self._add_one(PortScene.add_sphere, o2w, w2o, radius)
+
+    def add_disk(self, o2w, w2o, height, radius, inner=0.0):
+        return self._add_one(PortScene.add_disk, o2w, w2o, height, radius, inner)
+
+    def add_instance(self, obj, o2w, w2o):
+        self.instances.append((obj, np.asarray(o2w, np.float32).reshape(12), np.asarray(w2o, np.float32).reshape(12), self.n_items))
+        self.n_items += 1
+        return len(self.instances) - 1
+
+    def instance_bases(self):
+        base, out = self.n_items, []
+        for obj, _, _, _ in self.instances:
+            out.append(base)
+            base += len(self.objects[obj].kind)
+        return out
+
+    def instance_rays(self, k, rays):
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
+        _, _, w2o, _ = self.instances[k]
+        r = rays.copy()
+        r[:, 0], r[:, 1], r[:, 2] = xf_point32(w2o, rays[:, 0], rays[:, 1], rays[:, 2])
+        r[:, 4], r[:, 5], r[:, 6] = xf_vec32(w2o, rays[:, 4], rays[:, 5], rays[:, 6])
+        return r
+
+    def intersect(self, rays, nthreads=1):
+        """(t, global prim id, b1, b2, instance index or -1)"""
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
+        n = len(rays)
+        t = np.full(n, np.inf, np.float32); prim = np.full(n, -1, np.int32)
+        b1 = np.zeros(n, np.float32); b2 = np.zeros(n, np.float32); inst = np.full(n, -1, np.int32)
+        if self.world.kind:
+            wt, wp, wb1, wb2 = self.world.intersect(rays, nthreads)
+            items = np.asarray(self._item_of_world, np.int32)
+            hit = wp >= 0
+            t[hit], prim[hit], b1[hit], b2[hit] = wt[hit], items[wp[hit]], wb1[hit], wb2[hit]
+        for k, base in enumerate(self.instance_bases()):
+            it, ip, ib1, ib2 = self.objects[self.instances[k][0]].intersect(self.instance_rays(k, rays), nthreads)
+            gp = ip + base
+            better = (ip >= 0) & ((it < t) | ((it == t) & ((prim < 0) | (gp < prim))))
+            t[better], prim[better], b1[better], b2[better], inst[better] = it[better], gp[better], ib1[better], ib2[better], k
+        return t, prim, b1, b2, inst
+
+    def occluded(self, rays, nthreads=1):
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
+        occ = self.world.occluded(rays, nthreads) if self.world.kind else np.zeros(len(rays), np.uint8)
+        for k in range(len(self.instances)):
+            occ |= self.objects[self.instances[k][0]].occluded(self.instance_rays(k, rays), nthreads)
+        return occ
+
+
 def lbvh_build(box):
     """CPU restatement of the GPU builder on per-prim AABBs -> dict like Context.accel_download()."""
     box = np.ascontiguousarray(box, np.float32).reshape(-1, 6)
@@ -254,6 +362,39 @@ class RefScene:
 
     def num_cores(self):
         return self.lib.ref_num_cores()
+
+    # ---- object instances: pbrt's own ObjectInstance path (TransformedPrimitive over the object's BVHAccel) --------
+    def object_begin(self):
+        return self.lib.ref_scene_object_begin(self.h)
+
+    def object_end(self):
+        self.lib.ref_scene_object_end.restype = None
+        self.lib.ref_scene_object_end(self.h)
+
+    def add_instance(self, obj, o2w, w2o):
+        o2w = np.ascontiguousarray(o2w, np.float32).reshape(12)
+        w2o = np.ascontiguousarray(w2o, np.float32).reshape(12)
+        self.lib.ref_scene_add_instance.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+        return self.lib.ref_scene_add_instance(self.h, obj, _p(o2w), _p(w2o))
+
+    def intersect_inst(self, rays, nthreads=1):
+        """(t, prim, inst): prim is local to the object where inst >= 0"""
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
+        n = len(rays)
+        t, prim, inst = np.zeros(n, np.float32), np.zeros(n, np.int32), np.zeros(n, np.int32)
+        self.lib.ref_intersect_inst.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+        self.lib.ref_intersect_inst.restype = C.c_double
+        self.lib.ref_intersect_inst(self.h, n, _p(rays), _p(t), _p(prim), _p(inst), nthreads)
+        return t, prim, inst
+
+    def surface_at_inst(self, rays, nthreads=1):
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
+        out = np.zeros(len(rays), SURFACE_DTYPE)
+        inst = np.zeros(len(rays), np.int32)
+        self.lib.ref_surface_inst.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+        self.lib.ref_surface_inst.restype = None
+        self.lib.ref_surface_inst(self.h, len(rays), _p(rays), _p(out), _p(inst), nthreads)
+        return out, inst
 
     def close(self):
         if self.h:

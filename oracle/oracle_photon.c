@@ -210,17 +210,18 @@ static int closest_range(const port_scene *sc, v3 o, v3 d, float tmin, float tma
         const int32_t *vi = sc->idx + 3 * (int64_t)k;
         const float *p1 = sc->verts + 3 * (int64_t)vi[0], *p2 = sc->verts + 3 * (int64_t)vi[1], *p3 = sc->verts + 3 * (int64_t)vi[2];
         v3 e1 = V(p2[0] - p1[0], p2[1] - p1[1], p2[2] - p1[2]), e2 = V(p3[0] - p1[0], p3[1] - p1[1], p3[2] - p1[2]);
-        s->n = vnormalize(vcross(e2, e1));
+        s->n = vnormalize(vcross(e1, e2));      /* pbrt: Cross(dpdu, dpdv) with the default uv = the side of Cross(e1, e2) */
+        s->sn = e1;                             /* dpdu = p2 - p1 */
     } else {
         const float *A = sc->analytic + 28 * (int64_t)(~k);
         v3 no;
         if ((int)A[27] == 1) xfp(A + 12, s->p, &no); else no = V(0.f, 0.f, 1.f);
         s->n = vnormalize(xfn(A + 12, no));
         s->ray_eps = 5e-4f * t;
+        v3 dpdv;
+        coord_system(s->n, &s->sn, &dpdv);
     }
     s->ng = s->n;
-    v3 dpdv;
-    coord_system(s->n, &s->sn, &dpdv);
     s->sn = vnormalize(s->sn);
     s->tn = vcross(s->n, s->sn);
     return 1;

@@ -43,12 +43,27 @@ struct RefScene {
     Reference<Material> mtl;
     Primitive *accel;
     double build_seconds;
-    RefScene() : accel(NULL), build_seconds(0) {
+    RefScene() : accel(NULL), build_seconds(0), cur_object(-1) {
         Reference<Texture<Spectrum> > kd = new ConstantTexture<Spectrum>(Spectrum(0.5f));
         Reference<Texture<float> > sig = new ConstantTexture<float>(0.f);
         mtl = new MatteMaterial(kd, sig, NULL);
     }
+    // object instancing (pbrt ObjectBegin / ObjectEnd / ObjectInstance, core/api.cpp:1098-1178): while cur_object >= 0 the
+    // shapes go into that object's own primitive list with ids local to it
+    struct Object { std::vector<Reference<Primitive> > prims; int nshapes; bool aggregated; Object() : nshapes(0), aggregated(false) {} };
+    std::vector<Object> objects;
+    int cur_object;
+    struct Instance { int object; uint32_t primitiveId; };
+    std::vector<Instance> instances;
+    std::unordered_map<uint32_t, int> obj_id2prim;   // pbrt shapeId of an object's shape -> id local to the object
+    std::unordered_map<uint32_t, int> inst_of;       // primitiveId of a TransformedPrimitive -> instance index
     void push(const Reference<Shape> &s) {
+        if (cur_object >= 0) {
+            Object &o = objects[cur_object];
+            obj_id2prim[s->shapeId] = o.nshapes++;
+            o.prims.push_back(new GeometricPrimitive(s, mtl, NULL));
+            return;
+        }
         id2prim[s->shapeId] = (int)shapes.size();
         shapes.push_back(s);
         prims.push_back(new GeometricPrimitive(s, mtl, NULL));
@@ -164,6 +179,59 @@ double ref_scene_build(void *h) {
 
 int ref_scene_nprims(void *h) { return (int)((RefScene *)h)->shapes.size(); }
 
+// ---- object instances, exactly as pbrtObjectInstance makes them (core/api.cpp:1140-1172) -----------------------------
+int ref_scene_object_begin(void *h) {
+    RefScene *s = (RefScene *)h;
+    s->objects.push_back(RefScene::Object());
+    s->cur_object = (int)s->objects.size() - 1;
+    return s->cur_object;
+}
+void ref_scene_object_end(void *h) { ((RefScene *)h)->cur_object = -1; }
+// o2w = instance-to-world (pbrt's CTM at ObjectInstance), w2o its inverse.  The instance takes ONE slot in the scene's
+// primitive list; returns the instance index.  Hits inside it are reported as (instance, id local to the object).
+int ref_scene_add_instance(void *h, int object, const float o2w[12], const float w2o[12]) {
+    RefScene *s = (RefScene *)h;
+    RefScene::Object &o = s->objects[object];
+    if (o.prims.empty()) return -1;
+    if (!o.aggregated && (o.prims.size() > 1 || !o.prims[0]->CanIntersect())) {
+        Reference<Primitive> accel = CreateBVHAccelerator(o.prims, ParamSet());
+        o.prims.erase(o.prims.begin(), o.prims.end());
+        o.prims.push_back(accel);
+    }
+    o.aggregated = true;
+    Transform *t, *ti;
+    make_xforms(s, o2w, w2o, &t, &ti);
+    AnimatedTransform w2i(ti, 0.f, ti, 1.f);
+    Reference<Primitive> prim = new TransformedPrimitive(o.prims[0], w2i);
+    RefScene::Instance I; I.object = object; I.primitiveId = prim->primitiveId;
+    s->inst_of[prim->primitiveId] = (int)s->instances.size();
+    s->instances.push_back(I);
+    s->prims.push_back(prim);
+    s->shapes.push_back(Reference<Shape>());     // keeps "item" numbering: one slot per instance, never reported
+    return (int)s->instances.size() - 1;
+}
+// closest hit with the instance resolved: inst_out = instance index or -1, prim_out = id local to the object for an
+// instanced hit, global item id otherwise
+double ref_intersect_inst(void *h, int64_t nrays, const float *rays, float *t_out, int *prim_out, int *inst_out, int nthreads) {
+    RefScene *s = (RefScene *)h;
+    auto t0 = std::chrono::steady_clock::now();
+    parallel_for(nrays, nthreads, [=](int64_t lo, int64_t hi) {
+        for (int64_t i = lo; i < hi; ++i) {
+            const float *r = rays + 8 * i;
+            Ray ray(Point(r[0], r[1], r[2]), Vector(r[4], r[5], r[6]), r[3], r[7]);
+            Intersection isect;
+            t_out[i] = INFINITY; prim_out[i] = -1; inst_out[i] = -1;
+            if (s->accel->Intersect(ray, &isect)) {
+                t_out[i] = ray.maxt;
+                std::unordered_map<uint32_t, int>::const_iterator it = s->inst_of.find(isect.primitiveId);
+                if (it != s->inst_of.end()) { inst_out[i] = it->second; prim_out[i] = s->obj_id2prim.find(isect.shapeId)->second; }
+                else prim_out[i] = s->id2prim.find(isect.shapeId)->second;
+            }
+        }
+    });
+    return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+}
+
 void ref_scene_destroy(void *h) {
     RefScene *s = (RefScene *)h;
     if (!s) return;
@@ -198,7 +266,14 @@ double ref_intersect(void *h, int64_t nrays, const float *rays, float *t_out, in
 // Hit attributes as pbrt forms them: Intersection::GetBSDF runs Shape::GetShadingGeometry and MatteMaterial::GetBSDF,
 // i.e. BSDF(dgShading, dgGeom.nn) (core/reflection.cpp:601-609).  The BSDF's frame is private; LocalToWorld of the unit
 // axes returns sn, tn, nn (x * 1 + y * 0 + z * 0: exact up to the sign of a zero).  out: 20 floats per ray = b2rt_surface.
+void ref_surface_inst(void *h, int64_t nrays, const float *rays, float *out, int *inst_out, int nthreads);
 void ref_surface(void *h, int64_t nrays, const float *rays, float *out, int nthreads) {
+    ref_surface_inst(h, nrays, rays, out, NULL, nthreads);
+}
+// the same for scenes with object instances: inst_out (may be NULL) = instance index or -1; the prim field of an instanced
+// hit is the id local to its object.  TransformedPrimitive::Intersect has taken dg to world space and composed the
+// transforms GetShadingGeometry uses (core/primitive.cpp:104-117).
+void ref_surface_inst(void *h, int64_t nrays, const float *rays, float *out, int *inst_out, int nthreads) {
     RefScene *s = (RefScene *)h;
     parallel_for(nrays, nthreads, [=](int64_t lo, int64_t hi) {
         MemoryArena arena;
@@ -209,8 +284,11 @@ void ref_surface(void *h, int64_t nrays, const float *rays, float *out, int nthr
             Ray ray(Point(r[0], r[1], r[2]), Vector(r[4], r[5], r[6]), r[3], r[7]);
             Intersection isect;
             int prim = -1;
+            if (inst_out) inst_out[i] = -1;
             if (s->accel->Intersect(ray, &isect)) {
-                prim = s->id2prim.find(isect.shapeId)->second;
+                std::unordered_map<uint32_t, int>::const_iterator it = s->inst_of.find(isect.primitiveId);
+                if (it != s->inst_of.end()) { if (inst_out) inst_out[i] = it->second; prim = s->obj_id2prim.find(isect.shapeId)->second; }
+                else prim = s->id2prim.find(isect.shapeId)->second;
                 BSDF *bsdf = isect.GetBSDF(RayDifferential(ray), arena);
                 const Vector sn = bsdf->LocalToWorld(Vector(1, 0, 0)), tn = bsdf->LocalToWorld(Vector(0, 1, 0)),
                              nn = bsdf->LocalToWorld(Vector(0, 0, 1));
@@ -255,7 +333,7 @@ double ref_intersect_brute(void *h, int64_t nrays, const float *rays, float *t_o
             float best = INFINITY; int bp = -1; int cnt = 0;
             for (size_t k = 0; k < s->shapes.size(); ++k) {
                 float t, eps; DifferentialGeometry dg;
-                if (s->shapes[k]->Intersect(ray, &t, &eps, &dg)) {
+                if (s->shapes[k] && s->shapes[k]->Intersect(ray, &t, &eps, &dg)) {
                     if (t < best) { best = t; bp = (int)k; cnt = 1; }
                     else if (t == best) ++cnt;
                 }

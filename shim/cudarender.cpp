@@ -277,12 +277,30 @@ void CudaRender::createCudaShape(const std::string &name, Reference<Shape> &shap
     }
 }
 
-// instances are flattened: the shapes of the ObjectBegin block are re-submitted under the instance transform
-// (the reference builds an OptiX Transform node instead, cudarender.cpp:88-103)
+// Instances are NOT flattened: the shapes of an ObjectBegin block become one b2rt object (its own tree, built once, in the
+// block's space) the first time the block is instantiated, and every ObjectInstance adds a transform over it -- the
+// two-level BVH that stands in for the reference's OptiX Transform node over the object's Group (cudarender.cpp:38-103).
+// B2RT_FLATTEN_INSTANCES=1 re-submits the shapes under the instance transform instead (the round-1 behaviour, for A/B).
 void CudaRender::objectInstance(std::vector<Reference<Primitive> > *key, const Transform &transform) {
     std::map<std::vector<Reference<Primitive> > *, std::vector<ShapeRec> >::iterator it = instances_.find(key);
-    if (it == instances_.end()) return;
-    for (size_t i = 0; i < it->second.size(); ++i) submit(it->second[i], &transform, -1);
+    if (it == instances_.end() || it->second.empty()) return;
+    const char *flat = getenv("B2RT_FLATTEN_INSTANCES");
+    if (flat && atoi(flat)) {
+        for (size_t i = 0; i < it->second.size(); ++i) submit(it->second[i], &transform, -1);
+        return;
+    }
+    std::map<std::vector<Reference<Primitive> > *, int>::iterator ob = objectIds_.find(key);
+    int object = -1;
+    if (ob == objectIds_.end()) {
+        check(b2rt_object_begin(ctx_, &object), "b2rt_object_begin");
+        for (size_t i = 0; i < it->second.size(); ++i) submit(it->second[i], NULL, -1);
+        check(b2rt_object_end(ctx_), "b2rt_object_end");
+        objectIds_[key] = object;
+    } else object = ob->second;
+    float o2w[12], w2o[12];
+    m34(transform.GetMatrix(), o2w);
+    m34(transform.GetInverseMatrix(), w2o);
+    check(b2rt_add_instance(ctx_, object, o2w, w2o, NULL), "b2rt_add_instance");
 }
 
 void CudaRender::Render(const Scene *scene) {

@@ -69,6 +69,7 @@ private:
     Camera *camera_;
     std::map<const Material *, int> materialCache_;
     std::map<std::vector<Reference<Primitive> > *, std::vector<ShapeRec> > instances_;
+    std::map<std::vector<Reference<Primitive> > *, int> objectIds_;     // ObjectBegin block -> b2rt object, made on first use
     std::map<int, int> lightPrims_;
 };
 

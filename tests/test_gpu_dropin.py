@@ -15,7 +15,8 @@ BIN = os.path.join(ROOT, "shim", "_build", "pbrt_b2rt")
 EYE, LOOK, UP, FOV = (0, 1, 3.4), (0, 1, 0), (0, 1, 0), 40
 
 
-def _run(tmp_path, name, integrator, renderer, spp, res=96, pixelfilter='"box"', sampler="lowdiscrepancy", desc=None):
+def _run(tmp_path, name, integrator, renderer, spp, res=96, pixelfilter='"box"', sampler="lowdiscrepancy", desc=None,
+         extra_world="", gpu_env=None):
     out = {}
     desc = desc or S.cornell_scene(boxes=True)
     for tag, flag in (("gpu", ["-c"]), ("cpu", [])):
@@ -23,8 +24,9 @@ def _run(tmp_path, name, integrator, renderer, spp, res=96, pixelfilter='"box"',
         scene = str(tmp_path / ("%s_%s.pbrt" % (name, tag)))
         with open(scene, "w") as f:
             f.write(S.to_pbrt(desc, EYE, LOOK, UP, FOV, res, res, spp, integrator, pf, renderer=renderer,
-                              pixelfilter=pixelfilter, sampler=sampler))
-        r = subprocess.run([BIN, "--quiet"] + flag + [scene], capture_output=True, text=True, timeout=600)
+                              pixelfilter=pixelfilter, sampler=sampler, extra_world=extra_world))
+        env = dict(os.environ, **(gpu_env or {})) if tag == "gpu" else dict(os.environ)
+        r = subprocess.run([BIN, "--quiet"] + flag + [scene], capture_output=True, text=True, timeout=600, env=env)
         assert r.returncode == 0, r.stderr[-2000:]
         out[tag] = S.read_pfm(pf)
     return out["gpu"], out["cpu"]
@@ -160,3 +162,56 @@ def test_dropin_spot_and_distant_lights(tmp_path, light):
                     res=64, desc=desc)
     m = S.image_metrics(_block(gpu, 8), _block(cpu, 8))
     assert abs(m["bias_rel"]) < 0.015 and m["mean_rel"] < 0.04, m
+
+
+def _instanced_world():
+    """an ObjectBegin block (a smooth ball mesh with normals, an analytic sphere and a disk, each with its own material) and
+    five ObjectInstance lines under rotations, non-uniform scales and a mirroring transform"""
+    P, idx, N, uv = S.sphere_mesh(12, 6, 0.5, (0.0, 0.0, 0.0))
+    L = ['ObjectBegin "thing"',
+         '  AttributeBegin', '    Material "matte" "rgb Kd" [0.7 0.3 0.2]',
+         '    Shape "trianglemesh" "integer indices" [%s] "point P" [%s] "normal N" [%s]' % (
+             " ".join(str(int(v)) for v in idx.reshape(-1)), " ".join("%.9g" % v for v in P.reshape(-1)),
+             " ".join("%.9g" % v for v in N.reshape(-1))),
+         '  AttributeEnd',
+         '  AttributeBegin', '    Material "mirror" "rgb Kr" [0.9 0.9 0.9]', '    Translate 0 0.75 0',
+         '    Shape "sphere" "float radius" [0.25]', '  AttributeEnd',
+         '  AttributeBegin', '    Material "matte" "rgb Kd" [0.2 0.6 0.3]', '    Translate 0 -0.5 0', '    Rotate -90 1 0 0',
+         '    Shape "disk" "float radius" [0.7]', '  AttributeEnd',
+         'ObjectEnd']
+    for (t, r, sc) in (((-0.55, 0.45, -0.3), (20, 0, 1, 0), (0.5, 0.5, 0.5)), ((0.5, 0.35, -0.1), (35, 1, 1, 0), (0.45, 0.3, 0.45)),
+                       ((0.0, 0.4, 0.45), (-30, 0, 1, 1), (-0.35, 0.35, 0.35)), ((-0.45, 1.3, 0.2), (80, 1, 0, 0), (0.3, 0.5, 0.3)),
+                       ((0.5, 1.35, -0.4), (0, 0, 1, 0), (0.4, 0.4, 0.4))):
+        L += ['AttributeBegin', '  Translate %g %g %g' % t, '  Rotate %g %g %g %g' % r, '  Scale %g %g %g' % sc,
+              '  ObjectInstance "thing"', 'AttributeEnd']
+    return "\n".join(L)
+
+
+@pytest.mark.skipif(not os.path.exists(BIN), reason="shim/_build/pbrt_b2rt not built (needs /root/reference)")
+def test_dropin_object_instances_two_level(tmp_path):
+    """`ObjectBegin` / `ObjectInstance` in the scene file: the shim makes ONE b2rt object and five instances of it (two-level
+    BVH; the reference hangs them under OptiX Transform nodes, cudarender.cpp:38-103) -- against pbrt's CPU image of the
+    same file (TransformedPrimitive), and against the same run with B2RT_FLATTEN_INSTANCES=1 (every instance written out)."""
+    integ = 'SurfaceIntegrator "directlighting" "integer maxdepth" [5]'
+    desc = S.cornell_scene(spheres=False)
+    world = _instanced_world()
+    gpu, cpu = _run(tmp_path, "inst", integ, "simple", spp=256, res=96, desc=desc, extra_world=world)
+    m = S.image_metrics(_block(gpu, 4), _block(cpu, 4))
+    assert abs(m["bias_rel"]) < 0.005 and m["mean_rel"] < 0.015, m
+    flat, _ = _run(tmp_path, "instflat", integ, "simple", spp=256, res=96, desc=desc, extra_world=world,
+                   gpu_env={"B2RT_FLATTEN_INSTANCES": "1"})
+    d = np.abs(gpu - flat).sum(-1) > 1e-3 * (1.0 + flat.sum(-1))
+    assert d.mean() < 0.02, d.mean()
+    empty, _ = _run(tmp_path, "noinst", integ, "simple", spp=16, res=96, desc=desc)
+    assert np.abs(gpu - empty).mean() > 0.01 * empty.mean()          # the instances are in the picture
+
+
+@pytest.mark.skipif(not os.path.exists(BIN), reason="shim/_build/pbrt_b2rt not built (needs /root/reference)")
+def test_dropin_object_instances_photonmap(tmp_path):
+    """the same instanced file through the photon-mapping renderer (photon pass + final gathering trace the two-level tree)"""
+    prm = ('"integer causticphotons" [10000] "integer indirectphotons" [200000] "integer nused" [100] "float maxdist" [0.4] '
+           '"bool finalgather" ["false"]')
+    gpu, cpu = _run(tmp_path, "instpm", 'SurfaceIntegrator "photonmap" ' + prm, 'Renderer "photonmap" ' + prm, spp=64,
+                    desc=S.cornell_scene(spheres=False), extra_world=_instanced_world())
+    m = S.image_metrics(_block(gpu, 8), _block(cpu, 8))
+    assert abs(m["bias_rel"]) < 0.01 and m["mean_rel"] < 0.03, m
