@@ -122,3 +122,31 @@ def test_multi_resize_copies_the_scene(single):
         assert [m.ctxs[2].photons_download(k).tobytes() for k in (0, 1)] == ref["maps"]
         m.grid_build(0); m.grid_build(1)
         assert np.array_equal(m.render_frame(cam, spp=2, nused=40, max_dist=0.15), ref["box"])
+
+
+def test_multi_resize_copies_objects_and_instances(built):
+    """the same order of events for a scene with ObjectInstances: the objects (child contexts) and the instance list are
+    cloned too, every device builds the same two-level tree, and maps and frame equal the single-context results"""
+    desc = S.instanced_scene(n_inst=6, seed=13)
+    cam = b2rt.pbrt_camera((0.5, 3.0, 7.0), (0.0, 0.0, 0.0), (0.0, 1.0, 0.0), 50.0, 128, 96)
+
+    def fill(c):
+        S.fill_instanced(c, desc)
+        c.add_light(0, (60.0, 60.0, 60.0), p=(0.5, 4.5, 1.0))
+
+    with b2rt.Context(0, seed=7) as c:
+        fill(c)
+        c.build_accel()
+        c.photons_trace(0, 100_000)
+        want = [c.photons_download(k).tobytes() for k in (0, 1)]
+        c.grid_build(1)
+        img = c.render_frame(cam, spp=2, nused=30, max_dist=0.5)
+    with b2rt.MultiContext(1, seed=7, devices=[0]) as m:
+        fill(m.ctxs[0])
+        m.resize(3, devices=[0, 0, 0])
+        m.build_accel()
+        m.photons_trace(0, 100_000)
+        assert [m.ctxs[2].photons_download(k).tobytes() for k in (0, 1)] == want
+        m.grid_build(1)
+        assert np.array_equal(m.render_frame(cam, spp=2, nused=30, max_dist=0.5), img)
+        assert img.mean() > 1e-3
