@@ -285,6 +285,17 @@ int b2rt_add_sphere(b2rt_ctx *ctx, const float o2w[12], const float *w2o, float 
     return add_analytic(ctx, B2RT_PRIM_SPHERE, o2w, w2o, radius, 0.f, 0.f, material_id, arealight_id, prim);
 }
 
+int b2rt_add_sphere_ex(b2rt_ctx *ctx, const float o2w[12], const float *w2o, float radius, float zmin, float zmax,
+                       int32_t material_id, int32_t arealight_id, int32_t *prim) {
+    if (!ctx) return B2RT_E_ARG;
+    if (!(radius > 0.f) || !(zmin == zmin) || !(zmax == zmax)) { ctx->err = "add_sphere_ex: bad arguments"; return B2RT_E_ARG; }
+    // Sphere::Sphere (shapes/sphere.cpp:40-49): zmin = Clamp(min(z0, z1), -radius, radius), zmax likewise
+    float z0 = fminf(fmaxf(fminf(zmin, zmax), -radius), radius), z1 = fminf(fmaxf(fmaxf(zmin, zmax), -radius), radius);
+    if (!(z0 < z1)) { ctx->err = "add_sphere_ex: zmin and zmax leave no surface"; return B2RT_E_ARG; }
+    if (z0 <= -radius && z1 >= radius) z0 = z1 = 0.f;      // full sphere: no clipping (the record's "zmin >= zmax")
+    return add_analytic(ctx, B2RT_PRIM_SPHERE, o2w, w2o, radius, z0, z1, material_id, arealight_id, prim);
+}
+
 int b2rt_add_disk(b2rt_ctx *ctx, const float o2w[12], const float *w2o, float height, float radius,
                   float inner_radius, int32_t material_id, int32_t arealight_id, int32_t *prim) {
     return add_analytic(ctx, B2RT_PRIM_DISK, o2w, w2o, radius, height, inner_radius, material_id, arealight_id,

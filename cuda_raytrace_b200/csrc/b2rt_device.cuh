@@ -178,8 +178,8 @@ __device__ __forceinline__ f3 xf_normal(const float *w2o, f3 n) {
                w2o[2] * n.x + w2o[6] * n.y + w2o[10] * n.z);
 }
 
-// full sphere, pbrt Sphere::Intersect arithmetic (shapes/sphere.cpp:58-83); like the reference's device program
-// it ignores zmin/zmax/phiMax (cuda_render/util/shape/cudasphere.cu:27-72)
+// pbrt Sphere::Intersect arithmetic (shapes/sphere.cpp:58-106) with zmin / zmax clipping; the reference's device program
+// ignores zmin / zmax / phiMax (cuda_render/util/shape/cudasphere.cu:27-72)
 static __device__ __noinline__ bool sphere_test(const RayD &r, const AnalyticPrim &S, float tmax, float &t_out) {
     float ox, oy, oz, dx, dy, dz;
     xf_point(S.w2o, r.ox, r.oy, r.oz, ox, oy, oz);
@@ -198,6 +198,21 @@ static __device__ __noinline__ bool sphere_test(const RayD &r, const AnalyticPri
     if (t0 < r.tmin) {
         thit = t1;
         if (thit > tmax) return false;
+    }
+    // partial sphere: pbrt's zmin / zmax clipping (shapes/sphere.cpp:92-106), which the reference's device program ignores.
+    // For a sphere the record's height / inner fields hold zmin / zmax (already clamped to [-radius, radius] as pbrt's
+    // constructor does); zmin >= zmax = no clipping.  phimax is not clipped here (atan2f is not reproducible across
+    // libraries; the drop-in warns).
+    const float zmin = S.height, zmax = S.inner;
+    if (zmin < zmax) {
+        float pz = oz + dz * thit;
+        if ((zmin > -S.radius && pz < zmin) || (zmax < S.radius && pz > zmax)) {
+            if (thit == t1) return false;
+            if (t1 > tmax) return false;
+            thit = t1;
+            pz = oz + dz * thit;
+            if ((zmin > -S.radius && pz < zmin) || (zmax < S.radius && pz > zmax)) return false;
+        }
     }
     t_out = thit;
     return true;

@@ -81,6 +81,11 @@ int b2rt_add_mesh_ex(b2rt_ctx *ctx, int32_t nverts, const float *P, int32_t ntri
  * (cuda_render/util/shape/cudasphere.cpp:15-40); w2o may be NULL (then it is computed here). */
 int b2rt_add_sphere(b2rt_ctx *ctx, const float o2w[12], const float *w2o, float radius, int32_t material_id,
                     int32_t arealight_id, int32_t *prim);
+/* partial sphere: pbrt's "zmin" / "zmax" (shapes/sphere.cpp:40-49, 92-106; the reference's device program ignores them,
+ * cudasphere.cu:27-72): the surface with object-space z outside [zmin, zmax] is cut away, a ray that meets the cut-away part
+ * first continues to the far intersection.  Values are clamped to [-radius, radius] as pbrt does.  "phimax" is not supported. */
+int b2rt_add_sphere_ex(b2rt_ctx *ctx, const float o2w[12], const float *w2o, float radius, float zmin, float zmax,
+                       int32_t material_id, int32_t arealight_id, int32_t *prim);
 /* disk at object z = height (cuda_render/util/shape/cudadisk.cpp:15-45) */
 int b2rt_add_disk(b2rt_ctx *ctx, const float o2w[12], const float *w2o, float height, float radius,
                   float inner_radius, int32_t material_id, int32_t arealight_id, int32_t *prim);

@@ -100,8 +100,16 @@ class PortScene:
         self.analytic.append(rec)
         return len(self.kind) - 1
 
-    def add_sphere(self, o2w, w2o, radius):
-        return self._add_analytic(o2w, w2o, radius, 0.0, 0.0, 1)
+    def add_sphere(self, o2w, w2o, radius, zmin=None, zmax=None):
+        """zmin / zmax: pbrt's partial sphere; clamped as Sphere::Sphere does, (0, 0) in the record = full sphere"""
+        z0, z1 = 0.0, 0.0
+        if zmin is not None or zmax is not None:
+            a, b = (-radius if zmin is None else zmin), (radius if zmax is None else zmax)
+            z0 = float(np.clip(np.float32(min(a, b)), -np.float32(radius), np.float32(radius)))
+            z1 = float(np.clip(np.float32(max(a, b)), -np.float32(radius), np.float32(radius)))
+            if z0 <= -radius and z1 >= radius:
+                z0 = z1 = 0.0
+        return self._add_analytic(o2w, w2o, radius, z0, z1, 1)
 
     def add_disk(self, o2w, w2o, height, radius, inner=0.0):
         return self._add_analytic(o2w, w2o, height=height, radius=radius, inner=inner, typ=2)
@@ -320,9 +328,13 @@ class RefScene:
         self.lib.ref_surface(self.h, len(rays), _p(rays), _p(out), nthreads)
         return out
 
-    def add_sphere(self, o2w, w2o, radius):
+    def add_sphere(self, o2w, w2o, radius, zmin=None, zmax=None):
         o2w = np.ascontiguousarray(o2w, np.float32).reshape(12)
         w2o = np.ascontiguousarray(w2o, np.float32).reshape(12)
+        if zmin is not None or zmax is not None:
+            self.lib.ref_scene_add_sphere_ex.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_float]
+            return self.lib.ref_scene_add_sphere_ex(self.h, _p(o2w), _p(w2o), radius, -radius if zmin is None else zmin,
+                                                    radius if zmax is None else zmax)
         return self.lib.ref_scene_add_sphere(self.h, _p(o2w), _p(w2o), radius)
 
     def add_disk(self, o2w, w2o, height, radius, inner=0.0):
@@ -478,10 +490,10 @@ class PortFullScene:
         self.prim_light.extend([arealight] * len(np.asarray(idx).reshape(-1, 3)))
         return first
 
-    def add_sphere(self, o2w, radius, w2o=None, material=-1, arealight=-1):
+    def add_sphere(self, o2w, radius, w2o=None, material=-1, arealight=-1, zmin=None, zmax=None):
         self.prim_material.append(material)
         self.prim_light.append(arealight)
-        return self.geo.add_sphere(o2w, w2o, radius)
+        return self.geo.add_sphere(o2w, w2o, radius, zmin, zmax)
 
     def add_disk(self, o2w, height, radius, inner=0.0, w2o=None, material=-1, arealight=-1):
         self.prim_material.append(material)

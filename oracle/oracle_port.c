@@ -85,6 +85,19 @@ static int sphere_intersect(const float o_[3], const float d_[3], float tmin, fl
         thit = t1;
         if (thit > tmax) return 0;
     }
+    /* partial sphere, shapes/sphere.cpp:92-106 without the phi test: record slots 25 / 26 hold zmin / zmax for a sphere
+     * (already clamped to [-radius, radius]); zmin >= zmax = the full sphere */
+    float zmin = A28[25], zmax = A28[26];
+    if (zmin < zmax) {
+        float pz = o[2] + d[2] * thit;
+        if ((zmin > -radius && pz < zmin) || (zmax < radius && pz > zmax)) {
+            if (thit == t1) return 0;
+            if (t1 > tmax) return 0;
+            thit = t1;
+            pz = o[2] + d[2] * thit;
+            if ((zmin > -radius && pz < zmin) || (zmax < radius && pz > zmax)) return 0;
+        }
+    }
     *t = thit;
     return 1;
 }

@@ -157,6 +157,16 @@ int ref_scene_add_sphere(void *h, const float o2w[12], const float w2o[12], floa
     return first;
 }
 
+// pbrt's partial sphere ("zmin" / "zmax"; phimax stays 360)
+int ref_scene_add_sphere_ex(void *h, const float o2w[12], const float w2o[12], float radius, float zmin, float zmax) {
+    RefScene *s = (RefScene *)h;
+    Transform *t, *ti;
+    make_xforms(s, o2w, w2o, &t, &ti);
+    int first = (int)s->shapes.size();
+    s->push(new Sphere(t, ti, false, radius, zmin, zmax, 360.f));
+    return first;
+}
+
 int ref_scene_add_disk(void *h, const float o2w[12], const float w2o[12], float height, float radius,
                        float inner) {
     RefScene *s = (RefScene *)h;

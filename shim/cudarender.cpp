@@ -52,7 +52,10 @@ public:
 class CudaSphere {
 public:
     static float radius(const Sphere *s) { return s->radius; }
-    static bool partial(const Sphere *s) { return s->zmin > -s->radius || s->zmax < s->radius || s->phiMax < 2.f * M_PI; }
+    static bool clipped(const Sphere *s) { return s->zmin > -s->radius || s->zmax < s->radius; }
+    static float zmin(const Sphere *s) { return s->zmin; }
+    static float zmax(const Sphere *s) { return s->zmax; }
+    static bool partialPhi(const Sphere *s) { return s->phiMax < 2.f * M_PI; }
 };
 class CudaDisk {
 public:
@@ -216,7 +219,9 @@ int CudaRender::submit(const ShapeRec &r, const Transform *extra, int lightIndex
             Transform t = (*extra) * Transform(a);
             m34(t.GetMatrix(), o2w); m34(t.GetInverseMatrix(), w2o);
         }
-        if (r.kind == 1) check(b2rt_add_sphere(ctx_, o2w, w2o, r.radius, r.material, al, &prim), "b2rt_add_sphere");
+        if (r.kind == 1 && r.clipped)
+            check(b2rt_add_sphere_ex(ctx_, o2w, w2o, r.radius, r.height, r.inner, r.material, al, &prim), "b2rt_add_sphere_ex");
+        else if (r.kind == 1) check(b2rt_add_sphere(ctx_, o2w, w2o, r.radius, r.material, al, &prim), "b2rt_add_sphere");
         else check(b2rt_add_disk(ctx_, o2w, w2o, r.height, r.radius, r.inner, r.material, al, &prim), "b2rt_add_disk");
     }
     return prim;
@@ -229,7 +234,7 @@ void CudaRender::createCudaShape(const std::string &name, Reference<Shape> &shap
                                  int lightIndex) {
     ShapeRec r;
     r.radius = r.height = r.inner = 0.f;
-    r.reverse = false;
+    r.reverse = false; r.clipped = false;
     if (name == "trianglemesh") {
         const TriangleMesh *m = static_cast<const TriangleMesh *>(shape.GetPtr());
         r.kind = 0;
@@ -254,9 +259,11 @@ void CudaRender::createCudaShape(const std::string &name, Reference<Shape> &shap
     } else if (name == "sphere") {
         const Sphere *s = static_cast<const Sphere *>(shape.GetPtr());
         r.kind = 1; r.radius = CudaSphere::radius(s);
-        if (CudaSphere::partial(s))
-            Warning("CudaRender: partial sphere (zmin / zmax / phimax) rendered as a full sphere, like the reference's device "
-                    "code (cuda_render/util/shape/cudasphere.cu:27-72)");
+        r.clipped = CudaSphere::clipped(s);                // zmin / zmax are honoured (b2rt_add_sphere_ex)
+        r.height = CudaSphere::zmin(s); r.inner = CudaSphere::zmax(s);
+        if (CudaSphere::partialPhi(s))
+            Warning("CudaRender: \"phimax\" of a partial sphere is ignored (full turn), like the reference's device code "
+                    "(cuda_render/util/shape/cudasphere.cu:27-72)");
     } else if (name == "disk") {
         const Disk *d = static_cast<const Disk *>(shape.GetPtr());
         r.kind = 2; r.radius = CudaDisk::radius(d); r.height = CudaDisk::height(d); r.inner = CudaDisk::inner(d);

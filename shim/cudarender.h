@@ -57,6 +57,7 @@ private:
         std::vector<float> P; std::vector<int> idx;
         std::vector<float> N, uv;     // per-vertex world-space normals / uv of a mesh (empty: none)
         bool reverse;                 // ReverseOrientation ^ TransformSwapsHandedness
+        bool clipped;                 // sphere with zmin / zmax (kept in height / inner)
         float o2w[12], w2o[12], radius, height, inner;
         int material;
     };

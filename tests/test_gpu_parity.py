@@ -318,3 +318,31 @@ def test_chunked_host_path_with_ragged_tail(ctx):
     ctx.sync()
     assert np.array_equal(d_h.cpu().numpy().view(np.uint32).reshape(-1), np.ascontiguousarray(h).view(np.uint32))
     assert np.array_equal(d_o.cpu().numpy(), o)
+
+
+# ---- partial spheres (pbrt "zmin" / "zmax") ---------------------------------------------------------------------------
+def test_partial_spheres_bit_exact_vs_oracle_and_pbrt_golden(built):
+    """b2rt_add_sphere_ex: Sphere::Intersect's zmin / zmax clipping (shapes/sphere.cpp:92-106; the reference's device
+    program ignores it).  GPU == C port bit for bit; C port == pbrt's own hits (tests/test_oracle_cpu.py + here)."""
+    import make_golden_partial as GP
+    r = GP.rays()
+    ps = O.PortScene()
+    GP.fill(ps, "port")
+    et, ep, _, _ = ps.intersect(r, 4)
+    with b2rt.Context(0, seed=1) as c:
+        GP.fill(c, "b2rt")
+        c.build_accel()
+        hits = c.trace_closest(r)
+        occ = c.trace_any(r)
+        s = c.surface_at(r)
+        with pytest.raises(b2rt.B2rtError):
+            c.add_sphere(S.xf_translate(0, 0, 0)[0], 0.5, zmin=0.7, zmax=0.9)      # nothing left after the clamp
+    assert np.array_equal(hits["t"].view(np.uint32), et.view(np.uint32)) and np.array_equal(hits["prim"], ep)
+    assert np.array_equal(occ, (ep >= 0).astype(np.uint8))
+    g = load_golden("partial_spheres")
+    same = hits["t"].view(np.uint32) == g["t"].view(np.uint32)
+    assert (~same).sum() <= 2 and (hits["prim"][same] != g["prim"][same]).sum() <= 2
+    # rays that enter through the cut see the INSIDE of the sphere: the hit is the far root, the normal still points outwards
+    nprims = ep.max() + 1
+    inside = (ep >= nprims - 4) & (np.einsum("ij,ij->i", s["n"], r[:, 4:7]) > 0)
+    assert inside.sum() > 100

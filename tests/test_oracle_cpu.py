@@ -190,3 +190,25 @@ def test_bench_parity_block_against_reference():
     par = bench.hit_parity(hits, (sprim >= 0).astype(np.uint8), ref)
     ref["close"]()
     assert not par["ok"] and par["t_mismatch"] >= 1, par
+
+
+def test_partial_spheres_match_pbrt_golden(built):
+    """zmin / zmax clipping of Sphere::Intersect (shapes/sphere.cpp:92-106): the C port against pbrt's own hits (golden
+    from tests/golden/make_golden_partial.py), t bit for bit; the clipped-away part lets rays through to what is behind"""
+    import make_golden_partial as GP
+    g = np.load(os.path.join(ROOT, "tests", "golden", "partial_spheres.npz"))
+    ps = O.PortScene()
+    GP.fill(ps, "port")
+    r = GP.rays()
+    t, prim, _, _ = ps.intersect(r, 4)
+    same = t.view(np.uint32) == g["t"].view(np.uint32)
+    assert (~same).sum() <= 2 and np.all(t[~same] < g["t"][~same])       # BVHAccel's unpadded boxes may drop a hit
+    assert (prim[same] != g["prim"][same]).sum() <= 2
+    assert np.array_equal(ps.occluded(r, 4)[same], g["occ"][same])
+    full = O.PortScene()
+    (Pg, ig), sph = GP.shapes()
+    full.add_mesh(Pg, ig)
+    for (o2w, w2o, rad, z0, z1) in sph:
+        full.add_sphere(o2w, w2o, rad)
+    tf, pf, _, _ = full.intersect(r, 4)
+    assert (tf != t).sum() > 300                                          # the clipping changes many hits
