@@ -382,7 +382,10 @@ static __device__ __noinline__ bool instance_test(const RayD &rw, const Instance
 // lane that is still in the node loop has one, then the parked leaves are tested together (the if-if form ran the
 // primitive tests of these kernels with 2.5-6 of 32 threads per instruction).
 // Returns true on a hit (ANY: any accepted primitive).  `overflow` is set if the stack would have overflowed.
-template <bool ANY>
+// INST: the scene has object instances (instance records in the top-level tree).  A separate instantiation so that kernels
+// of scenes without instances keep their registers: with the nested call compiled in, photon_trace_kernel went from 80 to 128
+// registers and trace_spec_kernel started to spill (the Cfg2 step lost 19 %, run r06f).
+template <bool ANY, bool INST>
 __device__ __forceinline__ bool traverse(const WideNode *__restrict__ nodes, const PrimRec *__restrict__ recs,
                                          const AnalyticPrim *__restrict__ analytic, float ox, float oy, float oz,
                                          float dx, float dy, float dz, float tmin, float tmax, HitD &hit,
@@ -470,7 +473,7 @@ __device__ __forceinline__ bool traverse(const WideNode *__restrict__ nodes, con
                 int hslot = (int)s, hinst = -1;
                 if (type == B2RT_PRIM_TRI) h = tri_test_nobranch(r, A, B, C, best_t, t, b1, b2);
                 else if (type == B2RT_PRIM_SPHERE) h = sphere_test(r, analytic[__float_as_int(C.w)], best_t, t);
-                else if (type == B2RT_PRIM_DISK) h = disk_test(r, analytic[__float_as_int(C.w)], best_t, t);
+                else if (!INST || type == B2RT_PRIM_DISK) h = disk_test(r, analytic[__float_as_int(C.w)], best_t, t);
                 else {                                      // object instance: search its tree in its own space
                     int lprim;
                     h = instance_test<ANY>(r, instance_of(A), best_t, t, b1, b2, lprim, hslot, overflow);

@@ -171,8 +171,9 @@ static __device__ __noinline__ Surface make_surface_instanced(const DScene &sc, 
     return make_surface_impl(osc, lh, mk3(r.ox, r.oy, r.oz), mk3(r.dx, r.dy, r.dz), I);
 }
 
+template <bool INST>
 __device__ __forceinline__ Surface make_surface(const DScene &sc, const HitD &h, f3 o, f3 d) {
-    if (h.inst >= 0) return make_surface_instanced(sc, h, o, d);
+    if (INST && h.inst >= 0) return make_surface_instanced(sc, h, o, d);
     return make_surface_impl(sc, h, o, d, nullptr);
 }
 

@@ -23,6 +23,7 @@ constexpr int FG_NDIR = 50;              // nIndirSamplePhotons (photonmap.cpp:6
 // bounce order.  Same emission / bounce / roulette stream as photon_trace_kernel (photon.cu), so the paths are the very
 // paths whose caustic / indirect photons sit in maps 0 and 1; the radiance-photon draw is block 2 of the bounce counter,
 // which the path itself never reads.
+template <bool INST>
 __global__ void __launch_bounds__(FG_THREADS)
 fg_photon_kernel(DScene sc, uint32_t seed_lo, uint32_t seed_hi, int64_t first_path, int64_t n_paths, int max_depth,
                  b2rt_photon *__restrict__ slots, uint32_t *__restrict__ cnt_d, uint32_t *__restrict__ cnt_r, uint32_t *status,
@@ -42,10 +43,10 @@ fg_photon_kernel(DScene sc, uint32_t seed_lo, uint32_t seed_hi, int64_t first_pa
     bool overflow = false, specular_path = true;
     while (alive) {
         HitD h;
-        if (!traverse<false>(sc.nodes, sc.recs, sc.analytic, o.x, o.y, o.z, d.x, d.y, d.z, tmin, INFINITY, h, overflow))
+        if (!traverse<false, INST>(sc.nodes, sc.recs, sc.analytic, o.x, o.y, o.z, d.x, d.y, d.z, tmin, INFINITY, h, overflow))
             break;
         ++n_isect;
-        Surface s = make_surface(sc, h, o, d);
+        Surface s = make_surface<INST>(sc, h, o, d);
         Mat m = load_material(sc, s.material);
         f3 wo = -d;
         // pbrt's depositedPhoton (photonmap.cpp:455-490): a caustic-type hit is a deposit only while the caustic map still
@@ -311,6 +312,7 @@ __device__ __forceinline__ void fg_warp_sum_store(f3 accB, f3 accC, int lane, in
 // B2RT_FG_VARIANT=0, the first version, kept as the A/B reference of the split pipeline below (identical bytes): one warp
 // per shading point, lane = gather ray, traversal and the radiance-photon lookup inline.  A warp's 32 lanes walk 32
 // unrelated lookups with their own trip counts: 2.9 of 32 threads active per instruction (ncu r03g), 344 ms for 960 x 540.
+template <bool INST>
 __global__ void __launch_bounds__(FG_THREADS)
 final_gather_kernel(const FgArgs A) {
     __shared__ f3 s_dirs[FG_THREADS / 32][FG_NDIR];
@@ -341,10 +343,10 @@ final_gather_kernel(const FgArgs A) {
             (void)gpix;
             if (!R.act) continue;
             HitD h;
-            if (!traverse<false>(A.sc.nodes, A.sc.recs, A.sc.analytic, p.x, p.y, p.z, R.wi.x, R.wi.y, R.wi.z, ray_eps, INFINITY, h,
+            if (!traverse<false, INST>(A.sc.nodes, A.sc.recs, A.sc.analytic, p.x, p.y, p.z, R.wi.x, R.wi.y, R.wi.z, ray_eps, INFINITY, h,
                                  overflow))
                 continue;
-            const Surface s = make_surface(A.sc, h, p, R.wi);
+            const Surface s = make_surface<INST>(A.sc, h, p, R.wi);
             const f3 ng = dot3(s.ng, -R.wi) < 0.f ? -s.ng : s.ng;          // Faceforward(nGather, -bounceRay.d)
             float d2;
             const int ri = fg_radiance_nearest(A.g, A.rad_pos, A.rad_cells, A.rad_coarse1, A.rad_coarse2, A.rad_nbox1, A.rad_nbox2,
@@ -366,6 +368,7 @@ final_gather_kernel(const FgArgs A) {
 // combine launch sums in the same butterfly order, so the output is bit-identical to the fused kernel (tested).
 //
 // launch 1: one thread per gather ray (ray i of the chunk = query i / R, ray i % R): direction, traversal, hit record
+template <bool INST>
 __global__ void __launch_bounds__(FG_THREADS)
 fg_trace_kernel(const FgArgs A, int64_t nrays, int R) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -388,8 +391,8 @@ fg_trace_kernel(const FgArgs A, int64_t nrays, int R) {
     bool overflow = false;
     if (Ry.act) {
         HitD h;
-        if (traverse<false>(A.sc.nodes, A.sc.recs, A.sc.analytic, p.x, p.y, p.z, Ry.wi.x, Ry.wi.y, Ry.wi.z, q2.y, INFINITY, h, overflow)) {
-            const Surface s = make_surface(A.sc, h, p, Ry.wi);
+        if (traverse<false, INST>(A.sc.nodes, A.sc.recs, A.sc.analytic, p.x, p.y, p.z, Ry.wi.x, Ry.wi.y, Ry.wi.z, q2.y, INFINITY, h, overflow)) {
+            const Surface s = make_surface<INST>(A.sc, h, p, Ry.wi);
             const f3 ng = dot3(s.ng, -Ry.wi) < 0.f ? -s.ng : s.ng;          // Faceforward(nGather, -bounceRay.d)
             A.ray_recs[2 * i] = make_float4(s.p.x, s.p.y, s.p.z, 0.f);
             A.ray_recs[2 * i + 1] = make_float4(ng.x, ng.y, ng.z, 0.f);
@@ -546,7 +549,7 @@ int b2rt_photons_trace_fg_begin(b2rt_ctx *ctx, int64_t first_path, int64_t n_pat
     B2RT_CUDA(ctx, ctx->d_fg_cnt2.reserve((size_t)n_paths * 4));
     uint32_t *cnt_d = ctx->d_fg_cnt.as<uint32_t>(), *cnt_r = ctx->d_fg_cnt2.as<uint32_t>();
     uint32_t *counters = ctx->d_counters.as<uint32_t>();
-    fg_photon_kernel<<<(unsigned)((n_paths + FG_THREADS - 1) / FG_THREADS), FG_THREADS, 0, st>>>(
+    (sc.instances ? fg_photon_kernel<true> : fg_photon_kernel<false>)<<<(unsigned)((n_paths + FG_THREADS - 1) / FG_THREADS), FG_THREADS, 0, st>>>(
         sc, (uint32_t)ctx->seed, (uint32_t)(ctx->seed >> 32), first_path, n_paths, max_depth,
         ctx->d_fg_slots.as<b2rt_photon>(), cnt_d, cnt_r, counters + 8, ctx->fg_lim_c, ctx->fg_lim_i);
     B2RT_LAUNCH_CHECK(ctx);
@@ -720,7 +723,7 @@ int b2rt_final_gather_impl(b2rt_ctx *ctx, int64_t nq, const b2rt_query *d_querie
     if (ctx->fg_variant == 0) {
         A.idx = idx; A.found = found; A.queries = d_queries; A.nq = nq; A.out_rgb = d_rgb;
         int64_t blocks = std::min(cap, (nq + FG_THREADS / 32 - 1) / (FG_THREADS / 32));
-        final_gather_kernel<<<(unsigned)blocks, FG_THREADS, 0, st>>>(A);
+        (A.sc.instances ? final_gather_kernel<true> : final_gather_kernel<false>)<<<(unsigned)blocks, FG_THREADS, 0, st>>>(A);
         B2RT_LAUNCH_CHECK(ctx);
         return B2RT_OK;
     }
@@ -741,7 +744,7 @@ int b2rt_final_gather_impl(b2rt_ctx *ctx, int64_t nq, const b2rt_query *d_querie
     for (int64_t q0 = 0; q0 < nq; q0 += cq) {
         const int64_t n = std::min<int64_t>(cq, nq - q0), nrays = n * R;
         A.idx = idx + q0 * k; A.found = found + q0; A.queries = d_queries + q0; A.nq = n; A.out_rgb = d_rgb + 3 * q0;
-        fg_trace_kernel<<<(unsigned)((nrays + FG_THREADS - 1) / FG_THREADS), FG_THREADS, 0, st>>>(A, nrays, R);
+        (A.sc.instances ? fg_trace_kernel<true> : fg_trace_kernel<false>)<<<(unsigned)((nrays + FG_THREADS - 1) / FG_THREADS), FG_THREADS, 0, st>>>(A, nrays, R);
         B2RT_LAUNCH_CHECK(ctx);
         bool in_alt = false;
         rc = b2rt_sort_pairs_impl(ctx, nrays, A.ray_keys, A.ray_vals, ctx->d_fg_rkeys2.as<uint32_t>(), ctx->d_fg_rvals2.as<uint32_t>(),

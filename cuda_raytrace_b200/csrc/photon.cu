@@ -35,6 +35,7 @@ __device__ __forceinline__ uint32_t oct_encode(f3 v) {
 // K8+K9.  slots[(path-first)*max_depth + j]: j-th deposit of the path; cnt_c / cnt_i: how many of them are caustic /
 // indirect (a path deposits at most one caustic photon and it is always its first deposit, because specularPath
 // can only go from true to false).
+template <bool INST>
 __global__ void __launch_bounds__(PHOTON_THREADS)
 photon_trace_kernel(DScene sc, uint32_t seed_lo, uint32_t seed_hi, int64_t first_path, int64_t n_paths,
                     int max_depth, int flags, b2rt_photon *__restrict__ slots, uint32_t *__restrict__ cnt_c,
@@ -59,10 +60,10 @@ photon_trace_kernel(DScene sc, uint32_t seed_lo, uint32_t seed_hi, int64_t first
     bool overflow = false;
     while (alive) {
         HitD h;
-        if (!traverse<false>(sc.nodes, sc.recs, sc.analytic, o.x, o.y, o.z, d.x, d.y, d.z, tmin, INFINITY, h, overflow))
+        if (!traverse<false, INST>(sc.nodes, sc.recs, sc.analytic, o.x, o.y, o.z, d.x, d.y, d.z, tmin, INFINITY, h, overflow))
             break;
         ++n_isect;
-        Surface s = make_surface(sc, h, o, d);
+        Surface s = make_surface<INST>(sc, h, o, d);
         Mat m = load_material(sc, s.material);
         f3 wo = -d;
         if (m.type == B2RT_MAT_MATTE) {     // hasNonSpecular
@@ -103,6 +104,7 @@ photon_trace_kernel(DScene sc, uint32_t seed_lo, uint32_t seed_hi, int64_t first
 // atomicAdd per warp) and emit there, so the traversal and shading of an iteration run with (nearly) all 32 lanes
 // instead of the lanes that happen to survive to bounce b.  A path's randomness and its slot row depend only on its
 // index, so the output is byte-identical to photon_trace_kernel.
+template <bool INST>
 __global__ void __launch_bounds__(PHOTON_THREADS)
 photon_trace_regen_kernel(DScene sc, uint32_t seed_lo, uint32_t seed_hi, int64_t first_path, int64_t n_paths,
                           int max_depth, int flags, b2rt_photon *__restrict__ slots, uint32_t *__restrict__ cnt_c,
@@ -147,9 +149,9 @@ photon_trace_regen_kernel(DScene sc, uint32_t seed_lo, uint32_t seed_hi, int64_t
             // one bounce
             bool cont_path = false;
             HitD h;
-            if (traverse<false>(sc.nodes, sc.recs, sc.analytic, o.x, o.y, o.z, d.x, d.y, d.z, tmin, INFINITY, h, overflow)) {
+            if (traverse<false, INST>(sc.nodes, sc.recs, sc.analytic, o.x, o.y, o.z, d.x, d.y, d.z, tmin, INFINITY, h, overflow)) {
                 ++n_isect;
-                Surface s = make_surface(sc, h, o, d);
+                Surface s = make_surface<INST>(sc, h, o, d);
                 Mat m = load_material(sc, s.material);
                 f3 wo = -d;
                 if (m.type == B2RT_MAT_MATTE) {
@@ -368,7 +370,7 @@ int b2rt_photons_trace_begin(b2rt_ctx *ctx, int64_t first_path, int64_t n_paths,
     unsigned grid = (unsigned)((n_paths + PHOTON_THREADS - 1) / PHOTON_THREADS);
     if (ctx->photon_variant == 1) {
         if (ctx->photon_blocks_per_sm == 0) {
-            B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx->photon_blocks_per_sm, photon_trace_regen_kernel,
+            B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx->photon_blocks_per_sm, photon_trace_regen_kernel<false>,
                                                                          PHOTON_THREADS, 0));
             if (ctx->photon_blocks_per_sm < 1) ctx->photon_blocks_per_sm = 1;
         }
@@ -376,12 +378,12 @@ int b2rt_photons_trace_begin(b2rt_ctx *ctx, int64_t first_path, int64_t n_paths,
         photon_pool_reset_kernel<<<1, 1, 0, st>>>(pool);
         B2RT_LAUNCH_CHECK(ctx);
         unsigned pgrid = (unsigned)std::min<int64_t>(grid, (int64_t)ctx->sm_count * ctx->photon_blocks_per_sm);
-        photon_trace_regen_kernel<<<pgrid, PHOTON_THREADS, 0, st>>>(sc, (uint32_t)ctx->seed, (uint32_t)(ctx->seed >> 32),
+        (sc.instances ? photon_trace_regen_kernel<true> : photon_trace_regen_kernel<false>)<<<pgrid, PHOTON_THREADS, 0, st>>>(sc, (uint32_t)ctx->seed, (uint32_t)(ctx->seed >> 32),
                                                                    first_path, n_paths, max_depth, flags,
                                                                    ctx->d_slots.as<b2rt_photon>(), cnt_c, cnt_i, pool,
                                                                    counters + 8);
     } else {
-        photon_trace_kernel<<<grid, PHOTON_THREADS, 0, st>>>(sc, (uint32_t)ctx->seed, (uint32_t)(ctx->seed >> 32), first_path,
+        (sc.instances ? photon_trace_kernel<true> : photon_trace_kernel<false>)<<<grid, PHOTON_THREADS, 0, st>>>(sc, (uint32_t)ctx->seed, (uint32_t)(ctx->seed >> 32), first_path,
                                                              n_paths, max_depth, flags, ctx->d_slots.as<b2rt_photon>(),
                                                              cnt_c, cnt_i, counters + 8);
     }

@@ -82,6 +82,7 @@ __device__ __forceinline__ float disk_light_pdf(const AnalyticPrim &D, const Lig
 }
 
 // UniformSampleAllLights + EstimateDirect for a Lambertian surface (flags = BSDF_ALL & ~BSDF_SPECULAR)
+template <bool INST>
 __device__ f3 direct_lighting(const DScene &sc, const Surface &s, const Mat &m, f3 wo, uint32_t c0, uint32_t c1,
                               uint32_t node, uint32_t k0, uint32_t k1, bool &overflow, const SamplerD &sm) {
     f3 L = mk3(0.f, 0.f, 0.f);
@@ -111,7 +112,7 @@ __device__ f3 direct_lighting(const DScene &sc, const Surface &s, const Mat &m, 
                 // DistantLight::Sample_L (lights/distant.cpp:48-55): wi = lightDir, Li = L, visibility ray to infinity
                 const f3 wi = Lt.n;
                 if (!(dot3(wi, s.ng) * dot3(wo, s.ng) > 0.f)) continue;
-                if (traverse<true>(sc.nodes, sc.recs, sc.analytic, s.p.x, s.p.y, s.p.z, wi.x, wi.y, wi.z, s.ray_eps, INFINITY, h,
+                if (traverse<true, INST>(sc.nodes, sc.recs, sc.analytic, s.p.x, s.p.y, s.p.z, wi.x, wi.y, wi.z, s.ray_eps, INFINITY, h,
                                    overflow))
                     continue;
                 const float w = fabsf(dot3(wi, s.n));
@@ -132,7 +133,7 @@ __device__ f3 direct_lighting(const DScene &sc, const Surface &s, const Mat &m, 
                     I = I * fo;
                 }
                 // visibility segment p -> lightPos: direction (lightPos - p), [rayEps, 1]
-                if (traverse<true>(sc.nodes, sc.recs, sc.analytic, s.p.x, s.p.y, s.p.z, dl.x, dl.y, dl.z, s.ray_eps, 1.f, h,
+                if (traverse<true, INST>(sc.nodes, sc.recs, sc.analytic, s.p.x, s.p.y, s.p.z, dl.x, dl.y, dl.z, s.ray_eps, 1.f, h,
                                    overflow))
                     continue;
                 float w = fabsf(dot3(wi, s.n));     // / lightPdf (= 1)
@@ -149,7 +150,7 @@ __device__ f3 direct_lighting(const DScene &sc, const Surface &s, const Mat &m, 
                 bool emits = dot3(Lt.n, -wi) > 0.f;
                 bool same = dot3(wi, s.ng) * dot3(wo, s.ng) > 0.f;      // BSDF::f: sides by the geometric normal
                 if (lpdf > 0.f && emits && same) {
-                    if (!traverse<true>(sc.nodes, sc.recs, sc.analytic, s.p.x, s.p.y, s.p.z, dl.x, dl.y, dl.z, s.ray_eps,
+                    if (!traverse<true, INST>(sc.nodes, sc.recs, sc.analytic, s.p.x, s.p.y, s.p.z, dl.x, dl.y, dl.z, s.ray_eps,
                                         1.f - 1e-3f, h, overflow)) {
                         f3 wil = to_local(s, wi), wol = to_local(s, wo);
                         float bpdf = (wol.z * wil.z > 0.f) ? fabsf(wil.z) * B2_INV_PI : 0.f;
@@ -165,7 +166,7 @@ __device__ f3 direct_lighting(const DScene &sc, const Surface &s, const Mat &m, 
                 float lpdf = disk_light_pdf(D, Lt, s.p, bs.wi);
                 if (lpdf == 0.f) continue;
                 float weight = power_heuristic(bs.pdf, lpdf);
-                if (traverse<false>(sc.nodes, sc.recs, sc.analytic, s.p.x, s.p.y, s.p.z, bs.wi.x, bs.wi.y, bs.wi.z, s.ray_eps,
+                if (traverse<false, INST>(sc.nodes, sc.recs, sc.analytic, s.p.x, s.p.y, s.p.z, bs.wi.x, bs.wi.y, bs.wi.z, s.ray_eps,
                                     INFINITY, h, overflow) &&
                     h.prim == Lt.prim && dot3(Lt.n, -bs.wi) > 0.f) {
                     float w = bs.absdot * weight / bs.pdf;
@@ -183,6 +184,7 @@ struct TreeNode { f3 o, d; float tmin; f3 T; int depth; uint32_t id; };
 
 
 // K14 + K6 + K7.  sample s (chunk-local) -> pixel (crop-window row-major) and sample number k.
+template <bool INST>
 __global__ void __launch_bounds__(RENDER_THREADS)
 render_li_kernel(DScene sc, b2rt_camera cam, b2rt_frame_params fp, uint32_t seed_lo, uint32_t seed_hi, int64_t first_sample,
                  int64_t n_samples, int slots, float *__restrict__ sample_rgb, b2rt_query *__restrict__ qslots,
@@ -218,10 +220,10 @@ render_li_kernel(DScene sc, b2rt_camera cam, b2rt_frame_params fp, uint32_t seed
     while (sp > 0) {
         TreeNode nd = stack[--sp];
         HitD h;
-        if (!traverse<false>(sc.nodes, sc.recs, sc.analytic, nd.o.x, nd.o.y, nd.o.z, nd.d.x, nd.d.y, nd.d.z, nd.tmin, INFINITY, h,
+        if (!traverse<false, INST>(sc.nodes, sc.recs, sc.analytic, nd.o.x, nd.o.y, nd.o.z, nd.d.x, nd.d.y, nd.d.z, nd.tmin, INFINITY, h,
                              overflow))
             continue;
-        Surface sf = make_surface(sc, h, nd.o, nd.d);
+        Surface sf = make_surface<INST>(sc, h, nd.o, nd.d);
         Mat m = load_material(sc, sf.material);
         f3 wo = -nd.d;
         if (sf.light >= 0 && sf.light < sc.n_lights && dot3(sf.ng, wo) > 0.f) {     // isect.Le(wo): DiffuseAreaLight::L
@@ -230,7 +232,7 @@ render_li_kernel(DScene sc, b2rt_camera cam, b2rt_frame_params fp, uint32_t seed
         }
         if (m.type == B2RT_MAT_MATTE) {
             if (fp.direct_lighting)
-                L = L + nd.T * direct_lighting(sc, sf, m, wo, gpix, (uint32_t)k, nd.id, k0, k1, overflow, sm);
+                L = L + nd.T * direct_lighting<INST>(sc, sf, m, wo, gpix, (uint32_t)k, nd.id, k0, k1, overflow, sm);
             if (fp.use_caustic || fp.use_indirect) {
                 if ((int)nq < slots) {
                     f3 nf = dot3(sf.n, wo) < 0.f ? -sf.n : sf.n;              // Faceforward(n, wo)
@@ -358,6 +360,7 @@ sample_positions_kernel(int xres, int yres, int x0, int y0, int cw, int spp, uin
 }  // namespace
 
 // parity hook for K6: closest hit + the surface the shade stage derives from it, one thread per ray
+template <bool INST>
 __global__ void __launch_bounds__(128)
 surface_at_kernel(DScene sc, const b2rt_ray *__restrict__ rays, int64_t n, b2rt_surface *__restrict__ out, uint32_t *status) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -367,11 +370,11 @@ surface_at_kernel(DScene sc, const b2rt_ray *__restrict__ rays, int64_t n, b2rt_
     HitD h;
     bool overflow = false;
     float4 *o = reinterpret_cast<float4 *>(out + i);
-    if (!traverse<false>(sc.nodes, sc.recs, sc.analytic, a.x, a.y, a.z, b.x, b.y, b.z, a.w, b.w, h, overflow)) {
+    if (!traverse<false, INST>(sc.nodes, sc.recs, sc.analytic, a.x, a.y, a.z, b.x, b.y, b.z, a.w, b.w, h, overflow)) {
         for (int k = 0; k < 4; ++k) o[k] = make_float4(0.f, 0.f, 0.f, 0.f);
         o[4] = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
     } else {
-        const Surface s = make_surface(sc, h, mk3(a.x, a.y, a.z), mk3(b.x, b.y, b.z));
+        const Surface s = make_surface<INST>(sc, h, mk3(a.x, a.y, a.z), mk3(b.x, b.y, b.z));
         o[0] = make_float4(s.p.x, s.p.y, s.p.z, h.t);
         o[1] = make_float4(s.ng.x, s.ng.y, s.ng.z, s.u);
         o[2] = make_float4(s.n.x, s.n.y, s.n.z, s.v);
@@ -384,7 +387,7 @@ int b2rt_surface_at_impl(b2rt_ctx *ctx, int64_t n, const b2rt_ray *d_rays, b2rt_
     if (n <= 0) return B2RT_OK;
     DScene sc;
     b2rt_fill_dscene(ctx, &sc);
-    surface_at_kernel<<<(unsigned)((n + 127) / 128), 128, 0, ctx->stream>>>(sc, d_rays, n, d_out, ctx->d_counters.as<uint32_t>() + 8);
+    (sc.instances ? surface_at_kernel<true> : surface_at_kernel<false>)<<<(unsigned)((n + 127) / 128), 128, 0, ctx->stream>>>(sc, d_rays, n, d_out, ctx->d_counters.as<uint32_t>() + 8);
     B2RT_LAUNCH_CHECK(ctx);
     return B2RT_OK;
 }
@@ -419,7 +422,7 @@ int b2rt_camera_samples_impl(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_f
     const int64_t chunk = 1 << 20;
     for (int64_t s0 = 0; s0 < n; s0 += chunk) {
         const int64_t ns = std::min(chunk, n - s0);
-        render_li_kernel<<<(unsigned)((ns + RENDER_THREADS - 1) / RENDER_THREADS), RENDER_THREADS, 0, ctx->stream>>>(
+        (sc.instances ? render_li_kernel<true> : render_li_kernel<false>)<<<(unsigned)((ns + RENDER_THREADS - 1) / RENDER_THREADS), RENDER_THREADS, 0, ctx->stream>>>(
             sc, *cam, p, (uint32_t)ctx->seed, (uint32_t)(ctx->seed >> 32), s0, ns, slots, d_rgb + 3 * s0,
             d_q ? d_q + s0 * slots : nullptr, d_nq + s0, ctx->d_counters.as<uint32_t>() + 8, nullptr, sm, nullptr);
         B2RT_LAUNCH_CHECK(ctx);
@@ -499,7 +502,7 @@ int b2rt_render_pixels_impl(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_fr
         const int64_t np = (p0 + chunk_pixels <= n_cells) ? chunk_pixels : n_cells - p0;
         const int64_t ns = np * fp->spp;
         uint32_t *qcnt = ctx->d_qcnt.as<uint32_t>();
-        render_li_kernel<<<(unsigned)((ns + RENDER_THREADS - 1) / RENDER_THREADS), RENDER_THREADS, 0, st>>>(
+        (sc.instances ? render_li_kernel<true> : render_li_kernel<false>)<<<(unsigned)((ns + RENDER_THREADS - 1) / RENDER_THREADS), RENDER_THREADS, 0, st>>>(
             sc, *cam, p, (uint32_t)ctx->seed, (uint32_t)(ctx->seed >> 32), p0 * fp->spp, ns, slots,
             ctx->d_samples.as<float>(), ctx->d_qslots.as<b2rt_query>(), qcnt, counters + 8,
             filtered ? ctx->d_film_xy.as<float2>() + p0 * fp->spp : nullptr, sm, d_pixmap);

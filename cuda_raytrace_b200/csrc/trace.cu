@@ -20,7 +20,7 @@ namespace {
 
 constexpr int TRACE_THREADS = 128;
 
-template <bool ANY>
+template <bool ANY, bool INST>
 __global__ void __launch_bounds__(TRACE_THREADS)
 trace_kernel(const WideNode *__restrict__ nodes, const PrimRec *__restrict__ recs,
              const AnalyticPrim *__restrict__ analytic, const b2rt_ray *__restrict__ rays,
@@ -31,7 +31,7 @@ trace_kernel(const WideNode *__restrict__ nodes, const PrimRec *__restrict__ rec
     float4 r0 = __ldg(rp), r1 = __ldg(rp + 1);
     HitD h;
     bool overflow = false;
-    bool found = traverse<ANY>(nodes, recs, analytic, r0.x, r0.y, r0.z, r1.x, r1.y, r1.z, r0.w, r1.w, h, overflow);
+    bool found = traverse<ANY, INST>(nodes, recs, analytic, r0.x, r0.y, r0.z, r1.x, r1.y, r1.z, r0.w, r1.w, h, overflow);
     if (overflow) atomicAdd(status, 1u);
     if (ANY) {
         occ[i] = found ? 1 : 0;
@@ -56,7 +56,7 @@ trace_kernel(const WideNode *__restrict__ nodes, const PrimRec *__restrict__ rec
 constexpr int PT_THREADS = 128;
 constexpr int PT_SSTACK = 12;
 
-template <bool ANY>
+template <bool ANY, bool INST>
 __global__ void __launch_bounds__(PT_THREADS)
 trace_persistent_kernel(const WideNode *__restrict__ nodes, const PrimRec *__restrict__ recs,
                         const AnalyticPrim *__restrict__ analytic, const b2rt_ray *__restrict__ rays,
@@ -166,7 +166,7 @@ trace_persistent_kernel(const WideNode *__restrict__ nodes, const PrimRec *__res
                     bool h;
                     if (type == B2RT_PRIM_TRI) h = tri_test(r, A, B, C, best_t, t, b1, b2);
                     else if (type == B2RT_PRIM_SPHERE) h = sphere_test(r, analytic[__float_as_int(C.w)], best_t, t);
-                    else if (type == B2RT_PRIM_DISK) h = disk_test(r, analytic[__float_as_int(C.w)], best_t, t);
+                    else if (!INST || type == B2RT_PRIM_DISK) h = disk_test(r, analytic[__float_as_int(C.w)], best_t, t);
                     else {                                  // object instance (two-level BVH): b2rt_device.cuh instance_test
                         int lprim, lslot;
                         bool iovf = false;
@@ -219,7 +219,7 @@ trace_persistent_kernel(const WideNode *__restrict__ nodes, const PrimRec *__res
 // reverse for id < 0, with the clamped reciprocal also for d = +-0) with 6 instead of 12 FMNMX per child.  ncu r04i: the
 // ALU pipe (min / max, selects, compares) is the busiest pipe of this kernel, 48 / 54 % of its peak at 18 / 21.6 active
 // threads per instruction.
-template <bool ANY, int SORT, bool PL>
+template <bool ANY, int SORT, bool PL, bool INST>
 __global__ void __launch_bounds__(PT_THREADS, ANY ? 8 : 7)
 trace_spec_kernel(const WideNode *__restrict__ nodes, const PrimRec *__restrict__ recs,
                   const AnalyticPrim *__restrict__ analytic, const b2rt_ray *__restrict__ rays,
@@ -356,7 +356,7 @@ trace_spec_kernel(const WideNode *__restrict__ nodes, const PrimRec *__restrict_
                     bool h;
                     if (type == B2RT_PRIM_TRI) h = tri_test_nobranch(r, A, B, C, best_t, t, b1, b2);
                     else if (type == B2RT_PRIM_SPHERE) h = sphere_test(r, analytic[__float_as_int(C.w)], best_t, t);
-                    else if (type == B2RT_PRIM_DISK) h = disk_test(r, analytic[__float_as_int(C.w)], best_t, t);
+                    else if (!INST || type == B2RT_PRIM_DISK) h = disk_test(r, analytic[__float_as_int(C.w)], best_t, t);
                     else {                                  // object instance (two-level BVH): b2rt_device.cuh instance_test
                         int lprim, lslot;
                         bool iovf = false;
@@ -416,18 +416,19 @@ int b2rt_trace_impl(b2rt_ctx *ctx, int64_t n, const b2rt_ray *d_rays, b2rt_hit *
     const PrimRec *recs = ctx->d_prim_recs.as<PrimRec>();
     const AnalyticPrim *an = ctx->d_analytic.as<AnalyticPrim>();
     uint32_t *status = ctx->d_counters.as<uint32_t>() + 8;
+    const bool inst = !ctx->h_instances.empty();
     if (ctx->trace_variant == 1 || ctx->trace_variant == 2) {
         const bool spec = ctx->trace_variant == 2;
         // persistent grid: every SM holds as many blocks as the occupancy calculator allows
         int &per_sm = ctx->pt_blocks_per_sm[(spec ? 2 : 0) + (any_hit ? 1 : 0)];
         if (per_sm == 0 && spec) {
-            if (any_hit) B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_spec_kernel<true, 0, true>, PT_THREADS, 0));
-            else B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_spec_kernel<false, 2, true>, PT_THREADS, 0));
+            if (any_hit) B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_spec_kernel<true, 0, true, false>, PT_THREADS, 0));
+            else B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_spec_kernel<false, 2, true, false>, PT_THREADS, 0));
             if (per_sm < 1) per_sm = 1;
         }
         if (per_sm == 0) {
-            if (any_hit) B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_persistent_kernel<true>, PT_THREADS, 0));
-            else B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_persistent_kernel<false>, PT_THREADS, 0));
+            if (any_hit) B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_persistent_kernel<true, false>, PT_THREADS, 0));
+            else B2RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_persistent_kernel<false, false>, PT_THREADS, 0));
             if (per_sm < 1) per_sm = 1;
         }
         int64_t blocks = (int64_t)ctx->sm_count * per_sm;
@@ -451,34 +452,33 @@ int b2rt_trace_impl(b2rt_ctx *ctx, int64_t n, const b2rt_ray *d_rays, b2rt_hit *
             const int so = ctx->trace_sort < 0 ? (any_hit ? 0 : 2) : ctx->trace_sort;
             auto pick = [&](auto planes) {
                 constexpr bool P = decltype(planes)::value;
-                if (so == 2) return any_hit ? trace_spec_kernel<true, 2, P> : trace_spec_kernel<false, 2, P>;
-                if (so == 1) return any_hit ? trace_spec_kernel<true, 1, P> : trace_spec_kernel<false, 1, P>;
-                return any_hit ? trace_spec_kernel<true, 0, P> : trace_spec_kernel<false, 0, P>;
+                if (so == 2) return any_hit ? trace_spec_kernel<true, 2, P, false> : trace_spec_kernel<false, 2, P, false>;
+                if (so == 1) return any_hit ? trace_spec_kernel<true, 1, P, false> : trace_spec_kernel<false, 1, P, false>;
+                return any_hit ? trace_spec_kernel<true, 0, P, false> : trace_spec_kernel<false, 0, P, false>;
             };
             // r04k A/B (identical bytes): closest-hit rays 6426 -> 6570 Mrays/s, incoherent 3141 -> 3191, any-hit rays 7533 ->
             // 7455 -- so the sign-selected planes are the default for closest hit only (1), 2 = both, 0 = neither
             const bool planes = ctx->trace_planes == 2 || (ctx->trace_planes == 1 && !any_hit);
             auto kern = planes ? pick(std::true_type()) : pick(std::false_type());
+            // scenes with object instances: the instantiation that knows the instance record (one per ray type, default child
+            // order and plane selection) -- kept apart so that the instance call costs the other scenes no register or spill
+            if (inst) kern = any_hit ? trace_spec_kernel<true, 0, false, true> : trace_spec_kernel<false, 2, true, true>;
             kern<<<(unsigned)blocks, PT_THREADS, 0, ctx->stream>>>(nodes, recs, an, d_rays, any_hit ? nullptr : d_hits,
                                                                    any_hit ? d_occ : nullptr, n, pool, ctx->trace_refill,
                                                                    chunk, status, next_pool);
         }
-        else if (any_hit)
-            trace_persistent_kernel<true><<<(unsigned)blocks, PT_THREADS, 0, ctx->stream>>>(
-                nodes, recs, an, d_rays, nullptr, d_occ, n, pool, ctx->trace_refill, chunk, status);
-        else
-            trace_persistent_kernel<false><<<(unsigned)blocks, PT_THREADS, 0, ctx->stream>>>(
-                nodes, recs, an, d_rays, d_hits, nullptr, n, pool, ctx->trace_refill, chunk, status);
+        else {
+            auto kern = any_hit ? (inst ? trace_persistent_kernel<true, true> : trace_persistent_kernel<true, false>)
+                                : (inst ? trace_persistent_kernel<false, true> : trace_persistent_kernel<false, false>);
+            kern<<<(unsigned)blocks, PT_THREADS, 0, ctx->stream>>>(nodes, recs, an, d_rays, any_hit ? nullptr : d_hits,
+                                                                   any_hit ? d_occ : nullptr, n, pool, ctx->trace_refill, chunk, status);
+        }
         B2RT_LAUNCH_CHECK(ctx);
         return B2RT_OK;
     }
     int64_t grid = (n + TRACE_THREADS - 1) / TRACE_THREADS;
-    if (any_hit)
-        trace_kernel<true><<<(unsigned)grid, TRACE_THREADS, 0, ctx->stream>>>(nodes, recs, an, d_rays, nullptr,
-                                                                              d_occ, n, status);
-    else
-        trace_kernel<false><<<(unsigned)grid, TRACE_THREADS, 0, ctx->stream>>>(nodes, recs, an, d_rays, d_hits,
-                                                                               nullptr, n, status);
+    auto kern = any_hit ? (inst ? trace_kernel<true, true> : trace_kernel<true, false>) : (inst ? trace_kernel<false, true> : trace_kernel<false, false>);
+    kern<<<(unsigned)grid, TRACE_THREADS, 0, ctx->stream>>>(nodes, recs, an, d_rays, any_hit ? nullptr : d_hits, any_hit ? d_occ : nullptr, n, status);
     B2RT_LAUNCH_CHECK(ctx);
     return B2RT_OK;
 }
