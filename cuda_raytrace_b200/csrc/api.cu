@@ -60,6 +60,7 @@ int b2rt_create(int device, uint64_t seed, b2rt_ctx **out) {
     if (const char *v = getenv("B2RT_TRACE_CHUNK")) ctx->trace_chunk = atoi(v);
     if (const char *v = getenv("B2RT_GATHER_VARIANT")) ctx->gather_variant = atoi(v);
     if (const char *v = getenv("B2RT_SORT_VARIANT")) ctx->sort_variant = atoi(v);
+    if (const char *v = getenv("B2RT_SORT_RANK")) ctx->sort_rank = atoi(v);
     if (const char *v = getenv("B2RT_PHOTON_VARIANT")) ctx->photon_variant = atoi(v);
     if (const char *v = getenv("B2RT_FG_VARIANT")) ctx->fg_variant = atoi(v);
     if (const char *v = getenv("B2RT_TRACE_SORT")) ctx->trace_sort = atoi(v);
@@ -93,7 +94,7 @@ static void destroy_object(b2rt_ctx *c) {
 static b2rt_ctx *new_object(b2rt_ctx *ctx) {
     b2rt_ctx *c = new b2rt_ctx();
     c->device = ctx->device; c->seed = ctx->seed; c->sm_count = ctx->sm_count; c->stream = ctx->stream; c->parent = ctx;
-    c->sort_variant = ctx->sort_variant;
+    c->sort_variant = ctx->sort_variant; c->sort_rank = ctx->sort_rank;
     if (cudaSetDevice(ctx->device) != cudaSuccess || cudaEventCreate(&c->evb0) != cudaSuccess || cudaEventCreate(&c->evb1) != cudaSuccess ||
         cudaEventCreate(&c->evb_mid) != cudaSuccess || c->d_counters.reserve(256) != cudaSuccess ||
         cudaMemsetAsync(c->d_counters.p, 0, 256, ctx->stream) != cudaSuccess) {

@@ -64,10 +64,27 @@ radix_hist_kernel(const uint32_t *__restrict__ keys, int64_t n, int shift, uint3
 // lanes), but the tile is first permuted into digit order in shared memory and then written out by consecutive
 // threads: all elements of one digit of one block are contiguous in the output, so the global stores are coalesced
 // runs instead of 4-byte scatters (ncu r01b: the direct scatter reached ~0.8 TB/s of the 6.5 TB/s copy peak).
+// RANK: how a lane finds the lanes of its warp that hold the same digit: 0 = match.any, 1 = eight ballots (one per digit
+// bit) combined with and / not.  FULL: the tile is complete (no bounds checks; the tail tile takes the other instantiation).
+template <int RANK>
+__device__ __forceinline__ uint32_t digit_peers(uint32_t d, bool ok) {
+    if (RANK == 0) return __match_any_sync(0xffffffffu, ok ? d : 0x100u);
+    uint32_t peers = __ballot_sync(0xffffffffu, ok);
+    if (!ok) peers = ~peers;
+#pragma unroll
+    for (int b = 0; b < 8; ++b) {
+        const bool bit = (d >> b) & 1u;
+        const uint32_t m = __ballot_sync(0xffffffffu, bit);
+        peers &= bit ? m : ~m;
+    }
+    return peers;
+}
+
+template <int RANK, bool FULL>
 __global__ void __launch_bounds__(SORT_THREADS, 4)
 radix_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__restrict__ vals_in,
                      uint32_t *__restrict__ keys_out, uint32_t *__restrict__ vals_out, int64_t n, int shift,
-                     const uint32_t *__restrict__ scanned_hist, int nblocks) {
+                     const uint32_t *__restrict__ scanned_hist, int nblocks, int tile_first) {
     __shared__ uint32_t sh[SORT_WARPS][RADIX];  // first: running warp histogram; then: exclusive count of earlier warps
     __shared__ uint32_t s_off[RADIX];           // first tile slot of digit d
     __shared__ uint32_t s_gadj[RADIX];          // global position of digit d's first element minus s_off[d]
@@ -77,27 +94,23 @@ radix_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__res
     __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t lt = (1u << lane) - 1u;
-    const int64_t tile0 = (int64_t)blockIdx.x * SORT_TILE;
+    const int tile = tile_first + blockIdx.x;
+    const int64_t tile0 = (int64_t)tile * SORT_TILE;
     const int64_t base = tile0 + warp * (32 * SORT_ITEMS);
-    const int tile_n = (int)(n - tile0 < SORT_TILE ? n - tile0 : SORT_TILE);
+    const int tile_n = FULL ? SORT_TILE : (int)(n - tile0 < SORT_TILE ? n - tile0 : SORT_TILE);
+    const int wn = FULL ? 32 * SORT_ITEMS : max(0, min(32 * SORT_ITEMS, tile_n - warp * (32 * SORT_ITEMS)));   // valid keys of this warp
+    const uint32_t *kp = keys_in + base + lane, *vp = vals_in + base + lane;
 
-    // Three loops instead of one: the 16 loads and the 16 match.any are independent of each other and pipeline; only
+    // Three loops instead of one: the 16 loads and the 16 peer searches are independent of each other and pipeline; only
     // the counter updates are ordered (item r before item r+1 of the same digit: that order is the sort's stability).
     uint32_t k[SORT_ITEMS], rank[SORT_ITEMS], peers[SORT_ITEMS];
 #pragma unroll
-    for (int r = 0; r < SORT_ITEMS; ++r) {
-        int64_t i = base + r * 32 + lane;
-        k[r] = i < n ? keys_in[i] : 0u;
-    }
+    for (int r = 0; r < SORT_ITEMS; ++r) k[r] = (FULL || r * 32 + lane < wn) ? kp[r * 32] : 0u;
+#pragma unroll
+    for (int r = 0; r < SORT_ITEMS; ++r) peers[r] = digit_peers<RANK>((k[r] >> shift) & 0xff, FULL || r * 32 + lane < wn);
 #pragma unroll
     for (int r = 0; r < SORT_ITEMS; ++r) {
-        const bool ok = base + r * 32 + lane < n;
-        const uint32_t d = ok ? ((k[r] >> shift) & 0xff) : 0x100u;
-        peers[r] = __match_any_sync(0xffffffffu, d);
-    }
-#pragma unroll
-    for (int r = 0; r < SORT_ITEMS; ++r) {
-        const bool ok = base + r * 32 + lane < n;
+        const bool ok = FULL || r * 32 + lane < wn;
         const uint32_t d = (k[r] >> shift) & 0xff;
         const int leader = __ffs(peers[r]) - 1;
         uint32_t before = 0;
@@ -134,25 +147,34 @@ radix_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__res
             if (w < warp) wbase += s_wsum[w];
         const uint32_t off = wbase + inc - run;
         s_off[d] = off;
-        s_gadj[d] = scanned_hist[(int64_t)d * nblocks + blockIdx.x] - off;
+        s_gadj[d] = scanned_hist[(int64_t)d * nblocks + tile] - off;
     }
     __syncthreads();
 #pragma unroll
     for (int r = 0; r < SORT_ITEMS; ++r) {
-        int64_t i = base + r * 32 + lane;
-        if (i < n) {
+        if (FULL || r * 32 + lane < wn) {
             uint32_t d = (k[r] >> shift) & 0xff;
             uint32_t lp = s_off[d] + sh[warp][d] + rank[r];
             s_key[lp] = k[r];
-            s_val[lp] = vals_in[i];
+            s_val[lp] = vp[r * 32];
         }
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < tile_n; i += SORT_THREADS) {
-        uint32_t key = s_key[i];
-        uint32_t pos = s_gadj[(key >> shift) & 0xff] + (uint32_t)i;
-        keys_out[pos] = key;
-        vals_out[pos] = s_val[i];
+    if (FULL) {
+#pragma unroll 4
+        for (int i = threadIdx.x; i < SORT_TILE; i += SORT_THREADS) {
+            const uint32_t key = s_key[i];
+            const uint32_t pos = s_gadj[(key >> shift) & 0xff] + (uint32_t)i;
+            keys_out[pos] = key;
+            vals_out[pos] = s_val[i];
+        }
+    } else {
+        for (int i = threadIdx.x; i < tile_n; i += SORT_THREADS) {
+            uint32_t key = s_key[i];
+            uint32_t pos = s_gadj[(key >> shift) & 0xff] + (uint32_t)i;
+            keys_out[pos] = key;
+            vals_out[pos] = s_val[i];
+        }
     }
 }
 
@@ -241,11 +263,7 @@ onesweep_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__
         k[r] = i < n ? keys_in[i] : 0u;
     }
 #pragma unroll
-    for (int r = 0; r < SORT_ITEMS; ++r) {
-        const bool ok = base + r * 32 + lane < n;
-        const uint32_t d = ok ? ((k[r] >> shift) & 0xff) : 0x100u;
-        peers[r] = __match_any_sync(0xffffffffu, d);
-    }
+    for (int r = 0; r < SORT_ITEMS; ++r) peers[r] = digit_peers<1>((k[r] >> shift) & 0xff, base + r * 32 + lane < n);
 #pragma unroll
     for (int r = 0; r < SORT_ITEMS; ++r) {
         const bool ok = base + r * 32 + lane < n;
@@ -383,6 +401,24 @@ scan_add_kernel(uint32_t *__restrict__ data, int64_t n, const uint32_t *__restri
         if (base + j < n) data[base + j] += off;
 }
 
+// the complete tiles in one launch, the ragged last tile (if any) in a second one-block launch of the checked instantiation
+int launch_scatter(b2rt_ctx *ctx, const uint32_t *kin, const uint32_t *vin, uint32_t *kout, uint32_t *vout, int64_t n, int shift,
+                   const uint32_t *hist, int nblocks) {
+    const int full = (int)(n / SORT_TILE);
+    const bool ballots = ctx->sort_rank == 1;
+    if (full) {
+        if (ballots) radix_scatter_kernel<1, true><<<full, SORT_THREADS, 0, ctx->stream>>>(kin, vin, kout, vout, n, shift, hist, nblocks, 0);
+        else radix_scatter_kernel<0, true><<<full, SORT_THREADS, 0, ctx->stream>>>(kin, vin, kout, vout, n, shift, hist, nblocks, 0);
+        B2RT_LAUNCH_CHECK(ctx);
+    }
+    if (full < nblocks) {
+        if (ballots) radix_scatter_kernel<1, false><<<1, SORT_THREADS, 0, ctx->stream>>>(kin, vin, kout, vout, n, shift, hist, nblocks, full);
+        else radix_scatter_kernel<0, false><<<1, SORT_THREADS, 0, ctx->stream>>>(kin, vin, kout, vout, n, shift, hist, nblocks, full);
+        B2RT_LAUNCH_CHECK(ctx);
+    }
+    return B2RT_OK;
+}
+
 int scan_rec(b2rt_ctx *ctx, uint32_t *d, int64_t n, uint32_t *tmp, uint32_t *d_total) {
     int64_t nb = (n + SCAN_TILE - 1) / SCAN_TILE;
     if (nb <= 1) {
@@ -454,9 +490,8 @@ int b2rt_sort_pairs_impl(b2rt_ctx *ctx, int64_t n, uint32_t *keys, uint32_t *val
         B2RT_LAUNCH_CHECK(ctx);
         int rc = b2rt_exclusive_scan_u32(ctx, hist, (int64_t)RADIX * nblocks, nullptr);
         if (rc) return rc;
-        radix_scatter_kernel<<<nblocks, SORT_THREADS, 0, ctx->stream>>>(kin, vin, kout, vout, n, shift, hist,
-                                                                        nblocks);
-        B2RT_LAUNCH_CHECK(ctx);
+        rc = launch_scatter(ctx, kin, vin, kout, vout, n, shift, hist, nblocks);
+        if (rc) return rc;
         uint32_t *t;
         t = kin; kin = kout; kout = t;
         t = vin; vin = vout; vout = t;
@@ -555,8 +590,8 @@ int b2rt_sort_pairs_noalloc(b2rt_ctx *ctx, int64_t n, uint32_t *keys, uint32_t *
             B2RT_LAUNCH_CHECK(ctx);
             rc = scan_rec(ctx, hist, (int64_t)RADIX * nblocks, scan_tmp, nullptr);
             if (rc) return rc;
-            radix_scatter_kernel<<<nblocks, SORT_THREADS, 0, ctx->stream>>>(kin, vin, kout, vout, n, 8 * p, hist, nblocks);
-            B2RT_LAUNCH_CHECK(ctx);
+            rc = launch_scatter(ctx, kin, vin, kout, vout, n, 8 * p, hist, nblocks);
+            if (rc) return rc;
             std::swap(kin, kout);
             std::swap(vin, vout);
         }
