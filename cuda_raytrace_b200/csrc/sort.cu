@@ -11,6 +11,7 @@
 #include <algorithm>
 #include <mutex>
 #include <utility>
+#include <type_traits>
 
 namespace {
 
@@ -65,17 +66,26 @@ radix_hist_kernel(const uint32_t *__restrict__ keys, int64_t n, int shift, uint3
 // threads: all elements of one digit of one block are contiguous in the output, so the global stores are coalesced
 // runs instead of 4-byte scatters (ncu r01b: the direct scatter reached ~0.8 TB/s of the 6.5 TB/s copy peak).
 // RANK: how a lane finds the lanes of its warp that hold the same digit: 0 = match.any, 1 = eight ballots (one per digit
-// bit) combined with and / not.  FULL: the tile is complete (no bounds checks; the tail tile takes the other instantiation).
-template <int RANK>
+// bit) combined with and / not (default), 5 = a per-warp table of lane masks in shared memory (atomicOr, sync, read).
+// FULL: the tile is complete (no bounds checks; the tail tile takes the other instantiation).
+// Measured on B200, 2^26 pairs (profiles/r06h..r06k): match.any 2.50-2.80 ms, ballots 1.92-1.97 ms, shared-memory table 2.03 ms,
+// a mix of match.any for some items and ballots for the rest 1.95-2.06 ms (worse the more match.any): MATCH is the slow
+// instruction here, and once it is gone two very different rankings cost the same -- what is left (ncu r06i: issue-active
+// 47 %, 4 blocks of 64 registers per SM, five block barriers per tile, the 16 ordered counter rounds) is not the peer search.
+template <int RANK, bool FULL = false>
 __device__ __forceinline__ uint32_t digit_peers(uint32_t d, bool ok) {
-    if (RANK == 0) return __match_any_sync(0xffffffffu, ok ? d : 0x100u);
-    uint32_t peers = __ballot_sync(0xffffffffu, ok);
-    if (!ok) peers = ~peers;
+    if (RANK == 0) return __match_any_sync(0xffffffffu, (FULL || ok) ? d : 0x100u);
+    uint32_t peers = 0xffffffffu;
+    if (!FULL) {
+        peers = __ballot_sync(0xffffffffu, ok);
+        if (!ok) peers = ~peers;
+    }
+    // per bit: one LOP3 with a predicate result, one VOTE, one select-and (the sign-extended bit picks m or ~m)
 #pragma unroll
     for (int b = 0; b < 8; ++b) {
-        const bool bit = (d >> b) & 1u;
-        const uint32_t m = __ballot_sync(0xffffffffu, bit);
-        peers &= bit ? m : ~m;
+        const uint32_t m = __ballot_sync(0xffffffffu, (d & (1u << b)) != 0u);
+        const uint32_t s = (uint32_t)((int32_t)(d << (31 - b)) >> 31);     // all ones where the bit is set
+        peers &= ~(m ^ s);
     }
     return peers;
 }
@@ -106,8 +116,41 @@ radix_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__res
     uint32_t k[SORT_ITEMS], rank[SORT_ITEMS], peers[SORT_ITEMS];
 #pragma unroll
     for (int r = 0; r < SORT_ITEMS; ++r) k[r] = (FULL || r * 32 + lane < wn) ? kp[r * 32] : 0u;
+    if (RANK == 5) {
+        // Digit peers through shared memory instead of 8 ballots (~40 ALU instructions) per key: a per-warp table of lane
+        // masks indexed by digit -- every lane ORs its bit into T[d], the warp syncs, T[d] IS the peer mask.  Two tables
+        // used in turn; a lane takes its own bit of round r-1 out again (atomicAnd) after the sync of round r, when every
+        // lane has read it, so nothing has to be cleared wholesale.  The tables live where s_key is built later (zeroed
+        // here; only complete tiles take this path).  Results are the same integers as with match.any / ballots.
+        static_assert(2 * SORT_WARPS * RADIX <= SORT_TILE, "the mask tables alias s_key");
+        for (int i = threadIdx.x; i < 2 * SORT_WARPS * RADIX; i += SORT_THREADS) s_key[i] = 0;
+        __syncthreads();
+        uint32_t *T0 = s_key + warp * RADIX, *T1 = s_key + (SORT_WARPS + warp) * RADIX;
+        const uint32_t me = 1u << lane;
+        uint32_t dprev = 0;
 #pragma unroll
-    for (int r = 0; r < SORT_ITEMS; ++r) peers[r] = digit_peers<RANK>((k[r] >> shift) & 0xff, FULL || r * 32 + lane < wn);
+        for (int r = 0; r < SORT_ITEMS; ++r) {
+            const uint32_t d = (k[r] >> shift) & 0xff;
+            uint32_t *T = (r & 1) ? T1 : T0, *Tp = (r & 1) ? T0 : T1;
+            atomicOr(&T[d], me);
+            __syncwarp();
+            const uint32_t pr = T[d];
+            if (r > 0) atomicAnd(&Tp[dprev], ~me);
+            dprev = d;
+            const int leader = __ffs(pr) - 1;
+            uint32_t before = 0;
+            if (lane == leader) {
+                before = sh[warp][d];
+                sh[warp][d] = before + __popc(pr);
+            }
+            before = __shfl_sync(0xffffffffu, before, leader);
+            rank[r] = before + __popc(pr & lt);
+        }
+        __syncthreads();
+    } else {
+#pragma unroll
+    for (int r = 0; r < SORT_ITEMS; ++r)
+        peers[r] = digit_peers<(RANK == 0 ? 0 : 1), FULL>((k[r] >> shift) & 0xff, FULL || r * 32 + lane < wn);
 #pragma unroll
     for (int r = 0; r < SORT_ITEMS; ++r) {
         const bool ok = FULL || r * 32 + lane < wn;
@@ -123,6 +166,7 @@ radix_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__res
         __syncwarp();
     }
     __syncthreads();
+    }
     // thread d: per-warp counts of digit d -> exclusive over warps; block total -> exclusive scan over the digits
     {
         const int d = threadIdx.x;          // SORT_THREADS == RADIX
@@ -405,17 +449,18 @@ scan_add_kernel(uint32_t *__restrict__ data, int64_t n, const uint32_t *__restri
 int launch_scatter(b2rt_ctx *ctx, const uint32_t *kin, const uint32_t *vin, uint32_t *kout, uint32_t *vout, int64_t n, int shift,
                    const uint32_t *hist, int nblocks) {
     const int full = (int)(n / SORT_TILE);
-    const bool ballots = ctx->sort_rank == 1;
-    if (full) {
-        if (ballots) radix_scatter_kernel<1, true><<<full, SORT_THREADS, 0, ctx->stream>>>(kin, vin, kout, vout, n, shift, hist, nblocks, 0);
-        else radix_scatter_kernel<0, true><<<full, SORT_THREADS, 0, ctx->stream>>>(kin, vin, kout, vout, n, shift, hist, nblocks, 0);
-        B2RT_LAUNCH_CHECK(ctx);
+    auto launch = [&](auto rank) {
+        constexpr int R = decltype(rank)::value;
+        if (full) radix_scatter_kernel<R, true><<<full, SORT_THREADS, 0, ctx->stream>>>(kin, vin, kout, vout, n, shift, hist, nblocks, 0);
+        if (full < nblocks) radix_scatter_kernel<(R == 0 ? 0 : 1), false><<<1, SORT_THREADS, 0, ctx->stream>>>(kin, vin, kout, vout, n, shift, hist, nblocks, full);
+    };
+    switch (ctx->sort_rank) {
+        case 0: launch(std::integral_constant<int, 0>()); break;
+        case 5: launch(std::integral_constant<int, 5>()); break;
+        default: launch(std::integral_constant<int, 1>()); break;
     }
-    if (full < nblocks) {
-        if (ballots) radix_scatter_kernel<1, false><<<1, SORT_THREADS, 0, ctx->stream>>>(kin, vin, kout, vout, n, shift, hist, nblocks, full);
-        else radix_scatter_kernel<0, false><<<1, SORT_THREADS, 0, ctx->stream>>>(kin, vin, kout, vout, n, shift, hist, nblocks, full);
-        B2RT_LAUNCH_CHECK(ctx);
-    }
+    B2RT_LAUNCH_CHECK(ctx);
+    if (full && full < nblocks) ctx->launches++;
     return B2RT_OK;
 }
 
