@@ -210,6 +210,10 @@ __device__ __forceinline__ float box_area(const float *b) {
 
 // bottom-up refit + SAH leaf-collapse decision.  flag[i]: arrival counter.  collapse[i]=1 when the
 // whole subtree of internal i is cheaper as one leaf (count <= B2RT_LEAF_MAX).
+// The kernel is bound by the dependent round trips to L2 on the way to the root (1 M prims: ~40 levels), not by bytes: the
+// climbing thread keeps its own box and cost in registers and reads only its sibling's; the arrival counter, the parent,
+// the children and the range of a node are requested together (one round trip instead of four in a row).  Min / max and
+// cl + cr are commutative, so taking (mine, sibling) instead of (left, right) gives the same bits.
 __global__ void __launch_bounds__(256)
 refit_kernel(const float *__restrict__ leaf_box, const uint32_t *__restrict__ vals, int n,
              const int32_t *__restrict__ parent, const int32_t *__restrict__ child,
@@ -218,38 +222,44 @@ refit_kernel(const float *__restrict__ leaf_box, const uint32_t *__restrict__ va
     int j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= n) return;
     int node = (n - 1) + j;
+    float b[6], c_me;
     {
         const float *s = leaf_box + 6 * (int64_t)vals[j];
         float *d = box + 6 * (int64_t)node;
-        float b[6];
 #pragma unroll
         for (int a = 0; a < 6; ++a) { b[a] = s[a]; d[a] = b[a]; }
-        cost[node] = box_area(b);  // one prim, prim cost 1
+        c_me = box_area(b);  // one prim, prim cost 1
+        cost[node] = c_me;
     }
-    __threadfence();
     int cur = parent[node];
     while (cur >= 0) {
-        if (atomicAdd(&flag[cur], 1u) == 0u) return;  // first arriver leaves; second owns the node
+        const int2 ch = *reinterpret_cast<const int2 *>(child + 2 * (int64_t)cur);
+        const int2 rg = range[cur];
+        const int up = parent[cur];
+        __threadfence();                                   // my box / cost are visible before I announce myself
+        if (atomicAdd(&flag[cur], 1u) == 0u) return;       // first arriver leaves; second owns the node
         __threadfence();
-        int l = child[2 * cur], r = child[2 * cur + 1];
-        const volatile float *bl = box + 6 * (int64_t)l, *br = box + 6 * (int64_t)r;
-        float b[6];
+        const int sib = ch.x == node ? ch.y : ch.x;
+        const volatile float *bs = box + 6 * (int64_t)sib;
+        float sb[6];
 #pragma unroll
-        for (int a = 0; a < 3; ++a) { b[a] = fminf(bl[a], br[a]); b[3 + a] = fmaxf(bl[3 + a], br[3 + a]); }
+        for (int a = 0; a < 6; ++a) sb[a] = bs[a];
+        const float c_sib = ((const volatile float *)cost)[sib];
+#pragma unroll
+        for (int a = 0; a < 3; ++a) { b[a] = fminf(b[a], sb[a]); b[3 + a] = fmaxf(b[3 + a], sb[3 + a]); }
         float *d = box + 6 * (int64_t)cur;
 #pragma unroll
         for (int a = 0; a < 6; ++a) d[a] = b[a];
         float area = box_area(b);
-        float cl = ((const volatile float *)cost)[l], cr = ((const volatile float *)cost)[r];
-        float c_int = area + (cl + cr);  // node cost 1
-        int2 rg = range[cur];
+        float c_int = area + (c_me + c_sib);  // node cost 1
         int cnt = rg.y - rg.x + 1;
         float c_leaf = area * (float)cnt;
         bool col = (cnt <= B2RT_LEAF_MAX) && (c_leaf <= c_int);
         collapse[cur] = col ? 1 : 0;
-        cost[cur] = col ? c_leaf : c_int;
-        __threadfence();
-        cur = parent[cur];
+        c_me = col ? c_leaf : c_int;
+        cost[cur] = c_me;
+        node = cur;
+        cur = up;
     }
 }
 
