@@ -41,7 +41,7 @@ SYMBOLS = [
     "b2rt_create", "b2rt_destroy", "b2rt_last_error", "b2rt_device_count", "b2rt_add_mesh", "b2rt_add_sphere",
     "b2rt_add_disk", "b2rt_add_material", "b2rt_add_light", "b2rt_clear_scene", "b2rt_build_accel",
     "b2rt_accel_info_get", "b2rt_accel_download", "b2rt_trace_closest", "b2rt_trace_any", "b2rt_sort_pairs", "b2rt_sort_pairs_noalloc",
-    "b2rt_add_mesh_ex", "b2rt_add_sphere_ex", "b2rt_surface_at", "b2rt_object_begin", "b2rt_object_end", "b2rt_add_instance", "b2rt_instance_info", "b2rt_trace_stats", "b2rt_add_spot_light", "b2rt_add_distant_light", "b2rt_sync", "b2rt_timer_start", "b2rt_timer_stop", "b2rt_launch_count", "b2rt_stream", "b2rt_host_alloc", "b2rt_host_free",
+    "b2rt_add_mesh_ex", "b2rt_add_sphere_ex", "b2rt_surface_at", "b2rt_scene_save", "b2rt_scene_load", "b2rt_scene_counts", "b2rt_object_begin", "b2rt_object_end", "b2rt_add_instance", "b2rt_instance_info", "b2rt_trace_stats", "b2rt_add_spot_light", "b2rt_add_distant_light", "b2rt_sync", "b2rt_timer_start", "b2rt_timer_stop", "b2rt_launch_count", "b2rt_stream", "b2rt_host_alloc", "b2rt_host_free",
 ]
 
 _lib = None
@@ -236,6 +236,22 @@ class Context:
 
     def clear_scene(self):
         self._ck(self.lib.b2rt_clear_scene(self.h))
+
+    # ---- binary scene cache ---------------------------------------------------------------------------
+    def scene_save(self, path):
+        self.lib.b2rt_scene_save.argtypes = [C.c_void_p, C.c_char_p]
+        self._ck(self.lib.b2rt_scene_save(self.h, str(path).encode()))
+
+    def scene_load(self, path):
+        self.lib.b2rt_scene_load.argtypes = [C.c_void_p, C.c_char_p]
+        self._ck(self.lib.b2rt_scene_load(self.h, str(path).encode()))
+
+    def scene_counts(self):
+        """{items, lights, materials, objects, instances} staged in the context"""
+        c = (C.c_int32 * 5)()
+        self.lib.b2rt_scene_counts.argtypes = [C.c_void_p, C.c_void_p]
+        self._ck(self.lib.b2rt_scene_counts(self.h, c))
+        return dict(zip(("items", "lights", "materials", "objects", "instances"), list(c)))
 
     # ---- objects / instances (two-level BVH) ------------------------------------------------------
     def object_begin(self):

@@ -2,6 +2,7 @@
 // staging, buffer management; every compute step is a kernel in sort.cu / build.cu / trace.cu.
 // There is deliberately no CPU path: without a usable CUDA device b2rt_create fails.
 #include "b2rt_internal.cuh"
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 #include <math.h>
@@ -130,6 +131,104 @@ int b2rt_copy_staged_scene(const b2rt_ctx *src, b2rt_ctx *dst) {
     return B2RT_OK;
 }
 extern "C" {
+
+// ---- binary scene cache: the staged scene -> one file and back --------------------------------------
+// Layout: "B2RTSCN2", then the struct sizes (a cache written by another build of the library is refused), then one block
+// per context -- the top level first, then every object -- of length-prefixed arrays, then the instances.
+}  // extern "C"
+namespace {
+const char SCENE_MAGIC[8] = {'B', '2', 'R', 'T', 'S', 'C', 'N', '2'};
+template <typename T> bool put_vec(FILE *f, const std::vector<T> &v) {
+    const uint64_t n = v.size();
+    return fwrite(&n, 8, 1, f) == 1 && (n == 0 || fwrite(v.data(), sizeof(T), n, f) == n);
+}
+template <typename T> bool get_vec(FILE *f, std::vector<T> &v, uint64_t limit) {
+    uint64_t n = 0;
+    if (fread(&n, 8, 1, f) != 1 || n > limit) return false;
+    v.resize(n);
+    return n == 0 || fread(v.data(), sizeof(T), n, f) == n;
+}
+bool put_staging(FILE *f, const b2rt_ctx *c) {
+    const int32_t hdr[2] = {c->n_prims, c->any_attr ? 1 : 0};
+    return fwrite(hdr, 4, 2, f) == 2 && put_vec(f, c->h_verts) && put_vec(f, c->h_idx) && put_vec(f, c->h_tri_prim) &&
+           put_vec(f, c->h_vnormal) && put_vec(f, c->h_vuv) && put_vec(f, c->h_tri_flags) && put_vec(f, c->h_analytic) &&
+           put_vec(f, c->h_analytic_prim) && put_vec(f, c->h_analytic_type) && put_vec(f, c->h_prim_material) &&
+           put_vec(f, c->h_prim_light) && put_vec(f, c->h_materials) && put_vec(f, c->h_lights);
+}
+bool get_staging(FILE *f, b2rt_ctx *c) {
+    int32_t hdr[2];
+    const uint64_t L = 1ull << 33;
+    if (fread(hdr, 4, 2, f) != 2 || hdr[0] < 0) return false;
+    bool ok = get_vec(f, c->h_verts, L) && get_vec(f, c->h_idx, L) && get_vec(f, c->h_tri_prim, L) && get_vec(f, c->h_vnormal, L) &&
+              get_vec(f, c->h_vuv, L) && get_vec(f, c->h_tri_flags, L) && get_vec(f, c->h_analytic, L) &&
+              get_vec(f, c->h_analytic_prim, L) && get_vec(f, c->h_analytic_type, L) && get_vec(f, c->h_prim_material, L) &&
+              get_vec(f, c->h_prim_light, L) && get_vec(f, c->h_materials, L) && get_vec(f, c->h_lights, L);
+    if (!ok) return false;
+    c->n_prims = hdr[0]; c->any_attr = hdr[1] != 0; c->built = false;
+    // consistency: what the builder indexes must be in range
+    if (c->h_idx.size() != 3 * c->h_tri_prim.size() || c->h_prim_material.size() != (size_t)c->n_prims ||
+        c->h_prim_light.size() != (size_t)c->n_prims || c->h_analytic.size() != c->h_analytic_prim.size() ||
+        c->h_analytic.size() != c->h_analytic_type.size() || c->h_verts.size() % 3 != 0)
+        return false;
+    const int64_t nv = (int64_t)c->h_verts.size() / 3;
+    for (int32_t v : c->h_idx) if (v < 0 || v >= nv) return false;
+    for (int32_t q : c->h_tri_prim) if (q < 0 || q >= c->n_prims) return false;
+    for (int32_t q : c->h_analytic_prim) if (q < 0 || q >= c->n_prims) return false;
+    if (c->any_attr && (c->h_vnormal.size() != c->h_verts.size() || c->h_vuv.size() != 2 * (size_t)nv || c->h_tri_flags.size() != c->h_tri_prim.size()))
+        return false;
+    return true;
+}
+}  // namespace
+extern "C" {
+
+int b2rt_scene_counts(b2rt_ctx *ctx, int32_t counts[5]) {
+    if (!ctx || !counts) return B2RT_E_ARG;
+    counts[0] = ctx->n_prims; counts[1] = (int32_t)ctx->h_lights.size(); counts[2] = (int32_t)ctx->h_materials.size();
+    counts[3] = (int32_t)ctx->objects.size(); counts[4] = (int32_t)ctx->h_instances.size();
+    return B2RT_OK;
+}
+
+int b2rt_scene_save(b2rt_ctx *ctx, const char *path) {
+    if (!ctx || !path) return B2RT_E_ARG;
+    if (ctx->cur_object) { ctx->err = "scene_save: b2rt_object_end is missing"; return B2RT_E_STATE; }
+    FILE *f = fopen(path, "wb");
+    if (!f) { ctx->err = std::string("scene_save: cannot open ") + path; return B2RT_E_ARG; }
+    const uint32_t sizes[4] = {(uint32_t)sizeof(AnalyticPrim), (uint32_t)sizeof(Material), (uint32_t)sizeof(Light), (uint32_t)sizeof(b2rt_ctx::HostInstance)};
+    const uint64_t nobj = ctx->objects.size();
+    bool ok = fwrite(SCENE_MAGIC, 1, 8, f) == 8 && fwrite(sizes, 4, 4, f) == 4 && put_staging(f, ctx) && fwrite(&nobj, 8, 1, f) == 1;
+    for (size_t o = 0; ok && o < ctx->objects.size(); ++o) ok = put_staging(f, ctx->objects[o]);
+    ok = ok && put_vec(f, ctx->h_instances);
+    ok = (fclose(f) == 0) && ok;
+    if (!ok) { ctx->err = std::string("scene_save: write to ") + path + " failed"; return B2RT_E_ARG; }
+    return B2RT_OK;
+}
+
+int b2rt_scene_load(b2rt_ctx *ctx, const char *path) {
+    if (!ctx || !path) return B2RT_E_ARG;
+    if (ctx->parent) { ctx->err = "scene_load: not on an object"; return B2RT_E_STATE; }
+    FILE *f = fopen(path, "rb");
+    if (!f) { ctx->err = std::string("scene_load: cannot open ") + path; return B2RT_E_ARG; }
+    char magic[8]; uint32_t sizes[4]; uint64_t nobj = 0;
+    const uint32_t want[4] = {(uint32_t)sizeof(AnalyticPrim), (uint32_t)sizeof(Material), (uint32_t)sizeof(Light), (uint32_t)sizeof(b2rt_ctx::HostInstance)};
+    bool ok = fread(magic, 1, 8, f) == 8 && memcmp(magic, SCENE_MAGIC, 8) == 0 && fread(sizes, 4, 4, f) == 4 && memcmp(sizes, want, 16) == 0;
+    if (!ok) { fclose(f); ctx->err = std::string("scene_load: ") + path + " is not a scene cache of this library build"; return B2RT_E_ARG; }
+    b2rt_clear_scene(ctx);
+    ok = get_staging(f, ctx) && fread(&nobj, 8, 1, f) == 1 && nobj < (1u << 24);
+    for (uint64_t o = 0; ok && o < nobj; ++o) {
+        b2rt_ctx *c = new_object(ctx);
+        if (!c) { fclose(f); return B2RT_E_CUDA; }
+        ctx->objects.push_back(c);
+        ok = get_staging(f, c);
+    }
+    ok = ok && get_vec(f, ctx->h_instances, 1ull << 28);
+    fclose(f);
+    for (size_t k = 0; ok && k < ctx->h_instances.size(); ++k) {
+        const b2rt_ctx::HostInstance &H = ctx->h_instances[k];
+        ok = H.object >= 0 && (size_t)H.object < ctx->objects.size() && H.item >= 0 && H.item < ctx->n_prims && ctx->objects[H.object]->n_prims > 0;
+    }
+    if (!ok) { b2rt_clear_scene(ctx); ctx->err = std::string("scene_load: ") + path + " is truncated or inconsistent"; return B2RT_E_ARG; }
+    return B2RT_OK;
+}
 
 int b2rt_object_begin(b2rt_ctx *ctx, int32_t *object_id) {
     if (!ctx) return B2RT_E_ARG;

@@ -120,6 +120,16 @@ int b2rt_object_end(b2rt_ctx *ctx);
 int b2rt_add_instance(b2rt_ctx *ctx, int32_t object_id, const float o2w[12], const float *w2o, int32_t *instance_id);
 int b2rt_instance_info(b2rt_ctx *ctx, int32_t instance_id, int32_t *first_prim, int32_t *n_prims, int32_t *object_id);
 
+/* ---- binary scene cache (the reference has none: every run goes through pbrt's text parser).
+ * b2rt_scene_save writes everything staged so far -- meshes with their attributes, spheres / disks, objects and instances,
+ * materials, lights -- to one file; b2rt_scene_load replaces the staged scene by the file's (then b2rt_build_accel as
+ * usual).  The trees are not stored: the build is deterministic and takes milliseconds.  A file written by a library
+ * build with other struct layouts is refused. */
+int b2rt_scene_save(b2rt_ctx *ctx, const char *path);
+int b2rt_scene_load(b2rt_ctx *ctx, const char *path);
+/* what is staged: counts = {top-level items (primitives + instances), lights, materials, objects, instances} */
+int b2rt_scene_counts(b2rt_ctx *ctx, int32_t counts[5]);
+
 /* ---- acceleration structure: replaces OptiX "Sbvh"/"Bvh" (cudarender.cpp:44,50) ---------------- */
 int b2rt_build_accel(b2rt_ctx *ctx);
 int b2rt_accel_info_get(b2rt_ctx *ctx, b2rt_accel_info *info);

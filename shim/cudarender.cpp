@@ -310,9 +310,19 @@ void CudaRender::objectInstance(std::vector<Reference<Primitive> > *key, const T
     check(b2rt_add_instance(ctx_, object, o2w, w2o, NULL), "b2rt_add_instance");
 }
 
+void CudaRenderer::cacheParams(const ParamSet &params) {
+    saveScene = params.FindOneString("savescene", "");
+    loadScene = params.FindOneString("loadscene", "");
+}
+
 void CudaRender::Render(const Scene *scene) {
+    const bool fromCache = !renderer_->loadScene.empty();
+    if (fromCache) {
+        Info("CudaRender: scene from the cache %s (shapes and lights of the scene file are ignored)", renderer_->loadScene.c_str());
+        check(b2rt_scene_load(ctx_, renderer_->loadScene.c_str()), "b2rt_scene_load");
+    }
     // lights, in scene->lights order so that ids agree with the lightIndex api.cpp passed for area-light shapes
-    for (size_t i = 0; i < scene->lights.size(); ++i) {
+    for (size_t i = 0; !fromCache && i < scene->lights.size(); ++i) {
         const Light *l = scene->lights[i];
         float rgb[3], p[3] = {0, 0, 0};
         int id = -1;
@@ -348,6 +358,10 @@ void CudaRender::Render(const Scene *scene) {
             rgb[0] = rgb[1] = rgb[2] = 0.f;
             check(b2rt_add_light(ctx_, B2RT_LIGHT_POINT, p, rgb, -1, 1, &id), "b2rt_add_light");
         }
+    }
+    if (!renderer_->saveScene.empty()) {
+        check(b2rt_scene_save(ctx_, renderer_->saveScene.c_str()), "b2rt_scene_save");
+        Info("CudaRender: scene cache written to %s", renderer_->saveScene.c_str());
     }
     if (renderer_->gpus > 1) {
         // the other GPUs get a copy of the scene, lights and materials staged in the first context
@@ -469,7 +483,7 @@ static b2rt_frame_params frameParams(const b2rt_camera &cam, Sampler *sampler) {
     return fp;
 }
 
-SimpleRenderer::SimpleRenderer(const ParamSet &params) { gpus = gpusParam(params); }
+SimpleRenderer::SimpleRenderer(const ParamSet &params) { gpus = gpusParam(params); cacheParams(params); }
 
 void SimpleRenderer::render(const Scene *, CudaRender *cr, Camera *camera) {
     b2rt_camera cam = probeCamera(camera);
@@ -501,11 +515,14 @@ PhotonMappingRenderer::PhotonMappingRenderer(const ParamSet &params) {
     if (PbrtOptions.quickRender) gatherSamples = max(1, gatherSamples / 4);   // photonmap.cpp:795
     gatherAngle = params.FindOneFloat("gatherangle", 10.f);
     gpus = gpusParam(params);
+    cacheParams(params);
 }
 
 void PhotonMappingRenderer::render(const Scene *scene, CudaRender *cr, Camera *camera) {
     b2rt_multi *mg = cr->multi();
-    if (scene->lights.size() > 0 && (nCaustic > 0 || nIndirect > 0)) {
+    int32_t counts[5] = {0, 0, 0, 0, 0};
+    cr->check(b2rt_scene_counts(b2rt_multi_ctx(mg, 0), counts), "b2rt_scene_counts");     // the lights may come from a scene cache
+    if (counts[1] > 0 && (nCaustic > 0 || nIndirect > 0)) {
         int64_t paths[2], stored[2];
         int64_t batch = 262144;           // the same for every GPU count: the stopping rule counts whole batches, and the
                                           // image must not depend on "gpus"

@@ -22,6 +22,11 @@ public:
     CudaRenderer() : gpus(1) {}
     virtual ~CudaRenderer() {}
     int gpus;            // "integer gpus" of the Renderer line (default: $B2RT_GPUS, else 1; <= 0: every visible GPU)
+    // binary scene cache: "string savescene" writes what the parse staged (shapes, instances, materials,
+    // lights) to a file; "string loadscene" renders THAT scene instead of the parsed one, so a stub file with camera, film,
+    // sampler and the Renderer line starts without pbrt's text parser touching a single triangle
+    std::string saveScene, loadScene;
+    void cacheParams(const ParamSet &params);
     virtual void render(const Scene *scene, CudaRender *cudarender, Camera *camera) = 0;
 };
 

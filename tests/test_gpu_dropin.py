@@ -232,3 +232,24 @@ def test_dropin_partial_sphere(tmp_path):
     _, cpu_full = _run(tmp_path, "ball", integ, "simple", spp=64, res=96, desc=desc, extra_world=full)
     mf = S.image_metrics(_block(gpu, 4), _block(cpu_full, 4))
     assert mf["mean_rel"] > 3 * m["mean_rel"], (m, mf)                 # and it is not the full sphere
+
+
+@pytest.mark.skipif(not os.path.exists(BIN), reason="shim/_build/pbrt_b2rt not built (needs /root/reference)")
+def test_dropin_scene_cache(tmp_path):
+    """`Renderer "photonmap" "string savescene"` writes the parsed scene (instances, materials, area light) to a cache;
+    a stub file with no shapes and `"string loadscene"` renders it again without the text parser seeing a triangle: same PFM"""
+    prm = '"integer causticphotons" [2000] "integer indirectphotons" [50000] "integer nused" [50] "float maxdist" [0.4] "bool finalgather" ["false"]'
+    cache = str(tmp_path / "scene.b2rt")
+    out = []
+    for tag, desc, extra, rp in (("full", S.cornell_scene(spheres=True), _instanced_world(), '"string savescene" ["%s"]' % cache),
+                                 ("stub", {"materials": [], "shapes": [], "lights": []}, "", '"string loadscene" ["%s"]' % cache)):
+        pf = str(tmp_path / (tag + ".pfm"))
+        scene = str(tmp_path / (tag + ".pbrt"))
+        with open(scene, "w") as f:
+            f.write(S.to_pbrt(desc, EYE, LOOK, UP, FOV, 96, 96, 4, 'SurfaceIntegrator "photonmap" ' + prm, pf,
+                              renderer='Renderer "photonmap" %s %s' % (rp, prm), extra_world=extra))
+        r = subprocess.run([BIN, "--quiet", "-c", scene], capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stderr[-2000:]
+        out.append(S.read_pfm(pf))
+    assert os.path.getsize(cache) > 4000 and os.path.getsize(str(tmp_path / "stub.pbrt")) < 2000
+    assert out[0].max() > 0 and np.array_equal(out[0], out[1])

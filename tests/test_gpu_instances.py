@@ -175,3 +175,38 @@ def test_instance_api_errors(built):
         c.clear_scene()
         c.add_mesh(P, idx); c.build_accel()
         assert (c.trace_closest(r)["prim"] >= 0).any()
+
+
+def test_scene_cache_round_trip(built, tmp_path):
+    """b2rt_scene_save / b2rt_scene_load: a scene with attribute meshes, analytic shapes, objects, instances, materials and a
+    light goes to a file and comes back into a fresh context; hits, photon maps and frame are the same bytes"""
+    desc = S.instanced_scene(n_inst=6, seed=21)
+    cam = b2rt.pbrt_camera((0.5, 3.0, 7.0), (0.0, 0.0, 0.0), (0.0, 1.0, 0.0), 50.0, 64, 48)
+    r = S.incoherent_rays(20000, [-4, -1, -4], [4, 2, 4], seed=2)
+    path = str(tmp_path / "scene.b2rt")
+
+    def run(c):
+        c.build_accel()
+        h = c.trace_closest(r)
+        c.photons_trace(0, 50000)
+        ph = c.photons_download(1).tobytes()
+        c.grid_build(1)
+        return h.tobytes(), ph, c.render_frame(cam, spp=2, nused=20, max_dist=0.5).tobytes()
+
+    with b2rt.Context(0, seed=5) as c:
+        red = c.add_material(b2rt.MAT_MATTE, (0.7, 0.2, 0.2))
+        S.fill_instanced(c, desc)
+        c.add_sphere(S.xf_translate(0.3, 0.6, 2.0)[0], 0.4, material=red, zmax=0.2)
+        c.add_light(0, (60.0, 60.0, 60.0), p=(0.5, 4.5, 1.0))
+        c.scene_save(path)
+        want = run(c)
+    with b2rt.Context(0, seed=5) as c:
+        c.add_mesh(*S.heightfield_mesh(4, 4, None, seed=1))         # replaced by the load
+        c.scene_load(path)
+        assert c.scene_counts() == {"items": len(desc["world"][0][2]) + 1 + 6 + 1, "lights": 1, "materials": 1, "objects": 2, "instances": 6}
+        assert run(c) == want
+        with pytest.raises(b2rt.B2rtError):
+            c.scene_load(str(tmp_path / "missing.b2rt"))
+        open(str(tmp_path / "bad.b2rt"), "wb").write(open(path, "rb").read()[:1000])
+        with pytest.raises(b2rt.B2rtError):
+            c.scene_load(str(tmp_path / "bad.b2rt"))
