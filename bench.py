@@ -55,9 +55,9 @@ _TV = os.environ.get("B2RT_TRACE_VARIANT", "2")
 TRACE_KERNEL = {"0": "trace_kernel<closest>", "1": "trace_persistent_kernel<closest>"}.get(_TV, "trace_spec_kernel<closest>")
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the default closest-hit kernel on this exact workload,
 # from the ncu --set full capture of `bench.py --steps 2 --warmup 3` (profiles/r01h_ncu_trace.md, re-captured r01m and
-# r02m, profiles/r02m_ncu_full_summary.md): 135-136 MB read + 26 MB written, against 99.5 MB of compulsory ray / hit bytes (the difference is the cold 52 MB scene).
-TRAFFIC_BYTES = 161.8e6 if _TV == "2" else None
-TRAFFIC_SOURCE = "ncu --set full, r02m capture (profiles/r02m_ncu_full_summary.md): dram read 135 MB + write 26 MB per launch"
+# r07a, profiles/r07a_ncu_trace_full_summary.md; r02m had 135-136 + 26): 135 MB read + 24.1 MB written, against 99.5 MB of compulsory ray / hit bytes (the difference is the cold 52 MB scene).
+TRAFFIC_BYTES = 159.1e6 if _TV == "2" else None
+TRAFFIC_SOURCE = "ncu --set full, r07a capture (profiles/r07a_ncu_trace_full_summary.md): dram read 135 MB + write 24.1 MB per launch"
 METRIC = "Mrays/s (closest-hit primary + any-hit shadow rays, 1M-triangle scene, 1920x1080, 1 spp)"
 LIGHT = (0.5, 3.0, 0.5)
 
