@@ -41,7 +41,7 @@ SYMBOLS = [
     "b2rt_create", "b2rt_destroy", "b2rt_last_error", "b2rt_device_count", "b2rt_add_mesh", "b2rt_add_sphere",
     "b2rt_add_disk", "b2rt_add_material", "b2rt_add_light", "b2rt_clear_scene", "b2rt_build_accel",
     "b2rt_accel_info_get", "b2rt_accel_download", "b2rt_trace_closest", "b2rt_trace_any", "b2rt_sort_pairs", "b2rt_sort_pairs_noalloc",
-    "b2rt_add_mesh_ex", "b2rt_add_sphere_ex", "b2rt_surface_at", "b2rt_scene_save", "b2rt_scene_load", "b2rt_scene_counts", "b2rt_object_begin", "b2rt_object_end", "b2rt_add_instance", "b2rt_instance_info", "b2rt_trace_stats", "b2rt_add_spot_light", "b2rt_add_distant_light", "b2rt_sync", "b2rt_timer_start", "b2rt_timer_stop", "b2rt_launch_count", "b2rt_stream", "b2rt_host_alloc", "b2rt_host_free",
+    "b2rt_add_mesh_ex", "b2rt_add_sphere_ex", "b2rt_surface_at", "b2rt_scene_save", "b2rt_scene_load", "b2rt_scene_counts", "b2rt_timings_enable", "b2rt_get_timings", "b2rt_object_begin", "b2rt_object_end", "b2rt_add_instance", "b2rt_instance_info", "b2rt_trace_stats", "b2rt_add_spot_light", "b2rt_add_distant_light", "b2rt_sync", "b2rt_timer_start", "b2rt_timer_stop", "b2rt_launch_count", "b2rt_stream", "b2rt_host_alloc", "b2rt_host_free",
 ]
 
 _lib = None
@@ -236,6 +236,22 @@ class Context:
 
     def clear_scene(self):
         self._ck(self.lib.b2rt_clear_scene(self.h))
+
+    # ---- per-stage device times ------------------------------------------------------------------------
+    STAGES = ("build", "trace_closest", "trace_any", "photons", "grid", "gather", "render", "film")
+
+    def timings_enable(self, on=True):
+        self.lib.b2rt_timings_enable.argtypes = [C.c_void_p, C.c_int]
+        self._ck(self.lib.b2rt_timings_enable(self.h, 1 if on else 0))
+
+    def timings(self, reset=False):
+        """{stage: (device ms, calls)} accumulated while timings were enabled (b2rt_get_timings)"""
+        class T(C.Structure):
+            _fields_ = [("ms", C.c_double * 8), ("calls", C.c_int64 * 8)]
+        t = T()
+        self.lib.b2rt_get_timings.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
+        self._ck(self.lib.b2rt_get_timings(self.h, C.byref(t), 1 if reset else 0))
+        return {n: (t.ms[i], t.calls[i]) for i, n in enumerate(self.STAGES)}
 
     # ---- binary scene cache ---------------------------------------------------------------------------
     def scene_save(self, path):

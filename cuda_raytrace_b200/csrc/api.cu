@@ -79,6 +79,8 @@ int b2rt_create(int device, uint64_t seed, b2rt_ctx **out) {
     CK(cudaEventCreateWithFlags(&ctx->ev_in, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&ctx->ev_k, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&ctx->ev_out, cudaEventDisableTiming));
+    CK(cudaEventCreate(&ctx->ev_s0)); CK(cudaEventCreate(&ctx->ev_s1));
+    if (const char *v = getenv("B2RT_TIMINGS")) ctx->timings_on = atoi(v) != 0;
     CK(ctx->d_counters.reserve(256));
     CK(cudaMemsetAsync(ctx->d_counters.p, 0, 256, ctx->stream));
 #undef CK
@@ -288,6 +290,7 @@ void b2rt_destroy(b2rt_ctx *ctx) {
     cudaEventDestroy(ctx->ev0); cudaEventDestroy(ctx->ev1);
     cudaEventDestroy(ctx->evb0); cudaEventDestroy(ctx->evb1); cudaEventDestroy(ctx->evb_mid);
     cudaEventDestroy(ctx->ev_in); cudaEventDestroy(ctx->ev_k); cudaEventDestroy(ctx->ev_out);
+    cudaEventDestroy(ctx->ev_s0); cudaEventDestroy(ctx->ev_s1);
     cudaStreamDestroy(ctx->stream_in); cudaStreamDestroy(ctx->stream_out);
     cudaStreamDestroy(ctx->stream);
     for (b2rt_ctx *c : ctx->objects) destroy_object(c);
@@ -463,8 +466,22 @@ int b2rt_add_distant_light(b2rt_ctx *ctx, const float dir_to_light[3], const flo
     return B2RT_OK;
 }
 
+int b2rt_timings_enable(b2rt_ctx *ctx, int on) {
+    if (!ctx) return B2RT_E_ARG;
+    ctx->timings_on = on != 0;
+    return B2RT_OK;
+}
+
+int b2rt_get_timings(b2rt_ctx *ctx, b2rt_timings *out, int reset) {
+    if (!ctx || !out) return B2RT_E_ARG;
+    *out = ctx->timings;
+    if (reset) ctx->timings = b2rt_timings{};
+    return B2RT_OK;
+}
+
 int b2rt_build_accel(b2rt_ctx *ctx) {
     if (!ctx) return B2RT_E_ARG;
+    B2RT_STAGE(ctx, B2RT_STAGE_BUILD);
     B2RT_CUDA(ctx, cudaSetDevice(ctx->device));
     int rc = b2rt_build_impl(ctx);
     if (rc) return rc;
@@ -567,9 +584,11 @@ static int trace_common(b2rt_ctx *ctx, int64_t nrays, const b2rt_ray *rays, b2rt
 }
 
 int b2rt_trace_closest(b2rt_ctx *ctx, int64_t nrays, const b2rt_ray *rays, b2rt_hit *hits, int where) {
+    B2RT_STAGE(ctx, B2RT_STAGE_TRACE_CLOSEST);
     return trace_common(ctx, nrays, rays, hits, nullptr, where, false);
 }
 int b2rt_trace_any(b2rt_ctx *ctx, int64_t nrays, const b2rt_ray *rays, uint8_t *occluded, int where) {
+    B2RT_STAGE(ctx, B2RT_STAGE_TRACE_ANY);
     return trace_common(ctx, nrays, rays, nullptr, occluded, where, true);
 }
 

@@ -36,6 +36,7 @@ int b2rt_photons_clear(b2rt_ctx *ctx) {
 int b2rt_photons_trace(b2rt_ctx *ctx, int64_t first_path, int64_t n_paths, int32_t max_depth, int32_t flags,
                        int64_t n_stored[2]) {
     if (!ctx) return B2RT_E_ARG;
+    B2RT_STAGE(ctx, B2RT_STAGE_PHOTONS);
     if (first_path < 0 || n_paths < 0 || max_depth < 1 || max_depth > 64 || !(flags & 3)) {
         ctx->err = "photons_trace: bad arguments"; return B2RT_E_ARG;
     }
@@ -51,6 +52,7 @@ int b2rt_photons_trace(b2rt_ctx *ctx, int64_t first_path, int64_t n_paths, int32
 int b2rt_photons_shoot(b2rt_ctx *ctx, int64_t n_caustic_wanted, int64_t n_indirect_wanted, int32_t max_depth,
                        int64_t batch_paths, int64_t n_paths_out[2], int64_t n_stored_out[2]) {
     if (!ctx) return B2RT_E_ARG;
+    B2RT_STAGE(ctx, B2RT_STAGE_PHOTONS);
     if (n_caustic_wanted < 0 || n_indirect_wanted < 0 || batch_paths <= 0) { ctx->err = "photons_shoot: bad arguments"; return B2RT_E_ARG; }
     int rc = b2rt_photons_clear(ctx);
     if (rc) return rc;
@@ -135,6 +137,7 @@ void *b2rt_photons_device_ptr(b2rt_ctx *ctx, int32_t map) {
 
 int b2rt_photon_grid_build(b2rt_ctx *ctx, int32_t map, float cell_size, float target_per_cell) {
     if (!ctx) return B2RT_E_ARG;
+    B2RT_STAGE(ctx, B2RT_STAGE_GRID);
     int rc = check_map(ctx, map, "photon_grid_build");
     if (rc) return rc;
     if (ctx->maps[map].n >= (1ll << 32)) { ctx->err = "photon_grid_build: more than 2^32 photons"; return B2RT_E_ARG; }
@@ -207,18 +210,21 @@ static int gather_common(b2rt_ctx *ctx, int32_t map, int64_t nq, const b2rt_quer
 
 int b2rt_gather(b2rt_ctx *ctx, int32_t map, int64_t nqueries, const b2rt_query *queries, int32_t k, float max_dist2,
                 float *out_rgb, float *out_radius2, int32_t *out_found, int where) {
+    B2RT_STAGE(ctx, B2RT_STAGE_GATHER);
     return gather_common(ctx, map, nqueries, queries, k, max_dist2, out_rgb, out_radius2, out_found, nullptr, where);
 }
 
 int b2rt_gather_sets(b2rt_ctx *ctx, int32_t map, int64_t nqueries, const b2rt_query *queries, int32_t k,
                      float max_dist2, int32_t *idx_out, int where) {
     if (ctx && !idx_out) { ctx->err = "gather_sets: idx_out is NULL"; return B2RT_E_ARG; }
+    B2RT_STAGE(ctx, B2RT_STAGE_GATHER);
     return gather_common(ctx, map, nqueries, queries, k, max_dist2, nullptr, nullptr, nullptr, idx_out, where);
 }
 
 // ---- final gathering (finalgather.cu) ----------------------------------------------------------------------------------
 int b2rt_photons_trace_fg(b2rt_ctx *ctx, int64_t first_path, int64_t n_paths, int32_t max_depth, int64_t n_stored[2]) {
     if (!ctx) return B2RT_E_ARG;
+    B2RT_STAGE(ctx, B2RT_STAGE_PHOTONS);
     if (first_path < 0 || n_paths < 0 || max_depth < 1 || max_depth > 64) { ctx->err = "photons_trace_fg: bad arguments"; return B2RT_E_ARG; }
     int rc = need_built(ctx, "photons_trace_fg");
     if (rc) return rc;
@@ -232,6 +238,7 @@ int b2rt_photons_trace_fg(b2rt_ctx *ctx, int64_t first_path, int64_t n_paths, in
 int b2rt_irradiance(b2rt_ctx *ctx, int32_t map, int64_t nq, const b2rt_query *queries, int32_t k, float max_dist2,
                     float *out_E, int where) {
     if (!ctx) return B2RT_E_ARG;
+    B2RT_STAGE(ctx, B2RT_STAGE_GATHER);
     int rc = check_map(ctx, map, "irradiance");
     if (rc) return rc;
     if (nq < 0 || (nq && (!queries || !out_E)) || !(max_dist2 > 0.f) || k < 1 || k > 224) {
@@ -256,6 +263,7 @@ int b2rt_irradiance(b2rt_ctx *ctx, int32_t map, int64_t nq, const b2rt_query *qu
 
 int b2rt_radiance_compute(b2rt_ctx *ctx, int32_t nused, float max_dist2) {
     if (!ctx) return B2RT_E_ARG;
+    B2RT_STAGE(ctx, B2RT_STAGE_GRID);
     if (nused < 1 || nused > 224 || !(max_dist2 > 0.f)) { ctx->err = "radiance_compute: bad arguments (1 <= nused <= 224)"; return B2RT_E_ARG; }
     B2RT_CUDA(ctx, cudaSetDevice(ctx->device));
     int rc = b2rt_radiance_compute_impl(ctx, nused, max_dist2);
@@ -266,6 +274,7 @@ int b2rt_radiance_compute(b2rt_ctx *ctx, int32_t nused, float max_dist2) {
 
 int b2rt_radiance_lookup(b2rt_ctx *ctx, int64_t nq, const b2rt_query *queries, float *out_rgb, int32_t *out_idx, int where) {
     if (!ctx) return B2RT_E_ARG;
+    B2RT_STAGE(ctx, B2RT_STAGE_GATHER);
     if (nq < 0 || (nq && !queries)) { ctx->err = "radiance_lookup: bad arguments"; return B2RT_E_ARG; }
     PhotonMap &m = ctx->maps[B2RT_MAP_RADIANCE];
     if (!m.grid_built) { ctx->err = "radiance_lookup: the radiance-photon grid is not built (b2rt_radiance_compute)"; return B2RT_E_STATE; }
@@ -288,6 +297,7 @@ int b2rt_radiance_lookup(b2rt_ctx *ctx, int64_t nq, const b2rt_query *queries, f
 
 int b2rt_final_gather(b2rt_ctx *ctx, int64_t nq, const b2rt_query *queries, float max_dist2, float *out_rgb, int where) {
     if (!ctx) return B2RT_E_ARG;
+    B2RT_STAGE(ctx, B2RT_STAGE_GATHER);
     if (nq < 0 || (nq && (!queries || !out_rgb)) || !(max_dist2 > 0.f)) { ctx->err = "final_gather: bad arguments"; return B2RT_E_ARG; }
     int rc = need_built(ctx, "final_gather");
     if (rc) return rc;
@@ -336,6 +346,7 @@ int b2rt_final_gather_set(b2rt_ctx *ctx, int32_t enable, int32_t gather_samples,
 
 int b2rt_surface_at(b2rt_ctx *ctx, int64_t nrays, const b2rt_ray *rays, b2rt_surface *out, int where) {
     if (!ctx) return B2RT_E_ARG;
+    B2RT_STAGE(ctx, B2RT_STAGE_RENDER);
     if (nrays < 0 || (nrays && (!rays || !out))) { ctx->err = "surface_at: bad arguments"; return B2RT_E_ARG; }
     int rc = need_built(ctx, "surface_at");
     if (rc || nrays == 0) return rc;
@@ -359,6 +370,7 @@ int b2rt_surface_at(b2rt_ctx *ctx, int64_t nrays, const b2rt_ray *rays, b2rt_sur
 int b2rt_camera_samples(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_params *fp, float *out_rgb, uint32_t *out_nleaves,
                         b2rt_query *out_queries, int32_t *slots_out) {
     if (!ctx) return B2RT_E_ARG;
+    B2RT_STAGE(ctx, B2RT_STAGE_RENDER);
     if (!cam || !fp || !out_rgb || !out_nleaves || fp->spp < 1 || fp->x0 < 0 || fp->y0 < 0 || fp->x1 > cam->xres ||
         fp->y1 > cam->yres || fp->x0 >= fp->x1 || fp->y0 >= fp->y1) { ctx->err = "camera_samples: bad arguments"; return B2RT_E_ARG; }
     int rc = need_built(ctx, "camera_samples");
@@ -382,6 +394,7 @@ int b2rt_camera_samples(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_
 
 int b2rt_render_frame(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_frame_params *fp, float *out_rgb, int where) {
     if (!ctx) return B2RT_E_ARG;
+    B2RT_STAGE(ctx, B2RT_STAGE_RENDER);
     if (!cam || !fp || !out_rgb || fp->spp < 1 || fp->x0 < 0 || fp->y0 < 0 || fp->x1 > cam->xres || fp->y1 > cam->yres ||
         fp->x0 >= fp->x1 || fp->y0 >= fp->y1 || fp->nused > 224 || !(fp->max_dist2 > 0.f)) {
         ctx->err = "render_frame: bad arguments"; return B2RT_E_ARG;

@@ -5,6 +5,7 @@
 #include <string>
 #include <vector>
 #include "b2rt.h"
+#include <nvtx3/nvToolsExt.h>
 
 #define B2RT_SM_COUNT_DEFAULT 148
 
@@ -229,7 +230,34 @@ struct b2rt_ctx {
     uint64_t fg_tables_epoch = 0;                       // grid_epoch of maps[3] the tables above were built for (0 = none)
     DevBuf d_fg_rayrec, d_fg_rkeys, d_fg_rvals, d_fg_rkeys2, d_fg_rvals2, d_fg_ri;   // split gather pipeline, per gather ray
     b2rt_accel_info info{};
+    // b2rt_get_timings: accumulated device time per stage while timings_on (StageScope)
+    bool timings_on = false;
+    int stage_depth = 0;                                // entry points call each other (shoot -> trace): only the outermost counts
+    cudaEvent_t ev_s0 = nullptr, ev_s1 = nullptr;
+    b2rt_timings timings{};
 };
+
+// NVTX range + (optionally) CUDA-event timing of one stage entry point
+struct StageScope {
+    b2rt_ctx *ctx; int stage; bool timed;
+    StageScope(b2rt_ctx *c, int s, const char *name) : ctx(c), stage(s), timed(false) {
+        nvtxRangePushA(name);
+        if (!ctx) return;
+        if (ctx->stage_depth++ == 0 && ctx->timings_on && ctx->ev_s0 && cudaSetDevice(ctx->device) == cudaSuccess)
+            timed = cudaEventRecord(ctx->ev_s0, ctx->stream) == cudaSuccess;
+    }
+    ~StageScope() {
+        if (ctx) {
+            --ctx->stage_depth;
+            if (timed && cudaEventRecord(ctx->ev_s1, ctx->stream) == cudaSuccess && cudaEventSynchronize(ctx->ev_s1) == cudaSuccess) {
+                float ms = 0.f;
+                if (cudaEventElapsedTime(&ms, ctx->ev_s0, ctx->ev_s1) == cudaSuccess) { ctx->timings.ms[stage] += ms; ctx->timings.calls[stage]++; }
+            }
+        }
+        nvtxRangePop();
+    }
+};
+#define B2RT_STAGE(ctx, stage) StageScope stage_scope__((ctx), (stage), __func__)
 
 #define B2RT_CUDA(ctx, call)                                                              \
     do {                                                                                  \

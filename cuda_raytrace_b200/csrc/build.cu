@@ -270,43 +270,8 @@ __device__ __forceinline__ bool is_openable(int node, int n, const uint8_t *coll
     return node < n - 1 && !collapse[node];
 }
 
-// one thread per wide root in the current level's queue
-__global__ void __launch_bounds__(128)
-wide_collapse_level_kernel(const int32_t *__restrict__ queue_in, int nq, int n,
-                           const int32_t *__restrict__ child, const float *__restrict__ box,
-                           const uint8_t *__restrict__ collapse, WideTmp *__restrict__ tmp,
-                           uint32_t *__restrict__ wide_flag, int32_t *__restrict__ queue_out,
-                           uint32_t *__restrict__ out_count) {
-    int qi = blockIdx.x * blockDim.x + threadIdx.x;
-    if (qi >= nq) return;
-    int root = queue_in[qi];
-    int c[4]; int m = 2;
-    c[0] = child[2 * root]; c[1] = child[2 * root + 1]; c[2] = -1; c[3] = -1;
-    while (m < 4) {
-        int best = -1; float best_area = -1.f;
-        for (int k = 0; k < m; ++k) {
-            if (!is_openable(c[k], n, collapse)) continue;
-            float a = box_area(box + 6 * (int64_t)c[k]);
-            if (a > best_area) { best_area = a; best = k; }   // first max wins: deterministic
-        }
-        if (best < 0) break;
-        int node = c[best];
-        // keep order: left child takes the slot, right child is inserted right after it
-        for (int k = m; k > best + 1; --k) c[k] = c[k - 1];
-        c[best] = child[2 * node]; c[best + 1] = child[2 * node + 1];
-        ++m;
-    }
-    WideTmp t;
-#pragma unroll
-    for (int k = 0; k < 4; ++k) t.c[k] = c[k];
-    tmp[root] = t;
-    wide_flag[root] = 1u;
-    for (int k = 0; k < m; ++k)
-        if (is_openable(c[k], n, collapse)) queue_out[atomicAdd(out_count, 1u)] = c[k];
-}
-
-// The same collapse without the host: ONE cooperative launch walks the levels itself, grid.sync() between them.  The
-// level-synchronous host loop cost one launch, one 4-byte download and one stream synchronisation per level (15 levels
+// The collapse without the host: ONE cooperative launch walks the levels itself, grid.sync() between them (one thread per
+// wide root of the level's queue).  The level-synchronous host loop of round 1 (one launch per level) cost one launch, one 4-byte download and one stream synchronisation per level (15 levels
 // for the 1 M-triangle scene).  A first device-side version (r04c) used a single work queue with a ticket, a tail and a
 // pending counter: three same-address atomics per wide node, 568 us for 266 k nodes -- slower than the host loop.  Here the
 // only shared counter is the next level's queue tail, bumped once per warp (ballot + prefix over the lanes' child counts).

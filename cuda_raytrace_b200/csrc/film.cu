@@ -279,6 +279,7 @@ int b2rt_sample_positions(b2rt_ctx *ctx, int32_t xres, int32_t yres, const int32
 int b2rt_film_reconstruct(b2rt_ctx *ctx, const b2rt_filter *f, const int32_t cells[4], int32_t spp, const float *xy,
                           const float *rgb, const int32_t pixels[4], float *out_rgb, int where) {
     if (!ctx) return B2RT_E_ARG;
+    B2RT_STAGE(ctx, B2RT_STAGE_FILM);
     if (!b2rt_filter_valid(f) || !cells || !pixels || spp < 1 || !xy || !rgb || !out_rgb || cells[0] >= cells[2] ||
         cells[1] >= cells[3] || pixels[0] >= pixels[2] || pixels[1] >= pixels[3]) {
         ctx->err = "film_reconstruct: bad arguments"; return B2RT_E_ARG;

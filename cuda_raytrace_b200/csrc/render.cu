@@ -447,7 +447,6 @@ int b2rt_render_pixels_impl(b2rt_ctx *ctx, const b2rt_camera *cam, const b2rt_fr
     cudaStream_t st = ctx->stream;
     DScene sc;
     b2rt_fill_dscene(ctx, &sc);
-    const int64_t n_pixels = (int64_t)(fp->x1 - fp->x0) * (fp->y1 - fp->y0);
     const bool any_spec = [&] {
         for (const Material &m : ctx->h_materials) if (m.type != B2RT_MAT_MATTE) return true;
         return false;

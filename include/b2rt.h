@@ -390,6 +390,24 @@ int b2rt_sort_pairs_noalloc(b2rt_ctx *ctx, int64_t n, uint32_t *keys, uint32_t *
 void *b2rt_host_alloc(b2rt_ctx *ctx, int64_t bytes);
 void  b2rt_host_free(b2rt_ctx *ctx, void *p);
 
+/* ---- per-stage device times and NVTX ranges (the reference has no timing anywhere on its GPU path) -----
+ * Every stage entry point below opens an NVTX range named after itself (visible in Nsight Systems / Compute; free when no
+ * tool is attached).  With timings enabled (b2rt_timings_enable, or B2RT_TIMINGS=1 in the environment at b2rt_create) it
+ * also brackets the stage with CUDA events on the context stream and SYNCHRONISES at its end -- a measuring mode, not for
+ * production pipelines -- and b2rt_get_timings returns the accumulated device milliseconds and call counts per stage. */
+enum { B2RT_STAGE_BUILD = 0,        /* b2rt_build_accel */
+       B2RT_STAGE_TRACE_CLOSEST,    /* b2rt_trace_closest */
+       B2RT_STAGE_TRACE_ANY,        /* b2rt_trace_any */
+       B2RT_STAGE_PHOTONS,          /* b2rt_photons_trace / _shoot / _trace_fg */
+       B2RT_STAGE_GRID,             /* b2rt_photon_grid_build, b2rt_radiance_compute */
+       B2RT_STAGE_GATHER,           /* b2rt_gather / _gather_sets / _irradiance / _radiance_lookup / _final_gather */
+       B2RT_STAGE_RENDER,           /* b2rt_render_frame, b2rt_camera_samples, b2rt_surface_at */
+       B2RT_STAGE_FILM,             /* b2rt_film_reconstruct */
+       B2RT_STAGE_COUNT };
+typedef struct { double ms[B2RT_STAGE_COUNT]; int64_t calls[B2RT_STAGE_COUNT]; } b2rt_timings;
+int b2rt_timings_enable(b2rt_ctx *ctx, int on);
+int b2rt_get_timings(b2rt_ctx *ctx, b2rt_timings *out, int reset);
+
 /* ---- timing / stream ----------------------------------------------------------------------- */
 int b2rt_sync(b2rt_ctx *ctx);
 int b2rt_timer_start(b2rt_ctx *ctx);            /* cudaEventRecord on the context stream */

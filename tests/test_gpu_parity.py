@@ -346,3 +346,33 @@ def test_partial_spheres_bit_exact_vs_oracle_and_pbrt_golden(built):
     nprims = ep.max() + 1
     inside = (ep >= nprims - 4) & (np.einsum("ij,ij->i", s["n"], r[:, 4:7]) > 0)
     assert inside.sum() > 100
+
+
+# ---- per-stage device times (b2rt_get_timings) ------------------------------------------------------------------------
+def test_stage_timings(built):
+    """off by default (no events, no extra synchronisation); when enabled every stage entry point is bracketed by CUDA
+    events and b2rt_get_timings returns device milliseconds and call counts per stage"""
+    desc = S.cornell_scene()
+    rays = S.pinhole_rays(64, 48)
+    with b2rt.Context(0, seed=2) as c:
+        S.fill_scene(c, desc)
+        c.build_accel()
+        c.trace_closest(rays)
+        assert all(v == (0.0, 0) for v in c.timings().values())
+        c.timings_enable(True)
+        c.build_accel()
+        c.trace_closest(rays); c.trace_closest(rays); c.trace_any(rays)
+        c.photons_shoot(500, 20000, batch_paths=16384)          # calls the trace stage inside: counted once, as "photons"
+        c.grid_build(1)
+        q = np.zeros((32, 12), np.float32); q[:, 0] = np.linspace(-0.8, 0.8, 32); q[:, 4] = 1; q[:, 6:9] = 0.5
+        c.gather(1, q.view(b2rt.QUERY_DTYPE).reshape(-1), 20, 0.09)
+        cam = b2rt.pbrt_camera((0, 1, 3.4), (0, 1, 0), (0, 1, 0), 40, 32, 32)
+        c.render_frame(cam, spp=1, nused=20, max_dist=0.3)
+        t = c.timings(reset=True)
+        assert [t[k][1] for k in ("build", "trace_closest", "trace_any", "photons", "grid", "gather", "render", "film")] == [1, 2, 1, 1, 1, 1, 1, 0]
+        assert all(t[k][0] > 0 for k in ("build", "trace_closest", "trace_any", "photons", "grid", "gather", "render"))
+        assert t["build"][0] < 50 and t["trace_closest"][0] < 50
+        assert all(v == (0.0, 0) for v in c.timings().values())
+        c.timings_enable(False)
+        c.trace_closest(rays)
+        assert c.timings()["trace_closest"] == (0.0, 0)
