@@ -210,3 +210,32 @@ def test_scene_cache_round_trip(built, tmp_path):
         open(str(tmp_path / "bad.b2rt"), "wb").write(open(path, "rb").read()[:1000])
         with pytest.raises(b2rt.B2rtError):
             c.scene_load(str(tmp_path / "bad.b2rt"))
+
+
+def test_instanced_final_gathering_matches_flattened_scene(built):
+    """pbrt's default mode (final gathering) over the two-level tree: the radiance-photon pass, the gather rays and their
+    hit attributes all go through the instance-aware instantiations; statistical agreement with the flattened scene"""
+    desc = S.instanced_scene(n_inst=8, seed=9)
+    cam = b2rt.pbrt_camera((0.5, 3.0, 7.0), (0.0, 0.0, 0.0), (0.0, 1.0, 0.0), 50.0, 64, 48)
+
+    def run(fill):
+        with b2rt.Context(0, seed=3) as c:
+            fill(c)
+            c.add_light(0, (60.0, 60.0, 60.0), p=(0.5, 4.5, 1.0))
+            c.build_accel()
+            c.photons_trace(0, 400000)
+            c.grid_build(0); c.grid_build(1)
+            nd, nr = c.photons_trace_fg(0, 400000)
+            c.grid_build(2)
+            c.radiance_compute(50, 0.5)
+            c.set_final_gather(True, 16, 10.0)
+            return nd, nr, c.render_frame(cam, spp=4, nused=50, max_dist=0.5)
+
+    def fill_flat(c):
+        for sh in S.flatten_instanced(desc):
+            S._add_shape(c, sh, "b2rt")
+
+    a, b = run(lambda c: S.fill_instanced(c, desc)), run(fill_flat)
+    assert b[1] > 1000 and abs(a[1] - b[1]) <= 5.0 * np.sqrt(b[1]), (a[:2], b[:2])      # radiance photons
+    assert np.isfinite(a[2]).all() and b[2].mean() > 1e-3
+    assert abs(a[2].mean() - b[2].mean()) < 0.03 * b[2].mean(), (a[2].mean(), b[2].mean())
