@@ -90,8 +90,11 @@ __device__ __forceinline__ uint32_t digit_peers(uint32_t d, bool ok) {
     return peers;
 }
 
+#ifndef B2RT_SCATTER_BLOCKS
+#define B2RT_SCATTER_BLOCKS 4
+#endif
 template <int RANK, bool FULL>
-__global__ void __launch_bounds__(SORT_THREADS, 4)
+__global__ void __launch_bounds__(SORT_THREADS, B2RT_SCATTER_BLOCKS)
 radix_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__restrict__ vals_in,
                      uint32_t *__restrict__ keys_out, uint32_t *__restrict__ vals_out, int64_t n, int shift,
                      const uint32_t *__restrict__ scanned_hist, int nblocks, int tile_first) {
