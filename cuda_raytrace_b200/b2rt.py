@@ -41,7 +41,7 @@ SYMBOLS = [
     "b2rt_create", "b2rt_destroy", "b2rt_last_error", "b2rt_device_count", "b2rt_add_mesh", "b2rt_add_sphere",
     "b2rt_add_disk", "b2rt_add_material", "b2rt_add_light", "b2rt_clear_scene", "b2rt_build_accel",
     "b2rt_accel_info_get", "b2rt_accel_download", "b2rt_trace_closest", "b2rt_trace_any", "b2rt_sort_pairs", "b2rt_sort_pairs_noalloc",
-    "b2rt_add_mesh_ex", "b2rt_add_sphere_ex", "b2rt_surface_at", "b2rt_scene_save", "b2rt_scene_load", "b2rt_scene_counts", "b2rt_timings_enable", "b2rt_get_timings", "b2rt_object_begin", "b2rt_object_end", "b2rt_add_instance", "b2rt_instance_info", "b2rt_trace_stats", "b2rt_add_spot_light", "b2rt_add_distant_light", "b2rt_sync", "b2rt_timer_start", "b2rt_timer_stop", "b2rt_launch_count", "b2rt_stream", "b2rt_host_alloc", "b2rt_host_free",
+    "b2rt_add_mesh_ex", "b2rt_add_sphere_ex", "b2rt_add_disk_ex", "b2rt_surface_at", "b2rt_scene_save", "b2rt_scene_load", "b2rt_scene_counts", "b2rt_timings_enable", "b2rt_get_timings", "b2rt_object_begin", "b2rt_object_end", "b2rt_add_instance", "b2rt_instance_info", "b2rt_trace_stats", "b2rt_add_spot_light", "b2rt_add_distant_light", "b2rt_sync", "b2rt_timer_start", "b2rt_timer_stop", "b2rt_launch_count", "b2rt_stream", "b2rt_host_alloc", "b2rt_host_free",
 ]
 
 _lib = None
@@ -182,24 +182,30 @@ class Context:
         self._ck(self.lib.b2rt_surface_at(self.h, len(rays), _ptr(rays), _ptr(out), HOST))
         return out
 
-    def add_sphere(self, o2w, radius, w2o=None, material=-1, arealight=-1, zmin=None, zmax=None):
-        """zmin / zmax: pbrt's partial sphere (object-space z range that is kept)"""
+    def add_sphere(self, o2w, radius, w2o=None, material=-1, arealight=-1, zmin=None, zmax=None, phimax=None):
+        """zmin / zmax / phimax (degrees): pbrt's partial sphere"""
         o2w = _f32(o2w, (12,))
         w2o = None if w2o is None else _f32(w2o, (12,))
         p = C.c_int32()
-        if zmin is not None or zmax is not None:
-            self.lib.b2rt_add_sphere_ex.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_int32,
-                                                    C.c_int32, C.POINTER(C.c_int32)]
+        if zmin is not None or zmax is not None or phimax is not None:
+            self.lib.b2rt_add_sphere_ex.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_float,
+                                                    C.c_int32, C.c_int32, C.POINTER(C.c_int32)]
             self._ck(self.lib.b2rt_add_sphere_ex(self.h, _ptr(o2w), _ptr(w2o), radius, -radius if zmin is None else zmin,
-                                                 radius if zmax is None else zmax, material, arealight, C.byref(p)))
+                                                 radius if zmax is None else zmax, 360.0 if phimax is None else phimax,
+                                                 material, arealight, C.byref(p)))
             return p.value
         self._ck(self.lib.b2rt_add_sphere(self.h, _ptr(o2w), _ptr(w2o), radius, material, arealight, C.byref(p)))
         return p.value
 
-    def add_disk(self, o2w, height, radius, inner=0.0, w2o=None, material=-1, arealight=-1):
+    def add_disk(self, o2w, height, radius, inner=0.0, w2o=None, material=-1, arealight=-1, phimax=None):
         o2w = _f32(o2w, (12,))
         w2o = None if w2o is None else _f32(w2o, (12,))
         p = C.c_int32()
+        if phimax is not None:
+            self.lib.b2rt_add_disk_ex.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_float,
+                                                  C.c_int32, C.c_int32, C.POINTER(C.c_int32)]
+            self._ck(self.lib.b2rt_add_disk_ex(self.h, _ptr(o2w), _ptr(w2o), height, radius, inner, phimax, material, arealight, C.byref(p)))
+            return p.value
         self._ck(self.lib.b2rt_add_disk(self.h, _ptr(o2w), _ptr(w2o), height, radius, inner, material, arealight,
                                         C.byref(p)))
         return p.value

@@ -358,12 +358,19 @@ int b2rt_add_mesh(b2rt_ctx *ctx, int32_t nverts, const float *P, int32_t ntris, 
     return b2rt_add_mesh_ex(ctx, nverts, P, ntris, idx, N, uv, material_id, arealight_id, 0, first_prim);
 }
 
+// phimax in degrees as pbrt's parameter -> the record's value: radians after pbrt's clamp (Radians(Clamp(pm, 0, 360)),
+// sphere.cpp:48, disk.cpp:46), 0 for the full turn
+static float phimax_field(float phimax_deg) {
+    const float pm = fminf(fmaxf(phimax_deg, 0.f), 360.f);
+    return pm >= 360.f ? 0.f : ((float)M_PI / 180.f) * pm;
+}
+
 static int add_analytic(b2rt_ctx *ctx, int type, const float o2w[12], const float *w2o, float radius,
-                        float height, float inner, int32_t material_id, int32_t arealight_id, int32_t *prim) {
+                        float height, float inner, int32_t material_id, int32_t arealight_id, int32_t *prim, float phimax = 0.f) {
     if (!ctx) return B2RT_E_ARG;
     if (ctx->cur_object) {
         if (arealight_id >= 0) { ctx->err = "add_sphere/disk: area lights are not supported inside objects (pbrt: core/api.cpp:1009-1011)"; return B2RT_E_ARG; }
-        int rc = add_analytic(ctx->cur_object, type, o2w, w2o, radius, height, inner, material_id, -1, prim);
+        int rc = add_analytic(ctx->cur_object, type, o2w, w2o, radius, height, inner, material_id, -1, prim, phimax);
         if (rc) ctx->err = ctx->cur_object->err;
         return rc;
     }
@@ -372,7 +379,7 @@ static int add_analytic(b2rt_ctx *ctx, int type, const float o2w[12], const floa
     memcpy(a.o2w, o2w, sizeof(a.o2w));
     if (w2o) memcpy(a.w2o, w2o, sizeof(a.w2o));
     else if (invert34(o2w, a.w2o)) { ctx->err = "add_sphere/disk: singular transform"; return B2RT_E_ARG; }
-    a.radius = radius; a.height = height; a.inner = inner; a.pad = 0.f;
+    a.radius = radius; a.height = height; a.inner = inner; a.pad = phimax;
     ctx->h_analytic.push_back(a);
     ctx->h_analytic_type.push_back(type);
     if (prim) *prim = ctx->n_prims;
@@ -389,14 +396,22 @@ int b2rt_add_sphere(b2rt_ctx *ctx, const float o2w[12], const float *w2o, float 
 }
 
 int b2rt_add_sphere_ex(b2rt_ctx *ctx, const float o2w[12], const float *w2o, float radius, float zmin, float zmax,
-                       int32_t material_id, int32_t arealight_id, int32_t *prim) {
+                       float phimax_deg, int32_t material_id, int32_t arealight_id, int32_t *prim) {
     if (!ctx) return B2RT_E_ARG;
-    if (!(radius > 0.f) || !(zmin == zmin) || !(zmax == zmax)) { ctx->err = "add_sphere_ex: bad arguments"; return B2RT_E_ARG; }
+    if (!(radius > 0.f) || !(zmin == zmin) || !(zmax == zmax) || !(phimax_deg > 0.f)) { ctx->err = "add_sphere_ex: bad arguments"; return B2RT_E_ARG; }
     // Sphere::Sphere (shapes/sphere.cpp:40-49): zmin = Clamp(min(z0, z1), -radius, radius), zmax likewise
     float z0 = fminf(fmaxf(fminf(zmin, zmax), -radius), radius), z1 = fminf(fmaxf(fmaxf(zmin, zmax), -radius), radius);
     if (!(z0 < z1)) { ctx->err = "add_sphere_ex: zmin and zmax leave no surface"; return B2RT_E_ARG; }
-    if (z0 <= -radius && z1 >= radius) z0 = z1 = 0.f;      // full sphere: no clipping (the record's "zmin >= zmax")
-    return add_analytic(ctx, B2RT_PRIM_SPHERE, o2w, w2o, radius, z0, z1, material_id, arealight_id, prim);
+    if (z0 <= -radius && z1 >= radius) z0 = z1 = 0.f;      // no z clipping (the record's "zmin >= zmax")
+    return add_analytic(ctx, B2RT_PRIM_SPHERE, o2w, w2o, radius, z0, z1, material_id, arealight_id, prim, phimax_field(phimax_deg));
+}
+
+int b2rt_add_disk_ex(b2rt_ctx *ctx, const float o2w[12], const float *w2o, float height, float radius, float inner_radius,
+                     float phimax_deg, int32_t material_id, int32_t arealight_id, int32_t *prim) {
+    if (!ctx) return B2RT_E_ARG;
+    if (!(phimax_deg > 0.f)) { ctx->err = "add_disk_ex: bad arguments"; return B2RT_E_ARG; }
+    if (arealight_id >= 0 && phimax_field(phimax_deg) > 0.f) { ctx->err = "add_disk_ex: an area light needs the full disk"; return B2RT_E_ARG; }
+    return add_analytic(ctx, B2RT_PRIM_DISK, o2w, w2o, radius, height, inner_radius, material_id, arealight_id, prim, phimax_field(phimax_deg));
 }
 
 int b2rt_add_disk(b2rt_ctx *ctx, const float o2w[12], const float *w2o, float height, float radius,

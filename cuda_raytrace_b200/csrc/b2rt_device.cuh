@@ -178,6 +178,17 @@ __device__ __forceinline__ f3 xf_normal(const float *w2o, f3 n) {
                w2o[2] * n.x + w2o[6] * n.y + w2o[10] * n.z);
 }
 
+// phi > phimax of pbrt's partial quadrics (phi = atan2f(y, x) lifted to [0, 2 pi), shapes/sphere.cpp:88-90, disk.cpp:73-75)
+// WITHOUT atan2f, which is not reproducible between math libraries: the side of the direction (cos phimax, sin phimax)
+// the point lies on, from the deterministic sin / cos polynomial above.  Equal to pbrt's test except for points within
+// rounding of the cut.
+__device__ __forceinline__ bool phi_clipped(float x, float y, float phimax) {
+    float s, c;
+    b2_sincos_quarter(phimax * 0.63661977236758134308f, s, c);       // radians -> quarter turns
+    const float cr = c * y - s * x;                                  // |r| sin(phi - phimax)
+    return phimax <= B2_PI ? !(y >= 0.f && cr <= 0.f) : (y < 0.f && cr > 0.f);
+}
+
 // pbrt Sphere::Intersect arithmetic (shapes/sphere.cpp:58-106) with zmin / zmax clipping; the reference's device program
 // ignores zmin / zmax / phiMax (cuda_render/util/shape/cudasphere.cu:27-72)
 static __device__ __noinline__ bool sphere_test(const RayD &r, const AnalyticPrim &S, float tmax, float &t_out) {
@@ -199,26 +210,31 @@ static __device__ __noinline__ bool sphere_test(const RayD &r, const AnalyticPri
         thit = t1;
         if (thit > tmax) return false;
     }
-    // partial sphere: pbrt's zmin / zmax clipping (shapes/sphere.cpp:92-106), which the reference's device program ignores.
-    // For a sphere the record's height / inner fields hold zmin / zmax (already clamped to [-radius, radius] as pbrt's
-    // constructor does); zmin >= zmax = no clipping.  phimax is not clipped here (atan2f is not reproducible across
-    // libraries; the drop-in warns).
-    const float zmin = S.height, zmax = S.inner;
-    if (zmin < zmax) {
-        float pz = oz + dz * thit;
-        if ((zmin > -S.radius && pz < zmin) || (zmax < S.radius && pz > zmax)) {
+    // partial sphere: pbrt's zmin / zmax / phimax clipping (shapes/sphere.cpp:84-106), which the reference's device
+    // program ignores.  For a sphere the record's height / inner fields hold zmin / zmax (already clamped to [-radius,
+    // radius] as pbrt's constructor does; zmin >= zmax = no z clipping) and pad holds phimax in radians (0 = full turn).
+    const float zmin = S.height, zmax = S.inner, phimax = S.pad;
+    if (zmin < zmax || phimax > 0.f) {
+        auto clipped = [&](float t) {
+            float px = ox + dx * t;
+            const float py = oy + dy * t, pz = oz + dz * t;
+            if (px == 0.f && py == 0.f) px = 1e-5f * S.radius;
+            bool c = (zmin < zmax) && ((zmin > -S.radius && pz < zmin) || (zmax < S.radius && pz > zmax));
+            if (phimax > 0.f) c = c || phi_clipped(px, py, phimax);
+            return c;
+        };
+        if (clipped(thit)) {
             if (thit == t1) return false;
             if (t1 > tmax) return false;
             thit = t1;
-            pz = oz + dz * thit;
-            if ((zmin > -S.radius && pz < zmin) || (zmax < S.radius && pz > zmax)) return false;
+            if (clipped(thit)) return false;
         }
     }
     t_out = thit;
     return true;
 }
 
-// pbrt Disk::Intersect (shapes/disk.cpp:56-72), full phi range
+// pbrt Disk::Intersect (shapes/disk.cpp:56-76)
 static __device__ __noinline__ bool disk_test(const RayD &r, const AnalyticPrim &D, float tmax, float &t_out) {
     float ox, oy, oz, dx, dy, dz;
     xf_point(D.w2o, r.ox, r.oy, r.oz, ox, oy, oz);
@@ -229,6 +245,7 @@ static __device__ __noinline__ bool disk_test(const RayD &r, const AnalyticPrim 
     float px = ox + dx * thit, py = oy + dy * thit;
     float dist2 = px * px + py * py;
     if (dist2 > D.radius * D.radius || dist2 < D.inner * D.inner) return false;
+    if (D.pad > 0.f && phi_clipped(px, py, D.pad)) return false;    // pbrt's phimax (shapes/disk.cpp:73-76); pad = radians, 0 = full
     t_out = thit;
     return true;
 }

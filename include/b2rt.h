@@ -81,11 +81,16 @@ int b2rt_add_mesh_ex(b2rt_ctx *ctx, int32_t nverts, const float *P, int32_t ntri
  * (cuda_render/util/shape/cudasphere.cpp:15-40); w2o may be NULL (then it is computed here). */
 int b2rt_add_sphere(b2rt_ctx *ctx, const float o2w[12], const float *w2o, float radius, int32_t material_id,
                     int32_t arealight_id, int32_t *prim);
-/* partial sphere: pbrt's "zmin" / "zmax" (shapes/sphere.cpp:40-49, 92-106; the reference's device program ignores them,
- * cudasphere.cu:27-72): the surface with object-space z outside [zmin, zmax] is cut away, a ray that meets the cut-away part
- * first continues to the far intersection.  Values are clamped to [-radius, radius] as pbrt does.  "phimax" is not supported. */
+/* partial sphere: pbrt's "zmin" / "zmax" / "phimax" (shapes/sphere.cpp:40-49, 84-106; the reference's device program ignores
+ * all three, cudasphere.cu:27-72): the surface with object-space z outside [zmin, zmax] or azimuth beyond phimax_deg is cut
+ * away, a ray that meets the cut-away part first continues to the far intersection.  Values are clamped as pbrt does.  The
+ * azimuth test uses the side of the cut's direction instead of atan2f (not reproducible between math libraries): equal to
+ * pbrt's except for points within rounding of the cut.  b2rt_add_disk_ex: the same "phimax" for a disk (shapes/disk.cpp:
+ * 73-76); not for area lights. */
 int b2rt_add_sphere_ex(b2rt_ctx *ctx, const float o2w[12], const float *w2o, float radius, float zmin, float zmax,
-                       int32_t material_id, int32_t arealight_id, int32_t *prim);
+                       float phimax_deg, int32_t material_id, int32_t arealight_id, int32_t *prim);
+int b2rt_add_disk_ex(b2rt_ctx *ctx, const float o2w[12], const float *w2o, float height, float radius, float inner_radius,
+                     float phimax_deg, int32_t material_id, int32_t arealight_id, int32_t *prim);
 /* disk at object z = height (cuda_render/util/shape/cudadisk.cpp:15-45) */
 int b2rt_add_disk(b2rt_ctx *ctx, const float o2w[12], const float *w2o, float height, float radius,
                   float inner_radius, int32_t material_id, int32_t arealight_id, int32_t *prim);

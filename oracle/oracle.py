@@ -91,17 +91,26 @@ class PortScene:
             return None, None, None
         return np.ascontiguousarray(self.vnormal), np.ascontiguousarray(self.vuv), np.ascontiguousarray(self.tri_flags)
 
-    def _add_analytic(self, o2w, w2o, radius, height, inner, typ):
-        rec = np.zeros(28, np.float32)
+    def _add_analytic(self, o2w, w2o, radius, height, inner, typ, phimax=0.0):
+        rec = np.zeros(32, np.float32)                 # PORT_ANALYTIC_STRIDE
         rec[0:12] = np.asarray(o2w, np.float32).reshape(12)
         rec[12:24] = np.asarray(w2o, np.float32).reshape(12)
         rec[24:28] = (radius, height, inner, typ)
+        rec[28] = phimax                                # radians, 0 = full turn
         self.kind.append(~len(self.analytic))
         self.analytic.append(rec)
         return len(self.kind) - 1
 
-    def add_sphere(self, o2w, w2o, radius, zmin=None, zmax=None):
-        """zmin / zmax: pbrt's partial sphere; clamped as Sphere::Sphere does, (0, 0) in the record = full sphere"""
+    @staticmethod
+    def _phimax_field(phimax_deg):
+        """degrees -> the record's value: Radians(Clamp(pm, 0, 360)) in binary32 as pbrt forms it, 0 for the full turn"""
+        if phimax_deg is None:
+            return 0.0
+        pm = np.float32(min(max(phimax_deg, 0.0), 360.0))
+        return 0.0 if pm >= 360.0 else float((np.float32(np.pi) / np.float32(180.0)) * pm)
+
+    def add_sphere(self, o2w, w2o, radius, zmin=None, zmax=None, phimax=None):
+        """zmin / zmax / phimax: pbrt's partial sphere; clamped as Sphere::Sphere does, (0, 0) in the record = no z clipping"""
         z0, z1 = 0.0, 0.0
         if zmin is not None or zmax is not None:
             a, b = (-radius if zmin is None else zmin), (radius if zmax is None else zmax)
@@ -109,14 +118,14 @@ class PortScene:
             z1 = float(np.clip(np.float32(max(a, b)), -np.float32(radius), np.float32(radius)))
             if z0 <= -radius and z1 >= radius:
                 z0 = z1 = 0.0
-        return self._add_analytic(o2w, w2o, radius, z0, z1, 1)
+        return self._add_analytic(o2w, w2o, radius, z0, z1, 1, self._phimax_field(phimax))
 
-    def add_disk(self, o2w, w2o, height, radius, inner=0.0):
-        return self._add_analytic(o2w, w2o, height=height, radius=radius, inner=inner, typ=2)
+    def add_disk(self, o2w, w2o, height, radius, inner=0.0, phimax=None):
+        return self._add_analytic(o2w, w2o, height=height, radius=radius, inner=inner, typ=2, phimax=self._phimax_field(phimax))
 
     def _arrays(self):
         kind = np.asarray(self.kind, np.int32)
-        an = np.concatenate(self.analytic).astype(np.float32) if self.analytic else np.zeros(28, np.float32)
+        an = np.concatenate(self.analytic).astype(np.float32) if self.analytic else np.zeros(32, np.float32)
         return kind, np.ascontiguousarray(self.verts), np.ascontiguousarray(self.idx), an
 
     def intersect(self, rays, nthreads=1):
@@ -328,18 +337,21 @@ class RefScene:
         self.lib.ref_surface(self.h, len(rays), _p(rays), _p(out), nthreads)
         return out
 
-    def add_sphere(self, o2w, w2o, radius, zmin=None, zmax=None):
+    def add_sphere(self, o2w, w2o, radius, zmin=None, zmax=None, phimax=None):
         o2w = np.ascontiguousarray(o2w, np.float32).reshape(12)
         w2o = np.ascontiguousarray(w2o, np.float32).reshape(12)
-        if zmin is not None or zmax is not None:
-            self.lib.ref_scene_add_sphere_ex.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_float]
+        if zmin is not None or zmax is not None or phimax is not None:
+            self.lib.ref_scene_add_sphere_ex.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_float]
             return self.lib.ref_scene_add_sphere_ex(self.h, _p(o2w), _p(w2o), radius, -radius if zmin is None else zmin,
-                                                    radius if zmax is None else zmax)
+                                                    radius if zmax is None else zmax, 360.0 if phimax is None else phimax)
         return self.lib.ref_scene_add_sphere(self.h, _p(o2w), _p(w2o), radius)
 
-    def add_disk(self, o2w, w2o, height, radius, inner=0.0):
+    def add_disk(self, o2w, w2o, height, radius, inner=0.0, phimax=None):
         o2w = np.ascontiguousarray(o2w, np.float32).reshape(12)
         w2o = np.ascontiguousarray(w2o, np.float32).reshape(12)
+        if phimax is not None:
+            self.lib.ref_scene_add_disk_ex.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_float]
+            return self.lib.ref_scene_add_disk_ex(self.h, _p(o2w), _p(w2o), height, radius, inner, phimax)
         return self.lib.ref_scene_add_disk(self.h, _p(o2w), _p(w2o), height, radius, inner)
 
     def build(self):
@@ -490,15 +502,15 @@ class PortFullScene:
         self.prim_light.extend([arealight] * len(np.asarray(idx).reshape(-1, 3)))
         return first
 
-    def add_sphere(self, o2w, radius, w2o=None, material=-1, arealight=-1, zmin=None, zmax=None):
+    def add_sphere(self, o2w, radius, w2o=None, material=-1, arealight=-1, zmin=None, zmax=None, phimax=None):
         self.prim_material.append(material)
         self.prim_light.append(arealight)
-        return self.geo.add_sphere(o2w, w2o, radius, zmin, zmax)
+        return self.geo.add_sphere(o2w, w2o, radius, zmin, zmax, phimax)
 
-    def add_disk(self, o2w, height, radius, inner=0.0, w2o=None, material=-1, arealight=-1):
+    def add_disk(self, o2w, height, radius, inner=0.0, w2o=None, material=-1, arealight=-1, phimax=None):
         self.prim_material.append(material)
         self.prim_light.append(arealight)
-        return self.geo.add_disk(o2w, w2o, height, radius, inner)
+        return self.geo.add_disk(o2w, w2o, height, radius, inner, phimax)
 
     def add_light(self, ltype, rgb, p=None, prim=-1, nsamples=1):
         p = (0.0, 0.0, 0.0) if p is None else p

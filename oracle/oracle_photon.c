@@ -213,7 +213,7 @@ static int closest_range(const port_scene *sc, v3 o, v3 d, float tmin, float tma
         s->n = vnormalize(vcross(e1, e2));      /* pbrt: Cross(dpdu, dpdv) with the default uv = the side of Cross(e1, e2) */
         s->sn = e1;                             /* dpdu = p2 - p1 */
     } else {
-        const float *A = sc->analytic + 28 * (int64_t)(~k);
+        const float *A = sc->analytic + PORT_ANALYTIC_STRIDE * (int64_t)(~k);
         v3 no;
         if ((int)A[27] == 1) xfp(A + 12, s->p, &no); else no = V(0.f, 0.f, 1.f);
         s->n = vnormalize(xfn(A + 12, no));
@@ -375,7 +375,7 @@ static void derive_lights(const port_scene *sc, olight *L, float *cdf /* 2n+2 */
         } else {
             int prim = (int)l[7];
             int a = ~sc->kind[prim];
-            const float *D = sc->analytic + 28 * (int64_t)a;
+            const float *D = sc->analytic + PORT_ANALYTIC_STRIDE * (int64_t)a;
             float phimax = ((float)M_PI / 180.f) * 360.f;
             L[i].analytic = a;
             L[i].area = phimax * 0.5f * (D[24] * D[24] - D[26] * D[26]);       /* Disk::Area */
@@ -424,7 +424,7 @@ static void o_emit(const port_scene *sc, const olight *Ls, const uint32_t r0[4],
         *pdf = (float)(1.0 / (3.14159265358979323846 * (double)Ls->wr * (double)Ls->wr));
         *Le = Ls->rgb;
     } else {
-        const float *D = sc->analytic + 28 * (int64_t)Ls->analytic;
+        const float *D = sc->analytic + PORT_ANALYTIC_STRIDE * (int64_t)Ls->analytic;
         float x, y;
         concentric_disk(u01(r0[1]), u01(r0[2]), &x, &y);
         x *= D[24]; y *= D[24];

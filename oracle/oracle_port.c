@@ -62,7 +62,15 @@ static inline void xf_vec(const float *m, const float v[3], float out[3]) {
 }
 
 /* Sphere::Intersect for a full sphere, pbrt-v2/src/shapes/sphere.cpp:58-83; Quadratic core/pbrt.h:308-322 */
-static int sphere_intersect(const float o_[3], const float d_[3], float tmin, float tmax, const float *A28,
+/* phi > phimax without atan2f: csrc/b2rt_device.cuh phi_clipped, same operations */
+void port_sincos_quarter(float q, float *s, float *c);
+static int phi_clipped(float x, float y, float phimax) {
+    float s, c;
+    port_sincos_quarter(phimax * 0.63661977236758134308f, &s, &c);
+    const float cr = c * y - s * x;
+    return phimax <= 3.14159265358979323846f ? !(y >= 0.f && cr <= 0.f) : (y < 0.f && cr > 0.f);
+}
+static int sphere_intersect(const float o_[3], const float d_[3], float tmin, float tmax, const float *A28, float phimax,
                             float *t) {
     float o[3], d[3];
     xf_point(A28 + 12, o_, o);
@@ -85,17 +93,21 @@ static int sphere_intersect(const float o_[3], const float d_[3], float tmin, fl
         thit = t1;
         if (thit > tmax) return 0;
     }
-    /* partial sphere, shapes/sphere.cpp:92-106 without the phi test: record slots 25 / 26 hold zmin / zmax for a sphere
-     * (already clamped to [-radius, radius]); zmin >= zmax = the full sphere */
+    /* partial sphere, shapes/sphere.cpp:84-106: record slots 25 / 26 hold zmin / zmax for a sphere (already clamped to
+     * [-radius, radius]; zmin >= zmax = no z clipping).  phimax (radians, 0 = full turn) sits at the end of the record
+     * when the caller passes the long form; the 28-float record has none. */
     float zmin = A28[25], zmax = A28[26];
-    if (zmin < zmax) {
-        float pz = o[2] + d[2] * thit;
-        if ((zmin > -radius && pz < zmin) || (zmax < radius && pz > zmax)) {
+    if (zmin < zmax || phimax > 0.f) {
+        for (int pass = 0; pass < 2; ++pass) {
+            float px = o[0] + d[0] * thit, py = o[1] + d[1] * thit, pz = o[2] + d[2] * thit;
+            if (px == 0.f && py == 0.f) px = 1e-5f * radius;
+            int c = (zmin < zmax) && ((zmin > -radius && pz < zmin) || (zmax < radius && pz > zmax));
+            if (phimax > 0.f) c = c || phi_clipped(px, py, phimax);
+            if (!c) break;
+            if (pass == 1) return 0;
             if (thit == t1) return 0;
             if (t1 > tmax) return 0;
             thit = t1;
-            pz = o[2] + d[2] * thit;
-            if ((zmin > -radius && pz < zmin) || (zmax < radius && pz > zmax)) return 0;
         }
     }
     *t = thit;
@@ -103,7 +115,7 @@ static int sphere_intersect(const float o_[3], const float d_[3], float tmin, fl
 }
 
 /* Disk::Intersect, pbrt-v2/src/shapes/disk.cpp:56-72 (phiMax = 2pi) */
-static int disk_intersect(const float o_[3], const float d_[3], float tmin, float tmax, const float *A28,
+static int disk_intersect(const float o_[3], const float d_[3], float tmin, float tmax, const float *A28, float phimax,
                           float *t) {
     float o[3], d[3];
     xf_point(A28 + 12, o_, o);
@@ -115,6 +127,7 @@ static int disk_intersect(const float o_[3], const float d_[3], float tmin, floa
     float px = o[0] + d[0] * thit, py = o[1] + d[1] * thit;
     float dist2 = px * px + py * py;
     if (dist2 > radius * radius || dist2 < inner * inner) return 0;
+    if (phimax > 0.f && phi_clipped(px, py, phimax)) return 0;
     *t = thit;
     return 1;
 }
@@ -133,9 +146,9 @@ static int prim_test(const BruteJob *J, int p, const float *r, float *t, float *
         return tri_intersect(r, r + 4, r[3], r[7], J->verts + 3 * (int64_t)v[0], J->verts + 3 * (int64_t)v[1],
                              J->verts + 3 * (int64_t)v[2], t, b1, b2);
     }
-    const float *A = J->analytic + 28 * (int64_t)(~k);
-    if ((int)A[27] == 1) return sphere_intersect(r, r + 4, r[3], r[7], A, t);
-    return disk_intersect(r, r + 4, r[3], r[7], A, t);
+    const float *A = J->analytic + PORT_ANALYTIC_STRIDE * (int64_t)(~k);
+    if ((int)A[27] == 1) return sphere_intersect(r, r + 4, r[3], r[7], A, A[28], t);
+    return disk_intersect(r, r + 4, r[3], r[7], A, A[28], t);
 }
 
 static void *brute_worker(void *arg) {

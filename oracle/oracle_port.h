@@ -4,10 +4,12 @@
 #ifndef ORACLE_PORT_H
 #define ORACLE_PORT_H
 #include <stdint.h>
+#define PORT_ANALYTIC_STRIDE 32
 
 /* (1) pbrt primitive tests + the exhaustive loop of renderers/aggregatetest.cpp:93-102.
  * rays: 8 floats {o,tmin,d,tmax}.  prim kinds: kind[p] >= 0 -> triangle index, < 0 -> ~analytic index.
- * analytic record = 28 floats {o2w[12], w2o[12], radius, height, inner, type(1 sphere,2 disk)}.
+ * analytic record = PORT_ANALYTIC_STRIDE (32) floats {o2w[12], w2o[12], radius, height, inner, type(1 sphere,2 disk),
+ * phimax in radians (0 = full turn), 3 unused}; for a sphere height / inner hold pbrt's zmin / zmax (zmin >= zmax: none).
  * Winner = (min t, then min prim id).  Outputs t (INF on miss), prim (-1), b1, b2.           */
 void port_intersect_brute(int nprims, const int32_t *kind, const float *verts, const int32_t *idx,
                           const float *analytic, int64_t nrays, const float *rays, float *t_out,

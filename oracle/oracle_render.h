@@ -83,7 +83,7 @@ static v3 r_direct(const port_scene *sc, const olight *Ls, const osurf *s, const
                 Ld = vadd(Ld, V(f_lambert.x * (I.x / d2) * w, f_lambert.y * (I.y / d2) * w, f_lambert.z * (I.z / d2) * w));
                 continue;
             }
-            const float *D = sc->analytic + 28 * (int64_t)Lt->analytic;
+            const float *D = sc->analytic + PORT_ANALYTIC_STRIDE * (int64_t)Lt->analytic;
             {   /* light sampling */
                 float x, y;
                 concentric_disk(u_l1, u_l2, &x, &y);

@@ -157,13 +157,21 @@ int ref_scene_add_sphere(void *h, const float o2w[12], const float w2o[12], floa
     return first;
 }
 
-// pbrt's partial sphere ("zmin" / "zmax"; phimax stays 360)
-int ref_scene_add_sphere_ex(void *h, const float o2w[12], const float w2o[12], float radius, float zmin, float zmax) {
+// pbrt's partial sphere ("zmin" / "zmax" / "phimax") and partial disk ("phimax")
+int ref_scene_add_disk_ex(void *h, const float o2w[12], const float w2o[12], float height, float radius, float inner, float phimax) {
     RefScene *s = (RefScene *)h;
     Transform *t, *ti;
     make_xforms(s, o2w, w2o, &t, &ti);
     int first = (int)s->shapes.size();
-    s->push(new Sphere(t, ti, false, radius, zmin, zmax, 360.f));
+    s->push(new Disk(t, ti, false, height, radius, inner, phimax));
+    return first;
+}
+int ref_scene_add_sphere_ex(void *h, const float o2w[12], const float w2o[12], float radius, float zmin, float zmax, float phimax) {
+    RefScene *s = (RefScene *)h;
+    Transform *t, *ti;
+    make_xforms(s, o2w, w2o, &t, &ti);
+    int first = (int)s->shapes.size();
+    s->push(new Sphere(t, ti, false, radius, zmin, zmax, phimax));
     return first;
 }
 

@@ -55,13 +55,14 @@ public:
     static bool clipped(const Sphere *s) { return s->zmin > -s->radius || s->zmax < s->radius; }
     static float zmin(const Sphere *s) { return s->zmin; }
     static float zmax(const Sphere *s) { return s->zmax; }
-    static bool partialPhi(const Sphere *s) { return s->phiMax < 2.f * M_PI; }
+    static float phiMaxDeg(const Sphere *s) { return s->phiMax >= 2.f * (float)M_PI ? 360.f : s->phiMax * (180.f / (float)M_PI); }
 };
 class CudaDisk {
 public:
     static float height(const Disk *d) { return d->height; }
     static float radius(const Disk *d) { return d->radius; }
     static float inner(const Disk *d) { return d->innerRadius; }
+    static float phiMaxDeg(const Disk *d) { return d->phiMax >= 2.f * (float)M_PI ? 360.f : d->phiMax * (180.f / (float)M_PI); }
 };
 class CudaLight {
 public:
@@ -220,8 +221,9 @@ int CudaRender::submit(const ShapeRec &r, const Transform *extra, int lightIndex
             m34(t.GetMatrix(), o2w); m34(t.GetInverseMatrix(), w2o);
         }
         if (r.kind == 1 && r.clipped)
-            check(b2rt_add_sphere_ex(ctx_, o2w, w2o, r.radius, r.height, r.inner, r.material, al, &prim), "b2rt_add_sphere_ex");
+            check(b2rt_add_sphere_ex(ctx_, o2w, w2o, r.radius, r.height, r.inner, r.phimax, r.material, al, &prim), "b2rt_add_sphere_ex");
         else if (r.kind == 1) check(b2rt_add_sphere(ctx_, o2w, w2o, r.radius, r.material, al, &prim), "b2rt_add_sphere");
+        else if (r.clipped) check(b2rt_add_disk_ex(ctx_, o2w, w2o, r.height, r.radius, r.inner, r.phimax, r.material, al, &prim), "b2rt_add_disk_ex");
         else check(b2rt_add_disk(ctx_, o2w, w2o, r.height, r.radius, r.inner, r.material, al, &prim), "b2rt_add_disk");
     }
     return prim;
@@ -234,7 +236,7 @@ void CudaRender::createCudaShape(const std::string &name, Reference<Shape> &shap
                                  int lightIndex) {
     ShapeRec r;
     r.radius = r.height = r.inner = 0.f;
-    r.reverse = false; r.clipped = false;
+    r.reverse = false; r.clipped = false; r.phimax = 360.f;
     if (name == "trianglemesh") {
         const TriangleMesh *m = static_cast<const TriangleMesh *>(shape.GetPtr());
         r.kind = 0;
@@ -259,14 +261,18 @@ void CudaRender::createCudaShape(const std::string &name, Reference<Shape> &shap
     } else if (name == "sphere") {
         const Sphere *s = static_cast<const Sphere *>(shape.GetPtr());
         r.kind = 1; r.radius = CudaSphere::radius(s);
-        r.clipped = CudaSphere::clipped(s);                // zmin / zmax are honoured (b2rt_add_sphere_ex)
+        r.phimax = CudaSphere::phiMaxDeg(s);               // zmin / zmax / phimax are honoured (b2rt_add_sphere_ex)
+        r.clipped = CudaSphere::clipped(s) || r.phimax < 360.f;
         r.height = CudaSphere::zmin(s); r.inner = CudaSphere::zmax(s);
-        if (CudaSphere::partialPhi(s))
-            Warning("CudaRender: \"phimax\" of a partial sphere is ignored (full turn), like the reference's device code "
-                    "(cuda_render/util/shape/cudasphere.cu:27-72)");
     } else if (name == "disk") {
         const Disk *d = static_cast<const Disk *>(shape.GetPtr());
         r.kind = 2; r.radius = CudaDisk::radius(d); r.height = CudaDisk::height(d); r.inner = CudaDisk::inner(d);
+        r.phimax = CudaDisk::phiMaxDeg(d);
+        if (r.phimax < 360.f && lightIndex >= 0) {
+            Warning("CudaRender: \"phimax\" of a disk that is an area light is ignored (full disk)");
+            r.phimax = 360.f;
+        }
+        r.clipped = r.phimax < 360.f;
     } else {
         Warning("CudaRender: shape \"%s\" is not supported by the CUDA renderer, skipped", name.c_str());
         return;

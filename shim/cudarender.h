@@ -62,7 +62,8 @@ private:
         std::vector<float> P; std::vector<int> idx;
         std::vector<float> N, uv;     // per-vertex world-space normals / uv of a mesh (empty: none)
         bool reverse;                 // ReverseOrientation ^ TransformSwapsHandedness
-        bool clipped;                 // sphere with zmin / zmax (kept in height / inner)
+        bool clipped;                 // sphere with zmin / zmax (kept in height / inner) or phimax; disk with phimax
+        float phimax;                 // degrees
         float o2w[12], w2o[12], radius, height, inner;
         int material;
     };

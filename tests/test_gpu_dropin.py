@@ -219,16 +219,19 @@ def test_dropin_object_instances_photonmap(tmp_path):
 
 @pytest.mark.skipif(not os.path.exists(BIN), reason="shim/_build/pbrt_b2rt not built (needs /root/reference)")
 def test_dropin_partial_sphere(tmp_path):
-    """`Shape "sphere" "float zmax"`: a bowl open towards the camera.  The reference's device code renders the full sphere;
-    the drop-in passes zmin / zmax on (b2rt_add_sphere_ex) and must match pbrt's CPU image, inside of the bowl included."""
+    """`Shape "sphere" "float zmax" "float phimax"` (a bowl with a slice cut out, open towards the camera) and a 250-degree ring
+    (`Shape "disk" "float phimax"`).  The reference's device code renders the full shapes; the drop-in passes zmin / zmax /
+    phimax on (b2rt_add_sphere_ex, b2rt_add_disk_ex) and must match pbrt's CPU image, inside of the bowl included."""
     integ = 'SurfaceIntegrator "directlighting" "integer maxdepth" [5]'
     bowl = "\n".join(['AttributeBegin', '  Material "matte" "rgb Kd" [0.7 0.5 0.2]', '  Translate 0 0.7 0', '  Rotate -60 1 0 0',
-                      '  Shape "sphere" "float radius" [0.6] "float zmax" [0.15]', 'AttributeEnd'])
+                      '  Shape "sphere" "float radius" [0.6] "float zmax" [0.15] "float phimax" [300]', 'AttributeEnd',
+                      'AttributeBegin', '  Material "matte" "rgb Kd" [0.2 0.4 0.7]', '  Translate -0.55 1.4 -0.2', '  Rotate 60 1 0 0',
+                      '  Shape "disk" "float radius" [0.35] "float innerradius" [0.1] "float phimax" [250]', 'AttributeEnd'])
     desc = S.cornell_scene(spheres=False)
     gpu, cpu = _run(tmp_path, "bowl", integ, "simple", spp=256, res=96, desc=desc, extra_world=bowl)
     m = S.image_metrics(_block(gpu, 4), _block(cpu, 4))
     assert abs(m["bias_rel"]) < 0.005 and m["mean_rel"] < 0.015, m
-    full = bowl.replace(' "float zmax" [0.15]', "")
+    full = bowl.replace(' "float zmax" [0.15] "float phimax" [300]', "")
     _, cpu_full = _run(tmp_path, "ball", integ, "simple", spp=64, res=96, desc=desc, extra_world=full)
     mf = S.image_metrics(_block(gpu, 4), _block(cpu_full, 4))
     assert mf["mean_rel"] > 3 * m["mean_rel"], (m, mf)                 # and it is not the full sphere

@@ -322,8 +322,8 @@ def test_chunked_host_path_with_ragged_tail(ctx):
 
 # ---- partial spheres (pbrt "zmin" / "zmax") ---------------------------------------------------------------------------
 def test_partial_spheres_bit_exact_vs_oracle_and_pbrt_golden(built):
-    """b2rt_add_sphere_ex: Sphere::Intersect's zmin / zmax clipping (shapes/sphere.cpp:92-106; the reference's device
-    program ignores it).  GPU == C port bit for bit; C port == pbrt's own hits (tests/test_oracle_cpu.py + here)."""
+    """b2rt_add_sphere_ex / b2rt_add_disk_ex: zmin / zmax / phimax clipping (shapes/sphere.cpp:84-106, disk.cpp:73-76; the
+    reference's device programs ignore them).  GPU == C port bit for bit; C port == pbrt's own hits (tests/test_oracle_cpu.py + here)."""
     import make_golden_partial as GP
     r = GP.rays()
     ps = O.PortScene()
@@ -341,10 +341,10 @@ def test_partial_spheres_bit_exact_vs_oracle_and_pbrt_golden(built):
     assert np.array_equal(occ, (ep >= 0).astype(np.uint8))
     g = load_golden("partial_spheres")
     same = hits["t"].view(np.uint32) == g["t"].view(np.uint32)
-    assert (~same).sum() <= 2 and (hits["prim"][same] != g["prim"][same]).sum() <= 2
+    assert (~same).sum() <= 4 and (hits["prim"][same] != g["prim"][same]).sum() <= 2
     # rays that enter through the cut see the INSIDE of the sphere: the hit is the far root, the normal still points outwards
     nprims = ep.max() + 1
-    inside = (ep >= nprims - 4) & (np.einsum("ij,ij->i", s["n"], r[:, 4:7]) > 0)
+    inside = (ep >= nprims - 6) & (ep < nprims - 1) & (np.einsum("ij,ij->i", s["n"], r[:, 4:7]) > 0)
     assert inside.sum() > 100
 
 
