@@ -202,7 +202,7 @@ struct b2rt_ctx {
     DevBuf d_leaf_box;      // float[6*n] per-prim AABB (prim id order)
     DevBuf d_scene_box;     // uint32[12]: centroid bounds + scene bounds as ordered ints
     DevBuf d_keys, d_vals, d_keys_alt, d_vals_alt, d_hist;  // sort
-    DevBuf d_bin_parent, d_bin_child, d_bin_box, d_bin_flag, d_bin_cost, d_bin_count;
+    DevBuf d_bin_parent, d_bin_child, d_bin_box, d_bin_flag, d_bin_cost, d_bin_count, d_bin_info;
     DevBuf d_wide_tmp, d_wide_flag, d_wide_index, d_queue_a, d_queue_b, d_counters;
     DevBuf d_wide_nodes, d_prim_recs, d_leaf_prims;
     DevBuf d_rays, d_hits, d_occ;  // staging for host-pointer calls

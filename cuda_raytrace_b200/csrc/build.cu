@@ -219,7 +219,7 @@ __global__ void __launch_bounds__(256)
 refit_kernel(const float *__restrict__ leaf_box, const uint32_t *__restrict__ vals, int n,
              const int32_t *__restrict__ parent, const int32_t *__restrict__ child,
              const int2 *__restrict__ range, float *box, float *cost, uint32_t *flag,
-             uint8_t *__restrict__ collapse) {
+             uint8_t *__restrict__ collapse, int4 *__restrict__ info) {
     int j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= n) return;
     int node = (n - 1) + j;
@@ -263,6 +263,8 @@ refit_kernel(const float *__restrict__ leaf_box, const uint32_t *__restrict__ va
         collapse[cur] = col ? 1 : 0;
         c_me = col ? c_leaf : c_int;
         cost[cur] = c_me;
+        // everything the wide collapse needs to know about this node in one 16-byte record
+        info[cur] = make_int4(ch.x, ch.y, __float_as_int(area), col ? 0 : 1);
         node = cur;
         cur = up;
     }
@@ -285,8 +287,7 @@ __device__ __forceinline__ bool is_openable(int node, int n, const uint8_t *coll
 // ctl[0 .. 2] = queue sizes of levels L, L + 1, L + 2 in rotation (the third one is zeroed while level L runs, so one
 // grid.sync per level is enough), ctl[5] = number of levels
 __global__ void __launch_bounds__(256)
-wide_collapse_coop_kernel(int n, const int32_t *__restrict__ child, const float *__restrict__ box,
-                          const uint8_t *__restrict__ collapse, WideTmp *__restrict__ tmp,
+wide_collapse_coop_kernel(int n, const int4 *__restrict__ info, WideTmp *__restrict__ tmp,
                           uint32_t *__restrict__ wide_flag, int32_t *qa, int32_t *qb, uint32_t *ctl) {
     cg::grid_group grid = cg::this_grid();
     const int lane = threadIdx.x & 31;
@@ -304,31 +305,50 @@ wide_collapse_coop_kernel(int n, const int32_t *__restrict__ child, const float 
         for (int64_t w = (int64_t)blockIdx.x * blockDim.x + (threadIdx.x & ~31); w < (int64_t)nq; w += gsize) {
             const int64_t qi = w + lane;
             int open[4], no = 0;
+            bool live = false;
             if (qi < (int64_t)nq) {
                 const int root = qin[qi];
-                int c[4]; int m = 2;
-                c[0] = child[2 * root]; c[1] = child[2 * root + 1]; c[2] = -1; c[3] = -1;
-                while (m < 4) {
-                    int best = -1; float best_area = -1.f;
-                    for (int k = 0; k < m; ++k) {
-                        if (!is_openable(c[k], n, collapse)) continue;
-                        float a = box_area(box + 6 * (int64_t)c[k]);
-                        if (a > best_area) { best_area = a; best = k; }   // first max wins: deterministic
+                // node record {left, right, bits(area), openable} written by the refit: the chain of dependent loads per
+                // level is queue -> record of the root -> records of its two children -> records of the two children of
+                // the first node opened (was: queue -> children -> collapse flags -> boxes -> children -> flags -> boxes ...)
+                const int4 ri = __ldcg(info + root);
+                if (ri.w) {                                 // the queue may hold collapsed nodes: they are pushed unseen
+                    live = true;
+                    int c[4], kl[4], kr[4], op[4]; float ar[4];
+                    auto fetch = [&](int k) {
+                        op[k] = 0; kl[k] = -1; kr[k] = -1; ar[k] = 0.f;
+                        if (c[k] < n - 1) {
+                            const int4 t = __ldcg(info + c[k]);
+                            kl[k] = t.x; kr[k] = t.y; ar[k] = __int_as_float(t.z); op[k] = t.w;
+                        }
+                    };
+                    int m = 2;
+                    c[0] = ri.x; c[1] = ri.y; c[2] = -1; c[3] = -1;
+                    fetch(0); fetch(1);
+                    op[2] = op[3] = 0; kl[2] = kl[3] = kr[2] = kr[3] = -1; ar[2] = ar[3] = 0.f;
+                    while (m < 4) {
+                        int best = -1; float best_area = -1.f;
+                        for (int k = 0; k < m; ++k)
+                            if (op[k] && ar[k] > best_area) { best_area = ar[k]; best = k; }   // first max wins: deterministic
+                        if (best < 0) break;
+                        const int l = kl[best], r = kr[best];
+                        // keep order: left child takes the slot, right child is inserted right after it
+                        for (int k = m; k > best + 1; --k) { c[k] = c[k - 1]; kl[k] = kl[k - 1]; kr[k] = kr[k - 1]; op[k] = op[k - 1]; ar[k] = ar[k - 1]; }
+                        c[best] = l; c[best + 1] = r;
+                        ++m;
+                        if (m < 4) { fetch(best); fetch(best + 1); }
+                        else { op[best] = l < n - 1; op[best + 1] = r < n - 1; }     // not looked at: the next level filters them
                     }
-                    if (best < 0) break;
-                    int node = c[best];
-                    for (int k = m; k > best + 1; --k) c[k] = c[k - 1];
-                    c[best] = child[2 * node]; c[best + 1] = child[2 * node + 1];
-                    ++m;
-                }
-                WideTmp t;
+                    WideTmp t;
 #pragma unroll
-                for (int k = 0; k < 4; ++k) t.c[k] = c[k];
-                tmp[root] = t;
-                wide_flag[root] = 1u;
-                for (int k = 0; k < m; ++k)
-                    if (is_openable(c[k], n, collapse)) open[no++] = c[k];
+                    for (int k = 0; k < 4; ++k) t.c[k] = c[k];
+                    tmp[root] = t;
+                    wide_flag[root] = 1u;
+                    for (int k = 0; k < m; ++k)
+                        if (op[k]) open[no++] = c[k];
+                }
             }
+            if (__any_sync(0xffffffffu, live) && lane == 0) atomicMax(&ctl[6], (uint32_t)levels);
             // one atomic per warp: exclusive prefix of the lanes' child counts
             int inc = no;
 #pragma unroll
@@ -345,12 +365,13 @@ wide_collapse_coop_kernel(int n, const int32_t *__restrict__ child, const float 
         cur ^= 1;
         grid.sync();
     }
-    if (blockIdx.x == 0 && threadIdx.x == 0) ctl[5] = (uint32_t)levels;
+    grid.sync();
+    if (blockIdx.x == 0 && threadIdx.x == 0) ctl[5] = ((volatile uint32_t *)ctl)[6];      // levels that opened a node
 }
 __global__ void wide_collapse_init_kernel(int32_t *qa, uint32_t *ctl, const uint8_t *collapse) {
     // queue A = {root 0} unless the whole tree collapsed into one leaf (then there is nothing to do)
     const bool any = !collapse[0];
-    ctl[0] = any ? 1u : 0u; ctl[1] = 0u; ctl[2] = 0u; ctl[5] = 0u;
+    ctl[0] = any ? 1u : 0u; ctl[1] = 0u; ctl[2] = 0u; ctl[5] = 0u; ctl[6] = 0u;
     if (any) qa[0] = 0;
 }
 
@@ -545,6 +566,7 @@ int b2rt_build_impl(b2rt_ctx *ctx) {
     B2RT_CUDA(ctx, ctx->d_bin_count.reserve((size_t)nn * sizeof(int2)));   // ranges
     B2RT_CUDA(ctx, ctx->d_bin_box.reserve((size_t)(2 * nn) * 6 * sizeof(float)));
     B2RT_CUDA(ctx, ctx->d_bin_cost.reserve((size_t)(2 * nn) * sizeof(float)));
+    B2RT_CUDA(ctx, ctx->d_bin_info.reserve((size_t)nn * sizeof(int4)));      // {left, right, area, openable} per internal node
     B2RT_CUDA(ctx, ctx->d_bin_flag.reserve((size_t)nn * 5));               // uint32 flag + uint8 collapse
     B2RT_CUDA(ctx, ctx->d_wide_tmp.reserve((size_t)nn * sizeof(WideTmp)));
     B2RT_CUDA(ctx, ctx->d_wide_flag.reserve((size_t)nn * 4));
@@ -611,7 +633,7 @@ int b2rt_build_impl(b2rt_ctx *ctx) {
             karras_topology_kernel<<<(n - 1 + 255) / 256, 256, 0, st>>>(keys, n, parent, child, range);
             B2RT_LAUNCH_CHECK(ctx);
             refit_kernel<<<grid, 256, 0, st>>>(leaf_box, vals, n, parent, child, range, bin_box, cost, flag,
-                                               collapse);
+                                               collapse, ctx->d_bin_info.as<int4>());
             B2RT_LAUNCH_CHECK(ctx);
             // greedy collapse to 4-wide nodes: one persistent launch over a device-side queue, the node order from a
             // prefix sum over wide_flag; then ONE host read for everything the host needs (root collapsed?, node count,
@@ -637,8 +659,8 @@ int b2rt_build_impl(b2rt_ctx *ctx) {
                 if (blocks > want) blocks = want;
                 WideTmp *wtmp = ctx->d_wide_tmp.as<WideTmp>();
                 int nn_ = n;
-                const int32_t *child_ = child; const float *box_ = bin_box; const uint8_t *col_ = collapse;
-                void *args[] = {&nn_, &child_, &box_, &col_, &wtmp, &wide_flag, &qa, &qb, &ctl};
+                const int4 *info_ = ctx->d_bin_info.as<int4>();
+                void *args[] = {&nn_, &info_, &wtmp, &wide_flag, &qa, &qb, &ctl};
                 B2RT_CUDA(ctx, cudaLaunchCooperativeKernel((const void *)wide_collapse_coop_kernel, dim3((unsigned)blocks), dim3(256), args, 0, st));
                 B2RT_LAUNCH_CHECK(ctx);
             }
