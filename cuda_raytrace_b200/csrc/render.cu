@@ -20,6 +20,13 @@
 namespace {
 
 constexpr int RENDER_THREADS = 128;
+// Resident blocks per SM the camera-pass kernel is compiled for.  Left to itself ptxas gives it 128 registers (4 blocks) and
+// still spills 258 bytes; capped at 80 registers (6 blocks) it spills more (354 B) and is faster all the same -- the kernel
+// lives on latency hiding: Cfg4 frame (8 M triangles, 4K, 16 spp) 37.3 -> 33.2 ms, Cfg3 camera pass 16.9 -> 16.7 ms; 3 / 5 / 7 /
+// 8 blocks: 40.0 / 34.3 / 33.6 / 33.8 ms (profiles/r07q_render_blocks_ab.txt).
+#ifndef B2RT_RENDER_BLOCKS
+#define B2RT_RENDER_BLOCKS 6
+#endif
 constexpr int MAX_TREE_DEPTH = 8;
 
 // ---- K14 image-plane sample patterns: where inside its pixel sample k lies ------------------------------------------
@@ -185,7 +192,7 @@ struct TreeNode { f3 o, d; float tmin; f3 T; int depth; uint32_t id; };
 
 // K14 + K6 + K7.  sample s (chunk-local) -> pixel (crop-window row-major) and sample number k.
 template <bool INST>
-__global__ void __launch_bounds__(RENDER_THREADS)
+__global__ void __launch_bounds__(RENDER_THREADS, B2RT_RENDER_BLOCKS)
 render_li_kernel(DScene sc, b2rt_camera cam, b2rt_frame_params fp, uint32_t seed_lo, uint32_t seed_hi, int64_t first_sample,
                  int64_t n_samples, int slots, float *__restrict__ sample_rgb, b2rt_query *__restrict__ qslots,
                  uint32_t *__restrict__ qcnt, uint32_t *status, float2 *__restrict__ sample_xy, SamplerD sm,
