@@ -104,8 +104,13 @@ photon_trace_kernel(DScene sc, uint32_t seed_lo, uint32_t seed_hi, int64_t first
 // atomicAdd per warp) and emit there, so the traversal and shading of an iteration run with (nearly) all 32 lanes
 // instead of the lanes that happen to survive to bounce b.  A path's randomness and its slot row depend only on its
 // index, so the output is byte-identical to photon_trace_kernel.
+// resident blocks per SM the kernel is compiled for: 8 (64 registers, 44 B of spills) instead of ptxas' own 80 registers --
+// Cfg3 shoot 10.5 -> 10.1 ms; 5 / 7 / 9 / 10 / 12 blocks: 11.1 / 10.4 / 10.1 / 10.4 / 10.6 ms (r07t, r07u)
+#ifndef B2RT_PHOTON_BLOCKS
+#define B2RT_PHOTON_BLOCKS 8
+#endif
 template <bool INST>
-__global__ void __launch_bounds__(PHOTON_THREADS)
+__global__ void __launch_bounds__(PHOTON_THREADS, B2RT_PHOTON_BLOCKS)
 photon_trace_regen_kernel(DScene sc, uint32_t seed_lo, uint32_t seed_hi, int64_t first_path, int64_t n_paths,
                           int max_depth, int flags, b2rt_photon *__restrict__ slots, uint32_t *__restrict__ cnt_c,
                           uint32_t *__restrict__ cnt_i, unsigned long long *pool, uint32_t *status) {
