@@ -17,6 +17,9 @@
 
 namespace {
 
+#ifndef B2RT_GATHER_BLOCKS
+#define B2RT_GATHER_BLOCKS 7
+#endif
 constexpr int GATHER_WARPS = 4;
 constexpr int GATHER_CAP = 256;          // candidate buffer entries per warp (k <= GATHER_CAP - 32)
 constexpr int GATHER_PER_LANE = GATHER_CAP / 32;
@@ -939,7 +942,7 @@ int b2rt_gather_impl(b2rt_ctx *ctx, int map, int64_t nq, const b2rt_query *d_que
         if (k > 0 && ctx->gather_variant >= 2) {
             const int qt = ctx->gather_qt == 32 ? 32 : (ctx->gather_qt == 16 ? 16 : 8);
             // default: 1024-position tile, 7 blocks per SM (r01z sweep: camera pass 15.9 ms against 17.2 ms with 2048 / 5)
-            void (*kern)(const GatherArgs) = gather_block_kernel<8, 1024, 7>;
+            void (*kern)(const GatherArgs) = gather_block_kernel<8, 1024, B2RT_GATHER_BLOCKS>;
             if (qt == 32) kern = gather_block_kernel<32, 2048, 5>;
             else if (qt == 16) kern = gather_block_kernel<16, 2048, 5>;
             else if (ctx->gather_tcap == 2048) kern = gather_block_kernel<8, 2048, 5>;
