@@ -54,6 +54,13 @@ trace_kernel(const WideNode *__restrict__ nodes, const PrimRec *__restrict__ rec
 // Results are identical to trace_kernel by construction: the winner is (min t, then min prim id), independent of
 // the visiting order.
 constexpr int PT_THREADS = 128;
+#ifndef B2RT_TRACE_BLOCKS_CLOSEST
+#define B2RT_TRACE_BLOCKS_CLOSEST 7      // resident blocks per SM the speculative kernel is compiled for (72 / 64 registers);
+                                         // re-checked r08e: 6 / 7 -> 6711, 8 / 9 -> 6511, 9 / 10 -> 6177 against 6843 Mrays/s
+#endif
+#ifndef B2RT_TRACE_BLOCKS_ANY
+#define B2RT_TRACE_BLOCKS_ANY 8
+#endif
 constexpr int PT_SSTACK = 12;
 
 template <bool ANY, bool INST>
@@ -220,7 +227,7 @@ trace_persistent_kernel(const WideNode *__restrict__ nodes, const PrimRec *__res
 // ALU pipe (min / max, selects, compares) is the busiest pipe of this kernel, 48 / 54 % of its peak at 18 / 21.6 active
 // threads per instruction.
 template <bool ANY, int SORT, bool PL, bool INST>
-__global__ void __launch_bounds__(PT_THREADS, ANY ? 8 : 7)
+__global__ void __launch_bounds__(PT_THREADS, ANY ? B2RT_TRACE_BLOCKS_ANY : B2RT_TRACE_BLOCKS_CLOSEST)
 trace_spec_kernel(const WideNode *__restrict__ nodes, const PrimRec *__restrict__ recs,
                   const AnalyticPrim *__restrict__ analytic, const b2rt_ray *__restrict__ rays,
                   b2rt_hit *__restrict__ hits, uint8_t *__restrict__ occ, int64_t nrays,
