@@ -93,7 +93,7 @@ struct b2rt_multi {
     // camera pass: per device pixel lists of the last (xres, yres, window) and the frame on GPU 0
     std::vector<DevBuf *> pixmaps;
     std::vector<int64_t> pixmap_n;
-    int pm_xres = 0, pm_yres = 0, pm_win[4] = {0, 0, 0, 0};
+    int pm_xres = 0, pm_yres = 0, pm_win[4] = {0, 0, 0, 0}, pm_tile = 0;
     DevBuf *frame0 = nullptr;       // whole image on device 0
     std::vector<DevBuf *> bands;    // per-device band buffers (filtered frames)
 };
@@ -546,8 +546,14 @@ int b2rt_multi_film_set_filter(b2rt_multi *m, const b2rt_filter *filter) {
 }
 
 // 64 x 64 tiles of the crop window, tile t -> GPU t mod G; per GPU the pixels tile after tile, row-major inside a tile
+// tile edge in pixels: 64; B2RT_MGPU_TILE = 16 / 32 / 64 / 128 for A/B runs of the load balance
+static int tile_edge() {
+    int T = 64;
+    if (const char *v = getenv("B2RT_MGPU_TILE")) { const int t = atoi(v); if (t == 16 || t == 32 || t == 64 || t == 128) T = t; }
+    return T;
+}
 static void tile_pixel_lists(int G, const b2rt_frame_params *fp, std::vector<std::vector<uint32_t>> &lists) {
-    const int T = 64;
+    const int T = tile_edge();
     lists.assign(G, {});
     const int ntx = (fp->x1 - fp->x0 + T - 1) / T, nty = (fp->y1 - fp->y0 + T - 1) / T;
     for (int ty = 0; ty < nty; ++ty)
@@ -579,11 +585,28 @@ int b2rt_multi_render_frame(b2rt_multi *m, const b2rt_camera *cam, const b2rt_fr
     if (!filtered && (m->peer || G == 1)) {
         // ---- tiles: every GPU renders its pixel list, pixels land in the whole image on GPU 0 -----------------------
         if (m->frame0->reserve(full_bytes) != cudaSuccess) { m->err = "multi_render_frame: out of memory on GPU 0"; return B2RT_E_CUDA; }
-        const bool fresh = m->pm_xres != cam->xres || m->pm_yres != cam->yres || m->pm_win[0] != fp->x0 || m->pm_win[1] != fp->x1 ||
+        const bool fresh = m->pm_tile != tile_edge() || m->pm_xres != cam->xres || m->pm_yres != cam->yres || m->pm_win[0] != fp->x0 || m->pm_win[1] != fp->x1 ||
                            m->pm_win[2] != fp->y0 || m->pm_win[3] != fp->y1;
         std::vector<std::vector<uint32_t>> lists;
         if (fresh) tile_pixel_lists(G, fp, lists);
         float *full = m->frame0->as<float>();
+        // Whole image into page-locked host memory (b2rt_host_alloc, cudaHostAlloc, cudaHostRegister: portable and mapped
+        // under unified addressing): every GPU stores its pixels straight into the caller's buffer over its own PCIe link
+        // instead of GPU 0 collecting the frame and downloading 12 B / pixel in one serial copy at the end.  Same bytes.
+        // Measured on the Cfg3 camera pass (r08i / r08j): 8 GPUs 3.39 -> 3.00 ms, 4 GPUs 5.18 -> 4.97, 2 GPUs 9.08 -> 9.18,
+        // 1 GPU 16.73 -> 17.38 (one GPU's 12-byte stores over one PCIe link lose against one DMA copy): on from 4 GPUs.
+        // B2RT_MGPU_HOSTFRAME=0 / 1 forces it off / on (A/B).
+        bool direct = false;
+        if (where == B2RT_HOST && cw == cam->xres && chh == cam->yres) {
+            const char *e = getenv("B2RT_MGPU_HOSTFRAME");
+            const bool want = e ? atoi(e) != 0 : G >= 4;
+            cudaPointerAttributes at;
+            if (want && cudaPointerGetAttributes(&at, out_rgb) == cudaSuccess && at.type == cudaMemoryTypeHost && at.devicePointer) {
+                full = static_cast<float *>(at.devicePointer);
+                direct = true;
+            }
+            cudaGetLastError();
+        }
         rc = parallel(m, [&](int i) -> int {
             b2rt_ctx *c = m->ctx[i];
             if (fresh) {
@@ -597,13 +620,15 @@ int b2rt_multi_render_frame(b2rt_multi *m, const b2rt_camera *cam, const b2rt_fr
             return b2rt_sync(c);                 // also reports a traversal-stack overflow
         });
         if (rc) return rc;
-        m->pm_xres = cam->xres; m->pm_yres = cam->yres;
+        m->pm_xres = cam->xres; m->pm_yres = cam->yres; m->pm_tile = tile_edge();
         m->pm_win[0] = fp->x0; m->pm_win[1] = fp->x1; m->pm_win[2] = fp->y0; m->pm_win[3] = fp->y1;
         // the crop window out of the whole image (row pitch xres -> cw)
-        const float *src = full + 3 * ((size_t)fp->y0 * cam->xres + fp->x0);
-        B2RT_CUDA(c0, cudaMemcpy2DAsync(out_rgb, (size_t)cw * 12, src, (size_t)cam->xres * 12, (size_t)cw * 12, chh,
-                                        where == B2RT_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, c0->stream));
-        B2RT_CUDA(c0, cudaStreamSynchronize(c0->stream));
+        if (!direct) {
+            const float *src = full + 3 * ((size_t)fp->y0 * cam->xres + fp->x0);
+            B2RT_CUDA(c0, cudaMemcpy2DAsync(out_rgb, (size_t)cw * 12, src, (size_t)cam->xres * 12, (size_t)cw * 12, chh,
+                                            where == B2RT_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, c0->stream));
+            B2RT_CUDA(c0, cudaStreamSynchronize(c0->stream));
+        }
     } else {
         // ---- bands: one row band of the crop window per GPU through the crop-window path (halo cells re-traced) --------
         if (m->frame0->reserve(crop_bytes) != cudaSuccess) { m->err = "multi_render_frame: out of memory on GPU 0"; return B2RT_E_CUDA; }

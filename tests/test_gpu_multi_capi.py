@@ -150,3 +150,24 @@ def test_multi_resize_copies_objects_and_instances(built):
         m.grid_build(1)
         assert np.array_equal(m.render_frame(cam, spp=2, nused=30, max_dist=0.5), img)
         assert img.mean() > 1e-3
+
+
+def test_multi_frame_straight_into_pinned_host_memory(single, monkeypatch):
+    """a whole frame asked for in page-locked host memory is stored there by the GPUs themselves (no collection on GPU 0,
+    no final download); the bytes are those of the staged path (B2RT_MGPU_HOSTFRAME=0) and of a pageable output buffer"""
+    desc, cam, ref = single
+    with b2rt.MultiContext(3, seed=3, devices=[0, 0, 0]) as m:
+        m.fill(lambda c: S.fill_scene(c, desc))
+        m.build_accel()
+        m.photons_trace(0, N_PATHS)
+        m.grid_build(0); m.grid_build(1)
+        pin = m.ctxs[0].pinned_empty((cam.yres, cam.xres, 3))
+        pin[:] = -1.0
+        monkeypatch.setenv("B2RT_MGPU_HOSTFRAME", "1")            # default: on from 4 GPUs
+        got = m.render_frame(cam, spp=2, nused=40, max_dist=0.15, out=pin)
+        assert got is pin and np.array_equal(pin, ref["box"])
+        monkeypatch.setenv("B2RT_MGPU_HOSTFRAME", "0")
+        pin[:] = -1.0
+        m.render_frame(cam, spp=2, nused=40, max_dist=0.15, out=pin)
+        assert np.array_equal(pin, ref["box"])
+        assert np.array_equal(m.render_frame(cam, spp=2, nused=40, max_dist=0.15), ref["box"])

@@ -23,6 +23,7 @@ for job in "$@"; do
     ncutrace) python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-photon-extra > $O/plain_bench.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:trace_spec -s 8 -c 2 -f -o $O/trace_full python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-photon-extra > $O/ncu_trace.log 2>&1 ;;
     launchbench) python bench.py --steps 5 --warmup 3 --no-cpu-baseline > $O/plain_bench_short.json 2> $O/plain_bench_short.err && timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-file $O/launches_bench.csv python bench.py --steps 5 --warmup 3 --no-cpu-baseline > $O/ncu_launches_bench.log 2>&1 ;;
     instances) timeout 500 python tools/bench_instances.py 1000 20000 > $O/bench_instances_1000x20k.jsonl 2> $O/bench_instances.err ;;
+    tiles:*)  timeout 600 python tools/bench_tiles.py ${job#tiles:} > $O/tiles_n${job#tiles:}.jsonl 2> $O/tiles.err ;;
     sanmem)   python -c "import __graft_entry__ as g; g.smoke()" > $O/plain_smoke.log 2>&1 && timeout 1500 compute-sanitizer --tool memcheck --log-file $O/sanitizer_memcheck.txt python -c "import __graft_entry__ as g; g.smoke()" > $O/san_memcheck_run.log 2>&1; echo "rc=$?" >> $O/san_memcheck_run.log ;;
     sanrace)  python -c "import __graft_entry__ as g; g.smoke()" > $O/plain_smoke.log 2>&1 && timeout 1500 compute-sanitizer --tool racecheck --log-file $O/sanitizer_racecheck.txt python -c "import __graft_entry__ as g; g.smoke()" > $O/san_racecheck_run.log 2>&1; echo "rc=$?" >> $O/san_racecheck_run.log ;;
     saninit)  python -c "import __graft_entry__ as g; g.smoke()" > $O/plain_smoke.log 2>&1 && timeout 1500 compute-sanitizer --tool initcheck --log-file $O/sanitizer_initcheck.txt python -c "import __graft_entry__ as g; g.smoke()" > $O/san_initcheck_run.log 2>&1; echo "rc=$?" >> $O/san_initcheck_run.log ;;
