@@ -239,3 +239,38 @@ def test_instanced_final_gathering_matches_flattened_scene(built):
     assert b[1] > 1000 and abs(a[1] - b[1]) <= 5.0 * np.sqrt(b[1]), (a[:2], b[:2])      # radiance photons
     assert np.isfinite(a[2]).all() and b[2].mean() > 1e-3
     assert abs(a[2].mean() - b[2].mean()) < 0.03 * b[2].mean(), (a[2].mean(), b[2].mean())
+
+
+def test_instances_only_scene_and_tiny_objects(built):
+    """edge cases of the two-level build: a world that holds nothing but instances, an object of ONE triangle (single-node
+    tree), an object of one analytic sphere, and an identity instance that must return the bits of the plain mesh"""
+    P, idx = S.heightfield_mesh(12, 12, None, seed=4)
+    ident = S.xf_translate(0.0, 0.0, 0.0)
+    tri_P = np.float32([[-0.5, 0.9, -0.5], [0.5, 0.9, -0.5], [0.0, 0.9, 0.6]])
+    r = np.concatenate([S.pinhole_rays(64, 48, eye=(0.2, 3.0, 0.3), look=(0.0, 0.0, 0.0), up=(0, 0, 1)),
+                        S.incoherent_rays(4000, [-1.2, -0.5, -1.2], [1.2, 1.5, 1.2], seed=6)])
+    with b2rt.Context(0, seed=1) as c:
+        o_mesh = c.object_begin(); c.add_mesh(P, idx); c.object_end()
+        o_tri = c.object_begin(); c.add_mesh(tri_P, np.int32([[0, 1, 2]])); c.object_end()
+        o_sph = c.object_begin(); c.add_sphere(S.xf_translate(0.0, 0.0, 0.0)[0], 0.2); c.object_end()
+        k0 = c.add_instance(o_mesh, ident[0], w2o=ident[1])
+        k1 = c.add_instance(o_tri, ident[0], w2o=ident[1])
+        k2 = c.add_instance(o_sph, S.xf_translate(0.6, 1.3, 0.1)[0])
+        info = c.build_accel()
+        assert info.n_prims == 3
+        bases = [c.instance_info(k)[0] for k in (k0, k1, k2)]
+        assert bases == [3, 3 + len(idx), 3 + len(idx) + 1]
+        h2 = c.trace_closest(r)
+        o2 = c.trace_any(r)
+    with b2rt.Context(0, seed=1) as f:
+        f.add_mesh(P, idx)
+        f.add_mesh(tri_P, np.int32([[0, 1, 2]]))
+        f.add_sphere(S.xf_translate(0.6, 1.3, 0.1)[0], 0.2)
+        f.build_accel()
+        h1 = f.trace_closest(r)
+        o1 = f.trace_any(r)
+    mesh_or_tri = h1["prim"] <= len(idx)               # identity instances: the same bits as the plain shapes
+    assert np.array_equal(h1["t"][mesh_or_tri].view(np.uint32), h2["t"][mesh_or_tri].view(np.uint32))
+    assert np.array_equal(h1["prim"] + np.where(h1["prim"] >= 0, 3, 0), h2["prim"])
+    assert np.allclose(h1["t"], h2["t"], rtol=1e-5) and np.array_equal(o1, o2)
+    assert (h2["prim"] == 3 + len(idx)).sum() > 10 and (h2["prim"] == 3 + len(idx) + 1).sum() > 10
