@@ -23,8 +23,12 @@ constexpr int FG_NDIR = 50;              // nIndirSamplePhotons (photonmap.cpp:6
 // bounce order.  Same emission / bounce / roulette stream as photon_trace_kernel (photon.cu), so the paths are the very
 // paths whose caustic / indirect photons sit in maps 0 and 1; the radiance-photon draw is block 2 of the bounce counter,
 // which the path itself never reads.
+// 8 resident blocks per SM (64 registers) like photon_trace_regen_kernel: 2.45 -> 2.40 ms for 4 M paths (r08s)
+#ifndef B2RT_FGPHOTON_BLOCKS
+#define B2RT_FGPHOTON_BLOCKS 8
+#endif
 template <bool INST>
-__global__ void __launch_bounds__(FG_THREADS)
+__global__ void __launch_bounds__(FG_THREADS, B2RT_FGPHOTON_BLOCKS)
 fg_photon_kernel(DScene sc, uint32_t seed_lo, uint32_t seed_hi, int64_t first_path, int64_t n_paths, int max_depth,
                  b2rt_photon *__restrict__ slots, uint32_t *__restrict__ cnt_d, uint32_t *__restrict__ cnt_r, uint32_t *status,
                  int64_t lim_c, int64_t lim_i) {
@@ -368,6 +372,7 @@ final_gather_kernel(const FgArgs A) {
 // combine launch sums in the same butterfly order, so the output is bit-identical to the fused kernel (tested).
 //
 // launch 1: one thread per gather ray (ray i of the chunk = query i / R, ray i % R): direction, traversal, hit record
+// (ptxas' own 64 registers = 8 blocks per SM; 10 blocks measured slower, r08s)
 template <bool INST>
 __global__ void __launch_bounds__(FG_THREADS)
 fg_trace_kernel(const FgArgs A, int64_t nrays, int R) {
